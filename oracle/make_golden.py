@@ -1,0 +1,216 @@
+"""Mint golden fixtures by running the UNMODIFIED reference (authoring container only).
+
+TEST INFRASTRUCTURE ONLY.  Usage:  python -m oracle.make_golden
+Writes tests/golden/*.pt — seeded inputs plus the outputs (and input-gradients) that
+the reference's own functions return for them on CPU.  tests/test_oracle_golden.py
+checks oracle/muscle_oracle.py against these; the GPU parity tests check the CUDA path
+against the oracle and against these same files.
+"""
+import os
+import random
+import sys
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from oracle import reference_loader
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+def _blob_classes(b, h, w, n_cls, gen, smooth=7):
+    noise = torch.randn(b, n_cls, h, w, generator=gen)
+    noise = F.avg_pool2d(noise, smooth, 1, smooth // 2, count_include_pad=False)
+    return noise.argmax(1)
+
+
+def gen_info_nce(src):
+    out = {}
+    for dt, tag in ((torch.float32, "f32"), (torch.float64, "f64")):
+        g = torch.Generator().manual_seed(11)
+        q = F.normalize(torch.randn(64, 32, generator=g, dtype=dt), dim=1).requires_grad_()
+        p = F.normalize(torch.randn(16, 32, generator=g, dtype=dt), dim=1).requires_grad_()
+        k = F.normalize(torch.randn(96, 32, generator=g, dtype=dt), dim=1).requires_grad_()
+        loss = src.loss_multilabel.info_nce(q, p, k)
+        gq, gp, gk = torch.autograd.grad(loss, (q, p, k))
+        none = src.loss_multilabel.info_nce(q, p, k, temperature=0.07, reduction="none")
+        out[tag] = dict(q=q.detach(), p=p.detach(), k=k.detach(), loss=loss.detach(), gq=gq, gp=gp, gk=gk,
+                        none_t007=none.detach())
+    return out
+
+
+def gen_dense_infonce(src):
+    """The composition of SURVEY §8c evaluated with the reference primitive only."""
+    out = {}
+    for dt, tag in ((torch.float32, "f32"), (torch.float64, "f64")):
+        g = torch.Generator().manual_seed(23)
+        b, d, h, w, c = 2, 32, 12, 12, 5
+        cls = _blob_classes(b, h, w, c, g, smooth=5).reshape(-1)
+        cls[torch.rand(cls.shape, generator=g) < 0.05] = -1          # ignored pixels
+        x = torch.randn(b * h * w, d, generator=g, dtype=dt)
+        x = (x + 0.7 * torch.randn(c, d, generator=g, dtype=dt)[cls.clamp_min(0)]).requires_grad_()
+        e = F.normalize(x, dim=1)
+        valid = cls >= 0
+        per_query = []
+        for ci in sorted(set(cls[valid].tolist())):
+            sel = cls == ci
+            neg = valid & ~sel
+            per_query.append(src.loss_multilabel.info_nce(e[sel], e[sel], e[neg], temperature=0.1,
+                                                          reduction="none"))
+        loss = torch.cat(per_query).mean()
+        gx, = torch.autograd.grad(loss, x)
+        out[tag] = dict(x=x.detach(), cls=cls, loss=loss.detach(), gx=gx)
+    return out
+
+
+def gen_imc(src):
+    g = torch.Generator().manual_seed(5)
+    emb = torch.randn(8, 48, generator=g).abs().requires_grad_()
+    label = torch.zeros(8, 20)
+    sets = [[14], [14], [3], [3, 7], [14], [6], [14, 6], [2]]
+    for i, s in enumerate(sets):
+        label[i, s] = 1
+    loss = src.loss_multilabel.image_level_contrast(emb, label)
+    ge, = torch.autograd.grad(loss, emb)
+    # a batch where nothing qualifies -> python 0
+    label0 = torch.zeros(3, 20)
+    label0[:, 1] = 1
+    zero = src.loss_multilabel.image_level_contrast(torch.randn(3, 48, generator=g), label0)
+    g2 = torch.Generator().manual_seed(6)
+    emb2 = torch.randn(16, 384, generator=g2).abs().requires_grad_()
+    label2 = (torch.rand(16, 20, generator=g2) < 0.08).float()
+    label2[:, 14] = (torch.rand(16, generator=g2) < 0.4).float()
+    loss2 = src.loss_multilabel.image_level_contrast(emb2, label2)
+    ge2, = torch.autograd.grad(loss2, emb2) if torch.is_tensor(loss2) else (torch.zeros_like(emb2),)
+    return dict(emb=emb.detach(), label=label, loss=loss.detach(), ge=ge, zero_is_tensor=torch.is_tensor(zero),
+                zero_value=float(zero), emb2=emb2.detach(), label2=label2,
+                loss2=loss2.detach() if torch.is_tensor(loss2) else None, ge2=ge2)
+
+
+def gen_pixpro(src):
+    g = torch.Generator().manual_seed(7)
+    fm1 = torch.rand(3, 21, 28, 28, generator=g).requires_grad_()
+    fm2 = torch.rand(3, 21, 28, 28, generator=g)
+    fm1.data[:, 5] = 0  # an all-zero channel column set exercises the eps clamp
+    c1 = torch.tensor([[0, 4, 20, 18], [6, 0, 15, 28], [3, 3, 7, 9]])
+    c2 = torch.tensor([[8, 0, 20, 18], [0, 0, 15, 28], [20, 19, 7, 9]])
+    loss = src.loss_multilabel.PixPro(fm1, fm2, c1, c2)
+    g1, = torch.autograd.grad(loss, fm1)
+    return dict(fm1=fm1.detach(), fm2=fm2, c1=c1, c2=c2, loss=loss.detach(), g1=g1)
+
+
+def gen_emd(src):
+    g = torch.Generator().manual_seed(9)
+    raw1 = torch.randn(3, 21, 56, 56, generator=g)
+    raw2 = torch.randn(3, 21, 56, 56, generator=g)
+    raw1 = F.avg_pool2d(raw1, 5, 1, 2).requires_grad_()
+    raw2 = F.avg_pool2d(raw2, 5, 1, 2)
+    vw1 = F.normalize(torch.softmax(raw1 * 4, 1), dim=1)
+    vw2 = F.normalize(torch.softmax(raw2 * 4, 1), dim=1)
+    c1 = torch.tensor([[0, 8, 48, 44], [10, 0, 33, 56], [0, 0, 10, 40]])
+    c2 = torch.tensor([[8, 0, 48, 44], [0, 0, 33, 56], [30, 5, 10, 40]])
+    np.random.seed(1234)
+    crops1, crops2, bidx = src.torchutils.get_dynamic_crops(vw1, c1, vw2.detach(), c2)
+    loss = src.loss_multilabel.EMD()(crops1, crops2, mode="dynamic")
+    g1, = torch.autograd.grad(loss, raw1)
+    # one isolated Sinkhorn call for the kernel-level test
+    emd = src.loss_multilabel.EMD()
+    x = crops1[0][0].reshape(1, 21, -1).permute(2, 1, 0)
+    y = crops2[0][1].reshape(1, 21, -1).permute(2, 1, 0)
+    cost = emd.pair_wise_cos(x, y).squeeze(0).detach()
+    w1 = emd.get_weight_vector(crops1[0][0], crops2[0][1]).detach()
+    w2 = emd.get_weight_vector(crops2[0][1], crops1[0][0]).detach()
+    sk = emd.sinkhorn_logsumexp(cost, w1, w2, maxiter=10, grad=False)
+    return dict(raw1=raw1.detach(), raw2=raw2, c1=c1, c2=c2, np_seed=1234, batch_indices=bidx,
+                n_crops1=[len(c) for c in crops1], n_crops2=[len(c) for c in crops2],
+                crop_shapes1=[[tuple(t.shape) for t in c] for c in crops1],
+                crop_shapes2=[[tuple(t.shape) for t in c] for c in crops2],
+                loss=loss.detach(), g1=g1, sk_cost=cost, sk_w1=w1, sk_w2=w2, sk_value=sk)
+
+
+def gen_heads(src):
+    """CAM head + embedding + PCM evaluated in situ by the reference model (b3, random weights)."""
+    torch.manual_seed(3)
+    model = src.MuSCLe(num_classes=21, pretrained="efficientnet-b3", last_pooling=False, mode="enc")
+    model.eval()
+    x = torch.randn(2, 3, 64, 64)
+    with torch.no_grad():
+        fps = model.backbone(x)
+    p1, p3, p5, p7 = (fps[i].detach() for i in (model.p1_seq, model.p3_seq, model.p5_seq, model.p7_seq))
+    cams, sgc, emb, logits = model(x, cam="cam")
+    # PCM alone on leaf inputs so that gradients can be compared
+    g = torch.Generator().manual_seed(4)
+    n, h, w = 2, 10, 12
+    cin = model.fuse.weight.shape[1]
+    cam_in = torch.rand(n, 21, h, w, generator=g).requires_grad_()
+    f_in = torch.relu(torch.randn(n, cin, h, w, generator=g))
+    model.zero_grad()
+    out = model.PCM(cam_in, f_in)
+    go = torch.randn(out.shape, generator=g)
+    (out * go).sum().backward()
+    return dict(p1=p1, p3=p3, p5=p5, p7=p7, fc_w=model.fc.weight.detach().clone(),
+                fuse_w=model.fuse.weight.detach().clone(), fuse_b=model.fuse.bias.detach().clone(),
+                cams_up=cams.detach(), sgc_up=sgc.detach(), emb=emb.detach(), logits=logits.detach(),
+                img_hw=(64, 64),
+                pcm_cam=cam_in.detach(), pcm_f=f_in, pcm_out=out.detach(), pcm_go=go,
+                pcm_gcam=cam_in.grad.clone(), pcm_gw=model.fuse.weight.grad.clone(),
+                pcm_gb=model.fuse.bias.grad.clone())
+
+
+def gen_fieldloss(src):
+    g = torch.Generator().manual_seed(13)
+    n, c, h, w, ch, k, step = 2, 21, 44, 44, 24, 12, 3
+    label = torch.zeros(n, 20)
+    label[0, [2, 14]] = 1
+    label[1, [14]] = 1
+    label_bg = torch.cat([torch.ones(n, 1), label], 1)
+    noise = F.avg_pool2d(torch.randn(n, c, h, w, generator=g), 9, 1, 4, count_include_pad=False)
+    noise = noise.masked_fill(~label_bg.bool()[:, :, None, None], -1e4)
+    seg = (noise * 3 + 0.05 * torch.randn(n, c, h, w, generator=g)).requires_grad_()
+    mask = noise * 2 + 0.3 * torch.randn(n, c, h, w, generator=g)
+    dense = torch.randn(n, ch, h, w, generator=g).requires_grad_()
+    crit = src.edge.FieldLoss(sobel_size=5, beta=1e2, k=k)
+    random.seed(77)
+    loss, mag = crit(seg, dense, mask, label_bg, step)
+    assert torch.is_tensor(loss), "fixture must exercise the bifilter"
+    gd, = torch.autograd.grad(loss, dense)
+    # stage outputs
+    with torch.no_grad():
+        edges = crit.fg_edge(seg, label_bg, reduction=False)
+        mag2, orient = crit.quantize(edges.clone())
+        mx = torch.max(mag2.view(n, 20, -1), dim=-1)[0].unsqueeze(2).unsqueeze(2)
+        pos = (mag2 >= 0.8 * mx) & (mx > 1)
+        pos = pos * label_bg[:, 1:].unsqueeze(2).unsqueeze(2).bool()
+        out_i, in_i = crit.in_out_div(orient[0, 14] + 1, pos[0, 14], step_outs=[step], step_ins=[step])
+    # gate cases: no fg class present -> False (edge.py:377-378); enough boundary pixels but
+    # in/out lists never longer than k -> python 0 (edge.py:359-361)
+    crit2 = src.edge.FieldLoss(sobel_size=5, beta=1e2, k=k)
+    flat = torch.zeros(1, c, 24, 24)
+    only_bg = torch.cat([torch.ones(1, 1), torch.zeros(1, 20)], 1)
+    loss0, _ = crit2(flat, torch.randn(1, ch, 24, 24, generator=g), flat, only_bg, step)
+    crit3 = src.edge.FieldLoss(sobel_size=5, beta=1e2, k=100000)
+    loss1, _ = crit3(seg.detach(), dense.detach(), mask, label_bg, step)
+    return dict(seg=seg.detach(), dense=dense.detach(), mask=mask, label_bg=label_bg, k=k, step=step,
+                beta=1e2, py_seed=77, loss=loss.detach(), mag=mag, gd=gd, edges=edges, orient=orient,
+                pos=pos, out_idx_0_14=out_i, in_idx_0_14=in_i, gate_false=(loss0 is False), big_k_is_zero=(not torch.is_tensor(loss1) and loss1 == 0))
+
+
+def main():
+    src = reference_loader.load()
+    os.makedirs(OUT, exist_ok=True)
+    jobs = dict(info_nce=gen_info_nce, dense_infonce=gen_dense_infonce, imc=gen_imc, pixpro=gen_pixpro,
+                emd=gen_emd, heads=gen_heads, fieldloss=gen_fieldloss)
+    only = sys.argv[1:]
+    for name, fn in jobs.items():
+        if only and name not in only:
+            continue
+        torch.manual_seed(0)
+        data = fn(src)
+        path = os.path.join(OUT, name + ".pt")
+        torch.save(data, path)
+        print("%-14s -> %s (%.1f KiB)" % (name, path, os.path.getsize(path) / 1024))
+
+
+if __name__ == "__main__":
+    main()

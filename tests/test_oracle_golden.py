@@ -1,0 +1,165 @@
+"""The oracle (oracle/muscle_oracle.py) against fixtures minted by the unmodified reference
+(oracle/make_golden.py).  CPU only."""
+import random
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import muscle_oracle as O
+
+
+def close(a, b, rtol=1e-5, atol=1e-6):
+    torch.testing.assert_close(a, b, rtol=rtol, atol=atol)
+
+
+@pytest.mark.parametrize("tag", ["f32", "f64"])
+def test_info_nce(golden, tag):
+    g = golden("info_nce")[tag]
+    q, p, k = (g[n].clone().requires_grad_() for n in "qpk")
+    loss = O.info_nce(q, p, k)
+    gq, gp, gk = torch.autograd.grad(loss, (q, p, k))
+    tol = dict(rtol=1e-5, atol=1e-6) if tag == "f32" else dict(rtol=1e-11, atol=1e-12)
+    close(loss, g["loss"], **tol)
+    close(gq, g["gq"], **tol)
+    close(gp, g["gp"], **tol)
+    close(gk, g["gk"], **tol)
+    close(O.info_nce(q, p, k, temperature=0.07, reduction="none"), g["none_t007"], **tol)
+
+
+@pytest.mark.parametrize("tag", ["f32", "f64"])
+def test_dense_infonce_composition(golden, tag):
+    g = golden("dense_infonce")[tag]
+    x = g["x"].clone().requires_grad_()
+    loss = O.dense_infonce_from_features(x, g["cls"], temperature=0.1, num_classes=5)
+    gx, = torch.autograd.grad(loss, x)
+    tol = dict(rtol=2e-5, atol=1e-6) if tag == "f32" else dict(rtol=1e-10, atol=1e-12)
+    close(loss, g["loss"], **tol)
+    close(gx, g["gx"], **tol)
+
+
+def test_dense_infonce_chunking_and_anchor(golden):
+    g = golden("dense_infonce")["f64"]
+    e = O.l2_normalize_pixels(g["x"])
+    a = O.dense_infonce(e, g["cls"], row_chunk=7)
+    b = O.dense_infonce(e, g["cls"], row_chunk=4096)
+    close(a, b, rtol=1e-12, atol=0)
+    # hard-mask anchor: 0/1 weights as "CAM weights" give the same prototypes as the mean
+    valid = g["cls"] >= 0
+    w = torch.zeros(e.shape[0], 5, dtype=e.dtype)
+    w[valid, g["cls"][valid]] = 1
+    p_soft, _ = O.class_prototypes(e, g["cls"], 5, weights=w)
+    p_hard, _ = O.class_prototypes(e, g["cls"], 5)
+    close(p_soft, p_hard, rtol=1e-12, atol=0)
+
+
+def test_image_level_contrast(golden):
+    g = golden("imc")
+    emb = g["emb"].clone().requires_grad_()
+    loss = O.image_level_contrast(emb, g["label"])
+    ge, = torch.autograd.grad(loss, emb)
+    close(loss, g["loss"], rtol=1e-5, atol=1e-6)
+    close(ge, g["ge"], rtol=1e-4, atol=1e-6)
+    label0 = torch.zeros(3, 20)
+    label0[:, 1] = 1
+    z = O.image_level_contrast(torch.randn(3, 48), label0)
+    assert not torch.is_tensor(z) and z == 0 and not g["zero_is_tensor"]
+    emb2 = g["emb2"].clone().requires_grad_()
+    loss2 = O.image_level_contrast(emb2, g["label2"])
+    if g["loss2"] is None:
+        assert not torch.is_tensor(loss2)
+    else:
+        close(loss2, g["loss2"], rtol=1e-5, atol=1e-6)
+        close(torch.autograd.grad(loss2, emb2)[0], g["ge2"], rtol=1e-4, atol=1e-6)
+
+
+def test_pixpro(golden):
+    g = golden("pixpro")
+    fm1 = g["fm1"].clone().requires_grad_()
+    loss = O.pixpro(fm1, g["fm2"], g["c1"], g["c2"])
+    close(loss, g["loss"], rtol=1e-5, atol=1e-6)
+    close(torch.autograd.grad(loss, fm1)[0], g["g1"], rtol=1e-4, atol=1e-7)
+
+
+def test_emd_dynamic(golden):
+    g = golden("emd")
+    raw1 = g["raw1"].clone().requires_grad_()
+    vw1 = F.normalize(torch.softmax(raw1 * 4, 1), dim=1)
+    vw2 = F.normalize(torch.softmax(g["raw2"] * 4, 1), dim=1)
+    rng = np.random.RandomState(g["np_seed"])
+    crops1, crops2, bidx = O.get_dynamic_crops(vw1, g["c1"], vw2.detach(), g["c2"], rng=rng)
+    assert bidx == g["batch_indices"]
+    assert [[tuple(t.shape) for t in c] for c in crops1] == g["crop_shapes1"]
+    assert [[tuple(t.shape) for t in c] for c in crops2] == g["crop_shapes2"]
+    loss = O.emd_dynamic(crops1, crops2)
+    close(loss, g["loss"], rtol=1e-4, atol=1e-7)
+    close(torch.autograd.grad(loss, raw1)[0], g["g1"], rtol=1e-3, atol=1e-8)
+    sk = O.sinkhorn_logsumexp(g["sk_cost"], g["sk_w1"].squeeze(0), g["sk_w2"].squeeze(0))
+    close(sk, g["sk_value"], rtol=1e-5, atol=1e-8)
+
+
+def test_heads_in_situ(golden):
+    g = golden("heads")
+    p1, p3, p5, p7 = g["p1"], g["p3"], g["p5"], g["p7"]
+    emb, logits = O.image_embedding_logits(p7, g["fc_w"])
+    close(emb, g["emb"], rtol=1e-5, atol=1e-6)
+    close(logits, g["logits"], rtol=1e-4, atol=1e-5)
+    cams = O.cam_head(p7, g["fc_w"])
+    hw = p7.shape[2:]
+    fs = torch.cat([torch.relu(F.interpolate(p1, size=hw, mode="bilinear", align_corners=True)),
+                    torch.relu(F.interpolate(p3, size=hw, mode="bilinear", align_corners=True)),
+                    torch.relu(p5)], dim=1)
+    sgc = O.pcm(cams, fs, g["fuse_w"], g["fuse_b"])
+    up = lambda t: F.interpolate(t, size=g["img_hw"], mode="bilinear", align_corners=True)
+    close(up(cams), g["cams_up"], rtol=1e-4, atol=1e-5)
+    close(up(sgc), g["sgc_up"], rtol=1e-4, atol=1e-5)
+
+
+def test_pcm_gradients(golden):
+    g = golden("heads")
+    cam = g["pcm_cam"].clone().requires_grad_()
+    w = g["fuse_w"].clone().requires_grad_()
+    b = g["fuse_b"].clone().requires_grad_()
+    out = O.pcm(cam, g["pcm_f"], w, b)
+    close(out, g["pcm_out"], rtol=1e-4, atol=1e-6)
+    (out * g["pcm_go"]).sum().backward()
+    close(cam.grad, g["pcm_gcam"], rtol=1e-3, atol=1e-6)
+    close(w.grad, g["pcm_gw"], rtol=2e-3, atol=2e-5)
+    close(b.grad, g["pcm_gb"], rtol=2e-3, atol=2e-5)
+
+
+def test_fieldloss(golden):
+    g = golden("fieldloss")
+    edges = O.class_edges(g["seg"], g["label_bg"], beta=g["beta"], sobel_size=5)
+    close(edges, g["edges"], rtol=1e-4, atol=1e-5)
+    mag, orient = O.orient_quantize(g["edges"])
+    assert torch.equal(orient, g["orient"])
+    pos = O.boundary_positions(mag, g["label_bg"])
+    assert torch.equal(pos, g["pos"])
+    out_i, in_i = O.in_out_indices(g["orient"][0, 14] + 1, g["pos"][0, 14], g["step"])
+    assert torch.equal(out_i, g["out_idx_0_14"]) and torch.equal(in_i, g["in_idx_0_14"])
+    dense = g["dense"].clone().requires_grad_()
+    rng = random.Random(g["py_seed"])
+    loss, mag_sum = O.fieldloss_forward(g["seg"], dense, g["mask"], g["label_bg"], step=g["step"], k=g["k"],
+                                        beta=g["beta"], rng=rng)
+    close(mag_sum, g["mag"], rtol=1e-4, atol=1e-4)
+    close(loss, g["loss"], rtol=1e-4, atol=1e-7)
+    close(torch.autograd.grad(loss, dense)[0], g["gd"], rtol=1e-3, atol=1e-9)
+    flat = torch.zeros(1, 21, 24, 24)
+    only_bg = torch.cat([torch.ones(1, 1), torch.zeros(1, 20)], 1)
+    loss0, _ = O.fieldloss_forward(flat, torch.randn(1, 24, 24, 24), flat, only_bg, step=3, k=12, beta=g["beta"])
+    assert loss0 is False and g["gate_false"]
+    loss1, _ = O.fieldloss_forward(g["seg"], g["dense"], g["mask"], g["label_bg"], step=g["step"], k=100000,
+                                   beta=g["beta"])
+    assert (not torch.is_tensor(loss1)) and loss1 == 0 and g["big_k_is_zero"]
+
+
+def test_cam_normalisers():
+    x = torch.randn(2, 21, 6, 7)
+    sm = O.cam_softmaxnorm(x)
+    assert sm.shape == x.shape
+    close(sm[:, 1:].sum(1), torch.ones(2, 6, 7), rtol=1e-5, atol=1e-6)
+    close(sm[:, 0], 1 - sm[:, 1:].max(1)[0])
+    mn = O.cam_maxnorm(x)
+    assert float(mn.min()) >= 0 and float(mn.max()) <= 1
