@@ -1,0 +1,121 @@
+/* muscle_b200 — C ABI of the B200-native contrastive-loss hot path of SCoulY/MuSCLe.
+ *
+ * The reference is pure Python/PyTorch and has no FFI layer: its boundary for this path is the
+ * set of Python call expressions in train_mcl.py / train_muscle.py / src/MuSCLe.py (SURVEY.md
+ * §8b).  These entry points are what a binding for that boundary calls; INTEGRATION.md shows the
+ * ctypes stubs.  Conventions (all functions):
+ *   - plain device pointers + explicit sizes; the caller owns every buffer (inputs, outputs,
+ *     workspace); nothing is allocated, freed or synchronised inside; all work is enqueued on
+ *     `stream` (a cudaStream_t passed as void*); re-entrant, no global state;
+ *   - return value 0 = MUSCLE_OK, otherwise a MUSCLE_ERR_* code; muscle_last_error() returns a
+ *     thread-local description of the most recent failure;
+ *   - float tensors are fp32, row-major/contiguous in the stated layout; nothing is mutated
+ *     except the documented outputs and the workspace.
+ */
+#ifndef MUSCLE_B200_H_
+#define MUSCLE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MUSCLE_OK 0
+#define MUSCLE_ERR_BAD_ARG 1       /* unsupported shape / null pointer / misaligned buffer */
+#define MUSCLE_ERR_WORKSPACE 2     /* workspace too small */
+#define MUSCLE_ERR_CUDA 3          /* a CUDA runtime / driver call failed */
+#define MUSCLE_ERR_UNSUPPORTED 4   /* device is not sm_100 */
+
+/* Layout of a [pixels, dim] feature operand. */
+#define MUSCLE_LAYOUT_PIXEL_MAJOR 0 /* x[n*dim + d]            (N, D)            */
+#define MUSCLE_LAYOUT_NCHW 1        /* x[(b*dim + d)*P + p]    (B, D, h, w), P=h*w */
+
+#define MUSCLE_MAX_CLASSES 32
+
+const char* muscle_last_error(void);
+int muscle_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Dense label-masked pixel InfoNCE, forward + input gradient in one call.
+ * Replaces: the composition of reference `info_nce` (src/loss_multilabel.py:9-21) over a whole
+ * batch fixed in SURVEY.md §8c — for every valid pixel q of class c:
+ *     pos_q = e_q . mean_{k: cls_k = c} e_k ,  negs_q = { e_q . e_k : cls_k != c } ,
+ *     loss  = mean_q [ logsumexp([pos_q, negs_q] / T) - pos_q / T ],  e = x / max(||x||, eps)
+ * x        [B*P, dim] in `layout`, raw (un-normalised) embeddings
+ * cls      per-pixel class id in [0, num_classes), < 0 = pixel takes no part; int32 or int64
+ * loss_out device float[1];  dx_out device float[B*P*dim] in `layout`, or NULL for forward only
+ * dim in {64,128,256}; num_classes <= MUSCLE_MAX_CLASSES.
+ */
+size_t muscle_dense_infonce_workspace_bytes(int64_t n_pixels, int dim, int num_classes);
+int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
+                                 int64_t pixels_per_image, int dim, const void* cls,
+                                 int cls_is_int64, int num_classes, float temperature, float eps,
+                                 float* loss_out, float* dx_out, void* workspace,
+                                 size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Staged form of the same op, for the batch-sharded multi-GPU path: the host
+ * runs  prepare -> [all-gather ehat/bits, all-reduce class_sum/class_mass] -> pos -> rowsum ->
+ * [all-gather rowsum] -> mid -> [all-reduce dproto, loss_acc] -> grad -> final.
+ * "rows" are this rank's pixels, "cols" all pixels of all ranks; *_pad = round_up(n, 256).
+ */
+int64_t muscle_pad_rows(int64_t n);
+
+/* L2-normalise + bf16 cast + class bit per pixel + per-class sums of e (accumulated with
+ * atomics: the caller zeroes class_sum [C*dim] and class_mass [C] first). Pad rows are zeroed.
+ * ehat: bf16 [rows_pad, dim] pixel-major; bits: uint32 [rows_pad]; inv_norm: float [n]. */
+int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
+                           int dim, const void* cls, int cls_is_int64, int num_classes, float eps,
+                           void* ehat, uint32_t* bits, float* inv_norm, float* class_sum,
+                           float* class_mass, void* stream);
+
+/* pos[q] = e_q . proto_{c_q} / T and rowsum[q] = exp(pos[q] - bound/T) (0 for invalid rows). */
+int muscle_infonce_pos(const void* ehat, const uint32_t* bits, int64_t n_rows, int64_t rows_pad,
+                       int dim, int num_classes, const float* class_sum, const float* class_mass,
+                       float temperature, const float* bound, float* pos, float* rowsum,
+                       void* stream);
+
+/* rowsum[q] += sum_k [cls_k != cls_q] exp((e_q.e_k - bound)/T)   — tcgen05 pass 1. */
+int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows, int64_t rows_pad,
+                          const void* ehat_cols, const uint32_t* bits_cols, int64_t cols_pad,
+                          int dim, float temperature, const float* bound, float* rowsum,
+                          void* stream);
+
+/* w[q] = 1/rowsum[q] (0 for invalid rows), gpos[q] = (exp(pos-bound/T) w - 1)/T,
+ * loss_acc (double[1]) += sum_q (bound/T + ln rowsum[q] - pos[q]),
+ * dproto [C*dim] += gpos[q] * e_q  (both accumulated: caller zeroes them). */
+int muscle_infonce_mid(const void* ehat, const uint32_t* bits, int64_t n_rows, int dim,
+                       int num_classes, const float* pos, const float* rowsum,
+                       float temperature, const float* bound, float* w, float* gpos,
+                       double* loss_acc, float* dproto, void* stream);
+
+/* part[s][q][:] = sum_{k in split s} [cls_k != cls_q] exp((e_q.e_k - bound)/T) (w_rows[q] +
+ * w_cols[k]) e_k   — tcgen05 pass 2.  part: float [n_split, rows_pad, dim]. */
+int muscle_infonce_grad_splits(int64_t rows_pad, int64_t cols_pad, int dim);
+int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows, const float* w_rows,
+                        int64_t rows_pad, const void* ehat_cols, const uint32_t* bits_cols,
+                        const float* w_cols, int64_t cols_pad, int dim, float temperature,
+                        const float* bound, float* part, int n_split, void* stream);
+
+/* dx = d(loss)/dx: sums the splits, adds the prototype terms, back-propagates through the
+ * L2 normalisation and writes `layout`.  loss_out = loss_acc / n_valid (n_valid = sum of
+ * class_mass).  dx may be NULL (loss only). */
+int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* inv_norm,
+                         const float* part, int n_split, int64_t rows_pad, int64_t batch,
+                         int64_t pixels_per_image, int dim, int num_classes,
+                         const float* class_sum, const float* class_mass, const float* gpos,
+                         const float* dproto, const double* loss_acc, float temperature,
+                         int layout, float* dx, float* loss_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Debug / unit-test entry points for the tcgen05 building blocks (used by tests/ only).
+ * sim: S[128,128] = A[128,dim] B[128,dim]^T ;  tsg: G[128,dim] = bf16(S) B  (A from TMEM). */
+int muscle_debug_tile(const void* a_bf16, const void* b_bf16, int dim, float* s_out,
+                      float* g_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MUSCLE_B200_H_ */

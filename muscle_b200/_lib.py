@@ -1,0 +1,73 @@
+"""ctypes binding of libmuscle_b200.so (the C ABI declared in include/muscle_b200.h).
+
+There is no CPU or eager-PyTorch fallback: if the library is missing, or the device is not an
+sm_100 GPU, every op raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_double, c_float, c_int, c_int64, c_size_t, c_uint32, c_void_p, POINTER
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libmuscle_b200.so")
+
+MUSCLE_OK = 0
+LAYOUT_PIXEL_MAJOR = 0
+LAYOUT_NCHW = 1
+MAX_CLASSES = 32
+
+# name -> (restype, argtypes); mirrors include/muscle_b200.h one to one
+_SIGNATURES = {
+    "muscle_last_error": (c_char_p, []),
+    "muscle_version": (c_int, []),
+    "muscle_pad_rows": (c_int64, [c_int64]),
+    "muscle_dense_infonce_workspace_bytes": (c_size_t, [c_int64, c_int, c_int]),
+    "muscle_dense_infonce_fwd_bwd": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int, c_void_p, c_int, c_int,
+                                             c_float, c_float, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "muscle_infonce_prepare": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int, c_void_p, c_int, c_int, c_float,
+                                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "muscle_infonce_pos": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p,
+                                   c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "muscle_infonce_rowsum": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int, c_float,
+                                      c_void_p, c_void_p, c_void_p]),
+    "muscle_infonce_mid": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_float,
+                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "muscle_infonce_grad_splits": (c_int, [c_int64, c_int64, c_int]),
+    "muscle_infonce_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64,
+                                    c_int, c_float, c_void_p, c_void_p, c_int, c_void_p]),
+    "muscle_infonce_final": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64, c_int64,
+                                     c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
+                                     c_int, c_void_p, c_void_p, c_void_p]),
+    "muscle_debug_tile": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+}
+
+_lib = None
+
+
+def exported_symbols():
+    return sorted(_SIGNATURES)
+
+
+def load():
+    """Loads the shared library (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "muscle_b200: %s not found. Build it with `python -m muscle_b200.build` "
+            "(needs nvcc); there is no CPU fallback." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in _SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the header and the library disagree
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str):
+    if rc != MUSCLE_OK:
+        msg = load().muscle_last_error()
+        raise RuntimeError("muscle_b200 %s failed (code %d): %s" % (what, rc, msg.decode() if msg else "?"))

@@ -1,0 +1,105 @@
+"""PyTorch-facing ops of the hot path.  PyTorch supplies device memory, streams and autograd
+plumbing only; all arithmetic runs in libmuscle_b200.so through raw pointers."""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+
+
+def _stream_ptr(device):
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _require_cuda(t: torch.Tensor, name: str):
+    if not t.is_cuda:
+        raise RuntimeError("muscle_b200: `%s` must be a CUDA tensor (there is no CPU path)" % name)
+
+
+def _as_feature_operand(x: torch.Tensor):
+    """-> (contiguous tensor, layout, batch, pixels_per_image, dim)."""
+    if x.dim() == 4:            # [B, D, h, w]
+        b, d, h, w = x.shape
+        return x.contiguous(), _lib.LAYOUT_NCHW, b, h * w, d
+    if x.dim() == 3:            # [B, D, P]
+        b, d, p = x.shape
+        return x.contiguous(), _lib.LAYOUT_NCHW, b, p, d
+    if x.dim() == 2:            # [N, D]
+        n, d = x.shape
+        return x.contiguous(), _lib.LAYOUT_PIXEL_MAJOR, 1, n, d
+    raise ValueError("expected [B,D,h,w], [B,D,P] or [N,D] embeddings, got shape %s" % (tuple(x.shape),))
+
+
+class _DenseInfoNCE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, cls, temperature, num_classes, eps):
+        _require_cuda(x, "x")
+        _require_cuda(cls, "cls")
+        if x.dtype != torch.float32:
+            raise TypeError("embeddings must be float32 (the reference path is fp32)")
+        lib = _lib.load()
+        xc, layout, batch, ppi, dim = _as_feature_operand(x)
+        n = batch * ppi
+        cls_c = cls.reshape(-1).contiguous()
+        if cls_c.numel() != n:
+            raise ValueError("cls has %d entries for %d pixels" % (cls_c.numel(), n))
+        if cls_c.dtype == torch.int64:
+            cls64 = 1
+        elif cls_c.dtype == torch.int32:
+            cls64 = 0
+        else:
+            cls_c = cls_c.to(torch.int64)
+            cls64 = 1
+        need_grad = x.requires_grad
+        ws_bytes = lib.muscle_dense_infonce_workspace_bytes(n, dim, num_classes)
+        if ws_bytes == 0:
+            raise ValueError("unsupported shape: dim=%d (64/128/256), num_classes=%d (<=%d)"
+                             % (dim, num_classes, _lib.MAX_CLASSES))
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+        loss = torch.empty((), dtype=torch.float32, device=x.device)
+        dx = torch.empty_like(xc) if need_grad else None
+        with torch.cuda.device(x.device):
+            rc = lib.muscle_dense_infonce_fwd_bwd(
+                xc.data_ptr(), layout, batch, ppi, dim, cls_c.data_ptr(), cls64, num_classes,
+                float(temperature), float(eps), loss.data_ptr(), dx.data_ptr() if need_grad else None,
+                ws.data_ptr(), ws_bytes, _stream_ptr(x.device))
+        _lib.check(rc, "dense_infonce")
+        ctx.save_for_backward(dx)
+        ctx.x_shape = x.shape
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (dx,) = ctx.saved_tensors
+        if dx is None:
+            return None, None, None, None, None
+        return (dx * grad_out).reshape(ctx.x_shape), None, None, None, None
+
+
+def dense_infonce(x, cls, temperature=0.1, num_classes=21, eps=1e-12):
+    """Dense label-masked pixel InfoNCE over a batch (SURVEY.md §8c composition of the reference
+    ``info_nce``, src/loss_multilabel.py:9-21): every valid pixel is a query, its positive is the
+    prototype (mean normalised embedding) of its class, its negatives are all pixels of other
+    classes; mean over valid pixels.
+
+    x   : float32 CUDA [B, D, h, w] (the model's layout), [B, D, P] or [N, D]; D in {64,128,256}
+    cls : per-pixel class ids, same pixel order, int64/int32; < 0 = ignore
+    Returns a 0-dim float32 tensor with grad to ``x`` (forward and input gradient are produced by
+    one fused pass; backward only scales)."""
+    return _DenseInfoNCE.apply(x, cls, temperature, num_classes, eps)
+
+
+def debug_tile(a_bf16: torch.Tensor, b_bf16: torch.Tensor):
+    """S = A B^T [128,128] and G = bf16(S) B [128,D] through the tcgen05 building blocks (tests)."""
+    lib = _lib.load()
+    assert a_bf16.dtype == torch.bfloat16 and b_bf16.dtype == torch.bfloat16
+    assert a_bf16.shape == b_bf16.shape and a_bf16.shape[0] == 128
+    a = a_bf16.contiguous()
+    b = b_bf16.contiguous()
+    d = a.shape[1]
+    s = torch.empty(128, 128, dtype=torch.float32, device=a.device)
+    g = torch.empty(128, d, dtype=torch.float32, device=a.device)
+    with torch.cuda.device(a.device):
+        rc = lib.muscle_debug_tile(a.data_ptr(), b.data_ptr(), d, s.data_ptr(), g.data_ptr(), _stream_ptr(a.device))
+    _lib.check(rc, "debug_tile")
+    return s, g

@@ -1,0 +1,148 @@
+"""GPU parity tests of the dense InfoNCE path (through the C ABI) against the CPU oracle and the
+fixtures minted by the unmodified reference.  Tolerances are north_star's: loss within 1e-3
+relative of the fp32 reference, input-gradient cosine >= 0.999."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import muscle_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+LOSS_RTOL = 1e-3
+GRAD_COS = 0.999
+
+
+@pytest.fixture(scope="module")
+def M():
+    import muscle_b200
+    return muscle_b200
+
+
+def _cos(a, b):
+    return F.cosine_similarity(a.flatten().double(), b.flatten().double(), dim=0).item()
+
+
+@pytest.mark.parametrize("d", [64, 128, 256])
+def test_tcgen05_tile_blocks(M, d):
+    torch.manual_seed(d)
+    a = (torch.randn(128, d) / d ** 0.5).to(torch.bfloat16)
+    b = (torch.randn(128, d) / d ** 0.5).to(torch.bfloat16)
+    s, g = M.debug_tile(a.cuda(), b.cuda())
+    s_ref = a.float() @ b.float().t()
+    g_ref = s_ref.to(torch.bfloat16).float() @ b.float()
+    torch.testing.assert_close(s.cpu(), s_ref, rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(g.cpu(), g_ref, rtol=1e-2, atol=1e-2)
+
+
+def _run_both(M, x, cls, num_classes=21, temperature=0.1, nchw=True):
+    """x [B,D,h,w] cpu fp32, cls [B,h,w]."""
+    d = x.shape[1]
+    xr = x.clone().requires_grad_()
+    ref = O.dense_infonce_from_features(xr.permute(0, 2, 3, 1).reshape(-1, d), cls.reshape(-1),
+                                        temperature, num_classes)
+    gref, = torch.autograd.grad(ref, xr)
+    if nchw:
+        xg = x.cuda().requires_grad_()
+        loss = M.dense_infonce(xg, cls.cuda(), temperature, num_classes)
+        loss.backward()
+        g = xg.grad.cpu()
+    else:
+        xg = x.permute(0, 2, 3, 1).reshape(-1, d).contiguous().cuda().requires_grad_()
+        loss = M.dense_infonce(xg, cls.reshape(-1).cuda(), temperature, num_classes)
+        loss.backward()
+        g = xg.grad.cpu().reshape(x.shape[0], x.shape[2], x.shape[3], d).permute(0, 3, 1, 2)
+    return loss.item(), ref.item(), g, gref
+
+
+@pytest.mark.parametrize("batch,d,h,w,nchw", [
+    (2, 128, 16, 16, True), (2, 128, 16, 16, False), (2, 128, 32, 32, True),   # config 1 = (2,128,32,32)
+    (3, 64, 20, 24, True), (2, 256, 32, 32, True), (1, 128, 7, 9, True), (2, 128, 19, 23, False),
+])
+def test_dense_infonce_matches_oracle(M, batch, d, h, w, nchw):
+    x, cls, _ = O.synth_embeddings(batch, d, h, w, seed=100 + batch + d + h)
+    loss, ref, g, gref = _run_both(M, x, cls, nchw=nchw)
+    assert abs(loss - ref) <= LOSS_RTOL * abs(ref), (loss, ref)
+    assert _cos(g, gref) >= GRAD_COS
+    assert abs(g.norm().item() / gref.norm().item() - 1) < 2e-2
+
+
+def test_dense_infonce_golden_fixture(M, golden):
+    """The fixture was produced by calling the reference info_nce once per class (make_golden.py)."""
+    g = golden("dense_infonce")["f32"]
+    x = g["x"]
+    n, d = x.shape
+    if d not in (64, 128, 256):
+        pytest.skip("fixture dim %d not a tensor-core dim" % d)
+    xg = x.cuda().requires_grad_()
+    loss = M.dense_infonce(xg, g["cls"].cuda(), 0.1, 5)
+    loss.backward()
+    assert abs(loss.item() - g["loss"].item()) <= LOSS_RTOL * abs(g["loss"].item())
+    assert _cos(xg.grad.cpu(), g["gx"]) >= GRAD_COS
+
+
+def test_ignore_pixels_and_single_class(M):
+    x, cls, _ = O.synth_embeddings(2, 128, 16, 16, seed=7)
+    cls = cls.clone()
+    cls[0, :4] = -1                      # ignored pixels: neither queries nor keys
+    loss, ref, g, gref = _run_both(M, x, cls)
+    assert abs(loss - ref) <= LOSS_RTOL * abs(ref)
+    assert _cos(g, gref) >= GRAD_COS
+    assert float(g[0, :, :4].abs().max()) == 0.0
+    # one class only: no negatives -> every query's loss is exactly 0 (info_nce with K=0)
+    one = torch.zeros_like(cls)
+    xg = x.cuda().requires_grad_()
+    l1 = M.dense_infonce(xg, one.cuda(), 0.1, 21)
+    l1.backward()
+    assert abs(l1.item()) < 1e-5
+    assert float(xg.grad.abs().max()) < 1e-6
+
+
+def test_forward_only_and_determinism_of_value(M):
+    x, cls, _ = O.synth_embeddings(2, 128, 24, 24, seed=11)
+    a = M.dense_infonce(x.cuda(), cls.cuda(), 0.1, 21)
+    b = M.dense_infonce(x.cuda(), cls.cuda(), 0.1, 21)
+    assert not a.requires_grad
+    assert abs(a.item() - b.item()) <= 1e-5 * abs(a.item())
+
+
+def test_permutation_invariance_and_temperature(M):
+    x, cls, _ = O.synth_embeddings(2, 128, 16, 16, seed=13)
+    flat = x.permute(0, 2, 3, 1).reshape(-1, 128)
+    c = cls.reshape(-1)
+    perm = torch.randperm(flat.shape[0], generator=torch.Generator().manual_seed(1))
+    l0 = M.dense_infonce(flat.cuda(), c.cuda(), 0.07, 21).item()
+    l1 = M.dense_infonce(flat[perm].contiguous().cuda(), c[perm].cuda(), 0.07, 21).item()
+    ref = O.dense_infonce_from_features(flat, c, 0.07, 21).item()
+    assert abs(l0 - l1) <= 1e-4 * abs(l0)
+    assert abs(l0 - ref) <= LOSS_RTOL * abs(ref)
+
+
+def test_config2_full_size_properties(M):
+    """BASELINE config 2 (B=8, 448 crop -> 56x56, D=128): value against the row-chunked oracle,
+    gradient orthogonal to x (normalisation), finite, and equal across layouts."""
+    x, cls, _ = O.synth_embeddings(8, 128, 56, 56, seed=1234)
+    xg = x.cuda().requires_grad_()
+    loss = M.dense_infonce(xg, cls.cuda(), 0.1, 21)
+    loss.backward()
+    g = xg.grad
+    assert torch.isfinite(g).all()
+    radial = (g * xg.detach()).sum(1).abs().max().item()
+    assert radial <= 1e-3 * g.norm(dim=1).max().item() * xg.detach().norm(dim=1).max().item()
+    flat = x.permute(0, 2, 3, 1).reshape(-1, 128)
+    ref = O.dense_infonce_from_features(flat, cls.reshape(-1), 0.1, 21).item()
+    assert abs(loss.item() - ref) <= LOSS_RTOL * abs(ref)
+    xp = flat.contiguous().cuda().requires_grad_()
+    lp = M.dense_infonce(xp, cls.reshape(-1).cuda(), 0.1, 21)
+    lp.backward()
+    gp = xp.grad.reshape(8, 56, 56, 128).permute(0, 3, 1, 2)
+    assert abs(lp.item() - loss.item()) <= 1e-5 * abs(loss.item())
+    assert _cos(gp.cpu(), g.cpu()) >= 0.99999
+
+
+def test_errors_are_loud(M):
+    x = torch.randn(64, 96, device="cuda")
+    with pytest.raises((RuntimeError, ValueError)):
+        M.dense_infonce(x, torch.zeros(64, dtype=torch.int64, device="cuda"))
+    with pytest.raises(RuntimeError):
+        M.dense_infonce(torch.randn(64, 128), torch.zeros(64, dtype=torch.int64))
