@@ -1,0 +1,133 @@
+"""Batch-sharded dense InfoNCE with cross-GPU negatives (no reference counterpart).
+
+Each rank owns its images' pixels ("rows").  One all-gather of the L2-normalised bf16 embeddings
+(+ class bits) makes every pixel of every rank a key ("cols"); the row-sum pass and the gradient
+pass then run on  local rows x all cols.  Because the similarity matrix is symmetric, the
+gradient a pixel receives as a *key* of remote queries is sum_j p_ji e_j, which the owning rank can
+form itself once it knows every pixel's 1/rowsum — so the reduce-scatter of key gradients
+([N_g, D] fp32) that a query-side formulation needs is replaced by an all-gather of N_g floats.
+Small all-reduces carry the class sums, the prototype gradient and the loss.
+
+Result contract: loss and d(loss)/d(x_local) at G ranks == the single-GPU op on the concatenated
+batch == the CPU oracle on the concatenated batch.  The loss is already the GLOBAL mean: do not
+average the returned gradient across ranks again.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .ops import _as_feature_operand
+from .stages import CudaStages
+
+
+def _world(group):
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_world_size(group), dist.get_rank(group)
+    return 1, 0
+
+
+def _all_gather_into(out, inp, group):
+    try:
+        dist.all_gather_into_tensor(out, inp, group=group)
+    except (RuntimeError, NotImplementedError):   # backends without the flat form
+        g = dist.get_world_size(group)
+        dist.all_gather(list(out.chunk(g, dim=0)), inp, group=group)
+
+
+def sharded_fwd_bwd(stages, x, cls, temperature, num_classes, eps, need_grad, group=None):
+    """Runs the staged op on this rank.  -> (loss 0-dim tensor, dx or None).  `stages` is a
+    CudaStages (or the CPU stand-in the gloo tests use)."""
+    G, rank = _world(group)
+    xc, layout, batch, ppi, dim = _as_feature_operand(x)
+    n = batch * ppi
+    cls_c = cls.reshape(-1).contiguous()
+    if cls_c.dtype not in (torch.int64, torch.int32):
+        cls_c = cls_c.to(torch.int64)
+    if cls_c.numel() != n:
+        raise ValueError("cls has %d entries for %d pixels" % (cls_c.numel(), n))
+    rows_pad = stages.pad_rows(n)
+    if G > 1:
+        sizes = torch.tensor([rows_pad], dtype=torch.int64, device=xc.device)
+        lo, hi = sizes.clone(), sizes.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+        if int(lo) != int(hi):
+            raise ValueError("every rank must hold the same (padded) number of pixels")
+    cols_pad = rows_pad * G
+    C = num_classes
+    f32, i32 = torch.float32, torch.int32
+
+    ehat_all = stages.empty((cols_pad, dim), torch.bfloat16)
+    bits_all = stages.empty((cols_pad,), i32)
+    w_all = stages.zeros((cols_pad,), f32)
+    sl = slice(rank * rows_pad, (rank + 1) * rows_pad)
+    ehat, bits, w = ehat_all[sl], bits_all[sl], w_all[sl]
+    inv_norm = stages.empty((rows_pad,), f32)
+    pos = stages.empty((rows_pad,), f32)
+    rowsum = stages.empty((rows_pad,), f32)
+    gpos = stages.zeros((rows_pad,), f32)
+    stats = stages.zeros((C * dim + C,), f32)           # class_sum | class_mass
+    class_sum, class_mass = stats[:C * dim], stats[C * dim:]
+    dproto = stages.zeros((C * dim,), f32)
+    loss_acc = stages.zeros((1,), torch.float64)
+    bound = stages.zeros((1,), f32) + 1.0               # |cos| <= 1 for unit vectors
+    loss = stages.empty((), f32)
+
+    stages.prepare(xc, layout, batch, ppi, dim, cls_c, C, eps, ehat, bits, inv_norm, class_sum, class_mass)
+    if G > 1:
+        dist.all_reduce(stats, group=group)
+        _all_gather_into(ehat_all, ehat, group)
+        _all_gather_into(bits_all, bits, group)
+    stages.pos(ehat, bits, n, rows_pad, dim, C, class_sum, class_mass, temperature, bound, pos, rowsum)
+    stages.rowsum(ehat, bits, rows_pad, ehat_all, bits_all, cols_pad, dim, temperature, bound, rowsum)
+    stages.mid(ehat, bits, n, dim, C, pos, rowsum, temperature, bound, w, gpos, loss_acc, dproto)
+    if G > 1:
+        dist.all_reduce(loss_acc, group=group)
+    dx = None
+    n_split = 1
+    part = None
+    if need_grad:
+        if G > 1:
+            dist.all_reduce(dproto, group=group)
+            _all_gather_into(w_all, w, group)
+        n_split = stages.grad_splits(rows_pad, cols_pad, dim)
+        part = stages.empty((n_split, rows_pad, dim), f32)
+        stages.grad(ehat, bits, w, rows_pad, ehat_all, bits_all, w_all, cols_pad, dim, temperature, bound, part,
+                    n_split)
+        dx = stages.empty(tuple(xc.shape), f32)
+    else:
+        part = stages.empty((1,), f32)
+    stages.final(ehat, bits, inv_norm, part, n_split, rows_pad, batch, ppi, dim, C, class_sum, class_mass, gpos,
+                 dproto, loss_acc, temperature, layout, dx, loss)
+    return loss, dx
+
+
+class _ShardedDenseInfoNCE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, cls, temperature, num_classes, eps, group):
+        if not x.is_cuda:
+            raise RuntimeError("muscle_b200: `x` must be a CUDA tensor (there is no CPU path)")
+        if x.dtype != torch.float32:
+            raise TypeError("embeddings must be float32")
+        stages = CudaStages(x.device)
+        loss, dx = sharded_fwd_bwd(stages, x, cls, temperature, num_classes, eps, x.requires_grad, group)
+        ctx.save_for_backward(dx)
+        ctx.x_shape = x.shape
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (dx,) = ctx.saved_tensors
+        if dx is None:
+            return None, None, None, None, None, None
+        return (dx * grad_out).reshape(ctx.x_shape), None, None, None, None, None
+
+
+def dense_infonce_sharded(x, cls, temperature=0.1, num_classes=21, eps=1e-12, group=None):
+    """`muscle_b200.dense_infonce` over the union of all ranks' pixels (cross-GPU negatives).
+    Each rank passes its own images; returns the global-mean loss with grad to the local `x`."""
+    if num_classes > _lib.MAX_CLASSES:
+        raise ValueError("num_classes must be <= %d" % _lib.MAX_CLASSES)
+    return _ShardedDenseInfoNCE.apply(x, cls, temperature, num_classes, eps, group)
