@@ -255,26 +255,27 @@ def main():
     kern = {}
     if world == 1:
         cols_pad = rows_pad
-        f32 = torch.float32
+        f32, i32 = torch.float32, torch.int32
+        C = NUM_CLASSES
         ehat = st.empty((rows_pad, dim), torch.bfloat16)
-        bits = st.empty((rows_pad,), torch.int32)
+        bits = st.empty((rows_pad,), i32)
+        tor = st.empty((rows_pad // 128,), i32)
         inv_norm = st.empty((rows_pad,), f32)
-        stats = st.zeros((NUM_CLASSES * dim + NUM_CLASSES,), f32)
-        cs, cm = stats[:NUM_CLASSES * dim], stats[NUM_CLASSES * dim:]
-        pos, rowsum, wv, gpos = (st.zeros((rows_pad,), f32) for _ in range(4))
-        dproto = st.zeros((NUM_CLASSES * dim,), f32)
+        perm = st.empty((n_local,), i32)
+        seg = st.empty((C + 2,), i32)
+        stats = st.zeros((C * dim + C,), f32)
+        cs, cm = stats[:C * dim], stats[C * dim:]
+        rowsum, wv, gpos = (st.zeros((rows_pad,), f32) for _ in range(3))
+        dproto = st.zeros((C * dim,), f32)
         lacc = st.zeros((1,), torch.float64)
-        bound = st.zeros((1,), f32) + 1.0
-        st.prepare(x_d, _lib.LAYOUT_NCHW, lb, h * w, dim, c_d, NUM_CLASSES, 1e-12, ehat, bits, inv_norm, cs, cm)
-        st.pos(ehat, bits, n_local, rows_pad, dim, NUM_CLASSES, cs, cm, TEMPERATURE, bound, pos, rowsum)
-        rs0 = rowsum.clone()
-        st.rowsum(ehat, bits, rows_pad, ehat, bits, cols_pad, dim, TEMPERATURE, bound, rowsum)
-        st.mid(ehat, bits, n_local, dim, NUM_CLASSES, pos, rowsum, TEMPERATURE, bound, wv, gpos, lacc, dproto)
+        st.prepare(x_d, _lib.LAYOUT_NCHW, lb, h * w, dim, c_d, C, 1e-12, ehat, bits, inv_norm, perm, tor, seg, cs, cm)
+        st.rowsum(ehat, bits, tor, rows_pad, ehat, bits, tor, cols_pad, dim, TEMPERATURE, rowsum)
+        st.mid(ehat, seg, rows_pad, dim, C, cs, cm, rowsum, TEMPERATURE, wv, gpos, lacc, dproto)
         n_split = st.grad_splits(rows_pad, cols_pad, dim)
         part = st.empty((n_split, rows_pad, dim), f32)
-        grad_fn = lambda: st.grad(ehat, bits, wv, rows_pad, ehat, bits, wv, cols_pad, dim, TEMPERATURE, bound, part, n_split)
-        rs_tmp = rs0.clone()
-        rowsum_fn = lambda: st.rowsum(ehat, bits, rows_pad, ehat, bits, cols_pad, dim, TEMPERATURE, bound, rs_tmp)
+        grad_fn = lambda: st.grad(ehat, bits, tor, wv, rows_pad, ehat, bits, tor, wv, cols_pad, dim, TEMPERATURE, part, n_split)
+        rs_tmp = st.zeros((rows_pad,), f32)
+        rowsum_fn = lambda: st.rowsum(ehat, bits, tor, rows_pad, ehat, bits, tor, cols_pad, dim, TEMPERATURE, rs_tmp)
         for _ in range(3):
             grad_fn(); rowsum_fn()
         ksteps = max(10, min(args.steps, 50))

@@ -32,7 +32,7 @@ extern "C" {
 #define MUSCLE_LAYOUT_PIXEL_MAJOR 0 /* x[n*dim + d]            (N, D)            */
 #define MUSCLE_LAYOUT_NCHW 1        /* x[(b*dim + d)*P + p]    (B, D, h, w), P=h*w */
 
-#define MUSCLE_MAX_CLASSES 32
+#define MUSCLE_MAX_CLASSES 31
 
 const char* muscle_last_error(void);
 int muscle_version(void);
@@ -57,54 +57,60 @@ int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
 
 /* ------------------------------------------------------------------------------------------
  * Staged form of the same op, for the batch-sharded multi-GPU path: the host
- * runs  prepare -> [all-gather ehat/bits, all-reduce class_sum/class_mass] -> pos -> rowsum ->
- * [all-gather rowsum] -> mid -> [all-reduce dproto, loss_acc] -> grad -> final.
+ * runs  prepare -> [all-gather ehat/bits/tor, all-reduce class_sum/class_mass] -> rowsum ->
+ * mid -> [all-gather w, all-reduce dproto/loss_acc] -> grad -> final.
  * "rows" are this rank's pixels, "cols" all pixels of all ranks; *_pad = round_up(n, 256).
+ * Inside the library the pixels are kept SORTED BY CLASS (stable counting sort; invalid pixels
+ * and zero pad rows last): arrays marked [sorted] are indexed by sorted row, `perm` maps a
+ * source pixel to its sorted row.  `tor` has one word per 128 sorted rows: the OR of the class
+ * bits in the tile, bit 31 set when the tile holds an invalid or pad row; the pair passes skip
+ * every (row tile, column tile) whose pairs are all masked and drop the mask where none is.
  */
 int64_t muscle_pad_rows(int64_t n);
+size_t muscle_infonce_prepare_scratch_bytes(int64_t n_pixels);
 
-/* L2-normalise + bf16 cast + class bit per pixel + per-class sums of e (accumulated with
- * atomics: the caller zeroes class_sum [C*dim] and class_mass [C] first). Pad rows are zeroed.
- * ehat: bf16 [rows_pad, dim] pixel-major; bits: uint32 [rows_pad]; inv_norm: float [n]. */
+/* Class sort + L2-normalise + bf16 cast + per-class sums (accumulated with atomics: the caller
+ * zeroes class_sum [C*dim] and class_mass [C] first).  Pad rows are zeroed.
+ * ehat: bf16 [rows_pad, dim] [sorted]; bits: uint32 [rows_pad] [sorted] (1<<class, 0 = invalid);
+ * inv_norm: float [rows_pad] [sorted]; perm: int32 [n]; tor: uint32 [rows_pad/128];
+ * seg: uint32 [num_classes+2] first sorted row of every class, of the invalid pixels, and n. */
 int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
                            int dim, const void* cls, int cls_is_int64, int num_classes, float eps,
-                           void* ehat, uint32_t* bits, float* inv_norm, float* class_sum,
-                           float* class_mass, void* stream);
+                           void* ehat, uint32_t* bits, float* inv_norm, int32_t* perm,
+                           uint32_t* tor, uint32_t* seg, float* class_sum, float* class_mass,
+                           void* scratch, size_t scratch_bytes, void* stream);
 
-/* pos[q] = e_q . proto_{c_q} / T and rowsum[q] = exp(pos[q] - bound/T) (0 for invalid rows). */
-int muscle_infonce_pos(const void* ehat, const uint32_t* bits, int64_t n_rows, int64_t rows_pad,
-                       int dim, int num_classes, const float* class_sum, const float* class_mass,
-                       float temperature, const float* bound, float* pos, float* rowsum,
-                       void* stream);
+/* rowsum[q] += sum_k [cls_k != cls_q] exp((e_q.e_k - 1)/T)   — tcgen05 pass 1 (caller zeroes
+ * rowsum first). */
+int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows,
+                          const uint32_t* tor_rows, int64_t rows_pad, const void* ehat_cols,
+                          const uint32_t* bits_cols, const uint32_t* tor_cols, int64_t cols_pad,
+                          int dim, float temperature, float* rowsum, void* stream);
 
-/* rowsum[q] += sum_k [cls_k != cls_q] exp((e_q.e_k - bound)/T)   — tcgen05 pass 1. */
-int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows, int64_t rows_pad,
-                          const void* ehat_cols, const uint32_t* bits_cols, int64_t cols_pad,
-                          int dim, float temperature, const float* bound, float* rowsum,
-                          void* stream);
+/* pos[q] = e_q . proto_{c_q} / T; rowsum[q] += exp(pos - 1/T); w[q] = 1/rowsum[q];
+ * gpos[q] = (exp(pos - 1/T) w - 1)/T; loss_acc (double[1]) += sum_q (1/T + ln rowsum[q] - pos);
+ * dproto [C*dim] += gpos[q] e_q  (accumulated: caller zeroes loss_acc and dproto).
+ * Rows outside every class get w = gpos = 0.  class_sum / class_mass are the GLOBAL sums. */
+int muscle_infonce_mid(const void* ehat, const uint32_t* seg, int64_t rows_pad, int dim,
+                       int num_classes, const float* class_sum, const float* class_mass,
+                       float* rowsum, float temperature, float* w, float* gpos, double* loss_acc,
+                       float* dproto, void* stream);
 
-/* w[q] = 1/rowsum[q] (0 for invalid rows), gpos[q] = (exp(pos-bound/T) w - 1)/T,
- * loss_acc (double[1]) += sum_q (bound/T + ln rowsum[q] - pos[q]),
- * dproto [C*dim] += gpos[q] * e_q  (both accumulated: caller zeroes them). */
-int muscle_infonce_mid(const void* ehat, const uint32_t* bits, int64_t n_rows, int dim,
-                       int num_classes, const float* pos, const float* rowsum,
-                       float temperature, const float* bound, float* w, float* gpos,
-                       double* loss_acc, float* dproto, void* stream);
-
-/* part[s][q][:] = sum_{k in split s} [cls_k != cls_q] exp((e_q.e_k - bound)/T) (w_rows[q] +
+/* part[s][q][:] = sum_{k in split s} [cls_k != cls_q] exp((e_q.e_k - 1)/T) (w_rows[q] +
  * w_cols[k]) e_k   — tcgen05 pass 2.  part: float [n_split, rows_pad, dim]. */
 int muscle_infonce_grad_splits(int64_t rows_pad, int64_t cols_pad, int dim);
-int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows, const float* w_rows,
-                        int64_t rows_pad, const void* ehat_cols, const uint32_t* bits_cols,
-                        const float* w_cols, int64_t cols_pad, int dim, float temperature,
-                        const float* bound, float* part, int n_split, void* stream);
+int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows,
+                        const uint32_t* tor_rows, const float* w_rows, int64_t rows_pad,
+                        const void* ehat_cols, const uint32_t* bits_cols,
+                        const uint32_t* tor_cols, const float* w_cols, int64_t cols_pad, int dim,
+                        float temperature, float* part, int n_split, void* stream);
 
-/* dx = d(loss)/dx: sums the splits, adds the prototype terms, back-propagates through the
- * L2 normalisation and writes `layout`.  loss_out = loss_acc / n_valid (n_valid = sum of
- * class_mass).  dx may be NULL (loss only). */
+/* dx = d(loss)/dx in the caller's pixel order and `layout`: sums the splits, adds the prototype
+ * terms, back-propagates through the L2 normalisation.  loss_out = loss_acc / n_valid
+ * (n_valid = sum of class_mass).  dx may be NULL (loss only). */
 int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* inv_norm,
-                         const float* part, int n_split, int64_t rows_pad, int64_t batch,
-                         int64_t pixels_per_image, int dim, int num_classes,
+                         const int32_t* perm, const float* part, int n_split, int64_t rows_pad,
+                         int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
                          const float* class_sum, const float* class_mass, const float* gpos,
                          const float* dproto, const double* loss_acc, float temperature,
                          int layout, float* dx, float* loss_out, void* stream);

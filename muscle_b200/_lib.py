@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libmuscle_b200.so")
 MUSCLE_OK = 0
 LAYOUT_PIXEL_MAJOR = 0
 LAYOUT_NCHW = 1
-MAX_CLASSES = 32
+MAX_CLASSES = 31
 
 # name -> (restype, argtypes); mirrors include/muscle_b200.h one to one
 _SIGNATURES = {
@@ -25,20 +25,20 @@ _SIGNATURES = {
     "muscle_dense_infonce_workspace_bytes": (c_size_t, [c_int64, c_int, c_int]),
     "muscle_dense_infonce_fwd_bwd": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int, c_void_p, c_int, c_int,
                                              c_float, c_float, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "muscle_infonce_prepare_scratch_bytes": (c_size_t, [c_int64]),
     "muscle_infonce_prepare": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int, c_void_p, c_int, c_int, c_float,
-                                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
-    "muscle_infonce_pos": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p,
-                                   c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
-    "muscle_infonce_rowsum": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int, c_float,
-                                      c_void_p, c_void_p, c_void_p]),
-    "muscle_infonce_mid": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_float,
-                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+                                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_void_p, c_size_t, c_void_p]),
+    "muscle_infonce_rowsum": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64,
+                                      c_int, c_float, c_void_p, c_void_p]),
+    "muscle_infonce_mid": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                   c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "muscle_infonce_grad_splits": (c_int, [c_int64, c_int64, c_int]),
-    "muscle_infonce_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64,
-                                    c_int, c_float, c_void_p, c_void_p, c_int, c_void_p]),
-    "muscle_infonce_final": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64, c_int64,
-                                     c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float,
-                                     c_int, c_void_p, c_void_p, c_void_p]),
+    "muscle_infonce_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p,
+                                    c_void_p, c_int64, c_int, c_float, c_void_p, c_int, c_void_p]),
+    "muscle_infonce_final": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64,
+                                     c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_float, c_int, c_void_p, c_void_p, c_void_p]),
     "muscle_debug_tile": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
 }
 

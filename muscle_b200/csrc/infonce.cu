@@ -41,7 +41,7 @@ int choose_splits(int64_t n_row_blocks, int64_t n_col_tiles, int sm_count, int m
   return best;
 }
 
-template <int D, int MODE>
+template <int D, int MODE, int POLY>
 int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, int64_t cols_pad,
                 PairParams prm, cudaStream_t stream) {
   using C = PairCfg<D>;
@@ -50,7 +50,7 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
   if (rc) return rc;
   rc = make_bf16_tile_map(&tm_col, ehat_cols, cols_pad, D);
   if (rc) return rc;
-  auto kern = pair_kernel<D, MODE>;
+  auto kern = pair_kernel<D, MODE, POLY>;
   static thread_local bool attr_set = false;
   if (!attr_set) {
     MB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
@@ -63,70 +63,88 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
   return MUSCLE_OK;
 }
 
+// The FMA-pipe exponential is exact enough only while the exponent stays in range:
+// x = (s - 1) log2(e)/T lies in [-2 log2(e)/T, ~0].
+constexpr int kPoly = 2;  // of every 4 element pairs
+bool poly_ok(float temperature) { return 2.f * kLog2e / temperature < 100.f; }
+
 template <int MODE>
-int launch_pair_dim(int dim, const void* ehat_rows, int64_t rows_pad, const void* ehat_cols,
-                    int64_t cols_pad, PairParams prm, cudaStream_t stream) {
+int launch_pair_dim(int dim, bool poly, const void* ehat_rows, int64_t rows_pad,
+                    const void* ehat_cols, int64_t cols_pad, PairParams prm, cudaStream_t stream) {
+#define MB_PAIR(DD)                                                                              \
+  return poly ? launch_pair<DD, MODE, kPoly>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream) \
+              : launch_pair<DD, MODE, 0>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream);
   switch (dim) {
-    case 64: return launch_pair<64, MODE>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream);
-    case 128: return launch_pair<128, MODE>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream);
-    case 256: return launch_pair<256, MODE>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream);
+    case 64: MB_PAIR(64)
+    case 128: MB_PAIR(128)
+    case 256: MB_PAIR(256)
   }
+#undef MB_PAIR
   return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
 }
 
 int rows_per_block(int dim) { return dim == 256 ? 128 : 256; }
 
-size_t class_smem_bytes(int C, int D) { return (static_cast<size_t>(C) * D + C + 4) * sizeof(float); }
-size_t tile_smem_bytes(int D) { return static_cast<size_t>(TILE_PX) * (D + 1) * sizeof(float); }
-
-int row_grid(int64_t work_items) {
-  const int cap = device_info().sm_count * 8;
-  return static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(work_items, cap)));
-}
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 }  // namespace
 
 extern "C" {
 
 const char* muscle_last_error(void) { return err_buf(); }
-int muscle_version(void) { return 100; }
+int muscle_version(void) { return 200; }
 int64_t muscle_pad_rows(int64_t n) { return round_up(std::max<int64_t>(n, 1), 256); }
+
+size_t muscle_infonce_prepare_scratch_bytes(int64_t n_pixels) {
+  const int64_t n_blk = (std::max<int64_t>(n_pixels, 1) + SORT_CHUNK - 1) / SORT_CHUNK;
+  return align_up(static_cast<size_t>(n_blk) * MAX_BINS * sizeof(uint32_t), 256);
+}
 
 int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
                            int dim, const void* cls, int cls_is_int64, int num_classes, float eps,
-                           void* ehat, uint32_t* bits, float* inv_norm, float* class_sum,
-                           float* class_mass, void* stream_) {
+                           void* ehat, uint32_t* bits, float* inv_norm, int32_t* perm,
+                           uint32_t* tor, uint32_t* seg, float* class_sum, float* class_mass,
+                           void* scratch, size_t scratch_bytes, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_device()) return rc;
-  if (!x || !cls || !ehat || !bits || !inv_norm || !class_sum || !class_mass)
+  if (!x || !cls || !ehat || !bits || !inv_norm || !perm || !tor || !seg || !class_sum ||
+      !class_mass || !scratch)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
   if (num_classes < 1 || num_classes > MUSCLE_MAX_CLASSES)
     return fail(MUSCLE_ERR_BAD_ARG, "num_classes must be in [1,%d]", MUSCLE_MAX_CLASSES);
   if (layout != MUSCLE_LAYOUT_PIXEL_MAJOR && layout != MUSCLE_LAYOUT_NCHW)
     return fail(MUSCLE_ERR_BAD_ARG, "unknown layout %d", layout);
-  if (batch < 0 || pixels_per_image < 0) return fail(MUSCLE_ERR_BAD_ARG, "negative size");
+  if (batch <= 0 || pixels_per_image <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty input");
   const int64_t n = batch * pixels_per_image;
+  if (n >= (1ll << 31) - 256) return fail(MUSCLE_ERR_BAD_ARG, "too many pixels for one rank");
+  if (scratch_bytes < muscle_infonce_prepare_scratch_bytes(n))
+    return fail(MUSCLE_ERR_WORKSPACE, "prepare scratch too small");
   const int64_t rows_pad = muscle_pad_rows(n);
-  // pad rows: zero vectors that belong to no class
+  const int n_blk = static_cast<int>((n + SORT_CHUNK - 1) / SORT_CHUNK);
+  uint32_t* hist = static_cast<uint32_t*>(scratch);
+  // pad rows (and anything the scatter does not reach) are zero vectors that belong to no class
   MB_CUDA(cudaMemsetAsync(static_cast<char*>(ehat) + n * dim * 2, 0, (rows_pad - n) * dim * 2, stream));
   MB_CUDA(cudaMemsetAsync(bits + n, 0, (rows_pad - n) * sizeof(uint32_t), stream));
-  if (n == 0) return MUSCLE_OK;
+  MB_CUDA(cudaMemsetAsync(inv_norm + n, 0, (rows_pad - n) * sizeof(float), stream));
+  class_hist_kernel<<<n_blk, SORT_CHUNK, 0, stream>>>(cls, cls_is_int64, n, num_classes, hist);
+  MB_LAUNCH_CHECK();
+  class_scan_kernel<<<1, 1024, 0, stream>>>(hist, n_blk, num_classes, n, rows_pad, seg, class_mass, tor);
+  MB_LAUNCH_CHECK();
   PrepareParams p;
   p.x = x; p.cls = cls; p.cls64 = cls_is_int64; p.layout = layout; p.n = n;
-  p.ppi = pixels_per_image; p.C = num_classes; p.eps = eps;
-  p.ehat = static_cast<__nv_bfloat16*>(ehat); p.bits = bits; p.inv_norm = inv_norm;
-  p.class_sum = class_sum; p.class_mass = class_mass;
-  const size_t smem = tile_smem_bytes(dim) + class_smem_bytes(num_classes, dim);
-  const int64_t tiles = (layout == MUSCLE_LAYOUT_NCHW)
-                            ? batch * ((pixels_per_image + TILE_PX - 1) / TILE_PX)
-                            : (n + TILE_PX - 1) / TILE_PX;
-  const int grid = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(tiles, device_info().sm_count * 3)));
+  p.ppi = pixels_per_image; p.C = num_classes; p.eps = eps; p.chunk_off = hist;
+  p.ehat = static_cast<__nv_bfloat16*>(ehat); p.bits = bits; p.inv_norm = inv_norm; p.perm = perm;
+  const size_t smem = (layout == MUSCLE_LAYOUT_NCHW)
+                          ? static_cast<size_t>(SORT_CHUNK) * (dim / 2 + 1) * sizeof(uint32_t) : 0;
+  const int n_tiles = static_cast<int>(rows_pad / 128);
 #define MB_PREP(DD)                                                                               \
   {                                                                                               \
     MB_CUDA(cudaFuncSetAttribute(prepare_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                 static_cast<int>(smem)));                                        \
-    prepare_kernel<DD><<<grid, ROW_THREADS, smem, stream>>>(p);                                   \
+                                 static_cast<int>(SORT_CHUNK * (DD / 2 + 1) * sizeof(uint32_t)))); \
+    prepare_kernel<DD><<<n_blk, SORT_CHUNK, smem, stream>>>(p);                                   \
+    MB_LAUNCH_CHECK();                                                                            \
+    class_sum_kernel<DD><<<n_tiles, SEG_THREADS, 0, stream>>>(p.ehat, seg, num_classes, class_sum); \
   }
   if (dim == 64) MB_PREP(64) else if (dim == 128) MB_PREP(128) else MB_PREP(256)
 #undef MB_PREP
@@ -134,76 +152,50 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
   return MUSCLE_OK;
 }
 
-int muscle_infonce_pos(const void* ehat, const uint32_t* bits, int64_t n_rows, int64_t rows_pad,
-                       int dim, int num_classes, const float* class_sum, const float* class_mass,
-                       float temperature, const float* bound, float* pos, float* rowsum,
-                       void* stream_) {
+int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows,
+                          const uint32_t* tor_rows, int64_t rows_pad, const void* ehat_cols,
+                          const uint32_t* bits_cols, const uint32_t* tor_cols, int64_t cols_pad,
+                          int dim, float temperature, float* rowsum, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_device()) return rc;
-  if (!ehat || !bits || !class_sum || !class_mass || !bound || !pos || !rowsum)
+  if (!ehat_rows || !bits_rows || !tor_rows || !ehat_cols || !bits_cols || !tor_cols || !rowsum)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
-  (void)num_classes;
-  PosParams p;
-  p.ehat = static_cast<const __nv_bfloat16*>(ehat); p.bits = bits; p.n_rows = n_rows;
-  p.rows_pad = rows_pad; p.class_sum = class_sum; p.class_mass = class_mass; p.bound = bound;
-  p.inv_tau = 1.f / temperature; p.pos = pos; p.rowsum = rowsum;
-  const int grid = row_grid((rows_pad + ROW_WARPS - 1) / ROW_WARPS);
-  if (dim == 64) pos_kernel<64><<<grid, ROW_THREADS, 0, stream>>>(p);
-  else if (dim == 128) pos_kernel<128><<<grid, ROW_THREADS, 0, stream>>>(p);
-  else pos_kernel<256><<<grid, ROW_THREADS, 0, stream>>>(p);
-  MB_LAUNCH_CHECK();
-  return MUSCLE_OK;
-}
-
-int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows, int64_t rows_pad,
-                          const void* ehat_cols, const uint32_t* bits_cols, int64_t cols_pad,
-                          int dim, float temperature, const float* bound, float* rowsum,
-                          void* stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (int rc = check_device()) return rc;
-  if (!ehat_rows || !bits_rows || !ehat_cols || !bits_cols || !bound || !rowsum)
-    return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
-  if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
+  if (!(temperature > 0.f)) return fail(MUSCLE_ERR_BAD_ARG, "temperature must be > 0");
   if (rows_pad % 256 || cols_pad % 256 || rows_pad <= 0 || cols_pad <= 0)
     return fail(MUSCLE_ERR_BAD_ARG, "padded sizes must be positive multiples of 256");
   PairParams prm{};
-  prm.bits_row = bits_rows; prm.bits_col = bits_cols; prm.rowsum = rowsum; prm.bound = bound;
+  prm.bits_row = bits_rows; prm.bits_col = bits_cols; prm.tor_row = tor_rows; prm.tor_col = tor_cols;
+  prm.rowsum = rowsum;
   prm.scale_log2 = kLog2e / temperature;
   prm.n_row_blocks = static_cast<int>(rows_pad / rows_per_block(dim));
   prm.n_col_tiles = static_cast<int>(cols_pad / 128);
   prm.n_split = choose_splits(prm.n_row_blocks, prm.n_col_tiles, device_info().sm_count, 64);
   prm.rows_pad = static_cast<int>(rows_pad);
-  return launch_pair_dim<MODE_ROWSUM>(dim, ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream);
+  return launch_pair_dim<MODE_ROWSUM>(dim, poly_ok(temperature), ehat_rows, rows_pad, ehat_cols,
+                                      cols_pad, prm, stream);
 }
 
-int muscle_infonce_mid(const void* ehat, const uint32_t* bits, int64_t n_rows, int dim,
-                       int num_classes, const float* pos, const float* rowsum,
-                       float temperature, const float* bound, float* w, float* gpos,
-                       double* loss_acc, float* dproto, void* stream_) {
+int muscle_infonce_mid(const void* ehat, const uint32_t* seg, int64_t rows_pad, int dim,
+                       int num_classes, const float* class_sum, const float* class_mass,
+                       float* rowsum, float temperature, float* w, float* gpos, double* loss_acc,
+                       float* dproto, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_device()) return rc;
-  if (!ehat || !bits || !pos || !rowsum || !bound || !w || !gpos || !loss_acc || !dproto)
+  if (!ehat || !seg || !class_sum || !class_mass || !rowsum || !w || !gpos || !loss_acc || !dproto)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
   if (num_classes < 1 || num_classes > MUSCLE_MAX_CLASSES)
     return fail(MUSCLE_ERR_BAD_ARG, "num_classes must be in [1,%d]", MUSCLE_MAX_CLASSES);
-  if (n_rows <= 0) return MUSCLE_OK;
+  if (rows_pad <= 0 || rows_pad % 128) return fail(MUSCLE_ERR_BAD_ARG, "rows_pad must be a positive multiple of 128");
   MidParams p;
-  p.ehat = static_cast<const __nv_bfloat16*>(ehat); p.bits = bits; p.n_rows = n_rows;
-  p.C = num_classes; p.pos = pos; p.rowsum = rowsum; p.bound = bound;
+  p.ehat = static_cast<const __nv_bfloat16*>(ehat); p.seg = seg; p.C = num_classes;
+  p.class_sum = class_sum; p.class_mass = class_mass; p.rowsum = rowsum;
   p.inv_tau = 1.f / temperature; p.w = w; p.gpos = gpos; p.loss_acc = loss_acc; p.dproto = dproto;
-  const size_t smem = class_smem_bytes(num_classes, dim);
-  const int grid = static_cast<int>(std::max<int64_t>(
-      1, std::min<int64_t>((n_rows + ROW_WARPS * 16 - 1) / (ROW_WARPS * 16), device_info().sm_count * 4)));
-#define MB_MID(DD)                                                                             \
-  {                                                                                            \
-    MB_CUDA(cudaFuncSetAttribute(mid_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
-                                 static_cast<int>(smem)));                                     \
-    mid_kernel<DD><<<grid, ROW_THREADS, smem, stream>>>(p);                                    \
-  }
-  if (dim == 64) MB_MID(64) else if (dim == 128) MB_MID(128) else MB_MID(256)
-#undef MB_MID
+  const int grid = static_cast<int>(rows_pad / 128);
+  if (dim == 64) mid_kernel<64><<<grid, SEG_THREADS, 0, stream>>>(p);
+  else if (dim == 128) mid_kernel<128><<<grid, SEG_THREADS, 0, stream>>>(p);
+  else mid_kernel<256><<<grid, SEG_THREADS, 0, stream>>>(p);
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
 }
@@ -215,57 +207,66 @@ int muscle_infonce_grad_splits(int64_t rows_pad, int64_t cols_pad, int dim) {
   return choose_splits(rows_pad / rows_per_block(dim), cols_pad / 128, sms, 16);
 }
 
-int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows, const float* w_rows,
-                        int64_t rows_pad, const void* ehat_cols, const uint32_t* bits_cols,
-                        const float* w_cols, int64_t cols_pad, int dim, float temperature,
-                        const float* bound, float* part, int n_split, void* stream_) {
+int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows,
+                        const uint32_t* tor_rows, const float* w_rows, int64_t rows_pad,
+                        const void* ehat_cols, const uint32_t* bits_cols,
+                        const uint32_t* tor_cols, const float* w_cols, int64_t cols_pad, int dim,
+                        float temperature, float* part, int n_split, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_device()) return rc;
-  if (!ehat_rows || !bits_rows || !w_rows || !ehat_cols || !bits_cols || !w_cols || !bound || !part)
+  if (!ehat_rows || !bits_rows || !tor_rows || !w_rows || !ehat_cols || !bits_cols || !tor_cols ||
+      !w_cols || !part)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
+  if (!(temperature > 0.f)) return fail(MUSCLE_ERR_BAD_ARG, "temperature must be > 0");
   if (rows_pad % 256 || cols_pad % 256 || rows_pad <= 0 || cols_pad <= 0)
     return fail(MUSCLE_ERR_BAD_ARG, "padded sizes must be positive multiples of 256");
   if (n_split < 1 || n_split > cols_pad / 128)
     return fail(MUSCLE_ERR_BAD_ARG, "n_split must be in [1, cols_pad/128]");
   PairParams prm{};
-  prm.bits_row = bits_rows; prm.bits_col = bits_cols; prm.w_row = w_rows; prm.w_col = w_cols;
-  prm.part = part; prm.bound = bound; prm.scale_log2 = kLog2e / temperature;
+  prm.bits_row = bits_rows; prm.bits_col = bits_cols; prm.tor_row = tor_rows; prm.tor_col = tor_cols;
+  prm.w_row = w_rows; prm.w_col = w_cols; prm.part = part;
+  prm.scale_log2 = kLog2e / temperature;
   prm.n_row_blocks = static_cast<int>(rows_pad / rows_per_block(dim));
   prm.n_col_tiles = static_cast<int>(cols_pad / 128);
   prm.n_split = n_split;
   prm.rows_pad = static_cast<int>(rows_pad);
-  return launch_pair_dim<MODE_GRAD>(dim, ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream);
+  return launch_pair_dim<MODE_GRAD>(dim, poly_ok(temperature), ehat_rows, rows_pad, ehat_cols,
+                                    cols_pad, prm, stream);
 }
 
 int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* inv_norm,
-                         const float* part, int n_split, int64_t rows_pad, int64_t batch,
-                         int64_t pixels_per_image, int dim, int num_classes,
+                         const int32_t* perm, const float* part, int n_split, int64_t rows_pad,
+                         int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
                          const float* class_sum, const float* class_mass, const float* gpos,
                          const float* dproto, const double* loss_acc, float temperature,
                          int layout, float* dx, float* loss_out, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_device()) return rc;
   if (!class_mass || !loss_acc) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
-  if (dx && (!ehat || !bits || !inv_norm || !part || !class_sum || !gpos || !dproto))
+  if (dx && (!ehat || !bits || !inv_norm || !perm || !part || !class_sum || !gpos || !dproto))
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
   if (layout != MUSCLE_LAYOUT_PIXEL_MAJOR && layout != MUSCLE_LAYOUT_NCHW)
     return fail(MUSCLE_ERR_BAD_ARG, "unknown layout %d", layout);
   FinalParams p;
   p.ehat = static_cast<const __nv_bfloat16*>(ehat); p.bits = bits; p.inv_norm = inv_norm;
-  p.part = part; p.n_split = n_split; p.rows_pad = rows_pad; p.n = batch * pixels_per_image;
-  p.ppi = pixels_per_image; p.C = num_classes; p.class_sum = class_sum; p.class_mass = class_mass;
-  p.gpos = gpos; p.dproto = dproto; p.loss_acc = loss_acc; p.inv_tau = 1.f / temperature;
-  p.layout = layout; p.dx = dx; p.loss_out = loss_out;
-  const size_t smem = tile_smem_bytes(dim);
-  const int64_t tiles = (layout == MUSCLE_LAYOUT_NCHW)
-                            ? batch * ((pixels_per_image + TILE_PX - 1) / TILE_PX)
-                            : (p.n + TILE_PX - 1) / TILE_PX;
-  const int grid = dx ? static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(tiles, device_info().sm_count * 8))) : 1;
-  if (dim == 64) final_kernel<64><<<grid, ROW_THREADS, smem, stream>>>(p);
-  else if (dim == 128) final_kernel<128><<<grid, ROW_THREADS, smem, stream>>>(p);
-  else final_kernel<256><<<grid, ROW_THREADS, smem, stream>>>(p);
+  p.perm = perm; p.part = part; p.n_split = n_split; p.rows_pad = rows_pad;
+  p.n = batch * pixels_per_image; p.ppi = pixels_per_image; p.C = num_classes;
+  p.class_sum = class_sum; p.class_mass = class_mass; p.gpos = gpos; p.dproto = dproto;
+  p.loss_acc = loss_acc; p.inv_tau = 1.f / temperature; p.layout = layout; p.dx = dx;
+  p.loss_out = loss_out;
+  const size_t smem = (dx && layout == MUSCLE_LAYOUT_NCHW)
+                          ? static_cast<size_t>(SORT_CHUNK) * (dim + 1) * sizeof(float) : 0;
+  const int grid = dx ? static_cast<int>((p.n + SORT_CHUNK - 1) / SORT_CHUNK) : 1;
+#define MB_FINAL(DD)                                                                            \
+  {                                                                                             \
+    MB_CUDA(cudaFuncSetAttribute(final_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                 static_cast<int>(SORT_CHUNK * (DD + 1) * sizeof(float))));     \
+    final_kernel<DD><<<grid, SORT_CHUNK, smem, stream>>>(p);                                    \
+  }
+  if (dim == 64) MB_FINAL(64) else if (dim == 128) MB_FINAL(128) else MB_FINAL(256)
+#undef MB_FINAL
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
 }
@@ -277,13 +278,12 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
 namespace {
 
 struct Workspace {
-  size_t ehat, bits, inv_norm, pos, rowsum, w, gpos, small, part, total;
-  size_t class_sum, class_mass, dproto, loss_acc, bound, small_bytes;  // offsets inside `small`
+  size_t ehat, bits, inv_norm, perm, tor, rowsum, w, gpos, small, scratch, part, total;
+  size_t seg, class_sum, class_mass, dproto, loss_acc, small_bytes;  // offsets inside `small`
+  size_t zero_lo, zero_bytes;  // rowsum .. small are zeroed with one memset
   int n_split;
   int64_t rows_pad;
 };
-
-size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 Workspace plan_workspace(int64_t n, int dim, int C) {
   Workspace ws{};
@@ -295,25 +295,27 @@ Workspace plan_workspace(int64_t n, int dim, int C) {
   ws.ehat = take(rp * dim * 2);
   ws.bits = take(rp * 4);
   ws.inv_norm = take(rp * 4);
-  ws.pos = take(rp * 4);
-  ws.rowsum = take(rp * 4);
+  ws.perm = take(rp * 4);
+  ws.tor = take(rp / 128 * 4);
   ws.w = take(rp * 4);
   ws.gpos = take(rp * 4);
+  ws.rowsum = take(rp * 4);
   size_t s = 0;
   auto take_small = [&](size_t bytes) { size_t o = s; s = align_up(s + bytes, 16); return o; };
   ws.class_sum = take_small(static_cast<size_t>(C) * dim * 4);
   ws.class_mass = take_small(static_cast<size_t>(C) * 4);
   ws.dproto = take_small(static_cast<size_t>(C) * dim * 4);
   ws.loss_acc = take_small(8);
-  ws.bound = take_small(4);
+  ws.seg = take_small(static_cast<size_t>(C + 2) * 4);
   ws.small_bytes = s;
   ws.small = take(s);
+  ws.zero_lo = ws.rowsum;
+  ws.zero_bytes = off - ws.rowsum;
+  ws.scratch = take(muscle_infonce_prepare_scratch_bytes(n));
   ws.part = take(static_cast<size_t>(ws.n_split) * rp * dim * 4);
   ws.total = off;
   return ws;
 }
-
-__global__ void set_float_kernel(float* p, float v) { *p = v; }
 
 }  // namespace
 
@@ -347,7 +349,8 @@ int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
   void* ehat = base + ws.ehat;
   uint32_t* bits = reinterpret_cast<uint32_t*>(base + ws.bits);
   float* inv_norm = reinterpret_cast<float*>(base + ws.inv_norm);
-  float* pos = reinterpret_cast<float*>(base + ws.pos);
+  int32_t* perm = reinterpret_cast<int32_t*>(base + ws.perm);
+  uint32_t* tor = reinterpret_cast<uint32_t*>(base + ws.tor);
   float* rowsum = reinterpret_cast<float*>(base + ws.rowsum);
   float* w = reinterpret_cast<float*>(base + ws.w);
   float* gpos = reinterpret_cast<float*>(base + ws.gpos);
@@ -356,32 +359,27 @@ int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
   float* class_mass = reinterpret_cast<float*>(small + ws.class_mass);
   float* dproto = reinterpret_cast<float*>(small + ws.dproto);
   double* loss_acc = reinterpret_cast<double*>(small + ws.loss_acc);
-  float* bound = reinterpret_cast<float*>(small + ws.bound);
+  uint32_t* seg = reinterpret_cast<uint32_t*>(small + ws.seg);
   float* part = reinterpret_cast<float*>(base + ws.part);
 
-  MB_CUDA(cudaMemsetAsync(small, 0, ws.small_bytes, stream));
-  set_float_kernel<<<1, 1, 0, stream>>>(bound, 1.0f);
-  MB_LAUNCH_CHECK();
-  // w of pad rows (read as w_col by the gradient pass) must be 0
-  MB_CUDA(cudaMemsetAsync(w, 0, static_cast<size_t>(ws.rows_pad) * 4, stream));
+  MB_CUDA(cudaMemsetAsync(base + ws.zero_lo, 0, ws.zero_bytes, stream));
   int rc = muscle_infonce_prepare(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64,
-                                  num_classes, eps, ehat, bits, inv_norm, class_sum, class_mass, stream);
+                                  num_classes, eps, ehat, bits, inv_norm, perm, tor, seg, class_sum,
+                                  class_mass, base + ws.scratch,
+                                  muscle_infonce_prepare_scratch_bytes(n), stream);
   if (rc) return rc;
-  rc = muscle_infonce_pos(ehat, bits, n, ws.rows_pad, dim, num_classes, class_sum, class_mass,
-                          temperature, bound, pos, rowsum, stream);
+  rc = muscle_infonce_rowsum(ehat, bits, tor, ws.rows_pad, ehat, bits, tor, ws.rows_pad, dim,
+                             temperature, rowsum, stream);
   if (rc) return rc;
-  rc = muscle_infonce_rowsum(ehat, bits, ws.rows_pad, ehat, bits, ws.rows_pad, dim, temperature,
-                             bound, rowsum, stream);
-  if (rc) return rc;
-  rc = muscle_infonce_mid(ehat, bits, n, dim, num_classes, pos, rowsum, temperature, bound, w,
-                          gpos, loss_acc, dproto, stream);
+  rc = muscle_infonce_mid(ehat, seg, ws.rows_pad, dim, num_classes, class_sum, class_mass, rowsum,
+                          temperature, w, gpos, loss_acc, dproto, stream);
   if (rc) return rc;
   if (dx_out) {
-    rc = muscle_infonce_grad(ehat, bits, w, ws.rows_pad, ehat, bits, w, ws.rows_pad, dim,
-                             temperature, bound, part, ws.n_split, stream);
+    rc = muscle_infonce_grad(ehat, bits, tor, w, ws.rows_pad, ehat, bits, tor, w, ws.rows_pad, dim,
+                             temperature, part, ws.n_split, stream);
     if (rc) return rc;
   }
-  return muscle_infonce_final(ehat, bits, inv_norm, part, ws.n_split, ws.rows_pad, batch,
+  return muscle_infonce_final(ehat, bits, inv_norm, perm, part, ws.n_split, ws.rows_pad, batch,
                               pixels_per_image, dim, num_classes, class_sum, class_mass, gpos,
                               dproto, loss_acc, temperature, layout, dx_out, loss_out, stream);
 }

@@ -1,24 +1,32 @@
-// The dense pixel-pair mainloop shared by the InfoNCE row-sum pass, the InfoNCE gradient pass
-// and the PCM (ReLU-affinity) passes.
+// The dense pixel-pair mainloop of the InfoNCE row-sum pass and the InfoNCE gradient pass.
 //
 // One persistent CTA per SM, warp-specialised:
 //   warps 0-3  epilogue group 0  (TMEM lanes 32*(warp%4) .. +31, thread = one row of a 128-row tile)
 //   warps 4-7  epilogue group 1
-//   warp  8    TMA producer      (row tile once per work item, column tiles through a ring)
+//   warp  8    TMA producer      (row tiles once per work item, column tiles through a ring)
 //   warp  9    tcgen05.mma issuer (one lane) + TMEM allocator
 //
-// Work item = (row block, column split).  Per column tile of 128 pixels and per "slot"
-// (two S buffers in TMEM, one per epilogue group):
-//   S = R C^T        tcgen05.mma SS, bf16 x bf16 -> fp32 in TMEM        [128 x 128]
-//   epilogue         tcgen05.ld S, e = exp2(a*s - a*bound), label mask, then
-//       MODE_ROWSUM: row-sum of e kept in registers, one atomicAdd per row per item
-//       MODE_GRAD  : T = e * (w_row + w_col) -> bf16 -> tcgen05.st into the S columns
-//   (MODE_GRAD) G += T C   tcgen05.mma TS: A = T from TMEM, B = the same column tile, MN-major
-// so the N x N logits never leave the SM.
+// Work item = (row block, column split).  Pixels arrive sorted by class (row_kernels.cuh), and a
+// per-tile class union (`tor`) lets the producer drop every (row block, column tile) whose pairs
+// are all masked (same single class) before anything is loaded or multiplied; the epilogue takes a
+// mask-free path for tiles whose class sets are disjoint.
 //
-// TMEM columns: [0,128) S slot 0 (T aliases its first 64), [128,256) S slot 1, [256,512) G.
-// D = 64/128: two row tiles per item (slot == row tile, two accumulators of D columns);
-// D = 256    : one row tile per item, the two slots alternate column tiles into one accumulator.
+// Two "streams" run through the tensor pipe, one per epilogue group (D <= 128: stream = row
+// tile, both see every column tile; D = 256: one row tile, the streams alternate column tiles).
+// Within a stream every 128 x 128 similarity tile is produced and consumed as two 64-column halves
+// held in two TMEM buffers, so the group's epilogue on one half always overlaps the stream's MMAs
+// on the other:
+//   S_h = R C_h^T      tcgen05.mma SS, bf16 x bf16 -> fp32 in TMEM            [128 x 64]
+//   epilogue           tcgen05.ld S_h, e = exp2(a*s - a), label mask, then
+//       MODE_ROWSUM : row-sum of e kept in registers, one atomicAdd per row per item
+//       MODE_GRAD   : T_h = e * (w_row + w_col) -> bf16 -> tcgen05.st over the S_h columns
+//   (MODE_GRAD) G += T_h C_h   tcgen05.mma TS: A = T_h from TMEM, B = the same column rows, MN-major
+// so the N x N logits never leave the SM.  A share of the exponentials is evaluated with a cubic on
+// the FMA pipe (ptx.cuh: ex2_poly2) because MUFU alone (16/clk/SM) would cap the pass below the
+// tensor pipe; all elementwise math is packed fp32x2.
+//
+// TMEM columns: stream g: S halves at [128g, 128g+64) and [128g+64, 128g+128), T_h aliases the
+// first 32 columns of S_h; G accumulators from column 256 (D <= 128: one per stream; D = 256: one).
 #pragma once
 #include "ptx.cuh"
 
@@ -26,14 +34,18 @@ namespace mb200 {
 
 enum PairMode { MODE_ROWSUM = 0, MODE_GRAD = 1 };
 
+constexpr uint32_t TOR_INVALID = 0x80000000u;  // tile contains a pixel that is in no class
+constexpr uint32_t TOR_CLASSES = 0x7fffffffu;
+
 struct PairParams {
   const uint32_t* bits_row;  // [rows_pad]  1<<class, 0 = pixel not in the loss
   const uint32_t* bits_col;  // [cols_pad]
+  const uint32_t* tor_row;   // [rows_pad/128]  OR of bits over the tile | TOR_INVALID
+  const uint32_t* tor_col;   // [cols_pad/128]
   const float* w_row;        // [rows_pad]  MODE_GRAD: 1/rowsum of the row pixel (0 = no query role)
-  const float* w_col;        // [cols_pad]  MODE_GRAD: 1/rowsum of the column pixel (0 = no key->query role)
-  float* rowsum;             // [rows_pad]  MODE_ROWSUM: += sum_k mask * exp((s - bound)/tau)
+  const float* w_col;        // [cols_pad]  MODE_GRAD: 1/rowsum of the column pixel
+  float* rowsum;             // [rows_pad]  MODE_ROWSUM: += sum_k mask * exp((s - 1)/tau)
   float* part;               // [n_split][rows_pad][D]  MODE_GRAD: partial sum_k T_qk c_k
-  const float* bound;        // device scalar: upper bound of |s| (1 for unit vectors)
   float scale_log2;          // log2(e) / tau
   int n_row_blocks;          // row blocks of RB rows
   int n_col_tiles;           // column tiles of 128
@@ -55,14 +67,87 @@ struct PairCfg {
   static constexpr int SMEM_BITS = SMEM_K + NST * TILE_BYTES;
   static constexpr int SMEM_W = SMEM_BITS + NST * 512;
   static constexpr int SMEM_BAR = SMEM_W + NST * 512;
-  static constexpr int NBAR = 2 * NST + 12;
-  static constexpr int SMEM_TMEMPTR = SMEM_BAR + NBAR * 8;
+  static constexpr int NBAR = 2 * NST + 14;
+  static constexpr int SMEM_INFO = SMEM_BAR + NBAR * 8;  // item header [2], stage info [NST]
+  static constexpr int SMEM_TMEMPTR = SMEM_INFO + (2 + NST) * 4;
   static constexpr int SMEM_BYTES = SMEM_TMEMPTR + 16 + 1024;  // +1024: manual 1024-B alignment
   static constexpr int ACC_COL = 256;
   static constexpr int THREADS = 320;
 };
 
-template <int D, int MODE>
+// all pairs of (row tile, column tile) masked: one side empty, or both the same single class
+__device__ __forceinline__ bool tile_pair_dead(uint32_t tor_r, uint32_t tor_c) {
+  const uint32_t r = tor_r & TOR_CLASSES, c = tor_c & TOR_CLASSES;
+  return r == 0u || c == 0u || (r == c && (r & (r - 1u)) == 0u);
+}
+// no pair masked: disjoint class sets and every column pixel valid
+__device__ __forceinline__ bool tile_pair_full(uint32_t tor_r, uint32_t tor_c) {
+  return (tor_r & tor_c & TOR_CLASSES) == 0u && (tor_c & TOR_INVALID) == 0u;
+}
+
+// Epilogue of one 64-column half for one thread (= one row).  FULL: no label mask needed.
+// POLY of every 4 element pairs take the FMA-pipe exponential.
+template <int MODE, int POLY, bool FULL>
+__device__ __forceinline__ void pair_half_epilogue(uint32_t s_addr, const uint8_t* bits_sm,
+                                                   const uint8_t* w_sm, uint32_t qmask, float a,
+                                                   float wrow, uint64_t (&racc)[4]) {
+  uint32_t v[2][32];
+  tmem_ld32(s_addr, v[0]);
+  tmem_ld32(s_addr + 32, v[1]);
+  tmem_wait_ld();
+  const uint64_t a2 = pack2(a, a);
+  const uint64_t noff2 = pack2(-a, -a);  // the shift: exp((s - 1)/tau), |s| <= 1 for unit vectors
+  const uint64_t wr2 = pack2(wrow, wrow);
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    const uint4* kb4 = reinterpret_cast<const uint4*>(bits_sm) + c * 8;
+    const float4* kw4 = reinterpret_cast<const float4*>(w_sm) + c * 8;
+    uint32_t packed[16];
+#pragma unroll
+    for (int q4 = 0; q4 < 8; ++q4) {
+      uint64_t e[2];
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        const uint64_t x = fma2(pack2u(v[c][q4 * 4 + 2 * s], v[c][q4 * 4 + 2 * s + 1]), a2, noff2);
+        if (((q4 * 2 + s) & 3) < POLY) {
+          e[s] = ex2_poly2(x);
+        } else {
+          float x0, x1;
+          unpack2(x, x0, x1);
+          e[s] = pack2(ex2_approx(x0), ex2_approx(x1));
+        }
+      }
+      if (!FULL) {
+        const uint4 kb = kb4[q4];
+        float e0, e1, e2, e3;
+        unpack2(e[0], e0, e1);
+        unpack2(e[1], e2, e3);
+        e0 = (kb.x & qmask) ? e0 : 0.f;
+        e1 = (kb.y & qmask) ? e1 : 0.f;
+        e2 = (kb.z & qmask) ? e2 : 0.f;
+        e3 = (kb.w & qmask) ? e3 : 0.f;
+        e[0] = pack2(e0, e1);
+        e[1] = pack2(e2, e3);
+      }
+      if (MODE == MODE_ROWSUM) {
+        racc[(q4 * 2) & 3] = add2(racc[(q4 * 2) & 3], e[0]);
+        racc[(q4 * 2 + 1) & 3] = add2(racc[(q4 * 2 + 1) & 3], e[1]);
+      } else {
+        const float4 kw = kw4[q4];
+        const uint64_t t0 = mul2(e[0], add2(wr2, pack2(kw.x, kw.y)));
+        const uint64_t t1 = mul2(e[1], add2(wr2, pack2(kw.z, kw.w)));
+        float f0, f1, f2, f3;
+        unpack2(t0, f0, f1);
+        unpack2(t1, f2, f3);
+        packed[q4 * 2 + 0] = pack_bf16x2(f0, f1);
+        packed[q4 * 2 + 1] = pack_bf16x2(f2, f3);
+      }
+    }
+    if (MODE == MODE_GRAD) tmem_st16(s_addr + c * 16, packed);
+  }
+}
+
+template <int D, int MODE, int POLY>
 __global__ void __launch_bounds__(320, 1)
 pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ CUtensorMap tm_col,
             const PairParams p) {
@@ -82,11 +167,12 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
   auto k_empty = [&](int s) { return bar0 + 8u * (NST + s); };
   const uint32_t q_full = bar0 + 8u * (2 * NST);
   const uint32_t q_empty = bar0 + 8u * (2 * NST + 1);
-  auto s_full = [&](int s) { return bar0 + 8u * (2 * NST + 2 + s); };
-  auto s_free = [&](int s) { return bar0 + 8u * (2 * NST + 4 + s); };
-  auto t_full = [&](int s) { return bar0 + 8u * (2 * NST + 6 + s); };
-  auto acc_full = [&](int s) { return bar0 + 8u * (2 * NST + 8 + s); };
-  auto acc_empty = [&](int s) { return bar0 + 8u * (2 * NST + 10 + s); };
+  auto s_full = [&](int g, int h) { return bar0 + 8u * (2 * NST + 2 + g * 2 + h); };
+  auto t_full = [&](int g, int h) { return bar0 + 8u * (2 * NST + 6 + g * 2 + h); };  // GRAD: T stored; ROWSUM: S consumed
+  auto acc_full = [&](int s) { return bar0 + 8u * (2 * NST + 10 + s); };
+  auto acc_empty = [&](int s) { return bar0 + 8u * (2 * NST + 12 + s); };
+  volatile uint32_t* info = reinterpret_cast<volatile uint32_t*>(smem_gen + C::SMEM_INFO);
+  // info[0..1]: tiles of the item (double-buffered by item parity); info[2+st]: tor of the stage's column tile
   volatile uint32_t* tmem_ptr_smem =
       reinterpret_cast<volatile uint32_t*>(smem_gen + C::SMEM_TMEMPTR);
 
@@ -99,13 +185,14 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
       mbar_init(k_empty(s), 1 + (QT == 2 ? 8 : 4));
     }
     mbar_init(q_full, 1);
-    mbar_init(q_empty, 1);
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(s_full(s), 1);
-      mbar_init(s_free(s), 4);
-      mbar_init(t_full(s), 4);
-      mbar_init(acc_full(s), 1);
-      mbar_init(acc_empty(s), QT == 2 ? 4 : 8);
+    mbar_init(q_empty, 1 + 8);  // MMA issuer + every epilogue warp (after it has read the item header)
+    for (int g = 0; g < 2; ++g) {
+      for (int h = 0; h < 2; ++h) {
+        mbar_init(s_full(g, h), 1);
+        mbar_init(t_full(g, h), 4);
+      }
+      mbar_init(acc_full(g), 1);
+      mbar_init(acc_empty(g), QT == 2 ? 4 : 8);
     }
     fence_barrier_init();
   }
@@ -129,23 +216,39 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
     t0 = static_cast<int>((static_cast<long long>(p.n_col_tiles) * ks) / p.n_split);
     t1 = static_cast<int>((static_cast<long long>(p.n_col_tiles) * (ks + 1)) / p.n_split);
   };
+  // stream-local tile k of stream g -> index within the item's list of live column tiles
+  auto n_stream = [&](int n, int g) { return (QT == 2) ? n : ((n - g + 1) >> 1); };
+  auto tile_of = [&](int g, int k) { return (QT == 2) ? k : (2 * k + g); };
 
   if (warp == 8) {
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      uint32_t g = 0, it = 0;
+      uint32_t gcnt = 0, it = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
         int rb, ks, t0, t1;
         item_range(item, rb, ks, t0, t1);
+        uint32_t tor_r[QT];
+        for (int qt = 0; qt < QT; ++qt) tor_r[qt] = __ldg(p.tor_row + rb * QT + qt);
+        auto dead = [&](uint32_t tc) {
+          bool d = true;
+          for (int qt = 0; qt < QT; ++qt) d = d && tile_pair_dead(tor_r[qt], tc);
+          return d;
+        };
+        uint32_t n = 0;
+        for (int j = t0; j < t1; ++j) n += dead(__ldg(p.tor_col + j)) ? 0u : 1u;
         mbar_wait(q_empty, (it & 1) ^ 1);
+        info[it & 1] = n;
         mbar_arrive_expect_tx(q_full, QT * C::TILE_BYTES);
         for (int qt = 0; qt < QT; ++qt)
           for (int a = 0; a < C::NPANEL; ++a)
             tma_load_2d(q_smem + qt * C::TILE_BYTES + a * C::PANEL_BYTES, &tm_row, q_full, a * 64,
                         (rb * QT + qt) * 128);
-        for (int j = t0; j < t1; ++j, ++g) {
-          const int st = g % NST;
-          mbar_wait(k_empty(st), ((g / NST) & 1) ^ 1);
+        for (int j = t0; j < t1; ++j) {
+          const uint32_t tc = __ldg(p.tor_col + j);
+          if (dead(tc)) continue;
+          const int st = gcnt % NST;
+          mbar_wait(k_empty(st), ((gcnt / NST) & 1) ^ 1);
+          info[2 + st] = tc;
           mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES + 512 + (MODE == MODE_GRAD ? 512 : 0));
           for (int a = 0; a < C::NPANEL; ++a)
             tma_load_2d(k_smem + st * C::TILE_BYTES + a * C::PANEL_BYTES, &tm_col, k_full(st),
@@ -155,181 +258,180 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           if (MODE == MODE_GRAD)
             bulk_load_1d(w_smem + st * 512, p.w_col + static_cast<size_t>(j) * 128, 512,
                          k_full(st));
+          ++gcnt;
         }
       }
     }
   } else if (warp == 9) {
     // ------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      constexpr uint32_t IDESC_S = umma_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t IDESC_S = umma_idesc_bf16(128, 64, 0, 0);
       constexpr uint32_t IDESC_G = umma_idesc_bf16(128, D, 0, 1);
-      uint32_t g = 0, it = 0;
-      uint32_t cnt_s[2] = {0, 0};
-      uint32_t cnt_t[2] = {0, 0};
+      uint32_t gbase = 0, it = 0, ita = 0;
+      uint32_t cnt_t[2][2] = {{0, 0}, {0, 0}};
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-        int rb, ks, t0, t1;
-        item_range(item, rb, ks, t0, t1);
-        const int nkt = t1 - t0;
-        const int U = (QT == 2) ? 2 * nkt : nkt;
         mbar_wait(q_full, it & 1);
         tc_fence_after();
+        const int n = static_cast<int>(info[it & 1]);
+        if (n == 0) {
+          mbar_arrive(q_empty);
+          continue;
+        }
+        const int nk[2] = {n_stream(n, 0), n_stream(n, 1)};
+        const int kmax = nk[0];  // nk[0] >= nk[1]
 
-        auto issue_S = [&](int u) {
-          const int slot = u & 1;
-          const int j = (QT == 2) ? (u >> 1) : u;
-          const uint32_t gg = g + j;
-          const int st = gg % NST;
-          if (QT == 1 || slot == 0) {
-            mbar_wait(k_full(st), (gg / NST) & 1);
-            tc_fence_after();
-          }
-          if (MODE == MODE_ROWSUM) {
-            mbar_wait(s_free(slot), (cnt_s[slot] & 1) ^ 1);
-            tc_fence_after();
-          }
-          const uint32_t a_base = q_smem + (QT == 2 ? slot * C::TILE_BYTES : 0);
-          const uint32_t b_base = k_smem + st * C::TILE_BYTES;
+        auto stage_of = [&](int g, int k, uint32_t& par) {
+          const uint32_t gg = gbase + tile_of(g, k);
+          par = (gg / NST) & 1;
+          return static_cast<int>(gg % NST);
+        };
+        auto issue_S = [&](int g, int k, int h) {
+          uint32_t par;
+          const int st = stage_of(g, k, par);
+          mbar_wait(k_full(st), par);
+          tc_fence_after();
+          const uint32_t a_base = q_smem + (QT == 2 ? g * C::TILE_BYTES : 0);
+          const uint32_t b_base = k_smem + st * C::TILE_BYTES + h * 8192;
 #pragma unroll
           for (int kk = 0; kk < D / 16; ++kk) {
             const uint32_t off = (kk >> 2) * C::PANEL_BYTES + (kk & 3) * 32;
-            mma_ss(tmem + slot * 128, umma_desc_sw128(a_base + off, 16, 1024),
+            mma_ss(tmem + g * 128 + h * 64, umma_desc_sw128(a_base + off, 16, 1024),
                    umma_desc_sw128(b_base + off, 16, 1024), IDESC_S, kk > 0);
           }
-          tc_commit(s_full(slot));
-          ++cnt_s[slot];
-          if (MODE == MODE_ROWSUM && (QT == 1 || slot == 1)) tc_commit(k_empty(st));
+          tc_commit(s_full(g, h));
+          // ROWSUM: the stage is free once the last S MMA that reads it has run
+          if (MODE == MODE_ROWSUM && h == 1 && (QT == 1 || g == 1)) tc_commit(k_empty(st));
         };
 
-        issue_S(0);
-        if (U > 1) issue_S(1);
-        if (MODE == MODE_ROWSUM) {
-          for (int u = 2; u < U; ++u) issue_S(u);
-        } else {
-          for (int u = 0; u < U; ++u) {
-            const int slot = u & 1;
-            const int j = (QT == 2) ? (u >> 1) : u;
-            const int st = (g + j) % NST;
-            const int acc = (QT == 2) ? slot : 0;
-            const bool first = (QT == 2) ? (u < 2) : (u == 0);
-            const bool last = (QT == 2) ? (u >= U - 2) : (u == U - 1);
-            if (first) {
-              mbar_wait(acc_empty(acc), (it & 1) ^ 1);
-              tc_fence_after();
-            }
-            mbar_wait(t_full(slot), cnt_t[slot] & 1);
-            ++cnt_t[slot];
-            tc_fence_after();
-            const uint32_t b_base = k_smem + st * C::TILE_BYTES;
-#pragma unroll
-            for (int kk = 0; kk < 8; ++kk)
-              mma_ts(tmem + C::ACC_COL + acc * D, tmem + slot * 128 + kk * 8,
-                     umma_desc_sw128(b_base + kk * 2048, C::PANEL_BYTES, 1024), IDESC_G,
-                     (first && kk == 0) ? 0u : 1u);
-            if (QT == 1 || slot == 1) tc_commit(k_empty(st));
-            if (last) tc_commit(acc_full(acc));
-            if (u + 2 < U) issue_S(u + 2);
-          }
+        // prologue: both halves of every stream's first tile
+        for (int h = 0; h < 2; ++h)
+          for (int g = 0; g < 2; ++g)
+            if (nk[g] > 0) issue_S(g, 0, h);
+        if (kmax <= 1) tc_commit(q_empty);
+        if (MODE == MODE_GRAD) {
+          mbar_wait(acc_empty(0), (ita & 1) ^ 1);
+          if (QT == 2) mbar_wait(acc_empty(1), (ita & 1) ^ 1);
+          tc_fence_after();
         }
-        tc_commit(q_empty);
-        g += nkt;
+        for (int k = 0; k < kmax; ++k) {
+          for (int h = 0; h < 2; ++h) {
+            for (int g = 0; g < 2; ++g) {
+              if (k >= nk[g]) continue;
+              const bool more = (k + 1 < nk[g]);
+              // GRAD: T_h is stored; ROWSUM: S_h has been consumed (also guards the next item's prologue)
+              mbar_wait(t_full(g, h), cnt_t[g][h] & 1);
+              tc_fence_after();
+              ++cnt_t[g][h];
+              if (MODE == MODE_GRAD) {
+                uint32_t par;
+                const int st = stage_of(g, k, par);
+                const int acc = (QT == 2) ? g : 0;
+                const bool first = (k == 0 && h == 0) && (QT == 2 || g == 0);
+                const uint32_t b_base = k_smem + st * C::TILE_BYTES;
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk)
+                  mma_ts(tmem + C::ACC_COL + acc * D, tmem + g * 128 + h * 64 + kk * 8,
+                         umma_desc_sw128(b_base + (h * 4 + kk) * 2048, C::PANEL_BYTES, 1024),
+                         IDESC_G, (first && kk == 0) ? 0u : 1u);
+                if (h == 1 && (QT == 1 || g == 1)) tc_commit(k_empty(st));
+              }
+              if (more) issue_S(g, k + 1, h);
+            }
+          }
+          if (k == kmax - 2) tc_commit(q_empty);  // the last S MMAs of the item are in flight
+        }
+        if (MODE == MODE_GRAD) {
+          tc_commit(acc_full(0));
+          if (QT == 2) tc_commit(acc_full(1));
+        }
+        gbase += n;
+        ++ita;
       }
     }
   } else {
     // ------------------------------------------------------------ epilogue groups
-    const int slot = warp >> 2;
+    const int g = warp >> 2;
     const int wq = warp & 3;
     const uint32_t lane_addr = static_cast<uint32_t>(wq * 32) << 16;
-    const float off = p.scale_log2 * __ldg(p.bound);
     const float a = p.scale_log2;
-    uint32_t g = 0, it = 0, cnt = 0;
+    uint32_t gbase = 0, it = 0, ita = 0, cnt = 0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       int rb, ks, t0, t1;
       item_range(item, rb, ks, t0, t1);
-      const int nkt = t1 - t0;
-      const int row = rb * C::RB + (QT == 2 ? slot * 128 : 0) + wq * 32 + lane;
+      const int row_tile = rb * QT + (QT == 2 ? g : 0);
+      const int row = row_tile * 128 + wq * 32 + lane;
       const uint32_t rbits = __ldg(p.bits_row + row);
+      const uint32_t tor_r = __ldg(p.tor_row + row_tile);
       const uint32_t qmask = rbits ? ~rbits : 0u;
       float wrow = 0.f;
       if (MODE == MODE_GRAD) wrow = __ldg(p.w_row + row);
-      float rsum = 0.f;
-      const int n_my = (QT == 2) ? nkt : ((nkt - slot + 1) >> 1);
-      for (int i = 0; i < n_my; ++i) {
-        const int j = (QT == 2) ? i : (2 * i + slot);
-        const uint32_t gg = g + j;
+      mbar_wait(q_full, it & 1);
+      const int n = static_cast<int>(info[it & 1]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(q_empty);
+      const int my_n = n_stream(n, g);
+      uint64_t racc[4] = {0ull, 0ull, 0ull, 0ull};
+      for (int k = 0; k < my_n; ++k, ++cnt) {
+        const uint32_t gg = gbase + tile_of(g, k);
         const int st = gg % NST;
         mbar_wait(k_full(st), (gg / NST) & 1);
-        mbar_wait(s_full(slot), cnt & 1);
-        ++cnt;
-        tc_fence_after();
-        const uint4* kb4 = reinterpret_cast<const uint4*>(smem_gen + C::SMEM_BITS + st * 512);
-        const float4* kw4 = reinterpret_cast<const float4*>(smem_gen + C::SMEM_W + st * 512);
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint32_t v[32];
-          tmem_ld32(tmem + lane_addr + slot * 128 + c * 32, v);
-          tmem_wait_ld();
-          uint32_t packed[16];
-#pragma unroll
-          for (int q4 = 0; q4 < 8; ++q4) {
-            const uint4 kb = kb4[c * 8 + q4];
-            const uint32_t kbv[4] = {kb.x, kb.y, kb.z, kb.w};
-            float kwv[4] = {0.f, 0.f, 0.f, 0.f};
-            if (MODE == MODE_GRAD) {
-              const float4 kw = kw4[c * 8 + q4];
-              kwv[0] = kw.x; kwv[1] = kw.y; kwv[2] = kw.z; kwv[3] = kw.w;
-            }
-            float t[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float s = __uint_as_float(v[q4 * 4 + e]);
-              const float x = ex2_approx(fmaf(s, a, -off));
-              const bool m = (kbv[e] & qmask) != 0u;
-              if (MODE == MODE_ROWSUM) {
-                rsum += m ? x : 0.f;
-              } else {
-                t[e] = m ? x * (wrow + kwv[e]) : 0.f;
-              }
-            }
-            if (MODE == MODE_GRAD) {
-              packed[q4 * 2 + 0] = pack_bf16x2(t[0], t[1]);
-              packed[q4 * 2 + 1] = pack_bf16x2(t[2], t[3]);
-            }
-          }
-          if (MODE == MODE_GRAD) tmem_st16(tmem + lane_addr + slot * 128 + c * 16, packed);
+        const uint32_t tor_c = info[2 + st];
+        const bool full = tile_pair_full(tor_r, tor_c);
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+          mbar_wait(s_full(g, h), cnt & 1);
+          tc_fence_after();
+          const uint32_t s_addr = tmem + lane_addr + g * 128 + h * 64;
+          const uint8_t* bsm = smem_gen + C::SMEM_BITS + st * 512 + h * 256;
+          const uint8_t* wsm = smem_gen + C::SMEM_W + st * 512 + h * 256;
+          if (full)
+            pair_half_epilogue<MODE, POLY, true>(s_addr, bsm, wsm, qmask, a, wrow, racc);
+          else
+            pair_half_epilogue<MODE, POLY, false>(s_addr, bsm, wsm, qmask, a, wrow, racc);
+          if (MODE == MODE_GRAD) tmem_wait_st();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(t_full(g, h));
         }
-        if (MODE == MODE_GRAD) tmem_wait_st();
-        tc_fence_before();
         __syncwarp();
-        if (lane == 0) {
-          mbar_arrive(k_empty(st));
-          mbar_arrive(MODE == MODE_GRAD ? t_full(slot) : s_free(slot));
-        }
+        if (lane == 0) mbar_arrive(k_empty(st));
       }
       if (MODE == MODE_ROWSUM) {
-        atomicAdd(p.rowsum + row, rsum);
+        float r0, r1, r2, r3;
+        unpack2(add2(racc[0], racc[1]), r0, r1);
+        unpack2(add2(racc[2], racc[3]), r2, r3);
+        const float rsum = (r0 + r1) + (r2 + r3);
+        if (my_n > 0 && rbits) atomicAdd(p.rowsum + row, rsum);
       } else {
-        const int acc = (QT == 2) ? slot : 0;
-        mbar_wait(acc_full(acc), it & 1);
-        tc_fence_after();
+        const int acc = (QT == 2) ? g : 0;
         constexpr int NCH = (QT == 2) ? (D / 32) : (D / 64);
-        const int col0 = (QT == 2) ? 0 : slot * (D / 2);
+        const int col0 = (QT == 2) ? 0 : g * (D / 2);
         float* dst = p.part + (static_cast<size_t>(ks) * p.rows_pad + row) * D + col0;
+        if (n > 0) {
+          mbar_wait(acc_full(acc), ita & 1);
+          tc_fence_after();
 #pragma unroll 1
-        for (int c = 0; c < NCH; ++c) {
-          uint32_t v[32];
-          tmem_ld32(tmem + lane_addr + C::ACC_COL + acc * D + col0 + c * 32, v);
-          tmem_wait_ld();
+          for (int c = 0; c < NCH; ++c) {
+            uint32_t v[32];
+            tmem_ld32(tmem + lane_addr + C::ACC_COL + acc * D + col0 + c * 32, v);
+            tmem_wait_ld();
 #pragma unroll
-          for (int q4 = 0; q4 < 8; ++q4)
-            reinterpret_cast<float4*>(dst + c * 32)[q4] =
-                make_float4(__uint_as_float(v[q4 * 4]), __uint_as_float(v[q4 * 4 + 1]),
-                            __uint_as_float(v[q4 * 4 + 2]), __uint_as_float(v[q4 * 4 + 3]));
+            for (int q4 = 0; q4 < 8; ++q4)
+              reinterpret_cast<float4*>(dst + c * 32)[q4] =
+                  make_float4(__uint_as_float(v[q4 * 4]), __uint_as_float(v[q4 * 4 + 1]),
+                              __uint_as_float(v[q4 * 4 + 2]), __uint_as_float(v[q4 * 4 + 3]));
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(acc_empty(acc));
+        } else {
+#pragma unroll 1
+          for (int c = 0; c < NCH * 8; ++c)
+            reinterpret_cast<float4*>(dst)[c] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(acc_empty(acc));
       }
-      g += nkt;
+      if (n > 0) ++ita;
+      gbase += n;
     }
   }
 

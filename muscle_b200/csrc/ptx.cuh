@@ -196,6 +196,55 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 
+// ---------------------------------------------------------------- packed fp32 pairs (FFMA2 / FADD2 / FMUL2)
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ uint64_t pack2u(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+// 2^x for a pair on the FMA/ALU pipes (no MUFU): round-to-nearest split x = n + f, f in
+// [-0.5, 0.5], cubic minimax for 2^f (max relative error 7.5e-5), exponent patched in with one
+// shift-add per element.  Valid for -120 < x < 120 (the host only selects it in that range).
+__device__ __forceinline__ uint64_t ex2_poly2(uint64_t x) {
+  const float MAGIC = 12582912.f;  // 1.5 * 2^23
+  const uint64_t t = add2(x, pack2(MAGIC, MAGIC));
+  const uint64_t n = add2(t, pack2(-MAGIC, -MAGIC));
+  const uint64_t f = fma2(n, pack2(-1.f, -1.f), x);
+  uint64_t p = fma2(f, pack2(0.0551716648f, 0.0551716648f), pack2(0.2426111251f, 0.2426111251f));
+  p = fma2(p, f, pack2(0.6932609677f, 0.6932609677f));
+  p = fma2(p, f, pack2(0.9999280572f, 0.9999280572f));
+  float pl, ph, tl, th;
+  unpack2(p, pl, ph);
+  unpack2(t, tl, th);
+  const float r0 = __int_as_float(__float_as_int(pl) + (__float_as_int(tl) << 23));
+  const float r1 = __int_as_float(__float_as_int(ph) + (__float_as_int(th) << 23));
+  return pack2(r0, r1);
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   uint32_t r;
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));

@@ -1,10 +1,15 @@
-// HBM-bound per-pixel kernels around the tcgen05 pair passes of the dense InfoNCE:
-//   prepare : L2-normalise, cast to bf16 (pixel-major), class bit, per-class sums
-//   pos     : pixel -> class-prototype logit, seeds the row sums
-//   mid     : 1/rowsum, per-pixel loss term, prototype-gradient accumulation
-//   final   : sum the column splits, prototype terms, normalisation backward, layout
-// All vectors of one pixel are handled by one warp (D/32 elements per lane); the NCHW <->
-// pixel-major transposition goes through a padded shared-memory tile so both sides coalesce.
+// HBM-bound per-pixel kernels around the tcgen05 pair passes of the dense InfoNCE.
+//
+//   class_hist / class_scan : counting sort of the pixels by class (stable, deterministic):
+//                             per-chunk histograms, then per-class offsets, segment starts and the
+//                             per-tile class unions the pair kernel uses to skip masked tiles
+//   prepare   : L2-normalise, cast to bf16, write each pixel's row at its class-sorted position
+//   class_sum : per-class column sums of the sorted bf16 rows (segmented block reduction)
+//   mid       : pixel -> class-prototype logit, 1/rowsum, per-pixel loss term, prototype gradient
+//   final     : sum the column splits, prototype terms, normalisation backward, un-sort, layout
+//
+// Layouts: source order n = b*P + p (the caller's [B,D,h,w] or [N,D]); sorted order r in
+// [0, rows_pad): class 0 pixels first, ..., invalid pixels last, pad rows (zero) at the end.
 #pragma once
 #include <cuda_bf16.h>
 
@@ -12,9 +17,9 @@
 
 namespace mb200 {
 
-constexpr int ROW_THREADS = 256;
-constexpr int ROW_WARPS = ROW_THREADS / 32;
-constexpr int TILE_PX = 32;
+constexpr int SORT_CHUNK = 128;   // source pixels per block in hist / prepare / final (4 warps)
+constexpr int SORT_WARPS = SORT_CHUNK / 32;
+constexpr int MAX_BINS = 32;      // classes (<= 31) + one bin for invalid pixels
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -24,67 +29,85 @@ __device__ __forceinline__ float warp_sum(float v) {
 
 __device__ __forceinline__ int class_of_bits(uint32_t b) { return 31 - __clz(b); }
 
-// Loads the D/32 consecutive bf16 values of lane `lane` (elements lane*EPL .. +EPL-1) as floats.
-template <int EPL>
-__device__ __forceinline__ void load_bf16_lane(const __nv_bfloat16* row, int lane, float (&v)[EPL]) {
-  if constexpr (EPL == 2) {
-    const __nv_bfloat162 t = reinterpret_cast<const __nv_bfloat162*>(row)[lane];
-    v[0] = __low2float(t);
-    v[1] = __high2float(t);
-  } else if constexpr (EPL == 4) {
-    const uint2 t = reinterpret_cast<const uint2*>(row)[lane];
-    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&t.x);
-    const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(&t.y);
-    v[0] = __low2float(a); v[1] = __high2float(a);
-    v[2] = __low2float(b); v[3] = __high2float(b);
-  } else {
-    static_assert(EPL == 8, "EPL");
-    const uint4 t = reinterpret_cast<const uint4*>(row)[lane];
-    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+__device__ __forceinline__ int load_class(const void* cls, int cls64, long long n, int C) {
+  const long long c = cls64 ? reinterpret_cast<const long long*>(cls)[n]
+                            : static_cast<long long>(reinterpret_cast<const int*>(cls)[n]);
+  return (c >= 0 && c < C) ? static_cast<int>(c) : C;  // bin C = invalid
+}
+
+// ------------------------------------------------------------------------------------------
+// hist[blk][bin] = number of pixels of class `bin` among source pixels [blk*128, blk*128+128)
+__global__ void __launch_bounds__(SORT_CHUNK) class_hist_kernel(const void* cls, int cls64,
+                                                                long long n, int C,
+                                                                uint32_t* hist) {
+  __shared__ uint32_t h[MAX_BINS];
+  if (threadIdx.x < MAX_BINS) h[threadIdx.x] = 0u;
+  __syncthreads();
+  const long long i = static_cast<long long>(blockIdx.x) * SORT_CHUNK + threadIdx.x;
+  if (i < n) atomicAdd(&h[load_class(cls, cls64, i, C)], 1u);
+  __syncthreads();
+  if (threadIdx.x < MAX_BINS) hist[static_cast<size_t>(blockIdx.x) * MAX_BINS + threadIdx.x] = h[threadIdx.x];
+}
+
+// One block of 32 warps; warp c owns bin c.  In place: hist[blk][c] becomes the sorted position
+// of the first pixel of class c in chunk blk.  seg[c] = first sorted row of class c
+// (seg[C] = first invalid row, seg[C+1] = n).  class_mass[c] += count.  tor[t] = class union of
+// sorted tile t (rows 128t..128t+127) | TOR_INVALID when it holds invalid or pad rows.
+__global__ void __launch_bounds__(1024) class_scan_kernel(uint32_t* hist, int n_blk, int C,
+                                                          long long n, long long rows_pad,
+                                                          uint32_t* seg, float* class_mass,
+                                                          uint32_t* tor) {
+  __shared__ uint32_t total[MAX_BINS + 1];
+  __shared__ uint32_t start[MAX_BINS + 2];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // pass 1: class totals
+  uint32_t t = 0;
+  if (warp <= C)
+    for (int b = lane; b < n_blk; b += 32) t += hist[static_cast<size_t>(b) * MAX_BINS + warp];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
-      v[2 * i] = __low2float(a);
-      v[2 * i + 1] = __high2float(a);
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  if (lane == 0) total[warp] = (warp <= C) ? t : 0u;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t s = 0;
+    for (int c = 0; c <= C; ++c) {
+      start[c] = s;
+      s += total[c];
     }
+    start[C + 1] = s;  // == n
+  }
+  __syncthreads();
+  if (threadIdx.x <= C + 1) seg[threadIdx.x] = start[threadIdx.x];
+  if (threadIdx.x < C) atomicAdd(class_mass + threadIdx.x, static_cast<float>(total[threadIdx.x]));
+  // pass 2: exclusive scan over chunks, 32 chunks at a time
+  if (warp <= C) {
+    uint32_t run = start[warp];
+    for (int b0 = 0; b0 < n_blk; b0 += 32) {
+      const int b = b0 + lane;
+      const uint32_t v = (b < n_blk) ? hist[static_cast<size_t>(b) * MAX_BINS + warp] : 0u;
+      uint32_t inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+      }
+      if (b < n_blk) hist[static_cast<size_t>(b) * MAX_BINS + warp] = run + inc - v;
+      run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+  }
+  // tile class unions
+  const long long n_tiles = rows_pad / 128;
+  for (long long tile = threadIdx.x; tile < n_tiles; tile += blockDim.x) {
+    const long long r0 = tile * 128, r1 = r0 + 128;
+    uint32_t u = 0;
+    for (int c = 0; c < C; ++c)
+      if (static_cast<long long>(start[c]) < r1 && static_cast<long long>(start[c + 1]) > r0) u |= 1u << c;
+    if (r1 > static_cast<long long>(start[C])) u |= 0x80000000u;
+    tor[tile] = u;
   }
 }
 
-template <int EPL>
-__device__ __forceinline__ void store_bf16_lane(__nv_bfloat16* row, int lane, const float (&v)[EPL]) {
-  uint32_t w[EPL / 2];
-#pragma unroll
-  for (int i = 0; i < EPL / 2; ++i) w[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
-  if constexpr (EPL == 2) {
-    reinterpret_cast<uint32_t*>(row)[lane] = w[0];
-  } else if constexpr (EPL == 4) {
-    reinterpret_cast<uint2*>(row)[lane] = make_uint2(w[0], w[1]);
-  } else {
-    reinterpret_cast<uint4*>(row)[lane] = make_uint4(w[0], w[1], w[2], w[3]);
-  }
-}
-
-// Shared-memory per-class accumulators [C][D] with a bitmask of the classes that were touched,
-// flushed to global with one atomic per touched element.
-struct ClassAcc {
-  float* acc;         // [C*D]
-  float* cnt;         // [C]
-  uint32_t* present;  // [1]
-  __device__ void init(int C, int D) {
-    for (int i = threadIdx.x; i < C * D; i += blockDim.x) acc[i] = 0.f;
-    for (int i = threadIdx.x; i < C; i += blockDim.x) cnt[i] = 0.f;
-    if (threadIdx.x == 0) *present = 0u;
-  }
-  __device__ void flush(int C, int D, float* gsum, float* gcnt) {
-    const uint32_t pm = *present;
-    for (int c = 0; c < C; ++c) {
-      if (!((pm >> c) & 1u)) continue;
-      for (int d = threadIdx.x; d < D; d += blockDim.x) atomicAdd(gsum + c * D + d, acc[c * D + d]);
-      if (gcnt != nullptr && threadIdx.x == 0) atomicAdd(gcnt + c, cnt[c]);
-    }
-  }
-};
-
+// ------------------------------------------------------------------------------------------
 struct PrepareParams {
   const float* x;
   const void* cls;
@@ -94,194 +117,247 @@ struct PrepareParams {
   long long ppi;     // pixels per image (NCHW)
   int C;
   float eps;
-  __nv_bfloat16* ehat;
-  uint32_t* bits;
-  float* inv_norm;
-  float* class_sum;
-  float* class_mass;
+  const uint32_t* chunk_off;  // [n_blk][MAX_BINS]  scanned histogram (class_scan_kernel)
+  __nv_bfloat16* ehat;        // [rows_pad][D]  sorted
+  uint32_t* bits;             // [rows_pad]     sorted
+  float* inv_norm;            // [rows_pad]     sorted
+  int* perm;                  // [n]            source pixel -> sorted row
 };
 
+// One block = 128 consecutive source pixels, one warp = 32 of them.  The sorted position of a
+// pixel is  chunk_off[blk][class] + (pixels of that class earlier in the chunk), which keeps the
+// source order inside every class (stable) and needs no atomics.
 template <int D>
-__global__ void __launch_bounds__(ROW_THREADS) prepare_kernel(const PrepareParams p) {
-  constexpr int EPL = D / 32;
-  extern __shared__ float smem_f[];
-  float* xs = smem_f;                              // [TILE_PX][D+1]
-  ClassAcc ca;
-  ca.acc = xs + TILE_PX * (D + 1);                 // [C*D]
-  ca.cnt = ca.acc + p.C * D;                       // [C]
-  ca.present = reinterpret_cast<uint32_t*>(ca.cnt + p.C);
+__global__ void __launch_bounds__(SORT_CHUNK) prepare_kernel(const PrepareParams p) {
+  constexpr int WPR = D / 64;          // 32-bit words (bf16 pairs) per lane per row
+  constexpr int ROW_W = D / 2 + 1;     // smem row stride in words (odd: conflict-free columns)
+  extern __shared__ uint32_t smem_u[];  // NCHW only: [SORT_WARPS][32][ROW_W]
+  __shared__ uint32_t warp_hist[SORT_WARPS][MAX_BINS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  ca.init(p.C, D);
+  for (int i = threadIdx.x; i < SORT_WARPS * MAX_BINS; i += SORT_CHUNK) (&warp_hist[0][0])[i] = 0u;
   __syncthreads();
+  const long long n0 = static_cast<long long>(blockIdx.x) * SORT_CHUNK + warp * 32;
+  const long long i = n0 + lane;
+  const bool live = i < p.n;
+  const int c = live ? load_class(p.cls, p.cls64, i, p.C) : (MAX_BINS + lane);  // dead lanes: unique keys
+  const uint32_t peers = __match_any_sync(0xffffffffu, c);
+  const int rank = __popc(peers & ((1u << lane) - 1u));
+  if (live && rank == 0) warp_hist[warp][c] = __popc(peers);
+  __syncthreads();
+  int dest = 0;
+  if (live) {
+    uint32_t off = p.chunk_off[static_cast<size_t>(blockIdx.x) * MAX_BINS + c];
+    for (int w = 0; w < warp; ++w) off += warp_hist[w][c];
+    dest = static_cast<int>(off) + rank;
+    p.perm[i] = dest;
+    p.bits[dest] = (c < p.C) ? (1u << c) : 0u;
+  }
+  if (n0 >= p.n) return;
 
-  const long long tiles_per_img = (p.layout == MUSCLE_LAYOUT_NCHW) ? (p.ppi + TILE_PX - 1) / TILE_PX : 0;
-  const long long n_tiles = (p.layout == MUSCLE_LAYOUT_NCHW) ? (p.n / p.ppi) * tiles_per_img
-                                                             : (p.n + TILE_PX - 1) / TILE_PX;
-  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    long long n0;
-    int npx;
-    if (p.layout == MUSCLE_LAYOUT_NCHW) {
-      const long long b = tile / tiles_per_img;
-      const long long p0 = (tile - b * tiles_per_img) * TILE_PX;
-      n0 = b * p.ppi + p0;
-      npx = static_cast<int>(min(static_cast<long long>(TILE_PX), p.ppi - p0));
-      const float* src = p.x + b * D * p.ppi + p0;
-      for (int d = warp; d < D; d += ROW_WARPS)
-        xs[lane * (D + 1) + d] = (lane < npx) ? __ldg(src + static_cast<long long>(d) * p.ppi + lane) : 0.f;
-    } else {
-      n0 = tile * TILE_PX;
-      npx = static_cast<int>(min(static_cast<long long>(TILE_PX), p.n - n0));
-      for (int r = warp; r < npx; r += ROW_WARPS) {
-        const float* src = p.x + (n0 + r) * D;
-#pragma unroll
-        for (int k = 0; k < EPL; ++k) xs[r * (D + 1) + lane + 32 * k] = __ldg(src + lane + 32 * k);
+  if (p.layout == MUSCLE_LAYOUT_NCHW) {
+    // lane = pixel: coalesced across the warp for every channel
+    const long long b = live ? i / p.ppi : 0;
+    const float* src = p.x + (b * D) * p.ppi + (live ? i - b * p.ppi : 0);
+    float ss = 0.f;
+    if (live) {
+#pragma unroll 8
+      for (int d = 0; d < D; ++d) {
+        const float v = __ldg(src + static_cast<long long>(d) * p.ppi);
+        ss = fmaf(v, v, ss);
       }
     }
-    __syncthreads();
-    for (int r = warp; r < npx; r += ROW_WARPS) {
-      // lane holds elements lane*EPL .. lane*EPL+EPL-1 (what the bf16 row store wants)
-      float v[EPL];
+    const float inv = 1.f / fmaxf(sqrtf(ss), p.eps);
+    uint32_t* tile = smem_u + (warp * 32 + lane) * ROW_W;
+    if (live) {
+      p.inv_norm[dest] = inv;
+#pragma unroll 8
+      for (int d = 0; d < D; d += 2) {
+        const float v0 = __ldg(src + static_cast<long long>(d) * p.ppi) * inv;
+        const float v1 = __ldg(src + static_cast<long long>(d + 1) * p.ppi) * inv;
+        tile[d >> 1] = pack_bf16x2(v0, v1);
+      }
+    }
+    __syncwarp();
+    const int n_live = static_cast<int>(min(32ll, p.n - n0));
+    for (int r = 0; r < n_live; ++r) {
+      const int dr = __shfl_sync(0xffffffffu, dest, r);
+      const uint32_t* trow = smem_u + (warp * 32 + r) * ROW_W;
+      uint32_t* out = reinterpret_cast<uint32_t*>(p.ehat + static_cast<size_t>(dr) * D);
+#pragma unroll
+      for (int k = 0; k < WPR; ++k) out[lane + 32 * k] = trow[lane + 32 * k];
+    }
+  } else {
+    const int n_live = static_cast<int>(min(32ll, p.n - n0));
+    for (int r = 0; r < n_live; ++r) {
+      const int dr = __shfl_sync(0xffffffffu, dest, r);
+      const float2* src = reinterpret_cast<const float2*>(p.x + (n0 + r) * D);
+      float2 v[WPR];
       float ss = 0.f;
 #pragma unroll
-      for (int k = 0; k < EPL; ++k) {
-        v[k] = xs[r * (D + 1) + lane * EPL + k];
-        ss += v[k] * v[k];
+      for (int k = 0; k < WPR; ++k) {
+        v[k] = __ldg(src + lane + 32 * k);
+        ss += v[k].x * v[k].x + v[k].y * v[k].y;
       }
       ss = warp_sum(ss);
       const float inv = 1.f / fmaxf(sqrtf(ss), p.eps);
-      long long c = p.cls64 ? reinterpret_cast<const long long*>(p.cls)[n0 + r]
-                            : static_cast<long long>(reinterpret_cast<const int*>(p.cls)[n0 + r]);
-      const bool valid = (c >= 0 && c < p.C);
+      uint32_t* out = reinterpret_cast<uint32_t*>(p.ehat + static_cast<size_t>(dr) * D);
 #pragma unroll
-      for (int k = 0; k < EPL; ++k) v[k] *= inv;
-      store_bf16_lane<EPL>(p.ehat + (n0 + r) * D, lane, v);
-      if (lane == 0) {
-        p.bits[n0 + r] = valid ? (1u << c) : 0u;
-        p.inv_norm[n0 + r] = inv;
-      }
-      if (valid) {
-        // the prototypes are means of the SAME bf16-rounded vectors the tensor cores see
-#pragma unroll
-        for (int k = 0; k < EPL; ++k)
-          atomicAdd(&ca.acc[c * D + lane * EPL + k], __bfloat162float(__float2bfloat16_rn(v[k])));
-        if (lane == 0) {
-          atomicAdd(&ca.cnt[c], 1.f);
-          atomicOr(ca.present, 1u << c);
-        }
-      }
+      for (int k = 0; k < WPR; ++k) out[lane + 32 * k] = pack_bf16x2(v[k].x * inv, v[k].y * inv);
+      if (lane == 0) p.inv_norm[dr] = inv;
     }
-    __syncthreads();
   }
-  ca.flush(p.C, D, p.class_sum, p.class_mass);
 }
 
-struct PosParams {
-  const __nv_bfloat16* ehat;
-  const uint32_t* bits;
-  long long n_rows, rows_pad;
-  const float* class_sum;
-  const float* class_mass;
-  const float* bound;
-  float inv_tau;
-  float* pos;
-  float* rowsum;
-};
+// ------------------------------------------------------------------------------------------
+// Segmented column sums over the class-sorted rows.  One block per 128-row tile; a tile is cut
+// into at most a few single-class pieces at the segment starts, every piece is reduced in
+// registers + shared memory and leaves the block as one atomicAdd per channel.
+constexpr int SEG_THREADS = 256;
 
 template <int D>
-__global__ void __launch_bounds__(ROW_THREADS) pos_kernel(const PosParams p) {
-  constexpr int EPL = D / 32;
-  const int lane = threadIdx.x & 31;
-  const long long warp_g = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
-  const long long n_warps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
-  const float bt = __ldg(p.bound) * p.inv_tau;
-  for (long long r = warp_g; r < p.rows_pad; r += n_warps) {
-    const uint32_t b = (r < p.n_rows) ? p.bits[r] : 0u;
-    float pos = 0.f, rs = 0.f;
-    if (b) {
-      const int c = class_of_bits(b);
-      float v[EPL];
-      load_bf16_lane<EPL>(p.ehat + r * D, lane, v);
-      float dot = 0.f;
+__device__ __forceinline__ void load_row8(const __nv_bfloat16* row, int l, float (&v)[8]) {
+  const uint4 t = __ldg(reinterpret_cast<const uint4*>(row) + l);
+  const uint32_t w[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
-      for (int k = 0; k < EPL; ++k) dot += v[k] * __ldg(p.class_sum + c * D + lane * EPL + k);
-      dot = warp_sum(dot);
-      pos = dot / __ldg(p.class_mass + c) * p.inv_tau;
-      rs = __expf(pos - bt);
+  for (int i = 0; i < 4; ++i) {
+    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
+    v[2 * i] = __low2float(a);
+    v[2 * i + 1] = __high2float(a);
+  }
+}
+
+// red: shared [SEG_THREADS / (D/8)][D]; adds the block's column sums of `acc` to out[0..D)
+template <int D>
+__device__ __forceinline__ void block_colsum_flush(float (&acc)[8], float* red, float* out) {
+  constexpr int TPR = D / 8;
+  constexpr int RPP = SEG_THREADS / TPR;
+  const int sub = threadIdx.x / TPR, l = threadIdx.x % TPR;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) red[sub * D + l * 8 + i] = acc[i];
+  __syncthreads();
+  for (int d = threadIdx.x; d < D; d += SEG_THREADS) {
+    float s = 0.f;
+#pragma unroll 8
+    for (int r = 0; r < RPP; ++r) s += red[r * D + d];
+    if (s != 0.f) atomicAdd(out + d, s);
+  }
+  __syncthreads();
+}
+
+// class_sum[c][:] += sum of the (bf16-rounded) rows of class c in this tile
+template <int D>
+__global__ void __launch_bounds__(SEG_THREADS) class_sum_kernel(const __nv_bfloat16* ehat,
+                                                                const uint32_t* seg, int C,
+                                                                float* class_sum) {
+  constexpr int TPR = D / 8;
+  constexpr int RPP = SEG_THREADS / TPR;
+  __shared__ float red[RPP * D];
+  const int sub = threadIdx.x / TPR, l = threadIdx.x % TPR;
+  const long long r0 = static_cast<long long>(blockIdx.x) * 128, r1 = r0 + 128;
+  for (int c = 0; c < C; ++c) {
+    const long long lo = max(r0, static_cast<long long>(seg[c]));
+    const long long hi = min(r1, static_cast<long long>(seg[c + 1]));
+    if (lo >= hi) continue;  // block-uniform
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (long long r = lo + sub; r < hi; r += RPP) {
+      float v[8];
+      load_row8<D>(ehat + r * D, l, v);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] += v[i];
     }
-    if (lane == 0) {
-      p.pos[r] = pos;
-      p.rowsum[r] = rs;
-    }
+    block_colsum_flush<D>(acc, red, class_sum + c * D);
   }
 }
 
 struct MidParams {
-  const __nv_bfloat16* ehat;
-  const uint32_t* bits;
-  long long n_rows;
+  const __nv_bfloat16* ehat;   // sorted rows
+  const uint32_t* seg;         // [C+2]
   int C;
-  const float* pos;
-  const float* rowsum;
-  const float* bound;
+  const float* class_sum;      // [C][D]  (global sums when sharded)
+  const float* class_mass;     // [C]
+  float* rowsum;               // in: sum over negatives of exp((s-1)/tau); out: + the positive term
   float inv_tau;
-  float* w;
-  float* gpos;
-  double* loss_acc;
-  float* dproto;
+  float* w;                    // [rows_pad] 1/rowsum, 0 for rows outside the loss
+  float* gpos;                 // [rows_pad] d loss_q / d pos-logit_q (before the 1/n_valid factor)
+  double* loss_acc;            // += sum_q (1/tau + ln rowsum_q - pos_q)
+  float* dproto;               // [C][D] += sum_q gpos_q e_q
 };
 
+// Same tiling as class_sum_kernel.  Rows of the invalid segment and pad rows get w = gpos = 0.
 template <int D>
-__global__ void __launch_bounds__(ROW_THREADS) mid_kernel(const MidParams p) {
-  constexpr int EPL = D / 32;
-  extern __shared__ float smem_f[];
-  ClassAcc ca;
-  ca.acc = smem_f;
-  ca.cnt = ca.acc + p.C * D;
-  ca.present = reinterpret_cast<uint32_t*>(ca.cnt + p.C);
-  __shared__ double loss_sh[ROW_WARPS];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  ca.init(p.C, D);
-  __syncthreads();
-  const long long warp_g = static_cast<long long>(blockIdx.x) * ROW_WARPS + warp;
-  const long long n_warps = static_cast<long long>(gridDim.x) * ROW_WARPS;
-  const float bt = __ldg(p.bound) * p.inv_tau;
+__global__ void __launch_bounds__(SEG_THREADS) mid_kernel(const MidParams p) {
+  constexpr int TPR = D / 8;
+  constexpr int RPP = SEG_THREADS / TPR;
+  __shared__ float red[RPP * D];
+  __shared__ double loss_sh[SEG_THREADS / 32];
+  const int sub = threadIdx.x / TPR, l = threadIdx.x % TPR;
+  const long long r0 = static_cast<long long>(blockIdx.x) * 128, r1 = r0 + 128;
+  const float bt = p.inv_tau;  // the shift used by the pair passes: exp((s - 1)/tau)
   double loss = 0.0;
-  for (long long r = warp_g; r < p.n_rows; r += n_warps) {
-    const uint32_t b = p.bits[r];
-    float w = 0.f, g = 0.f;
-    if (b) {
-      const int c = class_of_bits(b);
-      const float rs = p.rowsum[r];
-      const float pos = p.pos[r];
-      w = 1.f / rs;
-      g = (__expf(pos - bt) * w - 1.f) * p.inv_tau;
-      loss += static_cast<double>(bt + logf(rs) - pos);
-      float v[EPL];
-      load_bf16_lane<EPL>(p.ehat + r * D, lane, v);
+  for (int c = 0; c < p.C; ++c) {
+    const long long lo = max(r0, static_cast<long long>(p.seg[c]));
+    const long long hi = min(r1, static_cast<long long>(p.seg[c + 1]));
+    if (lo >= hi) continue;
+    const float inv_mass = 1.f / __ldg(p.class_mass + c);
+    float proto[8];
 #pragma unroll
-      for (int k = 0; k < EPL; ++k) atomicAdd(&ca.acc[c * D + lane * EPL + k], g * v[k]);
-      if (lane == 0) atomicOr(ca.present, 1u << c);
+    for (int i = 0; i < 8; ++i) proto[i] = __ldg(p.class_sum + c * D + l * 8 + i) * inv_mass;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (long long rr = lo; rr < hi; rr += RPP) {   // uniform trip count: shuffles stay converged
+      const long long r = rr + sub;
+      const bool on = r < hi;
+      float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (on) load_row8<D>(p.ehat + r * D, l, v);
+      float dot = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) dot = fmaf(v[i], proto[i], dot);
+#pragma unroll
+      for (int o = TPR / 2; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+      if (on) {
+        const float pos = dot * p.inv_tau;
+        const float ep = __expf(pos - bt);
+        const float rs = p.rowsum[r] + ep;
+        const float w = 1.f / rs;
+        const float g = (ep * w - 1.f) * p.inv_tau;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = fmaf(g, v[i], acc[i]);
+        if (l == 0) {
+          p.rowsum[r] = rs;
+          p.w[r] = w;
+          p.gpos[r] = g;
+          loss += static_cast<double>(bt + logf(rs) - pos);
+        }
+      }
     }
-    if (lane == 0) {
-      p.w[r] = w;
-      p.gpos[r] = g;
+    block_colsum_flush<D>(acc, red, p.dproto + c * D);
+  }
+  // rows outside every class (invalid pixels, pad rows)
+  {
+    const long long lo = max(r0, static_cast<long long>(p.seg[p.C]));
+    for (long long r = lo + threadIdx.x; r < r1; r += SEG_THREADS) {
+      p.w[r] = 0.f;
+      p.gpos[r] = 0.f;
     }
   }
-  if (lane == 0) loss_sh[warp] = loss;  // every lane of the warp carries the same sum
+  // block loss
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) loss += __shfl_xor_sync(0xffffffffu, loss, o);
+  if ((threadIdx.x & 31) == 0) loss_sh[threadIdx.x >> 5] = loss;
   __syncthreads();
-  ca.flush(p.C, D, p.dproto, nullptr);
   if (threadIdx.x == 0) {
     double t = 0.0;
-    for (int i = 0; i < ROW_WARPS; ++i) t += loss_sh[i];
+    for (int i = 0; i < SEG_THREADS / 32; ++i) t += loss_sh[i];
     if (t != 0.0) atomicAdd(p.loss_acc, t);
   }
 }
 
+// ------------------------------------------------------------------------------------------
 struct FinalParams {
-  const __nv_bfloat16* ehat;
-  const uint32_t* bits;
-  const float* inv_norm;
-  const float* part;
+  const __nv_bfloat16* ehat;   // sorted
+  const uint32_t* bits;        // sorted
+  const float* inv_norm;       // sorted
+  const int* perm;             // [n] source pixel -> sorted row
+  const float* part;           // [n_split][rows_pad][D]
   int n_split;
   long long rows_pad;
   long long n;
@@ -289,20 +365,24 @@ struct FinalParams {
   int C;
   const float* class_sum;
   const float* class_mass;
-  const float* gpos;
+  const float* gpos;           // sorted
   const float* dproto;
   const double* loss_acc;
   float inv_tau;
   int layout;
-  float* dx;
+  float* dx;                   // source order, `layout`
   float* loss_out;
 };
 
+// One block = 128 consecutive source pixels (the chunks of prepare_kernel), one warp = 32.
+// Per pixel the warp gathers its sorted row (lane holds channels lane, lane+32, ...), forms
+//   g = 1/n_valid (1/tau sum_splits part + gpos/mass class_sum_c + dproto_c/mass),
+//   dx = inv_norm (g - e (g.e))
+// and writes it back in the caller's layout (NCHW through a shared-memory transpose).
 template <int D>
-__global__ void __launch_bounds__(ROW_THREADS) final_kernel(const FinalParams p) {
+__global__ void __launch_bounds__(SORT_CHUNK) final_kernel(const FinalParams p) {
   constexpr int EPL = D / 32;
-  extern __shared__ float smem_f[];
-  float* xs = smem_f;  // [TILE_PX][D+1]
+  extern __shared__ float smem_f[];  // NCHW only: [SORT_WARPS][32][D+1]
   __shared__ float n_valid_sh;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -315,67 +395,59 @@ __global__ void __launch_bounds__(ROW_THREADS) final_kernel(const FinalParams p)
   __syncthreads();
   if (p.dx == nullptr) return;
   const float inv_n = n_valid_sh > 0.f ? 1.f / n_valid_sh : 0.f;
-
-  const long long tiles_per_img = (p.layout == MUSCLE_LAYOUT_NCHW) ? (p.ppi + TILE_PX - 1) / TILE_PX : 0;
-  const long long n_tiles = (p.layout == MUSCLE_LAYOUT_NCHW) ? (p.n / p.ppi) * tiles_per_img
-                                                             : (p.n + TILE_PX - 1) / TILE_PX;
-  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    long long n0, b = 0, p0 = 0;
-    int npx;
+  const long long n0 = static_cast<long long>(blockIdx.x) * SORT_CHUNK + warp * 32;
+  if (n0 >= p.n) return;
+  const long long i = n0 + lane;
+  const bool live = i < p.n;
+  const int my_q = live ? p.perm[i] : 0;
+  const int n_live = static_cast<int>(min(32ll, p.n - n0));
+  float* tile = smem_f + warp * 32 * (D + 1);
+  for (int r = 0; r < n_live; ++r) {
+    const long long q = __shfl_sync(0xffffffffu, my_q, r);
+    const uint32_t bq = __ldg(p.bits + q);
+    float g[EPL];
+#pragma unroll
+    for (int k = 0; k < EPL; ++k) g[k] = 0.f;
+    if (bq) {
+      const int c = class_of_bits(bq);
+      for (int s = 0; s < p.n_split; ++s) {
+        const float* src = p.part + (static_cast<long long>(s) * p.rows_pad + q) * D + lane;
+#pragma unroll
+        for (int k = 0; k < EPL; ++k) g[k] += __ldg(src + 32 * k);
+      }
+      const float inv_mass = 1.f / __ldg(p.class_mass + c);
+      const float gq = __ldg(p.gpos + q) * inv_mass;
+      float e[EPL];
+      float dot = 0.f;
+#pragma unroll
+      for (int k = 0; k < EPL; ++k) {
+        const int d = lane + 32 * k;
+        e[k] = __bfloat162float(p.ehat[q * D + d]);
+        g[k] = inv_n * (p.inv_tau * g[k] + gq * __ldg(p.class_sum + c * D + d) +
+                        inv_mass * __ldg(p.dproto + c * D + d));
+        dot = fmaf(g[k], e[k], dot);
+      }
+      dot = warp_sum(dot);
+      const float inv = __ldg(p.inv_norm + q);
+#pragma unroll
+      for (int k = 0; k < EPL; ++k) g[k] = inv * (g[k] - e[k] * dot);
+    }
     if (p.layout == MUSCLE_LAYOUT_NCHW) {
-      b = tile / tiles_per_img;
-      p0 = (tile - b * tiles_per_img) * TILE_PX;
-      n0 = b * p.ppi + p0;
-      npx = static_cast<int>(min(static_cast<long long>(TILE_PX), p.ppi - p0));
+#pragma unroll
+      for (int k = 0; k < EPL; ++k) tile[r * (D + 1) + lane + 32 * k] = g[k];
     } else {
-      n0 = tile * TILE_PX;
-      npx = static_cast<int>(min(static_cast<long long>(TILE_PX), p.n - n0));
+      float* dst = p.dx + (n0 + r) * D + lane;
+#pragma unroll
+      for (int k = 0; k < EPL; ++k) dst[32 * k] = g[k];
     }
-    for (int r = warp; r < npx; r += ROW_WARPS) {
-      const long long q = n0 + r;
-      const uint32_t bq = p.bits[q];
-      float g[EPL];
-#pragma unroll
-      for (int k = 0; k < EPL; ++k) g[k] = 0.f;
-      if (bq) {
-        const int c = class_of_bits(bq);
-        for (int s = 0; s < p.n_split; ++s) {
-          const float* src = p.part + (static_cast<long long>(s) * p.rows_pad + q) * D + lane * EPL;
-#pragma unroll
-          for (int k = 0; k < EPL; ++k) g[k] += __ldg(src + k);
-        }
-        const float inv_mass = 1.f / __ldg(p.class_mass + c);
-        const float gq = p.gpos[q] * inv_mass;
-        float e[EPL];
-        load_bf16_lane<EPL>(p.ehat + q * D, lane, e);
-        float dot = 0.f;
-#pragma unroll
-        for (int k = 0; k < EPL; ++k) {
-          const int d = lane * EPL + k;
-          g[k] = inv_n * (p.inv_tau * g[k] + gq * __ldg(p.class_sum + c * D + d) +
-                          inv_mass * __ldg(p.dproto + c * D + d));
-          dot += g[k] * e[k];
-        }
-        dot = warp_sum(dot);
-        const float inv = p.inv_norm[q];
-#pragma unroll
-        for (int k = 0; k < EPL; ++k) g[k] = inv * (g[k] - e[k] * dot);
-      }
-      if (p.layout == MUSCLE_LAYOUT_NCHW) {
-#pragma unroll
-        for (int k = 0; k < EPL; ++k) xs[r * (D + 1) + lane * EPL + k] = g[k];
-      } else {
-        float* dst = p.dx + q * D + lane * EPL;
-#pragma unroll
-        for (int k = 0; k < EPL; ++k) dst[k] = g[k];
-      }
-    }
-    if (p.layout == MUSCLE_LAYOUT_NCHW) {
-      __syncthreads();
-      float* dst = p.dx + b * D * p.ppi + p0;
-      for (int d = warp; d < D; d += ROW_WARPS)
-        if (lane < npx) dst[static_cast<long long>(d) * p.ppi + lane] = xs[lane * (D + 1) + d];
-      __syncthreads();
+  }
+  if (p.layout == MUSCLE_LAYOUT_NCHW) {
+    __syncwarp();
+    if (live) {
+      const long long b = i / p.ppi;
+      float* dst = p.dx + (b * D) * p.ppi + (i - b * p.ppi);
+#pragma unroll 8
+      for (int d = 0; d < D; ++d) dst[static_cast<long long>(d) * p.ppi] = tile[lane * (D + 1) + d];
     }
   }
 }

@@ -61,46 +61,48 @@ def sharded_fwd_bwd(stages, x, cls, temperature, num_classes, eps, need_grad, gr
 
     ehat_all = stages.empty((cols_pad, dim), torch.bfloat16)
     bits_all = stages.empty((cols_pad,), i32)
-    w_all = stages.zeros((cols_pad,), f32)
+    tor_all = stages.empty((cols_pad // 128,), i32)
+    w_all = stages.empty((cols_pad,), f32)
     sl = slice(rank * rows_pad, (rank + 1) * rows_pad)
-    ehat, bits, w = ehat_all[sl], bits_all[sl], w_all[sl]
+    tl = slice(rank * (rows_pad // 128), (rank + 1) * (rows_pad // 128))
+    ehat, bits, tor, w = ehat_all[sl], bits_all[sl], tor_all[tl], w_all[sl]
     inv_norm = stages.empty((rows_pad,), f32)
-    pos = stages.empty((rows_pad,), f32)
-    rowsum = stages.empty((rows_pad,), f32)
-    gpos = stages.zeros((rows_pad,), f32)
+    perm = stages.empty((max(n, 1),), i32)
+    seg = stages.empty((C + 2,), i32)
+    rowsum = stages.zeros((rows_pad,), f32)
+    gpos = stages.empty((rows_pad,), f32)
     stats = stages.zeros((C * dim + C,), f32)           # class_sum | class_mass
     class_sum, class_mass = stats[:C * dim], stats[C * dim:]
     dproto = stages.zeros((C * dim,), f32)
     loss_acc = stages.zeros((1,), torch.float64)
-    bound = stages.zeros((1,), f32) + 1.0               # |cos| <= 1 for unit vectors
     loss = stages.empty((), f32)
 
-    stages.prepare(xc, layout, batch, ppi, dim, cls_c, C, eps, ehat, bits, inv_norm, class_sum, class_mass)
+    stages.prepare(xc, layout, batch, ppi, dim, cls_c, C, eps, ehat, bits, inv_norm, perm, tor, seg, class_sum,
+                   class_mass)
     if G > 1:
         dist.all_reduce(stats, group=group)
         _all_gather_into(ehat_all, ehat, group)
         _all_gather_into(bits_all, bits, group)
-    stages.pos(ehat, bits, n, rows_pad, dim, C, class_sum, class_mass, temperature, bound, pos, rowsum)
-    stages.rowsum(ehat, bits, rows_pad, ehat_all, bits_all, cols_pad, dim, temperature, bound, rowsum)
-    stages.mid(ehat, bits, n, dim, C, pos, rowsum, temperature, bound, w, gpos, loss_acc, dproto)
+        _all_gather_into(tor_all, tor, group)
+    stages.rowsum(ehat, bits, tor, rows_pad, ehat_all, bits_all, tor_all, cols_pad, dim, temperature, rowsum)
+    stages.mid(ehat, seg, rows_pad, dim, C, class_sum, class_mass, rowsum, temperature, w, gpos, loss_acc, dproto)
     if G > 1:
         dist.all_reduce(loss_acc, group=group)
     dx = None
     n_split = 1
-    part = None
     if need_grad:
         if G > 1:
             dist.all_reduce(dproto, group=group)
             _all_gather_into(w_all, w, group)
         n_split = stages.grad_splits(rows_pad, cols_pad, dim)
         part = stages.empty((n_split, rows_pad, dim), f32)
-        stages.grad(ehat, bits, w, rows_pad, ehat_all, bits_all, w_all, cols_pad, dim, temperature, bound, part,
-                    n_split)
+        stages.grad(ehat, bits, tor, w, rows_pad, ehat_all, bits_all, tor_all, w_all, cols_pad, dim, temperature,
+                    part, n_split)
         dx = stages.empty(tuple(xc.shape), f32)
     else:
         part = stages.empty((1,), f32)
-    stages.final(ehat, bits, inv_norm, part, n_split, rows_pad, batch, ppi, dim, C, class_sum, class_mass, gpos,
-                 dproto, loss_acc, temperature, layout, dx, loss)
+    stages.final(ehat, bits, inv_norm, perm, part, n_split, rows_pad, batch, ppi, dim, C, class_sum, class_mass,
+                 gpos, dproto, loss_acc, temperature, layout, dx, loss)
     return loss, dx
 
 

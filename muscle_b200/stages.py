@@ -36,56 +36,52 @@ class CudaStages:
         return torch.zeros(shape, dtype=dtype, device=self.device)
 
     # -- stages --------------------------------------------------------------------------------
-    def prepare(self, x, layout, batch, ppi, dim, cls, num_classes, eps, ehat, bits, inv_norm, class_sum,
-                class_mass):
+    def prepare(self, x, layout, batch, ppi, dim, cls, num_classes, eps, ehat, bits, inv_norm, perm, tor, seg,
+                class_sum, class_mass):
+        n = batch * ppi
+        sb = int(self.lib.muscle_infonce_prepare_scratch_bytes(n))
+        scratch = torch.empty(sb, dtype=torch.uint8, device=self.device)
         with torch.cuda.device(self.device):
             rc = self.lib.muscle_infonce_prepare(
                 x.data_ptr(), layout, batch, ppi, dim, cls.data_ptr(), 1 if cls.dtype == torch.int64 else 0,
-                num_classes, float(eps), ehat.data_ptr(), bits.data_ptr(), inv_norm.data_ptr(),
-                class_sum.data_ptr(), class_mass.data_ptr(), _sp(self.device))
+                num_classes, float(eps), ehat.data_ptr(), bits.data_ptr(), inv_norm.data_ptr(), perm.data_ptr(),
+                tor.data_ptr(), seg.data_ptr(), class_sum.data_ptr(), class_mass.data_ptr(), scratch.data_ptr(), sb,
+                _sp(self.device))
         _lib.check(rc, "infonce_prepare")
 
-    def pos(self, ehat, bits, n_rows, rows_pad, dim, num_classes, class_sum, class_mass, temperature, bound, pos,
-            rowsum):
-        with torch.cuda.device(self.device):
-            rc = self.lib.muscle_infonce_pos(
-                ehat.data_ptr(), bits.data_ptr(), n_rows, rows_pad, dim, num_classes, class_sum.data_ptr(),
-                class_mass.data_ptr(), float(temperature), bound.data_ptr(), pos.data_ptr(), rowsum.data_ptr(),
-                _sp(self.device))
-        _lib.check(rc, "infonce_pos")
-
-    def rowsum(self, ehat_rows, bits_rows, rows_pad, ehat_cols, bits_cols, cols_pad, dim, temperature, bound,
-               rowsum):
+    def rowsum(self, ehat_rows, bits_rows, tor_rows, rows_pad, ehat_cols, bits_cols, tor_cols, cols_pad, dim,
+               temperature, rowsum):
         with torch.cuda.device(self.device):
             rc = self.lib.muscle_infonce_rowsum(
-                ehat_rows.data_ptr(), bits_rows.data_ptr(), rows_pad, ehat_cols.data_ptr(), bits_cols.data_ptr(),
-                cols_pad, dim, float(temperature), bound.data_ptr(), rowsum.data_ptr(), _sp(self.device))
+                ehat_rows.data_ptr(), bits_rows.data_ptr(), tor_rows.data_ptr(), rows_pad, ehat_cols.data_ptr(),
+                bits_cols.data_ptr(), tor_cols.data_ptr(), cols_pad, dim, float(temperature), rowsum.data_ptr(),
+                _sp(self.device))
         _lib.check(rc, "infonce_rowsum")
 
-    def mid(self, ehat, bits, n_rows, dim, num_classes, pos, rowsum, temperature, bound, w, gpos, loss_acc,
-            dproto):
+    def mid(self, ehat, seg, rows_pad, dim, num_classes, class_sum, class_mass, rowsum, temperature, w, gpos,
+            loss_acc, dproto):
         with torch.cuda.device(self.device):
             rc = self.lib.muscle_infonce_mid(
-                ehat.data_ptr(), bits.data_ptr(), n_rows, dim, num_classes, pos.data_ptr(), rowsum.data_ptr(),
-                float(temperature), bound.data_ptr(), w.data_ptr(), gpos.data_ptr(), loss_acc.data_ptr(),
-                dproto.data_ptr(), _sp(self.device))
+                ehat.data_ptr(), seg.data_ptr(), rows_pad, dim, num_classes, class_sum.data_ptr(),
+                class_mass.data_ptr(), rowsum.data_ptr(), float(temperature), w.data_ptr(), gpos.data_ptr(),
+                loss_acc.data_ptr(), dproto.data_ptr(), _sp(self.device))
         _lib.check(rc, "infonce_mid")
 
-    def grad(self, ehat_rows, bits_rows, w_rows, rows_pad, ehat_cols, bits_cols, w_cols, cols_pad, dim,
-             temperature, bound, part, n_split):
+    def grad(self, ehat_rows, bits_rows, tor_rows, w_rows, rows_pad, ehat_cols, bits_cols, tor_cols, w_cols,
+             cols_pad, dim, temperature, part, n_split):
         with torch.cuda.device(self.device):
             rc = self.lib.muscle_infonce_grad(
-                ehat_rows.data_ptr(), bits_rows.data_ptr(), w_rows.data_ptr(), rows_pad, ehat_cols.data_ptr(),
-                bits_cols.data_ptr(), w_cols.data_ptr(), cols_pad, dim, float(temperature), bound.data_ptr(),
-                part.data_ptr(), n_split, _sp(self.device))
+                ehat_rows.data_ptr(), bits_rows.data_ptr(), tor_rows.data_ptr(), w_rows.data_ptr(), rows_pad,
+                ehat_cols.data_ptr(), bits_cols.data_ptr(), tor_cols.data_ptr(), w_cols.data_ptr(), cols_pad, dim,
+                float(temperature), part.data_ptr(), n_split, _sp(self.device))
         _lib.check(rc, "infonce_grad")
 
-    def final(self, ehat, bits, inv_norm, part, n_split, rows_pad, batch, ppi, dim, num_classes, class_sum,
+    def final(self, ehat, bits, inv_norm, perm, part, n_split, rows_pad, batch, ppi, dim, num_classes, class_sum,
               class_mass, gpos, dproto, loss_acc, temperature, layout, dx, loss_out):
         with torch.cuda.device(self.device):
             rc = self.lib.muscle_infonce_final(
-                ehat.data_ptr(), bits.data_ptr(), inv_norm.data_ptr(), part.data_ptr(), n_split, rows_pad, batch,
-                ppi, dim, num_classes, class_sum.data_ptr(), class_mass.data_ptr(), gpos.data_ptr(),
-                dproto.data_ptr(), loss_acc.data_ptr(), float(temperature), layout,
+                ehat.data_ptr(), bits.data_ptr(), inv_norm.data_ptr(), perm.data_ptr(), part.data_ptr(), n_split,
+                rows_pad, batch, ppi, dim, num_classes, class_sum.data_ptr(), class_mass.data_ptr(),
+                gpos.data_ptr(), dproto.data_ptr(), loss_acc.data_ptr(), float(temperature), layout,
                 dx.data_ptr() if dx is not None else None, loss_out.data_ptr(), _sp(self.device))
         _lib.check(rc, "infonce_final")
