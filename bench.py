@@ -269,19 +269,21 @@ def main():
         dproto = st.zeros((C * dim,), f32)
         lacc = st.zeros((1,), torch.float64)
         st.prepare(x_d, _lib.LAYOUT_NCHW, lb, h * w, dim, c_d, C, 1e-12, ehat, bits, inv_norm, perm, tor, seg, cs, cm)
-        st.rowsum(ehat, bits, tor, rows_pad, ehat, bits, tor, cols_pad, dim, TEMPERATURE, rowsum)
+        unit_off = st.empty((rows_pad // st.unit_rows(dim) + 1,), i32)
+        st.plan(tor, rows_pad, tor, cols_pad, dim, unit_off)
+        st.rowsum(ehat, bits, tor, rows_pad, ehat, bits, tor, cols_pad, unit_off, dim, TEMPERATURE, rowsum)
         st.mid(ehat, seg, rows_pad, dim, C, cs, cm, rowsum, TEMPERATURE, wv, gpos, lacc, dproto)
-        n_split = st.grad_splits(rows_pad, cols_pad, dim)
-        part = st.empty((n_split, rows_pad, dim), f32)
-        grad_fn = lambda: st.grad(ehat, bits, tor, wv, rows_pad, ehat, bits, tor, wv, cols_pad, dim, TEMPERATURE, part, n_split)
+        part = st.empty((st.part_slots(), rows_pad, dim), f32)
+        grad_fn = lambda: st.grad(ehat, bits, tor, wv, rows_pad, ehat, bits, tor, wv, cols_pad, unit_off, dim, TEMPERATURE, part)
         rs_tmp = st.zeros((rows_pad,), f32)
-        rowsum_fn = lambda: st.rowsum(ehat, bits, tor, rows_pad, ehat, bits, tor, cols_pad, dim, TEMPERATURE, rs_tmp)
+        rowsum_fn = lambda: st.rowsum(ehat, bits, tor, rows_pad, ehat, bits, tor, cols_pad, unit_off, dim, TEMPERATURE, rs_tmp)
+        live_units = int(unit_off[-1].item())
         for _ in range(3):
             grad_fn(); rowsum_fn()
         ksteps = max(10, min(args.steps, 50))
         kern["grad_s"] = timed(grad_fn, ksteps) / ksteps
         kern["rowsum_s"] = timed(rowsum_fn, ksteps) / ksteps
-        kern["n_split"] = n_split
+        kern["live_frac"] = live_units / float((rows_pad // st.unit_rows(dim)) * (cols_pad // 128))
 
     # max over ranks (device-timed)
     t = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device=dev)
@@ -315,7 +317,7 @@ def main():
                                     peak_source=pk["source"] + ", burst figure (kernel timed alone)",
                                     algorithmic="4*D flops per ordered pair (dQ+dK of the 6*D budget; S is recomputed, "
                                                 "the symmetric form needs one P@E product for both)",
-                                    us_per_launch=1e6 * kern["grad_s"], n_split=kern["n_split"])
+                                    us_per_launch=1e6 * kern["grad_s"], live_tile_fraction=kern["live_frac"])
             ach1 = 2.0 * dim * float(n_local) * float(n_global) / kern["rowsum_s"] / 1e12
             line["roofline_rowsum"] = dict(bound="tensor", kernel="pair_kernel<%d,MODE_ROWSUM>" % dim, achieved=ach1,
                                            peak=pk["bf16_burst"], unit="TFLOP/s", frac=ach1 / pk["bf16_burst"],

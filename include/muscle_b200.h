@@ -57,8 +57,8 @@ int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
 
 /* ------------------------------------------------------------------------------------------
  * Staged form of the same op, for the batch-sharded multi-GPU path: the host
- * runs  prepare -> [all-gather ehat/bits/tor, all-reduce class_sum/class_mass] -> rowsum ->
- * mid -> [all-gather w, all-reduce dproto/loss_acc] -> grad -> final.
+ * runs  prepare -> [all-gather ehat/bits/tor, all-reduce class_sum/class_mass] -> plan ->
+ * rowsum -> mid -> [all-gather w, all-reduce dproto/loss_acc] -> grad -> final.
  * "rows" are this rank's pixels, "cols" all pixels of all ranks; *_pad = round_up(n, 256).
  * Inside the library the pixels are kept SORTED BY CLASS (stable counting sort; invalid pixels
  * and zero pad rows last): arrays marked [sorted] are indexed by sorted row, `perm` maps a
@@ -80,12 +80,20 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
                            uint32_t* tor, uint32_t* seg, float* class_sum, float* class_mass,
                            void* scratch, size_t scratch_bytes, void* stream);
 
+/* Work partition of the two pair passes over rows x cols: unit_off [rows_pad/RB + 1] (RB = 256
+ * rows, 128 for dim 256) = running count of the LIVE (row block, column tile) units, i.e. those
+ * with at least one unmasked pair.  Every CTA of a pair pass takes an equal contiguous share of
+ * that range, so the passes stay balanced whatever the class mix. */
+int muscle_infonce_plan(const uint32_t* tor_rows, int64_t rows_pad, const uint32_t* tor_cols,
+                        int64_t cols_pad, int dim, uint32_t* unit_off, void* stream);
+
 /* rowsum[q] += sum_k [cls_k != cls_q] exp((e_q.e_k - 1)/T)   — tcgen05 pass 1 (caller zeroes
  * rowsum first). */
 int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows,
                           const uint32_t* tor_rows, int64_t rows_pad, const void* ehat_cols,
                           const uint32_t* bits_cols, const uint32_t* tor_cols, int64_t cols_pad,
-                          int dim, float temperature, float* rowsum, void* stream);
+                          const uint32_t* unit_off, int dim, float temperature, float* rowsum,
+                          void* stream);
 
 /* pos[q] = e_q . proto_{c_q} / T; rowsum[q] += exp(pos - 1/T); w[q] = 1/rowsum[q];
  * gpos[q] = (exp(pos - 1/T) w - 1)/T; loss_acc (double[1]) += sum_q (1/T + ln rowsum[q] - pos);
@@ -96,21 +104,24 @@ int muscle_infonce_mid(const void* ehat, const uint32_t* seg, int64_t rows_pad, 
                        float* rowsum, float temperature, float* w, float* gpos, double* loss_acc,
                        float* dproto, void* stream);
 
-/* part[s][q][:] = sum_{k in split s} [cls_k != cls_q] exp((e_q.e_k - 1)/T) (w_rows[q] +
- * w_cols[k]) e_k   — tcgen05 pass 2.  part: float [n_split, rows_pad, dim]. */
-int muscle_infonce_grad_splits(int64_t rows_pad, int64_t cols_pad, int dim);
+/* part[s][q][:] = sum_{k in share s} [cls_k != cls_q] exp((e_q.e_k - 1)/T) (w_rows[q] +
+ * w_cols[k]) e_k   — tcgen05 pass 2.  part: float [muscle_infonce_part_slots(), rows_pad, dim];
+ * slot s of a row holds the share of the s-th CTA that worked on the row's block (see plan);
+ * slots no CTA wrote are never read. */
+int muscle_infonce_part_slots(void);
 int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows,
                         const uint32_t* tor_rows, const float* w_rows, int64_t rows_pad,
                         const void* ehat_cols, const uint32_t* bits_cols,
-                        const uint32_t* tor_cols, const float* w_cols, int64_t cols_pad, int dim,
-                        float temperature, float* part, int n_split, void* stream);
+                        const uint32_t* tor_cols, const float* w_cols, int64_t cols_pad,
+                        const uint32_t* unit_off, int dim, float temperature, float* part,
+                        void* stream);
 
-/* dx = d(loss)/dx in the caller's pixel order and `layout`: sums the splits, adds the prototype
+/* dx = d(loss)/dx in the caller's pixel order and `layout`: sums the slots, adds the prototype
  * terms, back-propagates through the L2 normalisation.  loss_out = loss_acc / n_valid
  * (n_valid = sum of class_mass).  dx may be NULL (loss only). */
 int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* inv_norm,
-                         const int32_t* perm, const float* part, int n_split, int64_t rows_pad,
-                         int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
+                         const int32_t* perm, const float* part, const uint32_t* unit_off,
+                         int64_t rows_pad, int64_t cols_pad, int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
                          const float* class_sum, const float* class_mass, const float* gpos,
                          const float* dproto, const double* loss_acc, float temperature,
                          int layout, float* dx, float* loss_out, void* stream);

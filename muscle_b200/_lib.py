@@ -29,16 +29,17 @@ _SIGNATURES = {
     "muscle_infonce_prepare": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int, c_void_p, c_int, c_int, c_float,
                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                        c_void_p, c_void_p, c_size_t, c_void_p]),
+    "muscle_infonce_plan": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_void_p]),
     "muscle_infonce_rowsum": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64,
-                                      c_int, c_float, c_void_p, c_void_p]),
+                                      c_void_p, c_int, c_float, c_void_p, c_void_p]),
     "muscle_infonce_mid": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                    c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
-    "muscle_infonce_grad_splits": (c_int, [c_int64, c_int64, c_int]),
+    "muscle_infonce_part_slots": (c_int, []),
     "muscle_infonce_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p,
-                                    c_void_p, c_int64, c_int, c_float, c_void_p, c_int, c_void_p]),
-    "muscle_infonce_final": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64,
-                                     c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-                                     c_float, c_int, c_void_p, c_void_p, c_void_p]),
+                                    c_void_p, c_int64, c_void_p, c_int, c_float, c_void_p, c_void_p]),
+    "muscle_infonce_final": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64,
+                                     c_int64, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_float, c_int, c_void_p, c_void_p, c_void_p]),
     "muscle_debug_tile": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
 }
 

@@ -1,6 +1,7 @@
 // C-ABI of the dense label-masked pixel InfoNCE (include/muscle_b200.h) and its launch logic.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 #include "host_util.cuh"
 #include "pair_kernel.cuh"
@@ -22,25 +23,6 @@ int check_device() {
   return MUSCLE_OK;
 }
 
-// Column splits per row block: pick the split count whose wave-quantised cost is lowest.
-// cost(s) = waves(s) * (tiles per item + fixed per-item overhead in tile units).
-int choose_splits(int64_t n_row_blocks, int64_t n_col_tiles, int sm_count, int max_split) {
-  int best = 1;
-  double best_cost = 1e300;
-  const int hi = static_cast<int>(std::min<int64_t>(max_split, n_col_tiles));
-  for (int s = 1; s <= hi; ++s) {
-    const int64_t items = n_row_blocks * s;
-    const int64_t waves = (items + sm_count - 1) / sm_count;
-    const double per_item = std::ceil(static_cast<double>(n_col_tiles) / s) + 3.0;
-    const double cost = waves * per_item;
-    if (cost < best_cost * 0.999) {
-      best_cost = cost;
-      best = s;
-    }
-  }
-  return best;
-}
-
 template <int D, int MODE, int POLY>
 int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, int64_t cols_pad,
                 PairParams prm, cudaStream_t stream) {
@@ -56,8 +38,7 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
     MB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     attr_set = true;
   }
-  const int n_items = prm.n_row_blocks * prm.n_split;
-  const int grid = std::min(n_items, device_info().sm_count);
+  const int grid = device_info().sm_count;  // one persistent CTA per SM; shares come from unit_off
   kern<<<grid, C::THREADS, C::SMEM_BYTES, stream>>>(tm_row, tm_col, prm);
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
@@ -71,7 +52,11 @@ bool poly_ok(float temperature) { return 2.f * kLog2e / temperature < 100.f; }
 template <int MODE>
 int launch_pair_dim(int dim, bool poly, const void* ehat_rows, int64_t rows_pad,
                     const void* ehat_cols, int64_t cols_pad, PairParams prm, cudaStream_t stream) {
+  static const int dbg = getenv("MUSCLE_DEBUG_PAIR") ? atoi(getenv("MUSCLE_DEBUG_PAIR")) : 0;  // measurement variants
 #define MB_PAIR(DD)                                                                              \
+  if (DD == 128 && dbg == 1) return launch_pair<128, MODE, -1>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream); \
+  if (DD == 128 && dbg == 2) return launch_pair<128, MODE, 4>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream); \
+  if (DD == 128 && dbg == 3) return launch_pair<128, MODE, 0>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream); \
   return poly ? launch_pair<DD, MODE, kPoly>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream) \
               : launch_pair<DD, MODE, 0>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream);
   switch (dim) {
@@ -155,10 +140,11 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
 int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows,
                           const uint32_t* tor_rows, int64_t rows_pad, const void* ehat_cols,
                           const uint32_t* bits_cols, const uint32_t* tor_cols, int64_t cols_pad,
-                          int dim, float temperature, float* rowsum, void* stream_) {
+                          const uint32_t* unit_off, int dim, float temperature, float* rowsum,
+                          void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_device()) return rc;
-  if (!ehat_rows || !bits_rows || !tor_rows || !ehat_cols || !bits_cols || !tor_cols || !rowsum)
+  if (!ehat_rows || !bits_rows || !tor_rows || !ehat_cols || !bits_cols || !tor_cols || !unit_off || !rowsum)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
   if (!(temperature > 0.f)) return fail(MUSCLE_ERR_BAD_ARG, "temperature must be > 0");
@@ -166,11 +152,10 @@ int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows,
     return fail(MUSCLE_ERR_BAD_ARG, "padded sizes must be positive multiples of 256");
   PairParams prm{};
   prm.bits_row = bits_rows; prm.bits_col = bits_cols; prm.tor_row = tor_rows; prm.tor_col = tor_cols;
-  prm.rowsum = rowsum;
+  prm.rowsum = rowsum; prm.unit_off = unit_off;
   prm.scale_log2 = kLog2e / temperature;
   prm.n_row_blocks = static_cast<int>(rows_pad / rows_per_block(dim));
   prm.n_col_tiles = static_cast<int>(cols_pad / 128);
-  prm.n_split = choose_splits(prm.n_row_blocks, prm.n_col_tiles, device_info().sm_count, 64);
   prm.rows_pad = static_cast<int>(rows_pad);
   return launch_pair_dim<MODE_ROWSUM>(dim, poly_ok(temperature), ehat_rows, rows_pad, ehat_cols,
                                       cols_pad, prm, stream);
@@ -200,58 +185,71 @@ int muscle_infonce_mid(const void* ehat, const uint32_t* seg, int64_t rows_pad, 
   return MUSCLE_OK;
 }
 
-int muscle_infonce_grad_splits(int64_t rows_pad, int64_t cols_pad, int dim) {
-  if (!dim_ok(dim) || rows_pad <= 0 || cols_pad <= 0) return 1;
-  const DeviceInfo& di = device_info();
-  const int sms = di.ok ? di.sm_count : 148;
-  return choose_splits(rows_pad / rows_per_block(dim), cols_pad / 128, sms, 16);
+int muscle_infonce_part_slots(void) { return PAIR_SLOTS; }
+
+int muscle_infonce_plan(const uint32_t* tor_rows, int64_t rows_pad, const uint32_t* tor_cols,
+                        int64_t cols_pad, int dim, uint32_t* unit_off, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = check_device()) return rc;
+  if (!tor_rows || !tor_cols || !unit_off) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
+  if (rows_pad % 256 || cols_pad % 256 || rows_pad <= 0 || cols_pad <= 0)
+    return fail(MUSCLE_ERR_BAD_ARG, "padded sizes must be positive multiples of 256");
+  const int n_row_blocks = static_cast<int>(rows_pad / rows_per_block(dim));
+  const int n_col_tiles = static_cast<int>(cols_pad / 128);
+  if (static_cast<double>(n_row_blocks) * n_col_tiles >= 4.0e9)
+    return fail(MUSCLE_ERR_BAD_ARG, "too many tile units for one rank");
+  if (dim == 256) pair_plan_kernel<1><<<1, 1024, 0, stream>>>(tor_rows, n_row_blocks, tor_cols, n_col_tiles, unit_off);
+  else pair_plan_kernel<2><<<1, 1024, 0, stream>>>(tor_rows, n_row_blocks, tor_cols, n_col_tiles, unit_off);
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
 }
 
 int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows,
                         const uint32_t* tor_rows, const float* w_rows, int64_t rows_pad,
                         const void* ehat_cols, const uint32_t* bits_cols,
-                        const uint32_t* tor_cols, const float* w_cols, int64_t cols_pad, int dim,
-                        float temperature, float* part, int n_split, void* stream_) {
+                        const uint32_t* tor_cols, const float* w_cols, int64_t cols_pad,
+                        const uint32_t* unit_off, int dim, float temperature, float* part,
+                        void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_device()) return rc;
   if (!ehat_rows || !bits_rows || !tor_rows || !w_rows || !ehat_cols || !bits_cols || !tor_cols ||
-      !w_cols || !part)
+      !w_cols || !unit_off || !part)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
   if (!(temperature > 0.f)) return fail(MUSCLE_ERR_BAD_ARG, "temperature must be > 0");
   if (rows_pad % 256 || cols_pad % 256 || rows_pad <= 0 || cols_pad <= 0)
     return fail(MUSCLE_ERR_BAD_ARG, "padded sizes must be positive multiples of 256");
-  if (n_split < 1 || n_split > cols_pad / 128)
-    return fail(MUSCLE_ERR_BAD_ARG, "n_split must be in [1, cols_pad/128]");
   PairParams prm{};
   prm.bits_row = bits_rows; prm.bits_col = bits_cols; prm.tor_row = tor_rows; prm.tor_col = tor_cols;
-  prm.w_row = w_rows; prm.w_col = w_cols; prm.part = part;
+  prm.w_row = w_rows; prm.w_col = w_cols; prm.part = part; prm.unit_off = unit_off;
   prm.scale_log2 = kLog2e / temperature;
   prm.n_row_blocks = static_cast<int>(rows_pad / rows_per_block(dim));
   prm.n_col_tiles = static_cast<int>(cols_pad / 128);
-  prm.n_split = n_split;
   prm.rows_pad = static_cast<int>(rows_pad);
   return launch_pair_dim<MODE_GRAD>(dim, poly_ok(temperature), ehat_rows, rows_pad, ehat_cols,
                                     cols_pad, prm, stream);
 }
 
 int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* inv_norm,
-                         const int32_t* perm, const float* part, int n_split, int64_t rows_pad,
-                         int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
+                         const int32_t* perm, const float* part, const uint32_t* unit_off,
+                         int64_t rows_pad, int64_t cols_pad, int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
                          const float* class_sum, const float* class_mass, const float* gpos,
                          const float* dproto, const double* loss_acc, float temperature,
                          int layout, float* dx, float* loss_out, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_device()) return rc;
   if (!class_mass || !loss_acc) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
-  if (dx && (!ehat || !bits || !inv_norm || !perm || !part || !class_sum || !gpos || !dproto))
+  if (dx && (!ehat || !bits || !inv_norm || !perm || !part || !unit_off || !class_sum || !gpos || !dproto))
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
   if (layout != MUSCLE_LAYOUT_PIXEL_MAJOR && layout != MUSCLE_LAYOUT_NCHW)
     return fail(MUSCLE_ERR_BAD_ARG, "unknown layout %d", layout);
   FinalParams p;
   p.ehat = static_cast<const __nv_bfloat16*>(ehat); p.bits = bits; p.inv_norm = inv_norm;
-  p.perm = perm; p.part = part; p.n_split = n_split; p.rows_pad = rows_pad;
+  p.perm = perm; p.part = part; p.unit_off = unit_off; p.rows_pad = rows_pad;
+  p.n_row_blocks = static_cast<int>(rows_pad / rows_per_block(dim));
+  p.n_col_tiles = static_cast<int>(cols_pad / 128); p.n_ctas = device_info().sm_count;
   p.n = batch * pixels_per_image; p.ppi = pixels_per_image; p.C = num_classes;
   p.class_sum = class_sum; p.class_mass = class_mass; p.gpos = gpos; p.dproto = dproto;
   p.loss_acc = loss_acc; p.inv_tau = 1.f / temperature; p.layout = layout; p.dx = dx;
@@ -278,17 +276,15 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
 namespace {
 
 struct Workspace {
-  size_t ehat, bits, inv_norm, perm, tor, rowsum, w, gpos, small, scratch, part, total;
+  size_t ehat, bits, inv_norm, perm, tor, unit_off, rowsum, w, gpos, small, scratch, part, total;
   size_t seg, class_sum, class_mass, dproto, loss_acc, small_bytes;  // offsets inside `small`
   size_t zero_lo, zero_bytes;  // rowsum .. small are zeroed with one memset
-  int n_split;
   int64_t rows_pad;
 };
 
 Workspace plan_workspace(int64_t n, int dim, int C) {
   Workspace ws{};
   ws.rows_pad = muscle_pad_rows(n);
-  ws.n_split = muscle_infonce_grad_splits(ws.rows_pad, ws.rows_pad, dim);
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
   const size_t rp = static_cast<size_t>(ws.rows_pad);
@@ -297,6 +293,7 @@ Workspace plan_workspace(int64_t n, int dim, int C) {
   ws.inv_norm = take(rp * 4);
   ws.perm = take(rp * 4);
   ws.tor = take(rp / 128 * 4);
+  ws.unit_off = take((rp / 128 + 1) * 4);
   ws.w = take(rp * 4);
   ws.gpos = take(rp * 4);
   ws.rowsum = take(rp * 4);
@@ -312,7 +309,7 @@ Workspace plan_workspace(int64_t n, int dim, int C) {
   ws.zero_lo = ws.rowsum;
   ws.zero_bytes = off - ws.rowsum;
   ws.scratch = take(muscle_infonce_prepare_scratch_bytes(n));
-  ws.part = take(static_cast<size_t>(ws.n_split) * rp * dim * 4);
+  ws.part = take(static_cast<size_t>(PAIR_SLOTS) * rp * dim * 4);
   ws.total = off;
   return ws;
 }
@@ -351,6 +348,7 @@ int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
   float* inv_norm = reinterpret_cast<float*>(base + ws.inv_norm);
   int32_t* perm = reinterpret_cast<int32_t*>(base + ws.perm);
   uint32_t* tor = reinterpret_cast<uint32_t*>(base + ws.tor);
+  uint32_t* unit_off = reinterpret_cast<uint32_t*>(base + ws.unit_off);
   float* rowsum = reinterpret_cast<float*>(base + ws.rowsum);
   float* w = reinterpret_cast<float*>(base + ws.w);
   float* gpos = reinterpret_cast<float*>(base + ws.gpos);
@@ -368,19 +366,21 @@ int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
                                   class_mass, base + ws.scratch,
                                   muscle_infonce_prepare_scratch_bytes(n), stream);
   if (rc) return rc;
-  rc = muscle_infonce_rowsum(ehat, bits, tor, ws.rows_pad, ehat, bits, tor, ws.rows_pad, dim,
-                             temperature, rowsum, stream);
+  rc = muscle_infonce_plan(tor, ws.rows_pad, tor, ws.rows_pad, dim, unit_off, stream);
+  if (rc) return rc;
+  rc = muscle_infonce_rowsum(ehat, bits, tor, ws.rows_pad, ehat, bits, tor, ws.rows_pad, unit_off,
+                             dim, temperature, rowsum, stream);
   if (rc) return rc;
   rc = muscle_infonce_mid(ehat, seg, ws.rows_pad, dim, num_classes, class_sum, class_mass, rowsum,
                           temperature, w, gpos, loss_acc, dproto, stream);
   if (rc) return rc;
   if (dx_out) {
-    rc = muscle_infonce_grad(ehat, bits, tor, w, ws.rows_pad, ehat, bits, tor, w, ws.rows_pad, dim,
-                             temperature, part, ws.n_split, stream);
+    rc = muscle_infonce_grad(ehat, bits, tor, w, ws.rows_pad, ehat, bits, tor, w, ws.rows_pad,
+                             unit_off, dim, temperature, part, stream);
     if (rc) return rc;
   }
-  return muscle_infonce_final(ehat, bits, inv_norm, perm, part, ws.n_split, ws.rows_pad, batch,
-                              pixels_per_image, dim, num_classes, class_sum, class_mass, gpos,
+  return muscle_infonce_final(ehat, bits, inv_norm, perm, part, unit_off, ws.rows_pad, ws.rows_pad,
+                              batch, pixels_per_image, dim, num_classes, class_sum, class_mass, gpos,
                               dproto, loss_acc, temperature, layout, dx_out, loss_out, stream);
 }
 

@@ -6,10 +6,13 @@
 //   warp  8    TMA producer      (row tiles once per work item, column tiles through a ring)
 //   warp  9    tcgen05.mma issuer (one lane) + TMEM allocator
 //
-// Work item = (row block, column split).  Pixels arrive sorted by class (row_kernels.cuh), and a
-// per-tile class union (`tor`) lets the producer drop every (row block, column tile) whose pairs
-// are all masked (same single class) before anything is loaded or multiplied; the epilogue takes a
-// mask-free path for tiles whose class sets are disjoint.
+// Pixels arrive sorted by class (row_kernels.cuh), and a per-tile class union (`tor`) lets the
+// producer drop every (row block, column tile) whose pairs are all masked (same single class)
+// before anything is loaded or multiplied; the epilogue takes a mask-free path for tiles whose
+// class sets are disjoint.  The LIVE (row block, column tile) units are numbered row block by row
+// block (`unit_off`, pair_plan_kernel) and every CTA takes one contiguous share of that range, so
+// the SMs finish together whatever the class mix; a CTA's share of one row block is a work item,
+// and the item's index among the CTAs that touch the row block is its output `slot`.
 //
 // Two "streams" run through the tensor pipe, one per epilogue group (D <= 128: stream = row
 // tile, both see every column tile; D = 256: one row tile, the streams alternate column tiles).
@@ -42,16 +45,26 @@ struct PairParams {
   const uint32_t* bits_col;  // [cols_pad]
   const uint32_t* tor_row;   // [rows_pad/128]  OR of bits over the tile | TOR_INVALID
   const uint32_t* tor_col;   // [cols_pad/128]
+  const uint32_t* unit_off;  // [n_row_blocks+1]  first live unit of every row block
   const float* w_row;        // [rows_pad]  MODE_GRAD: 1/rowsum of the row pixel (0 = no query role)
   const float* w_col;        // [cols_pad]  MODE_GRAD: 1/rowsum of the column pixel
   float* rowsum;             // [rows_pad]  MODE_ROWSUM: += sum_k mask * exp((s - 1)/tau)
-  float* part;               // [n_split][rows_pad][D]  MODE_GRAD: partial sum_k T_qk c_k
+  float* part;               // [PAIR_SLOTS][rows_pad][D]  MODE_GRAD: partial sum_k T_qk c_k
   float scale_log2;          // log2(e) / tau
   int n_row_blocks;          // row blocks of RB rows
   int n_col_tiles;           // column tiles of 128
-  int n_split;               // column splits per row block
   int rows_pad;
 };
+
+constexpr int PAIR_SLOTS = 4;             // a row block is shared by at most this many CTAs
+constexpr uint32_t ITEM_END = 0xffffffffu;
+
+// live units per CTA: an even share, but never so small that a row block spans > PAIR_SLOTS CTAs
+__host__ __device__ inline uint32_t pair_units_per_cta(uint32_t total_units, int n_ctas, int n_col_tiles) {
+  const uint32_t even = (total_units + n_ctas - 1) / n_ctas;
+  const uint32_t floor_ = (n_col_tiles + PAIR_SLOTS - 2) / (PAIR_SLOTS - 1);
+  return even > floor_ ? even : floor_;
+}
 
 template <int D>
 struct PairCfg {
@@ -68,8 +81,8 @@ struct PairCfg {
   static constexpr int SMEM_W = SMEM_BITS + NST * 512;
   static constexpr int SMEM_BAR = SMEM_W + NST * 512;
   static constexpr int NBAR = 2 * NST + 14;
-  static constexpr int SMEM_INFO = SMEM_BAR + NBAR * 8;  // item header [2], stage info [NST]
-  static constexpr int SMEM_TMEMPTR = SMEM_INFO + (2 + NST) * 4;
+  static constexpr int SMEM_INFO = SMEM_BAR + NBAR * 8;  // item headers [2][4], stage info [NST]
+  static constexpr int SMEM_TMEMPTR = SMEM_INFO + (8 + NST) * 4;
   static constexpr int SMEM_BYTES = SMEM_TMEMPTR + 16 + 1024;  // +1024: manual 1024-B alignment
   static constexpr int ACC_COL = 256;
   static constexpr int THREADS = 320;
@@ -85,16 +98,74 @@ __device__ __forceinline__ bool tile_pair_full(uint32_t tor_r, uint32_t tor_c) {
   return (tor_r & tor_c & TOR_CLASSES) == 0u && (tor_c & TOR_INVALID) == 0u;
 }
 
-// Epilogue of one 64-column half for one thread (= one row).  FULL: no label mask needed.
-// POLY of every 4 element pairs take the FMA-pipe exponential.
+// ------------------------------------------------------------------------------------------
+// unit_off[rb] = number of live (row block, column tile) units before row block rb;
+// unit_off[n_row_blocks] = total.  A unit is dead when every row tile of the block is dead
+// against the column tile (tile_pair_dead), which depends on the column tile only through
+// "empty" / "exactly class c", so a histogram of the column tiles gives every row block's count.
+template <int QT>
+__global__ void __launch_bounds__(1024) pair_plan_kernel(const uint32_t* tor_row, int n_row_blocks,
+                                                         const uint32_t* tor_col, int n_col_tiles,
+                                                         uint32_t* unit_off) {
+  __shared__ uint32_t single[32];   // column tiles whose class set is exactly {c}
+  __shared__ uint32_t empty_cnt;    // column tiles without any class
+  __shared__ uint32_t warp_tot[32];
+  __shared__ uint32_t carry;
+  if (threadIdx.x < 32) single[threadIdx.x] = 0u;
+  if (threadIdx.x == 0) { empty_cnt = 0u; carry = 0u; }
+  __syncthreads();
+  for (int j = threadIdx.x; j < n_col_tiles; j += blockDim.x) {
+    const uint32_t c = tor_col[j] & TOR_CLASSES;
+    if (c == 0u) atomicAdd(&empty_cnt, 1u);
+    else if ((c & (c - 1u)) == 0u) atomicAdd(&single[31 - __clz(c)], 1u);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int base = 0; base < n_row_blocks; base += blockDim.x) {
+    const int rb = base + threadIdx.x;
+    uint32_t live = 0;
+    if (rb < n_row_blocks) {
+      uint32_t uni = 0;       // union of the block's row-tile class sets
+      bool one = true;        // every non-empty row tile is the same single class
+      for (int qt = 0; qt < QT; ++qt) {
+        const uint32_t r = tor_row[rb * QT + qt] & TOR_CLASSES;
+        if (r == 0u) continue;
+        if ((r & (r - 1u)) != 0u || (uni != 0u && uni != r)) one = false;
+        uni |= r;
+      }
+      if (uni != 0u) {
+        live = static_cast<uint32_t>(n_col_tiles) - empty_cnt;
+        if (one) live -= single[31 - __clz(uni)];
+      }
+    }
+    // block-wide exclusive scan of `live`
+    uint32_t inc = live;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += u;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    uint32_t woff = 0;
+    for (int w = 0; w < warp; ++w) woff += warp_tot[w];
+    const uint32_t before = carry + woff + inc - live;
+    if (rb < n_row_blocks) unit_off[rb] = before;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) carry = before + live;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) unit_off[n_row_blocks] = carry;
+}
+
+// ------------------------------------------------------------------------------------------
+// Epilogue math of one 64-column half for one thread (= one row); v = the S values.
+// FULL: no label mask needed.  POLY of every 4 element pairs take the FMA-pipe exponential.
 template <int MODE, int POLY, bool FULL>
-__device__ __forceinline__ void pair_half_epilogue(uint32_t s_addr, const uint8_t* bits_sm,
-                                                   const uint8_t* w_sm, uint32_t qmask, float a,
-                                                   float wrow, uint64_t (&racc)[4]) {
-  uint32_t v[2][32];
-  tmem_ld32(s_addr, v[0]);
-  tmem_ld32(s_addr + 32, v[1]);
-  tmem_wait_ld();
+__device__ __forceinline__ void pair_half_math(uint32_t (&v)[2][32], uint32_t t_addr,
+                                               const uint8_t* bits_sm, const uint8_t* w_sm,
+                                               uint32_t qmask, float a, float wrow,
+                                               uint64_t (&racc)[4]) {
   const uint64_t a2 = pack2(a, a);
   const uint64_t noff2 = pack2(-a, -a);  // the shift: exp((s - 1)/tau), |s| <= 1 for unit vectors
   const uint64_t wr2 = pack2(wrow, wrow);
@@ -109,7 +180,9 @@ __device__ __forceinline__ void pair_half_epilogue(uint32_t s_addr, const uint8_
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
         const uint64_t x = fma2(pack2u(v[c][q4 * 4 + 2 * s], v[c][q4 * 4 + 2 * s + 1]), a2, noff2);
-        if (((q4 * 2 + s) & 3) < POLY) {
+        if (POLY < 0) {
+          e[s] = x;  // measurement variant: no exponential
+        } else if (((q4 * 2 + s) & 3) < POLY) {
           e[s] = ex2_poly2(x);
         } else {
           float x0, x1;
@@ -143,7 +216,7 @@ __device__ __forceinline__ void pair_half_epilogue(uint32_t s_addr, const uint8_
         packed[q4 * 2 + 1] = pack_bf16x2(f2, f3);
       }
     }
-    if (MODE == MODE_GRAD) tmem_st16(s_addr + c * 16, packed);
+    if (MODE == MODE_GRAD) tmem_st16(t_addr + c * 16, packed);
   }
 }
 
@@ -172,7 +245,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
   auto acc_full = [&](int s) { return bar0 + 8u * (2 * NST + 10 + s); };
   auto acc_empty = [&](int s) { return bar0 + 8u * (2 * NST + 12 + s); };
   volatile uint32_t* info = reinterpret_cast<volatile uint32_t*>(smem_gen + C::SMEM_INFO);
-  // info[0..1]: tiles of the item (double-buffered by item parity); info[2+st]: tor of the stage's column tile
+  // info[4*(it&1) + {0,1,2}]: live tiles, row block, slot of item `it`; info[8+st]: tor of the stage's column tile
   volatile uint32_t* tmem_ptr_smem =
       reinterpret_cast<volatile uint32_t*>(smem_gen + C::SMEM_TMEMPTR);
 
@@ -209,24 +282,34 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem = *tmem_ptr_smem;
 
-  const int n_items = p.n_row_blocks * p.n_split;
-  auto item_range = [&](int item, int& rb, int& ks, int& t0, int& t1) {
-    rb = item / p.n_split;
-    ks = item - rb * p.n_split;
-    t0 = static_cast<int>((static_cast<long long>(p.n_col_tiles) * ks) / p.n_split);
-    t1 = static_cast<int>((static_cast<long long>(p.n_col_tiles) * (ks + 1)) / p.n_split);
-  };
   // stream-local tile k of stream g -> index within the item's list of live column tiles
   auto n_stream = [&](int n, int g) { return (QT == 2) ? n : ((n - g + 1) >> 1); };
   auto tile_of = [&](int g, int k) { return (QT == 2) ? k : (2 * k + g); };
 
   if (warp == 8) {
-    // ------------------------------------------------------------ TMA producer
+    // ------------------------------------------------------------ TMA producer + work partition
     if (lane == 0) {
+      const uint32_t total = __ldg(p.unit_off + p.n_row_blocks);
+      const uint32_t per = pair_units_per_cta(total, gridDim.x, p.n_col_tiles);
+      const uint64_t lo64 = static_cast<uint64_t>(per) * blockIdx.x;
+      uint32_t u = lo64 < total ? static_cast<uint32_t>(lo64) : total;
+      const uint32_t u1 = (lo64 + per < total) ? static_cast<uint32_t>(lo64 + per) : total;
+      // largest rb with unit_off[rb] <= u
+      int rb = 0;
+      {
+        int lo = 0, hi = p.n_row_blocks;  // unit_off[lo] <= u, unit_off[hi] > u (when u < total)
+        while (hi - lo > 1) {
+          const int mid = (lo + hi) >> 1;
+          if (__ldg(p.unit_off + mid) <= u) lo = mid; else hi = mid;
+        }
+        rb = lo;
+      }
       uint32_t gcnt = 0, it = 0;
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-        int rb, ks, t0, t1;
-        item_range(item, rb, ks, t0, t1);
+      while (u < u1) {
+        const uint32_t U0 = __ldg(p.unit_off + rb), U1 = __ldg(p.unit_off + rb + 1);
+        if (U1 <= u) { ++rb; continue; }   // row blocks without live units
+        const uint32_t a = u - U0;
+        const uint32_t e = (u1 < U1 ? u1 : U1) - U0;
         uint32_t tor_r[QT];
         for (int qt = 0; qt < QT; ++qt) tor_r[qt] = __ldg(p.tor_row + rb * QT + qt);
         auto dead = [&](uint32_t tc) {
@@ -234,25 +317,27 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           for (int qt = 0; qt < QT; ++qt) d = d && tile_pair_dead(tor_r[qt], tc);
           return d;
         };
-        uint32_t n = 0;
-        for (int j = t0; j < t1; ++j) n += dead(__ldg(p.tor_col + j)) ? 0u : 1u;
         mbar_wait(q_empty, (it & 1) ^ 1);
-        info[it & 1] = n;
+        info[4 * (it & 1) + 0] = e - a;
+        info[4 * (it & 1) + 1] = static_cast<uint32_t>(rb);
+        info[4 * (it & 1) + 2] = blockIdx.x - U0 / per;
         mbar_arrive_expect_tx(q_full, QT * C::TILE_BYTES);
         for (int qt = 0; qt < QT; ++qt)
-          for (int a = 0; a < C::NPANEL; ++a)
-            tma_load_2d(q_smem + qt * C::TILE_BYTES + a * C::PANEL_BYTES, &tm_row, q_full, a * 64,
+          for (int pa = 0; pa < C::NPANEL; ++pa)
+            tma_load_2d(q_smem + qt * C::TILE_BYTES + pa * C::PANEL_BYTES, &tm_row, q_full, pa * 64,
                         (rb * QT + qt) * 128);
-        for (int j = t0; j < t1; ++j) {
+        uint32_t li = 0;  // live index of column tile j within the row block
+        for (int j = 0; j < p.n_col_tiles && li < e; ++j) {
           const uint32_t tc = __ldg(p.tor_col + j);
           if (dead(tc)) continue;
+          if (li++ < a) continue;
           const int st = gcnt % NST;
           mbar_wait(k_empty(st), ((gcnt / NST) & 1) ^ 1);
-          info[2 + st] = tc;
+          info[8 + st] = tc;
           mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES + 512 + (MODE == MODE_GRAD ? 512 : 0));
-          for (int a = 0; a < C::NPANEL; ++a)
-            tma_load_2d(k_smem + st * C::TILE_BYTES + a * C::PANEL_BYTES, &tm_col, k_full(st),
-                        a * 64, j * 128);
+          for (int pa = 0; pa < C::NPANEL; ++pa)
+            tma_load_2d(k_smem + st * C::TILE_BYTES + pa * C::PANEL_BYTES, &tm_col, k_full(st),
+                        pa * 64, j * 128);
           bulk_load_1d(bits_smem + st * 512, p.bits_col + static_cast<size_t>(j) * 128, 512,
                        k_full(st));
           if (MODE == MODE_GRAD)
@@ -260,23 +345,28 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
                          k_full(st));
           ++gcnt;
         }
+        u = U0 + e;
+        ++it;
       }
+      mbar_wait(q_empty, (it & 1) ^ 1);
+      info[4 * (it & 1) + 0] = ITEM_END;
+      mbar_arrive(q_full);
     }
   } else if (warp == 9) {
     // ------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // (elect.sync, not lane == 0: ptxas then knows a single thread runs the region and feeds the
+    // uniform-register operands of UTCHMMA without a per-instruction waterfall loop)
+    if (elect_one()) {
       constexpr uint32_t IDESC_S = umma_idesc_bf16(128, 64, 0, 0);
       constexpr uint32_t IDESC_G = umma_idesc_bf16(128, D, 0, 1);
-      uint32_t gbase = 0, it = 0, ita = 0;
+      uint32_t gbase = 0;
       uint32_t cnt_t[2][2] = {{0, 0}, {0, 0}};
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+      for (uint32_t it = 0;; ++it) {
         mbar_wait(q_full, it & 1);
         tc_fence_after();
-        const int n = static_cast<int>(info[it & 1]);
-        if (n == 0) {
-          mbar_arrive(q_empty);
-          continue;
-        }
+        const uint32_t n_u = info[4 * (it & 1) + 0];
+        if (n_u == ITEM_END) break;
+        const int n = static_cast<int>(n_u);
         const int nk[2] = {n_stream(n, 0), n_stream(n, 1)};
         const int kmax = nk[0];  // nk[0] >= nk[1]
 
@@ -309,8 +399,8 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
             if (nk[g] > 0) issue_S(g, 0, h);
         if (kmax <= 1) tc_commit(q_empty);
         if (MODE == MODE_GRAD) {
-          mbar_wait(acc_empty(0), (ita & 1) ^ 1);
-          if (QT == 2) mbar_wait(acc_empty(1), (ita & 1) ^ 1);
+          mbar_wait(acc_empty(0), (it & 1) ^ 1);
+          if (QT == 2) mbar_wait(acc_empty(1), (it & 1) ^ 1);
           tc_fence_after();
         }
         for (int k = 0; k < kmax; ++k) {
@@ -335,7 +425,16 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
                          IDESC_G, (first && kk == 0) ? 0u : 1u);
                 if (h == 1 && (QT == 1 || g == 1)) tc_commit(k_empty(st));
               }
-              if (more) issue_S(g, k + 1, h);
+              // D = 256 (two ring stages, one per stream): the stream's next tile reuses the stage
+              // of its current one, which only frees after the G MMA of half 1
+              if (QT == 1 && MODE == MODE_GRAD) {
+                if (more && h == 1) {
+                  issue_S(g, k + 1, 0);
+                  issue_S(g, k + 1, 1);
+                }
+              } else if (more) {
+                issue_S(g, k + 1, h);
+              }
             }
           }
           if (k == kmax - 2) tc_commit(q_empty);  // the last S MMAs of the item are in flight
@@ -345,7 +444,6 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           if (QT == 2) tc_commit(acc_full(1));
         }
         gbase += n;
-        ++ita;
       }
     }
   } else {
@@ -354,10 +452,16 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
     const int wq = warp & 3;
     const uint32_t lane_addr = static_cast<uint32_t>(wq * 32) << 16;
     const float a = p.scale_log2;
-    uint32_t gbase = 0, it = 0, ita = 0, cnt = 0;
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-      int rb, ks, t0, t1;
-      item_range(item, rb, ks, t0, t1);
+    uint32_t gbase = 0, cnt = 0;
+    for (uint32_t it = 0;; ++it) {
+      mbar_wait(q_full, it & 1);
+      const uint32_t n_u = info[4 * (it & 1) + 0];
+      if (n_u == ITEM_END) break;
+      const int n = static_cast<int>(n_u);
+      const int rb = static_cast<int>(info[4 * (it & 1) + 1]);
+      const int slot = static_cast<int>(info[4 * (it & 1) + 2]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(q_empty);
       const int row_tile = rb * QT + (QT == 2 ? g : 0);
       const int row = row_tile * 128 + wq * 32 + lane;
       const uint32_t rbits = __ldg(p.bits_row + row);
@@ -365,17 +469,13 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
       const uint32_t qmask = rbits ? ~rbits : 0u;
       float wrow = 0.f;
       if (MODE == MODE_GRAD) wrow = __ldg(p.w_row + row);
-      mbar_wait(q_full, it & 1);
-      const int n = static_cast<int>(info[it & 1]);
-      __syncwarp();
-      if (lane == 0) mbar_arrive(q_empty);
       const int my_n = n_stream(n, g);
       uint64_t racc[4] = {0ull, 0ull, 0ull, 0ull};
       for (int k = 0; k < my_n; ++k, ++cnt) {
         const uint32_t gg = gbase + tile_of(g, k);
         const int st = gg % NST;
         mbar_wait(k_full(st), (gg / NST) & 1);
-        const uint32_t tor_c = info[2 + st];
+        const uint32_t tor_c = info[8 + st];
         const bool full = tile_pair_full(tor_r, tor_c);
 #pragma unroll 1
         for (int h = 0; h < 2; ++h) {
@@ -384,14 +484,25 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           const uint32_t s_addr = tmem + lane_addr + g * 128 + h * 64;
           const uint8_t* bsm = smem_gen + C::SMEM_BITS + st * 512 + h * 256;
           const uint8_t* wsm = smem_gen + C::SMEM_W + st * 512 + h * 256;
+          uint32_t v[2][32];
+          tmem_ld32(s_addr, v[0]);
+          tmem_ld32(s_addr + 32, v[1]);
+          tmem_wait_ld();
+          if (MODE == MODE_ROWSUM) {  // S_h is in registers: hand the buffer back before the math
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(t_full(g, h));
+          }
           if (full)
-            pair_half_epilogue<MODE, POLY, true>(s_addr, bsm, wsm, qmask, a, wrow, racc);
+            pair_half_math<MODE, POLY, true>(v, s_addr, bsm, wsm, qmask, a, wrow, racc);
           else
-            pair_half_epilogue<MODE, POLY, false>(s_addr, bsm, wsm, qmask, a, wrow, racc);
-          if (MODE == MODE_GRAD) tmem_wait_st();
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(t_full(g, h));
+            pair_half_math<MODE, POLY, false>(v, s_addr, bsm, wsm, qmask, a, wrow, racc);
+          if (MODE == MODE_GRAD) {
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(t_full(g, h));
+          }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(k_empty(st));
@@ -406,31 +517,24 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         const int acc = (QT == 2) ? g : 0;
         constexpr int NCH = (QT == 2) ? (D / 32) : (D / 64);
         const int col0 = (QT == 2) ? 0 : g * (D / 2);
-        float* dst = p.part + (static_cast<size_t>(ks) * p.rows_pad + row) * D + col0;
-        if (n > 0) {
-          mbar_wait(acc_full(acc), ita & 1);
-          tc_fence_after();
+        float* dst = p.part + (static_cast<size_t>(slot) * p.rows_pad + row) * D + col0;
+        mbar_wait(acc_full(acc), it & 1);
+        tc_fence_after();
 #pragma unroll 1
-          for (int c = 0; c < NCH; ++c) {
-            uint32_t v[32];
-            tmem_ld32(tmem + lane_addr + C::ACC_COL + acc * D + col0 + c * 32, v);
-            tmem_wait_ld();
+        for (int c = 0; c < NCH; ++c) {
+          uint32_t v[32];
+          tmem_ld32(tmem + lane_addr + C::ACC_COL + acc * D + col0 + c * 32, v);
+          tmem_wait_ld();
 #pragma unroll
-            for (int q4 = 0; q4 < 8; ++q4)
-              reinterpret_cast<float4*>(dst + c * 32)[q4] =
-                  make_float4(__uint_as_float(v[q4 * 4]), __uint_as_float(v[q4 * 4 + 1]),
-                              __uint_as_float(v[q4 * 4 + 2]), __uint_as_float(v[q4 * 4 + 3]));
-          }
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(acc_empty(acc));
-        } else {
-#pragma unroll 1
-          for (int c = 0; c < NCH * 8; ++c)
-            reinterpret_cast<float4*>(dst)[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int q4 = 0; q4 < 8; ++q4)
+            reinterpret_cast<float4*>(dst + c * 32)[q4] =
+                make_float4(__uint_as_float(v[q4 * 4]), __uint_as_float(v[q4 * 4 + 1]),
+                            __uint_as_float(v[q4 * 4 + 2]), __uint_as_float(v[q4 * 4 + 3]));
         }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_empty(acc));
       }
-      if (n > 0) ++ita;
       gbase += n;
     }
   }

@@ -357,8 +357,11 @@ struct FinalParams {
   const uint32_t* bits;        // sorted
   const float* inv_norm;       // sorted
   const int* perm;             // [n] source pixel -> sorted row
-  const float* part;           // [n_split][rows_pad][D]
-  int n_split;
+  const float* part;           // [PAIR_SLOTS][rows_pad][D]
+  const uint32_t* unit_off;    // [n_row_blocks+1]  the pair passes' work partition (pair_plan_kernel)
+  int n_row_blocks;
+  int n_col_tiles;
+  int n_ctas;                  // grid of the gradient pass
   long long rows_pad;
   long long n;
   long long ppi;
@@ -376,7 +379,7 @@ struct FinalParams {
 
 // One block = 128 consecutive source pixels (the chunks of prepare_kernel), one warp = 32.
 // Per pixel the warp gathers its sorted row (lane holds channels lane, lane+32, ...), forms
-//   g = 1/n_valid (1/tau sum_splits part + gpos/mass class_sum_c + dproto_c/mass),
+//   g = 1/n_valid (1/tau sum_slots part + gpos/mass class_sum_c + dproto_c/mass),
 //   dx = inv_norm (g - e (g.e))
 // and writes it back in the caller's layout (NCHW through a shared-memory transpose).
 template <int D>
@@ -395,6 +398,8 @@ __global__ void __launch_bounds__(SORT_CHUNK) final_kernel(const FinalParams p) 
   __syncthreads();
   if (p.dx == nullptr) return;
   const float inv_n = n_valid_sh > 0.f ? 1.f / n_valid_sh : 0.f;
+  constexpr int RB = (D == 256) ? 128 : 256;  // rows per row block of the pair passes
+  const uint32_t per = pair_units_per_cta(__ldg(p.unit_off + p.n_row_blocks), p.n_ctas, p.n_col_tiles);
   const long long n0 = static_cast<long long>(blockIdx.x) * SORT_CHUNK + warp * 32;
   if (n0 >= p.n) return;
   const long long i = n0 + lane;
@@ -410,7 +415,11 @@ __global__ void __launch_bounds__(SORT_CHUNK) final_kernel(const FinalParams p) 
     for (int k = 0; k < EPL; ++k) g[k] = 0.f;
     if (bq) {
       const int c = class_of_bits(bq);
-      for (int s = 0; s < p.n_split; ++s) {
+      // the row block's live units were shared by CTAs U0/per .. (U1-1)/per, one slot each
+      const int rbk = static_cast<int>(q / RB);
+      const uint32_t U0 = __ldg(p.unit_off + rbk), U1 = __ldg(p.unit_off + rbk + 1);
+      const int n_slots = (U1 > U0) ? static_cast<int>((U1 - 1) / per - U0 / per + 1) : 0;
+      for (int s = 0; s < n_slots; ++s) {
         const float* src = p.part + (static_cast<long long>(s) * p.rows_pad + q) * D + lane;
 #pragma unroll
         for (int k = 0; k < EPL; ++k) g[k] += __ldg(src + 32 * k);

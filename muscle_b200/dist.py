@@ -84,25 +84,26 @@ def sharded_fwd_bwd(stages, x, cls, temperature, num_classes, eps, need_grad, gr
         _all_gather_into(ehat_all, ehat, group)
         _all_gather_into(bits_all, bits, group)
         _all_gather_into(tor_all, tor, group)
-    stages.rowsum(ehat, bits, tor, rows_pad, ehat_all, bits_all, tor_all, cols_pad, dim, temperature, rowsum)
+    unit_off = stages.empty((rows_pad // stages.unit_rows(dim) + 1,), i32)
+    stages.plan(tor, rows_pad, tor_all, cols_pad, dim, unit_off)
+    stages.rowsum(ehat, bits, tor, rows_pad, ehat_all, bits_all, tor_all, cols_pad, unit_off, dim, temperature,
+                  rowsum)
     stages.mid(ehat, seg, rows_pad, dim, C, class_sum, class_mass, rowsum, temperature, w, gpos, loss_acc, dproto)
     if G > 1:
         dist.all_reduce(loss_acc, group=group)
     dx = None
-    n_split = 1
     if need_grad:
         if G > 1:
             dist.all_reduce(dproto, group=group)
             _all_gather_into(w_all, w, group)
-        n_split = stages.grad_splits(rows_pad, cols_pad, dim)
-        part = stages.empty((n_split, rows_pad, dim), f32)
-        stages.grad(ehat, bits, tor, w, rows_pad, ehat_all, bits_all, tor_all, w_all, cols_pad, dim, temperature,
-                    part, n_split)
+        part = stages.empty((stages.part_slots(), rows_pad, dim), f32)
+        stages.grad(ehat, bits, tor, w, rows_pad, ehat_all, bits_all, tor_all, w_all, cols_pad, unit_off, dim,
+                    temperature, part)
         dx = stages.empty(tuple(xc.shape), f32)
     else:
         part = stages.empty((1,), f32)
-    stages.final(ehat, bits, inv_norm, perm, part, n_split, rows_pad, batch, ppi, dim, C, class_sum, class_mass,
-                 gpos, dproto, loss_acc, temperature, layout, dx, loss)
+    stages.final(ehat, bits, inv_norm, perm, part, unit_off, rows_pad, cols_pad, batch, ppi, dim, C, class_sum,
+                 class_mass, gpos, dproto, loss_acc, temperature, layout, dx, loss)
     return loss, dx
 
 

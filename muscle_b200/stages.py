@@ -25,9 +25,12 @@ class CudaStages:
     def pad_rows(self, n):
         return int(self.lib.muscle_pad_rows(int(n)))
 
-    def grad_splits(self, rows_pad, cols_pad, dim):
-        with torch.cuda.device(self.device):
-            return int(self.lib.muscle_infonce_grad_splits(int(rows_pad), int(cols_pad), int(dim)))
+    def part_slots(self):
+        return int(self.lib.muscle_infonce_part_slots())
+
+    def unit_rows(self, dim):
+        """rows per row block of the pair passes (the granularity of `unit_off`)"""
+        return 128 if dim == 256 else 256
 
     def empty(self, shape, dtype):
         return torch.empty(shape, dtype=dtype, device=self.device)
@@ -49,13 +52,19 @@ class CudaStages:
                 _sp(self.device))
         _lib.check(rc, "infonce_prepare")
 
-    def rowsum(self, ehat_rows, bits_rows, tor_rows, rows_pad, ehat_cols, bits_cols, tor_cols, cols_pad, dim,
-               temperature, rowsum):
+    def plan(self, tor_rows, rows_pad, tor_cols, cols_pad, dim, unit_off):
+        with torch.cuda.device(self.device):
+            rc = self.lib.muscle_infonce_plan(tor_rows.data_ptr(), rows_pad, tor_cols.data_ptr(), cols_pad, dim,
+                                              unit_off.data_ptr(), _sp(self.device))
+        _lib.check(rc, "infonce_plan")
+
+    def rowsum(self, ehat_rows, bits_rows, tor_rows, rows_pad, ehat_cols, bits_cols, tor_cols, cols_pad, unit_off,
+               dim, temperature, rowsum):
         with torch.cuda.device(self.device):
             rc = self.lib.muscle_infonce_rowsum(
                 ehat_rows.data_ptr(), bits_rows.data_ptr(), tor_rows.data_ptr(), rows_pad, ehat_cols.data_ptr(),
-                bits_cols.data_ptr(), tor_cols.data_ptr(), cols_pad, dim, float(temperature), rowsum.data_ptr(),
-                _sp(self.device))
+                bits_cols.data_ptr(), tor_cols.data_ptr(), cols_pad, unit_off.data_ptr(), dim, float(temperature),
+                rowsum.data_ptr(), _sp(self.device))
         _lib.check(rc, "infonce_rowsum")
 
     def mid(self, ehat, seg, rows_pad, dim, num_classes, class_sum, class_mass, rowsum, temperature, w, gpos,
@@ -68,20 +77,20 @@ class CudaStages:
         _lib.check(rc, "infonce_mid")
 
     def grad(self, ehat_rows, bits_rows, tor_rows, w_rows, rows_pad, ehat_cols, bits_cols, tor_cols, w_cols,
-             cols_pad, dim, temperature, part, n_split):
+             cols_pad, unit_off, dim, temperature, part):
         with torch.cuda.device(self.device):
             rc = self.lib.muscle_infonce_grad(
                 ehat_rows.data_ptr(), bits_rows.data_ptr(), tor_rows.data_ptr(), w_rows.data_ptr(), rows_pad,
-                ehat_cols.data_ptr(), bits_cols.data_ptr(), tor_cols.data_ptr(), w_cols.data_ptr(), cols_pad, dim,
-                float(temperature), part.data_ptr(), n_split, _sp(self.device))
+                ehat_cols.data_ptr(), bits_cols.data_ptr(), tor_cols.data_ptr(), w_cols.data_ptr(), cols_pad,
+                unit_off.data_ptr(), dim, float(temperature), part.data_ptr(), _sp(self.device))
         _lib.check(rc, "infonce_grad")
 
-    def final(self, ehat, bits, inv_norm, perm, part, n_split, rows_pad, batch, ppi, dim, num_classes, class_sum,
-              class_mass, gpos, dproto, loss_acc, temperature, layout, dx, loss_out):
+    def final(self, ehat, bits, inv_norm, perm, part, unit_off, rows_pad, cols_pad, batch, ppi, dim, num_classes,
+              class_sum, class_mass, gpos, dproto, loss_acc, temperature, layout, dx, loss_out):
         with torch.cuda.device(self.device):
             rc = self.lib.muscle_infonce_final(
-                ehat.data_ptr(), bits.data_ptr(), inv_norm.data_ptr(), perm.data_ptr(), part.data_ptr(), n_split,
-                rows_pad, batch, ppi, dim, num_classes, class_sum.data_ptr(), class_mass.data_ptr(),
-                gpos.data_ptr(), dproto.data_ptr(), loss_acc.data_ptr(), float(temperature), layout,
-                dx.data_ptr() if dx is not None else None, loss_out.data_ptr(), _sp(self.device))
+                ehat.data_ptr(), bits.data_ptr(), inv_norm.data_ptr(), perm.data_ptr(), part.data_ptr(),
+                unit_off.data_ptr(), rows_pad, cols_pad, batch, ppi, dim, num_classes, class_sum.data_ptr(),
+                class_mass.data_ptr(), gpos.data_ptr(), dproto.data_ptr(), loss_acc.data_ptr(), float(temperature),
+                layout, dx.data_ptr() if dx is not None else None, loss_out.data_ptr(), _sp(self.device))
         _lib.check(rc, "infonce_final")
