@@ -126,6 +126,65 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
                          const float* dproto, const double* loss_acc, float temperature,
                          int layout, float* dx, float* loss_out, void* stream);
 
+/* ==========================================================================================
+ * The other members of the path.  Same conventions as above.
+ * ========================================================================================== */
+
+/* ------------------------------------------------------------------------------------------
+ * image_level_contrast — replaces src/loss_multilabel.py:36-66 (called at train_mcl.py:193).
+ * emb [batch, dim] fp32, label [batch, n_labels] fp32 multi-hot.  loss_out float[1];
+ * n_used_out int32[1] = number of images that contributed (0: the reference returns python 0);
+ * demb_out [batch, dim] = d loss / d emb, or NULL. */
+size_t muscle_imc_workspace_bytes(int batch, int dim);
+int muscle_imc_fwd_bwd(const float* emb, const float* label, int batch, int dim, int n_labels,
+                       float temperature, float* loss_out, int32_t* n_used_out, float* demb_out,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * PixPro — replaces src/loss_multilabel.py:93-105 (train_mcl.py:209).  fm1, fm2 [batch, 21,
+ * height, width] NCHW; box1, box2 device int32 [batch,4] = (top, left, h, w), equal h,w per image,
+ * inside the map; max_box_pixels = max_b h*w (grid sizing).  loss_out float[1]; dfm1_out (same
+ * shape as fm1, fully written) or NULL; view 2 receives no gradient (:103).  scratch: double[1]. */
+int muscle_pixpro_fwd_bwd(const float* fm1, const float* fm2, const int32_t* box1,
+                          const int32_t* box2, int batch, int channels, int height, int width,
+                          int max_box_pixels, float* loss_out, float* dfm1_out, double* scratch,
+                          void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * CAM head — replaces src/MuSCLe.py:242-247 (== :263-268): cam = relu(sum_ch p7 * W), W =
+ * fc.weight.data (no gradient to W).  p7 [batch, channels, pixels]; fc_weight [num_classes,
+ * channels]; cam [batch, num_classes, pixels].  bwd: dp7 = W^T (dcam [cam > 0]) (+ demb/pixels when
+ * demb != NULL — the GAP backward of :240, so dp7 is written once; dcam may be NULL). */
+int muscle_cam_head_fwd(const float* p7, const float* fc_weight, int batch, int channels,
+                        int pixels, int num_classes, float* cam_out, void* stream);
+int muscle_cam_head_bwd(const float* dcam, const float* cam, const float* fc_weight,
+                        const float* demb, int batch, int channels, int pixels, int num_classes,
+                        float* dp7_out, void* stream);
+/* Image embedding + logits — replaces src/MuSCLe.py:182-183,240-241: emb = mean over pixels,
+ * logits = emb W^T (gradient reaches W here). */
+int muscle_gap_fwd(const float* p7, int batch, int channels, int pixels, float* emb_out,
+                   void* stream);
+int muscle_linear_fwd(const float* emb, const float* weight, int batch, int channels,
+                      int num_classes, float* logits_out, void* stream);
+int muscle_linear_bwd(const float* dlogits, const float* emb, const float* weight, int batch,
+                      int channels, int num_classes, float* demb_out, float* dweight_out,
+                      void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * The trainers' CAM normalisers — replace train_mcl.py:30-36 (cam_softmaxnorm: softmax over the
+ * fg channels, bg = 1 - max fg) and train_mcl.py:21-28 (cam_maxnorm: relu, per-plane min-max with
+ * -1e-6 / +1e-6, relu).  cam [batch, num_classes, pixels]; planes = batch*num_classes;
+ * lohi float[planes*2], argmm int64[planes*2] are saved by the forward for the backward. */
+int muscle_cam_softmaxnorm_fwd(const float* cam, int batch, int num_classes, int64_t pixels,
+                               float* out, void* stream);
+int muscle_cam_softmaxnorm_bwd(const float* out, const float* dout, int batch, int num_classes,
+                               int64_t pixels, float* din, void* stream);
+int muscle_cam_maxnorm_fwd(const float* cam, int64_t planes, int64_t pixels, float* out,
+                           float* lohi, int64_t* argmm, void* stream);
+int muscle_cam_maxnorm_bwd(const float* cam, const float* dout, const float* lohi,
+                           const int64_t* argmm, int64_t planes, int64_t pixels, float* din,
+                           void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Debug / unit-test entry points for the tcgen05 building blocks (used by tests/ only).
  * sim: S[128,128] = A[128,dim] B[128,dim]^T ;  tsg: G[128,dim] = bf16(S) B  (A from TMEM). */
