@@ -171,6 +171,25 @@ int muscle_linear_bwd(const float* dlogits, const float* emb, const float* weigh
                       void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Projection head + PCM — replaces src/MuSCLe.py:181 (`fuse`, 1x1 conv Cin -> 128 + bias) and
+ * src/MuSCLe.py:213-223 (`PCM`): ghat = g/(||g||+1e-5); S = relu(ghat^T ghat); out = cam S /
+ * (colsum S + 1e-5).  cam [batch, num_classes, pixels], f [batch, cin, pixels] (detached in the
+ * reference, :254), fuse_w [128, cin], fuse_b [128], out [batch, num_classes, pixels]; fp32.
+ * `state` (muscle_pcm_state_bytes) is written by the forward and read by the backward: bf16 copies
+ * of f and ghat, ||g||, the column sums.  Backward: dcam (may be NULL), dfuse_w [128,cin] and
+ * dfuse_b [128] (both or neither); `scratch` (muscle_pcm_bwd_scratch_bytes) is free afterwards.
+ * num_classes <= 24, cin <= 383.  The P x P affinity never reaches HBM. */
+size_t muscle_pcm_state_bytes(int batch, int cin, int64_t pixels);
+size_t muscle_pcm_bwd_scratch_bytes(int batch, int cin, int64_t pixels);
+int muscle_pcm_fwd(const float* cam, const float* f, const float* fuse_w, const float* fuse_b,
+                   int batch, int num_classes, int cin, int64_t pixels, float* out, void* state,
+                   size_t state_bytes, void* stream);
+int muscle_pcm_bwd(const float* dout, const float* cam, const float* out, int batch,
+                   int num_classes, int cin, int64_t pixels, const void* state,
+                   size_t state_bytes, float* dcam, float* dfuse_w, float* dfuse_b,
+                   void* scratch, size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * The trainers' CAM normalisers — replace train_mcl.py:30-36 (cam_softmaxnorm: softmax over the
  * fg channels, bg = 1 - max fg) and train_mcl.py:21-28 (cam_maxnorm: relu, per-plane min-max with
  * -1e-6 / +1e-6, relu).  cam [batch, num_classes, pixels]; planes = batch*num_classes;

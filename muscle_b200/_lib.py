@@ -55,6 +55,12 @@ _SIGNATURES = {
     "muscle_cam_softmaxnorm_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p]),
     "muscle_cam_maxnorm_fwd": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "muscle_cam_maxnorm_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
+    "muscle_pcm_state_bytes": (c_size_t, [c_int, c_int, c_int64]),
+    "muscle_pcm_bwd_scratch_bytes": (c_size_t, [c_int, c_int, c_int64]),
+    "muscle_pcm_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p,
+                               c_void_p, c_size_t, c_void_p]),
+    "muscle_pcm_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_size_t,
+                               c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "muscle_debug_tile": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
 }
 

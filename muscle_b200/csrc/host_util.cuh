@@ -77,15 +77,16 @@ inline EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-// bf16 [rows, dim] row-major -> boxes of [128 rows x 64 elements], 128-B swizzle.
-inline int make_bf16_tile_map(CUtensorMap* map, const void* base, int64_t rows, int dim) {
+// bf16 [rows, cols] row-major -> boxes of [box_rows rows x 64 elements], 128-B swizzle.
+inline int make_bf16_box_map(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int box_rows) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return fail(MUSCLE_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   if ((reinterpret_cast<uintptr_t>(base) & 127) != 0)
     return fail(MUSCLE_ERR_BAD_ARG, "bf16 operand must be 128-byte aligned");
-  cuuint64_t gdim[2] = {static_cast<cuuint64_t>(dim), static_cast<cuuint64_t>(rows)};
-  cuuint64_t gstride[1] = {static_cast<cuuint64_t>(dim) * 2};
-  cuuint32_t box[2] = {64, 128};
+  if (cols % 8 != 0) return fail(MUSCLE_ERR_BAD_ARG, "bf16 operand rows must be multiples of 16 bytes");
+  cuuint64_t gdim[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t gstride[1] = {static_cast<cuuint64_t>(cols) * 2};
+  cuuint32_t box[2] = {64, static_cast<cuuint32_t>(box_rows)};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride,
                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -93,6 +94,11 @@ inline int make_bf16_tile_map(CUtensorMap* map, const void* base, int64_t rows, 
   if (r != CUDA_SUCCESS)
     return fail(MUSCLE_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return MUSCLE_OK;
+}
+
+// bf16 [rows, dim] row-major -> boxes of [128 rows x 64 elements], 128-B swizzle.
+inline int make_bf16_tile_map(CUtensorMap* map, const void* base, int64_t rows, int dim) {
+  return make_bf16_box_map(map, base, rows, dim, 128);
 }
 
 inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }

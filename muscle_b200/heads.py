@@ -147,3 +147,63 @@ class _MaxNorm(torch.autograd.Function):
 def cam_maxnorm(cams):
     """train_mcl.py:21-28: relu, per-(image,class) min-max with -1e-6 / +1e-6, relu."""
     return _MaxNorm.apply(cams)
+
+
+class _Pcm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, cam, f, fuse_weight, fuse_bias):
+        from . import _lib
+        lib = _lib.load()
+        b, k, h, w = cam.shape
+        cin = f.shape[1]
+        P = h * w
+        camc, fc = cam.contiguous(), f.contiguous()
+        wc = fuse_weight.reshape(fuse_weight.shape[0], -1).contiguous()
+        bc = fuse_bias.contiguous()
+        state_bytes = lib.muscle_pcm_state_bytes(b, cin, P)
+        state = torch.empty(state_bytes, dtype=torch.uint8, device=cam.device)
+        out = torch.empty((b, k, h, w), dtype=torch.float32, device=cam.device)
+        call("muscle_pcm_fwd", cam.device, camc.data_ptr(), fc.data_ptr(), wc.data_ptr(), bc.data_ptr(), b, k, cin, P,
+             out.data_ptr(), state.data_ptr(), state_bytes)
+        ctx.save_for_backward(camc, out, state)
+        ctx.dims = (b, k, cin, h, w)
+        ctx.w_shape = fuse_weight.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        from . import _lib
+        lib = _lib.load()
+        camc, out, state = ctx.saved_tensors
+        b, k, cin, h, w = ctx.dims
+        P = h * w
+        need_cam, _, need_w, need_b = ctx.needs_input_grad
+        dev = camc.device
+        dcam = torch.empty_like(camc) if need_cam else None
+        dw = db = None
+        if need_w or need_b:
+            dw = torch.empty((128, cin), dtype=torch.float32, device=dev)
+            db = torch.empty((128,), dtype=torch.float32, device=dev)
+        scratch_bytes = lib.muscle_pcm_bwd_scratch_bytes(b, cin, P)
+        scratch = torch.empty(scratch_bytes, dtype=torch.uint8, device=dev)
+        call("muscle_pcm_bwd", dev, dout.contiguous().data_ptr(), camc.data_ptr(), out.data_ptr(), b, k, cin, P,
+             state.data_ptr(), state.numel(), ptr(dcam), ptr(dw), ptr(db), scratch.data_ptr(), scratch_bytes)
+        return dcam, None, (dw.reshape(ctx.w_shape) if need_w else None), (db if need_b else None)
+
+
+def pcm(cam, f, fuse_weight, fuse_bias):
+    """src/MuSCLe.py:213-223 (`MuSCLe.PCM(cam, f)` with the `fuse` 1x1 conv of :181 passed in):
+    g = fuse(f); ghat = g/(||g||+1e-5); S = relu(ghat^T ghat); out = cam @ (S / (colsum S + 1e-5)).
+    cam [B,K,h,w] (grad), f [B,Cin,h',w'] (treated as detached, :254), fuse_weight [128,Cin,1,1] or
+    [128,Cin] and fuse_bias [128] (grad).  When cam and f differ in size the reference first resizes
+    cam bilinearly (:215); that resize stays a torch call, the projection, the affinity and the
+    aggregation run on the tensor pipe and the P x P affinity never exists in memory."""
+    require_cuda_f32(cam, "cam")
+    require_cuda_f32(f, "f")
+    require_cuda_f32(fuse_weight, "fuse_weight")
+    require_cuda_f32(fuse_bias, "fuse_bias")
+    if fuse_weight.shape[0] != 128:
+        raise ValueError("the projection width is 128 (src/MuSCLe.py:181), got %d" % fuse_weight.shape[0])
+    if cam.shape[2:] != f.shape[2:]:
+        cam = torch.nn.functional.interpolate(cam, f.shape[2:], mode="bilinear", align_corners=True)
+    return _Pcm.apply(cam, f.detach(), fuse_weight, fuse_bias)
