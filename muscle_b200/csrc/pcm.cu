@@ -12,9 +12,10 @@
 //   dcam = A S                                     the forward kernel again with V = A, no division
 //   dS_ij = sum_c cam_ci A_cj - r_j  =>  dghat_i = sum_j [z_ij > 0] (U_ij - r_i - r_j) ghat_j,
 //   U = cam^T A + A^T cam                          pcm_pair_kernel<BWD>: Z_h = Q K_h^T, W_h = X Y_h^T
-//                                                  with X_i = [cam_i | A_i | -r_i(hi,lo) | 1 1],
-//                                                       Y_j = [A_j | cam_j | 1 1 | -r_j(hi,lo)]  (K = 64)
-//                                                  T_h = [Z_h > 0] W_h -> bf16 -> G += T_h K_h (TS MMA)
+//     (U - r is a deviation from a weighted mean: bf16 cam/A lose it, so both are split hi + lo)
+//                                                  X_i = [ch ch cl | ah al ah]_i, Y_j = [ah al ah | ch ch cl]_j
+//                                                  (K = 6 x 21 -> 128);  r_i, r_j added in fp32
+//                                                  T_h = [Z_h > 0] (W_h - r_i - r_j) -> bf16 -> G += T_h K_h
 //   dg from dghat through the normalisation (kernel epilogue), stored d-major bf16
 //   dW = dg f^T, db = dg 1                          pcm_dw_kernel (f carries a row of ones)
 #include <algorithm>
@@ -30,6 +31,8 @@ namespace {
 constexpr int PD = 128;       // projection width, hard-coded in the reference (src/MuSCLe.py:181)
 constexpr int VROWS = 32;     // CAM classes padded; row 31 carries the ones of the column sum
 constexpr float PCM_EPS = 1e-5f;
+constexpr int XSEG = 21;      // classes per segment of the split X/Y operands of the backward pass
+constexpr int XK = 128;       // their K extent (6 segments of 21, 2 zero columns)
 constexpr int PANEL = 128 * 128;  // bytes of one [128 rows x 64 bf16] swizzle panel
 
 int need_sm100() {
@@ -62,7 +65,7 @@ PcmState plan_state(int batch, int cin, int64_t P) {
   return s;
 }
 struct PcmScratch {
-  size_t ab, xp, yp, dgt, dwp, total;
+  size_t ab, xp, yp, rr, dgt, dwp, total;
 };
 PcmScratch plan_scratch(int batch, int cin, int64_t P) {
   const int64_t pp = pad128(P);
@@ -71,8 +74,9 @@ PcmScratch plan_scratch(int batch, int cin, int64_t P) {
   size_t off = 0;
   auto take = [&](size_t b) { size_t o = off; off = al256(off + b); return o; };
   s.ab = take(static_cast<size_t>(batch) * VROWS * pp * 2);
-  s.xp = take(static_cast<size_t>(batch) * pp * 64 * 2);
-  s.yp = take(static_cast<size_t>(batch) * pp * 64 * 2);
+  s.xp = take(static_cast<size_t>(batch) * pp * XK * 2);
+  s.yp = take(static_cast<size_t>(batch) * pp * XK * 2);
+  s.rr = take(static_cast<size_t>(batch) * pp * 4);
   s.dgt = take(static_cast<size_t>(batch) * PD * pp * 2);
   s.dwp = take(static_cast<size_t>(PD) * cp * 4);
   s.total = off;
@@ -121,17 +125,19 @@ __global__ void __launch_bounds__(256) pcm_cast_v_kernel(const float* src, const
   }
 }
 // Per pixel: A = dOut/den, r = sum_c out A; A rows -> ab (V operand of the dcam pass);
-// X = [cam | A | -r hi, -r lo | 1, 1 | 0..], Y = [A | cam | 1, 1 | -r hi, -r lo | 0..]  (64 bf16 each)
+// X = [ch ch cl | ah al ah], Y = [ah al ah | ch ch cl] in segments of 21 (128 bf16 each), with
+// cam = ch + cl and A = ah + al split into bf16 hi + lo parts; rr = r (fp32).
 __global__ void __launch_bounds__(128) pcm_bwd_prep_kernel(const float* dout, const float* out, const float* cam,
                                                            const float* den, int K, int64_t P, int64_t pp,
-                                                           __nv_bfloat16* ab, __nv_bfloat16* xp, __nv_bfloat16* yp) {
+                                                           __nv_bfloat16* ab, __nv_bfloat16* xp, __nv_bfloat16* yp,
+                                                           float* rr) {
   const int b = blockIdx.y;
   const int64_t p = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (p >= pp) return;
   const bool in = p < P;
-  __align__(16) __nv_bfloat16 x[64], y[64];
+  __align__(16) __nv_bfloat16 x[XK], y[XK];
 #pragma unroll
-  for (int i = 0; i < 64; ++i) { x[i] = __float2bfloat16(0.f); y[i] = __float2bfloat16(0.f); }
+  for (int i = 0; i < XK; ++i) { x[i] = __float2bfloat16(0.f); y[i] = __float2bfloat16(0.f); }
   float r = 0.f;
   const float inv = in ? 1.f / den[static_cast<int64_t>(b) * pp + p] : 0.f;
 #pragma unroll
@@ -143,24 +149,20 @@ __global__ void __launch_bounds__(128) pcm_bwd_prep_kernel(const float* dout, co
       c = cam[idx];
       r = fmaf(out[idx], a, r);
     }
-    const __nv_bfloat16 a16 = __float2bfloat16(a), c16 = __float2bfloat16(c);
-    ab[(static_cast<int64_t>(b) * VROWS + k) * pp + p] = a16;
-    if (k < 24) {   // K <= 24 classes fit the 64-wide X/Y rows
-      x[k] = c16; x[24 + k] = a16;
-      y[k] = a16; y[24 + k] = c16;
+    const __nv_bfloat16 ah = __float2bfloat16(a), ch = __float2bfloat16(c);
+    ab[(static_cast<int64_t>(b) * VROWS + k) * pp + p] = ah;
+    if (k < XSEG) {
+      const __nv_bfloat16 al = __float2bfloat16(a - __bfloat162float(ah));
+      const __nv_bfloat16 cl = __float2bfloat16(c - __bfloat162float(ch));
+      x[k] = ch; x[XSEG + k] = ch; x[2 * XSEG + k] = cl; x[3 * XSEG + k] = ah; x[4 * XSEG + k] = al; x[5 * XSEG + k] = ah;
+      y[k] = ah; y[XSEG + k] = al; y[2 * XSEG + k] = ah; y[3 * XSEG + k] = ch; y[4 * XSEG + k] = ch; y[5 * XSEG + k] = cl;
     }
   }
-  if (in) {
-    const __nv_bfloat16 hi = __float2bfloat16(-r);
-    const __nv_bfloat16 lo = __float2bfloat16(-r - __bfloat162float(hi));
-    const __nv_bfloat16 one = __float2bfloat16(1.f);
-    x[48] = hi; x[49] = lo; x[50] = one; x[51] = one;
-    y[48] = one; y[49] = one; y[50] = hi; y[51] = lo;
-  }
-  uint4* xd = reinterpret_cast<uint4*>(xp + (static_cast<int64_t>(b) * pp + p) * 64);
-  uint4* yd = reinterpret_cast<uint4*>(yp + (static_cast<int64_t>(b) * pp + p) * 64);
+  rr[static_cast<int64_t>(b) * pp + p] = r;
+  uint4* xd = reinterpret_cast<uint4*>(xp + (static_cast<int64_t>(b) * pp + p) * XK);
+  uint4* yd = reinterpret_cast<uint4*>(yp + (static_cast<int64_t>(b) * pp + p) * XK);
 #pragma unroll
-  for (int i = 0; i < 8; ++i) { xd[i] = reinterpret_cast<uint4*>(x)[i]; yd[i] = reinterpret_cast<uint4*>(y)[i]; }
+  for (int i = 0; i < XK / 8; ++i) { xd[i] = reinterpret_cast<uint4*>(x)[i]; yd[i] = reinterpret_cast<uint4*>(y)[i]; }
 }
 // dw[d][c] = dwp[d][c] (c < cin), db[d] = dwp[d][cin]
 __global__ void __launch_bounds__(256) pcm_unpad_dw_kernel(const float* dwp, int cin, int cp, float* dw, float* db) {
@@ -322,16 +324,17 @@ pcm_project_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
 // pair passes over one image: work item = (image, 128-pixel row tile); loops over all column tiles
 // ==========================================================================================
 enum PcmMode { PCM_FWD = 0, PCM_BWD = 1 };
-constexpr int PP_NST = 3;
 constexpr int PP_THREADS = 192;
 
 template <int MODE>
 struct PpCfg {
-  static constexpr int Q_BYTES = 2 * PANEL + (MODE == PCM_BWD ? PANEL : 0);          // ghat row tile (+ X tile)
-  static constexpr int AUX_BYTES = (MODE == PCM_BWD) ? PANEL : 2 * VROWS * 128;      // Y tile | two V halves
-  static constexpr int STAGE = 2 * PANEL + AUX_BYTES;
+  static constexpr int NST = (MODE == PCM_BWD) ? 2 : 3;
+  static constexpr int Q_BYTES = 2 * PANEL + (MODE == PCM_BWD ? 2 * PANEL : 0);      // ghat row tile (+ X tile)
+  static constexpr int AUX_BYTES = (MODE == PCM_BWD) ? 2 * PANEL : 2 * VROWS * 128;  // Y tile | two V halves
+  static constexpr int TX_BYTES = 2 * PANEL + AUX_BYTES + (MODE == PCM_BWD ? 512 : 0);  // + r of the column pixels
+  static constexpr int STAGE = 2 * PANEL + AUX_BYTES + (MODE == PCM_BWD ? 1024 : 0);
   static constexpr int SMEM_K = Q_BYTES;
-  static constexpr int SMEM_BAR = SMEM_K + PP_NST * STAGE;
+  static constexpr int SMEM_BAR = SMEM_K + NST * STAGE;
   static constexpr int SMEM_BYTES = SMEM_BAR + 256 + 1024;
   static constexpr int ACC_COL = (MODE == PCM_BWD) ? 256 : 128;
   static constexpr int ACC_N = (MODE == PCM_BWD) ? PD : VROWS;
@@ -346,6 +349,7 @@ struct PpParams {
   float* den;             // FWD normalise: [B][pp]
   const __nv_bfloat16* ghat;  // BWD epilogue
   const float* gnorm;         // BWD epilogue
+  const float* rr;            // BWD: [B][pp] r of every pixel
   __nv_bfloat16* dgt;         // BWD: [B][128][pp]
 };
 
@@ -354,6 +358,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1)
 pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant__ CUtensorMap tm_aux_row,
                 const __grid_constant__ CUtensorMap tm_aux_col, const PpParams p) {
   using C = PpCfg<MODE>;
+  constexpr int PP_NST = C::NST;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
@@ -391,17 +396,22 @@ pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant_
       mbar_arrive_expect_tx(q_full, C::Q_BYTES);
       tma_load_2d(q_smem, &tm_g, q_full, 0, row0);
       tma_load_2d(q_smem + PANEL, &tm_g, q_full, 64, row0);
-      if (MODE == PCM_BWD) tma_load_2d(x_smem, &tm_aux_row, q_full, 0, row0);
+      if (MODE == PCM_BWD) {
+        tma_load_2d(x_smem, &tm_aux_row, q_full, 0, row0);
+        tma_load_2d(x_smem + PANEL, &tm_aux_row, q_full, 64, row0);
+      }
       for (int t = 0; t < T; ++t) {
         const int st = t % PP_NST;
         mbar_wait(k_empty(st), ((t / PP_NST) & 1) ^ 1);
-        mbar_arrive_expect_tx(k_full(st), C::STAGE);
+        mbar_arrive_expect_tx(k_full(st), C::TX_BYTES);
         const uint32_t ks = k_smem + st * C::STAGE;
         const int col_row = static_cast<int>(b * p.pp) + t * 128;
         tma_load_2d(ks, &tm_g, k_full(st), 0, col_row);
         tma_load_2d(ks + PANEL, &tm_g, k_full(st), 64, col_row);
         if (MODE == PCM_BWD) {
           tma_load_2d(ks + 2 * PANEL, &tm_aux_col, k_full(st), 0, col_row);
+          tma_load_2d(ks + 3 * PANEL, &tm_aux_col, k_full(st), 64, col_row);
+          bulk_load_1d(ks + 4 * PANEL, p.rr + col_row, 512, k_full(st));
         } else {
           for (int h = 0; h < 2; ++h)
             tma_load_2d(ks + 2 * PANEL + h * VROWS * 128, &tm_aux_col, k_full(st), t * 128 + h * 64, b * VROWS);
@@ -428,9 +438,11 @@ pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant_
         }
         if (MODE == PCM_BWD) {
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk)
-            mma_ss(tmem + 128 + h * 64, umma_desc_sw128(x_smem + kk * 32, 16, 1024),
-                   umma_desc_sw128(ks + 2 * PANEL + h * 8192 + kk * 32, 16, 1024), IDESC_S, kk > 0);
+          for (int kk = 0; kk < 8; ++kk) {
+            const uint32_t off = (kk >> 2) * PANEL + (kk & 3) * 32;
+            mma_ss(tmem + 128 + h * 64, umma_desc_sw128(x_smem + off, 16, 1024),
+                   umma_desc_sw128(ks + 2 * PANEL + h * 8192 + off, 16, 1024), IDESC_S, kk > 0);
+          }
         }
         tc_commit(s_full(h));
       };
@@ -456,8 +468,12 @@ pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant_
   } else {
     const uint32_t lane_addr = static_cast<uint32_t>(warp * 32) << 16;
     const int U = 2 * T;
+    float r_row = 0.f;
+    if (MODE == PCM_BWD) r_row = p.rr[row0 + warp * 32 + lane];
     for (int u = 0; u < U; ++u) {
       const int h = u & 1;
+      const int st = (u >> 1) % PP_NST;
+      if (MODE == PCM_BWD && h == 0) mbar_wait(k_full(st), ((u >> 1) / PP_NST) & 1);   // r of the column pixels landed
       mbar_wait(s_full(h), (u >> 1) & 1);
       tc_fence_after();
 #pragma unroll
@@ -469,10 +485,12 @@ pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant_
           uint32_t w[32];
           tmem_ld32(tmem + lane_addr + 128 + h * 64 + c * 32, w);
           tmem_wait_ld();
+          const float* rc = reinterpret_cast<const float*>(gen + C::SMEM_K + st * C::STAGE + 4 * PANEL) + h * 64 + c * 32;
 #pragma unroll
           for (int k = 0; k < 16; ++k) {
-            const float t0 = (__uint_as_float(z[2 * k]) > 0.f) ? __uint_as_float(w[2 * k]) : 0.f;
-            const float t1 = (__uint_as_float(z[2 * k + 1]) > 0.f) ? __uint_as_float(w[2 * k + 1]) : 0.f;
+            const float2 rj = reinterpret_cast<const float2*>(rc)[k];
+            const float t0 = (__uint_as_float(z[2 * k]) > 0.f) ? __uint_as_float(w[2 * k]) - r_row - rj.x : 0.f;
+            const float t1 = (__uint_as_float(z[2 * k + 1]) > 0.f) ? __uint_as_float(w[2 * k + 1]) - r_row - rj.y : 0.f;
             packed[k] = pack_bf16x2(t0, t1);
           }
         } else {
@@ -658,7 +676,7 @@ pcm_dw_kernel(const __grid_constant__ CUtensorMap tm_dg, const __grid_constant__
 
 int check_shapes(int batch, int num_classes, int cin, int64_t pixels) {
   if (batch <= 0 || pixels <= 0 || cin <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty input");
-  if (num_classes < 1 || num_classes > 24) return fail(MUSCLE_ERR_BAD_ARG, "PCM supports 1..24 CAM classes (got %d)", num_classes);
+  if (num_classes < 1 || num_classes > XSEG) return fail(MUSCLE_ERR_BAD_ARG, "PCM supports 1..%d CAM classes (got %d)", XSEG, num_classes);
   if (cin_pad(cin) > 384) return fail(MUSCLE_ERR_BAD_ARG, "PCM supports at most 383 input channels (got %d)", cin);
   if (static_cast<int64_t>(batch) * pad128(pixels) >= (1ll << 31)) return fail(MUSCLE_ERR_BAD_ARG, "too many pixels");
   return MUSCLE_OK;
@@ -758,10 +776,11 @@ int muscle_pcm_bwd(const float* dout, const float* cam, const float* out, int ba
   auto* ab = reinterpret_cast<__nv_bfloat16*>(wb + W.ab);
   auto* xp = reinterpret_cast<__nv_bfloat16*>(wb + W.xp);
   auto* yp = reinterpret_cast<__nv_bfloat16*>(wb + W.yp);
+  float* rr = reinterpret_cast<float*>(wb + W.rr);
   auto* dgt = reinterpret_cast<__nv_bfloat16*>(wb + W.dgt);
   float* dwp = reinterpret_cast<float*>(wb + W.dwp);
 
-  pcm_bwd_prep_kernel<<<dim3(static_cast<unsigned>((pp + 127) / 128), batch), 128, 0, stream>>>(dout, out, cam, den, num_classes, pixels, pp, ab, xp, yp);
+  pcm_bwd_prep_kernel<<<dim3(static_cast<unsigned>((pp + 127) / 128), batch), 128, 0, stream>>>(dout, out, cam, den, num_classes, pixels, pp, ab, xp, yp, rr);
   MB_LAUNCH_CHECK();
   CUtensorMap tm_g, tm_a, tm_x, tm_y;
   if (int rc = make_bf16_box_map(&tm_g, ghat, static_cast<int64_t>(batch) * pp, PD, 128)) return rc;
@@ -773,11 +792,11 @@ int muscle_pcm_bwd(const float* dout, const float* cam, const float* out, int ba
     if (int rc = launch_pair<PCM_FWD>(tm_g, tm_a, tm_a, prm, n_tiles, stream)) return rc;
   }
   if (dfuse_w) {
-    if (int rc = make_bf16_box_map(&tm_x, xp, static_cast<int64_t>(batch) * pp, 64, 128)) return rc;
-    if (int rc = make_bf16_box_map(&tm_y, yp, static_cast<int64_t>(batch) * pp, 64, 128)) return rc;
+    if (int rc = make_bf16_box_map(&tm_x, xp, static_cast<int64_t>(batch) * pp, XK, 128)) return rc;
+    if (int rc = make_bf16_box_map(&tm_y, yp, static_cast<int64_t>(batch) * pp, XK, 128)) return rc;
     PpParams prm{};
     prm.tiles_per_image = T; prm.P = pixels; prm.pp = pp; prm.K = num_classes;
-    prm.ghat = ghat; prm.gnorm = gnorm; prm.dgt = dgt;
+    prm.ghat = ghat; prm.gnorm = gnorm; prm.dgt = dgt; prm.rr = rr;
     if (int rc = launch_pair<PCM_BWD>(tm_g, tm_x, tm_y, prm, n_tiles, stream)) return rc;
     CUtensorMap tm_dg, tm_f;
     if (int rc = make_bf16_box_map(&tm_dg, dgt, static_cast<int64_t>(batch) * PD, pp, 128)) return rc;
