@@ -205,6 +205,37 @@ int muscle_cam_maxnorm_bwd(const float* cam, const float* dout, const float* loh
                            void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * FieldLoss — replaces src/edge.py:175-384 (constructed train_muscle.py:163, called :196).
+ * Stage 1 (muscle_field_edges; replaces Mix_fg.forward :423-440, OrientQuantize :65-89 and the
+ * selection of FieldLoss.forward :370-374): seg_map [batch, C, H, W], label_with_bg [batch, C]
+ * float -> orient u8 [batch, C-1, H, W] (bins 0..7), pos u8 (boundary flags), mag_sum
+ * [batch, H, W] (the second return value of the reference), plane_max u32 [batch, C-1] (float
+ * bits) and counts int32 [batch, C-1, 3] = {boundary pixels, kept outside indices, kept inside
+ * indices} (in_out_div :195-227 with `step`).  prob_scratch, mag_scratch: float [batch,C-1,H,W].
+ * The host reads `counts`, applies the gates (:378, :297) and draws the samples (random.sample).
+ * Stage 2 (muscle_field_compact): raster-ordered outside / inside index lists of the n_active
+ * planes (planes[i] = b*(C-1)+c; offsets[2i], offsets[2i+1] = start of the plane's outside /
+ * inside list in `lists`).
+ * Stage 3 (muscle_field_loss; replaces bifilter :261-361 + loss_constructor :229-258):
+ * sel int32 [n_active, 2, k] = positions in the plane's lists; channel softmax of dense_ft
+ * [batch, channels, H, W] and mask [batch, C, H, W] at the sampled pixels only; loss_out float[1]
+ * (already / batch); ddense_out = d loss / d dense_ft (fully written) or NULL. */
+int muscle_field_edges(const float* seg_map, const float* label_with_bg, int batch, int num_classes,
+                       int height, int width, float beta, int step, float* prob_scratch,
+                       float* mag_scratch, uint8_t* orient_out, uint8_t* pos_out,
+                       float* mag_sum_out, uint32_t* plane_max_out, int32_t* counts_out,
+                       void* stream);
+int muscle_field_compact(const uint8_t* orient, const uint8_t* pos, int height, int width, int step,
+                         const int32_t* planes, const int64_t* offsets, int n_active,
+                         int32_t* lists, void* stream);
+size_t muscle_field_loss_scratch_bytes(int n_active, int k, int channels, int num_classes);
+int muscle_field_loss(const float* dense_ft, const float* mask, int batch, int channels,
+                      int num_classes, int height, int width, const int32_t* planes,
+                      const int64_t* offsets, const int32_t* sel, const int32_t* lists, int n_active,
+                      int k, float* loss_out, float* ddense_out, void* scratch, size_t scratch_bytes,
+                      void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Debug / unit-test entry points for the tcgen05 building blocks (used by tests/ only).
  * sim: S[128,128] = A[128,dim] B[128,dim]^T ;  tsg: G[128,dim] = bf16(S) B  (A from TMEM). */
 int muscle_debug_tile(const void* a_bf16, const void* b_bf16, int dim, float* s_out,
