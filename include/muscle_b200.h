@@ -236,6 +236,38 @@ int muscle_field_loss(const float* dense_ft, const float* mask, int batch, int c
                       void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Region crops — replaces the tensor work of torchutils.get_dynamic_crops
+ * (src/torchutils.py:217-291; called train_mcl.py:220): every window of a batch in one launch.
+ * x [batch, channels, height, width]; desc int32 [n_crops, 10] = {image, top, left, lh, lw, rh, rw,
+ * pool, oh, ow}: window (top,left,lh,lw) of the map (absolute coordinates), resized bilinearly with
+ * align_corners=True to (rh,rw) (:270), then 4x4 average-pooled when pool != 0 (:271-272, :279;
+ * view-2 windows use rh=lh, rw=lw, pool=1); output [channels, oh, ow] at element offsets[i] of
+ * `flat`; offsets int64 [n_crops+1] ascending, offsets[n_crops] = total.  The window plan itself
+ * (numpy RNG, :240-254) is host integer work.  bwd: dx (fully written) from dflat. */
+int muscle_crops_fwd(const float* x, int channels, int height, int width, const int32_t* desc,
+                     const int64_t* offsets, int n_crops, int64_t total, float* flat_out,
+                     void* stream);
+int muscle_crops_bwd(const float* dflat, int batch, int channels, int height, int width,
+                     const int32_t* desc, const int64_t* offsets, int n_crops, int64_t total,
+                     float* dx_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * EMD()(crops1, crops2, mode='dynamic') — replaces src/loss_multilabel.py:201-257,287-326
+ * (train_mcl.py:221).  Regions live in two flat buffers as [21, pixels] blocks; pair_desc int64
+ * [n_pairs, 6] = {offset in flat1, N, offset in flat2, M, image, 0}, pairs of one image listed in
+ * the reference's order (crop1 outer, crop2 inner).  Per pair: cost 1 - x y^T, weights
+ * x.mean(y) / y.mean(x), `maxiter` log-domain Sinkhorn iterations with `reg`, value
+ * sum(exp(M) C)/(N M); per image the FIRST pair with the smallest value is kept; loss_out =
+ * mean over images; dflat1_out (size total1, fully written) = d loss / d flat1 through the
+ * unrolled iterations of the kept pairs, or NULL.  N, M <= 1024. */
+size_t muscle_emd_scratch_bytes(int n_pairs, int n_images, int64_t max_n_plus_m, int maxiter);
+int muscle_emd_dynamic_fwd_bwd(const float* flat1, const float* flat2, const int64_t* pair_desc,
+                               int n_pairs, int n_images, int channels, int64_t max_n,
+                               int64_t max_m, int64_t max_n_plus_m, float reg, int maxiter,
+                               float* loss_out, float* dflat1_out, int64_t total1, void* scratch,
+                               size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Debug / unit-test entry points for the tcgen05 building blocks (used by tests/ only).
  * sim: S[128,128] = A[128,dim] B[128,dim]^T ;  tsg: G[128,dim] = bf16(S) B  (A from TMEM). */
 int muscle_debug_tile(const void* a_bf16, const void* b_bf16, int dim, float* s_out,

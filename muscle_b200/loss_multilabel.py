@@ -84,3 +84,82 @@ def PixPro(fm1s, fm2s, coord1s, coord2s):
     max_px = int((c1[:, 2] * c1[:, 3]).max())
     boxes = torch.stack([c1, c2]).to(torch.int32).to(fm1s.device, non_blocking=True)
     return _PixPro.apply(fm1s, fm2s, boxes[0], boxes[1], max_px)
+
+
+class _EmdDynamic(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, flat1, flat2, pair_desc, n_pairs, n_images, channels, max_n, max_m, max_nm, reg, maxiter):
+        lib = _lib.load()
+        dev = flat1.device
+        f1, f2 = flat1.contiguous(), flat2.contiguous()
+        sb = lib.muscle_emd_scratch_bytes(n_pairs, n_images, max_nm, maxiter)
+        scratch = torch.empty(sb, dtype=torch.uint8, device=dev)
+        loss = torch.empty((), dtype=torch.float32, device=dev)
+        d1 = torch.empty_like(f1) if flat1.requires_grad else None
+        call("muscle_emd_dynamic_fwd_bwd", dev, f1.data_ptr(), f2.data_ptr(), pair_desc.data_ptr(), n_pairs, n_images,
+             channels, max_n, max_m, max_nm, float(reg), int(maxiter), loss.data_ptr(), ptr(d1), f1.numel(),
+             scratch.data_ptr(), sb)
+        ctx.save_for_backward(d1)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gloss):
+        d1, = ctx.saved_tensors
+        return (None if d1 is None else d1 * gloss,) + (None,) * 10
+
+
+def _pack_regions(crops):
+    """nested lists of [1,C,h,w] tensors -> (flat, meta, C).  Lists made by
+    muscle_b200.torchutils.get_dynamic_crops already carry their flat buffer; anything else is
+    concatenated (torch.cat is plumbing: autograd routes the gradient back to every tensor)."""
+    from .torchutils import CropPack
+    if isinstance(crops, CropPack) and crops.flat is not None:
+        return crops.flat, crops.meta, crops.channels
+    pieces, meta, off, ch = [], [], 0, None
+    for img in crops:
+        m = []
+        for t in img:
+            require_cuda_f32(t, "crop")
+            if t.dim() != 4 or t.shape[0] != 1:
+                raise ValueError("crops must be [1,C,h,w] tensors")
+            ch = t.shape[1] if ch is None else ch
+            pieces.append(t.reshape(-1))
+            m.append((off, t.shape[2] * t.shape[3]))
+            off += t.numel()
+        meta.append(m)
+    return torch.cat(pieces), meta, ch
+
+
+class EMD:
+    """src/loss_multilabel.py:108-338, the members on the trainer's path: ``EMD()(crops1, crops2,
+    mode='dynamic')`` (train_mcl.py:147,221).  Gradient flows to crops1; crops2 and the Sinkhorn
+    marginals are constants, as in the reference (:308-313, train_mcl.py:220 passes vw2.detach())."""
+
+    reg = 0.1        # :207
+    maxiter = 10     # :313,323
+
+    def dynamic_matching(self, crops1, crops2):
+        if len(crops1) == 0 or len(crops1) != len(crops2):
+            raise ValueError("crops1 and crops2 must be non-empty lists of equal length")
+        flat1, meta1, ch = _pack_regions(crops1)
+        flat2, meta2, _ = _pack_regions(crops2)
+        if flat2.requires_grad:
+            flat2 = flat2.detach()      # region 2 carries no gradient on the reference's path
+        rows, max_n, max_m, max_nm = [], 0, 0, 0
+        for i, (m1, m2) in enumerate(zip(meta1, meta2)):
+            for off1, n in m1:                      # crop1 outer, crop2 inner (:295,302)
+                for off2, m in m2:
+                    rows.append([off1, n, off2, m, i, 0])
+                    max_n, max_m, max_nm = max(max_n, n), max(max_m, m), max(max_nm, n + m)
+        desc = torch.tensor(rows, dtype=torch.int64).to(flat1.device, non_blocking=True)
+        return _EmdDynamic.apply(flat1, flat2, desc, len(rows), len(meta1), ch, max_n, max_m, max_nm, self.reg,
+                                 self.maxiter)
+
+    def __call__(self, crops1, crops2, mode="static"):
+        if mode == "dynamic":
+            return self.dynamic_matching(crops1, crops2)
+        if mode == "static":
+            raise NotImplementedError("EMD mode='static' is not on the trainer's path (train_mcl.py:221 uses "
+                                      "'dynamic') and is not built")
+        print("Unrecognised mode!")      # :335-336
+        return None

@@ -1,0 +1,134 @@
+"""Drop-in for ``torchutils.get_dynamic_crops`` (src/torchutils.py:217-291; train_mcl.py:220).
+
+The window plan is host integer work and consumes numpy's global RNG exactly like the reference
+(:246-254, one image after the other); the tensor work — every bilinear resize and average pool
+of the batch — is ONE kernel launch writing into a flat buffer.  The returned nested lists hold
+views of that buffer, so any consumer works; ``muscle_b200.loss_multilabel.EMD`` recognises the
+``CropPack`` lists and reads the flat buffer directly."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from ._call import call, require_cuda_f32
+
+
+def _plan_image(h, w, rng):
+    """Integer half of src/torchutils.py:240-280 for one h x w overlap box.  -> None (box rejected)
+    or (view-1 windows [(top,left,lh,lw)], (rh,rw), pooled?, view-2 windows)."""
+    if h < 15 or w < 15 or h / w > 5 or w / h > 5:                      # :240
+        return None
+    lh = rng.randint(h // 3, h // 2 + 1)                               # :246-247
+    lw = rng.randint(w // 3, w // 2 + 1)
+    while lh < 5 or lw < 5:                                            # :249-251
+        lh = rng.randint(h // 3, h // 2 + 1)
+        lw = rng.randint(w // 3, w // 2 + 1)
+    sh = rng.randint(lh // 2, lh + 1)                                  # :253-254
+    sw = rng.randint(lw // 2, lw + 1)
+    rh, rw = round(h / (h / sh)), round(w / (w / sw))                  # :255-256,266-267
+    wins1 = []
+    if rh >= 7 and rw >= 7:                                            # :268
+        for top in range(0, h, sh):
+            for left in range(0, w, sw):
+                if top + lh <= h and left + lw <= w:                   # :259
+                    wins1.append((top, left, lh, lw))
+    wins2 = [(top, left, min(h // 2, h - top), min(w // 2, w - left))
+             for top in range(0, h - 1, h // 2) for left in range(0, w - 1, w // 2)]   # :276-278
+    return wins1, (rh, rw), (rh > 28 or rw > 28), wins2
+
+
+class CropPack(list):
+    """A list of per-image lists of [1,C,h,w] crop tensors that also carries the flat buffer they
+    are views of (``flat``), per-crop (offset, pixels) (``meta``, same nesting) and the channel count."""
+    flat = None
+    meta = None
+    channels = 0
+
+
+class _Crops(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, desc, offs, n_crops, total):
+        xc = x.contiguous()
+        b, c, h, w = xc.shape
+        flat = torch.empty(total, dtype=torch.float32, device=x.device)
+        call("muscle_crops_fwd", x.device, xc.data_ptr(), c, h, w, desc.data_ptr(), offs.data_ptr(), n_crops, total,
+             flat.data_ptr())
+        ctx.save_for_backward(desc, offs)
+        ctx.dims = (b, c, h, w, n_crops, total)
+        return flat
+
+    @staticmethod
+    def backward(ctx, dflat):
+        desc, offs = ctx.saved_tensors
+        b, c, h, w, n_crops, total = ctx.dims
+        dx = torch.empty((b, c, h, w), dtype=torch.float32, device=dflat.device)
+        call("muscle_crops_bwd", dflat.device, dflat.contiguous().data_ptr(), b, c, h, w, desc.data_ptr(),
+             offs.data_ptr(), n_crops, total, dx.data_ptr())
+        return dx, None, None, None, None
+
+
+def _extract(x, rows, shapes_nested):
+    """rows: list of 10-int descriptors (flat order); shapes_nested: per image list of (oh, ow).
+    -> CropPack"""
+    c = x.shape[1]
+    offs, total = [], 0
+    for r in rows:
+        offs.append(total)
+        total += c * r[8] * r[9]
+    offs.append(total)
+    dev = x.device
+    desc_t = torch.tensor(rows, dtype=torch.int32).to(dev, non_blocking=True)
+    offs_t = torch.tensor(offs, dtype=torch.int64).to(dev, non_blocking=True)
+    flat = _Crops.apply(x, desc_t, offs_t, len(rows), total)
+    pack = CropPack()
+    pack.flat, pack.channels, pack.meta = flat, c, []
+    i = 0
+    for shapes in shapes_nested:
+        img, meta = [], []
+        for oh, ow in shapes:
+            img.append(flat[offs[i]:offs[i + 1]].view(1, c, oh, ow))
+            meta.append((offs[i], oh * ow))
+            i += 1
+        pack.append(img)
+        pack.meta.append(meta)
+    return pack
+
+
+def get_dynamic_crops(x1, coord1, x2, coord2):
+    """src/torchutils.py:217-291.  x1, x2 [B,C,H,W] fp32 CUDA; coord [B,4] = (top, left, h, w).
+    -> (crops1, crops2, batch_indices): nested lists of [1,C,h',w'] tensors (grad flows to x1/x2)."""
+    require_cuda_f32(x1, "x1")
+    require_cuda_f32(x2, "x2")
+    bsz, _, H, W = x1.shape
+    c1 = coord1.detach().to("cpu").long().tolist()
+    c2 = coord2.detach().to("cpu").long().tolist()
+    rows1, rows2, shapes1, shapes2, batch_indices = [], [], [], [], []
+    for b in range(bsz):
+        t1, l1, bh, bw = c1[b]
+        t2, l2, bh2, bw2 = c2[b]
+        h, w = min(bh, H - t1), min(bw, W - l1)          # python slicing clamps (:226)
+        h2, w2 = min(bh2, H - t2), min(bw2, W - l2)
+        plan = _plan_image(h, w, np.random)
+        if plan is None:
+            continue
+        wins1, (rh, rw), pool, wins2 = plan
+        if not wins1:
+            continue
+        r1, s1 = [], []
+        for top, left, lh, lw in wins1:
+            oh, ow = (rh // 4, rw // 4) if pool else (rh, rw)
+            r1.append([b, t1 + top, l1 + left, lh, lw, rh, rw, int(pool), oh, ow])
+            s1.append((oh, ow))
+        r2, s2 = [], []
+        for top, left, hh, ww in wins2:
+            hh, ww = min(hh, h2 - top), min(ww, w2 - left)   # slicing ins2 clamps at its own size
+            r2.append([b, t2 + top, l2 + left, hh, ww, hh, ww, 1, hh // 4, ww // 4])
+            s2.append((hh // 4, ww // 4))
+        rows1 += r1
+        rows2 += r2
+        shapes1.append(s1)
+        shapes2.append(s2)
+        batch_indices.append(b)
+    if not rows1:
+        return [], [], []
+    return _extract(x1, rows1, shapes1), _extract(x2, rows2, shapes2), batch_indices
