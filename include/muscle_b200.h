@@ -126,6 +126,21 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
                          const float* dproto, const double* loss_acc, float temperature,
                          int layout, float* dx, float* loss_out, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * info_nce — replaces src/loss_multilabel.py:9-21 with distinct operand sets: query [Q, dim],
+ * positive_keys [P, dim], negative_keys [K, dim], fp32 row-major, unit-norm rows (like the reference
+ * the function does not normalise; the tensor-pipe passes assume |q.k| <= 1).  loss_out float[1]
+ * = mean (reduction_mean != 0) or sum over queries; row_loss_out [Q] (reduction 'none') or NULL;
+ * dquery_out [Q,dim], dpositive_out [P,dim], dnegative_out [K,dim]: gradients of loss_out, each
+ * may be NULL.  dim in {64,128,256}. */
+size_t muscle_info_nce_workspace_bytes(int64_t n_query, int64_t n_negative, int dim);
+int muscle_info_nce_fwd_bwd(const float* query, const float* positive_keys,
+                            const float* negative_keys, int64_t n_query, int64_t n_positive,
+                            int64_t n_negative, int dim, float temperature, int reduction_mean,
+                            float* loss_out, float* row_loss_out, float* dquery_out,
+                            float* dpositive_out, float* dnegative_out, void* workspace,
+                            size_t workspace_bytes, void* stream);
+
 /* ==========================================================================================
  * The other members of the path.  Same conventions as above.
  * ========================================================================================== */

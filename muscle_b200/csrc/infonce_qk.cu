@@ -1,0 +1,199 @@
+// The InfoNCE primitive itself, src/loss_multilabel.py:9-21, with distinct query / positive /
+// negative sets:  pos_q = q . mean(P),  neg_qk = q . k,  loss_q = logsumexp([pos_q, neg_q.]/T) - pos_q/T,
+// and its gradients to all three operands.  Built from the staged tcgen05 passes of the dense op
+// (include/muscle_b200.h, "Staged form"): queries are "class 0" rows, negative keys "class 1"
+// columns, so every (query, key) pair is live; the gradient pass runs twice, once per role
+//   dQ = 1/T sum_k p_qk k + gpos_q proto        (rows = queries, w_row = 1/rowsum, w_col = 0)
+//   dK = 1/T sum_q p_qk q                        (rows = keys,    w_row = 0, w_col = 1/rowsum)
+// Like the reference, nothing is normalised here: the caller passes unit-norm rows (the exponent
+// shift of the pair passes assumes |q.k| <= 1).
+#include <algorithm>
+
+#include "host_util.cuh"
+#include "pair_kernel.cuh"
+
+using namespace mb200;
+
+namespace {
+
+size_t al(size_t v) { return (v + 255) / 256 * 256; }
+
+struct QkWs {
+  size_t eq, ek, bq, bk, tq, tk, inq, ink, pq, pk, segq, segk, cls, stats_tmp, cs, cm, rowsum, w, gpos, zk, dproto,
+      lacc, uo_qk, uo_kq, part_q, part_k, scratch, zero_lo, zero_hi, total;
+  int64_t qp, kp;
+};
+QkWs plan(int64_t Q, int64_t K, int dim) {
+  QkWs w{};
+  w.qp = muscle_pad_rows(Q);
+  w.kp = muscle_pad_rows(K);
+  size_t off = 0;
+  auto take = [&](size_t b) { size_t o = off; off = al(off + b); return o; };
+  const size_t qp = w.qp, kp = w.kp, mx = std::max(qp, kp);
+  w.eq = take(qp * dim * 2); w.ek = take(kp * dim * 2);
+  w.bq = take(qp * 4); w.bk = take(kp * 4);
+  w.tq = take(qp / 128 * 4); w.tk = take(kp / 128 * 4);
+  w.inq = take(qp * 4); w.ink = take(kp * 4);
+  w.pq = take(qp * 4); w.pk = take(kp * 4);
+  w.segq = take(16); w.segk = take(16);
+  w.cls = take(mx * 4);
+  w.uo_qk = take((qp / 128 + 1) * 4); w.uo_kq = take((kp / 128 + 1) * 4);
+  w.w = take(qp * 4); w.gpos = take(qp * 4);
+  w.zero_lo = off;                       // everything from here to zero_hi is cleared by one memset
+  w.stats_tmp = take((2 * dim + 2) * 4);
+  w.cs = take(2 * dim * 4); w.cm = take(8);
+  w.rowsum = take(qp * 4); w.zk = take(mx * 4);
+  w.dproto = take(2 * dim * 4); w.lacc = take(8);
+  w.zero_hi = off;
+  w.part_q = take(static_cast<size_t>(PAIR_SLOTS) * qp * dim * 4);
+  w.part_k = take(static_cast<size_t>(PAIR_SLOTS) * kp * dim * 4);
+  w.scratch = take(std::max(muscle_infonce_prepare_scratch_bytes(Q), muscle_infonce_prepare_scratch_bytes(K)));
+  w.total = off;
+  return w;
+}
+
+__global__ void fill_int_kernel(int* p, int v, long long n) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+// class_sum[0][d] = sum_p pos[p][d]; class_mass[0] = P
+__global__ void __launch_bounds__(256) pos_sum_kernel(const float* pos, long long P, int dim, float* cs, float* cm) {
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d < dim) {
+    float s = 0.f;
+    for (long long p = 0; p < P; ++p) s += pos[p * dim + d];
+    cs[d] = s;
+  }
+  if (d == 0) cm[0] = static_cast<float>(P);
+}
+
+struct QkFinal {
+  const float* part;       // [slots][rows_pad][dim]
+  const uint32_t* unit_off;
+  int n_row_blocks, n_col_tiles, n_ctas, rb;
+  long long rows_pad, n;
+  int dim;
+  const float* gpos;       // may be null (key side)
+  const float* proto_sum;  // class_sum[0] (query side)
+  float inv_mass, inv_tau, scale;
+  float* dst;              // [n][dim]
+  const float* w;          // query side: 1/rowsum -> per-row loss
+  float* row_loss;         // may be null
+};
+// one warp per row
+__global__ void __launch_bounds__(256) qk_final_kernel(const QkFinal p) {
+  const long long r = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (r >= p.n) return;
+  const int lane = threadIdx.x & 31;
+  const uint32_t per = pair_units_per_cta(p.unit_off[p.n_row_blocks], p.n_ctas, p.n_col_tiles);
+  const int rbk = static_cast<int>(r / p.rb);
+  const uint32_t U0 = p.unit_off[rbk], U1 = p.unit_off[rbk + 1];
+  const int n_slots = (U1 > U0) ? static_cast<int>((U1 - 1) / per - U0 / per + 1) : 0;
+  const float g = p.gpos ? p.gpos[r] * p.inv_mass : 0.f;
+  for (int d = lane; d < p.dim; d += 32) {
+    float s = 0.f;
+    for (int k = 0; k < n_slots; ++k) s += p.part[(static_cast<long long>(k) * p.rows_pad + r) * p.dim + d];
+    float v = p.inv_tau * s;
+    if (p.gpos) v = fmaf(g, p.proto_sum[d], v);
+    p.dst[r * p.dim + d] = p.scale * v;
+  }
+  if (p.row_loss && lane == 0) p.row_loss[r] = -logf(fmaxf(1.f + p.gpos[r] / p.inv_tau, 1e-30f));
+}
+// dpos[p][d] = scale * dproto[0][d] / P ;  loss = loss_acc * scale
+__global__ void __launch_bounds__(256) qk_pos_final_kernel(const float* dproto, const double* lacc, long long P, int dim,
+                                                           float scale, float* dpos, float* loss) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (dpos && i < P * dim) dpos[i] = scale * dproto[i % dim] / static_cast<float>(P);
+  if (i == 0 && loss) *loss = static_cast<float>(*lacc * static_cast<double>(scale));
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t muscle_info_nce_workspace_bytes(int64_t n_query, int64_t n_negative, int dim) {
+  if (n_query <= 0 || n_negative <= 0 || !(dim == 64 || dim == 128 || dim == 256)) return 0;
+  return plan(n_query, n_negative, dim).total;
+}
+
+int muscle_info_nce_fwd_bwd(const float* query, const float* positive_keys, const float* negative_keys,
+                            int64_t n_query, int64_t n_positive, int64_t n_negative, int dim, float temperature,
+                            int reduction_mean, float* loss_out, float* row_loss_out, float* dquery_out,
+                            float* dpositive_out, float* dnegative_out, void* workspace, size_t workspace_bytes,
+                            void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!query || !positive_keys || !negative_keys || !loss_out || !workspace)
+    return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (n_query <= 0 || n_positive <= 0 || n_negative <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty input");
+  if (!(dim == 64 || dim == 128 || dim == 256)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
+  if (!(temperature > 0.f)) return fail(MUSCLE_ERR_BAD_ARG, "temperature must be > 0");
+  if (reinterpret_cast<uintptr_t>(workspace) & 255) return fail(MUSCLE_ERR_BAD_ARG, "workspace must be 256-byte aligned");
+  const QkWs W = plan(n_query, n_negative, dim);
+  if (workspace_bytes < W.total) return fail(MUSCLE_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, W.total);
+  char* b = static_cast<char*>(workspace);
+  auto F = [&](size_t o) { return reinterpret_cast<float*>(b + o); };
+  auto U = [&](size_t o) { return reinterpret_cast<uint32_t*>(b + o); };
+  int* cls = reinterpret_cast<int*>(b + W.cls);
+  const int64_t Q = n_query, K = n_negative;
+  const bool need_grad = dquery_out || dnegative_out || dpositive_out;
+  MB_CUDA(cudaMemsetAsync(b + W.zero_lo, 0, W.zero_hi - W.zero_lo, stream));
+  // queries: class 0
+  MB_CUDA(cudaMemsetAsync(cls, 0, Q * 4, stream));
+  int rc = muscle_infonce_prepare(query, MUSCLE_LAYOUT_PIXEL_MAJOR, 1, Q, dim, cls, 0, 2, 1e-12f, b + W.eq, U(W.bq),
+                                  F(W.inq), reinterpret_cast<int32_t*>(b + W.pq), U(W.tq), U(W.segq), F(W.stats_tmp),
+                                  F(W.stats_tmp) + 2 * dim, b + W.scratch, muscle_infonce_prepare_scratch_bytes(Q), stream_);
+  if (rc) return rc;
+  // negative keys: class 1
+  fill_int_kernel<<<static_cast<unsigned>((K + 255) / 256), 256, 0, stream>>>(cls, 1, K);
+  MB_LAUNCH_CHECK();
+  rc = muscle_infonce_prepare(negative_keys, MUSCLE_LAYOUT_PIXEL_MAJOR, 1, K, dim, cls, 0, 2, 1e-12f, b + W.ek, U(W.bk),
+                              F(W.ink), reinterpret_cast<int32_t*>(b + W.pk), U(W.tk), U(W.segk), F(W.stats_tmp),
+                              F(W.stats_tmp) + 2 * dim, b + W.scratch, muscle_infonce_prepare_scratch_bytes(K), stream_);
+  if (rc) return rc;
+  pos_sum_kernel<<<(dim + 255) / 256, 256, 0, stream>>>(positive_keys, n_positive, dim, F(W.cs), F(W.cm));
+  MB_LAUNCH_CHECK();
+  if ((rc = muscle_infonce_plan(U(W.tq), W.qp, U(W.tk), W.kp, dim, U(W.uo_qk), stream_))) return rc;
+  if ((rc = muscle_infonce_rowsum(b + W.eq, U(W.bq), U(W.tq), W.qp, b + W.ek, U(W.bk), U(W.tk), W.kp, U(W.uo_qk), dim,
+                                  temperature, F(W.rowsum), stream_)))
+    return rc;
+  if ((rc = muscle_infonce_mid(b + W.eq, U(W.segq), W.qp, dim, 2, F(W.cs), F(W.cm), F(W.rowsum), temperature, F(W.w),
+                               F(W.gpos), reinterpret_cast<double*>(b + W.lacc), F(W.dproto), stream_)))
+    return rc;
+  const float scale = reduction_mean ? 1.f / static_cast<float>(Q) : 1.f;
+  const int rb = (dim == 256) ? 128 : 256;
+  const int n_ctas = device_info().sm_count;
+  if (dquery_out || row_loss_out) {
+    if (dquery_out)
+      if ((rc = muscle_infonce_grad(b + W.eq, U(W.bq), U(W.tq), F(W.w), W.qp, b + W.ek, U(W.bk), U(W.tk), F(W.zk), W.kp,
+                                    U(W.uo_qk), dim, temperature, F(W.part_q), stream_)))
+        return rc;
+    QkFinal f{};
+    f.part = F(W.part_q); f.unit_off = U(W.uo_qk); f.n_row_blocks = static_cast<int>(W.qp / rb);
+    f.n_col_tiles = static_cast<int>(W.kp / 128); f.n_ctas = n_ctas; f.rb = rb; f.rows_pad = W.qp; f.n = Q; f.dim = dim;
+    f.gpos = F(W.gpos); f.proto_sum = F(W.cs); f.inv_mass = 1.f / static_cast<float>(n_positive);
+    f.inv_tau = 1.f / temperature; f.scale = scale; f.dst = dquery_out; f.w = F(W.w); f.row_loss = row_loss_out;
+    if (!dquery_out) { f.dim = 0; }
+    qk_final_kernel<<<static_cast<unsigned>((Q + 7) / 8), 256, 0, stream>>>(f);
+    MB_LAUNCH_CHECK();
+  }
+  if (dnegative_out) {
+    if ((rc = muscle_infonce_plan(U(W.tk), W.kp, U(W.tq), W.qp, dim, U(W.uo_kq), stream_))) return rc;
+    if ((rc = muscle_infonce_grad(b + W.ek, U(W.bk), U(W.tk), F(W.zk), W.kp, b + W.eq, U(W.bq), U(W.tq), F(W.w), W.qp,
+                                  U(W.uo_kq), dim, temperature, F(W.part_k), stream_)))
+      return rc;
+    QkFinal f{};
+    f.part = F(W.part_k); f.unit_off = U(W.uo_kq); f.n_row_blocks = static_cast<int>(W.kp / rb);
+    f.n_col_tiles = static_cast<int>(W.qp / 128); f.n_ctas = n_ctas; f.rb = rb; f.rows_pad = W.kp; f.n = K; f.dim = dim;
+    f.gpos = nullptr; f.inv_tau = 1.f / temperature; f.scale = scale; f.dst = dnegative_out;
+    qk_final_kernel<<<static_cast<unsigned>((K + 7) / 8), 256, 0, stream>>>(f);
+    MB_LAUNCH_CHECK();
+  }
+  (void)need_grad;
+  const long long np = dpositive_out ? n_positive * dim : 1;
+  qk_pos_final_kernel<<<static_cast<unsigned>((np + 255) / 256), 256, 0, stream>>>(
+      F(W.dproto), reinterpret_cast<const double*>(b + W.lacc), n_positive, dim, scale, dpositive_out, loss_out);
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
+}
+
+}  // extern "C"

@@ -163,3 +163,61 @@ class EMD:
                                       "'dynamic') and is not built")
         print("Unrecognised mode!")      # :335-336
         return None
+
+
+class _InfoNce(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, query, positive_keys, negative_keys, temperature, mode, dim_pad):
+        lib = _lib.load()
+        dev = query.device
+
+        def padded(t):      # zero columns change no dot product; the tensor-pipe passes need dim in {64,128,256}
+            t = t.contiguous()
+            return t if t.shape[1] == dim_pad else torch.nn.functional.pad(t, (0, dim_pad - t.shape[1]))
+
+        q, p, k = padded(query), padded(positive_keys), padded(negative_keys)
+        nq, npos, nk = q.shape[0], p.shape[0], k.shape[0]
+        wsb = lib.muscle_info_nce_workspace_bytes(nq, nk, dim_pad)
+        ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+        loss = torch.empty((), dtype=torch.float32, device=dev)
+        rows = torch.empty(nq, dtype=torch.float32, device=dev) if mode == "none" else None
+        need = ctx.needs_input_grad
+        dq = torch.empty_like(q) if need[0] else None
+        dp = torch.empty_like(p) if need[1] else None
+        dk = torch.empty_like(k) if need[2] else None
+        call("muscle_info_nce_fwd_bwd", dev, q.data_ptr(), p.data_ptr(), k.data_ptr(), nq, npos, nk, dim_pad,
+             float(temperature), 1 if mode == "mean" else 0, loss.data_ptr(), ptr(rows), ptr(dq), ptr(dp), ptr(dk),
+             ws.data_ptr(), wsb)
+        d = query.shape[1]
+        ctx.save_for_backward(*(None if t is None else t[:, :d] for t in (dq, dp, dk)))
+        ctx.mode = mode
+        return rows if mode == "none" else loss
+
+    @staticmethod
+    def backward(ctx, g):
+        dq, dp, dk = ctx.saved_tensors
+        if ctx.mode == "none":
+            raise NotImplementedError("info_nce(reduction='none') is forward-only here; reduce before backward")
+        return (None if dq is None else dq * g, None if dp is None else dp * g, None if dk is None else dk * g,
+                None, None, None)
+
+
+def info_nce(query, positive_keys, negative_keys, temperature=0.1, reduction="mean"):
+    """src/loss_multilabel.py:9-21.  query [Q,D], positive_keys [P,D], negative_keys [K,D], fp32 CUDA,
+    rows unit-norm (the reference does not normalise either; it is the caller's job — here it is also
+    a precondition of the tensor-pipe passes and is checked).  reduction in {'mean','sum','none'};
+    'none' returns the [Q] losses without a backward."""
+    for name, t in (("query", query), ("positive_keys", positive_keys), ("negative_keys", negative_keys)):
+        require_cuda_f32(t, name)
+        if t.dim() != 2 or t.shape[1] != query.shape[1]:
+            raise ValueError("info_nce operands must be [rows, D] with a common D")
+    if reduction not in ("mean", "sum", "none"):
+        raise ValueError("reduction must be 'mean', 'sum' or 'none'")
+    d = query.shape[1]
+    if d > 256:
+        raise ValueError("info_nce supports D <= 256 (got %d)" % d)
+    worst = max(float(query.detach().norm(dim=1).max()), float(negative_keys.detach().norm(dim=1).max()))
+    if worst > 1.0 + 1e-3:
+        raise ValueError("info_nce expects unit-norm rows (max norm %.4f): normalise the embeddings first" % worst)
+    dim_pad = 64 if d <= 64 else (128 if d <= 128 else 256)
+    return _InfoNce.apply(query, positive_keys, negative_keys, temperature, reduction, dim_pad)
