@@ -1,0 +1,141 @@
+#!/usr/bin/env python
+"""Device-time table of every op on the path besides the dense InfoNCE (which bench.py measures):
+CUDA-event timing on the launching stream, L2 flushed between iterations, fwd+bwd through the
+public Python mirrors.  Prints one JSON object; profiles/ keeps a copy per round.
+
+    python scripts/bench_ops.py [--iters 20]
+"""
+import argparse
+import json
+import os
+import random
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--iters", type=int, default=20)
+    args = ap.parse_args()
+    from muscle_b200 import heads
+    from muscle_b200.edge import FieldLoss
+    from muscle_b200.loss_multilabel import EMD, PixPro, image_level_contrast
+    from muscle_b200.torchutils import get_dynamic_crops
+    dev = torch.device("cuda", 0)
+    gen = torch.Generator().manual_seed(0)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
+        os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        evs = []
+        for _ in range(args.iters):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record()
+            evs.append((a, b))
+        torch.cuda.synchronize()
+        return sum(x.elapsed_time(y) for x, y in evs) / len(evs)
+
+    out = {}
+    # ---- PCM + CAM head, config 2 at stride 8 (B=8, 56x56, b7: Cin=336, p7 ch=640)
+    B, P_h = 8, 56
+    cam = torch.rand(B, 21, P_h, P_h, generator=gen).to(dev).requires_grad_()
+    f = torch.relu(torch.randn(B, 336, P_h, P_h, generator=gen)).to(dev)
+    wt = (torch.randn(128, 336, 1, 1, generator=gen) / 336 ** 0.5).to(dev).requires_grad_()
+    bias = (torch.randn(128, generator=gen) * 0.1).to(dev).requires_grad_()
+    go = torch.randn(B, 21, P_h, P_h, generator=gen).to(dev)
+
+    def pcm_step():
+        o = heads.pcm(cam, f, wt, bias)
+        o.backward(go)
+        cam.grad = wt.grad = bias.grad = None
+    ms = timed(pcm_step)
+    pairs = B * (P_h * P_h) ** 2
+    flops = pairs * 2.0 * (128 + 32) + pairs * 2.0 * (128 + 32) + pairs * 2.0 * (128 + 128 + 128)   # fwd, dcam, bwd
+    out["pcm_fwd_bwd_config2_stride8"] = dict(ms=ms, pixel_pairs_per_s=pairs / ms * 1e3, executed_tflops=flops / ms / 1e9,
+                                              frac_of_bf16_burst=flops / ms / 1e9 / peaks["bf16_tflops"], bound="tensor")
+    p7 = torch.relu(torch.randn(B, 640, P_h, P_h, generator=gen)).to(dev).requires_grad_()
+    fw = (torch.randn(21, 640, generator=gen) * 0.05).to(dev).requires_grad_()
+    gcam = torch.randn(B, 21, P_h, P_h, generator=gen).to(dev)
+
+    def cam_step():
+        c = heads.cam_head(p7, fw)
+        e, l = heads.image_embedding_logits(p7, fw)
+        (c * gcam).sum().backward(retain_graph=False, inputs=[p7]) if False else torch.autograd.backward(
+            [c, l], [gcam, torch.ones_like(l)])
+        p7.grad = fw.grad = None
+    ms = timed(cam_step)
+    byt = p7.numel() * 4 * 4 + B * 21 * P_h * P_h * 4 * 3      # p7 read x2 (cam, gap), dp7 written x2, cam w + r, dcam r
+    out["cam_head_gap_logits_fwd_bwd"] = dict(ms=ms, algorithmic_gb_s=byt / ms / 1e6, frac_of_hbm=byt / ms / 1e6 / peaks["hbm_gbs"],
+                                             bound="hbm")
+    # ---- IMC, B=64 images, ch=640
+    emb = torch.randn(64, 640, generator=gen).abs().to(dev).requires_grad_()
+    from oracle import muscle_oracle as O   # synthetic label generator only
+    lab = O.synth_labels(64, gen).to(dev)
+
+    def imc_step():
+        l = image_level_contrast(emb, lab)
+        if torch.is_tensor(l):
+            l.backward()
+        emb.grad = None
+    out["imc_fwd_bwd_B64"] = dict(ms=timed(imc_step), bound="latency")
+    # ---- PixPro, B=8, 21x224x224
+    fm1 = torch.rand(8, 21, 224, 224, generator=gen).to(dev).requires_grad_()
+    fm2 = torch.rand(8, 21, 224, 224, generator=gen).to(dev)
+    hw = torch.randint(100, 200, (8, 2), generator=gen)
+    c1 = torch.cat([(torch.rand(8, 2, generator=gen) * (224 - hw)).long(), hw], 1)
+    c2 = torch.cat([(torch.rand(8, 2, generator=gen) * (224 - hw)).long(), hw], 1)
+
+    def pix_step():
+        PixPro(fm1, fm2, c1, c2).backward()
+        fm1.grad = None
+    ms = timed(pix_step)
+    byt = float((hw[:, 0] * hw[:, 1]).sum()) * 21 * 4 * 3 + fm1.numel() * 4
+    out["pixpro_fwd_bwd_B8"] = dict(ms=ms, algorithmic_gb_s=byt / ms / 1e6, bound="hbm/latency")
+    # ---- crops + EMD dynamic, B=8
+    raw1 = F.avg_pool2d(torch.randn(8, 21, 224, 224, generator=gen), 9, 1, 4).to(dev).requires_grad_()
+    raw2 = F.avg_pool2d(torch.randn(8, 21, 224, 224, generator=gen), 9, 1, 4).to(dev)
+
+    def emd_step():
+        v1 = F.normalize(heads.cam_softmaxnorm(raw1), dim=1)
+        v2 = F.normalize(heads.cam_softmaxnorm(raw2), dim=1)
+        np.random.seed(3)
+        a, b, _ = get_dynamic_crops(v1, c1, v2.detach(), c2)
+        EMD()(a, b, mode="dynamic").backward()
+        raw1.grad = None
+    out["crops_emd_dynamic_fwd_bwd_B8"] = dict(ms=timed(emd_step), bound="latency")
+    # ---- FieldLoss, config 3 scale reduced to B=4 (512x512, 256 ch) to bound memory in this table
+    n, h, w, ch = 4, 512, 512, 256
+    label = O.synth_labels(n, gen)
+    label_bg = torch.cat([torch.ones(n, 1), label], 1)
+    noise = F.avg_pool2d(torch.randn(n, 21, h, w, generator=gen), 31, 1, 15, count_include_pad=False)
+    noise = noise.masked_fill(~label_bg.bool()[:, :, None, None], -1e4)
+    seg = (noise * 3).to(dev)
+    mask = (noise * 2).to(dev)
+    dense = torch.randn(n, ch, h, w, generator=gen).to(dev).requires_grad_()
+    crit = FieldLoss(sobel_size=5, beta=1e2, k=128)
+    lbg = label_bg.to(dev)
+
+    def field_step():
+        random.seed(1)
+        l, _ = crit(seg, dense, mask, lbg, 7)
+        if torch.is_tensor(l):
+            l.backward()
+        dense.grad = None
+    ms = timed(field_step)
+    out["fieldloss_fwd_bwd_B4_512"] = dict(ms=ms, note="includes the one device->host read of the counts and the "
+                                           "memset of the dense gradient (%.0f MB)" % (dense.numel() * 4 / 1e6), bound="hbm/latency")
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
