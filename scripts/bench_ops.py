@@ -70,8 +70,7 @@ def main():
     def cam_step():
         c = heads.cam_head(p7, fw)
         e, l = heads.image_embedding_logits(p7, fw)
-        (c * gcam).sum().backward(retain_graph=False, inputs=[p7]) if False else torch.autograd.backward(
-            [c, l], [gcam, torch.ones_like(l)])
+        torch.autograd.backward([c, l], [gcam, torch.ones_like(l)])
         p7.grad = fw.grad = None
     ms = timed(cam_step)
     byt = p7.numel() * 4 * 4 + B * 21 * P_h * P_h * 4 * 3      # p7 read x2 (cam, gap), dp7 written x2, cam w + r, dcam r
