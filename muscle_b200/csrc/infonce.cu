@@ -23,6 +23,12 @@ int check_device() {
   return MUSCLE_OK;
 }
 
+// grid of the pair passes: one persistent CTA per SM (MUSCLE_PAIR_GRID overrides it for experiments)
+int pair_grid() {
+  static const int g = getenv("MUSCLE_PAIR_GRID") ? atoi(getenv("MUSCLE_PAIR_GRID")) : 0;
+  return g > 0 ? g : device_info().sm_count;
+}
+
 template <int D, int MODE, int POLY>
 int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, int64_t cols_pad,
                 PairParams prm, cudaStream_t stream) {
@@ -38,9 +44,37 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
     MB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     attr_set = true;
   }
-  const int grid = device_info().sm_count;  // one persistent CTA per SM; shares come from unit_off
+  const int grid = pair_grid();  // one persistent CTA per SM; shares come from unit_off
+  static const bool timing = getenv("MUSCLE_PAIR_TIMING") != nullptr;   // debug: per-phase cycle counters
+  static unsigned long long* dbg = nullptr;
+  if (timing) {
+    if (!dbg) cudaMalloc(&dbg, grid * 16 * sizeof(unsigned long long));
+    cudaMemsetAsync(dbg, 0, grid * 16 * sizeof(unsigned long long), stream);
+    prm.dbg = dbg;
+  }
   kern<<<grid, C::THREADS, C::SMEM_BYTES, stream>>>(tm_row, tm_col, prm);
   MB_LAUNCH_CHECK();
+  if (timing) {
+    static int printed = 0;
+    cudaStreamSynchronize(stream);
+    unsigned long long h[148 * 16];
+    cudaMemcpy(h, dbg, std::min(grid, 148) * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    if (printed++ < 6) {
+      double s[16] = {0};
+      int n = 0;
+      for (int c = 0; c < std::min(grid, 148); ++c)
+        if (h[c * 16 + 6]) { for (int k = 0; k < 15; ++k) s[k] += double(h[c * 16 + k]); ++n; }
+      if (n) {
+        const double tiles = s[6] / n;
+        fprintf(stderr, "[pair D=%d mode=%d] active CTAs %d, tiles/CTA(stream0) %.1f | per tile: q %.0f kfull %.0f sfull %.0f ld %.0f math %.0f tail %.0f cycles\n",
+                D, MODE, n, tiles, s[0] / n / tiles, s[1] / n / tiles, s[2] / n / tiles, s[3] / n / tiles, s[4] / n / tiles, s[5] / n / tiles);
+        fprintf(stderr, "    producer: wait k_empty %.0f of %.0f per tile | issuer: wait k_full %.0f, wait t_full %.0f of %.0f per tile\n",
+                s[8] / n / tiles, s[9] / n / tiles, s[10] / n / tiles, s[11] / n / tiles, s[12] / n / tiles);
+        fprintf(stderr, "    TMA issue -> k_full observed (only when the epilogue had to wait): %.0f cycles avg over %.0f%% of tiles\n",
+                s[14] > 0 ? s[13] / s[14] : 0.0, 100.0 * s[14] / s[6]);
+      }
+    }
+  }
   return MUSCLE_OK;
 }
 
@@ -249,7 +283,7 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
   p.ehat = static_cast<const __nv_bfloat16*>(ehat); p.bits = bits; p.inv_norm = inv_norm;
   p.perm = perm; p.part = part; p.unit_off = unit_off; p.rows_pad = rows_pad;
   p.n_row_blocks = static_cast<int>(rows_pad / rows_per_block(dim));
-  p.n_col_tiles = static_cast<int>(cols_pad / 128); p.n_ctas = device_info().sm_count;
+  p.n_col_tiles = static_cast<int>(cols_pad / 128); p.n_ctas = pair_grid();
   p.n = batch * pixels_per_image; p.ppi = pixels_per_image; p.C = num_classes;
   p.class_sum = class_sum; p.class_mass = class_mass; p.gpos = gpos; p.dproto = dproto;
   p.loss_acc = loss_acc; p.inv_tau = 1.f / temperature; p.layout = layout; p.dx = dx;
@@ -261,7 +295,7 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
   {                                                                                             \
     MB_CUDA(cudaFuncSetAttribute(final_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                  static_cast<int>(SORT_CHUNK * (DD + 1) * sizeof(float))));     \
-    final_kernel<DD><<<grid, SORT_CHUNK, smem, stream>>>(p);                                    \
+    final_kernel<DD><<<grid, FINAL_THREADS, smem, stream>>>(p);                                    \
   }
   if (dim == 64) MB_FINAL(64) else if (dim == 128) MB_FINAL(128) else MB_FINAL(256)
 #undef MB_FINAL

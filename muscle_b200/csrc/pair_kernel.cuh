@@ -54,9 +54,10 @@ struct PairParams {
   int n_row_blocks;          // row blocks of RB rows
   int n_col_tiles;           // column tiles of 128
   int rows_pad;
+  unsigned long long* dbg;   // optional [gridDim.x][16] cycle counters (MUSCLE_PAIR_TIMING), else null
 };
 
-constexpr int PAIR_SLOTS = 4;             // a row block is shared by at most this many CTAs
+constexpr int PAIR_SLOTS = 8;             // a row block is shared by at most this many CTAs
 constexpr uint32_t ITEM_END = 0xffffffffu;
 
 // live units per CTA: an even share, but never so small that a row block spans > PAIR_SLOTS CTAs
@@ -82,7 +83,7 @@ struct PairCfg {
   static constexpr int SMEM_BAR = SMEM_W + NST * 512;
   static constexpr int NBAR = 2 * NST + 14;
   static constexpr int SMEM_INFO = SMEM_BAR + NBAR * 8;  // item headers [2][4], stage info [NST]
-  static constexpr int SMEM_TMEMPTR = SMEM_INFO + (8 + NST) * 4;
+  static constexpr int SMEM_TMEMPTR = SMEM_INFO + (8 + NST) * 4 + NST * 4;   // + debug: TMA issue clocks [NST]
   static constexpr int SMEM_BYTES = SMEM_TMEMPTR + 16 + 1024;  // +1024: manual 1024-B alignment
   static constexpr int ACC_COL = 256;
   static constexpr int THREADS = 320;
@@ -305,6 +306,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         rb = lo;
       }
       uint32_t gcnt = 0, it = 0;
+      long long p_wait = 0, p_t0 = p.dbg ? clock64() : 0;
       while (u < u1) {
         const uint32_t U0 = __ldg(p.unit_off + rb), U1 = __ldg(p.unit_off + rb + 1);
         if (U1 <= u) { ++rb; continue; }   // row blocks without live units
@@ -332,8 +334,11 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           if (dead(tc)) continue;
           if (li++ < a) continue;
           const int st = gcnt % NST;
-          mbar_wait(k_empty(st), ((gcnt / NST) & 1) ^ 1);
+          { const long long w0 = p.dbg ? clock64() : 0;
+            mbar_wait(k_empty(st), ((gcnt / NST) & 1) ^ 1);
+            if (p.dbg) p_wait += clock64() - w0; }
           info[8 + st] = tc;
+          if (p.dbg) info[8 + NST + st] = static_cast<uint32_t>(clock64());
           mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES + 512 + (MODE == MODE_GRAD ? 512 : 0));
           for (int pa = 0; pa < C::NPANEL; ++pa)
             tma_load_2d(k_smem + st * C::TILE_BYTES + pa * C::PANEL_BYTES, &tm_col, k_full(st),
@@ -348,6 +353,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         u = U0 + e;
         ++it;
       }
+      if (p.dbg) { p.dbg[blockIdx.x * 16 + 8] = p_wait; p.dbg[blockIdx.x * 16 + 9] = clock64() - p_t0; }
       mbar_wait(q_empty, (it & 1) ^ 1);
       info[4 * (it & 1) + 0] = ITEM_END;
       mbar_arrive(q_full);
@@ -361,6 +367,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
       constexpr uint32_t IDESC_G = umma_idesc_bf16(128, D, 0, 1);
       uint32_t gbase = 0;
       uint32_t cnt_t[2][2] = {{0, 0}, {0, 0}};
+      long long i_kfull = 0, i_tfull = 0, i_t0 = p.dbg ? clock64() : 0;
       for (uint32_t it = 0;; ++it) {
         mbar_wait(q_full, it & 1);
         tc_fence_after();
@@ -378,7 +385,9 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         auto issue_S = [&](int g, int k, int h) {
           uint32_t par;
           const int st = stage_of(g, k, par);
-          mbar_wait(k_full(st), par);
+          { const long long w0 = p.dbg ? clock64() : 0;
+            mbar_wait(k_full(st), par);
+            if (p.dbg) i_kfull += clock64() - w0; }
           tc_fence_after();
           const uint32_t a_base = q_smem + (QT == 2 ? g * C::TILE_BYTES : 0);
           const uint32_t b_base = k_smem + st * C::TILE_BYTES + h * 8192;
@@ -409,7 +418,9 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
               if (k >= nk[g]) continue;
               const bool more = (k + 1 < nk[g]);
               // GRAD: T_h is stored; ROWSUM: S_h has been consumed (also guards the next item's prologue)
-              mbar_wait(t_full(g, h), cnt_t[g][h] & 1);
+              { const long long w0 = p.dbg ? clock64() : 0;
+                mbar_wait(t_full(g, h), cnt_t[g][h] & 1);
+                if (p.dbg) i_tfull += clock64() - w0; }
               tc_fence_after();
               ++cnt_t[g][h];
               if (MODE == MODE_GRAD) {
@@ -445,6 +456,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         }
         gbase += n;
       }
+      if (p.dbg) { p.dbg[blockIdx.x * 16 + 10] = i_kfull; p.dbg[blockIdx.x * 16 + 11] = i_tfull; p.dbg[blockIdx.x * 16 + 12] = clock64() - i_t0; }
     }
   } else {
     // ------------------------------------------------------------ epilogue groups
@@ -453,8 +465,12 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
     const uint32_t lane_addr = static_cast<uint32_t>(wq * 32) << 16;
     const float a = p.scale_log2;
     uint32_t gbase = 0, cnt = 0;
+    const bool timing = (p.dbg != nullptr) && warp == 0 && lane == 0;
+    long long t_lat = 0, n_lat = 0, t_kfull = 0, t_sfull = 0, t_ld = 0, t_math = 0, t_q = 0, t_tail = 0, t_mark = timing ? clock64() : 0;
+    auto lap = [&](long long& acc) { if (timing) { const long long t = clock64(); acc += t - t_mark; t_mark = t; } };
     for (uint32_t it = 0;; ++it) {
       mbar_wait(q_full, it & 1);
+      lap(t_q);
       const uint32_t n_u = info[4 * (it & 1) + 0];
       if (n_u == ITEM_END) break;
       const int n = static_cast<int>(n_u);
@@ -474,12 +490,17 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
       for (int k = 0; k < my_n; ++k, ++cnt) {
         const uint32_t gg = gbase + tile_of(g, k);
         const int st = gg % NST;
-        mbar_wait(k_full(st), (gg / NST) & 1);
+        { const long long w0 = timing ? clock64() : 0;
+          mbar_wait(k_full(st), (gg / NST) & 1);
+          if (timing) { const long long w1 = clock64();
+            if (w1 - w0 > 100) { t_lat += static_cast<uint32_t>(static_cast<uint32_t>(w1) - info[8 + NST + st]); ++n_lat; } } }
+        lap(t_kfull);
         const uint32_t tor_c = info[8 + st];
         const bool full = tile_pair_full(tor_r, tor_c);
 #pragma unroll 1
         for (int h = 0; h < 2; ++h) {
           mbar_wait(s_full(g, h), cnt & 1);
+          lap(t_sfull);
           tc_fence_after();
           const uint32_t s_addr = tmem + lane_addr + g * 128 + h * 64;
           const uint8_t* bsm = smem_gen + C::SMEM_BITS + st * 512 + h * 256;
@@ -488,6 +509,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           tmem_ld32(s_addr, v[0]);
           tmem_ld32(s_addr + 32, v[1]);
           tmem_wait_ld();
+          lap(t_ld);
           if (MODE == MODE_ROWSUM) {  // S_h is in registers: hand the buffer back before the math
             tc_fence_before();
             __syncwarp();
@@ -503,6 +525,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
             __syncwarp();
             if (lane == 0) mbar_arrive(t_full(g, h));
           }
+          lap(t_math);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(k_empty(st));
@@ -535,7 +558,12 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         __syncwarp();
         if (lane == 0) mbar_arrive(acc_empty(acc));
       }
+      lap(t_tail);
       gbase += n;
+    }
+    if (timing) {
+      unsigned long long* d = p.dbg + blockIdx.x * 16;
+      d[0] = t_q; d[1] = t_kfull; d[2] = t_sfull; d[3] = t_ld; d[4] = t_math; d[5] = t_tail; d[6] = cnt; d[13] = t_lat; d[14] = n_lat;
     }
   }
 

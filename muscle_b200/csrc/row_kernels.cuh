@@ -377,15 +377,20 @@ struct FinalParams {
   float* loss_out;
 };
 
-// One block = 128 consecutive source pixels (the chunks of prepare_kernel), one warp = 32.
-// Per pixel the warp gathers its sorted row (lane holds channels lane, lane+32, ...), forms
+// One block = 128 consecutive source pixels, 16 warps of 8 pixels each (two pixels in flight per
+// warp, so the dependent gather -> reduce -> store chains of different pixels overlap).  Per pixel
+// the warp gathers its sorted row (lane holds channels lane, lane+32, ...), forms
 //   g = 1/n_valid (1/tau sum_slots part + gpos/mass class_sum_c + dproto_c/mass),
 //   dx = inv_norm (g - e (g.e))
-// and writes it back in the caller's layout (NCHW through a shared-memory transpose).
+// and writes it back in the caller's layout (NCHW through a shared-memory transpose, so the global
+// stores are coalesced along the pixel index).
+constexpr int FINAL_THREADS = 512;
+constexpr int FINAL_ROWS_PER_WARP = SORT_CHUNK / (FINAL_THREADS / 32);
+
 template <int D>
-__global__ void __launch_bounds__(SORT_CHUNK) final_kernel(const FinalParams p) {
+__global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams p) {
   constexpr int EPL = D / 32;
-  extern __shared__ float smem_f[];  // NCHW only: [SORT_WARPS][32][D+1]
+  extern __shared__ float smem_f[];  // NCHW only: [SORT_CHUNK][D+1]
   __shared__ float n_valid_sh;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -400,63 +405,72 @@ __global__ void __launch_bounds__(SORT_CHUNK) final_kernel(const FinalParams p) 
   const float inv_n = n_valid_sh > 0.f ? 1.f / n_valid_sh : 0.f;
   constexpr int RB = (D == 256) ? 128 : 256;  // rows per row block of the pair passes
   const uint32_t per = pair_units_per_cta(__ldg(p.unit_off + p.n_row_blocks), p.n_ctas, p.n_col_tiles);
-  const long long n0 = static_cast<long long>(blockIdx.x) * SORT_CHUNK + warp * 32;
-  if (n0 >= p.n) return;
-  const long long i = n0 + lane;
-  const bool live = i < p.n;
-  const int my_q = live ? p.perm[i] : 0;
-  const int n_live = static_cast<int>(min(32ll, p.n - n0));
-  float* tile = smem_f + warp * 32 * (D + 1);
-  for (int r = 0; r < n_live; ++r) {
-    const long long q = __shfl_sync(0xffffffffu, my_q, r);
+  const long long blk0 = static_cast<long long>(blockIdx.x) * SORT_CHUNK;
+
+  auto row_grad = [&](long long i, float (&g)[EPL]) {   // i = source pixel (< p.n)
+    const long long q = p.perm[i];
     const uint32_t bq = __ldg(p.bits + q);
-    float g[EPL];
 #pragma unroll
     for (int k = 0; k < EPL; ++k) g[k] = 0.f;
-    if (bq) {
-      const int c = class_of_bits(bq);
-      // the row block's live units were shared by CTAs U0/per .. (U1-1)/per, one slot each
-      const int rbk = static_cast<int>(q / RB);
-      const uint32_t U0 = __ldg(p.unit_off + rbk), U1 = __ldg(p.unit_off + rbk + 1);
-      const int n_slots = (U1 > U0) ? static_cast<int>((U1 - 1) / per - U0 / per + 1) : 0;
-      for (int s = 0; s < n_slots; ++s) {
-        const float* src = p.part + (static_cast<long long>(s) * p.rows_pad + q) * D + lane;
+    if (!bq) return;
+    const int c = class_of_bits(bq);
+    // the row block's live units were shared by CTAs U0/per .. (U1-1)/per, one slot each
+    const int rbk = static_cast<int>(q / RB);
+    const uint32_t U0 = __ldg(p.unit_off + rbk), U1 = __ldg(p.unit_off + rbk + 1);
+    const int n_slots = (U1 > U0) ? static_cast<int>((U1 - 1) / per - U0 / per + 1) : 0;
+    for (int s = 0; s < n_slots; ++s) {
+      const float* src = p.part + (static_cast<long long>(s) * p.rows_pad + q) * D + lane;
 #pragma unroll
-        for (int k = 0; k < EPL; ++k) g[k] += __ldg(src + 32 * k);
-      }
-      const float inv_mass = 1.f / __ldg(p.class_mass + c);
-      const float gq = __ldg(p.gpos + q) * inv_mass;
-      float e[EPL];
-      float dot = 0.f;
-#pragma unroll
-      for (int k = 0; k < EPL; ++k) {
-        const int d = lane + 32 * k;
-        e[k] = __bfloat162float(p.ehat[q * D + d]);
-        g[k] = inv_n * (p.inv_tau * g[k] + gq * __ldg(p.class_sum + c * D + d) +
-                        inv_mass * __ldg(p.dproto + c * D + d));
-        dot = fmaf(g[k], e[k], dot);
-      }
-      dot = warp_sum(dot);
-      const float inv = __ldg(p.inv_norm + q);
-#pragma unroll
-      for (int k = 0; k < EPL; ++k) g[k] = inv * (g[k] - e[k] * dot);
+      for (int k = 0; k < EPL; ++k) g[k] += __ldg(src + 32 * k);
     }
+    const float inv_mass = 1.f / __ldg(p.class_mass + c);
+    const float gq = __ldg(p.gpos + q) * inv_mass;
+    float e[EPL];
+    float dot = 0.f;
+#pragma unroll
+    for (int k = 0; k < EPL; ++k) {
+      const int d = lane + 32 * k;
+      e[k] = __bfloat162float(p.ehat[q * D + d]);
+      g[k] = inv_n * (p.inv_tau * g[k] + gq * __ldg(p.class_sum + c * D + d) + inv_mass * __ldg(p.dproto + c * D + d));
+      dot = fmaf(g[k], e[k], dot);
+    }
+    dot = warp_sum(dot);
+    const float inv = __ldg(p.inv_norm + q);
+#pragma unroll
+    for (int k = 0; k < EPL; ++k) g[k] = inv * (g[k] - e[k] * dot);
+  };
+
+#pragma unroll 1
+  for (int r = 0; r < FINAL_ROWS_PER_WARP; r += 2) {
+    const int l0 = warp * FINAL_ROWS_PER_WARP + r, l1 = l0 + 1;   // local pixel index within the block
+    const long long i0 = blk0 + l0, i1 = blk0 + l1;
+    float g0[EPL], g1[EPL];
+    if (i0 < p.n) row_grad(i0, g0);
+    if (i1 < p.n) row_grad(i1, g1);
     if (p.layout == MUSCLE_LAYOUT_NCHW) {
 #pragma unroll
-      for (int k = 0; k < EPL; ++k) tile[r * (D + 1) + lane + 32 * k] = g[k];
+      for (int k = 0; k < EPL; ++k) {
+        if (i0 < p.n) smem_f[l0 * (D + 1) + lane + 32 * k] = g0[k];
+        if (i1 < p.n) smem_f[l1 * (D + 1) + lane + 32 * k] = g1[k];
+      }
     } else {
-      float* dst = p.dx + (n0 + r) * D + lane;
 #pragma unroll
-      for (int k = 0; k < EPL; ++k) dst[32 * k] = g[k];
+      for (int k = 0; k < EPL; ++k) {
+        if (i0 < p.n) p.dx[i0 * D + lane + 32 * k] = g0[k];
+        if (i1 < p.n) p.dx[i1 * D + lane + 32 * k] = g1[k];
+      }
     }
   }
   if (p.layout == MUSCLE_LAYOUT_NCHW) {
-    __syncwarp();
-    if (live) {
+    __syncthreads();
+    // thread -> (pixel = tid % 128, channel group = tid / 128): consecutive threads write consecutive pixels
+    const int px = threadIdx.x & (SORT_CHUNK - 1);
+    const long long i = blk0 + px;
+    if (i < p.n) {
       const long long b = i / p.ppi;
       float* dst = p.dx + (b * D) * p.ppi + (i - b * p.ppi);
-#pragma unroll 8
-      for (int d = 0; d < D; ++d) dst[static_cast<long long>(d) * p.ppi] = tile[lane * (D + 1) + d];
+      for (int d = threadIdx.x / SORT_CHUNK; d < D; d += FINAL_THREADS / SORT_CHUNK)
+        dst[static_cast<long long>(d) * p.ppi] = smem_f[px * (D + 1) + d];
     }
   }
 }

@@ -235,70 +235,84 @@ __global__ void pixpro_final_kernel(const double* acc, int batch, float* loss) {
 // =============================================================================================
 // a9  CAM head  relu(sum_ch p7 * W)  (src/MuSCLe.py:242-247),  a10 GAP + logits (:240-241)
 // =============================================================================================
-constexpr int CAM_THREADS = 128;
-constexpr int CAM_PX = 4;  // pixels per thread (one float4)
+constexpr int CAM_PXT = 64;     // pixel-threads per block (2 pixels each -> 128 pixels per block)
+constexpr int CAM_SLICES = 8;   // channel slices per block (one warp pair per slice)
+constexpr int CAM_THREADS = CAM_PXT * CAM_SLICES;
+constexpr int CAM_PX = 2;
 
-// cam[b,k,p] = relu(sum_c W[k,c] p7[b,c,p]).  Thread = 4 consecutive pixels; W transposed in smem
-// as [c][KP] so a channel's weights are one broadcast LDS.128 run.  P % 4 == 0 fast path, scalar tail
-// handled by clamping (loads repeat the last valid pixel, stores are guarded).
+// cam[b,k,p] = relu(sum_c W[k,c] p7[b,c,p]).  Thread = (2 consecutive pixels, channel slice): it
+// accumulates the 21 class sums over its channels, the slices are then reduced through shared
+// memory.  W is transposed in smem as [c][KP] so a channel's weights are broadcast LDS.128 runs.
+// Splitting the channels (not only the pixels) over threads keeps every SM busy at feature-map
+// sizes where pixels alone give < 1 warp per SM-quarter.
 template <int KP>
 __global__ void __launch_bounds__(CAM_THREADS) cam_head_fwd_kernel(const float* p7, const float* w, int ch, int P,
                                                                    int K, float* cam) {
-  extern __shared__ float wsm[];  // [ch][KP]
+  extern __shared__ float wsm[];            // [ch][KP] | red [CAM_SLICES][KP][128]
+  float* red = wsm + static_cast<size_t>(ch) * KP;
   const int b = blockIdx.y;
   for (int i = threadIdx.x; i < ch * KP; i += blockDim.x) {
     const int c = i / KP, k = i - c * KP;
     wsm[i] = (k < K) ? w[static_cast<size_t>(k) * ch + c] : 0.f;
   }
   __syncthreads();
-  const int p0 = (blockIdx.x * CAM_THREADS + threadIdx.x) * CAM_PX;
-  if (p0 >= P) return;
-  const bool vec = (P % 4 == 0);
+  const int pt = threadIdx.x % CAM_PXT, slice = threadIdx.x / CAM_PXT;
+  const int p0 = (blockIdx.x * CAM_PXT + pt) * CAM_PX;
+  const bool vec = (P % 2 == 0);
   float acc[CAM_PX][KP];
 #pragma unroll
   for (int q = 0; q < CAM_PX; ++q)
 #pragma unroll
     for (int k = 0; k < KP; ++k) acc[q][k] = 0.f;
-  const float* src = p7 + static_cast<size_t>(b) * ch * P;
-  for (int c = 0; c < ch; ++c) {
-    float v[CAM_PX];
-    if (vec) {
-      const float4 t = *reinterpret_cast<const float4*>(src + static_cast<size_t>(c) * P + p0);
-      v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-    } else {
+  if (p0 < P) {
+    const float* src = p7 + static_cast<size_t>(b) * ch * P;
+    const int c_lo = (ch * slice) / CAM_SLICES, c_hi = (ch * (slice + 1)) / CAM_SLICES;
+#pragma unroll 4
+    for (int c = c_lo; c < c_hi; ++c) {
+      float v[CAM_PX];
+      if (vec) {
+        const float2 t = *reinterpret_cast<const float2*>(src + static_cast<size_t>(c) * P + p0);
+        v[0] = t.x; v[1] = t.y;
+      } else {
+        v[0] = src[static_cast<size_t>(c) * P + p0];
+        v[1] = src[static_cast<size_t>(c) * P + min(p0 + 1, P - 1)];
+      }
+      const float4* wr = reinterpret_cast<const float4*>(wsm + c * KP);
 #pragma unroll
-      for (int q = 0; q < CAM_PX; ++q) v[q] = src[static_cast<size_t>(c) * P + min(p0 + q, P - 1)];
-    }
-    const float4* wr = reinterpret_cast<const float4*>(wsm + c * KP);
+      for (int k4 = 0; k4 < KP / 4; ++k4) {
+        const float4 ww = wr[k4];
 #pragma unroll
-    for (int k4 = 0; k4 < KP / 4; ++k4) {
-      const float4 ww = wr[k4];
-#pragma unroll
-      for (int q = 0; q < CAM_PX; ++q) {
-        acc[q][k4 * 4 + 0] = fmaf(v[q], ww.x, acc[q][k4 * 4 + 0]);
-        acc[q][k4 * 4 + 1] = fmaf(v[q], ww.y, acc[q][k4 * 4 + 1]);
-        acc[q][k4 * 4 + 2] = fmaf(v[q], ww.z, acc[q][k4 * 4 + 2]);
-        acc[q][k4 * 4 + 3] = fmaf(v[q], ww.w, acc[q][k4 * 4 + 3]);
+        for (int q = 0; q < CAM_PX; ++q) {
+          acc[q][k4 * 4 + 0] = fmaf(v[q], ww.x, acc[q][k4 * 4 + 0]);
+          acc[q][k4 * 4 + 1] = fmaf(v[q], ww.y, acc[q][k4 * 4 + 1]);
+          acc[q][k4 * 4 + 2] = fmaf(v[q], ww.z, acc[q][k4 * 4 + 2]);
+          acc[q][k4 * 4 + 3] = fmaf(v[q], ww.w, acc[q][k4 * 4 + 3]);
+        }
       }
     }
   }
+  // red[slice][k][pixel-in-block]
+#pragma unroll
+  for (int k = 0; k < KP; ++k)
+#pragma unroll
+    for (int q = 0; q < CAM_PX; ++q) red[(slice * KP + k) * (CAM_PXT * CAM_PX) + pt * CAM_PX + q] = acc[q][k];
+  __syncthreads();
   float* dst = cam + static_cast<size_t>(b) * K * P;
+  const int pb = blockIdx.x * CAM_PXT * CAM_PX;
+  for (int i = threadIdx.x; i < K * CAM_PXT * CAM_PX; i += blockDim.x) {
+    const int k = i / (CAM_PXT * CAM_PX), px = i - k * (CAM_PXT * CAM_PX);
+    if (pb + px >= P) continue;
+    float sum = 0.f;
 #pragma unroll
-  for (int k = 0; k < KP; ++k) {
-    if (k >= K) break;
-    if (vec) {
-      *reinterpret_cast<float4*>(dst + static_cast<size_t>(k) * P + p0) =
-          make_float4(fmaxf(acc[0][k], 0.f), fmaxf(acc[1][k], 0.f), fmaxf(acc[2][k], 0.f), fmaxf(acc[3][k], 0.f));
-    } else {
-#pragma unroll
-      for (int q = 0; q < CAM_PX; ++q)
-        if (p0 + q < P) dst[static_cast<size_t>(k) * P + p0 + q] = fmaxf(acc[q][k], 0.f);
-    }
+    for (int sl = 0; sl < CAM_SLICES; ++sl) sum += red[(sl * KP + k) * (CAM_PXT * CAM_PX) + px];
+    dst[static_cast<size_t>(k) * P + pb + px] = fmaxf(sum, 0.f);
   }
 }
 
 // dp7[b,c,p] = sum_k W[k,c] dcam[b,k,p] [cam[b,k,p] > 0]  (+ demb[b,c] / P when demb != null:
 // the GAP backward, so p7's gradient is written once).  No gradient reaches W (fc.weight.data).
+// Thread = (2 consecutive pixels, channel slice): the gated CAM gradients of its pixels stay in
+// registers, it writes its slice of the channels.
 template <int KP>
 __global__ void __launch_bounds__(CAM_THREADS) cam_head_bwd_kernel(const float* dcam, const float* cam,
                                                                    const float* w, const float* demb, int ch,
@@ -310,9 +324,10 @@ __global__ void __launch_bounds__(CAM_THREADS) cam_head_bwd_kernel(const float* 
     wsm[i] = (k < K) ? w[static_cast<size_t>(k) * ch + c] : 0.f;
   }
   __syncthreads();
-  const int p0 = (blockIdx.x * CAM_THREADS + threadIdx.x) * CAM_PX;
+  const int pt = threadIdx.x % CAM_PXT, slice = threadIdx.x / CAM_PXT;
+  const int p0 = (blockIdx.x * CAM_PXT + pt) * CAM_PX;
   if (p0 >= P) return;
-  const bool vec = (P % 4 == 0);
+  const bool vec = (P % 2 == 0);
   float g[CAM_PX][KP];
 #pragma unroll
   for (int k = 0; k < KP; ++k) {
@@ -328,9 +343,11 @@ __global__ void __launch_bounds__(CAM_THREADS) cam_head_bwd_kernel(const float* 
   }
   const float inv_p = 1.f / static_cast<float>(P);
   float* dst = dp7 + static_cast<size_t>(b) * ch * P;
-  for (int c = 0; c < ch; ++c) {
+  const int c_lo = (ch * slice) / CAM_SLICES, c_hi = (ch * (slice + 1)) / CAM_SLICES;
+#pragma unroll 2
+  for (int c = c_lo; c < c_hi; ++c) {
     const float base = demb ? demb[static_cast<size_t>(b) * ch + c] * inv_p : 0.f;
-    float o[CAM_PX] = {base, base, base, base};
+    float o[CAM_PX] = {base, base};
     const float4* wr = reinterpret_cast<const float4*>(wsm + c * KP);
 #pragma unroll
     for (int k4 = 0; k4 < KP / 4; ++k4) {
@@ -344,11 +361,10 @@ __global__ void __launch_bounds__(CAM_THREADS) cam_head_bwd_kernel(const float* 
       }
     }
     if (vec) {
-      *reinterpret_cast<float4*>(dst + static_cast<size_t>(c) * P + p0) = make_float4(o[0], o[1], o[2], o[3]);
+      *reinterpret_cast<float2*>(dst + static_cast<size_t>(c) * P + p0) = make_float2(o[0], o[1]);
     } else {
-#pragma unroll
-      for (int q = 0; q < CAM_PX; ++q)
-        if (p0 + q < P) dst[static_cast<size_t>(c) * P + p0 + q] = o[q];
+      dst[static_cast<size_t>(c) * P + p0] = o[0];
+      if (p0 + 1 < P) dst[static_cast<size_t>(c) * P + p0 + 1] = o[1];
     }
   }
 }
@@ -611,12 +627,12 @@ int muscle_cam_head_fwd(const float* p7, const float* fc_weight, int batch, int 
   if (int rc = need_sm100()) return rc;
   if (!p7 || !fc_weight || !cam_out) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (batch <= 0 || channels <= 0 || pixels <= 0 || num_classes <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty input");
-  if ((reinterpret_cast<uintptr_t>(p7) | reinterpret_cast<uintptr_t>(cam_out)) & 15)
-    return fail(MUSCLE_ERR_BAD_ARG, "feature maps must be 16-byte aligned");
-  const dim3 grid((pixels + CAM_THREADS * CAM_PX - 1) / (CAM_THREADS * CAM_PX), batch);
+  if ((reinterpret_cast<uintptr_t>(p7) | reinterpret_cast<uintptr_t>(cam_out)) & 7)
+    return fail(MUSCLE_ERR_BAD_ARG, "feature maps must be 8-byte aligned");
+  const dim3 grid((pixels + CAM_PXT * CAM_PX - 1) / (CAM_PXT * CAM_PX), batch);
   return dispatch_kp(num_classes, [&](auto kp) -> int {
     constexpr int KP = decltype(kp)::value;
-    const size_t smem = static_cast<size_t>(channels) * KP * sizeof(float);
+    const size_t smem = (static_cast<size_t>(channels) * KP + static_cast<size_t>(CAM_SLICES) * KP * CAM_PXT * CAM_PX) * sizeof(float);
     if (smem > 200 * 1024) return fail(MUSCLE_ERR_BAD_ARG, "too many channels (%d) for the CAM head", channels);
     MB_CUDA(cudaFuncSetAttribute(cam_head_fwd_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     cam_head_fwd_kernel<KP><<<grid, CAM_THREADS, smem, stream>>>(p7, fc_weight, channels, pixels, num_classes, cam_out);
@@ -631,8 +647,8 @@ int muscle_cam_head_bwd(const float* dcam, const float* cam, const float* fc_wei
   if (int rc = need_sm100()) return rc;
   if (!fc_weight || !dp7_out || (dcam && !cam)) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (batch <= 0 || channels <= 0 || pixels <= 0 || num_classes <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty input");
-  if (reinterpret_cast<uintptr_t>(dp7_out) & 15) return fail(MUSCLE_ERR_BAD_ARG, "feature maps must be 16-byte aligned");
-  const dim3 grid((pixels + CAM_THREADS * CAM_PX - 1) / (CAM_THREADS * CAM_PX), batch);
+  if (reinterpret_cast<uintptr_t>(dp7_out) & 7) return fail(MUSCLE_ERR_BAD_ARG, "feature maps must be 8-byte aligned");
+  const dim3 grid((pixels + CAM_PXT * CAM_PX - 1) / (CAM_PXT * CAM_PX), batch);
   return dispatch_kp(num_classes, [&](auto kp) -> int {
     constexpr int KP = decltype(kp)::value;
     const size_t smem = static_cast<size_t>(channels) * KP * sizeof(float);

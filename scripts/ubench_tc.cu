@@ -10,7 +10,8 @@
 using namespace mb200;
 
 // mode 0: SS M128 N64 K16 ; 1: SS M128 N128 ; 2: TS M128 N128 ; 3: SS N=256
-__global__ void __launch_bounds__(128, 1) mma_bench(int mode, int reps, long long* out) {
+template <int mode>
+__global__ void __launch_bounds__(128, 1) mma_bench(int reps, long long* out) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   __shared__ uint32_t tptr;
@@ -27,7 +28,8 @@ __global__ void __launch_bounds__(128, 1) mma_bench(int mode, int reps, long lon
   __syncthreads();
   if (warp == 1) {
     if (elect_one()) {
-      const int N = (mode == 0) ? 64 : (mode == 3 ? 256 : 128);
+      const int N = (mode == 0 || mode >= 4) ? 64 : (mode == 3 ? 256 : 128);
+      const uint32_t idesc_ts64 = umma_idesc_bf16(128, 64, 0, 0);
       const uint32_t idesc_ss = umma_idesc_bf16(128, N, 0, 0);
       const uint32_t idesc_ts = umma_idesc_bf16(128, 128, 0, 1);
       const uint32_t a_smem = base, b_smem = base + 32768;
@@ -38,6 +40,13 @@ __global__ void __launch_bounds__(128, 1) mma_bench(int mode, int reps, long lon
           const uint32_t off = (kk >> 2) * 16384 + (kk & 3) * 32;
           if (mode == 2)
             mma_ts(tmem + 256, tmem + kk * 8, umma_desc_sw128(b_smem + kk * 2048, 16384, 1024), idesc_ts, 1);
+          else if (mode == 4)   // S from a TMEM-resident row tile: A in TMEM, B K-major N=64
+            mma_ts(tmem + 256, tmem + kk * 8, umma_desc_sw128(b_smem + off, 16, 1024), idesc_ts64, kk > 0);
+          else if (mode == 5)   // SS N=64, consecutive MMAs on alternating accumulators
+            mma_ss(tmem + (kk & 1) * 64, umma_desc_sw128(a_smem + off, 16, 1024), umma_desc_sw128(b_smem + off, 16, 1024), idesc_ss, kk > 1);
+          else if (mode == 6)   // TS N=64 K-major B followed by TS N=128 MN-major B (the gradient pass mix)
+            { mma_ts(tmem + 256, tmem + kk * 8, umma_desc_sw128(b_smem + off, 16, 1024), idesc_ts64, kk > 0);
+              if (kk < 4) mma_ts(tmem + 384, tmem + 64 + kk * 8, umma_desc_sw128(b_smem + kk * 2048, 16384, 1024), idesc_ts, 1); }
           else
             mma_ss(tmem, umma_desc_sw128(a_smem + off, 16, 1024), umma_desc_sw128(b_smem + off, 16, 1024), idesc_ss, kk > 0);
         }
@@ -107,12 +116,27 @@ __global__ void __launch_bounds__(256, 1) alu_bench(int mode, int reps, float se
 int main() {
   long long* out; float* sink;
   cudaMallocManaged(&out, 64); cudaMalloc(&sink, 64);
-  cudaFuncSetAttribute(mma_bench, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-  const char* names[4] = {"SS M128 N64 K16", "SS M128 N128 K16", "TS M128 N128 K16", "SS M128 N256 K16"};
-  for (int mode = 0; mode < 4; ++mode) {
+  cudaFuncSetAttribute(mma_bench<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  cudaFuncSetAttribute(mma_bench<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  cudaFuncSetAttribute(mma_bench<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  cudaFuncSetAttribute(mma_bench<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  cudaFuncSetAttribute(mma_bench<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  cudaFuncSetAttribute(mma_bench<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  cudaFuncSetAttribute(mma_bench<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  const char* names[7] = {"SS M128 N64 K16", "SS M128 N128 K16", "TS M128 N128 K16", "SS M128 N256 K16",
+                          "TS M128 N64 Kmaj", "SS N64 alt-acc", "TS64x8+TS128x4 /8"};
+  for (int mode = 0; mode < 7; ++mode) {
     for (int grid : {1, 148}) {
-      const int reps = 64;
-      mma_bench<<<grid, 128, 100 * 1024>>>(mode, reps, out);
+      const int reps = 512;
+      switch (mode) {
+        case 0: mma_bench<0><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        case 1: mma_bench<1><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        case 2: mma_bench<2><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        case 3: mma_bench<3><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        case 4: mma_bench<4><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        case 5: mma_bench<5><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        default: mma_bench<6><<<grid, 128, 100 * 1024>>>(reps, out); break;
+      }
       cudaError_t e = cudaDeviceSynchronize();
       if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
       printf("%-18s grid %3d: issue %.1f cyc/mma, complete %.1f cyc/mma\n", names[mode], grid,
