@@ -32,7 +32,7 @@ int pair_grid() {
 template <int D, int MODE, int POLY>
 int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, int64_t cols_pad,
                 PairParams prm, cudaStream_t stream) {
-  using C = PairCfg<D>;
+  using C = PairCfg<D, MODE>;
   CUtensorMap tm_row, tm_col;
   int rc = make_bf16_tile_map(&tm_row, ehat_rows, rows_pad, D);
   if (rc) return rc;
@@ -47,6 +47,8 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
   const int grid = pair_grid();  // one persistent CTA per SM; shares come from unit_off
   static const bool timing = getenv("MUSCLE_PAIR_TIMING") != nullptr;   // debug: per-phase cycle counters
   static unsigned long long* dbg = nullptr;
+  static const int flags = getenv("MUSCLE_PAIR_FLAGS") ? atoi(getenv("MUSCLE_PAIR_FLAGS")) : 0;
+  prm.dbg_flags = flags;
   if (timing) {
     if (!dbg) cudaMalloc(&dbg, grid * 16 * sizeof(unsigned long long));
     cudaMemsetAsync(dbg, 0, grid * 16 * sizeof(unsigned long long), stream);
@@ -66,12 +68,10 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
         if (h[c * 16 + 6]) { for (int k = 0; k < 15; ++k) s[k] += double(h[c * 16 + k]); ++n; }
       if (n) {
         const double tiles = s[6] / n;
-        fprintf(stderr, "[pair D=%d mode=%d] active CTAs %d, tiles/CTA(stream0) %.1f | per tile: q %.0f kfull %.0f sfull %.0f ld %.0f math %.0f tail %.0f cycles\n",
+        fprintf(stderr, "[pair D=%d mode=%d] active CTAs %d, units/CTA (group 0) %.1f | per own unit: q %.0f kfull %.0f sfull %.0f ld %.0f math %.0f tail %.0f cycles\n",
                 D, MODE, n, tiles, s[0] / n / tiles, s[1] / n / tiles, s[2] / n / tiles, s[3] / n / tiles, s[4] / n / tiles, s[5] / n / tiles);
-        fprintf(stderr, "    producer: wait k_empty %.0f of %.0f per tile | issuer: wait k_full %.0f, wait t_full %.0f of %.0f per tile\n",
-                s[8] / n / tiles, s[9] / n / tiles, s[10] / n / tiles, s[11] / n / tiles, s[12] / n / tiles);
-        fprintf(stderr, "    TMA issue -> k_full observed (only when the epilogue had to wait): %.0f cycles avg over %.0f%% of tiles\n",
-                s[14] > 0 ? s[13] / s[14] : 0.0, 100.0 * s[14] / s[6]);
+        fprintf(stderr, "    producer: wait k_empty %.0f of %.0f per unit | issuer: wait k_full %.0f, wait t_full %.0f of %.0f per unit\n",
+                s[8] / n / tiles / 2, s[9] / n / tiles / 2, s[10] / n / tiles / 2, s[11] / n / tiles / 2, s[12] / n / tiles / 2);
       }
     }
   }
@@ -102,7 +102,7 @@ int launch_pair_dim(int dim, bool poly, const void* ehat_rows, int64_t rows_pad,
   return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
 }
 
-int rows_per_block(int dim) { return dim == 256 ? 128 : 256; }
+int rows_per_block(int) { return PAIR_RB; }
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -233,8 +233,7 @@ int muscle_infonce_plan(const uint32_t* tor_rows, int64_t rows_pad, const uint32
   const int n_col_tiles = static_cast<int>(cols_pad / 128);
   if (static_cast<double>(n_row_blocks) * n_col_tiles >= 4.0e9)
     return fail(MUSCLE_ERR_BAD_ARG, "too many tile units for one rank");
-  if (dim == 256) pair_plan_kernel<1><<<1, 1024, 0, stream>>>(tor_rows, n_row_blocks, tor_cols, n_col_tiles, unit_off);
-  else pair_plan_kernel<2><<<1, 1024, 0, stream>>>(tor_rows, n_row_blocks, tor_cols, n_col_tiles, unit_off);
+  pair_plan_kernel<1><<<1, 1024, 0, stream>>>(tor_rows, n_row_blocks, tor_cols, n_col_tiles, unit_off);
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
 }

@@ -160,7 +160,7 @@ int muscle_info_nce_fwd_bwd(const float* query, const float* positive_keys, cons
                                F(W.gpos), reinterpret_cast<double*>(b + W.lacc), F(W.dproto), stream_)))
     return rc;
   const float scale = reduction_mean ? 1.f / static_cast<float>(Q) : 1.f;
-  const int rb = (dim == 256) ? 128 : 256;
+  const int rb = PAIR_RB;
   const int n_ctas = device_info().sm_count;
   if (dquery_out || row_loss_out) {
     if (dquery_out)

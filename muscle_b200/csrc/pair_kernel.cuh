@@ -1,35 +1,35 @@
 // The dense pixel-pair mainloop of the InfoNCE row-sum pass and the InfoNCE gradient pass.
 //
 // One persistent CTA per SM, warp-specialised:
-//   warps 0-3  epilogue group 0  (TMEM lanes 32*(warp%4) .. +31, thread = one row of a 128-row tile)
+//   warps 0-3  epilogue group 0  (TMEM lanes 32*(warp%4) .. +31, thread = one row of the 128-row tile)
 //   warps 4-7  epilogue group 1
-//   warp  8    TMA producer      (row tiles once per work item, column tiles through a ring)
+//   warp  8    TMA producer      (the row tile once per work item, column tiles through a ring)
 //   warp  9    tcgen05.mma issuer (one lane) + TMEM allocator
 //
 // Pixels arrive sorted by class (row_kernels.cuh), and a per-tile class union (`tor`) lets the
-// producer drop every (row block, column tile) whose pairs are all masked (same single class)
+// producer drop every (row tile, column tile) whose pairs are all masked (same single class)
 // before anything is loaded or multiplied; the epilogue takes a mask-free path for tiles whose
-// class sets are disjoint.  The LIVE (row block, column tile) units are numbered row block by row
-// block (`unit_off`, pair_plan_kernel) and every CTA takes one contiguous share of that range, so
-// the SMs finish together whatever the class mix; a CTA's share of one row block is a work item,
-// and the item's index among the CTAs that touch the row block is its output `slot`.
+// class sets are disjoint.  The LIVE (row tile, column tile) units are numbered row tile by row
+// tile (`unit_off`, pair_plan_kernel) and every CTA takes one contiguous share of that range, so
+// the SMs finish together whatever the class mix; a CTA's share of one row tile is a work item,
+// and the item's index among the CTAs that touch the row tile is its output `slot`.
 //
-// Two "streams" run through the tensor pipe, one per epilogue group (D <= 128: stream = row
-// tile, both see every column tile; D = 256: one row tile, the streams alternate column tiles).
-// Within a stream every 128 x 128 similarity tile is produced and consumed as two 64-column halves
-// held in two TMEM buffers, so the group's epilogue on one half always overlaps the stream's MMAs
-// on the other:
-//   S_h = R C_h^T      tcgen05.mma SS, bf16 x bf16 -> fp32 in TMEM            [128 x 64]
-//   epilogue           tcgen05.ld S_h, e = exp2(a*s - a), label mask, then
-//       MODE_ROWSUM : row-sum of e kept in registers, one atomicAdd per row per item
-//       MODE_GRAD   : T_h = e * (w_row + w_col) -> bf16 -> tcgen05.st over the S_h columns
-//   (MODE_GRAD) G += T_h C_h   tcgen05.mma TS: A = T_h from TMEM, B = the same column rows, MN-major
-// so the N x N logits never leave the SM.  A share of the exponentials is evaluated with a cubic on
-// the FMA pipe (ptx.cuh: ex2_poly2) because MUFU alone (16/clk/SM) would cap the pass below the
-// tensor pipe; all elementwise math is packed fp32x2.
+// A unit is one 128 x 128 similarity tile.  Its S = R C^T goes into one of NB TMEM buffers of
+// 128 columns (round robin over the CTA's units), the two epilogue groups take alternate units, so
+// while a group works on unit k the tensor pipe fills the buffers of units k+1 .. k+NB-1:
+//   S = R C^T          tcgen05.mma SS, bf16 x bf16 -> fp32 in TMEM            [128 x 128], N = 128
+//   epilogue           tcgen05.ld S (64 columns at a time), e = exp2(a*s - a), label mask, then
+//       MODE_ROWSUM : row-sum of e kept in registers, one atomicAdd per row per item and group
+//       MODE_GRAD   : T = e * (w_row + w_col) -> bf16 -> tcgen05.st over the first 64 columns of S
+//   (MODE_GRAD) G += T C   tcgen05.mma TS: A = T from TMEM, B = the same column rows, MN-major
+// so the N x N logits never leave the SM.  (Measured on B200, scripts/ubench_tc.cu: an N = 128 SS
+// MMA costs 64 cycles where two N = 64 ones cost 96, and one barrier round trip between the
+// epilogue and the issuer is ~1000 cycles: whole tiles and NB-deep buffering hide it, the earlier
+// 64-column ping-pong could not.)  A share of the exponentials is evaluated with a cubic on the
+// FMA pipe (ptx.cuh: ex2_poly2) because MUFU alone (16/clk/SM) would cap the pass below the tensor
+// pipe; all elementwise math is packed fp32x2.
 //
-// TMEM columns: stream g: S halves at [128g, 128g+64) and [128g+64, 128g+128), T_h aliases the
-// first 32 columns of S_h; G accumulators from column 256 (D <= 128: one per stream; D = 256: one).
+// TMEM columns: S buffer b at [128 b, 128 b + 128); MODE_GRAD: G accumulator [128 x D] after them.
 #pragma once
 #include "ptx.cuh"
 
@@ -51,10 +51,11 @@ struct PairParams {
   float* rowsum;             // [rows_pad]  MODE_ROWSUM: += sum_k mask * exp((s - 1)/tau)
   float* part;               // [PAIR_SLOTS][rows_pad][D]  MODE_GRAD: partial sum_k T_qk c_k
   float scale_log2;          // log2(e) / tau
-  int n_row_blocks;          // row blocks of RB rows
+  int n_row_blocks;          // row blocks of PAIR_RB rows
   int n_col_tiles;           // column tiles of 128
   int rows_pad;
   unsigned long long* dbg;   // optional [gridDim.x][16] cycle counters (MUSCLE_PAIR_TIMING), else null
+  int dbg_flags;             // experiments (MUSCLE_PAIR_FLAGS): 1 = column tiles loaded once per stage only, 2 = no S MMAs
 };
 
 constexpr int PAIR_SLOTS = 8;             // a row block is shared by at most this many CTAs
@@ -67,26 +68,29 @@ __host__ __device__ inline uint32_t pair_units_per_cta(uint32_t total_units, int
   return even > floor_ ? even : floor_;
 }
 
-template <int D>
+constexpr int PAIR_RB = 128;              // rows per row block of the pair passes (= one row tile)
+
+template <int D, int MODE>
 struct PairCfg {
   static_assert(D == 64 || D == 128 || D == 256, "projection dim must be 64, 128 or 256");
-  static constexpr int QT = (D == 256) ? 1 : 2;          // row tiles per item
-  static constexpr int RB = 128 * QT;                    // rows per item
-  static constexpr int NST = (D == 256) ? 2 : (D == 128 ? 4 : 6);
+  static constexpr int NB = (MODE == MODE_ROWSUM) ? 4 : (D == 256 ? 2 : 3);   // S buffers in TMEM
+  static constexpr int NST = (D == 256) ? 2 : (D == 128 ? 5 : 8);             // column-tile ring
   static constexpr int TILE_BYTES = 128 * D * 2;         // one 128-pixel bf16 tile
   static constexpr int PANEL_BYTES = 128 * 128;          // one [128 x 64] swizzle panel
   static constexpr int NPANEL = D / 64;
   static constexpr int SMEM_Q = 0;
-  static constexpr int SMEM_K = SMEM_Q + QT * TILE_BYTES;
+  static constexpr int SMEM_K = SMEM_Q + TILE_BYTES;
   static constexpr int SMEM_BITS = SMEM_K + NST * TILE_BYTES;
   static constexpr int SMEM_W = SMEM_BITS + NST * 512;
   static constexpr int SMEM_BAR = SMEM_W + NST * 512;
-  static constexpr int NBAR = 2 * NST + 14;
+  static constexpr int NBAR = 2 * NST + 2 + 2 * NB + 2;
   static constexpr int SMEM_INFO = SMEM_BAR + NBAR * 8;  // item headers [2][4], stage info [NST]
-  static constexpr int SMEM_TMEMPTR = SMEM_INFO + (8 + NST) * 4 + NST * 4;   // + debug: TMA issue clocks [NST]
+  static constexpr int SMEM_TMEMPTR = SMEM_INFO + (8 + NST) * 4;
   static constexpr int SMEM_BYTES = SMEM_TMEMPTR + 16 + 1024;  // +1024: manual 1024-B alignment
-  static constexpr int ACC_COL = 256;
+  static constexpr int ACC_COL = NB * 128;
   static constexpr int THREADS = 320;
+  static_assert(ACC_COL + (MODE == MODE_GRAD ? D : 0) <= 512, "TMEM budget");
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
 
 // all pairs of (row tile, column tile) masked: one side empty, or both the same single class
@@ -225,9 +229,9 @@ template <int D, int MODE, int POLY>
 __global__ void __launch_bounds__(320, 1)
 pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ CUtensorMap tm_col,
             const PairParams p) {
-  using C = PairCfg<D>;
-  constexpr int QT = C::QT;
+  using C = PairCfg<D, MODE>;
   constexpr int NST = C::NST;
+  constexpr int NB = C::NB;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -241,10 +245,10 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
   auto k_empty = [&](int s) { return bar0 + 8u * (NST + s); };
   const uint32_t q_full = bar0 + 8u * (2 * NST);
   const uint32_t q_empty = bar0 + 8u * (2 * NST + 1);
-  auto s_full = [&](int g, int h) { return bar0 + 8u * (2 * NST + 2 + g * 2 + h); };
-  auto t_full = [&](int g, int h) { return bar0 + 8u * (2 * NST + 6 + g * 2 + h); };  // GRAD: T stored; ROWSUM: S consumed
-  auto acc_full = [&](int s) { return bar0 + 8u * (2 * NST + 10 + s); };
-  auto acc_empty = [&](int s) { return bar0 + 8u * (2 * NST + 12 + s); };
+  auto s_full = [&](int b) { return bar0 + 8u * (2 * NST + 2 + b); };
+  auto t_full = [&](int b) { return bar0 + 8u * (2 * NST + 2 + NB + b); };  // GRAD: T stored; ROWSUM: S consumed
+  const uint32_t acc_full = bar0 + 8u * (2 * NST + 2 + 2 * NB);
+  const uint32_t acc_empty = bar0 + 8u * (2 * NST + 3 + 2 * NB);
   volatile uint32_t* info = reinterpret_cast<volatile uint32_t*>(smem_gen + C::SMEM_INFO);
   // info[4*(it&1) + {0,1,2}]: live tiles, row block, slot of item `it`; info[8+st]: tor of the stage's column tile
   volatile uint32_t* tmem_ptr_smem =
@@ -256,18 +260,16 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NST; ++s) {
       mbar_init(k_full(s), 1);
-      mbar_init(k_empty(s), 1 + (QT == 2 ? 8 : 4));
+      mbar_init(k_empty(s), 1 + 4);   // MMA issuer + the four warps of the group that owns the unit
     }
     mbar_init(q_full, 1);
     mbar_init(q_empty, 1 + 8);  // MMA issuer + every epilogue warp (after it has read the item header)
-    for (int g = 0; g < 2; ++g) {
-      for (int h = 0; h < 2; ++h) {
-        mbar_init(s_full(g, h), 1);
-        mbar_init(t_full(g, h), 4);
-      }
-      mbar_init(acc_full(g), 1);
-      mbar_init(acc_empty(g), QT == 2 ? 4 : 8);
+    for (int b = 0; b < NB; ++b) {
+      mbar_init(s_full(b), 1);
+      mbar_init(t_full(b), 4);
     }
+    mbar_init(acc_full, 1);
+    mbar_init(acc_empty, 8);
     fence_barrier_init();
   }
   if (warp == 9) {
@@ -283,13 +285,12 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem = *tmem_ptr_smem;
 
-  // stream-local tile k of stream g -> index within the item's list of live column tiles
-  auto n_stream = [&](int n, int g) { return (QT == 2) ? n : ((n - g + 1) >> 1); };
-  auto tile_of = [&](int g, int k) { return (QT == 2) ? k : (2 * k + g); };
-
   if (warp == 8) {
     // ------------------------------------------------------------ TMA producer + work partition
-    if (lane == 0) {
+    // The whole warp walks the work list (32 column-tile class unions per coalesced load, the next
+    // 32 prefetched: a dependent L2 load per tile on one lane made this warp the bottleneck);
+    // lane 0 alone touches barriers and issues the copies.
+    {
       const uint32_t total = __ldg(p.unit_off + p.n_row_blocks);
       const uint32_t per = pair_units_per_cta(total, gridDim.x, p.n_col_tiles);
       const uint64_t lo64 = static_cast<uint64_t>(per) * blockIdx.x;
@@ -312,61 +313,73 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         if (U1 <= u) { ++rb; continue; }   // row blocks without live units
         const uint32_t a = u - U0;
         const uint32_t e = (u1 < U1 ? u1 : U1) - U0;
-        uint32_t tor_r[QT];
-        for (int qt = 0; qt < QT; ++qt) tor_r[qt] = __ldg(p.tor_row + rb * QT + qt);
-        auto dead = [&](uint32_t tc) {
-          bool d = true;
-          for (int qt = 0; qt < QT; ++qt) d = d && tile_pair_dead(tor_r[qt], tc);
-          return d;
-        };
-        mbar_wait(q_empty, (it & 1) ^ 1);
-        info[4 * (it & 1) + 0] = e - a;
-        info[4 * (it & 1) + 1] = static_cast<uint32_t>(rb);
-        info[4 * (it & 1) + 2] = blockIdx.x - U0 / per;
-        mbar_arrive_expect_tx(q_full, QT * C::TILE_BYTES);
-        for (int qt = 0; qt < QT; ++qt)
+        const uint32_t tor_r = __ldg(p.tor_row + rb);
+        if (lane == 0) {
+          mbar_wait(q_empty, (it & 1) ^ 1);
+          info[4 * (it & 1) + 0] = e - a;
+          info[4 * (it & 1) + 1] = static_cast<uint32_t>(rb);
+          info[4 * (it & 1) + 2] = blockIdx.x - U0 / per;
+          mbar_arrive_expect_tx(q_full, C::TILE_BYTES);
           for (int pa = 0; pa < C::NPANEL; ++pa)
-            tma_load_2d(q_smem + qt * C::TILE_BYTES + pa * C::PANEL_BYTES, &tm_row, q_full, pa * 64,
-                        (rb * QT + qt) * 128);
-        uint32_t li = 0;  // live index of column tile j within the row block
-        for (int j = 0; j < p.n_col_tiles && li < e; ++j) {
-          const uint32_t tc = __ldg(p.tor_col + j);
-          if (dead(tc)) continue;
-          if (li++ < a) continue;
-          const int st = gcnt % NST;
-          { const long long w0 = p.dbg ? clock64() : 0;
-            mbar_wait(k_empty(st), ((gcnt / NST) & 1) ^ 1);
-            if (p.dbg) p_wait += clock64() - w0; }
-          info[8 + st] = tc;
-          if (p.dbg) info[8 + NST + st] = static_cast<uint32_t>(clock64());
-          mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES + 512 + (MODE == MODE_GRAD ? 512 : 0));
-          for (int pa = 0; pa < C::NPANEL; ++pa)
-            tma_load_2d(k_smem + st * C::TILE_BYTES + pa * C::PANEL_BYTES, &tm_col, k_full(st),
-                        pa * 64, j * 128);
-          bulk_load_1d(bits_smem + st * 512, p.bits_col + static_cast<size_t>(j) * 128, 512,
-                       k_full(st));
-          if (MODE == MODE_GRAD)
-            bulk_load_1d(w_smem + st * 512, p.w_col + static_cast<size_t>(j) * 128, 512,
-                         k_full(st));
-          ++gcnt;
+            tma_load_2d(q_smem + pa * C::PANEL_BYTES, &tm_row, q_full, pa * 64, rb * 128);
+        }
+        uint32_t li = 0;  // live index of the next live column tile within the row block
+        uint32_t tc_next = (lane < p.n_col_tiles) ? __ldg(p.tor_col + lane) : 0u;
+        for (int j0 = 0; j0 < p.n_col_tiles && li < e; j0 += 32) {
+          const uint32_t tc = tc_next;
+          const int jn = j0 + 32 + lane;
+          tc_next = (jn < p.n_col_tiles) ? __ldg(p.tor_col + jn) : 0u;
+          uint32_t live = __ballot_sync(0xffffffffu, (j0 + lane < p.n_col_tiles) && !tile_pair_dead(tor_r, tc));
+          // skip whole words that end before the share starts
+          const uint32_t cnt = __popc(live);
+          if (li + cnt <= a) { li += cnt; continue; }
+          while (live != 0u && li < e) {
+            const int jj = __ffs(live) - 1;
+            live &= live - 1u;
+            const uint32_t tcj = __shfl_sync(0xffffffffu, tc, jj);
+            if (li++ < a) continue;
+            const int j = j0 + jj;
+            const int st = gcnt % NST;
+            if (lane == 0) {
+              { const long long w0 = p.dbg ? clock64() : 0;
+                mbar_wait(k_empty(st), ((gcnt / NST) & 1) ^ 1);
+                if (p.dbg) p_wait += clock64() - w0; }
+              info[8 + st] = tcj;
+              if ((p.dbg_flags & 1) && gcnt >= static_cast<uint32_t>(NST)) {
+                mbar_arrive(k_full(st));
+              } else {
+                mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES + 512 + (MODE == MODE_GRAD ? 512 : 0));
+                for (int pa = 0; pa < C::NPANEL; ++pa)
+                  tma_load_2d(k_smem + st * C::TILE_BYTES + pa * C::PANEL_BYTES, &tm_col, k_full(st),
+                              pa * 64, j * 128);
+                bulk_load_1d(bits_smem + st * 512, p.bits_col + static_cast<size_t>(j) * 128, 512,
+                             k_full(st));
+                if (MODE == MODE_GRAD)
+                  bulk_load_1d(w_smem + st * 512, p.w_col + static_cast<size_t>(j) * 128, 512,
+                               k_full(st));
+              }
+            }
+            ++gcnt;
+          }
         }
         u = U0 + e;
         ++it;
       }
-      if (p.dbg) { p.dbg[blockIdx.x * 16 + 8] = p_wait; p.dbg[blockIdx.x * 16 + 9] = clock64() - p_t0; }
-      mbar_wait(q_empty, (it & 1) ^ 1);
-      info[4 * (it & 1) + 0] = ITEM_END;
-      mbar_arrive(q_full);
+      if (lane == 0) {
+        if (p.dbg) { p.dbg[blockIdx.x * 16 + 8] = p_wait; p.dbg[blockIdx.x * 16 + 9] = clock64() - p_t0; }
+        mbar_wait(q_empty, (it & 1) ^ 1);
+        info[4 * (it & 1) + 0] = ITEM_END;
+        mbar_arrive(q_full);
+      }
     }
   } else if (warp == 9) {
     // ------------------------------------------------------------ MMA issuer
     // (elect.sync, not lane == 0: ptxas then knows a single thread runs the region and feeds the
     // uniform-register operands of UTCHMMA without a per-instruction waterfall loop)
     if (elect_one()) {
-      constexpr uint32_t IDESC_S = umma_idesc_bf16(128, 64, 0, 0);
+      constexpr uint32_t IDESC_S = umma_idesc_bf16(128, 128, 0, 0);
       constexpr uint32_t IDESC_G = umma_idesc_bf16(128, D, 0, 1);
       uint32_t gbase = 0;
-      uint32_t cnt_t[2][2] = {{0, 0}, {0, 0}};
       long long i_kfull = 0, i_tfull = 0, i_t0 = p.dbg ? clock64() : 0;
       for (uint32_t it = 0;; ++it) {
         mbar_wait(q_full, it & 1);
@@ -374,85 +387,60 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         const uint32_t n_u = info[4 * (it & 1) + 0];
         if (n_u == ITEM_END) break;
         const int n = static_cast<int>(n_u);
-        const int nk[2] = {n_stream(n, 0), n_stream(n, 1)};
-        const int kmax = nk[0];  // nk[0] >= nk[1]
 
-        auto stage_of = [&](int g, int k, uint32_t& par) {
-          const uint32_t gg = gbase + tile_of(g, k);
-          par = (gg / NST) & 1;
-          return static_cast<int>(gg % NST);
-        };
-        auto issue_S = [&](int g, int k, int h) {
-          uint32_t par;
-          const int st = stage_of(g, k, par);
+        // S of the item's unit k into buffer (gbase + k) % NB
+        auto issue_S = [&](int k) {
+          const uint32_t gk = gbase + k;
+          const int st = static_cast<int>(gk % NST);
+          const int b = static_cast<int>(gk % NB);
           { const long long w0 = p.dbg ? clock64() : 0;
-            mbar_wait(k_full(st), par);
+            mbar_wait(k_full(st), (gk / NST) & 1);
             if (p.dbg) i_kfull += clock64() - w0; }
+          if (MODE == MODE_ROWSUM) {   // the buffer's previous unit has been read out
+            const long long w0 = p.dbg ? clock64() : 0;
+            mbar_wait(t_full(b), ((gk / NB) & 1) ^ 1);
+            if (p.dbg) i_tfull += clock64() - w0;
+          }   // MODE_GRAD: the G MMA of that unit was issued earlier and the pipe runs in order
           tc_fence_after();
-          const uint32_t a_base = q_smem + (QT == 2 ? g * C::TILE_BYTES : 0);
-          const uint32_t b_base = k_smem + st * C::TILE_BYTES + h * 8192;
+          const uint32_t b_base = k_smem + st * C::TILE_BYTES;
+          if (!(p.dbg_flags & 2)) {
 #pragma unroll
-          for (int kk = 0; kk < D / 16; ++kk) {
-            const uint32_t off = (kk >> 2) * C::PANEL_BYTES + (kk & 3) * 32;
-            mma_ss(tmem + g * 128 + h * 64, umma_desc_sw128(a_base + off, 16, 1024),
-                   umma_desc_sw128(b_base + off, 16, 1024), IDESC_S, kk > 0);
-          }
-          tc_commit(s_full(g, h));
-          // ROWSUM: the stage is free once the last S MMA that reads it has run
-          if (MODE == MODE_ROWSUM && h == 1 && (QT == 1 || g == 1)) tc_commit(k_empty(st));
-        };
-
-        // prologue: both halves of every stream's first tile
-        for (int h = 0; h < 2; ++h)
-          for (int g = 0; g < 2; ++g)
-            if (nk[g] > 0) issue_S(g, 0, h);
-        if (kmax <= 1) tc_commit(q_empty);
-        if (MODE == MODE_GRAD) {
-          mbar_wait(acc_empty(0), (it & 1) ^ 1);
-          if (QT == 2) mbar_wait(acc_empty(1), (it & 1) ^ 1);
-          tc_fence_after();
-        }
-        for (int k = 0; k < kmax; ++k) {
-          for (int h = 0; h < 2; ++h) {
-            for (int g = 0; g < 2; ++g) {
-              if (k >= nk[g]) continue;
-              const bool more = (k + 1 < nk[g]);
-              // GRAD: T_h is stored; ROWSUM: S_h has been consumed (also guards the next item's prologue)
-              { const long long w0 = p.dbg ? clock64() : 0;
-                mbar_wait(t_full(g, h), cnt_t[g][h] & 1);
-                if (p.dbg) i_tfull += clock64() - w0; }
-              tc_fence_after();
-              ++cnt_t[g][h];
-              if (MODE == MODE_GRAD) {
-                uint32_t par;
-                const int st = stage_of(g, k, par);
-                const int acc = (QT == 2) ? g : 0;
-                const bool first = (k == 0 && h == 0) && (QT == 2 || g == 0);
-                const uint32_t b_base = k_smem + st * C::TILE_BYTES;
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk)
-                  mma_ts(tmem + C::ACC_COL + acc * D, tmem + g * 128 + h * 64 + kk * 8,
-                         umma_desc_sw128(b_base + (h * 4 + kk) * 2048, C::PANEL_BYTES, 1024),
-                         IDESC_G, (first && kk == 0) ? 0u : 1u);
-                if (h == 1 && (QT == 1 || g == 1)) tc_commit(k_empty(st));
-              }
-              // D = 256 (two ring stages, one per stream): the stream's next tile reuses the stage
-              // of its current one, which only frees after the G MMA of half 1
-              if (QT == 1 && MODE == MODE_GRAD) {
-                if (more && h == 1) {
-                  issue_S(g, k + 1, 0);
-                  issue_S(g, k + 1, 1);
-                }
-              } else if (more) {
-                issue_S(g, k + 1, h);
-              }
+            for (int kk = 0; kk < D / 16; ++kk) {
+              const uint32_t off = (kk >> 2) * C::PANEL_BYTES + (kk & 3) * 32;
+              mma_ss(tmem + b * 128, umma_desc_sw128(q_smem + off, 16, 1024),
+                     umma_desc_sw128(b_base + off, 16, 1024), IDESC_S, kk > 0);
             }
           }
-          if (k == kmax - 2) tc_commit(q_empty);  // the last S MMAs of the item are in flight
-        }
-        if (MODE == MODE_GRAD) {
-          tc_commit(acc_full(0));
-          if (QT == 2) tc_commit(acc_full(1));
+          tc_commit(s_full(b));
+          if (MODE == MODE_ROWSUM) tc_commit(k_empty(st));   // the stage's last reader on the tensor pipe
+          if (k == n - 1) tc_commit(q_empty);                // the last S MMAs of the item are in flight
+        };
+
+        if (MODE == MODE_ROWSUM) {
+          for (int k = 0; k < n; ++k) issue_S(k);
+        } else {
+          const int pro = n < NB ? n : NB;
+          for (int k = 0; k < pro; ++k) issue_S(k);
+          mbar_wait(acc_empty, (it & 1) ^ 1);   // the previous item's G has been read out
+          tc_fence_after();
+          for (int k = 0; k < n; ++k) {
+            const uint32_t gk = gbase + k;
+            const int st = static_cast<int>(gk % NST);
+            const int b = static_cast<int>(gk % NB);
+            { const long long w0 = p.dbg ? clock64() : 0;
+              mbar_wait(t_full(b), (gk / NB) & 1);
+              if (p.dbg) i_tfull += clock64() - w0; }
+            tc_fence_after();
+            const uint32_t b_base = k_smem + st * C::TILE_BYTES;
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk)
+              mma_ts(tmem + C::ACC_COL, tmem + b * 128 + kk * 8,
+                     umma_desc_sw128(b_base + kk * 2048, C::PANEL_BYTES, 1024), IDESC_G,
+                     (k == 0 && kk == 0) ? 0u : 1u);
+            tc_commit(k_empty(st));
+            if (k + NB < n) issue_S(k + NB);
+          }
+          tc_commit(acc_full);
         }
         gbase += n;
       }
@@ -464,9 +452,9 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
     const int wq = warp & 3;
     const uint32_t lane_addr = static_cast<uint32_t>(wq * 32) << 16;
     const float a = p.scale_log2;
-    uint32_t gbase = 0, cnt = 0;
+    uint32_t gbase = 0;
     const bool timing = (p.dbg != nullptr) && warp == 0 && lane == 0;
-    long long t_lat = 0, n_lat = 0, t_kfull = 0, t_sfull = 0, t_ld = 0, t_math = 0, t_q = 0, t_tail = 0, t_mark = timing ? clock64() : 0;
+    long long t_kfull = 0, t_sfull = 0, t_ld = 0, t_math = 0, t_q = 0, t_tail = 0, n_mine = 0, t_mark = timing ? clock64() : 0;
     auto lap = [&](long long& acc) { if (timing) { const long long t = clock64(); acc += t - t_mark; t_mark = t; } };
     for (uint32_t it = 0;; ++it) {
       mbar_wait(q_full, it & 1);
@@ -478,31 +466,30 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
       const int slot = static_cast<int>(info[4 * (it & 1) + 2]);
       __syncwarp();
       if (lane == 0) mbar_arrive(q_empty);
-      const int row_tile = rb * QT + (QT == 2 ? g : 0);
-      const int row = row_tile * 128 + wq * 32 + lane;
+      const int row = rb * 128 + wq * 32 + lane;
       const uint32_t rbits = __ldg(p.bits_row + row);
-      const uint32_t tor_r = __ldg(p.tor_row + row_tile);
+      const uint32_t tor_r = __ldg(p.tor_row + rb);
       const uint32_t qmask = rbits ? ~rbits : 0u;
       float wrow = 0.f;
       if (MODE == MODE_GRAD) wrow = __ldg(p.w_row + row);
-      const int my_n = n_stream(n, g);
       uint64_t racc[4] = {0ull, 0ull, 0ull, 0ull};
-      for (int k = 0; k < my_n; ++k, ++cnt) {
-        const uint32_t gg = gbase + tile_of(g, k);
-        const int st = gg % NST;
-        { const long long w0 = timing ? clock64() : 0;
-          mbar_wait(k_full(st), (gg / NST) & 1);
-          if (timing) { const long long w1 = clock64();
-            if (w1 - w0 > 100) { t_lat += static_cast<uint32_t>(static_cast<uint32_t>(w1) - info[8 + NST + st]); ++n_lat; } } }
+      // this group's units: every other one of the CTA's running unit count
+      for (int k = static_cast<int>((gbase & 1u) ^ static_cast<uint32_t>(g)); k < n; k += 2) {
+        const uint32_t gk = gbase + k;
+        const int st = static_cast<int>(gk % NST);
+        const int b = static_cast<int>(gk % NB);
+        mbar_wait(k_full(st), (gk / NST) & 1);
         lap(t_kfull);
         const uint32_t tor_c = info[8 + st];
         const bool full = tile_pair_full(tor_r, tor_c);
+        mbar_wait(s_full(b), (gk / NB) & 1);
+        lap(t_sfull);
+        tc_fence_after();
+        if (timing) ++n_mine;
 #pragma unroll 1
         for (int h = 0; h < 2; ++h) {
-          mbar_wait(s_full(g, h), cnt & 1);
-          lap(t_sfull);
-          tc_fence_after();
-          const uint32_t s_addr = tmem + lane_addr + g * 128 + h * 64;
+          const uint32_t s_addr = tmem + lane_addr + b * 128 + h * 64;
+          const uint32_t t_addr = tmem + lane_addr + b * 128 + h * 32;
           const uint8_t* bsm = smem_gen + C::SMEM_BITS + st * 512 + h * 256;
           const uint8_t* wsm = smem_gen + C::SMEM_W + st * 512 + h * 256;
           uint32_t v[2][32];
@@ -510,22 +497,22 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           tmem_ld32(s_addr + 32, v[1]);
           tmem_wait_ld();
           lap(t_ld);
-          if (MODE == MODE_ROWSUM) {  // S_h is in registers: hand the buffer back before the math
+          if (MODE == MODE_ROWSUM && h == 1) {  // S is in registers: hand the buffer back before the math
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(t_full(g, h));
+            if (lane == 0) mbar_arrive(t_full(b));
           }
           if (full)
-            pair_half_math<MODE, POLY, true>(v, s_addr, bsm, wsm, qmask, a, wrow, racc);
+            pair_half_math<MODE, POLY, true>(v, t_addr, bsm, wsm, qmask, a, wrow, racc);
           else
-            pair_half_math<MODE, POLY, false>(v, s_addr, bsm, wsm, qmask, a, wrow, racc);
-          if (MODE == MODE_GRAD) {
-            tmem_wait_st();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(t_full(g, h));
-          }
+            pair_half_math<MODE, POLY, false>(v, t_addr, bsm, wsm, qmask, a, wrow, racc);
           lap(t_math);
+        }
+        if (MODE == MODE_GRAD) {
+          tmem_wait_st();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(t_full(b));
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(k_empty(st));
@@ -535,18 +522,17 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         unpack2(add2(racc[0], racc[1]), r0, r1);
         unpack2(add2(racc[2], racc[3]), r2, r3);
         const float rsum = (r0 + r1) + (r2 + r3);
-        if (my_n > 0 && rbits) atomicAdd(p.rowsum + row, rsum);
+        if (rbits && rsum != 0.f) atomicAdd(p.rowsum + row, rsum);
       } else {
-        const int acc = (QT == 2) ? g : 0;
-        constexpr int NCH = (QT == 2) ? (D / 32) : (D / 64);
-        const int col0 = (QT == 2) ? 0 : g * (D / 2);
+        constexpr int NCH = D / 64;          // 32-column chunks of this group's half of G
+        const int col0 = g * (D / 2);
         float* dst = p.part + (static_cast<size_t>(slot) * p.rows_pad + row) * D + col0;
-        mbar_wait(acc_full(acc), it & 1);
+        mbar_wait(acc_full, it & 1);
         tc_fence_after();
 #pragma unroll 1
         for (int c = 0; c < NCH; ++c) {
           uint32_t v[32];
-          tmem_ld32(tmem + lane_addr + C::ACC_COL + acc * D + col0 + c * 32, v);
+          tmem_ld32(tmem + lane_addr + C::ACC_COL + col0 + c * 32, v);
           tmem_wait_ld();
 #pragma unroll
           for (int q4 = 0; q4 < 8; ++q4)
@@ -556,14 +542,14 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(acc_empty(acc));
+        if (lane == 0) mbar_arrive(acc_empty);
       }
       lap(t_tail);
       gbase += n;
     }
     if (timing) {
       unsigned long long* d = p.dbg + blockIdx.x * 16;
-      d[0] = t_q; d[1] = t_kfull; d[2] = t_sfull; d[3] = t_ld; d[4] = t_math; d[5] = t_tail; d[6] = cnt; d[13] = t_lat; d[14] = n_lat;
+      d[0] = t_q; d[1] = t_kfull; d[2] = t_sfull; d[3] = t_ld; d[4] = t_math; d[5] = t_tail; d[6] = n_mine;
     }
   }
 

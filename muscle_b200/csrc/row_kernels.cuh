@@ -403,7 +403,7 @@ __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams 
   __syncthreads();
   if (p.dx == nullptr) return;
   const float inv_n = n_valid_sh > 0.f ? 1.f / n_valid_sh : 0.f;
-  constexpr int RB = (D == 256) ? 128 : 256;  // rows per row block of the pair passes
+  constexpr int RB = 128;  // rows per row block of the pair passes (PAIR_RB)
   const uint32_t per = pair_units_per_cta(__ldg(p.unit_off + p.n_row_blocks), p.n_ctas, p.n_col_tiles);
   const long long blk0 = static_cast<long long>(blockIdx.x) * SORT_CHUNK;
 

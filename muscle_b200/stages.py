@@ -30,7 +30,7 @@ class CudaStages:
 
     def unit_rows(self, dim):
         """rows per row block of the pair passes (the granularity of `unit_off`)"""
-        return 128 if dim == 256 else 256
+        return 128
 
     def empty(self, shape, dtype):
         return torch.empty(shape, dtype=dtype, device=self.device)

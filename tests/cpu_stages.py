@@ -29,7 +29,7 @@ class CpuStages:
         return 4
 
     def unit_rows(self, dim):
-        return 128 if dim == 256 else 256
+        return 128
 
     def empty(self, shape, dtype):
         # poison instead of garbage: reading a buffer nobody wrote shows up as NaN / huge values
