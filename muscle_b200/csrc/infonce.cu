@@ -34,9 +34,9 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
                 PairParams prm, cudaStream_t stream) {
   using C = PairCfg<D, MODE>;
   CUtensorMap tm_row, tm_col;
-  int rc = make_bf16_tile_map(&tm_row, ehat_rows, rows_pad, D);
+  int rc = make_bf16_panel_map(&tm_row, ehat_rows, rows_pad, D);
   if (rc) return rc;
-  rc = make_bf16_tile_map(&tm_col, ehat_cols, cols_pad, D);
+  rc = make_bf16_panel_map(&tm_col, ehat_cols, cols_pad, D);
   if (rc) return rc;
   auto kern = pair_kernel<D, MODE, POLY>;
   static thread_local bool attr_set = false;

@@ -289,7 +289,9 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
     // ------------------------------------------------------------ TMA producer + work partition
     // The whole warp walks the work list (32 column-tile class unions per coalesced load, the next
     // 32 prefetched: a dependent L2 load per tile on one lane made this warp the bottleneck);
-    // lane 0 alone touches barriers and issues the copies.
+    // lane 0 alone touches barriers and issues the copies.  (A second producer warp taking
+    // alternate units changed nothing: what remains of this warp's time per unit is the copy
+    // engine itself, ~32 KB per unit against shared-memory bandwidth the S MMAs saturate.)
     {
       const uint32_t total = __ldg(p.unit_off + p.n_row_blocks);
       const uint32_t per = pair_units_per_cta(total, gridDim.x, p.n_col_tiles);
@@ -320,8 +322,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           info[4 * (it & 1) + 1] = static_cast<uint32_t>(rb);
           info[4 * (it & 1) + 2] = blockIdx.x - U0 / per;
           mbar_arrive_expect_tx(q_full, C::TILE_BYTES);
-          for (int pa = 0; pa < C::NPANEL; ++pa)
-            tma_load_2d(q_smem + pa * C::PANEL_BYTES, &tm_row, q_full, pa * 64, rb * 128);
+          tma_load_3d(q_smem, &tm_row, q_full, 0, rb * 128, 0);
         }
         uint32_t li = 0;  // live index of the next live column tile within the row block
         uint32_t tc_next = (lane < p.n_col_tiles) ? __ldg(p.tor_col + lane) : 0u;
@@ -349,9 +350,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
                 mbar_arrive(k_full(st));
               } else {
                 mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES + 512 + (MODE == MODE_GRAD ? 512 : 0));
-                for (int pa = 0; pa < C::NPANEL; ++pa)
-                  tma_load_2d(k_smem + st * C::TILE_BYTES + pa * C::PANEL_BYTES, &tm_col, k_full(st),
-                              pa * 64, j * 128);
+                tma_load_3d(k_smem + st * C::TILE_BYTES, &tm_col, k_full(st), 0, j * 128, 0);
                 bulk_load_1d(bits_smem + st * 512, p.bits_col + static_cast<size_t>(j) * 128, 512,
                              k_full(st));
                 if (MODE == MODE_GRAD)
@@ -482,6 +481,11 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         lap(t_kfull);
         const uint32_t tor_c = info[8 + st];
         const bool full = tile_pair_full(tor_r, tor_c);
+        const bool early = (MODE == MODE_ROWSUM) && full;
+        if (early) {   // no label mask to read: the stage is only the tensor pipe's now
+          __syncwarp();
+          if (lane == 0) mbar_arrive(k_empty(st));
+        }
         mbar_wait(s_full(b), (gk / NB) & 1);
         lap(t_sfull);
         tc_fence_after();
@@ -514,8 +518,10 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           __syncwarp();
           if (lane == 0) mbar_arrive(t_full(b));
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(k_empty(st));
+        if (!early) {
+          __syncwarp();
+          if (lane == 0) mbar_arrive(k_empty(st));
+        }
       }
       if (MODE == MODE_ROWSUM) {
         float r0, r1, r2, r3;

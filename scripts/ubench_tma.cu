@@ -22,8 +22,9 @@ constexpr int NST = 4;
 constexpr int TILE = 32768;
 
 // hammer: 0 none, 1 SS M128 N64, 2 TS M128 N64 (A in TMEM)
-template <int HAMMER>
-__global__ void __launch_bounds__(128, 1) ring_kernel(const __grid_constant__ CUtensorMap tm, int n_tiles_total,
+// OPS: 0 = two 2-D panel copies, 1 = + two 512-B bulk copies, 2 = one 3-D copy, 3 = one 3-D copy + one 1-KB bulk copy
+template <int HAMMER, int OPS>
+__global__ void __launch_bounds__(128, 1) ring_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ CUtensorMap tm3, const char* meta, int n_tiles_total,
                                                        int tiles, int delay, int stride, long long* out) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -60,9 +61,18 @@ __global__ void __launch_bounds__(128, 1) ring_kernel(const __grid_constant__ CU
       wait_empty += clock64() - w0;
       const int j = static_cast<int>((static_cast<long long>(blockIdx.x) * stride + t) % n_tiles_total);
       issue_clk[st] = static_cast<uint32_t>(clock64());
-      mbar_arrive_expect_tx(k_full(st), TILE);
-      tma_load_2d(k_smem + st * TILE, &tm, k_full(st), 0, j * 128);
-      tma_load_2d(k_smem + st * TILE + 16384, &tm, k_full(st), 64, j * 128);
+      mbar_arrive_expect_tx(k_full(st), TILE + (OPS == 1 || OPS == 3 ? 1024 : 0));
+      if (OPS < 2) {
+        tma_load_2d(k_smem + st * TILE, &tm, k_full(st), 0, j * 128);
+        tma_load_2d(k_smem + st * TILE + 16384, &tm, k_full(st), 64, j * 128);
+      } else {
+        tma_load_3d(k_smem + st * TILE, &tm3, k_full(st), 0, j * 128, 0);
+      }
+      if (OPS == 1) {
+        bulk_load_1d(ham + 65536 + st * 1024, meta + j * 1024, 512, k_full(st));
+        bulk_load_1d(ham + 65536 + st * 1024 + 512, meta + j * 1024 + 512, 512, k_full(st));
+      }
+      if (OPS == 3) bulk_load_1d(ham + 65536 + st * 1024, meta + j * 1024, 1024, k_full(st));
     }
     out[blockIdx.x * 8 + 0] = clock64() - t0;
     out[blockIdx.x * 8 + 1] = wait_empty;
@@ -121,46 +131,57 @@ __global__ void __launch_bounds__(128, 1) ring_kernel(const __grid_constant__ CU
   if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
+template <int HAMMER, int OPS>
+void run(const CUtensorMap& tm, const CUtensorMap& tm3, const char* meta, int n_tiles_total, long long* out, int smem) {
+  cudaFuncSetAttribute(ring_kernel<HAMMER, OPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  const int tiles = 2000;
+  for (int grid : {148, 1})
+    for (int delay : {0, 600, 2000}) {
+      const int stride = 97;
+      cudaMemset(out, 0, 148 * 8 * 8);
+      for (int rep = 0; rep < 2; ++rep)
+        ring_kernel<HAMMER, OPS><<<grid, 128, smem>>>(tm, tm3, meta, n_tiles_total, tiles, delay, stride, out);
+      cudaError_t e = cudaDeviceSynchronize();
+      if (e != cudaSuccess) { printf("error: %s\n", cudaGetErrorString(e)); exit(1); }
+      std::vector<long long> h(148 * 8);
+      cudaMemcpy(h.data(), out, 148 * 8 * 8, cudaMemcpyDeviceToHost);
+      double cyc = 0, lat = 0, lmax = 0, nm = 0, busy = 0;
+      for (int b = 0; b < grid; ++b) {
+        cyc += (double)h[b * 8 + 4] / tiles;
+        lat += (double)h[b * 8 + 2] / tiles;
+        lmax = std::max(lmax, (double)h[b * 8 + 3]);
+        nm += (double)h[b * 8 + 6] / tiles;
+        busy += (double)(h[b * 8 + 0] - h[b * 8 + 1]) / tiles;
+      }
+      cyc /= grid; lat /= grid; nm /= grid; busy /= grid;
+      printf("%-7d %-4d %-5d %-6d | %-9.0f %-9.0f %-9.0f %-9.1f %-9.1f %-9.0f\n", HAMMER, OPS, grid, delay, cyc, lat, lmax,
+             TILE / cyc, nm, busy);
+    }
+}
+
 int main(int argc, char** argv) {
   const int64_t rows = 65536;   // 16 MB of bf16 [rows][128]: L2 resident
   void* buf;
   cudaMalloc(&buf, rows * 128 * 2);
   cudaMemset(buf, 0, rows * 128 * 2);
-  CUtensorMap tm;
+  char* meta;
+  cudaMalloc(&meta, rows / 128 * 1024);
+  cudaMemset(meta, 0, rows / 128 * 1024);
+  CUtensorMap tm, tm3;
   if (make_bf16_box_map(&tm, buf, rows, 128, 128)) { printf("map failed\n"); return 1; }
+  if (make_bf16_panel_map(&tm3, buf, rows, 128)) { printf("panel map failed\n"); return 1; }
   long long* out;
   cudaMalloc(&out, 148 * 8 * 8);
-  const int smem = NST * TILE + 65536 + 1024;
-  cudaFuncSetAttribute(ring_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  cudaFuncSetAttribute(ring_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  cudaFuncSetAttribute(ring_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  const int tiles = 2000;
-  printf("%-8s %-6s %-7s %-7s | %-10s %-10s %-10s %-12s %-10s\n", "hammer", "grid", "delay", "stride", "cyc/tile", "lat_avg",
-         "lat_max", "B/clk/SM", "mma/tile");
-  for (int hammer = 0; hammer < 3; ++hammer)
-    for (int grid : {148, 37, 1})
-      for (int delay : {0, 1000, 4000})
-        for (int stride : {1, 97}) {
-          cudaMemset(out, 0, 148 * 8 * 8);
-          for (int rep = 0; rep < 2; ++rep) {
-            if (hammer == 0) ring_kernel<0><<<grid, 128, smem>>>(tm, (int)(rows / 128), tiles, delay, stride, out);
-            if (hammer == 1) ring_kernel<1><<<grid, 128, smem>>>(tm, (int)(rows / 128), tiles, delay, stride, out);
-            if (hammer == 2) ring_kernel<2><<<grid, 128, smem>>>(tm, (int)(rows / 128), tiles, delay, stride, out);
-          }
-          cudaError_t e = cudaDeviceSynchronize();
-          if (e != cudaSuccess) { printf("error: %s\n", cudaGetErrorString(e)); return 1; }
-          std::vector<long long> h(148 * 8);
-          cudaMemcpy(h.data(), out, 148 * 8 * 8, cudaMemcpyDeviceToHost);
-          double cyc = 0, lat = 0, lmax = 0, nm = 0;
-          for (int b = 0; b < grid; ++b) {
-            cyc += (double)h[b * 8 + 4] / tiles;
-            lat += (double)h[b * 8 + 2] / tiles;
-            lmax = std::max(lmax, (double)h[b * 8 + 3]);
-            nm += (double)h[b * 8 + 6] / tiles;
-          }
-          cyc /= grid; lat /= grid; nm /= grid;
-          printf("%-8d %-6d %-7d %-7d | %-10.0f %-10.0f %-10.0f %-12.1f %-10.1f\n", hammer, grid, delay, stride, cyc, lat, lmax,
-                 TILE / cyc, nm);
-        }
+  const int smem = NST * TILE + 65536 + NST * 1024 + 1024;
+  printf("%-7s %-4s %-5s %-6s | %-9s %-9s %-9s %-9s %-9s %-9s\n", "hammer", "ops", "grid", "delay", "cyc/tile", "lat_avg",
+         "lat_max", "B/clk/SM", "mma/tile", "prod_busy");
+  const int nt = (int)(rows / 128);
+  run<0, 0>(tm, tm3, meta, nt, out, smem);
+  run<0, 1>(tm, tm3, meta, nt, out, smem);
+  run<0, 2>(tm, tm3, meta, nt, out, smem);
+  run<0, 3>(tm, tm3, meta, nt, out, smem);
+  run<1, 0>(tm, tm3, meta, nt, out, smem);
+  run<1, 1>(tm, tm3, meta, nt, out, smem);
+  run<1, 3>(tm, tm3, meta, nt, out, smem);
   return 0;
 }
