@@ -45,7 +45,7 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
     attr_set = true;
   }
   const int grid = pair_grid();  // one persistent CTA per SM; shares come from unit_off
-  static const bool timing = getenv("MUSCLE_PAIR_TIMING") != nullptr;   // debug: per-phase cycle counters
+  static const bool timing = kPairTiming && getenv("MUSCLE_PAIR_TIMING") != nullptr;   // debug: per-phase cycle counters (-DMB_PAIR_TIMING=1 builds)
   static unsigned long long* dbg = nullptr;
   static const int flags = getenv("MUSCLE_PAIR_FLAGS") ? atoi(getenv("MUSCLE_PAIR_FLAGS")) : 0;
   prm.dbg_flags = flags;
@@ -70,6 +70,18 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
         const double tiles = s[6] / n;
         fprintf(stderr, "[pair D=%d mode=%d] active CTAs %d, units/CTA (group 0) %.1f | per own unit: q %.0f kfull %.0f sfull %.0f ld %.0f math %.0f tail %.0f cycles\n",
                 D, MODE, n, tiles, s[0] / n / tiles, s[1] / n / tiles, s[2] / n / tiles, s[3] / n / tiles, s[4] / n / tiles, s[5] / n / tiles);
+        {
+          unsigned long long mn = ~0ull, mx = 0;
+          for (int c = 0; c < std::min(grid, 148); ++c)
+            if (h[c * 16 + 6]) { mn = std::min(mn, h[c * 16 + 12]); mx = std::max(mx, h[c * 16 + 12]); }
+          fprintf(stderr, "    issuer lifetime per CTA: min %llu mean %.0f max %llu cycles\n", mn, s[12] / n, mx);
+          if (getenv("MUSCLE_PAIR_TIMING_ALL")) {
+            fprintf(stderr, "    per CTA (issuer lifetime k cycles / group-0 units: all, select-masked, bias-masked / epilogue math k cycles):");
+            for (int c = 0; c < std::min(grid, 148); ++c)
+              fprintf(stderr, "%s%llu/%llu,%llu,%llu/%llu", c % 6 ? " " : "\n      ", h[c * 16 + 12] / 1000, h[c * 16 + 6], h[c * 16 + 7], h[c * 16 + 13], h[c * 16 + 4] / 1000);
+            fprintf(stderr, "\n");
+          }
+        }
         fprintf(stderr, "    producer: wait k_empty %.0f of %.0f per unit | issuer: wait k_full %.0f, wait t_full %.0f of %.0f per unit\n",
                 s[8] / n / tiles / 2, s[9] / n / tiles / 2, s[10] / n / tiles / 2, s[11] / n / tiles / 2, s[12] / n / tiles / 2);
       }
@@ -81,7 +93,8 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
 // The FMA-pipe exponential is exact enough only while the exponent stays in range:
 // x = (s - 1) log2(e)/T lies in [-2 log2(e)/T, ~0].
 constexpr int kPoly = 2;  // of every 4 element pairs
-bool poly_ok(float temperature) { return 2.f * kLog2e / temperature < 100.f; }
+// (MASK_BIAS pushes masked columns another 64 down: x in [-2 log2(e)/T - 64, ~0])
+bool poly_ok(float temperature) { return 2.f * kLog2e / temperature + 64.f < 118.f; }
 
 template <int MODE>
 int launch_pair_dim(int dim, bool poly, const void* ehat_rows, int64_t rows_pad,
@@ -159,11 +172,15 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
   const int n_tiles = static_cast<int>(rows_pad / 128);
 #define MB_PREP(DD)                                                                               \
   {                                                                                               \
-    MB_CUDA(cudaFuncSetAttribute(prepare_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                 static_cast<int>(SORT_CHUNK * (DD / 2 + 1) * sizeof(uint32_t)))); \
-    prepare_kernel<DD><<<n_blk, SORT_CHUNK, smem, stream>>>(p);                                   \
+    if (layout == MUSCLE_LAYOUT_NCHW) {                                                           \
+      MB_CUDA(cudaFuncSetAttribute(prepare_nchw_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                   static_cast<int>(SORT_CHUNK * (DD / 2 + 1) * sizeof(uint32_t)))); \
+      prepare_nchw_kernel<DD><<<n_blk, PREP_THREADS, smem, stream>>>(p);                          \
+    } else {                                                                                      \
+      prepare_kernel<DD><<<n_blk, SORT_CHUNK, 0, stream>>>(p);                                    \
+    }                                                                                             \
     MB_LAUNCH_CHECK();                                                                            \
-    class_sum_kernel<DD><<<n_tiles, SEG_THREADS, 0, stream>>>(p.ehat, seg, num_classes, class_sum); \
+    class_sum_kernel<DD><<<n_tiles * (128 / SEG_ROWS), SEG_THREADS, 0, stream>>>(p.ehat, seg, num_classes, class_sum); \
   }
   if (dim == 64) MB_PREP(64) else if (dim == 128) MB_PREP(128) else MB_PREP(256)
 #undef MB_PREP
@@ -211,7 +228,7 @@ int muscle_infonce_mid(const void* ehat, const uint32_t* seg, int64_t rows_pad, 
   p.ehat = static_cast<const __nv_bfloat16*>(ehat); p.seg = seg; p.C = num_classes;
   p.class_sum = class_sum; p.class_mass = class_mass; p.rowsum = rowsum;
   p.inv_tau = 1.f / temperature; p.w = w; p.gpos = gpos; p.loss_acc = loss_acc; p.dproto = dproto;
-  const int grid = static_cast<int>(rows_pad / 128);
+  const int grid = static_cast<int>(rows_pad / SEG_ROWS);
   if (dim == 64) mid_kernel<64><<<grid, SEG_THREADS, 0, stream>>>(p);
   else if (dim == 128) mid_kernel<128><<<grid, SEG_THREADS, 0, stream>>>(p);
   else mid_kernel<256><<<grid, SEG_THREADS, 0, stream>>>(p);

@@ -31,9 +31,16 @@
 //
 // TMEM columns: S buffer b at [128 b, 128 b + 128); MODE_GRAD: G accumulator [128 x D] after them.
 #pragma once
+// Cycle counters of the pair kernel's phases (printed by infonce.cu under MUSCLE_PAIR_TIMING=1) cost
+// ~20 registers per epilogue thread: compiled in only with -DMB_PAIR_TIMING=1 (scripts/build_variants.sh).
+#ifndef MB_PAIR_TIMING
+#define MB_PAIR_TIMING 0
+#endif
 #include "ptx.cuh"
 
 namespace mb200 {
+
+constexpr bool kPairTiming = MB_PAIR_TIMING != 0;
 
 enum PairMode { MODE_ROWSUM = 0, MODE_GRAD = 1 };
 
@@ -68,6 +75,7 @@ __host__ __device__ inline uint32_t pair_units_per_cta(uint32_t total_units, int
   return even > floor_ ? even : floor_;
 }
 
+constexpr int BIAS_SLOTS = 4;            // distinct row classes per tile the exponent-bias mask handles
 constexpr int PAIR_RB = 128;              // rows per row block of the pair passes (= one row tile)
 
 template <int D, int MODE>
@@ -82,7 +90,8 @@ struct PairCfg {
   static constexpr int SMEM_K = SMEM_Q + TILE_BYTES;
   static constexpr int SMEM_BITS = SMEM_K + NST * TILE_BYTES;
   static constexpr int SMEM_W = SMEM_BITS + NST * 512;
-  static constexpr int SMEM_BAR = SMEM_W + NST * 512;
+  static constexpr int SMEM_CB = SMEM_W + NST * 512;     // exponent-shift vectors [2 groups][2][BIAS_SLOTS][128] (MASK_BIAS)
+  static constexpr int SMEM_BAR = SMEM_CB + 4 * BIAS_SLOTS * 512;
   static constexpr int NBAR = 2 * NST + 2 + 2 * NB + 2;
   static constexpr int SMEM_INFO = SMEM_BAR + NBAR * 8;  // item headers [2][4], stage info [NST]
   static constexpr int SMEM_TMEMPTR = SMEM_INFO + (8 + NST) * 4;
@@ -165,10 +174,17 @@ __global__ void __launch_bounds__(1024) pair_plan_kernel(const uint32_t* tor_row
 
 // ------------------------------------------------------------------------------------------
 // Epilogue math of one 64-column half for one thread (= one row); v = the S values.
-// FULL: no label mask needed.  POLY of every 4 element pairs take the FMA-pipe exponential.
-template <int MODE, int POLY, bool FULL>
+// MASK_NONE: no label mask needed.  MASK_SELECT: per-element select on the class bits.  MASK_BIAS:
+// the rows of the tile have at most BIAS_SLOTS distinct classes, so the mask is one vector per row
+// class and column tile, folded into the exponent shift: bias_sm[k] = -a for a kept column,
+// -a - 64 for a masked one (exp2 leaves < 2^-64 of the term: below fp32 resolution of any row sum,
+// at no instruction cost); every thread reads the vector of its row's class.  POLY of every 4 element pairs take the FMA-pipe exponential.
+enum { MASK_NONE = 0, MASK_SELECT = 1, MASK_BIAS = 2 };
+constexpr float MASK_BIAS_SHIFT = 64.f;
+template <int MODE, int POLY, int MASK>
 __device__ __forceinline__ void pair_half_math(uint32_t (&v)[2][32], uint32_t t_addr,
                                                const uint8_t* bits_sm, const uint8_t* w_sm,
+                                               const uint8_t* bias_sm,
                                                uint32_t qmask, float a, float wrow,
                                                uint64_t (&racc)[4]) {
   const uint64_t a2 = pack2(a, a);
@@ -178,13 +194,20 @@ __device__ __forceinline__ void pair_half_math(uint32_t (&v)[2][32], uint32_t t_
   for (int c = 0; c < 2; ++c) {
     const uint4* kb4 = reinterpret_cast<const uint4*>(bits_sm) + c * 8;
     const float4* kw4 = reinterpret_cast<const float4*>(w_sm) + c * 8;
+    const float4* kc4 = reinterpret_cast<const float4*>(bias_sm) + c * 8;
     uint32_t packed[16];
 #pragma unroll
     for (int q4 = 0; q4 < 8; ++q4) {
       uint64_t e[2];
+      uint64_t off2[2] = {noff2, noff2};
+      if (MASK == MASK_BIAS) {
+        const float4 kc = kc4[q4];
+        off2[0] = pack2(kc.x, kc.y);
+        off2[1] = pack2(kc.z, kc.w);
+      }
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
-        const uint64_t x = fma2(pack2u(v[c][q4 * 4 + 2 * s], v[c][q4 * 4 + 2 * s + 1]), a2, noff2);
+        const uint64_t x = fma2(pack2u(v[c][q4 * 4 + 2 * s], v[c][q4 * 4 + 2 * s + 1]), a2, off2[s]);
         if (POLY < 0) {
           e[s] = x;  // measurement variant: no exponential
         } else if (((q4 * 2 + s) & 3) < POLY) {
@@ -195,7 +218,7 @@ __device__ __forceinline__ void pair_half_math(uint32_t (&v)[2][32], uint32_t t_
           e[s] = pack2(ex2_approx(x0), ex2_approx(x1));
         }
       }
-      if (!FULL) {
+      if (MASK == MASK_SELECT) {
         const uint4 kb = kb4[q4];
         float e0, e1, e2, e3;
         unpack2(e[0], e0, e1);
@@ -309,7 +332,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         rb = lo;
       }
       uint32_t gcnt = 0, it = 0;
-      long long p_wait = 0, p_t0 = p.dbg ? clock64() : 0;
+      long long p_wait = 0, p_t0 = (kPairTiming && p.dbg) ? clock64() : 0;
       while (u < u1) {
         const uint32_t U0 = __ldg(p.unit_off + rb), U1 = __ldg(p.unit_off + rb + 1);
         if (U1 <= u) { ++rb; continue; }   // row blocks without live units
@@ -342,11 +365,11 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
             const int j = j0 + jj;
             const int st = gcnt % NST;
             if (lane == 0) {
-              { const long long w0 = p.dbg ? clock64() : 0;
+              { const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
                 mbar_wait(k_empty(st), ((gcnt / NST) & 1) ^ 1);
-                if (p.dbg) p_wait += clock64() - w0; }
+                if (kPairTiming && p.dbg) p_wait += clock64() - w0; }
               info[8 + st] = tcj;
-              if ((p.dbg_flags & 1) && gcnt >= static_cast<uint32_t>(NST)) {
+              if ((kPairTiming && (p.dbg_flags & 1)) && gcnt >= static_cast<uint32_t>(NST)) {
                 mbar_arrive(k_full(st));
               } else {
                 mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES + 512 + (MODE == MODE_GRAD ? 512 : 0));
@@ -365,7 +388,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         ++it;
       }
       if (lane == 0) {
-        if (p.dbg) { p.dbg[blockIdx.x * 16 + 8] = p_wait; p.dbg[blockIdx.x * 16 + 9] = clock64() - p_t0; }
+        if (kPairTiming && p.dbg) { p.dbg[blockIdx.x * 16 + 8] = p_wait; p.dbg[blockIdx.x * 16 + 9] = clock64() - p_t0; }
         mbar_wait(q_empty, (it & 1) ^ 1);
         info[4 * (it & 1) + 0] = ITEM_END;
         mbar_arrive(q_full);
@@ -379,7 +402,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
       constexpr uint32_t IDESC_S = umma_idesc_bf16(128, 128, 0, 0);
       constexpr uint32_t IDESC_G = umma_idesc_bf16(128, D, 0, 1);
       uint32_t gbase = 0;
-      long long i_kfull = 0, i_tfull = 0, i_t0 = p.dbg ? clock64() : 0;
+      long long i_kfull = 0, i_tfull = 0, i_t0 = (kPairTiming && p.dbg) ? clock64() : 0;
       for (uint32_t it = 0;; ++it) {
         mbar_wait(q_full, it & 1);
         tc_fence_after();
@@ -392,17 +415,17 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           const uint32_t gk = gbase + k;
           const int st = static_cast<int>(gk % NST);
           const int b = static_cast<int>(gk % NB);
-          { const long long w0 = p.dbg ? clock64() : 0;
+          { const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
             mbar_wait(k_full(st), (gk / NST) & 1);
-            if (p.dbg) i_kfull += clock64() - w0; }
+            if (kPairTiming && p.dbg) i_kfull += clock64() - w0; }
           if (MODE == MODE_ROWSUM) {   // the buffer's previous unit has been read out
-            const long long w0 = p.dbg ? clock64() : 0;
+            const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
             mbar_wait(t_full(b), ((gk / NB) & 1) ^ 1);
-            if (p.dbg) i_tfull += clock64() - w0;
+            if (kPairTiming && p.dbg) i_tfull += clock64() - w0;
           }   // MODE_GRAD: the G MMA of that unit was issued earlier and the pipe runs in order
           tc_fence_after();
           const uint32_t b_base = k_smem + st * C::TILE_BYTES;
-          if (!(p.dbg_flags & 2)) {
+          if (!(kPairTiming && (p.dbg_flags & 2))) {
 #pragma unroll
             for (int kk = 0; kk < D / 16; ++kk) {
               const uint32_t off = (kk >> 2) * C::PANEL_BYTES + (kk & 3) * 32;
@@ -426,9 +449,9 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
             const uint32_t gk = gbase + k;
             const int st = static_cast<int>(gk % NST);
             const int b = static_cast<int>(gk % NB);
-            { const long long w0 = p.dbg ? clock64() : 0;
+            { const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
               mbar_wait(t_full(b), (gk / NB) & 1);
-              if (p.dbg) i_tfull += clock64() - w0; }
+              if (kPairTiming && p.dbg) i_tfull += clock64() - w0; }
             tc_fence_after();
             const uint32_t b_base = k_smem + st * C::TILE_BYTES;
 #pragma unroll
@@ -443,7 +466,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         }
         gbase += n;
       }
-      if (p.dbg) { p.dbg[blockIdx.x * 16 + 10] = i_kfull; p.dbg[blockIdx.x * 16 + 11] = i_tfull; p.dbg[blockIdx.x * 16 + 12] = clock64() - i_t0; }
+      if (kPairTiming && p.dbg) { p.dbg[blockIdx.x * 16 + 10] = i_kfull; p.dbg[blockIdx.x * 16 + 11] = i_tfull; p.dbg[blockIdx.x * 16 + 12] = clock64() - i_t0; }
     }
   } else {
     // ------------------------------------------------------------ epilogue groups
@@ -451,9 +474,9 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
     const int wq = warp & 3;
     const uint32_t lane_addr = static_cast<uint32_t>(wq * 32) << 16;
     const float a = p.scale_log2;
-    uint32_t gbase = 0;
-    const bool timing = (p.dbg != nullptr) && warp == 0 && lane == 0;
-    long long t_kfull = 0, t_sfull = 0, t_ld = 0, t_math = 0, t_q = 0, t_tail = 0, n_mine = 0, t_mark = timing ? clock64() : 0;
+    uint32_t gbase = 0, n_bias = 0;
+    const bool timing = kPairTiming && (p.dbg != nullptr) && warp == 0 && lane == 0;
+    long long t_kfull = 0, t_sfull = 0, t_ld = 0, t_math = 0, t_q = 0, t_tail = 0, n_mine = 0, n_sel = 0, n_bi = 0, t_mark = timing ? clock64() : 0;
     auto lap = [&](long long& acc) { if (timing) { const long long t = clock64(); acc += t - t_mark; t_mark = t; } };
     for (uint32_t it = 0;; ++it) {
       mbar_wait(q_full, it & 1);
@@ -469,6 +492,10 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
       const uint32_t rbits = __ldg(p.bits_row + row);
       const uint32_t tor_r = __ldg(p.tor_row + rb);
       const uint32_t qmask = rbits ? ~rbits : 0u;
+      // few enough distinct row classes for the bias form; my_slot = rank of this row's class among
+      // them (rows outside the loss read slot 0: their sums are never used)
+      const bool bias_ok = __popc(tor_r & TOR_CLASSES) <= BIAS_SLOTS;
+      const int my_slot = rbits ? __popc(tor_r & TOR_CLASSES & (rbits - 1u)) : 0;
       float wrow = 0.f;
       if (MODE == MODE_GRAD) wrow = __ldg(p.w_row + row);
       uint64_t racc[4] = {0ull, 0ull, 0ull, 0ull};
@@ -481,15 +508,27 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         lap(t_kfull);
         const uint32_t tor_c = info[8 + st];
         const bool full = tile_pair_full(tor_r, tor_c);
-        const bool early = (MODE == MODE_ROWSUM) && full;
-        if (early) {   // no label mask to read: the stage is only the tensor pipe's now
+        const int mask = full ? MASK_NONE : (bias_ok ? MASK_BIAS : MASK_SELECT);
+        const uint8_t* cb = smem_gen + C::SMEM_CB + ((g * 2 + (n_bias & 1)) * BIAS_SLOTS) * 512;
+        if (mask == MASK_BIAS) {   // one shift vector per row class of the tile
+          const int t = wq * 32 + lane;
+          const uint32_t kb = reinterpret_cast<const uint32_t*>(smem_gen + C::SMEM_BITS + st * 512)[t];
+          float* cbw = reinterpret_cast<float*>(const_cast<uint8_t*>(cb)) + t;
+          uint32_t rem = tor_r & TOR_CLASSES;
+          for (int j = 0; rem != 0u; ++j, rem &= rem - 1u)
+            cbw[j * 128] = (kb & ~(rem & (0u - rem))) ? -a : -a - MASK_BIAS_SHIFT;
+          ++n_bias;   // double buffered: the barrier of the next masked tile orders reuse
+          asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+        }
+        const bool early = (MODE == MODE_ROWSUM) && mask != MASK_SELECT;
+        if (early) {   // no class bits left to read: the stage is only the tensor pipe's now
           __syncwarp();
           if (lane == 0) mbar_arrive(k_empty(st));
         }
         mbar_wait(s_full(b), (gk / NB) & 1);
         lap(t_sfull);
         tc_fence_after();
-        if (timing) ++n_mine;
+        if (timing) { ++n_mine; n_sel += (mask == MASK_SELECT); n_bi += (mask == MASK_BIAS); }
 #pragma unroll 1
         for (int h = 0; h < 2; ++h) {
           const uint32_t s_addr = tmem + lane_addr + b * 128 + h * 64;
@@ -506,10 +545,12 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
             __syncwarp();
             if (lane == 0) mbar_arrive(t_full(b));
           }
-          if (full)
-            pair_half_math<MODE, POLY, true>(v, t_addr, bsm, wsm, qmask, a, wrow, racc);
+          if (mask == MASK_NONE)
+            pair_half_math<MODE, POLY, MASK_NONE>(v, t_addr, bsm, wsm, cb, qmask, a, wrow, racc);
+          else if (mask == MASK_BIAS)
+            pair_half_math<MODE, POLY, MASK_BIAS>(v, t_addr, bsm, wsm, cb + my_slot * 512 + h * 256, qmask, a, wrow, racc);
           else
-            pair_half_math<MODE, POLY, false>(v, t_addr, bsm, wsm, qmask, a, wrow, racc);
+            pair_half_math<MODE, POLY, MASK_SELECT>(v, t_addr, bsm, wsm, cb, qmask, a, wrow, racc);
           lap(t_math);
         }
         if (MODE == MODE_GRAD) {
@@ -555,7 +596,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
     }
     if (timing) {
       unsigned long long* d = p.dbg + blockIdx.x * 16;
-      d[0] = t_q; d[1] = t_kfull; d[2] = t_sfull; d[3] = t_ld; d[4] = t_math; d[5] = t_tail; d[6] = n_mine;
+      d[0] = t_q; d[1] = t_kfull; d[2] = t_sfull; d[3] = t_ld; d[4] = t_math; d[5] = t_tail; d[6] = n_mine; d[7] = n_sel; d[13] = n_bi;
     }
   }
 

@@ -208,11 +208,80 @@ __global__ void __launch_bounds__(SORT_CHUNK) prepare_kernel(const PrepareParams
   }
 }
 
+// NCHW input: the same job with 16 warps per 128 pixels -- warp = (32 pixels, a quarter of the
+// channels), lane = pixel, so every channel read is one coalesced 128-byte line and each value is
+// read ONCE (kept in registers between the norm and the scale); 4x the loads in flight of the
+// one-warp-per-32-pixels form above, which left this kernel latency bound (5 warps per SM).
+constexpr int PREP_THREADS = 512;
+template <int D>
+__global__ void __launch_bounds__(PREP_THREADS) prepare_nchw_kernel(const PrepareParams p) {
+  constexpr int DQ = D / 4;            // channels per warp
+  constexpr int WPR = D / 64;          // 32-bit words (bf16 pairs) per lane per row
+  constexpr int ROW_W = D / 2 + 1;     // smem row stride in words (odd: conflict-free columns)
+  extern __shared__ uint32_t smem_u[];  // [128][ROW_W]
+  __shared__ uint32_t warp_hist[SORT_WARPS][MAX_BINS];
+  __shared__ float ss_sm[4][SORT_CHUNK];
+  __shared__ int dest_sm[SORT_CHUNK];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int pg = warp & 3, cq = warp >> 2;
+  for (int i = threadIdx.x; i < SORT_WARPS * MAX_BINS; i += PREP_THREADS) (&warp_hist[0][0])[i] = 0u;
+  __syncthreads();
+  const long long n0 = static_cast<long long>(blockIdx.x) * SORT_CHUNK + pg * 32;
+  const long long i = n0 + lane;
+  const bool live = i < p.n;
+  // values first: the loads are in flight while the sort position is worked out
+  float v[DQ];
+  {
+    const long long b = live ? i / p.ppi : 0;
+    const float* src = p.x + (b * D + cq * DQ) * p.ppi + (live ? i - b * p.ppi : 0);
+#pragma unroll
+    for (int d = 0; d < DQ; ++d) v[d] = live ? __ldg(src + static_cast<long long>(d) * p.ppi) : 0.f;
+  }
+  int c = 0, rank = 0;
+  if (cq == 0) {
+    c = live ? load_class(p.cls, p.cls64, i, p.C) : (MAX_BINS + lane);  // dead lanes: unique keys
+    const uint32_t peers = __match_any_sync(0xffffffffu, c);
+    rank = __popc(peers & ((1u << lane) - 1u));
+    if (live && rank == 0) warp_hist[pg][c] = __popc(peers);
+  }
+  float ss = 0.f;
+#pragma unroll
+  for (int d = 0; d < DQ; ++d) ss = fmaf(v[d], v[d], ss);
+  ss_sm[cq][pg * 32 + lane] = ss;
+  __syncthreads();
+  if (cq == 0 && live) {
+    uint32_t off = p.chunk_off[static_cast<size_t>(blockIdx.x) * MAX_BINS + c];
+    for (int w = 0; w < pg; ++w) off += warp_hist[w][c];
+    const int dest = static_cast<int>(off) + rank;
+    dest_sm[pg * 32 + lane] = dest;
+    p.perm[i] = dest;
+    p.bits[dest] = (c < p.C) ? (1u << c) : 0u;
+  }
+  const int px = pg * 32 + lane;
+  const float tot = (ss_sm[0][px] + ss_sm[1][px]) + (ss_sm[2][px] + ss_sm[3][px]);
+  const float inv = 1.f / fmaxf(sqrtf(tot), p.eps);
+  uint32_t* tile = smem_u + px * ROW_W + cq * (DQ / 2);
+#pragma unroll
+  for (int d = 0; d < DQ; d += 2) tile[d >> 1] = pack_bf16x2(v[d] * inv, v[d + 1] * inv);
+  __syncthreads();
+  if (cq == 0 && live) p.inv_norm[dest_sm[px]] = inv;
+  // rows out: warp w writes rows w, w+16, ... (a full 2*D-byte row per step, coalesced)
+  const int n_live = static_cast<int>(min(static_cast<long long>(SORT_CHUNK),
+                                          p.n - static_cast<long long>(blockIdx.x) * SORT_CHUNK));
+  for (int r = warp; r < n_live; r += PREP_THREADS / 32) {
+    const uint32_t* trow = smem_u + r * ROW_W;
+    uint32_t* out = reinterpret_cast<uint32_t*>(p.ehat + static_cast<size_t>(dest_sm[r]) * D);
+#pragma unroll
+    for (int k = 0; k < WPR; ++k) out[lane + 32 * k] = trow[lane + 32 * k];
+  }
+}
+
 // ------------------------------------------------------------------------------------------
-// Segmented column sums over the class-sorted rows.  One block per 128-row tile; a tile is cut
+// Segmented column sums over the class-sorted rows.  One block per SEG_ROWS rows; a block is cut
 // into at most a few single-class pieces at the segment starts, every piece is reduced in
 // registers + shared memory and leaves the block as one atomicAdd per channel.
 constexpr int SEG_THREADS = 256;
+constexpr int SEG_ROWS = 64;      // sorted rows per block (small blocks: these kernels are latency bound)
 
 template <int D>
 __device__ __forceinline__ void load_row8(const __nv_bfloat16* row, int l, float (&v)[8]) {
@@ -253,7 +322,7 @@ __global__ void __launch_bounds__(SEG_THREADS) class_sum_kernel(const __nv_bfloa
   constexpr int RPP = SEG_THREADS / TPR;
   __shared__ float red[RPP * D];
   const int sub = threadIdx.x / TPR, l = threadIdx.x % TPR;
-  const long long r0 = static_cast<long long>(blockIdx.x) * 128, r1 = r0 + 128;
+  const long long r0 = static_cast<long long>(blockIdx.x) * SEG_ROWS, r1 = r0 + SEG_ROWS;
   for (int c = 0; c < C; ++c) {
     const long long lo = max(r0, static_cast<long long>(seg[c]));
     const long long hi = min(r1, static_cast<long long>(seg[c + 1]));
@@ -291,7 +360,7 @@ __global__ void __launch_bounds__(SEG_THREADS) mid_kernel(const MidParams p) {
   __shared__ float red[RPP * D];
   __shared__ double loss_sh[SEG_THREADS / 32];
   const int sub = threadIdx.x / TPR, l = threadIdx.x % TPR;
-  const long long r0 = static_cast<long long>(blockIdx.x) * 128, r1 = r0 + 128;
+  const long long r0 = static_cast<long long>(blockIdx.x) * SEG_ROWS, r1 = r0 + SEG_ROWS;
   const float bt = p.inv_tau;  // the shift used by the pair passes: exp((s - 1)/tau)
   double loss = 0.0;
   for (int c = 0; c < p.C; ++c) {
