@@ -377,6 +377,7 @@ __global__ void __launch_bounds__(SEG_THREADS) mid_kernel(const MidParams p) {
       const bool on = r < hi;
       float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       if (on) load_row8<D>(p.ehat + r * D, l, v);
+      const float rs_in = on ? p.rowsum[r] : 0.f;   // issued with the row: off the shuffle chain
       float dot = 0.f;
 #pragma unroll
       for (int i = 0; i < 8; ++i) dot = fmaf(v[i], proto[i], dot);
@@ -385,7 +386,7 @@ __global__ void __launch_bounds__(SEG_THREADS) mid_kernel(const MidParams p) {
       if (on) {
         const float pos = dot * p.inv_tau;
         const float ep = __expf(pos - bt);
-        const float rs = p.rowsum[r] + ep;
+        const float rs = rs_in + ep;
         const float w = 1.f / rs;
         const float g = (ep * w - 1.f) * p.inv_tau;
 #pragma unroll
@@ -476,24 +477,44 @@ __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams 
   const uint32_t per = pair_units_per_cta(__ldg(p.unit_off + p.n_row_blocks), p.n_ctas, p.n_col_tiles);
   const long long blk0 = static_cast<long long>(blockIdx.x) * SORT_CHUNK;
 
-  auto row_grad = [&](long long i, float (&g)[EPL]) {   // i = source pixel (< p.n)
-    const long long q = p.perm[i];
-    const uint32_t bq = __ldg(p.bits + q);
+  // Per-row scalars of this warp's rows, fetched up front by lane (r mod 8 = row): the dependent
+  // chain perm -> bits / unit_off / gpos / inv_norm is paid once per warp instead of once per row.
+  static_assert(FINAL_ROWS_PER_WARP == 8, "lane & 7 = row of the warp");
+  const long long my_i = blk0 + warp * FINAL_ROWS_PER_WARP + (lane & 7);
+  long long q_l = 0;
+  uint32_t bq_l = 0u;
+  int ns_l = 0;
+  float gq_l = 0.f, inv_l = 0.f, im_l = 0.f;
+  if (my_i < p.n) {
+    q_l = p.perm[my_i];
+    bq_l = __ldg(p.bits + q_l);
+    if (bq_l) {
+      // the row block's live units were shared by CTAs U0/per .. (U1-1)/per, one slot each
+      const int rbk = static_cast<int>(q_l / RB);
+      const uint32_t U0 = __ldg(p.unit_off + rbk), U1 = __ldg(p.unit_off + rbk + 1);
+      ns_l = (U1 > U0) ? static_cast<int>((U1 - 1) / per - U0 / per + 1) : 0;
+      im_l = 1.f / __ldg(p.class_mass + class_of_bits(bq_l));
+      gq_l = __ldg(p.gpos + q_l) * im_l;
+      inv_l = __ldg(p.inv_norm + q_l);
+    }
+  }
+
+  auto row_grad = [&](int r, float (&g)[EPL]) {   // r = row of the warp (its pixel is < p.n)
+    const long long q = __shfl_sync(0xffffffffu, q_l, r);
+    const uint32_t bq = __shfl_sync(0xffffffffu, bq_l, r);
+    const int n_slots = __shfl_sync(0xffffffffu, ns_l, r);
+    const float gq = __shfl_sync(0xffffffffu, gq_l, r);
+    const float inv = __shfl_sync(0xffffffffu, inv_l, r);
+    const float inv_mass = __shfl_sync(0xffffffffu, im_l, r);
 #pragma unroll
     for (int k = 0; k < EPL; ++k) g[k] = 0.f;
     if (!bq) return;
     const int c = class_of_bits(bq);
-    // the row block's live units were shared by CTAs U0/per .. (U1-1)/per, one slot each
-    const int rbk = static_cast<int>(q / RB);
-    const uint32_t U0 = __ldg(p.unit_off + rbk), U1 = __ldg(p.unit_off + rbk + 1);
-    const int n_slots = (U1 > U0) ? static_cast<int>((U1 - 1) / per - U0 / per + 1) : 0;
     for (int s = 0; s < n_slots; ++s) {
       const float* src = p.part + (static_cast<long long>(s) * p.rows_pad + q) * D + lane;
 #pragma unroll
       for (int k = 0; k < EPL; ++k) g[k] += __ldg(src + 32 * k);
     }
-    const float inv_mass = 1.f / __ldg(p.class_mass + c);
-    const float gq = __ldg(p.gpos + q) * inv_mass;
     float e[EPL];
     float dot = 0.f;
 #pragma unroll
@@ -504,7 +525,6 @@ __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams 
       dot = fmaf(g[k], e[k], dot);
     }
     dot = warp_sum(dot);
-    const float inv = __ldg(p.inv_norm + q);
 #pragma unroll
     for (int k = 0; k < EPL; ++k) g[k] = inv * (g[k] - e[k] * dot);
   };
@@ -514,8 +534,8 @@ __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams 
     const int l0 = warp * FINAL_ROWS_PER_WARP + r, l1 = l0 + 1;   // local pixel index within the block
     const long long i0 = blk0 + l0, i1 = blk0 + l1;
     float g0[EPL], g1[EPL];
-    if (i0 < p.n) row_grad(i0, g0);
-    if (i1 < p.n) row_grad(i1, g1);
+    if (i0 < p.n) row_grad(r, g0);       // warp-uniform conditions: the shuffles stay converged
+    if (i1 < p.n) row_grad(r + 1, g1);
     if (p.layout == MUSCLE_LAYOUT_NCHW) {
 #pragma unroll
       for (int k = 0; k < EPL; ++k) {
