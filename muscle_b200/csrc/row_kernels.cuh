@@ -82,9 +82,11 @@ __global__ void __launch_bounds__(1024) class_scan_kernel(uint32_t* hist, int n_
   // pass 2: exclusive scan over chunks, 32 chunks at a time
   if (warp <= C) {
     uint32_t run = start[warp];
+    uint32_t v_next = (lane < n_blk) ? hist[static_cast<size_t>(lane) * MAX_BINS + warp] : 0u;
     for (int b0 = 0; b0 < n_blk; b0 += 32) {
       const int b = b0 + lane;
-      const uint32_t v = (b < n_blk) ? hist[static_cast<size_t>(b) * MAX_BINS + warp] : 0u;
+      const uint32_t v = v_next;   // the next 32 chunks are fetched under this round's scan
+      v_next = (b + 32 < n_blk) ? hist[static_cast<size_t>(b + 32) * MAX_BINS + warp] : 0u;
       uint32_t inc = v;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {

@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """Device-time table of every op on the path besides the dense InfoNCE (which bench.py measures):
 CUDA-event timing on the launching stream, L2 flushed between iterations, fwd+bwd through the
-public Python mirrors.  Prints one JSON object; profiles/ keeps a copy per round.
+public Python mirrors; beside each, the oracle (the CPU restatement of the reference, fp32 torch
+on all host cores) timed on the same inputs as the reported CPU baseline (bounded: a few
+repeats).  Prints one JSON object; profiles/ keeps a copy per round.
 
     python scripts/bench_ops.py [--iters 20]
 """
@@ -45,6 +47,26 @@ def main():
         torch.cuda.synchronize()
         return sum(x.elapsed_time(y) for x, y in evs) / len(evs)
 
+    import time
+    from oracle import muscle_oracle as O   # CPU baseline legs + synthetic label generator
+
+    def cpu_timed(fn, budget_s=6.0, max_reps=5):
+        fn()
+        t, reps = 0.0, 0
+        while t < budget_s and reps < max_reps:
+            t0 = time.perf_counter(); fn(); t += time.perf_counter() - t0; reps += 1
+        return 1e3 * t / reps
+
+    def beside(entry, cpu_ms):
+        entry["cpu_ms"] = cpu_ms
+        entry["cpu_cores"] = torch.get_num_threads()
+        entry["cpu_kind"] = "port (oracle, fp32 torch CPU, same inputs)"
+        entry["gpu_over_cpu"] = cpu_ms / entry["ms"]
+        return entry
+
+    def cpu_leaf(t):
+        return t.detach().cpu().requires_grad_()
+
     out = {}
     # ---- PCM + CAM head, config 2 at stride 8 (B=8, 56x56, b7: Cin=336, p7 ch=640)
     B, P_h = 8, 56
@@ -61,8 +83,14 @@ def main():
     ms = timed(pcm_step)
     pairs = B * (P_h * P_h) ** 2
     flops = pairs * 2.0 * (128 + 32) + pairs * 2.0 * (128 + 32) + pairs * 2.0 * (128 + 128 + 128)   # fwd, dcam, bwd
-    out["pcm_fwd_bwd_config2_stride8"] = dict(ms=ms, pixel_pairs_per_s=pairs / ms * 1e3, executed_tflops=flops / ms / 1e9,
-                                              frac_of_bf16_burst=flops / ms / 1e9 / peaks["bf16_tflops"], bound="tensor")
+    cam_c, wt_c, b_c, f_c, go_c = cpu_leaf(cam), cpu_leaf(wt), cpu_leaf(bias), f.cpu(), go.cpu()
+
+    def pcm_cpu():
+        O.pcm(cam_c, f_c, wt_c, b_c).backward(go_c)
+        cam_c.grad = wt_c.grad = b_c.grad = None
+    out["pcm_fwd_bwd_config2_stride8"] = beside(dict(ms=ms, pixel_pairs_per_s=pairs / ms * 1e3, executed_tflops=flops / ms / 1e9,
+                                                     frac_of_bf16_burst=flops / ms / 1e9 / peaks["bf16_tflops"], bound="tensor"),
+                                                cpu_timed(pcm_cpu))
     p7 = torch.relu(torch.randn(B, 640, P_h, P_h, generator=gen)).to(dev).requires_grad_()
     fw = (torch.randn(21, 640, generator=gen) * 0.05).to(dev).requires_grad_()
     gcam = torch.randn(B, 21, P_h, P_h, generator=gen).to(dev)
@@ -74,11 +102,18 @@ def main():
         p7.grad = fw.grad = None
     ms = timed(cam_step)
     byt = p7.numel() * 4 * 4 + B * 21 * P_h * P_h * 4 * 3      # p7 read x2 (cam, gap), dp7 written x2, cam w + r, dcam r
-    out["cam_head_gap_logits_fwd_bwd"] = dict(ms=ms, algorithmic_gb_s=byt / ms / 1e6, frac_of_hbm=byt / ms / 1e6 / peaks["hbm_gbs"],
-                                             bound="hbm")
+    p7_c, fw_c, gcam_c = cpu_leaf(p7), cpu_leaf(fw), gcam.cpu()
+
+    def cam_cpu():
+        c = O.cam_head(p7_c, fw_c)
+        e, l = O.image_embedding_logits(p7_c, fw_c)
+        torch.autograd.backward([c, l], [gcam_c, torch.ones_like(l)])
+        p7_c.grad = fw_c.grad = None
+    out["cam_head_gap_logits_fwd_bwd"] = beside(dict(ms=ms, algorithmic_gb_s=byt / ms / 1e6,
+                                                     frac_of_hbm=byt / ms / 1e6 / peaks["hbm_gbs"], bound="hbm"),
+                                                cpu_timed(cam_cpu))
     # ---- IMC, B=64 images, ch=640
     emb = torch.randn(64, 640, generator=gen).abs().to(dev).requires_grad_()
-    from oracle import muscle_oracle as O   # synthetic label generator only
     lab = O.synth_labels(64, gen).to(dev)
 
     def imc_step():
@@ -86,7 +121,14 @@ def main():
         if torch.is_tensor(l):
             l.backward()
         emb.grad = None
-    out["imc_fwd_bwd_B64"] = dict(ms=timed(imc_step), bound="latency")
+    emb_c, lab_c = cpu_leaf(emb), lab.cpu()
+
+    def imc_cpu():
+        l = O.image_level_contrast(emb_c, lab_c)
+        if torch.is_tensor(l):
+            l.backward()
+        emb_c.grad = None
+    out["imc_fwd_bwd_B64"] = beside(dict(ms=timed(imc_step), bound="latency"), cpu_timed(imc_cpu))
     # ---- PixPro, B=8, 21x224x224
     fm1 = torch.rand(8, 21, 224, 224, generator=gen).to(dev).requires_grad_()
     fm2 = torch.rand(8, 21, 224, 224, generator=gen).to(dev)
@@ -99,7 +141,12 @@ def main():
         fm1.grad = None
     ms = timed(pix_step)
     byt = float((hw[:, 0] * hw[:, 1]).sum()) * 21 * 4 * 3 + fm1.numel() * 4
-    out["pixpro_fwd_bwd_B8"] = dict(ms=ms, algorithmic_gb_s=byt / ms / 1e6, bound="hbm/latency")
+    fm1_c, fm2_c = cpu_leaf(fm1), fm2.cpu()
+
+    def pix_cpu():
+        O.pixpro(fm1_c, fm2_c, c1, c2).backward()
+        fm1_c.grad = None
+    out["pixpro_fwd_bwd_B8"] = beside(dict(ms=ms, algorithmic_gb_s=byt / ms / 1e6, bound="hbm/latency"), cpu_timed(pix_cpu))
     # ---- crops + EMD dynamic, B=8
     raw1 = F.avg_pool2d(torch.randn(8, 21, 224, 224, generator=gen), 9, 1, 4).to(dev).requires_grad_()
     raw2 = F.avg_pool2d(torch.randn(8, 21, 224, 224, generator=gen), 9, 1, 4).to(dev)
@@ -111,7 +158,15 @@ def main():
         a, b, _ = get_dynamic_crops(v1, c1, v2.detach(), c2)
         EMD()(a, b, mode="dynamic").backward()
         raw1.grad = None
-    out["crops_emd_dynamic_fwd_bwd_B8"] = dict(ms=timed(emd_step), bound="latency")
+    raw1_c, raw2_c = cpu_leaf(raw1), raw2.cpu()
+
+    def emd_cpu():
+        v1 = F.normalize(O.cam_softmaxnorm(raw1_c), dim=1)
+        v2 = F.normalize(O.cam_softmaxnorm(raw2_c), dim=1)
+        a, b, _ = O.get_dynamic_crops(v1, c1, v2.detach(), c2, rng=np.random.RandomState(3))
+        O.emd_dynamic(a, b).backward()
+        raw1_c.grad = None
+    out["crops_emd_dynamic_fwd_bwd_B8"] = beside(dict(ms=timed(emd_step), bound="latency"), cpu_timed(emd_cpu))
     # ---- FieldLoss, config 3 scale reduced to B=4 (512x512, 256 ch) to bound memory in this table
     n, h, w, ch = 4, 512, 512, 256
     label = O.synth_labels(n, gen)
@@ -131,8 +186,17 @@ def main():
             l.backward()
         dense.grad = None
     ms = timed(field_step)
-    out["fieldloss_fwd_bwd_B4_512"] = dict(ms=ms, note="includes the one device->host read of the counts and the "
-                                           "memset of the dense gradient (%.0f MB)" % (dense.numel() * 4 / 1e6), bound="hbm/latency")
+    seg_c, mask_c, dense_c = seg.cpu(), mask.cpu(), cpu_leaf(dense)
+
+    def field_cpu():
+        l, _ = O.fieldloss_forward(seg_c, dense_c, mask_c, label_bg, step=7, k=128, beta=1e2, sobel_size=5,
+                                   rng=random.Random(1))
+        if torch.is_tensor(l):
+            l.backward()
+        dense_c.grad = None
+    out["fieldloss_fwd_bwd_B4_512"] = beside(dict(ms=ms, note="includes the one device->host read of the counts and the "
+                                                  "memset of the dense gradient (%.0f MB)" % (dense.numel() * 4 / 1e6),
+                                                  bound="hbm/latency"), cpu_timed(field_cpu, budget_s=10.0, max_reps=2))
     print(json.dumps(out))
 
 
