@@ -55,6 +55,19 @@ int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
                                  float* loss_out, float* dx_out, void* workspace,
                                  size_t workspace_bytes, void* stream);
 
+/* The same op as an autograd pair (what torch.autograd.Function.forward / .backward call): _fwd runs
+ * everything up to the loss and leaves its state in `workspace`; _bwd, given the SAME untouched
+ * workspace and the same shape arguments, runs the gradient pass and writes
+ * dx_out = grad_scale[0] * d(loss)/dx  (grad_scale: device float[1], NULL = 1), so the upstream
+ * gradient costs no extra pass over dx. */
+int muscle_dense_infonce_fwd(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
+                             int dim, const void* cls, int cls_is_int64, int num_classes,
+                             float temperature, float eps, float* loss_out, void* workspace,
+                             size_t workspace_bytes, void* stream);
+int muscle_dense_infonce_bwd(int layout, int64_t batch, int64_t pixels_per_image, int dim,
+                             int num_classes, float temperature, const float* grad_scale,
+                             float* dx_out, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Staged form of the same op, for the batch-sharded multi-GPU path: the host
  * runs  prepare -> [all-gather ehat/bits/tor, all-reduce class_sum/class_mass] -> plan ->
@@ -118,13 +131,15 @@ int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows,
 
 /* dx = d(loss)/dx in the caller's pixel order and `layout`: sums the slots, adds the prototype
  * terms, back-propagates through the L2 normalisation.  loss_out = loss_acc / n_valid
- * (n_valid = sum of class_mass).  dx may be NULL (loss only). */
+ * (n_valid = sum of class_mass).  dx may be NULL (loss only); loss_out may be NULL (gradient only).
+ * grad_scale: device pointer to the upstream gradient of the (scalar) loss, multiplied into dx
+ * inside the kernel — what autograd hands to backward(); NULL = 1. */
 int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* inv_norm,
                          const int32_t* perm, const float* part, const uint32_t* unit_off,
                          int64_t rows_pad, int64_t cols_pad, int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
                          const float* class_sum, const float* class_mass, const float* gpos,
                          const float* dproto, const double* loss_acc, float temperature,
-                         int layout, float* dx, float* loss_out, void* stream);
+                         int layout, float* dx, float* loss_out, const float* grad_scale, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * info_nce — replaces src/loss_multilabel.py:9-21 with distinct operand sets: query [Q, dim],

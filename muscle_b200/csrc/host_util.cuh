@@ -65,6 +65,14 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 inline EncodeTiledFn encode_tiled_fn() {
+  // cuTensorMapEncodeTiled is a driver call and needs the primary context current on THIS thread;
+  // a thread that has only been handed device pointers (autograd's backward thread) has none until
+  // its first runtime call that touches the device (CUDA_ERROR_INVALID_CONTEXT otherwise).
+  static thread_local bool bound = false;
+  if (!bound) {
+    cudaFree(nullptr);
+    bound = true;
+  }
   static EncodeTiledFn fn = nullptr;
   if (!fn) {
     void* p = nullptr;

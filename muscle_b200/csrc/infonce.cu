@@ -286,7 +286,7 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
                          int64_t rows_pad, int64_t cols_pad, int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
                          const float* class_sum, const float* class_mass, const float* gpos,
                          const float* dproto, const double* loss_acc, float temperature,
-                         int layout, float* dx, float* loss_out, void* stream_) {
+                         int layout, float* dx, float* loss_out, const float* grad_scale, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_device()) return rc;
   if (!class_mass || !loss_acc) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
@@ -303,7 +303,7 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
   p.n = batch * pixels_per_image; p.ppi = pixels_per_image; p.C = num_classes;
   p.class_sum = class_sum; p.class_mass = class_mass; p.gpos = gpos; p.dproto = dproto;
   p.loss_acc = loss_acc; p.inv_tau = 1.f / temperature; p.layout = layout; p.dx = dx;
-  p.loss_out = loss_out;
+  p.loss_out = loss_out; p.grad_scale = grad_scale;
   const size_t smem = (dx && layout == MUSCLE_LAYOUT_NCHW)
                           ? static_cast<size_t>(SORT_CHUNK) * (dim + 1) * sizeof(float) : 0;
   const int grid = dx ? static_cast<int>((p.n + SORT_CHUNK - 1) / SORT_CHUNK) : 1;
@@ -373,14 +373,40 @@ size_t muscle_dense_infonce_workspace_bytes(int64_t n_pixels, int dim, int num_c
   return plan_workspace(n_pixels, dim, num_classes).total;
 }
 
-int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
-                                 int64_t pixels_per_image, int dim, const void* cls,
-                                 int cls_is_int64, int num_classes, float temperature, float eps,
-                                 float* loss_out, float* dx_out, void* workspace,
-                                 size_t workspace_bytes, void* stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+namespace {
+// the composite's view of its workspace
+struct Carved {
+  void* ehat; uint32_t* bits; float* inv_norm; int32_t* perm; uint32_t* tor; uint32_t* unit_off;
+  float *rowsum, *w, *gpos, *class_sum, *class_mass, *dproto, *part;
+  double* loss_acc; uint32_t* seg; char* scratch;
+};
+Carved carve(void* workspace, const Workspace& ws) {
+  char* base = static_cast<char*>(workspace);
+  char* small = base + ws.small;
+  Carved c;
+  c.ehat = base + ws.ehat;
+  c.bits = reinterpret_cast<uint32_t*>(base + ws.bits);
+  c.inv_norm = reinterpret_cast<float*>(base + ws.inv_norm);
+  c.perm = reinterpret_cast<int32_t*>(base + ws.perm);
+  c.tor = reinterpret_cast<uint32_t*>(base + ws.tor);
+  c.unit_off = reinterpret_cast<uint32_t*>(base + ws.unit_off);
+  c.rowsum = reinterpret_cast<float*>(base + ws.rowsum);
+  c.w = reinterpret_cast<float*>(base + ws.w);
+  c.gpos = reinterpret_cast<float*>(base + ws.gpos);
+  c.class_sum = reinterpret_cast<float*>(small + ws.class_sum);
+  c.class_mass = reinterpret_cast<float*>(small + ws.class_mass);
+  c.dproto = reinterpret_cast<float*>(small + ws.dproto);
+  c.loss_acc = reinterpret_cast<double*>(small + ws.loss_acc);
+  c.seg = reinterpret_cast<uint32_t*>(small + ws.seg);
+  c.part = reinterpret_cast<float*>(base + ws.part);
+  c.scratch = base + ws.scratch;
+  return c;
+}
+
+int check_composite(int dim, int num_classes, float temperature, int64_t batch, int64_t pixels_per_image,
+                    const void* workspace, size_t workspace_bytes, Workspace* ws) {
   if (int rc = check_device()) return rc;
-  if (!x || !cls || !loss_out || !workspace) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (!workspace) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
   if (num_classes < 1 || num_classes > MUSCLE_MAX_CLASSES)
     return fail(MUSCLE_ERR_BAD_ARG, "num_classes must be in [1,%d]", MUSCLE_MAX_CLASSES);
@@ -388,50 +414,94 @@ int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
   if (batch <= 0 || pixels_per_image <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty input");
   if ((reinterpret_cast<uintptr_t>(workspace) & 255) != 0)
     return fail(MUSCLE_ERR_BAD_ARG, "workspace must be 256-byte aligned");
-  const int64_t n = batch * pixels_per_image;
-  const Workspace ws = plan_workspace(n, dim, num_classes);
-  if (workspace_bytes < ws.total)
-    return fail(MUSCLE_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, ws.total);
-  char* base = static_cast<char*>(workspace);
-  void* ehat = base + ws.ehat;
-  uint32_t* bits = reinterpret_cast<uint32_t*>(base + ws.bits);
-  float* inv_norm = reinterpret_cast<float*>(base + ws.inv_norm);
-  int32_t* perm = reinterpret_cast<int32_t*>(base + ws.perm);
-  uint32_t* tor = reinterpret_cast<uint32_t*>(base + ws.tor);
-  uint32_t* unit_off = reinterpret_cast<uint32_t*>(base + ws.unit_off);
-  float* rowsum = reinterpret_cast<float*>(base + ws.rowsum);
-  float* w = reinterpret_cast<float*>(base + ws.w);
-  float* gpos = reinterpret_cast<float*>(base + ws.gpos);
-  char* small = base + ws.small;
-  float* class_sum = reinterpret_cast<float*>(small + ws.class_sum);
-  float* class_mass = reinterpret_cast<float*>(small + ws.class_mass);
-  float* dproto = reinterpret_cast<float*>(small + ws.dproto);
-  double* loss_acc = reinterpret_cast<double*>(small + ws.loss_acc);
-  uint32_t* seg = reinterpret_cast<uint32_t*>(small + ws.seg);
-  float* part = reinterpret_cast<float*>(base + ws.part);
+  *ws = plan_workspace(batch * pixels_per_image, dim, num_classes);
+  if (workspace_bytes < ws->total)
+    return fail(MUSCLE_ERR_WORKSPACE, "workspace too small: %zu < %zu", workspace_bytes, ws->total);
+  return MUSCLE_OK;
+}
 
-  MB_CUDA(cudaMemsetAsync(base + ws.zero_lo, 0, ws.zero_bytes, stream));
+// prepare -> plan -> row sums -> mid: everything the loss needs
+int composite_forward(const float* x, int layout, int64_t batch, int64_t pixels_per_image, int dim,
+                      const void* cls, int cls_is_int64, int num_classes, float temperature, float eps,
+                      void* workspace, const Workspace& ws, const Carved& c, cudaStream_t stream) {
+  const int64_t n = batch * pixels_per_image;
+  MB_CUDA(cudaMemsetAsync(static_cast<char*>(workspace) + ws.zero_lo, 0, ws.zero_bytes, stream));
   int rc = muscle_infonce_prepare(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64,
-                                  num_classes, eps, ehat, bits, inv_norm, perm, tor, seg, class_sum,
-                                  class_mass, base + ws.scratch,
+                                  num_classes, eps, c.ehat, c.bits, c.inv_norm, c.perm, c.tor, c.seg,
+                                  c.class_sum, c.class_mass, c.scratch,
                                   muscle_infonce_prepare_scratch_bytes(n), stream);
   if (rc) return rc;
-  rc = muscle_infonce_plan(tor, ws.rows_pad, tor, ws.rows_pad, dim, unit_off, stream);
+  rc = muscle_infonce_plan(c.tor, ws.rows_pad, c.tor, ws.rows_pad, dim, c.unit_off, stream);
   if (rc) return rc;
-  rc = muscle_infonce_rowsum(ehat, bits, tor, ws.rows_pad, ehat, bits, tor, ws.rows_pad, unit_off,
-                             dim, temperature, rowsum, stream);
+  rc = muscle_infonce_rowsum(c.ehat, c.bits, c.tor, ws.rows_pad, c.ehat, c.bits, c.tor, ws.rows_pad,
+                             c.unit_off, dim, temperature, c.rowsum, stream);
   if (rc) return rc;
-  rc = muscle_infonce_mid(ehat, seg, ws.rows_pad, dim, num_classes, class_sum, class_mass, rowsum,
-                          temperature, w, gpos, loss_acc, dproto, stream);
-  if (rc) return rc;
+  return muscle_infonce_mid(c.ehat, c.seg, ws.rows_pad, dim, num_classes, c.class_sum, c.class_mass,
+                            c.rowsum, temperature, c.w, c.gpos, c.loss_acc, c.dproto, stream);
+}
+
+// gradient pass + final (dx may be null: loss only)
+int composite_backward(int layout, int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
+                       float temperature, const float* grad_scale, float* dx_out, float* loss_out,
+                       const Workspace& ws, const Carved& c, cudaStream_t stream) {
   if (dx_out) {
-    rc = muscle_infonce_grad(ehat, bits, tor, w, ws.rows_pad, ehat, bits, tor, w, ws.rows_pad,
-                             unit_off, dim, temperature, part, stream);
+    int rc = muscle_infonce_grad(c.ehat, c.bits, c.tor, c.w, ws.rows_pad, c.ehat, c.bits, c.tor, c.w,
+                                 ws.rows_pad, c.unit_off, dim, temperature, c.part, stream);
     if (rc) return rc;
   }
-  return muscle_infonce_final(ehat, bits, inv_norm, perm, part, unit_off, ws.rows_pad, ws.rows_pad,
-                              batch, pixels_per_image, dim, num_classes, class_sum, class_mass, gpos,
-                              dproto, loss_acc, temperature, layout, dx_out, loss_out, stream);
+  return muscle_infonce_final(c.ehat, c.bits, c.inv_norm, c.perm, c.part, c.unit_off, ws.rows_pad,
+                              ws.rows_pad, batch, pixels_per_image, dim, num_classes, c.class_sum,
+                              c.class_mass, c.gpos, c.dproto, c.loss_acc, temperature, layout, dx_out,
+                              loss_out, grad_scale, stream);
+}
+}  // namespace
+
+int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
+                                 int64_t pixels_per_image, int dim, const void* cls,
+                                 int cls_is_int64, int num_classes, float temperature, float eps,
+                                 float* loss_out, float* dx_out, void* workspace,
+                                 size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!x || !cls || !loss_out) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  Workspace ws;
+  if (int rc = check_composite(dim, num_classes, temperature, batch, pixels_per_image, workspace, workspace_bytes, &ws))
+    return rc;
+  const Carved c = carve(workspace, ws);
+  if (int rc = composite_forward(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes,
+                                 temperature, eps, workspace, ws, c, stream))
+    return rc;
+  return composite_backward(layout, batch, pixels_per_image, dim, num_classes, temperature, nullptr, dx_out,
+                            loss_out, ws, c, stream);
+}
+
+int muscle_dense_infonce_fwd(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
+                             int dim, const void* cls, int cls_is_int64, int num_classes,
+                             float temperature, float eps, float* loss_out, void* workspace,
+                             size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!x || !cls || !loss_out) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  Workspace ws;
+  if (int rc = check_composite(dim, num_classes, temperature, batch, pixels_per_image, workspace, workspace_bytes, &ws))
+    return rc;
+  const Carved c = carve(workspace, ws);
+  if (int rc = composite_forward(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes,
+                                 temperature, eps, workspace, ws, c, stream))
+    return rc;
+  return composite_backward(layout, batch, pixels_per_image, dim, num_classes, temperature, nullptr, nullptr,
+                            loss_out, ws, c, stream);
+}
+
+int muscle_dense_infonce_bwd(int layout, int64_t batch, int64_t pixels_per_image, int dim,
+                             int num_classes, float temperature, const float* grad_scale,
+                             float* dx_out, void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!dx_out) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  Workspace ws;
+  if (int rc = check_composite(dim, num_classes, temperature, batch, pixels_per_image, workspace, workspace_bytes, &ws))
+    return rc;
+  const Carved c = carve(workspace, ws);
+  return composite_backward(layout, batch, pixels_per_image, dim, num_classes, temperature, grad_scale, dx_out,
+                            nullptr, ws, c, stream);
 }
 
 }  // extern "C"

@@ -447,6 +447,7 @@ struct FinalParams {
   int layout;
   float* dx;                   // source order, `layout`
   float* loss_out;
+  const float* grad_scale;     // upstream gradient of the loss (device scalar), or null = 1
 };
 
 // One block = 128 consecutive source pixels, 16 warps of 8 pixels each (two pixels in flight per
@@ -474,7 +475,7 @@ __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams 
   }
   __syncthreads();
   if (p.dx == nullptr) return;
-  const float inv_n = n_valid_sh > 0.f ? 1.f / n_valid_sh : 0.f;
+  const float inv_n = (n_valid_sh > 0.f ? 1.f / n_valid_sh : 0.f) * (p.grad_scale ? __ldg(p.grad_scale) : 1.f);
   constexpr int RB = 128;  // rows per row block of the pair passes (PAIR_RB)
   const uint32_t per = pair_units_per_cta(__ldg(p.unit_off + p.n_row_blocks), p.n_ctas, p.n_col_tiles);
   const long long blk0 = static_cast<long long>(blockIdx.x) * SORT_CHUNK;

@@ -36,8 +36,8 @@ def _all_gather_into(out, inp, group):
         dist.all_gather(list(out.chunk(g, dim=0)), inp, group=group)
 
 
-def sharded_fwd_bwd(stages, x, cls, temperature, num_classes, eps, need_grad, group=None):
-    """Runs the staged op on this rank.  -> (loss 0-dim tensor, dx or None).  `stages` is a
+def sharded_fwd(stages, x, cls, temperature, num_classes, eps, need_grad, group=None):
+    """Runs the forward stages on this rank.  -> (loss 0-dim tensor, state for `sharded_bwd` or None).  `stages` is a
     CudaStages (or the CPU stand-in the gloo tests use)."""
     G, rank = _world(group)
     xc, layout, batch, ppi, dim = _as_feature_operand(x)
@@ -91,20 +91,42 @@ def sharded_fwd_bwd(stages, x, cls, temperature, num_classes, eps, need_grad, gr
     stages.mid(ehat, seg, rows_pad, dim, C, class_sum, class_mass, rowsum, temperature, w, gpos, loss_acc, dproto)
     if G > 1:
         dist.all_reduce(loss_acc, group=group)
-    dx = None
+    part0 = stages.empty((1,), f32)
+    stages.final(ehat, bits, inv_norm, perm, part0, unit_off, rows_pad, cols_pad, batch, ppi, dim, C, class_sum,
+                 class_mass, gpos, dproto, loss_acc, temperature, layout, None, loss)
+    state = None
     if need_grad:
-        if G > 1:
-            dist.all_reduce(dproto, group=group)
-            _all_gather_into(w_all, w, group)
-        part = stages.empty((stages.part_slots(), rows_pad, dim), f32)
-        stages.grad(ehat, bits, tor, w, rows_pad, ehat_all, bits_all, tor_all, w_all, cols_pad, unit_off, dim,
-                    temperature, part)
-        dx = stages.empty(tuple(xc.shape), f32)
-    else:
-        part = stages.empty((1,), f32)
-    stages.final(ehat, bits, inv_norm, perm, part, unit_off, rows_pad, cols_pad, batch, ppi, dim, C, class_sum,
-                 class_mass, gpos, dproto, loss_acc, temperature, layout, dx, loss)
-    return loss, dx
+        state = dict(G=G, group=group, xc_shape=tuple(xc.shape), layout=layout, batch=batch, ppi=ppi, dim=dim, C=C,
+                     temperature=temperature, rows_pad=rows_pad, cols_pad=cols_pad, ehat=ehat, bits=bits, tor=tor,
+                     w=w, ehat_all=ehat_all, bits_all=bits_all, tor_all=tor_all, w_all=w_all, inv_norm=inv_norm,
+                     perm=perm, unit_off=unit_off, class_sum=class_sum, class_mass=class_mass, gpos=gpos,
+                     dproto=dproto, loss_acc=loss_acc)
+    return loss, state
+
+
+def sharded_bwd(stages, st, grad_scale=None):
+    """The gradient half: all-gather of `w` (N_g floats) and all-reduce of the prototype gradient, the
+    gradient pass, and the final kernel with the upstream gradient `grad_scale` (0-dim tensor or None)
+    multiplied in.  -> dx in the layout of the forward input."""
+    f32 = torch.float32
+    if st["G"] > 1:
+        dist.all_reduce(st["dproto"], group=st["group"])
+        _all_gather_into(st["w_all"], st["w"], st["group"])
+    dim, rows_pad, cols_pad = st["dim"], st["rows_pad"], st["cols_pad"]
+    part = stages.empty((stages.part_slots(), rows_pad, dim), f32)
+    stages.grad(st["ehat"], st["bits"], st["tor"], st["w"], rows_pad, st["ehat_all"], st["bits_all"], st["tor_all"],
+                st["w_all"], cols_pad, st["unit_off"], dim, st["temperature"], part)
+    dx = stages.empty(st["xc_shape"], f32)
+    stages.final(st["ehat"], st["bits"], st["inv_norm"], st["perm"], part, st["unit_off"], rows_pad, cols_pad,
+                 st["batch"], st["ppi"], dim, st["C"], st["class_sum"], st["class_mass"], st["gpos"], st["dproto"],
+                 st["loss_acc"], st["temperature"], st["layout"], dx, None, grad_scale)
+    return dx
+
+
+def sharded_fwd_bwd(stages, x, cls, temperature, num_classes, eps, need_grad, group=None):
+    """Forward and (if `need_grad`) gradient in one go.  -> (loss 0-dim tensor, dx or None)."""
+    loss, st = sharded_fwd(stages, x, cls, temperature, num_classes, eps, need_grad, group)
+    return loss, (sharded_bwd(stages, st) if st is not None else None)
 
 
 class _ShardedDenseInfoNCE(torch.autograd.Function):
@@ -115,17 +137,20 @@ class _ShardedDenseInfoNCE(torch.autograd.Function):
         if x.dtype != torch.float32:
             raise TypeError("embeddings must be float32")
         stages = CudaStages(x.device)
-        loss, dx = sharded_fwd_bwd(stages, x, cls, temperature, num_classes, eps, x.requires_grad, group)
-        ctx.save_for_backward(dx)
+        loss, st = sharded_fwd(stages, x, cls, temperature, num_classes, eps, x.requires_grad, group)
+        ctx.state, ctx.stages = st, stages
         ctx.x_shape = x.shape
         return loss
 
     @staticmethod
     def backward(ctx, grad_out):
-        (dx,) = ctx.saved_tensors
-        if dx is None:
+        st = ctx.state
+        if st is None:
             return None, None, None, None, None, None
-        return (dx * grad_out).reshape(ctx.x_shape), None, None, None, None, None
+        g = grad_out.detach().to(dtype=torch.float32).reshape(1).contiguous()
+        dx = sharded_bwd(ctx.stages, st, g)
+        ctx.state = None
+        return dx.reshape(ctx.x_shape), None, None, None, None, None
 
 
 def dense_infonce_sharded(x, cls, temperature=0.1, num_classes=21, eps=1e-12, group=None):

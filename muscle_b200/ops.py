@@ -57,23 +57,34 @@ class _DenseInfoNCE(torch.autograd.Function):
                              % (dim, num_classes, _lib.MAX_CLASSES))
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
         loss = torch.empty((), dtype=torch.float32, device=x.device)
-        dx = torch.empty_like(xc) if need_grad else None
+        # forward: prepare -> plan -> row sums -> loss; the gradient pass runs in backward() from the
+        # state kept in `ws`, with the upstream gradient multiplied in by the last kernel
         with torch.cuda.device(x.device):
-            rc = lib.muscle_dense_infonce_fwd_bwd(
+            rc = lib.muscle_dense_infonce_fwd(
                 xc.data_ptr(), layout, batch, ppi, dim, cls_c.data_ptr(), cls64, num_classes,
-                float(temperature), float(eps), loss.data_ptr(), dx.data_ptr() if need_grad else None,
-                ws.data_ptr(), ws_bytes, _stream_ptr(x.device))
+                float(temperature), float(eps), loss.data_ptr(), ws.data_ptr(), ws_bytes, _stream_ptr(x.device))
         _lib.check(rc, "dense_infonce")
-        ctx.save_for_backward(dx)
-        ctx.x_shape = x.shape
+        if need_grad:
+            ctx.ws, ctx.ws_bytes = ws, ws_bytes
+            ctx.args = (layout, batch, ppi, dim, int(num_classes), float(temperature))
+            ctx.x_shape, ctx.xc_shape = x.shape, xc.shape
         return loss
 
     @staticmethod
     def backward(ctx, grad_out):
-        (dx,) = ctx.saved_tensors
-        if dx is None:
+        ws = getattr(ctx, "ws", None)
+        if ws is None:
             return None, None, None, None, None
-        return (dx * grad_out).reshape(ctx.x_shape), None, None, None, None
+        lib = _lib.load()
+        layout, batch, ppi, dim, num_classes, temperature = ctx.args
+        g = grad_out.detach().to(device=ws.device, dtype=torch.float32).reshape(1).contiguous()
+        dx = torch.empty(ctx.xc_shape, dtype=torch.float32, device=ws.device)
+        with torch.cuda.device(ws.device):
+            rc = lib.muscle_dense_infonce_bwd(layout, batch, ppi, dim, num_classes, temperature, g.data_ptr(),
+                                              dx.data_ptr(), ws.data_ptr(), ctx.ws_bytes, _stream_ptr(ws.device))
+        _lib.check(rc, "dense_infonce backward")
+        ctx.ws = None   # the 8-slot partial buffer is the large part of the state: free it now
+        return dx.reshape(ctx.x_shape), None, None, None, None
 
 
 def dense_infonce(x, cls, temperature=0.1, num_classes=21, eps=1e-12):

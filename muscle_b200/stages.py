@@ -86,11 +86,13 @@ class CudaStages:
         _lib.check(rc, "infonce_grad")
 
     def final(self, ehat, bits, inv_norm, perm, part, unit_off, rows_pad, cols_pad, batch, ppi, dim, num_classes,
-              class_sum, class_mass, gpos, dproto, loss_acc, temperature, layout, dx, loss_out):
+              class_sum, class_mass, gpos, dproto, loss_acc, temperature, layout, dx, loss_out, grad_scale=None):
         with torch.cuda.device(self.device):
             rc = self.lib.muscle_infonce_final(
                 ehat.data_ptr(), bits.data_ptr(), inv_norm.data_ptr(), perm.data_ptr(), part.data_ptr(),
                 unit_off.data_ptr(), rows_pad, cols_pad, batch, ppi, dim, num_classes, class_sum.data_ptr(),
                 class_mass.data_ptr(), gpos.data_ptr(), dproto.data_ptr(), loss_acc.data_ptr(), float(temperature),
-                layout, dx.data_ptr() if dx is not None else None, loss_out.data_ptr(), _sp(self.device))
+                layout, dx.data_ptr() if dx is not None else None,
+                loss_out.data_ptr() if loss_out is not None else None,
+                grad_scale.data_ptr() if grad_scale is not None else None, _sp(self.device))
         _lib.check(rc, "infonce_final")

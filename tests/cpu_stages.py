@@ -120,9 +120,10 @@ class CpuStages:
         part[0] = t @ ehat_cols.float()
 
     def final(self, ehat, bits, inv_norm, perm, part, unit_off, rows_pad, cols_pad, batch, ppi, dim, num_classes,
-              class_sum, class_mass, gpos, dproto, loss_acc, temperature, layout, dx, loss_out):
+              class_sum, class_mass, gpos, dproto, loss_acc, temperature, layout, dx, loss_out, grad_scale=None):
         n_valid = class_mass.sum()
-        loss_out.copy_((loss_acc[0] / n_valid.double()).float())
+        if loss_out is not None:
+            loss_out.copy_((loss_acc[0] / n_valid.double()).float())
         if dx is None:
             return
         n = batch * ppi
@@ -138,6 +139,8 @@ class CpuStages:
         g = g / n_valid
         g = inv_norm[q][:, None] * (g - e * (g * e).sum(1, keepdim=True))
         g = g * ok[:, None]
+        if grad_scale is not None:
+            g = g * grad_scale.reshape(()).float()
         if layout == 1:
             dx.copy_(g.reshape(batch, ppi, dim).permute(0, 2, 1).reshape(dx.shape))
         else:

@@ -106,6 +106,38 @@ def test_forward_only_and_determinism_of_value(M):
     assert abs(a.item() - b.item()) <= 1e-5 * abs(a.item())
 
 
+def test_upstream_gradient_is_applied_in_backward(M):
+    """The gradient pass runs in backward() with autograd's upstream gradient multiplied in by the
+    last kernel (muscle_dense_infonce_bwd's grad_scale): d(2.5 L)/dx == 2.5 dL/dx, both layouts."""
+    x, cls, _ = O.synth_embeddings(2, 128, 20, 20, seed=17)
+    for to_layout in (lambda t: t, lambda t: t.permute(0, 2, 3, 1).reshape(-1, 128).contiguous()):
+        xa = to_layout(x).cuda().requires_grad_()
+        xb = to_layout(x).cuda().requires_grad_()
+        c = cls.reshape(-1).cuda() if xa.dim() == 2 else cls.cuda()
+        M.dense_infonce(xa, c, 0.1, 21).backward()
+        (2.5 * M.dense_infonce(xb, c, 0.1, 21)).backward()
+        assert torch.allclose(xb.grad, 2.5 * xa.grad, rtol=1e-5, atol=1e-9)
+    # the fused C entry point and the fwd / bwd pair agree (row sums are float atomics: not bit for bit)
+    import muscle_b200._lib as L
+    lib = L.load()
+    xc = x.cuda().contiguous()
+    n, dim = 2 * 20 * 20, 128
+    wsb = lib.muscle_dense_infonce_workspace_bytes(n, dim, 21)
+    ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
+    loss = torch.empty((), device="cuda")
+    dx = torch.empty_like(xc)
+    sp = torch.cuda.current_stream().cuda_stream
+    cc = cls.cuda().contiguous()
+    rc = lib.muscle_dense_infonce_fwd_bwd(xc.data_ptr(), 1, 2, 400, dim, cc.data_ptr(), 1, 21, 0.1, 1e-12,
+                                          loss.data_ptr(), dx.data_ptr(), ws.data_ptr(), wsb, sp)
+    assert rc == 0
+    xg = xc.clone().requires_grad_()
+    l2 = M.dense_infonce(xg, cc, 0.1, 21)
+    l2.backward()
+    assert abs(l2.item() - loss.item()) <= 1e-5 * abs(loss.item())
+    assert torch.allclose(xg.grad, dx, rtol=1e-3, atol=1e-8)
+
+
 def test_permutation_invariance_and_temperature(M):
     x, cls, _ = O.synth_embeddings(2, 128, 16, 16, seed=13)
     flat = x.permute(0, 2, 3, 1).reshape(-1, 128)
