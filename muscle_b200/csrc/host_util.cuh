@@ -2,6 +2,7 @@
 // TMA tensor-map construction (driver entry point fetched at run time, so the library links
 // against cudart only and still loads on a machine without libcuda for symbol checks).
 #pragma once
+#include <utility>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -127,6 +128,23 @@ inline int make_bf16_panel_map(CUtensorMap* map, const void* base, int64_t rows,
   if (r != CUDA_SUCCESS)
     return fail(MUSCLE_ERR_CUDA, "cuTensorMapEncodeTiled (panel map) failed with CUresult %d", (int)r);
   return MUSCLE_OK;
+}
+
+// Launch with programmatic stream serialization (see ptx.cuh: pdl_wait / pdl_trigger).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 
 inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }

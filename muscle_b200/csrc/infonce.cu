@@ -54,7 +54,7 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
     cudaMemsetAsync(dbg, 0, grid * 16 * sizeof(unsigned long long), stream);
     prm.dbg = dbg;
   }
-  kern<<<grid, C::THREADS, C::SMEM_BYTES, stream>>>(tm_row, tm_col, prm);
+  MB_CUDA(launch_pdl(kern, dim3(grid), dim3(C::THREADS), C::SMEM_BYTES, stream, tm_row, tm_col, prm));
   MB_LAUNCH_CHECK();
   if (timing) {
     static int printed = 0;
@@ -75,6 +75,15 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
           for (int c = 0; c < std::min(grid, 148); ++c)
             if (h[c * 16 + 6]) { mn = std::min(mn, h[c * 16 + 12]); mx = std::max(mx, h[c * 16 + 12]); }
           fprintf(stderr, "    issuer lifetime per CTA: min %llu mean %.0f max %llu cycles\n", mn, s[12] / n, mx);
+          unsigned long long t0 = ~0ull, t1 = 0, t0x = 0;
+          double span = 0;
+          for (int c = 0; c < std::min(grid, 148); ++c) {
+            t0 = std::min(t0, h[c * 16 + 14]); t0x = std::max(t0x, h[c * 16 + 14]); t1 = std::max(t1, h[c * 16 + 15]);
+            span += double(h[c * 16 + 15] - h[c * 16 + 14]);
+          }
+          fprintf(stderr, "    globaltimer: first CTA start -> last CTA end %.1f us, CTA starts spread over %.1f us, mean CTA span %.1f us"
+                          " (mean SM clock while running %.0f MHz)\n",
+                  (t1 - t0) / 1e3, (t0x - t0) / 1e3, span / std::min(grid, 148) / 1e3, s[12] / n / (span / std::min(grid, 148)) * 1e3);
           if (getenv("MUSCLE_PAIR_TIMING_ALL")) {
             fprintf(stderr, "    per CTA (issuer lifetime k cycles / group-0 units: all, select-masked, bias-masked / epilogue math k cycles):");
             for (int c = 0; c < std::min(grid, 148); ++c)
@@ -159,9 +168,9 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
   MB_CUDA(cudaMemsetAsync(static_cast<char*>(ehat) + n * dim * 2, 0, (rows_pad - n) * dim * 2, stream));
   MB_CUDA(cudaMemsetAsync(bits + n, 0, (rows_pad - n) * sizeof(uint32_t), stream));
   MB_CUDA(cudaMemsetAsync(inv_norm + n, 0, (rows_pad - n) * sizeof(float), stream));
-  class_hist_kernel<<<n_blk, SORT_CHUNK, 0, stream>>>(cls, cls_is_int64, n, num_classes, hist);
+  MB_CUDA(launch_pdl(class_hist_kernel, dim3(n_blk), dim3(SORT_CHUNK), 0, stream, cls, cls_is_int64, static_cast<long long>(n), num_classes, hist));
   MB_LAUNCH_CHECK();
-  class_scan_kernel<<<1, 1024, 0, stream>>>(hist, n_blk, num_classes, n, rows_pad, seg, class_mass, tor);
+  MB_CUDA(launch_pdl(class_scan_kernel, dim3(1), dim3(1024), 0, stream, hist, n_blk, num_classes, static_cast<long long>(n), static_cast<long long>(rows_pad), seg, class_mass, tor));
   MB_LAUNCH_CHECK();
   PrepareParams p;
   p.x = x; p.cls = cls; p.cls64 = cls_is_int64; p.layout = layout; p.n = n;
@@ -175,12 +184,13 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
     if (layout == MUSCLE_LAYOUT_NCHW) {                                                           \
       MB_CUDA(cudaFuncSetAttribute(prepare_nchw_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                    static_cast<int>(SORT_CHUNK * (DD / 2 + 1) * sizeof(uint32_t)))); \
-      prepare_nchw_kernel<DD><<<n_blk, PREP_THREADS, smem, stream>>>(p);                          \
+      MB_CUDA(launch_pdl(prepare_nchw_kernel<DD>, dim3(n_blk), dim3(PREP_THREADS), smem, stream, p)); \
     } else {                                                                                      \
-      prepare_kernel<DD><<<n_blk, SORT_CHUNK, 0, stream>>>(p);                                    \
+      MB_CUDA(launch_pdl(prepare_kernel<DD>, dim3(n_blk), dim3(SORT_CHUNK), 0, stream, p));       \
     }                                                                                             \
     MB_LAUNCH_CHECK();                                                                            \
-    class_sum_kernel<DD><<<n_tiles * (128 / SEG_ROWS), SEG_THREADS, 0, stream>>>(p.ehat, seg, num_classes, class_sum); \
+    MB_CUDA(launch_pdl(class_sum_kernel<DD>, dim3(n_tiles * (128 / SEG_ROWS)), dim3(SEG_THREADS), 0, stream, \
+                       static_cast<const __nv_bfloat16*>(p.ehat), static_cast<const uint32_t*>(seg), num_classes, class_sum)); \
   }
   if (dim == 64) MB_PREP(64) else if (dim == 128) MB_PREP(128) else MB_PREP(256)
 #undef MB_PREP
@@ -229,9 +239,9 @@ int muscle_infonce_mid(const void* ehat, const uint32_t* seg, int64_t rows_pad, 
   p.class_sum = class_sum; p.class_mass = class_mass; p.rowsum = rowsum;
   p.inv_tau = 1.f / temperature; p.w = w; p.gpos = gpos; p.loss_acc = loss_acc; p.dproto = dproto;
   const int grid = static_cast<int>(rows_pad / SEG_ROWS);
-  if (dim == 64) mid_kernel<64><<<grid, SEG_THREADS, 0, stream>>>(p);
-  else if (dim == 128) mid_kernel<128><<<grid, SEG_THREADS, 0, stream>>>(p);
-  else mid_kernel<256><<<grid, SEG_THREADS, 0, stream>>>(p);
+  if (dim == 64) MB_CUDA(launch_pdl(mid_kernel<64>, dim3(grid), dim3(SEG_THREADS), 0, stream, p));
+  else if (dim == 128) MB_CUDA(launch_pdl(mid_kernel<128>, dim3(grid), dim3(SEG_THREADS), 0, stream, p));
+  else MB_CUDA(launch_pdl(mid_kernel<256>, dim3(grid), dim3(SEG_THREADS), 0, stream, p));
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
 }
@@ -250,7 +260,7 @@ int muscle_infonce_plan(const uint32_t* tor_rows, int64_t rows_pad, const uint32
   const int n_col_tiles = static_cast<int>(cols_pad / 128);
   if (static_cast<double>(n_row_blocks) * n_col_tiles >= 4.0e9)
     return fail(MUSCLE_ERR_BAD_ARG, "too many tile units for one rank");
-  pair_plan_kernel<1><<<1, 1024, 0, stream>>>(tor_rows, n_row_blocks, tor_cols, n_col_tiles, unit_off);
+  MB_CUDA(launch_pdl(pair_plan_kernel<1>, dim3(1), dim3(1024), 0, stream, tor_rows, n_row_blocks, tor_cols, n_col_tiles, unit_off));
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
 }
@@ -311,7 +321,7 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
   {                                                                                             \
     MB_CUDA(cudaFuncSetAttribute(final_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                  static_cast<int>(SORT_CHUNK * (DD + 1) * sizeof(float))));     \
-    final_kernel<DD><<<grid, FINAL_THREADS, smem, stream>>>(p);                                    \
+    MB_CUDA(launch_pdl(final_kernel<DD>, dim3(grid), dim3(FINAL_THREADS), smem, stream, p));     \
   }
   if (dim == 64) MB_FINAL(64) else if (dim == 128) MB_FINAL(128) else MB_FINAL(256)
 #undef MB_FINAL

@@ -121,6 +121,8 @@ template <int QT>
 __global__ void __launch_bounds__(1024) pair_plan_kernel(const uint32_t* tor_row, int n_row_blocks,
                                                          const uint32_t* tor_col, int n_col_tiles,
                                                          uint32_t* unit_off) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ uint32_t single[32];   // column tiles whose class set is exactly {c}
   __shared__ uint32_t empty_cnt;    // column tiles without any class
   __shared__ uint32_t warp_tot[32];
@@ -279,6 +281,11 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (kPairTiming && p.dbg && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    p.dbg[blockIdx.x * 16 + 14] = t;
+  }
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NST; ++s) {
@@ -303,10 +310,12 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
     tma_prefetch_desc(&tm_row);
     tma_prefetch_desc(&tm_col);
   }
+  pdl_trigger();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_ptr_smem;
+  pdl_wait();   // barriers, TMEM and descriptors are set up under the previous kernel's tail
 
   if (warp == 8) {
     // ------------------------------------------------------------ TMA producer + work partition
@@ -321,13 +330,23 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
       const uint64_t lo64 = static_cast<uint64_t>(per) * blockIdx.x;
       uint32_t u = lo64 < total ? static_cast<uint32_t>(lo64) : total;
       const uint32_t u1 = (lo64 + per < total) ? static_cast<uint32_t>(lo64 + per) : total;
-      // largest rb with unit_off[rb] <= u
+      // largest rb with unit_off[rb] <= u: a 32-ary search, one coalesced-ish probe per lane and
+      // round (2 rounds up to 1024 row blocks; the 8+ dependent loads of a binary search were
+      // ~5 us of every launch, cold)
       int rb = 0;
       {
         int lo = 0, hi = p.n_row_blocks;  // unit_off[lo] <= u, unit_off[hi] > u (when u < total)
         while (hi - lo > 1) {
-          const int mid = (lo + hi) >> 1;
-          if (__ldg(p.unit_off + mid) <= u) lo = mid; else hi = mid;
+          const int span = hi - lo;
+          const int step = (span + 31) / 32;                  // probes at lo + step*(lane+1), clipped below hi
+          const int probe = lo + step * (lane + 1);
+          const bool le = (probe < hi) && (__ldg(p.unit_off + probe) <= u);
+          const uint32_t m = __ballot_sync(0xffffffffu, le);  // monotone: a prefix of the lanes
+          const int k = __popc(m);                            // probes that are <= u
+          const int new_lo = lo + step * k;
+          const int new_hi = lo + step * (k + 1);
+          lo = new_lo;
+          hi = new_hi < hi ? new_hi : hi;
         }
         rb = lo;
       }
@@ -603,6 +622,11 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   if (warp == 9) tmem_dealloc(tmem, 512);
+  if (kPairTiming && p.dbg && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    p.dbg[blockIdx.x * 16 + 15] = t;
+  }
 }
 
 }  // namespace mb200

@@ -22,6 +22,15 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Every kernel of the dense-InfoNCE chain starts with pdl_trigger(); pdl_wait(): the trigger lets the
+// NEXT kernel of the stream be scheduled now (its blocks then sit in its own pdl_wait), the wait
+// returns once the PREVIOUS kernel has completed and its writes are visible.  Launch latency and
+// prologue of a chain of short dependent kernels overlap instead of adding up.  (A kernel launched
+// without the attribute, or after a non-kernel operation, simply finds the wait already satisfied.)
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---------------------------------------------------------------- mbarrier
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));

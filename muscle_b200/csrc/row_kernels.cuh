@@ -40,6 +40,8 @@ __device__ __forceinline__ int load_class(const void* cls, int cls64, long long 
 __global__ void __launch_bounds__(SORT_CHUNK) class_hist_kernel(const void* cls, int cls64,
                                                                 long long n, int C,
                                                                 uint32_t* hist) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ uint32_t h[MAX_BINS];
   if (threadIdx.x < MAX_BINS) h[threadIdx.x] = 0u;
   __syncthreads();
@@ -57,6 +59,8 @@ __global__ void __launch_bounds__(1024) class_scan_kernel(uint32_t* hist, int n_
                                                           long long n, long long rows_pad,
                                                           uint32_t* seg, float* class_mass,
                                                           uint32_t* tor) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ uint32_t total[MAX_BINS + 1];
   __shared__ uint32_t start[MAX_BINS + 2];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -131,6 +135,8 @@ struct PrepareParams {
 // source order inside every class (stable) and needs no atomics.
 template <int D>
 __global__ void __launch_bounds__(SORT_CHUNK) prepare_kernel(const PrepareParams p) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int WPR = D / 64;          // 32-bit words (bf16 pairs) per lane per row
   constexpr int ROW_W = D / 2 + 1;     // smem row stride in words (odd: conflict-free columns)
   extern __shared__ uint32_t smem_u[];  // NCHW only: [SORT_WARPS][32][ROW_W]
@@ -217,6 +223,8 @@ __global__ void __launch_bounds__(SORT_CHUNK) prepare_kernel(const PrepareParams
 constexpr int PREP_THREADS = 512;
 template <int D>
 __global__ void __launch_bounds__(PREP_THREADS) prepare_nchw_kernel(const PrepareParams p) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int DQ = D / 4;            // channels per warp
   constexpr int WPR = D / 64;          // 32-bit words (bf16 pairs) per lane per row
   constexpr int ROW_W = D / 2 + 1;     // smem row stride in words (odd: conflict-free columns)
@@ -320,6 +328,8 @@ template <int D>
 __global__ void __launch_bounds__(SEG_THREADS) class_sum_kernel(const __nv_bfloat16* ehat,
                                                                 const uint32_t* seg, int C,
                                                                 float* class_sum) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int TPR = D / 8;
   constexpr int RPP = SEG_THREADS / TPR;
   __shared__ float red[RPP * D];
@@ -357,6 +367,8 @@ struct MidParams {
 // Same tiling as class_sum_kernel.  Rows of the invalid segment and pad rows get w = gpos = 0.
 template <int D>
 __global__ void __launch_bounds__(SEG_THREADS) mid_kernel(const MidParams p) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int TPR = D / 8;
   constexpr int RPP = SEG_THREADS / TPR;
   __shared__ float red[RPP * D];
@@ -462,6 +474,8 @@ constexpr int FINAL_ROWS_PER_WARP = SORT_CHUNK / (FINAL_THREADS / 32);
 
 template <int D>
 __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams p) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int EPL = D / 32;
   extern __shared__ float smem_f[];  // NCHW only: [SORT_CHUNK][D+1]
   __shared__ float n_valid_sh;
