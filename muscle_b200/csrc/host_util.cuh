@@ -2,6 +2,7 @@
 // TMA tensor-map construction (driver entry point fetched at run time, so the library links
 // against cudart only and still loads on a machine without libcuda for symbol checks).
 #pragma once
+#include <cstdlib>
 #include <utility>
 #include <cstdarg>
 #include <cstdio>
@@ -142,8 +143,9 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
+  static const bool off = getenv("MUSCLE_NO_PDL") != nullptr;   // debugging: plain stream order
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = off ? 0 : 1;
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 

@@ -81,6 +81,10 @@ constexpr int PAIR_RB = 128;              // rows per row block of the pair pass
 template <int D, int MODE>
 struct PairCfg {
   static_assert(D == 64 || D == 128 || D == 256, "projection dim must be 64, 128 or 256");
+  // epilogue groups of 4 warps: the row-sum pass's epilogue fits 128 registers, so a third group (4
+  // warps per scheduler instead of 3) hides more of its MUFU / TMEM-load latency; the gradient pass
+  // needs ~156 registers and stays at two (and D = 256 has only two ring stages: see the assert below)
+  static constexpr int NG = (MODE == MODE_ROWSUM && D != 256) ? 3 : 2;
   static constexpr int NB = (MODE == MODE_ROWSUM) ? 4 : (D == 256 ? 2 : 3);   // S buffers in TMEM
   static constexpr int NST = (D == 256) ? 2 : (D == 128 ? 5 : 8);             // column-tile ring
   static constexpr int TILE_BYTES = 128 * D * 2;         // one 128-pixel bf16 tile
@@ -90,15 +94,22 @@ struct PairCfg {
   static constexpr int SMEM_K = SMEM_Q + TILE_BYTES;
   static constexpr int SMEM_BITS = SMEM_K + NST * TILE_BYTES;
   static constexpr int SMEM_W = SMEM_BITS + NST * 512;
-  static constexpr int SMEM_CB = SMEM_W + NST * 512;     // exponent-shift vectors [2 groups][2][BIAS_SLOTS][128] (MASK_BIAS)
-  static constexpr int SMEM_BAR = SMEM_CB + 4 * BIAS_SLOTS * 512;
+  static constexpr int SMEM_CB = SMEM_W + NST * 512;     // exponent-shift vectors [NG groups][2][BIAS_SLOTS][128] (MASK_BIAS)
+  static constexpr int SMEM_BAR = SMEM_CB + 2 * NG * BIAS_SLOTS * 512;
   static constexpr int NBAR = 2 * NST + 2 + 2 * NB + 2;
   static constexpr int SMEM_INFO = SMEM_BAR + NBAR * 8;  // item headers [2][4], stage info [NST]
   static constexpr int SMEM_TMEMPTR = SMEM_INFO + (8 + NST) * 4;
   static constexpr int SMEM_BYTES = SMEM_TMEMPTR + 16 + 1024;  // +1024: manual 1024-B alignment
   static constexpr int ACC_COL = NB * 128;
-  static constexpr int THREADS = 320;
+  static constexpr int WARP_PRODUCER = 4 * NG;
+  static constexpr int WARP_ISSUER = 4 * NG + 1;
+  static constexpr int THREADS = (4 * NG + 2) * 32;
   static_assert(ACC_COL + (MODE == MODE_GRAD ? D : 0) <= 512, "TMEM budget");
+  // A group waits on a stage's / buffer's mbarrier by phase parity.  Its previous unit is NG units
+  // back; the previous user of the same stage (buffer) is NST (NB) units back.  Only if NG <= NST and
+  // NG <= NB has the group itself seen that earlier phase complete -- otherwise a wait for phase n+2
+  // can be satisfied by phase n (same parity) and the group runs ahead of the data.
+  static_assert(NG <= NST && NG <= NB, "epilogue groups must not outnumber ring stages or S buffers");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
 
@@ -251,7 +262,7 @@ __device__ __forceinline__ void pair_half_math(uint32_t (&v)[2][32], uint32_t t_
 }
 
 template <int D, int MODE, int POLY>
-__global__ void __launch_bounds__(320, 1)
+__global__ void __launch_bounds__((PairCfg<D, MODE>::THREADS), 1)
 pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ CUtensorMap tm_col,
             const PairParams p) {
   using C = PairCfg<D, MODE>;
@@ -293,7 +304,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
       mbar_init(k_empty(s), 1 + 4);   // MMA issuer + the four warps of the group that owns the unit
     }
     mbar_init(q_full, 1);
-    mbar_init(q_empty, 1 + 8);  // MMA issuer + every epilogue warp (after it has read the item header)
+    mbar_init(q_empty, 1 + 4 * C::NG);  // MMA issuer + every epilogue warp (after it has read the item header)
     for (int b = 0; b < NB; ++b) {
       mbar_init(s_full(b), 1);
       mbar_init(t_full(b), 4);
@@ -302,11 +313,11 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
     mbar_init(acc_empty, 8);
     fence_barrier_init();
   }
-  if (warp == 9) {
+  if (warp == C::WARP_ISSUER) {
     tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_ptr_smem)), 512);
     tmem_relinquish();
   }
-  if (warp == 8 && lane == 0) {
+  if (warp == C::WARP_PRODUCER && lane == 0) {
     tma_prefetch_desc(&tm_row);
     tma_prefetch_desc(&tm_col);
   }
@@ -317,7 +328,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
   const uint32_t tmem = *tmem_ptr_smem;
   pdl_wait();   // barriers, TMEM and descriptors are set up under the previous kernel's tail
 
-  if (warp == 8) {
+  if (warp == C::WARP_PRODUCER) {
     // ------------------------------------------------------------ TMA producer + work partition
     // The whole warp walks the work list (32 column-tile class unions per coalesced load, the next
     // 32 prefetched: a dependent L2 load per tile on one lane made this warp the bottleneck);
@@ -413,7 +424,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         mbar_arrive(q_full);
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == C::WARP_ISSUER) {
     // ------------------------------------------------------------ MMA issuer
     // (elect.sync, not lane == 0: ptxas then knows a single thread runs the region and feeds the
     // uniform-register operands of UTCHMMA without a per-instruction waterfall loop)
@@ -518,8 +529,8 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
       float wrow = 0.f;
       if (MODE == MODE_GRAD) wrow = __ldg(p.w_row + row);
       uint64_t racc[4] = {0ull, 0ull, 0ull, 0ull};
-      // this group's units: every other one of the CTA's running unit count
-      for (int k = static_cast<int>((gbase & 1u) ^ static_cast<uint32_t>(g)); k < n; k += 2) {
+      // this group's units: every NG-th one of the CTA's running unit count
+      for (int k = static_cast<int>((static_cast<uint32_t>(g) + C::NG - gbase % C::NG) % C::NG); k < n; k += C::NG) {
         const uint32_t gk = gbase + k;
         const int st = static_cast<int>(gk % NST);
         const int b = static_cast<int>(gk % NB);
@@ -621,7 +632,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) tmem_dealloc(tmem, 512);
+  if (warp == C::WARP_ISSUER) tmem_dealloc(tmem, 512);
   if (kPairTiming && p.dbg && threadIdx.x == 0) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
