@@ -270,6 +270,7 @@ def main():
         return xg, cg, ev
 
     def e2e_pipelined(steps):
+        t_host0 = time.perf_counter()
         main = torch.cuda.current_stream()
         nxt = upload()
         for i in range(steps):
@@ -286,15 +287,22 @@ def main():
                 loss = M.dense_infonce(xg, cg, TEMPERATURE, NUM_CLASSES)
             loss.backward()
             loss_pinned[i].copy_(loss.detach(), non_blocking=True)   # device -> host read of the step's result
+        e2e_pipelined.host_s = time.perf_counter() - t_host0          # all steps enqueued (host side only)
         torch.cuda.synchronize()
         return loss_pinned[:steps].tolist()
 
     e2e_pipelined(3)
-    barrier()
-    t0 = time.perf_counter()
-    e2e_losses = e2e_pipelined(args.steps)
-    t_e2e = time.perf_counter() - t0
-    assert all(v == v for v in e2e_losses), "NaN loss in the end-to-end run"
+    # the loop is host bound by a small margin (enqueue ~0.27 ms/step against ~0.28 ms of kernels at
+    # config 2), so one descheduled host thread doubles a run: three runs of K steps, the median reported
+    e2e_runs = []
+    for _ in range(3):
+        barrier()
+        t0 = time.perf_counter()
+        e2e_losses = e2e_pipelined(args.steps)
+        e2e_runs.append((time.perf_counter() - t0, e2e_pipelined.host_s))
+        assert all(v == v for v in e2e_losses), "NaN loss in the end-to-end run"
+    e2e_runs.sort()
+    t_e2e, e2e_pipelined.host_s = e2e_runs[1]
     barrier()
 
     # dominant kernel (gradient pass) and the row-sum pass, timed alone through the staged C ABI
@@ -354,6 +362,9 @@ def main():
                              d2h_bytes_per_step=4, ms_per_step=1e3 * t_e2e / args.steps,
                              mode="pipelined: next step's pinned-host upload on a copy stream, loss read back "
                                   "asynchronously; every step's H2D and D2H are inside the timed region",
+                             host_enqueue_ms_per_step=1e3 * e2e_pipelined.host_s / args.steps,
+                             runs_ms_per_step=[1e3 * r[0] / args.steps for r in e2e_runs],
+                             runs_note="three runs of `steps` steps each, the median is `value`",
                              serial_value=pairs_per_step * args.steps / t_e2e_serial,
                              serial_ms_per_step=1e3 * t_e2e_serial / args.steps,
                              serial_note="upload -> step -> blocking .item() per step, nothing overlapped"),

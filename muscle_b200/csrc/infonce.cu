@@ -182,8 +182,12 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
 #define MB_PREP(DD)                                                                               \
   {                                                                                               \
     if (layout == MUSCLE_LAYOUT_NCHW) {                                                           \
-      MB_CUDA(cudaFuncSetAttribute(prepare_nchw_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                   static_cast<int>(SORT_CHUNK * (DD / 2 + 1) * sizeof(uint32_t)))); \
+      static thread_local bool attr_set = false;   /* once per thread and instantiation: ~2 us per call */ \
+      if (!attr_set) {                                                                            \
+        MB_CUDA(cudaFuncSetAttribute(prepare_nchw_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                     static_cast<int>(SORT_CHUNK * (DD / 2 + 1) * sizeof(uint32_t)))); \
+        attr_set = true;                                                                          \
+      }                                                                                           \
       MB_CUDA(launch_pdl(prepare_nchw_kernel<DD>, dim3(n_blk), dim3(PREP_THREADS), smem, stream, p)); \
     } else {                                                                                      \
       MB_CUDA(launch_pdl(prepare_kernel<DD>, dim3(n_blk), dim3(SORT_CHUNK), 0, stream, p));       \
@@ -319,8 +323,12 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
   const int grid = dx ? static_cast<int>((p.n + SORT_CHUNK - 1) / SORT_CHUNK) : 1;
 #define MB_FINAL(DD)                                                                            \
   {                                                                                             \
-    MB_CUDA(cudaFuncSetAttribute(final_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                 static_cast<int>(SORT_CHUNK * (DD + 1) * sizeof(float))));     \
+    static thread_local bool attr_set = false;                                                  \
+    if (!attr_set) {                                                                            \
+      MB_CUDA(cudaFuncSetAttribute(final_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                   static_cast<int>(SORT_CHUNK * (DD + 1) * sizeof(float))));   \
+      attr_set = true;                                                                          \
+    }                                                                                           \
     MB_CUDA(launch_pdl(final_kernel<DD>, dim3(grid), dim3(FINAL_THREADS), smem, stream, p));     \
   }
   if (dim == 64) MB_FINAL(64) else if (dim == 128) MB_FINAL(128) else MB_FINAL(256)

@@ -1,10 +1,11 @@
 // The dense pixel-pair mainloop of the InfoNCE row-sum pass and the InfoNCE gradient pass.
 //
-// One persistent CTA per SM, warp-specialised:
-//   warps 0-3  epilogue group 0  (TMEM lanes 32*(warp%4) .. +31, thread = one row of the 128-row tile)
-//   warps 4-7  epilogue group 1
-//   warp  8    TMA producer      (the row tile once per work item, column tiles through a ring)
-//   warp  9    tcgen05.mma issuer (one lane) + TMEM allocator
+// One persistent CTA per SM, warp-specialised (NG epilogue groups: 3 in the row-sum pass, 2 in the
+// gradient pass and for D = 256, see PairCfg):
+//   warps 0 .. 4 NG-1   epilogue groups of four warps (TMEM lanes 32*(warp%4) .. +31, thread = one row
+//                       of the 128-row tile); group g takes every NG-th unit
+//   warp  4 NG          TMA producer      (the row tile once per work item, column tiles through a ring)
+//   warp  4 NG + 1      tcgen05.mma issuer (one lane) + TMEM allocator
 //
 // Pixels arrive sorted by class (row_kernels.cuh), and a per-tile class union (`tor`) lets the
 // producer drop every (row tile, column tile) whose pairs are all masked (same single class)
@@ -30,6 +31,14 @@
 // pipe; all elementwise math is packed fp32x2.
 //
 // TMEM columns: S buffer b at [128 b, 128 b + 128); MODE_GRAD: G accumulator [128 x D] after them.
+//
+// Variants of the gradient pass that were built, verified and measured slower or equal on B200
+// (config 2, 125 us as is): a third epilogue group at 128 registers (128 us); T in separate 64-column
+// TMEM buffers with two S buffers, so that S(k+2) is issued as soon as S(k) has been read (125 us:
+// the "T done -> G(k) -> S(k+3)" chain is not what bounds the pass); that plus both groups on every
+// unit, 64 columns each, to halve the time a column tile is held between S(k) and G(k) (151 us: four
+// more barrier operations per unit and group cost more than the shorter residence buys); the next
+// tcgen05.ld issued under the math of the current 32-column chunk (+3 %: more registers, no gain).
 #pragma once
 // Cycle counters of the pair kernel's phases (printed by infonce.cu under MUSCLE_PAIR_TIMING=1) cost
 // ~20 registers per epilogue thread: compiled in only with -DMB_PAIR_TIMING=1 (scripts/build_variants.sh).
