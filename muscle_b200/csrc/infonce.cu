@@ -438,39 +438,85 @@ int check_composite(int dim, int num_classes, float temperature, int64_t batch, 
   return MUSCLE_OK;
 }
 
+// MUSCLE_STAGE_TIMING=1: CUDA events around every stage of the composite (debugging aid; the event
+// records break the programmatic-launch chain, so the sum is a little above the real step)
+struct StageTimer {
+  bool on;
+  cudaStream_t stream;
+  cudaEvent_t ev[16];
+  const char* name[16];
+  int n = 0;
+  explicit StageTimer(cudaStream_t s) : stream(s) {
+    static const bool env = getenv("MUSCLE_STAGE_TIMING") != nullptr;
+    on = env;
+  }
+  void mark(const char* what) {
+    if (!on || n >= 16) return;
+    cudaEventCreate(&ev[n]);
+    cudaEventRecord(ev[n], stream);
+    name[n++] = what;
+  }
+  void report(const char* title) {
+    if (!on || n < 2) return;
+    cudaEventSynchronize(ev[n - 1]);
+    fprintf(stderr, "[stages %s]", title);
+    for (int i = 1; i < n; ++i) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, ev[i - 1], ev[i]);
+      fprintf(stderr, " %s %.1f us |", name[i], ms * 1e3f);
+    }
+    fprintf(stderr, "\n");
+    for (int i = 0; i < n; ++i) cudaEventDestroy(ev[i]);
+  }
+};
+
 // prepare -> plan -> row sums -> mid: everything the loss needs
 int composite_forward(const float* x, int layout, int64_t batch, int64_t pixels_per_image, int dim,
                       const void* cls, int cls_is_int64, int num_classes, float temperature, float eps,
                       void* workspace, const Workspace& ws, const Carved& c, cudaStream_t stream) {
   const int64_t n = batch * pixels_per_image;
+  StageTimer tm(stream);
+  tm.mark("start");
   MB_CUDA(cudaMemsetAsync(static_cast<char*>(workspace) + ws.zero_lo, 0, ws.zero_bytes, stream));
   int rc = muscle_infonce_prepare(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64,
                                   num_classes, eps, c.ehat, c.bits, c.inv_norm, c.perm, c.tor, c.seg,
                                   c.class_sum, c.class_mass, c.scratch,
                                   muscle_infonce_prepare_scratch_bytes(n), stream);
   if (rc) return rc;
+  tm.mark("memsets+hist+scan+prepare+class_sum");
   rc = muscle_infonce_plan(c.tor, ws.rows_pad, c.tor, ws.rows_pad, dim, c.unit_off, stream);
   if (rc) return rc;
+  tm.mark("plan");
   rc = muscle_infonce_rowsum(c.ehat, c.bits, c.tor, ws.rows_pad, c.ehat, c.bits, c.tor, ws.rows_pad,
                              c.unit_off, dim, temperature, c.rowsum, stream);
   if (rc) return rc;
-  return muscle_infonce_mid(c.ehat, c.seg, ws.rows_pad, dim, num_classes, c.class_sum, c.class_mass,
-                            c.rowsum, temperature, c.w, c.gpos, c.loss_acc, c.dproto, stream);
+  tm.mark("rowsum");
+  rc = muscle_infonce_mid(c.ehat, c.seg, ws.rows_pad, dim, num_classes, c.class_sum, c.class_mass,
+                          c.rowsum, temperature, c.w, c.gpos, c.loss_acc, c.dproto, stream);
+  tm.mark("mid");
+  tm.report("forward");
+  return rc;
 }
 
 // gradient pass + final (dx may be null: loss only)
 int composite_backward(int layout, int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
                        float temperature, const float* grad_scale, float* dx_out, float* loss_out,
                        const Workspace& ws, const Carved& c, cudaStream_t stream) {
+  StageTimer tm(stream);
+  tm.mark("start");
   if (dx_out) {
     int rc = muscle_infonce_grad(c.ehat, c.bits, c.tor, c.w, ws.rows_pad, c.ehat, c.bits, c.tor, c.w,
                                  ws.rows_pad, c.unit_off, dim, temperature, c.part, stream);
     if (rc) return rc;
+    tm.mark("grad");
   }
-  return muscle_infonce_final(c.ehat, c.bits, c.inv_norm, c.perm, c.part, c.unit_off, ws.rows_pad,
+  const int rcf = muscle_infonce_final(c.ehat, c.bits, c.inv_norm, c.perm, c.part, c.unit_off, ws.rows_pad,
                               ws.rows_pad, batch, pixels_per_image, dim, num_classes, c.class_sum,
                               c.class_mass, c.gpos, c.dproto, c.loss_acc, temperature, layout, dx_out,
                               loss_out, grad_scale, stream);
+  tm.mark(dx_out ? "final" : "final (loss only)");
+  tm.report(dx_out ? "backward" : "loss");
+  return rcf;
 }
 }  // namespace
 
