@@ -22,6 +22,9 @@ from .ops import _as_feature_operand
 from .stages import CudaStages
 
 
+_SIZES_CHECKED = set()   # (rows_pad, world, group id) already validated across ranks
+
+
 def _world(group):
     if dist.is_available() and dist.is_initialized():
         return dist.get_world_size(group), dist.get_rank(group)
@@ -48,13 +51,16 @@ def sharded_fwd(stages, x, cls, temperature, num_classes, eps, need_grad, group=
     if cls_c.numel() != n:
         raise ValueError("cls has %d entries for %d pixels" % (cls_c.numel(), n))
     rows_pad = stages.pad_rows(n)
-    if G > 1:
+    if G > 1 and (rows_pad, G, id(group)) not in _SIZES_CHECKED:
+        # once per shape and group: the check reads two reduced scalars back (a host sync every step
+        # would keep the host from running ahead of the device)
         sizes = torch.tensor([rows_pad], dtype=torch.int64, device=xc.device)
         lo, hi = sizes.clone(), sizes.clone()
         dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
         dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
         if int(lo) != int(hi):
             raise ValueError("every rank must hold the same (padded) number of pixels")
+        _SIZES_CHECKED.add((rows_pad, G, id(group)))
     cols_pad = rows_pad * G
     C = num_classes
     f32, i32 = torch.float32, torch.int32
