@@ -164,11 +164,9 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
   const int64_t rows_pad = muscle_pad_rows(n);
   const int n_blk = static_cast<int>((n + SORT_CHUNK - 1) / SORT_CHUNK);
   uint32_t* hist = static_cast<uint32_t*>(scratch);
-  // pad rows (and anything the scatter does not reach) are zero vectors that belong to no class
-  MB_CUDA(cudaMemsetAsync(static_cast<char*>(ehat) + n * dim * 2, 0, (rows_pad - n) * dim * 2, stream));
-  MB_CUDA(cudaMemsetAsync(bits + n, 0, (rows_pad - n) * sizeof(uint32_t), stream));
-  MB_CUDA(cudaMemsetAsync(inv_norm + n, 0, (rows_pad - n) * sizeof(float), stream));
-  MB_CUDA(launch_pdl(class_hist_kernel, dim3(n_blk), dim3(SORT_CHUNK), 0, stream, cls, cls_is_int64, static_cast<long long>(n), num_classes, hist));
+  // (pad rows -- zero vectors that belong to no class -- are cleared by the histogram kernel)
+  MB_CUDA(launch_pdl(class_hist_kernel, dim3(n_blk), dim3(SORT_CHUNK), 0, stream, cls, cls_is_int64, static_cast<long long>(n), num_classes, hist,
+                     static_cast<long long>(rows_pad), dim, static_cast<uint32_t*>(ehat), bits, inv_norm));
   MB_LAUNCH_CHECK();
   MB_CUDA(launch_pdl(class_scan_kernel, dim3(1), dim3(1024), 0, stream, hist, n_blk, num_classes, static_cast<long long>(n), static_cast<long long>(rows_pad), seg, class_mass, tor));
   MB_LAUNCH_CHECK();

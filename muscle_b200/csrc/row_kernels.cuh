@@ -37,9 +37,13 @@ __device__ __forceinline__ int load_class(const void* cls, int cls64, long long 
 
 // ------------------------------------------------------------------------------------------
 // hist[blk][bin] = number of pixels of class `bin` among source pixels [blk*128, blk*128+128)
+// Also zeroes the pad rows [n, rows_pad) of ehat / bits / inv_norm (zero vectors that belong to no
+// class), spread over the grid: three memsets less on the launch chain.
 __global__ void __launch_bounds__(SORT_CHUNK) class_hist_kernel(const void* cls, int cls64,
                                                                 long long n, int C,
-                                                                uint32_t* hist) {
+                                                                uint32_t* hist, long long rows_pad, int dim,
+                                                                uint32_t* ehat_words, uint32_t* bits,
+                                                                float* inv_norm) {
   pdl_trigger();
   pdl_wait();
   __shared__ uint32_t h[MAX_BINS];
@@ -49,6 +53,16 @@ __global__ void __launch_bounds__(SORT_CHUNK) class_hist_kernel(const void* cls,
   if (i < n) atomicAdd(&h[load_class(cls, cls64, i, C)], 1u);
   __syncthreads();
   if (threadIdx.x < MAX_BINS) hist[static_cast<size_t>(blockIdx.x) * MAX_BINS + threadIdx.x] = h[threadIdx.x];
+  // pad rows: (rows_pad - n) * (dim/2 + 2) words in all
+  const long long wpr = dim / 2;
+  const long long pad_rows = rows_pad - n;
+  const long long total = pad_rows * (wpr + 2);
+  for (long long k = static_cast<long long>(blockIdx.x) * SORT_CHUNK + threadIdx.x; k < total;
+       k += static_cast<long long>(gridDim.x) * SORT_CHUNK) {
+    if (k < pad_rows * wpr) ehat_words[n * wpr + k] = 0u;
+    else if (k < pad_rows * (wpr + 1)) bits[n + (k - pad_rows * wpr)] = 0u;
+    else inv_norm[n + (k - pad_rows * (wpr + 1))] = 0.f;
+  }
 }
 
 // One block of 32 warps; warp c owns bin c.  In place: hist[blk][c] becomes the sorted position
