@@ -383,9 +383,20 @@ def main():
             # the same class are masked by the loss and are never multiplied
             allp = 4.0 * dim * float(n_local) * float(n_global) / kern["grad_s"] / 1e12
             ach = allp * kern["live_frac"]
+            # DRAM bytes per launch of this kernel from the committed ncu --set full capture (same workload only)
+            traffic, traffic_src = None, None
+            tpath = os.path.join(ROOT, "profiles", "traffic.json")
+            if os.path.exists(tpath) and wl["name"].startswith("config2") and world == 1:
+                with open(tpath) as f:
+                    tj = json.load(f)
+                traffic = tj["bytes_per_launch"].get("pair_kernel<%d,MODE_GRAD>" % dim)
+                traffic_src = tj["source"]
             line["roofline"] = dict(bound="tensor", kernel="pair_kernel<%d,MODE_GRAD>" % dim, achieved=ach,
                                     peak=pk["bf16_burst"], unit="TFLOP/s", frac=ach / pk["bf16_burst"],
-                                    frac_of_sustained=ach / pk["bf16_sustained"], traffic=None,
+                                    frac_of_sustained=ach / pk["bf16_sustained"], traffic=traffic,
+                                    traffic_source=traffic_src,
+                                    traffic_note="algorithmic DRAM bytes per launch = the bf16 operand once: "
+                                                 "%d bytes" % (rows_pad * dim * 2),
                                     peak_source=pk["source"] + ", burst figure (kernel timed alone)",
                                     algorithmic="4*D flops per ordered pixel pair of every live (row tile, column tile) "
                                                 "unit: S recomputed (2*D) + one T@E product (2*D) that serves dQ and dK "
