@@ -33,10 +33,27 @@ template <int D, int MODE, int POLY>
 int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, int64_t cols_pad,
                 PairParams prm, cudaStream_t stream) {
   using C = PairCfg<D, MODE>;
+  // Tensor maps depend only on (base, rows, D); a training loop presents the same few buffers again and
+  // again (the caching allocator hands the workspace back at the same address), and one
+  // cuTensorMapEncodeTiled costs a few microseconds of host time, four times per step.
+  struct MapEntry { const void* base; int64_t rows; int dim; CUtensorMap map; };
+  static thread_local MapEntry cache[8] = {};
+  static thread_local int next_slot = 0;
+  auto cached_map = [&](const void* base, int64_t rows, CUtensorMap* out) -> int {
+    for (const MapEntry& e : cache)
+      if (e.base == base && e.rows == rows && e.dim == D) { *out = e.map; return MUSCLE_OK; }
+    MapEntry& e = cache[next_slot];
+    next_slot = (next_slot + 1) % 8;
+    e.base = nullptr;
+    if (int rc2 = make_bf16_panel_map(&e.map, base, rows, D)) return rc2;
+    e.base = base; e.rows = rows; e.dim = D;
+    *out = e.map;
+    return MUSCLE_OK;
+  };
   CUtensorMap tm_row, tm_col;
-  int rc = make_bf16_panel_map(&tm_row, ehat_rows, rows_pad, D);
+  int rc = cached_map(ehat_rows, rows_pad, &tm_row);
   if (rc) return rc;
-  rc = make_bf16_panel_map(&tm_col, ehat_cols, cols_pad, D);
+  rc = cached_map(ehat_cols, cols_pad, &tm_col);
   if (rc) return rc;
   auto kern = pair_kernel<D, MODE, POLY>;
   static thread_local bool attr_set = false;
