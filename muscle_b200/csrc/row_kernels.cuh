@@ -78,42 +78,47 @@ __global__ void __launch_bounds__(1024) class_scan_kernel(uint32_t* hist, int n_
   __shared__ uint32_t total[MAX_BINS + 1];
   __shared__ uint32_t start[MAX_BINS + 2];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // pass 1: class totals
-  uint32_t t = 0;
+  // Lane l of warp c owns the contiguous run of chunks [l*per, l*per + per) of bin c: one round of
+  // independent loads, serial adds in registers, ONE warp scan -- instead of a 5-step shuffle scan
+  // per 32 chunks.
+  const int per = (n_blk + 31) / 32;
+  const int b0 = lane * per;
+  uint32_t mine = 0;
   if (warp <= C)
-    for (int b = lane; b < n_blk; b += 32) t += hist[static_cast<size_t>(b) * MAX_BINS + warp];
+    for (int i = 0; i < per; ++i)
+      if (b0 + i < n_blk) mine += hist[static_cast<size_t>(b0 + i) * MAX_BINS + warp];
+  uint32_t inc = mine;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-  if (lane == 0) total[warp] = (warp <= C) ? t : 0u;
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += u;
+  }
+  if (lane == 31) total[warp] = (warp <= C) ? inc : 0u;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    uint32_t s = 0;
-    for (int c = 0; c <= C; ++c) {
-      start[c] = s;
-      s += total[c];
+  if (warp == 0) {   // exclusive prefix over the bins (lane = bin)
+    const uint32_t v = (lane <= C) ? total[lane] : 0u;
+    uint32_t x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += u;
     }
-    start[C + 1] = s;  // == n
+    if (lane <= C) start[lane] = x - v;
+    if (lane == C) start[C + 1] = x;  // == n
   }
   __syncthreads();
   if (threadIdx.x <= C + 1) seg[threadIdx.x] = start[threadIdx.x];
   if (threadIdx.x < C) atomicAdd(class_mass + threadIdx.x, static_cast<float>(total[threadIdx.x]));
-  // pass 2: exclusive scan over chunks, 32 chunks at a time
+  // in place: hist[blk][c] -> sorted position of the first pixel of class c in chunk blk
   if (warp <= C) {
-    uint32_t run = start[warp];
-    uint32_t v_next = (lane < n_blk) ? hist[static_cast<size_t>(lane) * MAX_BINS + warp] : 0u;
-    for (int b0 = 0; b0 < n_blk; b0 += 32) {
-      const int b = b0 + lane;
-      const uint32_t v = v_next;   // the next 32 chunks are fetched under this round's scan
-      v_next = (b + 32 < n_blk) ? hist[static_cast<size_t>(b + 32) * MAX_BINS + warp] : 0u;
-      uint32_t inc = v;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += u;
+    uint32_t run = start[warp] + inc - mine;
+    for (int i = 0; i < per; ++i)
+      if (b0 + i < n_blk) {
+        const size_t idx = static_cast<size_t>(b0 + i) * MAX_BINS + warp;
+        const uint32_t v = hist[idx];
+        hist[idx] = run;
+        run += v;
       }
-      if (b < n_blk) hist[static_cast<size_t>(b) * MAX_BINS + warp] = run + inc - v;
-      run += __shfl_sync(0xffffffffu, inc, 31);
-    }
   }
   // tile class unions
   const long long n_tiles = rows_pad / 128;
@@ -337,6 +342,25 @@ __device__ __forceinline__ void block_colsum_flush(float (&acc)[8], float* red, 
   __syncthreads();
 }
 
+// Bit c set <=> class c has rows in [r0, r1): one parallel look at the segment table instead of a
+// serial walk over all classes in every block (C <= 31).  Ends with a __syncthreads().
+__device__ __forceinline__ uint32_t block_class_mask(const uint32_t* seg, int C, long long r0, long long r1,
+                                                     uint32_t* sh) {
+  if (threadIdx.x < 32) {
+    const int c = threadIdx.x;
+    bool ov = false;
+    if (c < C) {
+      const long long lo = max(r0, static_cast<long long>(seg[c]));
+      const long long hi = min(r1, static_cast<long long>(seg[c + 1]));
+      ov = lo < hi;
+    }
+    const uint32_t m = __ballot_sync(0xffffffffu, ov);
+    if (threadIdx.x == 0) *sh = m;
+  }
+  __syncthreads();
+  return *sh;
+}
+
 // class_sum[c][:] += sum of the (bf16-rounded) rows of class c in this tile
 template <int D>
 __global__ void __launch_bounds__(SEG_THREADS) class_sum_kernel(const __nv_bfloat16* ehat,
@@ -348,11 +372,12 @@ __global__ void __launch_bounds__(SEG_THREADS) class_sum_kernel(const __nv_bfloa
   constexpr int RPP = SEG_THREADS / TPR;
   __shared__ float red[RPP * D];
   const int sub = threadIdx.x / TPR, l = threadIdx.x % TPR;
+  __shared__ uint32_t cmask_sh;
   const long long r0 = static_cast<long long>(blockIdx.x) * SEG_ROWS, r1 = r0 + SEG_ROWS;
-  for (int c = 0; c < C; ++c) {
+  for (uint32_t cm = block_class_mask(seg, C, r0, r1, &cmask_sh); cm != 0u; cm &= cm - 1u) {
+    const int c = __ffs(cm) - 1;
     const long long lo = max(r0, static_cast<long long>(seg[c]));
     const long long hi = min(r1, static_cast<long long>(seg[c + 1]));
-    if (lo >= hi) continue;  // block-uniform
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (long long r = lo + sub; r < hi; r += RPP) {
       float v[8];
@@ -391,10 +416,11 @@ __global__ void __launch_bounds__(SEG_THREADS) mid_kernel(const MidParams p) {
   const long long r0 = static_cast<long long>(blockIdx.x) * SEG_ROWS, r1 = r0 + SEG_ROWS;
   const float bt = p.inv_tau;  // the shift used by the pair passes: exp((s - 1)/tau)
   double loss = 0.0;
-  for (int c = 0; c < p.C; ++c) {
+  __shared__ uint32_t cmask_sh;
+  for (uint32_t cm = block_class_mask(p.seg, p.C, r0, r1, &cmask_sh); cm != 0u; cm &= cm - 1u) {
+    const int c = __ffs(cm) - 1;
     const long long lo = max(r0, static_cast<long long>(p.seg[c]));
     const long long hi = min(r1, static_cast<long long>(p.seg[c + 1]));
-    if (lo >= hi) continue;
     const float inv_mass = 1.f / __ldg(p.class_mass + c);
     float proto[8];
 #pragma unroll

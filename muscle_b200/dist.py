@@ -153,7 +153,9 @@ class _ShardedDenseInfoNCE(torch.autograd.Function):
         st = ctx.state
         if st is None:
             return None, None, None, None, None, None
-        g = grad_out.detach().to(dtype=torch.float32).reshape(1).contiguous()
+        g = grad_out.detach()
+        if g.dtype != torch.float32 or not g.is_contiguous():
+            g = g.to(dtype=torch.float32).contiguous()
         dx = sharded_bwd(ctx.stages, st, g)
         ctx.state = None
         return dx.reshape(ctx.x_shape), None, None, None, None, None

@@ -101,7 +101,9 @@ class _DenseInfoNCE(torch.autograd.Function):
             return None, None, None, None, None
         lib = _lib.load()
         layout, batch, ppi, dim, num_classes, temperature = ctx.args
-        g = grad_out.detach().to(device=ws.device, dtype=torch.float32).reshape(1).contiguous()
+        g = grad_out.detach()
+        if g.dtype != torch.float32 or g.device != ws.device or not g.is_contiguous():
+            g = g.to(device=ws.device, dtype=torch.float32).contiguous()
         dx = torch.empty(ctx.xc_shape, dtype=torch.float32, device=ws.device)
         with _on_device(ws.device):
             rc = lib.muscle_dense_infonce_bwd(layout, batch, ppi, dim, num_classes, temperature, g.data_ptr(),
