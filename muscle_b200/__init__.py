@@ -4,6 +4,6 @@ path of SCoulY/MuSCLe, behind the reference's own loss call signatures.
 Everything computes in hand-written CUDA (libmuscle_b200.so, C ABI in include/muscle_b200.h);
 there is no CPU or eager fallback.
 """
-from .ops import dense_infonce, debug_tile  # noqa: F401
+from .ops import dense_infonce, dense_infonce_value_and_grad, debug_tile  # noqa: F401
 
-__all__ = ["dense_infonce", "debug_tile"]
+__all__ = ["dense_infonce", "dense_infonce_value_and_grad", "debug_tile"]

@@ -126,6 +126,44 @@ def dense_infonce(x, cls, temperature=0.1, num_classes=21, eps=1e-12):
     return _DenseInfoNCE.apply(x, cls, temperature, num_classes, eps)
 
 
+def dense_infonce_value_and_grad(x, cls, temperature=0.1, num_classes=21, eps=1e-12):
+    """Loss and its input gradient from ONE call of the fused C entry point
+    (``muscle_dense_infonce_fwd_bwd``), without autograd bookkeeping: for a loss at the end of the
+    graph, ``loss, dx = dense_infonce_value_and_grad(feat.detach(), cls); feat.backward(dx)`` saves
+    the autograd engine's thread hand-off (~0.1 ms of host time per step at a 0.3 ms step).
+    Same operands and checks as :func:`dense_infonce`; returns (0-dim loss, dx shaped like ``x``)."""
+    _require_cuda(x, "x")
+    _require_cuda(cls, "cls")
+    if x.dtype != torch.float32:
+        raise TypeError("embeddings must be float32 (the reference path is fp32)")
+    lib = _lib.load()
+    xc, layout, batch, ppi, dim = _as_feature_operand(x.detach())
+    n = batch * ppi
+    cls_c = cls.reshape(-1).contiguous()
+    if cls_c.numel() != n:
+        raise ValueError("cls has %d entries for %d pixels" % (cls_c.numel(), n))
+    if cls_c.dtype not in (torch.int64, torch.int32):
+        cls_c = cls_c.to(torch.int64)
+    cls64 = 1 if cls_c.dtype == torch.int64 else 0
+    key = (n, dim, int(num_classes))
+    ws_bytes = _WS_BYTES.get(key)
+    if ws_bytes is None:
+        ws_bytes = _WS_BYTES[key] = lib.muscle_dense_infonce_workspace_bytes(n, dim, num_classes)
+    if ws_bytes == 0:
+        raise ValueError("unsupported shape: dim=%d (64/128/256), num_classes=%d (<=%d)"
+                         % (dim, num_classes, _lib.MAX_CLASSES))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+    loss = torch.empty((), dtype=torch.float32, device=x.device)
+    dx = torch.empty(xc.shape, dtype=torch.float32, device=x.device)
+    with _on_device(x.device):
+        rc = lib.muscle_dense_infonce_fwd_bwd(
+            xc.data_ptr(), layout, batch, ppi, dim, cls_c.data_ptr(), cls64, num_classes,
+            float(temperature), float(eps), loss.data_ptr(), dx.data_ptr(), ws.data_ptr(), ws_bytes,
+            _stream_ptr(x.device))
+    _lib.check(rc, "dense_infonce_value_and_grad")
+    return loss, dx.reshape(x.shape)
+
+
 def debug_tile(a_bf16: torch.Tensor, b_bf16: torch.Tensor):
     """S = A B^T [128,128] and G = bf16(S) B [128,D] through the tcgen05 building blocks (tests)."""
     lib = _lib.load()

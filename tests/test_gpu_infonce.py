@@ -138,6 +138,28 @@ def test_upstream_gradient_is_applied_in_backward(M):
     assert torch.allclose(xg.grad, dx, rtol=1e-3, atol=1e-8)
 
 
+def test_value_and_grad_matches_autograd_path(M):
+    """dense_infonce_value_and_grad (one fused C call, no autograd) == dense_infonce + backward, both
+    layouts, and against the oracle."""
+    x, cls, _ = O.synth_embeddings(2, 128, 24, 20, seed=23)
+    xr = x.clone().requires_grad_()
+    ref = O.dense_infonce_from_features(xr.permute(0, 2, 3, 1).reshape(-1, 128), cls.reshape(-1), 0.1, 21)
+    gref, = torch.autograd.grad(ref, xr)
+    for to_layout in (lambda t: t, lambda t: t.permute(0, 2, 3, 1).reshape(-1, 128).contiguous()):
+        xa = to_layout(x).cuda().requires_grad_()
+        c = cls.reshape(-1).cuda() if xa.dim() == 2 else cls.cuda()
+        la = M.dense_infonce(xa, c, 0.1, 21)
+        la.backward()
+        lv, dx = M.dense_infonce_value_and_grad(to_layout(x).cuda(), c, 0.1, 21)
+        assert dx.shape == xa.shape and not lv.requires_grad
+        assert abs(lv.item() - la.item()) <= 1e-5 * abs(la.item())
+        assert torch.allclose(dx, xa.grad, rtol=1e-3, atol=1e-8)
+        assert abs(lv.item() - ref.item()) <= LOSS_RTOL * abs(ref.item())
+        assert _cos(dx.cpu(), to_layout(gref)) >= GRAD_COS
+    with pytest.raises(RuntimeError):
+        M.dense_infonce_value_and_grad(torch.randn(64, 128), torch.zeros(64, dtype=torch.int64))
+
+
 def test_permutation_invariance_and_temperature(M):
     x, cls, _ = O.synth_embeddings(2, 128, 16, 16, seed=13)
     flat = x.permute(0, 2, 3, 1).reshape(-1, 128)
