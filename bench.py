@@ -321,6 +321,13 @@ def main():
         assert all(v == v for v in e2e_losses), "NaN loss in the end-to-end run"
     e2e_runs.sort()
     t_e2e, e2e_host_s = e2e_runs[1]
+    # the uploads alone (same buffers, same stream): the PCIe floor of any end-to-end step
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        upload(i)
+    torch.cuda.synchronize()
+    t_h2d = time.perf_counter() - t0
     fused_e2e = None
     if world == 1:      # informational: the same loop through the autograd-free public call
         e2e_pipelined(3, fused=True)
@@ -395,6 +402,8 @@ def main():
                                   "asynchronously; every step's H2D and D2H are inside the timed region",
                              host_enqueue_ms_per_step=1e3 * e2e_host_s / args.steps,
                              value_and_grad=fused_e2e,
+                             h2d_only_ms_per_step=1e3 * t_h2d / args.steps,
+                             h2d_gb_per_s=(x_h.numel() * 4 + c_h.numel() * 8) * args.steps / t_h2d / 1e9,
                              runs_ms_per_step=[1e3 * r[0] / args.steps for r in e2e_runs],
                              runs_note="three runs of `steps` steps each, the median is `value`",
                              serial_value=pairs_per_step * args.steps / t_e2e_serial,
