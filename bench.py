@@ -409,7 +409,7 @@ def main():
                              serial_value=pairs_per_step * args.steps / t_e2e_serial,
                              serial_ms_per_step=1e3 * t_e2e_serial / args.steps,
                              serial_note="upload -> step -> blocking .item() per step, nothing overlapped"),
-                    gpu_launches=int(args.steps * 10), clocks=clocks)
+                    gpu_launches=int(args.steps * 8), clocks=clocks)
         flops_step = 6.0 * dim * pairs_per_step
         line["step_tensor"] = dict(algorithmic_tflops_per_gpu=flops_step * args.steps / t_dev / 1e12 / world,
                                    frac_of_sustained=flops_step * args.steps / t_dev / 1e12 / world / pk["bf16_sustained"],

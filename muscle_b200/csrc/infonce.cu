@@ -158,12 +158,15 @@ size_t muscle_infonce_prepare_scratch_bytes(int64_t n_pixels) {
   return align_up(static_cast<size_t>(n_blk) * MAX_BINS * sizeof(uint32_t), 256);
 }
 
-int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
-                           int dim, const void* cls, int cls_is_int64, int num_classes, float eps,
-                           void* ehat, uint32_t* bits, float* inv_norm, int32_t* perm,
-                           uint32_t* tor, uint32_t* seg, float* class_sum, float* class_mass,
-                           void* scratch, size_t scratch_bytes, void* stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+}  // extern "C"
+
+namespace {
+// unit_off != null: rows == columns, the work partition of the pair passes comes out of the scan kernel
+int prepare_impl(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
+                 int dim, const void* cls, int cls_is_int64, int num_classes, float eps,
+                 void* ehat, uint32_t* bits, float* inv_norm, int32_t* perm,
+                 uint32_t* tor, uint32_t* seg, float* class_sum, float* class_mass,
+                 void* scratch, size_t scratch_bytes, uint32_t* unit_off, cudaStream_t stream) {
   if (int rc = check_device()) return rc;
   if (!x || !cls || !ehat || !bits || !inv_norm || !perm || !tor || !seg || !class_sum ||
       !class_mass || !scratch)
@@ -185,7 +188,7 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
   MB_CUDA(launch_pdl(class_hist_kernel, dim3(n_blk), dim3(SORT_CHUNK), 0, stream, cls, cls_is_int64, static_cast<long long>(n), num_classes, hist,
                      static_cast<long long>(rows_pad), dim, static_cast<uint32_t*>(ehat), bits, inv_norm));
   MB_LAUNCH_CHECK();
-  MB_CUDA(launch_pdl(class_scan_kernel, dim3(1), dim3(1024), 0, stream, hist, n_blk, num_classes, static_cast<long long>(n), static_cast<long long>(rows_pad), seg, class_mass, tor));
+  MB_CUDA(launch_pdl(class_scan_kernel, dim3(1), dim3(1024), 0, stream, hist, n_blk, num_classes, static_cast<long long>(n), static_cast<long long>(rows_pad), seg, class_mass, tor, unit_off));
   MB_LAUNCH_CHECK();
   PrepareParams p;
   p.x = x; p.cls = cls; p.cls64 = cls_is_int64; p.layout = layout; p.n = n;
@@ -216,6 +219,19 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
 }
+}  // namespace
+
+extern "C" {
+
+int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
+                           int dim, const void* cls, int cls_is_int64, int num_classes, float eps,
+                           void* ehat, uint32_t* bits, float* inv_norm, int32_t* perm,
+                           uint32_t* tor, uint32_t* seg, float* class_sum, float* class_mass,
+                           void* scratch, size_t scratch_bytes, void* stream_) {
+  return prepare_impl(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes, eps, ehat,
+                      bits, inv_norm, perm, tor, seg, class_sum, class_mass, scratch, scratch_bytes, nullptr,
+                      static_cast<cudaStream_t>(stream_));
+}
 
 int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows,
                           const uint32_t* tor_rows, int64_t rows_pad, const void* ehat_cols,
@@ -241,11 +257,13 @@ int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows,
                                       cols_pad, prm, stream);
 }
 
-int muscle_infonce_mid(const void* ehat, const uint32_t* seg, int64_t rows_pad, int dim,
-                       int num_classes, const float* class_sum, const float* class_mass,
-                       float* rowsum, float temperature, float* w, float* gpos, double* loss_acc,
-                       float* dproto, void* stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+}  // extern "C"
+
+namespace {
+int launch_mid(const void* ehat, const uint32_t* seg, int64_t rows_pad, int dim, int num_classes,
+               const float* class_sum, const float* class_mass, float* rowsum, float temperature,
+               float* w, float* gpos, double* loss_acc, float* dproto, float* loss_out,
+               unsigned int* ticket, cudaStream_t stream) {
   if (int rc = check_device()) return rc;
   if (!ehat || !seg || !class_sum || !class_mass || !rowsum || !w || !gpos || !loss_acc || !dproto)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
@@ -257,12 +275,24 @@ int muscle_infonce_mid(const void* ehat, const uint32_t* seg, int64_t rows_pad, 
   p.ehat = static_cast<const __nv_bfloat16*>(ehat); p.seg = seg; p.C = num_classes;
   p.class_sum = class_sum; p.class_mass = class_mass; p.rowsum = rowsum;
   p.inv_tau = 1.f / temperature; p.w = w; p.gpos = gpos; p.loss_acc = loss_acc; p.dproto = dproto;
+  p.loss_out = loss_out; p.ticket = ticket;
   const int grid = static_cast<int>(rows_pad / SEG_ROWS);
   if (dim == 64) MB_CUDA(launch_pdl(mid_kernel<64>, dim3(grid), dim3(SEG_THREADS), 0, stream, p));
   else if (dim == 128) MB_CUDA(launch_pdl(mid_kernel<128>, dim3(grid), dim3(SEG_THREADS), 0, stream, p));
   else MB_CUDA(launch_pdl(mid_kernel<256>, dim3(grid), dim3(SEG_THREADS), 0, stream, p));
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int muscle_infonce_mid(const void* ehat, const uint32_t* seg, int64_t rows_pad, int dim,
+                       int num_classes, const float* class_sum, const float* class_mass,
+                       float* rowsum, float temperature, float* w, float* gpos, double* loss_acc,
+                       float* dproto, void* stream_) {
+  return launch_mid(ehat, seg, rows_pad, dim, num_classes, class_sum, class_mass, rowsum, temperature, w,
+                    gpos, loss_acc, dproto, nullptr, nullptr, static_cast<cudaStream_t>(stream_));
 }
 
 int muscle_infonce_part_slots(void) { return PAIR_SLOTS; }
@@ -360,7 +390,7 @@ namespace {
 
 struct Workspace {
   size_t ehat, bits, inv_norm, perm, tor, unit_off, rowsum, w, gpos, small, scratch, part, total;
-  size_t seg, class_sum, class_mass, dproto, loss_acc, small_bytes;  // offsets inside `small`
+  size_t seg, class_sum, class_mass, dproto, loss_acc, ticket, small_bytes;  // offsets inside `small`
   size_t zero_lo, zero_bytes;  // rowsum .. small are zeroed with one memset
   int64_t rows_pad;
 };
@@ -386,6 +416,7 @@ Workspace plan_workspace(int64_t n, int dim, int C) {
   ws.class_mass = take_small(static_cast<size_t>(C) * 4);
   ws.dproto = take_small(static_cast<size_t>(C) * dim * 4);
   ws.loss_acc = take_small(8);
+  ws.ticket = take_small(4);
   ws.seg = take_small(static_cast<size_t>(C + 2) * 4);
   ws.small_bytes = s;
   ws.small = take(s);
@@ -411,7 +442,7 @@ namespace {
 struct Carved {
   void* ehat; uint32_t* bits; float* inv_norm; int32_t* perm; uint32_t* tor; uint32_t* unit_off;
   float *rowsum, *w, *gpos, *class_sum, *class_mass, *dproto, *part;
-  double* loss_acc; uint32_t* seg; char* scratch;
+  double* loss_acc; uint32_t* seg; char* scratch; unsigned int* ticket;
 };
 Carved carve(void* workspace, const Workspace& ws) {
   char* base = static_cast<char*>(workspace);
@@ -430,6 +461,7 @@ Carved carve(void* workspace, const Workspace& ws) {
   c.class_mass = reinterpret_cast<float*>(small + ws.class_mass);
   c.dproto = reinterpret_cast<float*>(small + ws.dproto);
   c.loss_acc = reinterpret_cast<double*>(small + ws.loss_acc);
+  c.ticket = reinterpret_cast<unsigned int*>(small + ws.ticket);
   c.seg = reinterpret_cast<uint32_t*>(small + ws.seg);
   c.part = reinterpret_cast<float*>(base + ws.part);
   c.scratch = base + ws.scratch;
@@ -488,27 +520,27 @@ struct StageTimer {
 // prepare -> plan -> row sums -> mid: everything the loss needs
 int composite_forward(const float* x, int layout, int64_t batch, int64_t pixels_per_image, int dim,
                       const void* cls, int cls_is_int64, int num_classes, float temperature, float eps,
-                      void* workspace, const Workspace& ws, const Carved& c, cudaStream_t stream) {
+                      float* loss_out, void* workspace, const Workspace& ws, const Carved& c,
+                      cudaStream_t stream) {
   const int64_t n = batch * pixels_per_image;
   StageTimer tm(stream);
   tm.mark("start");
   MB_CUDA(cudaMemsetAsync(static_cast<char*>(workspace) + ws.zero_lo, 0, ws.zero_bytes, stream));
-  int rc = muscle_infonce_prepare(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64,
-                                  num_classes, eps, c.ehat, c.bits, c.inv_norm, c.perm, c.tor, c.seg,
-                                  c.class_sum, c.class_mass, c.scratch,
-                                  muscle_infonce_prepare_scratch_bytes(n), stream);
+  if (static_cast<double>(ws.rows_pad / 128) * static_cast<double>(ws.rows_pad / 128) >= 4.0e9)
+    return fail(MUSCLE_ERR_BAD_ARG, "too many tile units for one rank");
+  // (the work partition `unit_off` comes out of the scan kernel: no plan launch)
+  int rc = prepare_impl(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes, eps,
+                        c.ehat, c.bits, c.inv_norm, c.perm, c.tor, c.seg, c.class_sum, c.class_mass,
+                        c.scratch, muscle_infonce_prepare_scratch_bytes(n), c.unit_off, stream);
   if (rc) return rc;
-  tm.mark("memsets+hist+scan+prepare+class_sum");
-  rc = muscle_infonce_plan(c.tor, ws.rows_pad, c.tor, ws.rows_pad, dim, c.unit_off, stream);
-  if (rc) return rc;
-  tm.mark("plan");
+  tm.mark("memset+hist+scan(+plan)+prepare+class_sum");
   rc = muscle_infonce_rowsum(c.ehat, c.bits, c.tor, ws.rows_pad, c.ehat, c.bits, c.tor, ws.rows_pad,
                              c.unit_off, dim, temperature, c.rowsum, stream);
   if (rc) return rc;
   tm.mark("rowsum");
-  rc = muscle_infonce_mid(c.ehat, c.seg, ws.rows_pad, dim, num_classes, c.class_sum, c.class_mass,
-                          c.rowsum, temperature, c.w, c.gpos, c.loss_acc, c.dproto, stream);
-  tm.mark("mid");
+  rc = launch_mid(c.ehat, c.seg, ws.rows_pad, dim, num_classes, c.class_sum, c.class_mass, c.rowsum,
+                  temperature, c.w, c.gpos, c.loss_acc, c.dproto, loss_out, c.ticket, stream);
+  tm.mark("mid (+ loss)");
   tm.report("forward");
   return rc;
 }
@@ -547,10 +579,11 @@ int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
     return rc;
   const Carved c = carve(workspace, ws);
   if (int rc = composite_forward(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes,
-                                 temperature, eps, workspace, ws, c, stream))
+                                 temperature, eps, loss_out, workspace, ws, c, stream))
     return rc;
+  if (!dx_out) return MUSCLE_OK;
   return composite_backward(layout, batch, pixels_per_image, dim, num_classes, temperature, nullptr, dx_out,
-                            loss_out, ws, c, stream);
+                            nullptr, ws, c, stream);
 }
 
 int muscle_dense_infonce_fwd(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
@@ -563,11 +596,9 @@ int muscle_dense_infonce_fwd(const float* x, int layout, int64_t batch, int64_t 
   if (int rc = check_composite(dim, num_classes, temperature, batch, pixels_per_image, workspace, workspace_bytes, &ws))
     return rc;
   const Carved c = carve(workspace, ws);
-  if (int rc = composite_forward(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes,
-                                 temperature, eps, workspace, ws, c, stream))
-    return rc;
-  return composite_backward(layout, batch, pixels_per_image, dim, num_classes, temperature, nullptr, nullptr,
-                            loss_out, ws, c, stream);
+  // the loss is written by the last block of mid_kernel: no separate launch for it
+  return composite_forward(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes,
+                           temperature, eps, loss_out, workspace, ws, c, stream);
 }
 
 int muscle_dense_infonce_bwd(int layout, int64_t batch, int64_t pixels_per_image, int dim,

@@ -138,11 +138,9 @@ __device__ __forceinline__ bool tile_pair_full(uint32_t tor_r, uint32_t tor_c) {
 // against the column tile (tile_pair_dead), which depends on the column tile only through
 // "empty" / "exactly class c", so a histogram of the column tiles gives every row block's count.
 template <int QT>
-__global__ void __launch_bounds__(1024) pair_plan_kernel(const uint32_t* tor_row, int n_row_blocks,
-                                                         const uint32_t* tor_col, int n_col_tiles,
-                                                         uint32_t* unit_off) {
-  pdl_trigger();
-  pdl_wait();
+__device__ __forceinline__ void pair_plan_body(const uint32_t* tor_row, int n_row_blocks,
+                                               const uint32_t* tor_col, int n_col_tiles,
+                                               uint32_t* unit_off) {
   __shared__ uint32_t single[32];   // column tiles whose class set is exactly {c}
   __shared__ uint32_t empty_cnt;    // column tiles without any class
   __shared__ uint32_t warp_tot[32];
@@ -192,6 +190,17 @@ __global__ void __launch_bounds__(1024) pair_plan_kernel(const uint32_t* tor_row
     __syncthreads();
   }
   if (threadIdx.x == 0) unit_off[n_row_blocks] = carry;
+}
+
+// One block of 1024 threads.  (The single-GPU composite runs the same body at the end of
+// class_scan_kernel, which produces `tor`, instead of launching this.)
+template <int QT>
+__global__ void __launch_bounds__(1024) pair_plan_kernel(const uint32_t* tor_row, int n_row_blocks,
+                                                         const uint32_t* tor_col, int n_col_tiles,
+                                                         uint32_t* unit_off) {
+  pdl_trigger();
+  pdl_wait();
+  pair_plan_body<QT>(tor_row, n_row_blocks, tor_col, n_col_tiles, unit_off);
 }
 
 // ------------------------------------------------------------------------------------------

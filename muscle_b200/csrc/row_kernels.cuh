@@ -14,6 +14,7 @@
 #include <cuda_bf16.h>
 
 #include "ptx.cuh"
+#include "pair_kernel.cuh"
 
 namespace mb200 {
 
@@ -72,7 +73,7 @@ __global__ void __launch_bounds__(SORT_CHUNK) class_hist_kernel(const void* cls,
 __global__ void __launch_bounds__(1024) class_scan_kernel(uint32_t* hist, int n_blk, int C,
                                                           long long n, long long rows_pad,
                                                           uint32_t* seg, float* class_mass,
-                                                          uint32_t* tor) {
+                                                          uint32_t* tor, uint32_t* unit_off) {
   pdl_trigger();
   pdl_wait();
   __shared__ uint32_t total[MAX_BINS + 1];
@@ -129,6 +130,12 @@ __global__ void __launch_bounds__(1024) class_scan_kernel(uint32_t* hist, int n_
       if (static_cast<long long>(start[c]) < r1 && static_cast<long long>(start[c + 1]) > r0) u |= 1u << c;
     if (r1 > static_cast<long long>(start[C])) u |= 0x80000000u;
     tor[tile] = u;
+  }
+  // rows and columns are the same pixels (single GPU): number the live (row tile, column tile)
+  // units here instead of in a launch of their own
+  if (unit_off != nullptr) {
+    __syncthreads();
+    pair_plan_body<1>(tor, static_cast<int>(n_tiles), tor, static_cast<int>(n_tiles), unit_off);
   }
 }
 
@@ -401,6 +408,8 @@ struct MidParams {
   float* gpos;                 // [rows_pad] d loss_q / d pos-logit_q (before the 1/n_valid factor)
   double* loss_acc;            // += sum_q (1/tau + ln rowsum_q - pos_q)
   float* dproto;               // [C][D] += sum_q gpos_q e_q
+  float* loss_out;             // optional: the last block to finish writes loss_acc / n_valid here
+  unsigned int* ticket;        // zeroed counter of finished blocks (with loss_out)
 };
 
 // Same tiling as class_sum_kernel.  Rows of the invalid segment and pad rows get w = gpos = 0.
@@ -472,6 +481,16 @@ __global__ void __launch_bounds__(SEG_THREADS) mid_kernel(const MidParams p) {
     double t = 0.0;
     for (int i = 0; i < SEG_THREADS / 32; ++i) t += loss_sh[i];
     if (t != 0.0) atomicAdd(p.loss_acc, t);
+    if (p.loss_out != nullptr) {   // single-GPU composite: the mean is written here, no extra launch
+      __threadfence();
+      if (atomicAdd(p.ticket, 1u) == gridDim.x - 1) {
+        __threadfence();
+        float nv = 0.f;
+        for (int c = 0; c < p.C; ++c) nv += p.class_mass[c];
+        const double tot = atomicAdd(p.loss_acc, 0.0);
+        *p.loss_out = static_cast<float>(tot / static_cast<double>(nv));  // 0/0 -> NaN like the reference
+      }
+    }
   }
 }
 
