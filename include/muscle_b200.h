@@ -298,6 +298,21 @@ int muscle_emd_dynamic_fwd_bwd(const float* flat1, const float* flat2, const int
                                size_t scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * EMD()(crops1, crops2, mode='static') — replaces src/loss_multilabel.py:259-285 (the class's
+ * default mode; fed by get_static_crops, src/torchutils.py:177-214).  Regions are [n, C, h, w]
+ * blocks in two flat buffers; pair_desc int64 [n_pairs, 12] = {offset in flat1, n*C, h1, w1, oh1,
+ * ow1, offset in flat2, h2, w2, oh2, ow2, n} with (oh, ow) the resize target of :265-269 /
+ * :275-278 (host integer arithmetic), h, w <= 1024.  Per pair: mean over the resized position
+ * pairs and the batch dim of 1 - x.y; loss_out = sum of the two smallest (stable order);
+ * dists_out [n_pairs] (optional) = every pair's value; dflat1_out (size total1, fully written) =
+ * d loss / d flat1, or NULL.  n_pairs >= 2 (the reference indexes dists[1]). */
+size_t muscle_emd_static_scratch_bytes(int n_pairs, int max_planes);
+int muscle_emd_static_fwd_bwd(const float* flat1, const float* flat2, const int64_t* pair_desc,
+                              int n_pairs, int max_planes, float* loss_out, float* dists_out,
+                              float* dflat1_out, int64_t total1, void* scratch,
+                              size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Debug / unit-test entry points for the tcgen05 building blocks (used by tests/ only).
  * sim: S[128,128] = A[128,dim] B[128,dim]^T ;  tsg: G[128,dim] = bf16(S) B  (A from TMEM). */
 int muscle_debug_tile(const void* a_bf16, const void* b_bf16, int dim, float* s_out,

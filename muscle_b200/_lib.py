@@ -80,6 +80,9 @@ _SIGNATURES = {
     "muscle_emd_dynamic_fwd_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64,
                                            c_int64, c_float, c_int, c_void_p, c_void_p, c_int64, c_void_p, c_size_t,
                                            c_void_p]),
+    "muscle_emd_static_scratch_bytes": (c_size_t, [c_int, c_int]),
+    "muscle_emd_static_fwd_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                          c_int64, c_void_p, c_size_t, c_void_p]),
     "muscle_info_nce_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int]),
     "muscle_info_nce_fwd_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_float, c_int,
                                         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,

@@ -350,6 +350,123 @@ __global__ void __launch_bounds__(256) emd_select_kernel(const float* scores, co
   if (threadIdx.x == 0) *loss_out = tot / static_cast<float>(n_images);
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// EMD.static_matching (src/loss_multilabel.py:259-285).  For pair i both regions are resized
+// (bilinear, align_corners=True) to at most 7x7 and the value is the MEAN of 1 - x_p . y_q over all
+// position pairs and the batch dim; a mean of a bilinear form factorises:
+//   dist_i = 1 - (1/n) sum_{b,c} xbar[b,c] ybar[b,c],  xbar = mean over the resized grid,
+// and the mean over the resized grid is a separable weighted mean of the SOURCE pixels
+// (weight = wr[row] wc[col] / (oh ow), wr/wc = column sums of the interpolation matrices).  So the
+// resized maps and the [M,N,C] broadcast product of the reference are never formed: one read of
+// both regions, two scalars per plane.
+struct StaticDesc {   // int64[12] rows from the host
+  long long off1, planes, h1, w1, oh1, ow1, off2, h2, w2, oh2, ow2, batch;
+};
+constexpr int ST_MAX_SIDE = 1024;
+constexpr int ST_THREADS = 256;
+
+// wts[r] = sum over output index i of the bilinear weight of source index r (align_corners=True:
+// src = i (in-1)/(out-1), out == 1 reads index 0), times `norm`.
+__device__ void static_axis_weights(float* wts, int in, int out, float norm) {
+  const float scale = out > 1 ? static_cast<float>(in - 1) / static_cast<float>(out - 1) : 0.f;
+  for (int r = threadIdx.x; r < in; r += blockDim.x) {
+    float acc = 0.f;
+    for (int i = 0; i < out; ++i) {
+      const float src = scale * static_cast<float>(i);
+      const int i0 = min(static_cast<int>(src), in - 1);
+      const int i1 = i0 + (i0 < in - 1 ? 1 : 0);
+      const float l1 = src - static_cast<float>(i0);
+      acc += (i0 == r ? 1.f - l1 : 0.f) + (i1 == r ? l1 : 0.f);
+    }
+    wts[r] = acc * norm;
+  }
+}
+
+// grid (n_pairs, 2 sides): means[(pair*2 + side) * max_planes + plane].
+__global__ void __launch_bounds__(ST_THREADS) emd_static_mean_kernel(const float* flat1, const float* flat2,
+                                                                     const StaticDesc* desc, int max_planes,
+                                                                     float* means) {
+  __shared__ float wr[ST_MAX_SIDE], wc[ST_MAX_SIDE];
+  const StaticDesc d = desc[blockIdx.x];
+  const int side = blockIdx.y;
+  const int h = static_cast<int>(side ? d.h2 : d.h1), w = static_cast<int>(side ? d.w2 : d.w1);
+  const int oh = static_cast<int>(side ? d.oh2 : d.oh1), ow = static_cast<int>(side ? d.ow2 : d.ow1);
+  const float* src = side ? flat2 + d.off2 : flat1 + d.off1;
+  float* out = means + (static_cast<size_t>(blockIdx.x) * 2 + side) * max_planes;
+  if (h < 1 || w < 1 || h > ST_MAX_SIDE || w > ST_MAX_SIDE || oh < 1 || ow < 1) {   // descriptor out of range: poison, loudly
+    for (int p = threadIdx.x; p < d.planes; p += blockDim.x) out[p] = __int_as_float(0x7fc00000);
+    return;
+  }
+  static_axis_weights(wr, h, oh, 1.f / static_cast<float>(oh));
+  static_axis_weights(wc, w, ow, 1.f / static_cast<float>(ow));
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, hw = h * w;
+  for (int p = warp; p < d.planes; p += ST_THREADS / 32) {
+    const float* x = src + static_cast<size_t>(p) * hw;
+    float acc = 0.f;
+    for (int i = lane; i < hw; i += 32) {
+      const int r = i / w;
+      acc = fmaf(x[i], wr[r] * wc[i - r * w], acc);
+    }
+    acc = warp_sum_f(acc);
+    if (lane == 0) out[p] = acc;
+  }
+}
+
+// One block: dist per pair (a warp each), then the two smallest in list.sort() order (stable: the
+// first of equal values wins), loss = their sum (:283-284).
+__global__ void __launch_bounds__(ST_THREADS) emd_static_select_kernel(const StaticDesc* desc, const float* means,
+                                                                       int n_pairs, int max_planes, float* dists,
+                                                                       int* sel, float* loss_out) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int p = warp; p < n_pairs; p += ST_THREADS / 32) {
+    const float* xb = means + static_cast<size_t>(p) * 2 * max_planes;
+    const float* yb = xb + max_planes;
+    const int planes = static_cast<int>(desc[p].planes);
+    float acc = 0.f;
+    for (int i = lane; i < planes; i += 32) acc = fmaf(xb[i], yb[i], acc);
+    acc = warp_sum_f(acc);
+    if (lane == 0) dists[p] = 1.f - acc / static_cast<float>(desc[p].batch);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int a = 0;
+    for (int p = 1; p < n_pairs; ++p)
+      if (dists[p] < dists[a]) a = p;
+    int b = -1;
+    for (int p = 0; p < n_pairs; ++p)
+      if (p != a && (b < 0 || dists[p] < dists[b])) b = p;
+    sel[0] = a;
+    sel[1] = b;
+    *loss_out = dists[a] + dists[b];
+  }
+}
+
+// grid (plane chunks, 2 kept pairs): d dist / d x[b,c,r,col] = -(1/n) ybar[b,c] wr[r] wc[col].
+__global__ void __launch_bounds__(ST_THREADS) emd_static_grad_kernel(const StaticDesc* desc, const float* means,
+                                                                     const int* sel, int max_planes, float* dflat1) {
+  __shared__ float wr[ST_MAX_SIDE], wc[ST_MAX_SIDE];
+  const int pair = sel[blockIdx.y];
+  const StaticDesc d = desc[pair];
+  const int h = static_cast<int>(d.h1), w = static_cast<int>(d.w1), hw = h * w;
+  if (h < 1 || w < 1 || h > ST_MAX_SIDE || w > ST_MAX_SIDE || d.oh1 < 1 || d.ow1 < 1) return;
+  static_axis_weights(wr, h, static_cast<int>(d.oh1), 1.f / static_cast<float>(d.oh1));
+  static_axis_weights(wc, w, static_cast<int>(d.ow1), 1.f / static_cast<float>(d.ow1));
+  __syncthreads();
+  const float* yb = means + (static_cast<size_t>(pair) * 2 + 1) * max_planes;
+  const float inv_n = -1.f / static_cast<float>(d.batch);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int p = blockIdx.x * (ST_THREADS / 32) + warp; p < d.planes; p += gridDim.x * (ST_THREADS / 32)) {
+    const float coef = yb[p] * inv_n;
+    float* g = dflat1 + d.off1 + static_cast<size_t>(p) * hw;
+    for (int i = lane; i < hw; i += 32) {
+      const int r = i / w;
+      g[i] = coef * wr[r] * wc[i - r * w];
+    }
+  }
+}
+
 }  // namespace
 
 namespace {
@@ -576,6 +693,45 @@ int muscle_emd_dynamic_fwd_bwd(const float* flat1, const float* flat2, const int
     emd_grad_kernel<<<n_images, EMD_THREADS, smem_g, stream>>>(flat1, flat2, pairs, best, reg, maxiter,
                                                                1.f / static_cast<float>(n_images), hist,
                                                                static_cast<size_t>(maxiter + 1) * max_n_plus_m, dflat1_out);
+    MB_LAUNCH_CHECK();
+  }
+  return MUSCLE_OK;
+}
+
+size_t muscle_emd_static_scratch_bytes(int n_pairs, int max_planes) {
+  if (n_pairs <= 0 || max_planes <= 0) return 0;
+  const size_t means = (static_cast<size_t>(n_pairs) * 2 * max_planes * 4 + 255) / 256 * 256;
+  const size_t dists = (static_cast<size_t>(n_pairs) * 4 + 255) / 256 * 256;
+  return means + dists + 256;
+}
+
+int muscle_emd_static_fwd_bwd(const float* flat1, const float* flat2, const int64_t* pair_desc, int n_pairs,
+                              int max_planes, float* loss_out, float* dists_out, float* dflat1_out, int64_t total1,
+                              void* scratch, size_t scratch_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = need_sm100()) return rc;
+  if (!flat1 || !flat2 || !pair_desc || !loss_out || !scratch) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (n_pairs < 2) return fail(MUSCLE_ERR_BAD_ARG, "static matching sums the two smallest distances: needs >= 2 pairs (got %d)", n_pairs);
+  if (max_planes <= 0) return fail(MUSCLE_ERR_BAD_ARG, "regions must have batch*channels >= 1 planes");
+  if (scratch_bytes < muscle_emd_static_scratch_bytes(n_pairs, max_planes))
+    return fail(MUSCLE_ERR_WORKSPACE, "scratch too small");
+  char* base = static_cast<char*>(scratch);
+  float* means = reinterpret_cast<float*>(base);
+  size_t off = (static_cast<size_t>(n_pairs) * 2 * max_planes * 4 + 255) / 256 * 256;
+  float* dists = reinterpret_cast<float*>(base + off);
+  off += (static_cast<size_t>(n_pairs) * 4 + 255) / 256 * 256;
+  int* sel = reinterpret_cast<int*>(base + off);
+  const StaticDesc* desc = reinterpret_cast<const StaticDesc*>(pair_desc);
+  emd_static_mean_kernel<<<dim3(n_pairs, 2), ST_THREADS, 0, stream>>>(flat1, flat2, desc, max_planes, means);
+  MB_LAUNCH_CHECK();
+  emd_static_select_kernel<<<1, ST_THREADS, 0, stream>>>(desc, means, n_pairs, max_planes, dists, sel, loss_out);
+  MB_LAUNCH_CHECK();
+  if (dists_out)
+    MB_CUDA(cudaMemcpyAsync(dists_out, dists, static_cast<size_t>(n_pairs) * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  if (dflat1_out) {
+    MB_CUDA(cudaMemsetAsync(dflat1_out, 0, static_cast<size_t>(total1) * sizeof(float), stream));
+    const int chunks = std::min(16, (max_planes + ST_THREADS / 32 - 1) / (ST_THREADS / 32));
+    emd_static_grad_kernel<<<dim3(chunks, 2), ST_THREADS, 0, stream>>>(desc, means, sel, max_planes, dflat1_out);
     MB_LAUNCH_CHECK();
   }
   return MUSCLE_OK;

@@ -108,6 +108,36 @@ class _EmdDynamic(torch.autograd.Function):
         return (None if d1 is None else d1 * gloss,) + (None,) * 10
 
 
+class _EmdStatic(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, flat1, flat2, pair_desc, n_pairs, max_planes):
+        lib = _lib.load()
+        dev = flat1.device
+        f1, f2 = flat1.contiguous(), flat2.contiguous()
+        sb = lib.muscle_emd_static_scratch_bytes(n_pairs, max_planes)
+        scratch = torch.empty(sb, dtype=torch.uint8, device=dev)
+        loss = torch.empty((), dtype=torch.float32, device=dev)
+        dists = torch.empty(n_pairs, dtype=torch.float32, device=dev)
+        d1 = torch.empty_like(f1) if flat1.requires_grad else None
+        call("muscle_emd_static_fwd_bwd", dev, f1.data_ptr(), f2.data_ptr(), pair_desc.data_ptr(), n_pairs, max_planes,
+             loss.data_ptr(), dists.data_ptr(), ptr(d1), f1.numel(), scratch.data_ptr(), sb)
+        ctx.save_for_backward(d1)
+        ctx.mark_non_differentiable(dists)
+        return loss, dists
+
+    @staticmethod
+    def backward(ctx, gloss, _gdists):
+        d1, = ctx.saved_tensors
+        return (None if d1 is None else d1 * gloss,) + (None,) * 4
+
+
+def _static_target_shape(h, w, long_side=7):
+    """src/loss_multilabel.py:265-269, :275-278 (python round: half to even, as the reference)."""
+    if w < h:
+        return int(round(w * long_side / h)), long_side
+    return long_side, int(round(h * long_side / w))
+
+
 def _pack_regions(crops):
     """nested lists of [1,C,h,w] tensors -> (flat, meta, C).  Lists made by
     muscle_b200.torchutils.get_dynamic_crops already carry their flat buffer; anything else is
@@ -131,8 +161,8 @@ def _pack_regions(crops):
 
 
 class EMD:
-    """src/loss_multilabel.py:108-338, the members on the trainer's path: ``EMD()(crops1, crops2,
-    mode='dynamic')`` (train_mcl.py:147,221).  Gradient flows to crops1; crops2 and the Sinkhorn
+    """src/loss_multilabel.py:108-338: ``EMD()(crops1, crops2, mode='dynamic')`` (train_mcl.py:147,221,
+    the trainer's path) and ``mode='static'`` (:259-285, the class default, fed by get_static_crops).  Gradient flows to crops1; crops2 and the Sinkhorn
     marginals are constants, as in the reference (:308-313, train_mcl.py:220 passes vw2.detach())."""
 
     reg = 0.1        # :207
@@ -155,12 +185,40 @@ class EMD:
         return _EmdDynamic.apply(flat1, flat2, desc, len(rows), len(meta1), ch, max_n, max_m, max_nm, self.reg,
                                  self.maxiter)
 
+    def static_matching(self, crops1, crops2, return_dists=False):
+        """src/loss_multilabel.py:259-285.  crops1, crops2: flat lists of [n,C,h,w] tensors of equal
+        length >= 2 (what get_static_crops makes); pair i is (crops1[i], crops2[i]).  Returns the sum
+        of the two smallest pair distances (0-dim tensor; grad flows to crops1 only, :273)."""
+        if len(crops1) != len(crops2) or len(crops1) < 2:
+            raise ValueError("static matching needs two lists of equal length >= 2 (the reference sums dists[0] + dists[1])")
+        rows, p1, p2, off1, off2, max_planes = [], [], [], 0, 0, 0
+        for a, b in zip(crops1, crops2):
+            require_cuda_f32(a, "crop")
+            require_cuda_f32(b, "crop")
+            if a.dim() != 4 or b.dim() != 4 or a.shape[:2] != b.shape[:2]:
+                raise ValueError("paired crops must be [n,C,h,w] tensors with the same n and C")
+            n, c, h1, w1 = a.shape
+            h2, w2 = b.shape[2:]
+            (oh1, ow1), (oh2, ow2) = _static_target_shape(h1, w1), _static_target_shape(h2, w2)
+            if min(h1, w1, h2, w2, oh1, ow1, oh2, ow2) < 1 or max(h1, w1, h2, w2) > 1024:
+                raise ValueError("crop sides must be 1..1024 px and resize to at least one pixel (got %s, %s)"
+                                 % (tuple(a.shape), tuple(b.shape)))
+            rows.append([off1, n * c, h1, w1, oh1, ow1, off2, h2, w2, oh2, ow2, n])
+            p1.append(a.reshape(-1))
+            p2.append(b.detach().reshape(-1))
+            off1 += a.numel()
+            off2 += b.numel()
+            max_planes = max(max_planes, n * c)
+        flat1, flat2 = torch.cat(p1), torch.cat(p2)      # plumbing: autograd routes d flat1 back to every crop
+        desc = torch.tensor(rows, dtype=torch.int64).to(flat1.device, non_blocking=True)
+        loss, dists = _EmdStatic.apply(flat1, flat2, desc, len(rows), max_planes)
+        return (loss, dists) if return_dists else loss
+
     def __call__(self, crops1, crops2, mode="static"):
         if mode == "dynamic":
             return self.dynamic_matching(crops1, crops2)
         if mode == "static":
-            raise NotImplementedError("EMD mode='static' is not on the trainer's path (train_mcl.py:221 uses "
-                                      "'dynamic') and is not built")
+            return self.static_matching(crops1, crops2)
         print("Unrecognised mode!")      # :335-336
         return None
 

@@ -132,3 +132,32 @@ def get_dynamic_crops(x1, coord1, x2, coord2):
     if not rows1:
         return [], [], []
     return _extract(x1, rows1, shapes1), _extract(x2, rows2, shapes2), batch_indices
+
+
+def get_static_crops(x1, coord1, x2, coord2):
+    """src/torchutils.py:177-214.  x1, x2 [B,C,H,W] fp32 CUDA; coord [B,4] = (top, left, h, w).
+    -> (crops1, crops2, batch_indices): flat lists of nine half-size windows of view 1's overlap box
+    and nine third-size windows of view 2's per kept image, as [1,C,·,·] VIEWS (slicing only, no
+    arithmetic: grad flows to x1/x2 through autograd's own slice nodes); boxes under 15 px or more
+    elongated than 7:1 are skipped (:199).  Feed to ``EMD()(crops1, crops2, mode='static')``."""
+    require_cuda_f32(x1, "x1")
+    require_cuda_f32(x2, "x2")
+    c1 = coord1.detach().to("cpu").long().tolist()
+    c2 = coord2.detach().to("cpu").long().tolist()
+    crops1, crops2, batch_indices = [], [], []
+    for b in range(x1.shape[0]):
+        t1, l1, bh1, bw1 = c1[b]
+        t2, l2, bh2, bw2 = c2[b]
+        ins1 = x1[b:b + 1, :, t1:t1 + bh1, l1:l1 + bw1]
+        ins2 = x2[b:b + 1, :, t2:t2 + bh2, l2:l2 + bw2]
+        h, w = ins1.shape[2:]                             # both window grids use view 1's box size (:197)
+        if h < 15 or w < 15 or h / w > 7 or w / h > 7:
+            continue
+        for i in (0, h // 4, h // 2):
+            for j in (0, w // 4, w // 2):
+                crops1.append(ins1[:, :, i:i + h // 2, j:j + w // 2])
+        for i in (0, h // 3, 2 * h // 3):
+            for j in (0, w // 3, 2 * w // 3):
+                crops2.append(ins2[:, :, i:i + h // 3, j:j + w // 3])
+                batch_indices.append(b)
+    return crops1, crops2, batch_indices

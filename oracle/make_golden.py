@@ -129,6 +129,27 @@ def gen_emd(src):
                 loss=loss.detach(), g1=g1, sk_cost=cost, sk_w1=w1, sk_w2=w2, sk_value=sk)
 
 
+def gen_emd_static(src):
+    """get_static_crops + EMD()(…, mode='static') (src/torchutils.py:177-214, src/loss_multilabel.py:259-285)."""
+    g = torch.Generator().manual_seed(15)
+    raw1 = F.avg_pool2d(torch.randn(3, 21, 40, 40, generator=g), 5, 1, 2).requires_grad_()
+    raw2 = F.avg_pool2d(torch.randn(3, 21, 40, 40, generator=g), 5, 1, 2)
+    vw1 = F.normalize(torch.softmax(raw1 * 4, 1), dim=1)
+    vw2 = F.normalize(torch.softmax(raw2 * 4, 1), dim=1)
+    c1 = torch.tensor([[0, 6, 34, 22], [4, 0, 17, 40], [0, 0, 10, 30]])      # third box is skipped (h < 15)
+    c2 = torch.tensor([[6, 0, 34, 22], [0, 0, 17, 40], [20, 5, 10, 30]])
+    crops1, crops2, bidx = src.torchutils.get_static_crops(vw1, c1, vw2.detach(), c2)
+    emd = src.loss_multilabel.EMD()
+    loss = emd(crops1, crops2)                                                # default mode is 'static'
+    g1, = torch.autograd.grad(loss, raw1)
+    dists = []
+    for a, b in zip(crops1, crops2):
+        dists.append(emd.static_matching([a, a], [b, b]).detach() / 2)
+    return dict(raw1=raw1.detach(), raw2=raw2, c1=c1, c2=c2, batch_indices=bidx,
+                crop_shapes1=[tuple(t.shape) for t in crops1], crop_shapes2=[tuple(t.shape) for t in crops2],
+                loss=loss.detach(), g1=g1, dists=torch.stack(dists))
+
+
 def gen_heads(src):
     """CAM head + embedding + PCM evaluated in situ by the reference model (b3, random weights)."""
     torch.manual_seed(3)
@@ -200,7 +221,7 @@ def main():
     src = reference_loader.load()
     os.makedirs(OUT, exist_ok=True)
     jobs = dict(info_nce=gen_info_nce, dense_infonce=gen_dense_infonce, imc=gen_imc, pixpro=gen_pixpro,
-                emd=gen_emd, heads=gen_heads, fieldloss=gen_fieldloss)
+                emd=gen_emd, emd_static=gen_emd_static, heads=gen_heads, fieldloss=gen_fieldloss)
     only = sys.argv[1:]
     for name, fn in jobs.items():
         if only and name not in only:

@@ -246,6 +246,58 @@ def emd_dynamic(crops1, crops2):
     return total / len(crops1)
 
 
+def static_target_shape(h, w, long_side=7):
+    """src/loss_multilabel.py:265-269 (and :275-278): the output size handed to F.interpolate —
+    (round(w*7/h), 7) when w < h, else (7, round(h*7/w)); python round (half to even)."""
+    if w < h:
+        return (int(round(w * long_side / h)), long_side)
+    return (long_side, int(round(h * long_side / w)))
+
+
+def emd_static(crops1, crops2):
+    """src/loss_multilabel.py:259-285 (EMD()(…, mode='static'), the default mode).
+
+    Pair i: both regions resized (bilinear, align_corners=True) to static_target_shape, cost
+    1 - x y^T over all position pairs and the batch dim (:281), its mean (:282); region 2 is
+    resized without grad (:273).  The list of means is sorted and the two smallest are summed
+    (:283-284).  Returns (loss, dists [L])."""
+    dists = []
+    for a, b in zip(crops1, crops2):
+        n, c = a.shape[:2]
+        x = F.interpolate(a, size=static_target_shape(*a.shape[2:]), mode="bilinear", align_corners=True)
+        with torch.no_grad():
+            y = F.interpolate(b, size=static_target_shape(*b.shape[2:]), mode="bilinear", align_corners=True)
+        x, y = x.reshape(n, c, -1), y.reshape(n, c, -1)
+        cost = 1 - torch.einsum("bcn,bcm->bnm", x, y)
+        dists.append(cost.mean())
+    order = sorted(range(len(dists)), key=lambda i: float(dists[i].detach()))      # stable, like list.sort()
+    return dists[order[0]] + dists[order[1]], torch.stack([d.detach() for d in dists])
+
+
+def get_static_crops(x1, coord1, x2, coord2):
+    """src/torchutils.py:177-214: per image the overlap boxes (y0, x0, h, w) of both views;
+    boxes under 15 px or more elongated than 7:1 are skipped (:199); view 1 is cut into nine
+    half-size windows at offsets (0, h//4, h//2) x (0, w//4, w//2) (:203-205), view 2 into nine
+    third-size windows at (0, h//3, 2h//3) x (0, w//3, 2w//3) (:210-213), all with view 1's h, w.
+    Returns flat lists of [1,C,·,·] views and the image index of every window."""
+    crops1, crops2, batch_indices = [], [], []
+    for b in range(x1.shape[0]):
+        b1, b2 = [int(v) for v in coord1[b]], [int(v) for v in coord2[b]]
+        ins1 = x1[b:b + 1, :, b1[0]:b1[0] + b1[2], b1[1]:b1[1] + b1[3]]
+        ins2 = x2[b:b + 1, :, b2[0]:b2[0] + b2[2], b2[1]:b2[1] + b2[3]]
+        h, w = ins1.shape[2:]
+        if h < 15 or w < 15 or h / w > 7 or w / h > 7:
+            continue
+        for i in (0, h // 4, h // 2):
+            for j in (0, w // 4, w // 2):
+                crops1.append(ins1[:, :, i:i + h // 2, j:j + w // 2])
+        for i in (0, h // 3, 2 * h // 3):
+            for j in (0, w // 3, 2 * w // 3):
+                crops2.append(ins2[:, :, i:i + h // 3, j:j + w // 3])
+                batch_indices.append(b)
+    return crops1, crops2, batch_indices
+
+
 def dynamic_crop_plan(h, w, rng=np.random):
     """Integer half of src/torchutils.py:240-280 for ONE overlap box of size h x w:
     returns None when the box is rejected (:240), else

@@ -101,3 +101,69 @@ def test_emd_generic_lists_and_full_size():
     l2.backward()
     assert abs(l2.item() - loss.item()) <= 1e-5 * abs(loss.item())
     assert sum(float(t.grad.abs().sum()) > 0 for img in plain1 for t in img) == len(plain1)   # one crop per image
+
+
+def _static_views(g, device):
+    raw1 = g["raw1"].to(device).requires_grad_()
+    vw1 = F.normalize(torch.softmax(raw1 * 4, 1), dim=1)
+    vw2 = F.normalize(torch.softmax(g["raw2"].to(device) * 4, 1), dim=1)
+    return raw1, vw1, vw2
+
+
+def test_emd_static_golden(golden):
+    """EMD()(…) in its default mode on get_static_crops windows, against the reference-minted fixture:
+    every pair distance, the two-smallest sum and the gradient reaching the raw CAMs."""
+    from muscle_b200.loss_multilabel import EMD
+    from muscle_b200.torchutils import get_static_crops
+    g = golden("emd_static")
+    raw1, vw1, vw2 = _static_views(g, "cuda")
+    c1, c2, idx = get_static_crops(vw1, g["c1"], vw2.detach(), g["c2"])
+    assert idx == list(g["batch_indices"])
+    assert [tuple(t.shape) for t in c1] == g["crop_shapes1"]
+    assert [tuple(t.shape) for t in c2] == g["crop_shapes2"]
+    loss, dists = EMD().static_matching(c1, c2, return_dists=True)
+    torch.testing.assert_close(dists.cpu(), g["dists"], rtol=1e-4, atol=1e-6)
+    loss.backward()
+    assert abs(loss.item() - g["loss"].item()) <= 1e-3 * abs(g["loss"].item()), (loss.item(), g["loss"].item())
+    assert _cos(raw1.grad.cpu(), g["g1"]) >= 0.999
+    torch.testing.assert_close(raw1.grad.cpu(), g["g1"], rtol=1e-3, atol=1e-4 * float(g["g1"].abs().max()))
+    again = EMD()(c1, c2)                       # default mode, as the reference's signature
+    assert again.item() == loss.item()          # deterministic
+
+
+def test_emd_static_matches_oracle_ragged_and_batched():
+    """Batched [n,C,h,w] regions of ragged sizes incl. tall, wide, 1-pixel-wide resize targets and
+    a tie (duplicated pair): distances vs the oracle, selection = the oracle's stable order."""
+    from muscle_b200.loss_multilabel import EMD
+    gen = torch.Generator().manual_seed(5)
+    shapes = [((3, 16, 20, 9), (3, 16, 7, 7)), ((3, 16, 5, 33), (3, 16, 40, 6)), ((3, 16, 64, 64), (3, 16, 31, 17)),
+              ((3, 16, 8, 8), (3, 16, 3, 2)), ((3, 16, 50, 4), (3, 16, 4, 50))]
+    a = [F.normalize(torch.rand(s1, generator=gen), dim=1) for s1, _ in shapes]
+    b = [F.normalize(torch.rand(s2, generator=gen), dim=1) for _, s2 in shapes]
+    a.append(a[1].clone())
+    b.append(b[1].clone())                      # equal distances: list.sort() keeps the first
+    ra = [t.clone().requires_grad_() for t in a]
+    ref, ref_d = O.emd_static(ra, b)
+    ref.backward()
+    ga = [t.cuda().requires_grad_() for t in a]
+    loss, dists = EMD().static_matching(ga, [t.cuda() for t in b], return_dists=True)
+    loss.backward()
+    torch.testing.assert_close(dists.cpu(), ref_d, rtol=1e-4, atol=1e-6)
+    assert abs(loss.item() - ref.item()) <= 1e-3 * abs(ref.item())
+    for ours, theirs in zip(ga, ra):
+        assert (ours.grad is None or float(ours.grad.abs().sum()) == 0) == (theirs.grad is None or float(theirs.grad.abs().sum()) == 0)
+        if theirs.grad is not None and float(theirs.grad.abs().sum()) > 0:
+            torch.testing.assert_close(ours.grad.cpu(), theirs.grad, rtol=1e-3, atol=1e-7)
+
+
+def test_emd_static_errors_are_loud():
+    from muscle_b200.loss_multilabel import EMD
+    x = torch.rand(1, 21, 16, 16, device="cuda")
+    with pytest.raises(ValueError):
+        EMD()([x], [x])                         # fewer than two pairs: the reference raises IndexError
+    with pytest.raises(ValueError):
+        EMD()([x, x], [x])
+    with pytest.raises((ValueError, RuntimeError)):
+        EMD()([x.cpu(), x.cpu()], [x.cpu(), x.cpu()])
+    with pytest.raises(ValueError):
+        EMD()([torch.rand(1, 21, 200, 3, device="cuda")] * 2, [x, x])      # resizes to 0 x 7

@@ -99,6 +99,21 @@ def test_emd_dynamic(golden):
     close(sk, g["sk_value"], rtol=1e-5, atol=1e-8)
 
 
+def test_emd_static(golden):
+    g = golden("emd_static")
+    raw1 = g["raw1"].clone().requires_grad_()
+    vw1 = F.normalize(torch.softmax(raw1 * 4, 1), dim=1)
+    vw2 = F.normalize(torch.softmax(g["raw2"] * 4, 1), dim=1)
+    crops1, crops2, bidx = O.get_static_crops(vw1, g["c1"], vw2.detach(), g["c2"])
+    assert bidx == g["batch_indices"] and len(crops1) == len(crops2) == 18
+    assert [tuple(t.shape) for t in crops1] == g["crop_shapes1"]
+    assert [tuple(t.shape) for t in crops2] == g["crop_shapes2"]
+    loss, dists = O.emd_static(crops1, crops2)
+    close(dists, g["dists"], rtol=1e-5, atol=1e-7)
+    close(loss, g["loss"], rtol=1e-5, atol=1e-7)
+    close(torch.autograd.grad(loss, raw1)[0], g["g1"], rtol=1e-4, atol=1e-9)
+
+
 def test_heads_in_situ(golden):
     g = golden("heads")
     p1, p3, p5, p7 = g["p1"], g["p3"], g["p5"], g["p7"]
