@@ -194,6 +194,31 @@ def test_config2_full_size_properties(M):
     assert _cos(gp.cpu(), g.cpu()) >= 0.99999
 
 
+def test_config3_full_size_value_and_relabelling(M):
+    """BASELINE config 3 (B=16, 512 crop -> 64x64, D=128; 65 536 pixels, 4.3e9 pairs): value against
+    the row-chunked oracle forward; gradient finite and orthogonal to x; and a size-independent
+    property of the loss — renaming the classes (a permutation of the 21 labels, which reorders
+    the class-sorted layout and every tile's mask) changes neither the value nor the gradient."""
+    x, cls, _ = O.synth_embeddings(16, 128, 64, 64, seed=77)
+    xg = x.cuda().requires_grad_()
+    loss = M.dense_infonce(xg, cls.cuda(), 0.1, 21)
+    loss.backward()
+    g = xg.grad
+    assert torch.isfinite(g).all()
+    radial = (g * xg.detach()).sum(1).abs().max().item()
+    assert radial <= 1e-3 * g.norm(dim=1).max().item() * xg.detach().norm(dim=1).max().item()
+    with torch.no_grad():
+        ref = O.dense_infonce_from_features(x.permute(0, 2, 3, 1).reshape(-1, 128), cls.reshape(-1), 0.1, 21).item()
+    assert abs(loss.item() - ref) <= LOSS_RTOL * abs(ref), (loss.item(), ref)
+    pi = torch.randperm(21, generator=torch.Generator().manual_seed(3))
+    relabelled = torch.where(cls >= 0, pi[cls.clamp(min=0)], cls)
+    xr = x.cuda().requires_grad_()
+    lr = M.dense_infonce(xr, relabelled.cuda(), 0.1, 21)
+    lr.backward()
+    assert abs(lr.item() - loss.item()) <= 1e-5 * abs(loss.item()), (lr.item(), loss.item())
+    assert _cos(xr.grad.cpu(), g.cpu()) >= 0.99999
+
+
 def test_errors_are_loud(M):
     x = torch.randn(64, 96, device="cuda")
     with pytest.raises((RuntimeError, ValueError)):
