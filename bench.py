@@ -39,6 +39,10 @@ def workload(n_gpus, name=None):
     if (name is None and n_gpus == 1) or name == "config2":
         return dict(name="config2: MCL dense InfoNCE fwd+bwd, B=8, 448x448 crop, stride 8 (56x56), D=128, 21 classes",
                     global_batch=8, h=56, w=56, dim=128)
+    if name == "config5":
+        return dict(name="config5 (stress): full pixel-pixel dense InfoNCE with cross-GPU negatives, global batch 256, "
+                         "512x512 crop, stride 8 (64x64), D=256, 21 classes",
+                    global_batch=256, h=64, w=64, dim=256)
     return dict(name="config4: dense InfoNCE with cross-GPU negatives (all-gather), global batch 64, 512x512 crop, "
                      "stride 8 (64x64), D=128, 21 classes",
                 global_batch=64, h=64, w=64, dim=128)
@@ -161,7 +165,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default=None, choices=["config2", "config3", "config4"],
+    ap.add_argument("--workload", default=None, choices=["config2", "config3", "config4", "config5"],
                     help="override the default (config2 at 1 GPU, config4 at N>1), e.g. config4 on 1 GPU")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
