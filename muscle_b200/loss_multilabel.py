@@ -191,8 +191,16 @@ class EMD:
         of the two smallest pair distances (0-dim tensor; grad flows to crops1 only, :273)."""
         if len(crops1) != len(crops2) or len(crops1) < 2:
             raise ValueError("static matching needs two lists of equal length >= 2 (the reference sums dists[0] + dists[1])")
+        from .torchutils import CropList
         rows, p1, p2, off1, off2, max_planes = [], [], [], 0, 0, 0
-        for a, b in zip(crops1, crops2):
+
+        def is_packed(crops):     # still the untouched list get_static_crops made (same tensors, same order)?
+            if not (isinstance(crops, CropList) and crops.flat is not None and len(crops.offsets) == len(crops)):
+                return False
+            base = crops.flat.data_ptr()
+            return all(torch.is_tensor(t) and t.data_ptr() == base + 4 * o for t, o in zip(crops, crops.offsets))
+        packed1, packed2 = is_packed(crops1), is_packed(crops2)
+        for k, (a, b) in enumerate(zip(crops1, crops2)):
             require_cuda_f32(a, "crop")
             require_cuda_f32(b, "crop")
             if a.dim() != 4 or b.dim() != 4 or a.shape[:2] != b.shape[:2]:
@@ -203,13 +211,22 @@ class EMD:
             if min(h1, w1, h2, w2, oh1, ow1, oh2, ow2) < 1 or max(h1, w1, h2, w2) > 1024:
                 raise ValueError("crop sides must be 1..1024 px and resize to at least one pixel (got %s, %s)"
                                  % (tuple(a.shape), tuple(b.shape)))
+            if packed1:
+                off1 = crops1.offsets[k]
+            if packed2:
+                off2 = crops2.offsets[k]
             rows.append([off1, n * c, h1, w1, oh1, ow1, off2, h2, w2, oh2, ow2, n])
-            p1.append(a.reshape(-1))
-            p2.append(b.detach().reshape(-1))
-            off1 += a.numel()
-            off2 += b.numel()
+            if not packed1:
+                p1.append(a.reshape(-1))
+                off1 += a.numel()
+            if not packed2:
+                p2.append(b.detach().reshape(-1))
+                off2 += b.numel()
             max_planes = max(max_planes, n * c)
-        flat1, flat2 = torch.cat(p1), torch.cat(p2)      # plumbing: autograd routes d flat1 back to every crop
+        # lists made by torchutils.get_static_crops already are views of one buffer; anything else is
+        # concatenated (plumbing: autograd routes d flat1 back to every crop)
+        flat1 = crops1.flat if packed1 else torch.cat(p1)
+        flat2 = crops2.flat.detach() if packed2 else torch.cat(p2)
         desc = torch.tensor(rows, dtype=torch.int64).to(flat1.device, non_blocking=True)
         loss, dists = _EmdStatic.apply(flat1, flat2, desc, len(rows), max_planes)
         return (loss, dists) if return_dists else loss

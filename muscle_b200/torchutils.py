@@ -134,30 +134,65 @@ def get_dynamic_crops(x1, coord1, x2, coord2):
     return _extract(x1, rows1, shapes1), _extract(x2, rows2, shapes2), batch_indices
 
 
+class CropList(list):
+    """A flat list of [1,C,h,w] crop tensors that are views of ONE buffer (``flat``); ``offsets[i]`` is
+    crop i's first element in it.  ``EMD.static_matching`` reads the buffer directly."""
+    flat = None
+    offsets = None
+
+
+def _extract_flat(x, rows):
+    """rows: 10-int window descriptors with resize target == window size (an exact copy: every
+    bilinear tap has weight 1 or 0).  One gather launch forward, one scatter launch backward —
+    python slicing would cost one autograd node and one full-size zero-filled gradient per window."""
+    c = x.shape[1]
+    offs, total = [], 0
+    for r in rows:
+        offs.append(total)
+        total += c * r[8] * r[9]
+    offs.append(total)
+    desc_t = torch.tensor(rows, dtype=torch.int32).to(x.device, non_blocking=True)
+    offs_t = torch.tensor(offs, dtype=torch.int64).to(x.device, non_blocking=True)
+    flat = _Crops.apply(x, desc_t, offs_t, len(rows), total)
+    out = CropList(flat[offs[i]:offs[i + 1]].view(1, c, r[8], r[9]) for i, r in enumerate(rows))
+    out.flat, out.offsets = flat, offs[:-1]
+    return out
+
+
 def get_static_crops(x1, coord1, x2, coord2):
     """src/torchutils.py:177-214.  x1, x2 [B,C,H,W] fp32 CUDA; coord [B,4] = (top, left, h, w).
     -> (crops1, crops2, batch_indices): flat lists of nine half-size windows of view 1's overlap box
-    and nine third-size windows of view 2's per kept image, as [1,C,·,·] VIEWS (slicing only, no
-    arithmetic: grad flows to x1/x2 through autograd's own slice nodes); boxes under 15 px or more
-    elongated than 7:1 are skipped (:199).  Feed to ``EMD()(crops1, crops2, mode='static')``."""
+    and nine third-size windows of view 2's per kept image, as [1,C,·,·] tensors (grad flows to
+    x1/x2); boxes under 15 px or more elongated than 7:1 are skipped (:199).  Window sizes follow
+    python slicing (clamped at the box, :186,:191,:205,:212).  Feed to ``EMD()(crops1, crops2)``."""
     require_cuda_f32(x1, "x1")
     require_cuda_f32(x2, "x2")
+    H1, W1 = x1.shape[2:]
+    H2, W2 = x2.shape[2:]
     c1 = coord1.detach().to("cpu").long().tolist()
     c2 = coord2.detach().to("cpu").long().tolist()
-    crops1, crops2, batch_indices = [], [], []
+    rows1, rows2, batch_indices = [], [], []
+
+    def window(b, top, left, bh, bw, i, j, hh, ww):      # ins[:, :, i:i+hh, j:j+ww] of a bh x bw box
+        hh, ww = min(hh, bh - i), min(ww, bw - j)
+        if hh < 1 or ww < 1:
+            raise ValueError("static crop window is empty (view-2 box smaller than view 1's window grid)")
+        return [b, top + i, left + j, hh, ww, hh, ww, 0, hh, ww]
+
     for b in range(x1.shape[0]):
         t1, l1, bh1, bw1 = c1[b]
         t2, l2, bh2, bw2 = c2[b]
-        ins1 = x1[b:b + 1, :, t1:t1 + bh1, l1:l1 + bw1]
-        ins2 = x2[b:b + 1, :, t2:t2 + bh2, l2:l2 + bw2]
-        h, w = ins1.shape[2:]                             # both window grids use view 1's box size (:197)
+        h, w = max(min(bh1, H1 - t1), 0), max(min(bw1, W1 - l1), 0)      # both window grids use view 1's box size (:197)
+        h2, w2 = max(min(bh2, H2 - t2), 0), max(min(bw2, W2 - l2), 0)
         if h < 15 or w < 15 or h / w > 7 or w / h > 7:
             continue
         for i in (0, h // 4, h // 2):
             for j in (0, w // 4, w // 2):
-                crops1.append(ins1[:, :, i:i + h // 2, j:j + w // 2])
+                rows1.append(window(b, t1, l1, h, w, i, j, h // 2, w // 2))
         for i in (0, h // 3, 2 * h // 3):
             for j in (0, w // 3, 2 * w // 3):
-                crops2.append(ins2[:, :, i:i + h // 3, j:j + w // 3])
+                rows2.append(window(b, t2, l2, h2, w2, i, j, h // 3, w // 3))
                 batch_indices.append(b)
-    return crops1, crops2, batch_indices
+    if not rows1:
+        return [], [], []
+    return _extract_flat(x1, rows1), _extract_flat(x2, rows2), batch_indices

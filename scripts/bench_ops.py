@@ -167,6 +167,25 @@ def main():
         O.emd_dynamic(a, b).backward()
         raw1_c.grad = None
     out["crops_emd_dynamic_fwd_bwd_B8"] = beside(dict(ms=timed(emd_step), bound="latency"), cpu_timed(emd_cpu))
+    # ---- static crops + EMD static (the class's default mode), same CAM maps
+    from muscle_b200.torchutils import get_static_crops
+
+    def emd_static_step():
+        v1 = F.normalize(heads.cam_softmaxnorm(raw1), dim=1)
+        v2 = F.normalize(heads.cam_softmaxnorm(raw2), dim=1)
+        a, b, _ = get_static_crops(v1, c1, v2.detach(), c2)
+        EMD()(a, b).backward()
+        raw1.grad = None
+
+    def emd_static_cpu():
+        v1 = F.normalize(O.cam_softmaxnorm(raw1_c), dim=1)
+        v2 = F.normalize(O.cam_softmaxnorm(raw2_c), dim=1)
+        a, b, _ = O.get_static_crops(v1, c1, v2.detach(), c2)
+        O.emd_static(a, b)[0].backward()
+        raw1_c.grad = None
+    out["crops_emd_static_fwd_bwd_B8"] = beside(dict(ms=timed(emd_static_step), bound="latency",
+                                                     note="72 window pairs; windows gathered by one launch per view (muscle_crops_fwd), 3 launches for the matching"),
+                                                cpu_timed(emd_static_cpu))
     # ---- FieldLoss, config 3 scale reduced to B=4 (512x512, 256 ch) to bound memory in this table
     n, h, w, ch = 4, 512, 512, 256
     label = O.synth_labels(n, gen)

@@ -167,3 +167,33 @@ def test_emd_static_errors_are_loud():
         EMD()([x.cpu(), x.cpu()], [x.cpu(), x.cpu()])
     with pytest.raises(ValueError):
         EMD()([torch.rand(1, 21, 200, 3, device="cuda")] * 2, [x, x])      # resizes to 0 x 7
+
+
+def test_static_crops_are_exact_windows_and_generic_lists_agree(golden):
+    """get_static_crops windows are bit-exact copies of the python slices the reference takes; plain
+    lists of sliced views (not made by our feeder) take the concatenating path and give the same
+    loss and the same gradient on the raw maps."""
+    from muscle_b200.loss_multilabel import EMD
+    from muscle_b200.torchutils import get_static_crops
+    g = golden("emd_static")
+    raw1, vw1, vw2 = _static_views(g, "cuda")
+    c1, c2, _ = get_static_crops(vw1, g["c1"], vw2.detach(), g["c2"])
+    r1, r2, _ = O.get_static_crops(vw1.detach(), g["c1"], vw2.detach(), g["c2"])      # slicing on the GPU tensors
+    for ours, ref in ((c1, r1), (c2, r2)):
+        assert len(ours) == len(ref)
+        for t, u in zip(ours, ref):
+            assert torch.equal(t.detach(), u)
+    loss = EMD()(c1, c2)
+    loss.backward()
+    g_packed = raw1.grad.clone()
+    raw1.grad = None
+    vw1b = F.normalize(torch.softmax(raw1 * 4, 1), dim=1)
+    p1, p2, _ = O.get_static_crops(vw1b, g["c1"], vw2.detach(), g["c2"])
+    l2 = EMD()(list(p1), list(p2))
+    l2.backward()
+    assert abs(l2.item() - loss.item()) <= 1e-6 * abs(loss.item())
+    torch.testing.assert_close(raw1.grad, g_packed, rtol=1e-4, atol=1e-7 * float(g_packed.abs().max()) + 1e-12)
+    shuffled = type(c1)(reversed(c1))       # a reordered feeder list must not be read through stale offsets
+    shuffled.flat, shuffled.offsets = c1.flat, c1.offsets
+    l3 = EMD()(shuffled, type(c2)(reversed(c2)))
+    assert abs(l3.item() - loss.item()) <= 1e-5 * abs(loss.item())     # same pairs in another order: same two smallest
