@@ -317,7 +317,12 @@ __global__ void __launch_bounds__(PREP_THREADS) prepare_nchw_kernel(const Prepar
 // into at most a few single-class pieces at the segment starts, every piece is reduced in
 // registers + shared memory and leaves the block as one atomicAdd per channel.
 constexpr int SEG_THREADS = 256;
-constexpr int SEG_ROWS = 64;      // sorted rows per block (small blocks: these kernels are latency bound)
+#ifndef MB_SEG_ROWS
+#define MB_SEG_ROWS 64
+#endif
+constexpr int SEG_ROWS = MB_SEG_ROWS;   // sorted rows per block (small blocks: these kernels are latency bound;
+                                        // measured 64 / 32 / 16: 0.2835 / 0.2870 / 0.2913 ms per config-2 step, profiles/r1l_variants_seg_rows.txt)
+static_assert(128 % SEG_ROWS == 0 && SEG_ROWS >= 8, "a block covers a whole fraction of a 128-row tile");
 
 template <int D>
 __device__ __forceinline__ void load_row8(const __nv_bfloat16* row, int l, float (&v)[8]) {
