@@ -118,7 +118,11 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
 
 // The FMA-pipe exponential is exact enough only while the exponent stays in range:
 // x = (s - 1) log2(e)/T lies in [-2 log2(e)/T, ~0].
-constexpr int kPoly = 2;  // of every 4 element pairs
+// Share on the FMA pipe: 1 of every 4 element pairs.  Measured on B200 (profiles/r1l_variants_poly.txt, three
+// alternating runs): share 2/4 -> 1/4 takes the config-2 step from 0.277 to 0.268 ms and config 3 from 1.31
+// to 1.22 ms (both passes are issue bound, and a polynomial pair costs ~10 issue slots against 2 for two
+// MUFU.EX2); 0/4 is slower again in the row-sum pass (MUFU, 16/clk/SM, becomes the cap), 3/4 and 4/4 slower.
+constexpr int kPoly = 1;
 // (MASK_BIAS pushes masked columns another 64 down: x in [-2 log2(e)/T - 64, ~0])
 bool poly_ok(float temperature) { return 2.f * kLog2e / temperature + 64.f < 118.f; }
 
@@ -130,6 +134,8 @@ int launch_pair_dim(int dim, bool poly, const void* ehat_rows, int64_t rows_pad,
   if (DD == 128 && dbg == 1) return launch_pair<128, MODE, -1>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream); \
   if (DD == 128 && dbg == 2) return launch_pair<128, MODE, 4>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream); \
   if (DD == 128 && dbg == 3) return launch_pair<128, MODE, 0>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream); \
+  if (DD == 128 && dbg == 5) return launch_pair<128, MODE, 3>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream); \
+  if (DD == 128 && dbg == 6) return launch_pair<128, MODE, 2>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream); \
   return poly ? launch_pair<DD, MODE, kPoly>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream) \
               : launch_pair<DD, MODE, 0>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream);
   switch (dim) {
