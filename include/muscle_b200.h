@@ -93,8 +93,7 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
                            uint32_t* tor, uint32_t* seg, float* class_sum, float* class_mass,
                            void* scratch, size_t scratch_bytes, void* stream);
 
-/* Work partition of the two pair passes over rows x cols: unit_off [rows_pad/RB + 1] (RB = 256
- * rows, 128 for dim 256) = running count of the LIVE (row block, column tile) units, i.e. those
+/* Work partition of the two pair passes over rows x cols: unit_off [rows_pad/128 + 1] = running count of the LIVE (row block, column tile) units, i.e. those
  * with at least one unmasked pair.  Every CTA of a pair pass takes an equal contiguous share of
  * that range, so the passes stay balanced whatever the class mix. */
 int muscle_infonce_plan(const uint32_t* tor_rows, int64_t rows_pad, const uint32_t* tor_cols,
@@ -107,6 +106,17 @@ int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows,
                           const uint32_t* bits_cols, const uint32_t* tor_cols, int64_t cols_pad,
                           const uint32_t* unit_off, int dim, float temperature, float* rowsum,
                           void* stream);
+
+/* The row-sum pass when rows and columns are THE SAME pixels (single GPU; dim 64 or 128): the
+ * similarity matrix and the label mask are symmetric, so only the live units with column tile >= row
+ * tile are visited and every off-diagonal tile feeds the row sums of both its row pixels and its
+ * column pixels (half the products and half the exponentials of muscle_infonce_rowsum; same result up
+ * to fp32 summation order).  muscle_infonce_plan_sym numbers those units: unit_off_sym [rows_pad/128 + 1].
+ * No reference counterpart: the reference materialises the logits (src/loss_multilabel.py:15-21). */
+int muscle_infonce_plan_sym(const uint32_t* tor, int64_t rows_pad, uint32_t* unit_off_sym, void* stream);
+int muscle_infonce_rowsum_sym(const void* ehat, const uint32_t* bits, const uint32_t* tor,
+                              int64_t rows_pad, const uint32_t* unit_off_sym, int dim,
+                              float temperature, float* rowsum, void* stream);
 
 /* pos[q] = e_q . proto_{c_q} / T; rowsum[q] += exp(pos - 1/T); w[q] = 1/rowsum[q];
  * gpos[q] = (exp(pos - 1/T) w - 1)/T; loss_acc (double[1]) += sum_q (1/T + ln rowsum[q] - pos);

@@ -36,6 +36,9 @@ _SIGNATURES = {
     "muscle_infonce_plan": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_void_p]),
     "muscle_infonce_rowsum": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64,
                                       c_void_p, c_int, c_float, c_void_p, c_void_p]),
+    "muscle_infonce_plan_sym": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
+    "muscle_infonce_rowsum_sym": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_float, c_void_p,
+                                          c_void_p]),
     "muscle_infonce_mid": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                    c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "muscle_infonce_part_slots": (c_int, []),

@@ -2,6 +2,7 @@
 // TMA tensor-map construction (driver entry point fetched at run time, so the library links
 // against cudart only and still loads on a machine without libcuda for symbol checks).
 #pragma once
+#include <atomic>
 #include <cstdlib>
 #include <utility>
 #include <cstdarg>
@@ -147,6 +148,21 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   cfg.attrs = attr;
   cfg.numAttrs = off ? 0 : 1;
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device property of a kernel: set it once per
+// (kernel instantiation, device) -- not once per thread, which left a thread's second GPU without it.
+template <auto Kern>
+inline int ensure_dynamic_smem(int bytes) {
+  static std::atomic<unsigned long long> done{0ull};   // bit d: set on device d
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const bool tracked = dev >= 0 && dev < 64;
+  if (!tracked || !((done.load(std::memory_order_acquire) >> dev) & 1ull)) {
+    MB_CUDA(cudaFuncSetAttribute(Kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    if (tracked) done.fetch_or(1ull << dev, std::memory_order_release);
+  }
+  return MUSCLE_OK;
 }
 
 inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }

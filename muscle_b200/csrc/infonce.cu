@@ -5,6 +5,7 @@
 
 #include "host_util.cuh"
 #include "pair_kernel.cuh"
+#include "pair_sym_kernel.cuh"
 #include "row_kernels.cuh"
 
 using namespace mb200;
@@ -29,51 +30,27 @@ int pair_grid() {
   return g > 0 ? g : device_info().sm_count;
 }
 
-template <int D, int MODE, int POLY>
-int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, int64_t cols_pad,
-                PairParams prm, cudaStream_t stream) {
-  using C = PairCfg<D, MODE>;
-  // Tensor maps depend only on (base, rows, D); a training loop presents the same few buffers again and
-  // again (the caching allocator hands the workspace back at the same address), and one
-  // cuTensorMapEncodeTiled costs a few microseconds of host time, four times per step.
+// Tensor maps depend only on (base, rows, D); a training loop presents the same few buffers again and
+// again (the caching allocator hands the workspace back at the same address), and one
+// cuTensorMapEncodeTiled costs a few microseconds of host time, four times per step.
+int cached_panel_map(const void* base, int64_t rows, int dim, CUtensorMap* out) {
   struct MapEntry { const void* base; int64_t rows; int dim; CUtensorMap map; };
   static thread_local MapEntry cache[8] = {};
   static thread_local int next_slot = 0;
-  auto cached_map = [&](const void* base, int64_t rows, CUtensorMap* out) -> int {
-    for (const MapEntry& e : cache)
-      if (e.base == base && e.rows == rows && e.dim == D) { *out = e.map; return MUSCLE_OK; }
-    MapEntry& e = cache[next_slot];
-    next_slot = (next_slot + 1) % 8;
-    e.base = nullptr;
-    if (int rc2 = make_bf16_panel_map(&e.map, base, rows, D)) return rc2;
-    e.base = base; e.rows = rows; e.dim = D;
-    *out = e.map;
-    return MUSCLE_OK;
-  };
-  CUtensorMap tm_row, tm_col;
-  int rc = cached_map(ehat_rows, rows_pad, &tm_row);
-  if (rc) return rc;
-  rc = cached_map(ehat_cols, cols_pad, &tm_col);
-  if (rc) return rc;
-  auto kern = pair_kernel<D, MODE, POLY>;
-  static thread_local bool attr_set = false;
-  if (!attr_set) {
-    MB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    attr_set = true;
-  }
-  const int grid = pair_grid();  // one persistent CTA per SM; shares come from unit_off
-  static const bool timing = kPairTiming && getenv("MUSCLE_PAIR_TIMING") != nullptr;   // debug: per-phase cycle counters (-DMB_PAIR_TIMING=1 builds)
-  static unsigned long long* dbg = nullptr;
-  static const int flags = getenv("MUSCLE_PAIR_FLAGS") ? atoi(getenv("MUSCLE_PAIR_FLAGS")) : 0;
-  prm.dbg_flags = flags;
-  if (timing) {
-    if (!dbg) cudaMalloc(&dbg, grid * 16 * sizeof(unsigned long long));
-    cudaMemsetAsync(dbg, 0, grid * 16 * sizeof(unsigned long long), stream);
-    prm.dbg = dbg;
-  }
-  MB_CUDA(launch_pdl(kern, dim3(grid), dim3(C::THREADS), C::SMEM_BYTES, stream, tm_row, tm_col, prm));
-  MB_LAUNCH_CHECK();
-  if (timing) {
+  for (const MapEntry& e : cache)
+    if (e.base == base && e.rows == rows && e.dim == dim) { *out = e.map; return MUSCLE_OK; }
+  MapEntry& e = cache[next_slot];
+  next_slot = (next_slot + 1) % 8;
+  e.base = nullptr;
+  if (int rc2 = make_bf16_panel_map(&e.map, base, rows, dim)) return rc2;
+  e.base = base; e.rows = rows; e.dim = dim;
+  *out = e.map;
+  return MUSCLE_OK;
+}
+
+#if MB_PAIR_TIMING
+template <int D, int MODE>
+void pair_timing_report(unsigned long long* dbg, int grid, cudaStream_t stream) {
     static int printed = 0;
     cudaStreamSynchronize(stream);
     unsigned long long h[148 * 16];
@@ -112,7 +89,37 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
                 s[8] / n / tiles / 2, s[9] / n / tiles / 2, s[10] / n / tiles / 2, s[11] / n / tiles / 2, s[12] / n / tiles / 2);
       }
     }
+}
+#endif
+
+template <int D, int MODE, int POLY>
+int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, int64_t cols_pad,
+                PairParams prm, cudaStream_t stream) {
+  using C = PairCfg<D, MODE>;
+  CUtensorMap tm_row, tm_col;
+  int rc = cached_panel_map(ehat_rows, rows_pad, D, &tm_row);
+  if (rc) return rc;
+  rc = cached_panel_map(ehat_cols, cols_pad, D, &tm_col);
+  if (rc) return rc;
+  if (int rc2 = ensure_dynamic_smem<pair_kernel<D, MODE, POLY>>(C::SMEM_BYTES)) return rc2;
+  const int grid = pair_grid();  // one persistent CTA per SM; shares come from unit_off
+#if MB_PAIR_TIMING
+  // measurement builds only (scripts/build_variants.sh with -DMB_PAIR_TIMING=1): per-phase cycle counters
+  static const bool timing = getenv("MUSCLE_PAIR_TIMING") != nullptr;
+  static unsigned long long* dbg = nullptr;
+  static const int flags = getenv("MUSCLE_PAIR_FLAGS") ? atoi(getenv("MUSCLE_PAIR_FLAGS")) : 0;
+  prm.dbg_flags = flags;
+  if (timing) {
+    if (!dbg) cudaMalloc(&dbg, grid * 16 * sizeof(unsigned long long));
+    cudaMemsetAsync(dbg, 0, grid * 16 * sizeof(unsigned long long), stream);
+    prm.dbg = dbg;
   }
+#endif
+  MB_CUDA(launch_pdl(pair_kernel<D, MODE, POLY>, dim3(grid), dim3(C::THREADS), C::SMEM_BYTES, stream, tm_row, tm_col, prm));
+  MB_LAUNCH_CHECK();
+#if MB_PAIR_TIMING
+  if (timing) pair_timing_report<D, MODE>(dbg, grid, stream);
+#endif
   return MUSCLE_OK;
 }
 
@@ -123,12 +130,16 @@ int launch_pair(const void* ehat_rows, int64_t rows_pad, const void* ehat_cols, 
 // to 1.22 ms (both passes are issue bound, and a polynomial pair costs ~10 issue slots against 2 for two
 // MUFU.EX2); 0/4 is slower again in the row-sum pass (MUFU, 16/clk/SM, becomes the cap), 3/4 and 4/4 slower.
 constexpr int kPoly = 1;
-// (MASK_BIAS pushes masked columns another 64 down: x in [-2 log2(e)/T - 64, ~0])
-bool poly_ok(float temperature) { return 2.f * kLog2e / temperature + 64.f < 118.f; }
+// (MASK_BIAS pushes masked columns another pair_mask_shift down: x in [-2 log2(e)/T - shift, ~0])
+bool poly_ok(float temperature) { return pair_poly_ok(kLog2e / temperature); }
+// exp((s - 1)/T) leaves the fp32 range for every s < 0 once log2(e)/T > 126: refuse instead of returning
+// a silently wrong loss (the reference works in log space and has no such limit)
+constexpr float kMinTemperature = 0.0125f;
 
 template <int MODE>
 int launch_pair_dim(int dim, bool poly, const void* ehat_rows, int64_t rows_pad,
                     const void* ehat_cols, int64_t cols_pad, PairParams prm, cudaStream_t stream) {
+#if MB_PAIR_TIMING
   static const int dbg = getenv("MUSCLE_DEBUG_PAIR") ? atoi(getenv("MUSCLE_DEBUG_PAIR")) : 0;  // measurement variants
 #define MB_PAIR(DD)                                                                              \
   if (DD == 128 && dbg == 1) return launch_pair<128, MODE, -1>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream); \
@@ -138,6 +149,11 @@ int launch_pair_dim(int dim, bool poly, const void* ehat_rows, int64_t rows_pad,
   if (DD == 128 && dbg == 6) return launch_pair<128, MODE, 2>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream); \
   return poly ? launch_pair<DD, MODE, kPoly>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream) \
               : launch_pair<DD, MODE, 0>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream);
+#else
+#define MB_PAIR(DD)                                                                              \
+  return poly ? launch_pair<DD, MODE, kPoly>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream) \
+              : launch_pair<DD, MODE, 0>(ehat_rows, rows_pad, ehat_cols, cols_pad, prm, stream);
+#endif
   switch (dim) {
     case 64: MB_PAIR(64)
     case 128: MB_PAIR(128)
@@ -145,6 +161,40 @@ int launch_pair_dim(int dim, bool poly, const void* ehat_rows, int64_t rows_pad,
   }
 #undef MB_PAIR
   return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
+}
+
+// Row-sum pass over rows == columns (pair_sym_kernel.cuh): only the live units with c >= r.
+template <int D, int POLY>
+int launch_rowsum_sym(const void* ehat, int64_t rows_pad, PairParams prm, cudaStream_t stream) {
+  using C = SymCfg<D>;
+  CUtensorMap tm;
+  if (int rc = cached_panel_map(ehat, rows_pad, D, &tm)) return rc;
+  if (int rc = ensure_dynamic_smem<pair_sym_kernel<D, POLY>>(C::SMEM_BYTES)) return rc;
+  MB_CUDA(launch_pdl(pair_sym_kernel<D, POLY>, dim3(pair_grid()), dim3(C::THREADS), C::SMEM_BYTES, stream, tm, prm));
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
+}
+
+// MUSCLE_ROWSUM_SYM=0 keeps the ordered row-sum pass in the single-GPU composite (A/B measurements)
+bool rowsum_sym_enabled(int dim) {
+  static const bool off = getenv("MUSCLE_ROWSUM_SYM") != nullptr && atoi(getenv("MUSCLE_ROWSUM_SYM")) == 0;
+  return !off && (dim == 64 || dim == 128);
+}
+
+int rowsum_sym(const void* ehat, const uint32_t* bits, const uint32_t* tor, int64_t rows_pad,
+               const uint32_t* unit_off_sym, int dim, float temperature, float* rowsum, cudaStream_t stream) {
+  PairParams prm{};
+  prm.bits_row = bits; prm.bits_col = bits; prm.tor_row = tor; prm.tor_col = tor;
+  prm.rowsum = rowsum; prm.unit_off = unit_off_sym;
+  prm.scale_log2 = kLog2e / temperature;
+  const bool poly = poly_ok(temperature);
+  prm.mask_shift = pair_mask_shift(prm.scale_log2, poly);
+  prm.n_row_blocks = static_cast<int>(rows_pad / 128);
+  prm.n_col_tiles = prm.n_row_blocks;
+  prm.rows_pad = static_cast<int>(rows_pad);
+  if (dim == 64)
+    return poly ? launch_rowsum_sym<64, kPoly>(ehat, rows_pad, prm, stream) : launch_rowsum_sym<64, 0>(ehat, rows_pad, prm, stream);
+  return poly ? launch_rowsum_sym<128, kPoly>(ehat, rows_pad, prm, stream) : launch_rowsum_sym<128, 0>(ehat, rows_pad, prm, stream);
 }
 
 int rows_per_block(int) { return PAIR_RB; }
@@ -172,7 +222,7 @@ int prepare_impl(const float* x, int layout, int64_t batch, int64_t pixels_per_i
                  int dim, const void* cls, int cls_is_int64, int num_classes, float eps,
                  void* ehat, uint32_t* bits, float* inv_norm, int32_t* perm,
                  uint32_t* tor, uint32_t* seg, float* class_sum, float* class_mass,
-                 void* scratch, size_t scratch_bytes, uint32_t* unit_off, cudaStream_t stream) {
+                 void* scratch, size_t scratch_bytes, uint32_t* unit_off, uint32_t* unit_off_sym, cudaStream_t stream) {
   if (int rc = check_device()) return rc;
   if (!x || !cls || !ehat || !bits || !inv_norm || !perm || !tor || !seg || !class_sum ||
       !class_mass || !scratch)
@@ -194,7 +244,7 @@ int prepare_impl(const float* x, int layout, int64_t batch, int64_t pixels_per_i
   MB_CUDA(launch_pdl(class_hist_kernel, dim3(n_blk), dim3(SORT_CHUNK), 0, stream, cls, cls_is_int64, static_cast<long long>(n), num_classes, hist,
                      static_cast<long long>(rows_pad), dim, static_cast<uint32_t*>(ehat), bits, inv_norm));
   MB_LAUNCH_CHECK();
-  MB_CUDA(launch_pdl(class_scan_kernel, dim3(1), dim3(1024), 0, stream, hist, n_blk, num_classes, static_cast<long long>(n), static_cast<long long>(rows_pad), seg, class_mass, tor, unit_off));
+  MB_CUDA(launch_pdl(class_scan_kernel, dim3(1), dim3(1024), 0, stream, hist, n_blk, num_classes, static_cast<long long>(n), static_cast<long long>(rows_pad), seg, class_mass, tor, unit_off, unit_off_sym));
   MB_LAUNCH_CHECK();
   PrepareParams p;
   p.x = x; p.cls = cls; p.cls64 = cls_is_int64; p.layout = layout; p.n = n;
@@ -235,7 +285,7 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
                            uint32_t* tor, uint32_t* seg, float* class_sum, float* class_mass,
                            void* scratch, size_t scratch_bytes, void* stream_) {
   return prepare_impl(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes, eps, ehat,
-                      bits, inv_norm, perm, tor, seg, class_sum, class_mass, scratch, scratch_bytes, nullptr,
+                      bits, inv_norm, perm, tor, seg, class_sum, class_mass, scratch, scratch_bytes, nullptr, nullptr,
                       static_cast<cudaStream_t>(stream_));
 }
 
@@ -249,13 +299,15 @@ int muscle_infonce_rowsum(const void* ehat_rows, const uint32_t* bits_rows,
   if (!ehat_rows || !bits_rows || !tor_rows || !ehat_cols || !bits_cols || !tor_cols || !unit_off || !rowsum)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
-  if (!(temperature > 0.f)) return fail(MUSCLE_ERR_BAD_ARG, "temperature must be > 0");
+  if (!(temperature >= kMinTemperature))
+    return fail(MUSCLE_ERR_BAD_ARG, "temperature must be >= %g (exp((s-1)/T) underflows fp32 below it)", kMinTemperature);
   if (rows_pad % 256 || cols_pad % 256 || rows_pad <= 0 || cols_pad <= 0)
     return fail(MUSCLE_ERR_BAD_ARG, "padded sizes must be positive multiples of 256");
   PairParams prm{};
   prm.bits_row = bits_rows; prm.bits_col = bits_cols; prm.tor_row = tor_rows; prm.tor_col = tor_cols;
   prm.rowsum = rowsum; prm.unit_off = unit_off;
   prm.scale_log2 = kLog2e / temperature;
+  prm.mask_shift = pair_mask_shift(prm.scale_log2, poly_ok(temperature));
   prm.n_row_blocks = static_cast<int>(rows_pad / rows_per_block(dim));
   prm.n_col_tiles = static_cast<int>(cols_pad / 128);
   prm.rows_pad = static_cast<int>(rows_pad);
@@ -320,6 +372,30 @@ int muscle_infonce_plan(const uint32_t* tor_rows, int64_t rows_pad, const uint32
   return MUSCLE_OK;
 }
 
+int muscle_infonce_plan_sym(const uint32_t* tor, int64_t rows_pad, uint32_t* unit_off_sym, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = check_device()) return rc;
+  if (!tor || !unit_off_sym) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (rows_pad % 256 || rows_pad <= 0) return fail(MUSCLE_ERR_BAD_ARG, "padded size must be a positive multiple of 256");
+  const int n_tiles = static_cast<int>(rows_pad / 128);
+  if (static_cast<double>(n_tiles) * n_tiles >= 8.0e9) return fail(MUSCLE_ERR_BAD_ARG, "too many tile units for one rank");
+  MB_CUDA(launch_pdl(pair_plan_sym_kernel, dim3(1), dim3(1024), 0, stream, tor, n_tiles, unit_off_sym));
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
+}
+
+int muscle_infonce_rowsum_sym(const void* ehat, const uint32_t* bits, const uint32_t* tor, int64_t rows_pad,
+                              const uint32_t* unit_off_sym, int dim, float temperature, float* rowsum,
+                              void* stream_) {
+  if (int rc = check_device()) return rc;
+  if (!ehat || !bits || !tor || !unit_off_sym || !rowsum) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (dim != 64 && dim != 128) return fail(MUSCLE_ERR_BAD_ARG, "symmetric row-sum pass: dim must be 64 or 128 (got %d)", dim);
+  if (!(temperature >= kMinTemperature))
+    return fail(MUSCLE_ERR_BAD_ARG, "temperature must be >= %g (exp((s-1)/T) underflows fp32 below it)", kMinTemperature);
+  if (rows_pad % 256 || rows_pad <= 0) return fail(MUSCLE_ERR_BAD_ARG, "padded size must be a positive multiple of 256");
+  return rowsum_sym(ehat, bits, tor, rows_pad, unit_off_sym, dim, temperature, rowsum, static_cast<cudaStream_t>(stream_));
+}
+
 int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows,
                         const uint32_t* tor_rows, const float* w_rows, int64_t rows_pad,
                         const void* ehat_cols, const uint32_t* bits_cols,
@@ -332,13 +408,15 @@ int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows,
       !w_cols || !unit_off || !part)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
-  if (!(temperature > 0.f)) return fail(MUSCLE_ERR_BAD_ARG, "temperature must be > 0");
+  if (!(temperature >= kMinTemperature))
+    return fail(MUSCLE_ERR_BAD_ARG, "temperature must be >= %g (exp((s-1)/T) underflows fp32 below it)", kMinTemperature);
   if (rows_pad % 256 || cols_pad % 256 || rows_pad <= 0 || cols_pad <= 0)
     return fail(MUSCLE_ERR_BAD_ARG, "padded sizes must be positive multiples of 256");
   PairParams prm{};
   prm.bits_row = bits_rows; prm.bits_col = bits_cols; prm.tor_row = tor_rows; prm.tor_col = tor_cols;
   prm.w_row = w_rows; prm.w_col = w_cols; prm.part = part; prm.unit_off = unit_off;
   prm.scale_log2 = kLog2e / temperature;
+  prm.mask_shift = pair_mask_shift(prm.scale_log2, poly_ok(temperature));
   prm.n_row_blocks = static_cast<int>(rows_pad / rows_per_block(dim));
   prm.n_col_tiles = static_cast<int>(cols_pad / 128);
   prm.rows_pad = static_cast<int>(rows_pad);
@@ -395,7 +473,7 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
 namespace {
 
 struct Workspace {
-  size_t ehat, bits, inv_norm, perm, tor, unit_off, rowsum, w, gpos, small, scratch, part, total;
+  size_t ehat, bits, inv_norm, perm, tor, unit_off, unit_off_sym, rowsum, w, gpos, small, scratch, part, total;
   size_t seg, class_sum, class_mass, dproto, loss_acc, ticket, small_bytes;  // offsets inside `small`
   size_t zero_lo, zero_bytes;  // rowsum .. small are zeroed with one memset
   int64_t rows_pad;
@@ -413,6 +491,7 @@ Workspace plan_workspace(int64_t n, int dim, int C) {
   ws.perm = take(rp * 4);
   ws.tor = take(rp / 128 * 4);
   ws.unit_off = take((rp / 128 + 1) * 4);
+  ws.unit_off_sym = take((rp / 128 + 1) * 4);
   ws.w = take(rp * 4);
   ws.gpos = take(rp * 4);
   ws.rowsum = take(rp * 4);
@@ -446,7 +525,7 @@ size_t muscle_dense_infonce_workspace_bytes(int64_t n_pixels, int dim, int num_c
 namespace {
 // the composite's view of its workspace
 struct Carved {
-  void* ehat; uint32_t* bits; float* inv_norm; int32_t* perm; uint32_t* tor; uint32_t* unit_off;
+  void* ehat; uint32_t* bits; float* inv_norm; int32_t* perm; uint32_t* tor; uint32_t* unit_off; uint32_t* unit_off_sym;
   float *rowsum, *w, *gpos, *class_sum, *class_mass, *dproto, *part;
   double* loss_acc; uint32_t* seg; char* scratch; unsigned int* ticket;
 };
@@ -460,6 +539,7 @@ Carved carve(void* workspace, const Workspace& ws) {
   c.perm = reinterpret_cast<int32_t*>(base + ws.perm);
   c.tor = reinterpret_cast<uint32_t*>(base + ws.tor);
   c.unit_off = reinterpret_cast<uint32_t*>(base + ws.unit_off);
+  c.unit_off_sym = reinterpret_cast<uint32_t*>(base + ws.unit_off_sym);
   c.rowsum = reinterpret_cast<float*>(base + ws.rowsum);
   c.w = reinterpret_cast<float*>(base + ws.w);
   c.gpos = reinterpret_cast<float*>(base + ws.gpos);
@@ -481,7 +561,8 @@ int check_composite(int dim, int num_classes, float temperature, int64_t batch, 
   if (!dim_ok(dim)) return fail(MUSCLE_ERR_BAD_ARG, "dim must be 64, 128 or 256 (got %d)", dim);
   if (num_classes < 1 || num_classes > MUSCLE_MAX_CLASSES)
     return fail(MUSCLE_ERR_BAD_ARG, "num_classes must be in [1,%d]", MUSCLE_MAX_CLASSES);
-  if (!(temperature > 0.f)) return fail(MUSCLE_ERR_BAD_ARG, "temperature must be > 0");
+  if (!(temperature >= kMinTemperature))
+    return fail(MUSCLE_ERR_BAD_ARG, "temperature must be >= %g (exp((s-1)/T) underflows fp32 below it)", kMinTemperature);
   if (batch <= 0 || pixels_per_image <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty input");
   if ((reinterpret_cast<uintptr_t>(workspace) & 255) != 0)
     return fail(MUSCLE_ERR_BAD_ARG, "workspace must be 256-byte aligned");
@@ -537,11 +618,17 @@ int composite_forward(const float* x, int layout, int64_t batch, int64_t pixels_
   // (the work partition `unit_off` comes out of the scan kernel: no plan launch)
   int rc = prepare_impl(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes, eps,
                         c.ehat, c.bits, c.inv_norm, c.perm, c.tor, c.seg, c.class_sum, c.class_mass,
-                        c.scratch, muscle_infonce_prepare_scratch_bytes(n), c.unit_off, stream);
+                        c.scratch, muscle_infonce_prepare_scratch_bytes(n), c.unit_off,
+                        rowsum_sym_enabled(dim) ? c.unit_off_sym : nullptr, stream);
   if (rc) return rc;
   tm.mark("memset+hist+scan(+plan)+prepare+class_sum");
-  rc = muscle_infonce_rowsum(c.ehat, c.bits, c.tor, ws.rows_pad, c.ehat, c.bits, c.tor, ws.rows_pad,
-                             c.unit_off, dim, temperature, c.rowsum, stream);
+  if (!(temperature >= kMinTemperature))
+    return fail(MUSCLE_ERR_BAD_ARG, "temperature must be >= %g (exp((s-1)/T) underflows fp32 below it)", kMinTemperature);
+  if (rowsum_sym_enabled(dim))   // rows == columns: the symmetric pass (half the products and exponentials)
+    rc = rowsum_sym(c.ehat, c.bits, c.tor, ws.rows_pad, c.unit_off_sym, dim, temperature, c.rowsum, stream);
+  else
+    rc = muscle_infonce_rowsum(c.ehat, c.bits, c.tor, ws.rows_pad, c.ehat, c.bits, c.tor, ws.rows_pad,
+                               c.unit_off, dim, temperature, c.rowsum, stream);
   if (rc) return rc;
   tm.mark("rowsum");
   rc = launch_mid(c.ehat, c.seg, ws.rows_pad, dim, num_classes, c.class_sum, c.class_mass, c.rowsum,

@@ -67,6 +67,7 @@ struct PairParams {
   float* rowsum;             // [rows_pad]  MODE_ROWSUM: += sum_k mask * exp((s - 1)/tau)
   float* part;               // [PAIR_SLOTS][rows_pad][D]  MODE_GRAD: partial sum_k T_qk c_k
   float scale_log2;          // log2(e) / tau
+  float mask_shift;          // extra exponent shift of a masked column in the MASK_BIAS form (see pair_mask_shift)
   int n_row_blocks;          // row blocks of PAIR_RB rows
   int n_col_tiles;           // column tiles of 128
   int rows_pad;
@@ -208,10 +209,20 @@ __global__ void __launch_bounds__(1024) pair_plan_kernel(const uint32_t* tor_row
 // MASK_NONE: no label mask needed.  MASK_SELECT: per-element select on the class bits.  MASK_BIAS:
 // the rows of the tile have at most BIAS_SLOTS distinct classes, so the mask is one vector per row
 // class and column tile, folded into the exponent shift: bias_sm[k] = -a for a kept column,
-// -a - 64 for a masked one (exp2 leaves < 2^-64 of the term: below fp32 resolution of any row sum,
+// -a - mask_shift for a masked one (pair_mask_shift: the leak stays below fp32 resolution of any row sum,
 // at no instruction cost); every thread reads the vector of its row's class.  POLY of every 4 element pairs take the FMA-pipe exponential.
 enum { MASK_NONE = 0, MASK_SELECT = 1, MASK_BIAS = 2 };
-constexpr float MASK_BIAS_SHIFT = 64.f;
+// A masked column keeps 2^-shift of its term.  The smallest term a kept column can have is 2^(-2a)
+// (s = -1), so the shift is at least 2a + 26: a masked column then leaks < 2^-26 of the smallest possible
+// negative whatever the temperature (a fixed 64 leaked as much as a real negative for tau < 0.027).
+// With the FMA-pipe polynomial in use the exponent must stay above -120 (ex2_poly2), which bounds
+// a; without it the shift is 200 and ex2.approx.ftz returns exactly 0 for a masked column.
+__host__ __device__ inline float pair_mask_shift(float a, bool poly) {
+  if (!poly) return 200.f;
+  const float s = 2.f * a + 26.f;
+  return s > 64.f ? s : 64.f;
+}
+__host__ __device__ inline bool pair_poly_ok(float a) { return 2.f * a + pair_mask_shift(a, true) < 118.f; }
 template <int MODE, int POLY, int MASK>
 __device__ __forceinline__ void pair_half_math(uint32_t (&v)[2][32], uint32_t t_addr,
                                                const uint8_t* bits_sm, const uint8_t* w_sm,
@@ -564,7 +575,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           float* cbw = reinterpret_cast<float*>(const_cast<uint8_t*>(cb)) + t;
           uint32_t rem = tor_r & TOR_CLASSES;
           for (int j = 0; rem != 0u; ++j, rem &= rem - 1u)
-            cbw[j * 128] = (kb & ~(rem & (0u - rem))) ? -a : -a - MASK_BIAS_SHIFT;
+            cbw[j * 128] = (kb & ~(rem & (0u - rem))) ? -a : -a - p.mask_shift;
           ++n_bias;   // double buffered: the barrier of the next masked tile orders reuse
           asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
         }

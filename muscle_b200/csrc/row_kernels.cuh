@@ -15,6 +15,7 @@
 
 #include "ptx.cuh"
 #include "pair_kernel.cuh"
+#include "pair_sym_kernel.cuh"
 
 namespace mb200 {
 
@@ -73,7 +74,8 @@ __global__ void __launch_bounds__(SORT_CHUNK) class_hist_kernel(const void* cls,
 __global__ void __launch_bounds__(1024) class_scan_kernel(uint32_t* hist, int n_blk, int C,
                                                           long long n, long long rows_pad,
                                                           uint32_t* seg, float* class_mass,
-                                                          uint32_t* tor, uint32_t* unit_off) {
+                                                          uint32_t* tor, uint32_t* unit_off,
+                                                          uint32_t* unit_off_sym) {
   pdl_trigger();
   pdl_wait();
   __shared__ uint32_t total[MAX_BINS + 1];
@@ -136,6 +138,10 @@ __global__ void __launch_bounds__(1024) class_scan_kernel(uint32_t* hist, int n_
   if (unit_off != nullptr) {
     __syncthreads();
     pair_plan_body<1>(tor, static_cast<int>(n_tiles), tor, static_cast<int>(n_tiles), unit_off);
+  }
+  if (unit_off_sym != nullptr) {   // and the units with column tile >= row tile for the symmetric row-sum pass
+    __syncthreads();
+    pair_plan_sym_body(tor, static_cast<int>(n_tiles), unit_off_sym);
   }
 }
 

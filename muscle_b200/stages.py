@@ -67,6 +67,19 @@ class CudaStages:
                 rowsum.data_ptr(), _sp(self.device))
         _lib.check(rc, "infonce_rowsum")
 
+    def plan_sym(self, tor, rows_pad, unit_off_sym):
+        with torch.cuda.device(self.device):
+            rc = self.lib.muscle_infonce_plan_sym(tor.data_ptr(), rows_pad, unit_off_sym.data_ptr(), _sp(self.device))
+        _lib.check(rc, "infonce_plan_sym")
+
+    def rowsum_sym(self, ehat, bits, tor, rows_pad, unit_off_sym, dim, temperature, rowsum):
+        """rows == columns (single GPU): only the live units with column tile >= row tile"""
+        with torch.cuda.device(self.device):
+            rc = self.lib.muscle_infonce_rowsum_sym(ehat.data_ptr(), bits.data_ptr(), tor.data_ptr(), rows_pad,
+                                                    unit_off_sym.data_ptr(), dim, float(temperature),
+                                                    rowsum.data_ptr(), _sp(self.device))
+        _lib.check(rc, "infonce_rowsum_sym")
+
     def mid(self, ehat, seg, rows_pad, dim, num_classes, class_sum, class_mass, rowsum, temperature, w, gpos,
             loss_acc, dproto):
         with torch.cuda.device(self.device):

@@ -570,46 +570,23 @@ def fieldloss_forward(seg_map, dense_ft, mask, label_with_bg, step=7, k=100, bet
 
 
 # --------------------------------------------------------------------------
-# synthetic inputs shared by tests, smoke() and bench.py
+# synthetic inputs of the tests: the generator lives beside bench.py (workloads.py); these keep the
+# tests' historical inputs (background channel biased by +0.15, i.e. ~75 % background pixels)
 # --------------------------------------------------------------------------
+import os as _os
+import sys as _sys
 
-VOC_CLASS_FREQ = np.array(
-    [0.0565, 0.0485, 0.0672, 0.0449, 0.0673, 0.0388, 0.1061, 0.0934, 0.1123, 0.0281,
-     0.0572, 0.1094, 0.0436, 0.0472, 0.3823, 0.0505, 0.0297, 0.0614, 0.0488, 0.0533])
-"""Per-class image frequency of data/cls_labels.npy (mean 1.55 labels per image)."""
+_sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
+import workloads as _workloads  # noqa: E402
 
-
-def synth_labels(batch, gen):
-    """Multi-hot [B,20] float labels with VOC-like statistics; every image has >=1 label."""
-    p = torch.tensor(VOC_CLASS_FREQ, dtype=torch.float32)
-    lab = (torch.rand(batch, 20, generator=gen) < p).float()
-    for i in range(batch):
-        if lab[i].sum() == 0:
-            lab[i, int(torch.multinomial(p, 1, generator=gen))] = 1
-    return lab
+VOC_CLASS_FREQ = _workloads.VOC_CLASS_FREQ
+synth_labels = _workloads.synth_labels
 
 
-def synth_pixel_classes(label, h, w, gen, smooth=9):
-    """Blob-structured per-pixel class ids [B,h,w] in {0=bg} U image labels: argmax of
-    low-pass-filtered noise restricted to the allowed classes."""
-    b = label.shape[0]
-    noise = torch.randn(b, 21, h, w, generator=gen)
-    k = smooth if smooth % 2 == 1 else smooth + 1
-    k = min(k, 2 * (min(h, w) // 2) + 1)
-    noise = F.avg_pool2d(noise, k, 1, k // 2, count_include_pad=False)
-    noise[:, 0] += 0.15  # background a little more likely
-    allowed = torch.cat([torch.ones(b, 1), label], dim=1).bool()
-    noise = noise.masked_fill(~allowed[:, :, None, None], float("-inf"))
-    return noise.argmax(1)
+def synth_pixel_classes(label, h, w, gen, smooth=9, bg_bias=0.15):
+    return _workloads.synth_pixel_classes(label, h, w, gen, smooth=smooth, bg_bias=bg_bias)
 
 
-def synth_embeddings(batch, dim, h, w, seed):
-    """(x [B,D,h,w] fp32, cls [B,h,w] int64, label [B,20]) for the dense InfoNCE configs."""
-    gen = torch.Generator().manual_seed(seed)
-    label = synth_labels(batch, gen)
-    cls = synth_pixel_classes(label, h, w, gen)
-    x = torch.randn(batch, dim, h, w, generator=gen)
-    # give the classes some structure so the loss is not at its trivial value
-    centers = torch.randn(21, dim, generator=gen)
-    x = x + 0.5 * centers[cls].permute(0, 3, 1, 2)
-    return x, cls, label
+def synth_embeddings(batch, dim, h, w, seed, bg_bias=0.15):
+    """(x [B,D,h,w] fp32, cls [B,h,w] int64, label [B,20]); see workloads.synth_embeddings."""
+    return _workloads.synth_embeddings(batch, dim, h, w, seed, bg_bias=bg_bias)
