@@ -5,11 +5,20 @@ fwd+bwd, pixel-pairs/s).
     python bench.py --gpus N --steps K --warmup W          # this repo's CUDA path
     python bench.py --impl reference --gpus N ...          # the reference algorithm on host cores
 
-One "step" = one forward + input-gradient pass of the dense label-masked InfoNCE over one batch
-of synthetic EfficientNet-stride-8 embeddings.  N=1: BASELINE config 2 (B=8, 448 crop -> 56x56
-pixels, D=128, 21 classes).  N>1: config 4 (global batch 64, 512 crop -> 64x64, D=128) sharded by
-image, cross-GPU negatives via all-gather (strong scaling: the global batch is fixed).
-Prints ONE JSON line on rank 0.
+One "step" = one forward + input-gradient pass of the dense label-masked InfoNCE over one batch of
+synthetic EfficientNet-stride-8 embeddings.  The workload is THE SAME at every N (so that the driver's
+1 -> 8 efficiency is one strong-scaling curve): BASELINE config 4 — global batch 64, 512x512 crop ->
+64x64 pixels, D = 128, 21 classes, 262 144 pixels, 6.9e10 pixel pairs — sharded by image over the N
+ranks, cross-GPU negatives through one all-gather (N = 1: the single-GPU op on the whole batch).
+The N = 1 line also carries config 2 (the configuration the metric is quoted on: B = 8, 448 crop ->
+56x56) and config 3 (the largest single-GPU configuration: B = 16, 512 crop -> 64x64) as keyed
+sub-records under "configs", each with its own roofline / e2e / cpu_baseline.
+`--workload configN` benches one configuration alone.  Prints ONE JSON line on rank 0.
+
+What the line counts: `value` = ALL (query, key) entries of the global similarity matrix per second
+(SURVEY.md §8d's pixel pair: N_g^2 per step); pairs of equal class are masked by the loss and cost
+nothing on either arm, so `live_pair_fraction` / `live_pairs_per_s` state the cross-class share, and
+`class_histogram` the mix it comes from (`config.bg_bias` is the generator's one free parameter).
 """
 from __future__ import annotations
 
@@ -26,32 +35,26 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
+import workloads  # noqa: E402
+
 METRIC = "contrastive_loss_fwd_bwd_pixel_pairs_per_s"
 UNIT = "pixel-pairs/s"
 TEMPERATURE = 0.1
 NUM_CLASSES = 21
+SEED = 1234
 
-
-def workload(n_gpus, name=None):
-    if name == "config3":
-        return dict(name="config3: dense pseudo-mask pixel-pixel InfoNCE fwd+bwd, batch 16, 512x512 crop, stride 8 "
-                         "(64x64), D=128, 21 classes", global_batch=16, h=64, w=64, dim=128)
-    if (name is None and n_gpus == 1) or name == "config2":
-        return dict(name="config2: MCL dense InfoNCE fwd+bwd, B=8, 448x448 crop, stride 8 (56x56), D=128, 21 classes",
-                    global_batch=8, h=56, w=56, dim=128)
-    if name == "config5":
-        return dict(name="config5 (stress): full pixel-pixel dense InfoNCE with cross-GPU negatives, global batch 256, "
-                         "512x512 crop, stride 8 (64x64), D=256, 21 classes",
-                    global_batch=256, h=64, w=64, dim=256)
-    return dict(name="config4: dense InfoNCE with cross-GPU negatives (all-gather), global batch 64, 512x512 crop, "
-                     "stride 8 (64x64), D=128, 21 classes",
-                global_batch=64, h=64, w=64, dim=128)
-
-
-def synth(batch, dim, h, w, seed):
-    from oracle import muscle_oracle as O   # synthetic-input generator shared with the tests
-    x, cls, _ = O.synth_embeddings(batch, dim, h, w, seed)
-    return x, cls
+WORKLOADS = {
+    "config2": dict(name="config2: MCL dense InfoNCE fwd+bwd, B=8, 448x448 crop, stride 8 (56x56), D=128, 21 classes",
+                    global_batch=8, h=56, w=56, dim=128),
+    "config3": dict(name="config3: dense pseudo-mask pixel-pixel InfoNCE fwd+bwd, batch 16, 512x512 crop, stride 8 "
+                         "(64x64), D=128, 21 classes", global_batch=16, h=64, w=64, dim=128),
+    "config4": dict(name="config4: dense InfoNCE with cross-GPU negatives (all-gather), global batch 64, 512x512 crop, "
+                         "stride 8 (64x64), D=128, 21 classes", global_batch=64, h=64, w=64, dim=128),
+    "config5": dict(name="config5 (stress): full pixel-pixel dense InfoNCE with cross-GPU negatives, global batch 256, "
+                         "512x512 crop, stride 8 (64x64), D=256, 21 classes", global_batch=256, h=64, w=64, dim=256),
+}
+DEFAULT_WORKLOAD = "config4"      # at EVERY --gpus N
+SUB_WORKLOADS = ("config2", "config3")
 
 
 def peaks():
@@ -112,10 +115,36 @@ class ClockSampler:
                     samples=len(s))
 
 
-def cpu_reference_step(x, cls, q_rows, threads):
-    """One fwd+bwd of the reference algorithm (oracle port of src/loss_multilabel.py:9-21 composed
-    per SURVEY.md §8c) for the first `q_rows` queries against ALL keys, fp32, on the host cores.
-    -> seconds, pixel pairs processed."""
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's algorithm on the host cores (checker code: the only use of oracle/ here)
+# ------------------------------------------------------------------------------------------------
+
+def cpu_query_sample(cls, q_rows, top=3):
+    """The bounded sample of query pixels one CPU step covers.  The reference composition is one info_nce
+    call per class, and every call first gathers its negatives E[cls != c] — a fixed cost the full run
+    spreads over ALL queries of the class.  A sample spread thinly over all ~20 classes would pay that
+    gather 20 times for a few hundred queries each and understate the CPU arm, so the sample is drawn
+    (evenly spread, in proportion) from the `top` largest classes, which hold most of the pixels."""
+    c = cls.reshape(-1)
+    n = c.numel()
+    q_rows = min(n, q_rows)
+    hist = torch.bincount(c[c >= 0], minlength=NUM_CLASSES)
+    classes = torch.argsort(hist, descending=True)[:top]
+    classes = classes[hist[classes] > 0]
+    tot = int(hist[classes].sum())
+    picks = []
+    for ci in classes.tolist():
+        idx = torch.nonzero(c == ci).reshape(-1)
+        k = max(1, min(idx.numel(), int(round(q_rows * idx.numel() / tot))))
+        picks.append(idx[(torch.arange(k, dtype=torch.int64) * idx.numel()) // k])
+    return torch.cat(picks)
+
+
+def cpu_reference_step(x, cls, q_idx, threads):
+    """One fwd+bwd of the reference composition for the sampled queries against ALL keys, fp32: one
+    reference-style info_nce(E[cls==c], E[cls==c], E[cls!=c]) call per class (oracle port of
+    src/loss_multilabel.py:9-21), so — like the GPU arm — only cross-class pairs are
+    multiplied.  -> seconds, pixel pairs covered (sampled queries x all keys), loss share of the sample."""
     from oracle import muscle_oracle as O
     torch.set_num_threads(threads)
     d = x.shape[1]
@@ -123,119 +152,102 @@ def cpu_reference_step(x, cls, q_rows, threads):
     c = cls.reshape(-1)
     t0 = time.perf_counter()
     e = O.l2_normalize_pixels(flat)
-    proto, _ = O.class_prototypes(e, c, NUM_CLASSES)
-    loss = O.dense_infonce(e[:q_rows], c[:q_rows], e, c, TEMPERATURE, NUM_CLASSES, proto=proto, row_chunk=2048)
+    loss = O.dense_infonce_per_class(e, c, TEMPERATURE, query_idx=q_idx)
     loss.backward()
     dt = time.perf_counter() - t0
-    return dt, float(q_rows) * flat.shape[0]
+    return dt, float(q_idx.numel()) * flat.shape[0], float(loss.detach())
 
 
-def run_reference(args, wl):
-    """--impl reference: the reference algorithm timed on this box's host cores (bounded sample)."""
+def cpu_sample_rows(n):
+    """Queries per CPU step: ~1e9 pairs (a few seconds on 16 host threads), at most the whole batch."""
+    return int(max(256, min(n, (1 << 30) // n)))
+
+
+def cpu_baseline_record(x, cls, budget_s, max_reps, kind_note):
+    threads = os.cpu_count() or 1
+    n = x.shape[0] * x.shape[2] * x.shape[3]
+    q_idx = cpu_query_sample(cls, cpu_sample_rows(n))
+    cpu_reference_step(x, cls, q_idx, threads)                        # warm-up
+    tt, pp, reps = 0.0, 0.0, 0
+    while tt < budget_s and reps < max_reps:
+        dt, pairs, _ = cpu_reference_step(x, cls, q_idx, threads)
+        tt += dt
+        pp += pairs
+        reps += 1
+    return dict(value=pp / tt, unit=UNIT, cores=threads, kind="port",
+                sample="%d query pixels (evenly spread over the 3 largest classes) x all %d key pixels fwd+bwd, %d repeats, fp32 torch CPU; %s"
+                       % (q_idx.numel(), n, reps, kind_note))
+
+
+CPU_NOTE = ("oracle port of the reference info_nce called once per class (src/loss_multilabel.py:9-21 composed per "
+            "SURVEY.md 8c): cross-class pairs only, like the GPU arm; the reference is Python and has no package to "
+            "install, and /root/reference does not exist on the GPU box")
+
+
+def run_reference(args, wl, bg_bias):
+    """--impl reference: the reference algorithm timed on this box's host cores; every step is a bounded
+    sample of the workload (a few seconds), W warm-up steps then exactly K timed steps."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    x, cls = synth(wl["global_batch"], wl["dim"], wl["h"], wl["w"], 1234)
+    x, cls, _ = workloads.synth_embeddings(wl["global_batch"], wl["dim"], wl["h"], wl["w"], SEED, bg_bias=bg_bias)
     n = x.shape[0] * x.shape[2] * x.shape[3]
-    q_rows = min(n, 4096)
-    for _ in range(min(args.warmup, 1)):
-        cpu_reference_step(x, cls, q_rows, threads)
-    steps = max(1, min(args.steps, 5))
+    q_idx = cpu_query_sample(cls, cpu_sample_rows(n))
+    for _ in range(args.warmup):
+        cpu_reference_step(x, cls, q_idx, threads)
     tot_t, tot_p = 0.0, 0.0
-    for _ in range(steps):
-        dt, pairs = cpu_reference_step(x, cls, q_rows, threads)
+    for _ in range(args.steps):
+        dt, pairs, _ = cpu_reference_step(x, cls, q_idx, threads)
         tot_t += dt
         tot_p += pairs
     v = tot_p / tot_t
-    sample = "%d query pixels x all %d key pixels per step, %d steps, fp32, torch CPU" % (q_rows, n, steps)
-    line = dict(impl="reference", metric=METRIC, value=v, unit=UNIT, n_gpus=args.gpus, steps=steps,
-                warmup=min(args.warmup, 1), ms_per_step=1e3 * tot_t / steps, higher_is_better=True,
-                scaling="strong" if args.gpus > 1 else "weak", vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload=wl["name"]),
+    lf = workloads.live_pair_fraction(cls, NUM_CLASSES)
+    sample = "%d query pixels (evenly spread over the 3 largest classes) x all %d key pixels per step, fp32 torch CPU; %s" % (q_idx.numel(), n, CPU_NOTE)
+    line = dict(impl="reference", metric=METRIC, value=v, unit=UNIT, n_gpus=args.gpus, steps=args.steps,
+                warmup=args.warmup, ms_per_step=1e3 * tot_t / args.steps, higher_is_better=True,
+                scaling="strong", vs_baseline=None, dtype="f32", data="synthetic",
+                config=dict(workload=wl["name"]), bg_bias=bg_bias,
+                live_pair_fraction=lf, live_pairs_per_s=v * lf,
                 cpu_baseline=dict(value=v, unit=UNIT, cores=threads, kind="port", sample=sample),
                 e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(line))
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
-    ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default=None, choices=["config2", "config3", "config4", "config5"],
-                    help="override the default (config2 at 1 GPU, config4 at N>1), e.g. config4 on 1 GPU")
-    args = ap.parse_args()
-    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
-    wl = workload(args.gpus, args.workload)
-    if args.impl == "reference":
-        return run_reference(args, wl)
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
 
-    import torch.distributed as dist
-    import muscle_b200 as M
-    from muscle_b200 import dist as MD
-    from muscle_b200.stages import CudaStages
-    from muscle_b200 import _lib
+class Env:
+    """Process-wide state of the GPU arm."""
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
+    def __init__(self, args):
+        import torch.distributed as dist
+        self.dist = dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world != args.gpus and self.world == 1 and args.gpus > 1:
             raise SystemExit("launch with torch.distributed.run --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        # NCCL prints its version banner on STDOUT at NCCL_DEBUG=VERSION; stdout carries the one JSON line
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
-        dist.init_process_group("nccl", device_id=dev)
+        torch.cuda.set_device(self.local_rank)
+        self.dev = torch.device("cuda", self.local_rank)
+        if self.world > 1:
+            # NCCL prints its version banner on STDOUT at NCCL_DEBUG=VERSION; stdout carries the one JSON line
+            if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+                os.environ["NCCL_DEBUG"] = "WARN"
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=self.dev)   # > 126 MB L2
 
-    gb, h, w, dim = wl["global_batch"], wl["h"], wl["w"], wl["dim"]
-    assert gb % world == 0
-    lb = gb // world
-    x_all, cls_all = synth(gb, dim, h, w, 1234)
-    x_h = x_all[rank * lb:(rank + 1) * lb].contiguous().pin_memory()
-    c_h = cls_all[rank * lb:(rank + 1) * lb].contiguous().pin_memory()
-    x_d = x_h.to(dev)
-    c_d = c_h.to(dev)
-    n_local = lb * h * w
-    n_global = gb * h * w
-    pairs_per_step = float(n_global) * float(n_global)     # whole job: every (query, key) entry of the global matrix
-
-    def step_device():
-        xg = x_d.detach().requires_grad_()
-        if world > 1:
-            loss = MD.dense_infonce_sharded(xg, c_d, TEMPERATURE, NUM_CLASSES)
-        else:
-            loss = M.dense_infonce(xg, c_d, TEMPERATURE, NUM_CLASSES)
-        loss.backward()
-        return loss, xg.grad
-
-    def step_e2e():
-        xg = x_h.to(dev, non_blocking=True).requires_grad_()
-        cg = c_h.to(dev, non_blocking=True)
-        if world > 1:
-            loss = MD.dense_infonce_sharded(xg, cg, TEMPERATURE, NUM_CLASSES)
-        else:
-            loss = M.dense_infonce(xg, cg, TEMPERATURE, NUM_CLASSES)
-        loss.backward()
-        return float(loss.item())          # device -> host read of the step's result
-
-    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
-        """Per-step CUDA-event timing on the launching stream, L2 flushed (untimed) before each step."""
+    def timed(self, fn, steps):
+        """Per-step CUDA-event timing on the launching stream, L2 flushed (untimed) before each step. -> seconds"""
         evs = []
         for _ in range(steps):
-            flush.zero_()
+            self.flush.zero_()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             fn()
@@ -244,32 +256,92 @@ def main():
         torch.cuda.synchronize()
         return sum(a.elapsed_time(b) for a, b in evs) / 1e3
 
-    for _ in range(args.warmup):
+    def max_over_ranks(self, values):
+        t = torch.tensor(values, dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return [float(v) for v in t]
+
+
+def traffic_for(key, kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture of this workload."""
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(tpath):
+        return None, None
+    with open(tpath) as f:
+        tj = json.load(f)
+    rec = tj.get(key)
+    if not rec:
+        return None, None
+    return rec.get("bytes_per_launch", {}).get(kernel), rec.get("source")
+
+
+def measure(env, key, wl, steps, warmup, bg_bias, e2e_runs_n, with_fused, cpu_budget_s):
+    """Benches one workload on env.world ranks.  -> the record (rank 0) or None."""
+    import muscle_b200 as M
+    from muscle_b200 import dist as MD
+    from muscle_b200.stages import CudaStages
+    from muscle_b200 import _lib
+
+    world, rank, dev = env.world, env.rank, env.dev
+    gb, h, w, dim = wl["global_batch"], wl["h"], wl["w"], wl["dim"]
+    assert gb % world == 0, "global batch must divide over the ranks"
+    lb = gb // world
+    x_all, cls_all, _ = workloads.synth_embeddings(gb, dim, h, w, SEED, bg_bias=bg_bias)
+    x_h = x_all[rank * lb:(rank + 1) * lb].contiguous().pin_memory()
+    c_h = cls_all[rank * lb:(rank + 1) * lb].contiguous().pin_memory()
+    x_d = x_h.to(dev)
+    c_d = c_h.to(dev)
+    n_local = lb * h * w
+    n_global = gb * h * w
+    pairs_per_step = float(n_global) * float(n_global)     # every (query, key) entry of the global matrix
+    live_frac_pairs = workloads.live_pair_fraction(cls_all, NUM_CLASSES)
+
+    def loss_of(xg, cg):
+        if world > 1:
+            return MD.dense_infonce_sharded(xg, cg, TEMPERATURE, NUM_CLASSES)
+        return M.dense_infonce(xg, cg, TEMPERATURE, NUM_CLASSES)
+
+    last = {}
+
+    def step_device():
+        xg = x_d.detach().requires_grad_()
+        loss = loss_of(xg, c_d)
+        loss.backward()
+        last["loss"] = loss.detach()
+
+    def step_e2e():
+        xg = x_h.to(dev, non_blocking=True).requires_grad_()
+        cg = c_h.to(dev, non_blocking=True)
+        loss = loss_of(xg, cg)
+        loss.backward()
+        return float(loss.item())          # device -> host read of the step's result
+
+    for _ in range(warmup):
         step_device()
-    barrier()
-    sampler = ClockSampler(local_rank)
+    env.barrier()
+    sampler = ClockSampler(env.local_rank)
     sampler.start()
-    t_dev = timed(step_device, args.steps)
-    barrier()
+    t_dev = env.timed(step_device, steps)
+    env.barrier()
     clocks = sampler.stop()
+    loss_value = float(last["loss"].item())
     for _ in range(3):
         step_e2e()
-    barrier()
+    env.barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(steps):
         step_e2e()
     torch.cuda.synchronize()
     t_e2e_serial = time.perf_counter() - t0
-    barrier()
+    env.barrier()
 
     # The same through the public API the way a training loop feeds it: every step's inputs still go
     # pinned host -> device and every step's loss still comes back to the host inside the timed region,
     # but the next step's upload runs on a copy stream under the current step's kernels and the loss is
     # read back asynchronously (checked one step later), so no step waits on PCIe or on a host sync.
     copy_stream = torch.cuda.Stream(device=dev)
-    loss_pinned = torch.empty(args.steps + 3, dtype=torch.float32).pin_memory()
-
-    # two device-resident input buffers filled in turn (the usual prefetcher): no allocator traffic per step
+    loss_pinned = torch.empty(steps + 3, dtype=torch.float32).pin_memory()
     x_buf = [torch.empty(x_h.shape, dtype=x_h.dtype, device=dev) for _ in range(2)]
     c_buf = [torch.empty(c_h.shape, dtype=c_h.dtype, device=dev) for _ in range(2)]
     up_ev = [torch.cuda.Event() for _ in range(2)]     # upload into buffer b has finished
@@ -283,27 +355,24 @@ def main():
             c_buf[b].copy_(c_h, non_blocking=True)
             up_ev[b].record(copy_stream)
 
-    def e2e_pipelined(steps, fused=False):
+    def e2e_pipelined(n_steps, fused=False):
         main = torch.cuda.current_stream()
         for e in use_ev:
             e.record(main)
         gc_was = gc.isenabled()
-        gc.disable()                  # a collection in the middle of a 0.3 ms step costs several steps
+        gc.disable()                  # a collection in the middle of a short step costs several steps
         t_host0 = time.perf_counter()
         upload(0)
-        for i in range(steps):
+        for i in range(n_steps):
             b = i & 1
             main.wait_event(up_ev[b])
-            if i + 1 < steps:
+            if i + 1 < n_steps:
                 upload(i + 1)
             if fused:       # loss and dx from one C call, no autograd (dense_infonce_value_and_grad)
                 loss, _dx = M.dense_infonce_value_and_grad(x_buf[b], c_buf[b], TEMPERATURE, NUM_CLASSES)
             else:
                 xg = x_buf[b].detach().requires_grad_()
-                if world > 1:
-                    loss = MD.dense_infonce_sharded(xg, c_buf[b], TEMPERATURE, NUM_CLASSES)
-                else:
-                    loss = M.dense_infonce(xg, c_buf[b], TEMPERATURE, NUM_CLASSES)
+                loss = loss_of(xg, c_buf[b])
                 loss.backward()
             use_ev[b].record(main)
             loss_pinned[i].copy_(loss.detach(), non_blocking=True)   # device -> host read of the step's result
@@ -311,160 +380,196 @@ def main():
         torch.cuda.synchronize()
         if gc_was:
             gc.enable()
-        return loss_pinned[:steps].tolist()
+        return loss_pinned[:n_steps].tolist()
 
     e2e_pipelined(3)
-    # the loop is host bound by a small margin (enqueue ~0.27 ms/step against ~0.28 ms of kernels at
-    # config 2), so one descheduled host thread doubles a run: three runs of K steps, the median reported
     e2e_runs = []
-    for _ in range(3):
-        barrier()
+    for _ in range(e2e_runs_n):
+        env.barrier()
         t0 = time.perf_counter()
-        e2e_losses = e2e_pipelined(args.steps)
+        e2e_losses = e2e_pipelined(steps)
         e2e_runs.append((time.perf_counter() - t0, e2e_pipelined.host_s))
         assert all(v == v for v in e2e_losses), "NaN loss in the end-to-end run"
     e2e_runs.sort()
-    t_e2e, e2e_host_s = e2e_runs[1]
-    # the uploads alone (same buffers, same stream): the PCIe floor of any end-to-end step
-    barrier()
+    t_e2e, e2e_host_s = e2e_runs[len(e2e_runs) // 2]
+    env.barrier()
     t0 = time.perf_counter()
-    for i in range(args.steps):
+    for i in range(steps):
         upload(i)
     torch.cuda.synchronize()
     t_h2d = time.perf_counter() - t0
     fused_e2e = None
-    if world == 1:      # informational: the same loop through the autograd-free public call
+    if world == 1 and with_fused:      # informational: the same loop through the autograd-free public call
         e2e_pipelined(3, fused=True)
         fr = []
-        for _ in range(3):
-            barrier()
+        for _ in range(e2e_runs_n):
+            env.barrier()
             t0 = time.perf_counter()
-            e2e_pipelined(args.steps, fused=True)
+            e2e_pipelined(steps, fused=True)
             fr.append((time.perf_counter() - t0, e2e_pipelined.host_s))
         fr.sort()
-        fused_e2e = dict(ms_per_step=1e3 * fr[1][0] / args.steps, value=pairs_per_step * args.steps / fr[1][0],
-                         host_enqueue_ms_per_step=1e3 * fr[1][1] / args.steps,
+        mid = fr[len(fr) // 2]
+        fused_e2e = dict(ms_per_step=1e3 * mid[0] / steps, value=pairs_per_step * steps / mid[0],
+                         host_enqueue_ms_per_step=1e3 * mid[1] / steps,
                          note="dense_infonce_value_and_grad: loss and dx from one C call, no autograd engine")
-    barrier()
+    env.barrier()
+    del x_buf, c_buf
 
-    # dominant kernel (gradient pass) and the row-sum pass, timed alone through the staged C ABI
+    # ---- the two pair passes timed alone through the staged C ABI (this rank's rows x all columns)
     st = CudaStages(dev)
-    rows_pad = st.pad_rows(n_local)
-    kern = {}
-    if world == 1:
-        cols_pad = rows_pad
-        f32, i32 = torch.float32, torch.int32
-        C = NUM_CLASSES
-        ehat = st.empty((rows_pad, dim), torch.bfloat16)
-        bits = st.empty((rows_pad,), i32)
-        tor = st.empty((rows_pad // 128,), i32)
-        inv_norm = st.empty((rows_pad,), f32)
-        perm = st.empty((n_local,), i32)
-        seg = st.empty((C + 2,), i32)
-        stats = st.zeros((C * dim + C,), f32)
-        cs, cm = stats[:C * dim], stats[C * dim:]
-        rowsum, wv, gpos = (st.zeros((rows_pad,), f32) for _ in range(3))
-        dproto = st.zeros((C * dim,), f32)
-        lacc = st.zeros((1,), torch.float64)
-        st.prepare(x_d, _lib.LAYOUT_NCHW, lb, h * w, dim, c_d, C, 1e-12, ehat, bits, inv_norm, perm, tor, seg, cs, cm)
-        unit_off = st.empty((rows_pad // st.unit_rows(dim) + 1,), i32)
-        st.plan(tor, rows_pad, tor, cols_pad, dim, unit_off)
-        st.rowsum(ehat, bits, tor, rows_pad, ehat, bits, tor, cols_pad, unit_off, dim, TEMPERATURE, rowsum)
-        st.mid(ehat, seg, rows_pad, dim, C, cs, cm, rowsum, TEMPERATURE, wv, gpos, lacc, dproto)
-        part = st.empty((st.part_slots(), rows_pad, dim), f32)
-        grad_fn = lambda: st.grad(ehat, bits, tor, wv, rows_pad, ehat, bits, tor, wv, cols_pad, unit_off, dim, TEMPERATURE, part)
-        rs_tmp = st.zeros((rows_pad,), f32)
-        rowsum_fn = lambda: st.rowsum(ehat, bits, tor, rows_pad, ehat, bits, tor, cols_pad, unit_off, dim, TEMPERATURE, rs_tmp)
-        live_units = int(unit_off[-1].item())
-        for _ in range(3):
-            grad_fn(); rowsum_fn()
-        ksteps = max(10, min(args.steps, 50))
-        kern["grad_s"] = timed(grad_fn, ksteps) / ksteps
-        kern["rowsum_s"] = timed(rowsum_fn, ksteps) / ksteps
-        kern["live_frac"] = live_units / float((rows_pad // st.unit_rows(dim)) * (cols_pad // 128))
-
-    # max over ranks (device-timed)
-    t = torch.tensor([t_dev, t_e2e, t_e2e_serial], dtype=torch.float64, device=dev)
+    C = NUM_CLASSES
+    f32, i32 = torch.float32, torch.int32
+    xg = x_d.detach().requires_grad_()
+    loss0, state = MD.sharded_fwd(st, xg, c_d, TEMPERATURE, C, 1e-12, True, None)
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    t_dev, t_e2e, t_e2e_serial = float(t[0]), float(t[1]), float(t[2])
+        MD._all_gather_into(state["w_all"], state["w"], None)
+    rows_pad, cols_pad = state["rows_pad"], state["cols_pad"]
+    part = st.empty((st.part_slots(), rows_pad, dim), f32)
+    w_cols = state["w_all"] if world > 1 else state["w"]
 
-    if rank == 0:
-        pk = peaks()
-        value = pairs_per_step * args.steps / t_dev
-        e2e_v = pairs_per_step * args.steps / t_e2e
-        line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
-                    ms_per_step=1e3 * t_dev / args.steps, higher_is_better=True,
-                    scaling="strong" if world > 1 else "weak", vs_baseline=None, dtype="bf16", data="synthetic",
-                    config=dict(workload=wl["name"], global_batch=gb, pixels_per_image=h * w, proj_dim=dim,
-                                temperature=TEMPERATURE, parallelism="dp%d (batch-sharded, all-gather keys)" % world,
+    def grad_fn():
+        st.grad(state["ehat"], state["bits"], state["tor"], state["w"], rows_pad, state["ehat_all"], state["bits_all"],
+                state["tor_all"], w_cols, cols_pad, state["unit_off"], dim, TEMPERATURE, part)
+
+    rs_tmp = st.zeros((rows_pad,), f32)
+    sym = world == 1 and dim <= 128 and os.environ.get("MUSCLE_ROWSUM_SYM", "1") != "0"
+    if sym:
+        uo_sym = st.empty((rows_pad // 128 + 1,), i32)
+        st.plan_sym(state["tor"], rows_pad, uo_sym)
+
+        def rowsum_fn():
+            st.rowsum_sym(state["ehat"], state["bits"], state["tor"], rows_pad, uo_sym, dim, TEMPERATURE, rs_tmp)
+        rowsum_kernel = "pair_sym_kernel<%d>" % dim
+    else:
+        def rowsum_fn():
+            st.rowsum(state["ehat"], state["bits"], state["tor"], rows_pad, state["ehat_all"], state["bits_all"],
+                      state["tor_all"], cols_pad, state["unit_off"], dim, TEMPERATURE, rs_tmp)
+        rowsum_kernel = "pair_kernel<%d,MODE_ROWSUM>" % dim
+    live_units = int(state["unit_off"][-1].item())
+    for _ in range(3):
+        grad_fn()
+        rowsum_fn()
+    ksteps = max(5, min(steps, 30))
+    grad_s = env.timed(grad_fn, ksteps) / ksteps
+    rowsum_s = env.timed(rowsum_fn, ksteps) / ksteps
+    live_tile_frac = live_units / float((rows_pad // 128) * (cols_pad // 128))
+    del part, state
+
+    t_dev, t_e2e, t_e2e_serial, grad_s, rowsum_s = env.max_over_ranks([t_dev, t_e2e, t_e2e_serial, grad_s, rowsum_s])
+    live_units_all = env.max_over_ranks([float(live_units)])[0]     # slowest rank's share (the one timed)
+    if rank != 0:
+        return None
+
+    pk = peaks()
+    value = pairs_per_step * steps / t_dev
+    rec = dict(workload=wl["name"], value=value, unit=UNIT, ms_per_step=1e3 * t_dev / steps, steps=steps, warmup=warmup,
+               loss=loss_value, live_pair_fraction=live_frac_pairs, live_pairs_per_s=value * live_frac_pairs,
+               class_histogram=workloads.class_histogram(cls_all, NUM_CLASSES),
+               global_batch=gb, pixels=n_global, pixels_per_image=h * w, proj_dim=dim, clocks=clocks)
+    h2d_bytes = int(x_h.numel() * 4 + c_h.numel() * 8)
+    rec["e2e"] = dict(value=pairs_per_step * steps / t_e2e, unit=UNIT, h2d_bytes_per_step=h2d_bytes, d2h_bytes_per_step=4,
+                      ms_per_step=1e3 * t_e2e / steps,
+                      mode="pipelined: next step's pinned-host upload on a copy stream into one of two device buffers, "
+                           "loss read back asynchronously; every step's H2D and D2H are inside the timed region",
+                      host_enqueue_ms_per_step=1e3 * e2e_host_s / steps, value_and_grad=fused_e2e,
+                      h2d_only_ms_per_step=1e3 * t_h2d / steps, h2d_gb_per_s=h2d_bytes * steps / t_h2d / 1e9,
+                      runs_ms_per_step=[1e3 * r[0] / steps for r in e2e_runs],
+                      runs_note="%d run(s) of `steps` steps each, the median is `value`" % len(e2e_runs),
+                      serial_value=pairs_per_step * steps / t_e2e_serial, serial_ms_per_step=1e3 * t_e2e_serial / steps,
+                      serial_note="upload -> step -> blocking .item() per step, nothing overlapped")
+    # whole step on the pairs the loss keeps: 6*D flops per ordered LIVE pixel pair (S, dQ, dK) / step time
+    live_pairs = pairs_per_step * live_frac_pairs
+    live_tf = 6.0 * dim * live_pairs * steps / t_dev / 1e12 / world
+    all_tf = 6.0 * dim * pairs_per_step * steps / t_dev / 1e12 / world
+    rec["step_tensor"] = dict(live_tflops_per_gpu=live_tf, live_frac_of_sustained=live_tf / pk["bf16_sustained"],
+                              live_frac_of_burst=live_tf / pk["bf16_burst"], all_pairs_tflops_per_gpu=all_tf,
+                              note="per GPU, whole step incl. HBM kernels and collectives; 6*D flops per ordered pixel "
+                                   "pair of different class (the pairs the loss keeps); all_pairs counts the masked "
+                                   "same-class pairs too, which no arm multiplies")
+    # dominant kernel: the gradient pass.  Algorithmic flops of a launch = 4*D per ordered pair of every LIVE
+    # 128 x 128 tile pair (tile pairs of one single class are masked entirely and never multiplied)
+    unit_pairs = live_units_all * 128.0 * 128.0
+    ach = 4.0 * dim * unit_pairs / grad_s / 1e12
+    traffic, traffic_src = traffic_for(key, "pair_kernel<%d,MODE_GRAD>" % dim) if world == 1 else (None, None)
+    rec["roofline"] = dict(bound="tensor", kernel="pair_kernel<%d,MODE_GRAD>" % dim, achieved=ach, peak=pk["bf16_burst"],
+                           unit="TFLOP/s", frac=ach / pk["bf16_burst"], frac_of_sustained=ach / pk["bf16_sustained"],
+                           traffic=traffic, traffic_source=traffic_src,
+                           traffic_note="algorithmic DRAM bytes per launch = the bf16 operands once: %d bytes"
+                                        % ((rows_pad + (cols_pad if world > 1 else 0)) * dim * 2),
+                           peak_source=pk["source"] + ", burst figure (kernel timed alone)",
+                           algorithmic="4*D flops per ordered pixel pair of every live (row tile, column tile) unit: S "
+                                       "recomputed (2*D) + one T@E product (2*D) that serves dQ and dK through the "
+                                       "symmetric form; slowest rank's launch",
+                           us_per_launch=1e6 * grad_s, live_tile_fraction=live_tile_frac, live_units=int(live_units_all))
+    ach1 = 2.0 * dim * unit_pairs / rowsum_s / 1e12
+    traffic1, traffic1_src = traffic_for(key, rowsum_kernel) if world == 1 else (None, None)
+    rec["roofline_rowsum"] = dict(bound="tensor", kernel=rowsum_kernel, achieved=ach1, peak=pk["bf16_burst"], unit="TFLOP/s",
+                                  frac=ach1 / pk["bf16_burst"], us_per_launch=1e6 * rowsum_s, traffic=traffic1,
+                                  traffic_source=traffic1_src,
+                                  algorithmic="2*D flops per ordered pixel pair of every live unit (S = E E^T); the "
+                                              "symmetric pass executes half of them (S of a tile pair serves both "
+                                              "orders), so frac can exceed the executed tensor rate" if sym else
+                                              "2*D flops per ordered pixel pair of every live unit (S = R C^T)")
+    if cpu_budget_s > 0:
+        rec["cpu_baseline"] = cpu_baseline_record(x_all, cls_all, cpu_budget_s, 20, CPU_NOTE)
+    return rec
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sub", action="store_true", help="N=1: skip the config2 / config3 sub-records")
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
+                    help="bench this configuration alone (default: config4 at every N, + config2/config3 sub-records at N=1)")
+    ap.add_argument("--bg-bias", type=float, default=0.0,
+                    help="bias of the background channel in the synthetic class maps (0 = SURVEY 8d; 0.15 = round 1, ~75%% bg)")
+    args = ap.parse_args()
+    key = args.workload or DEFAULT_WORKLOAD
+    wl = WORKLOADS[key]
+    if args.impl == "reference":
+        return run_reference(args, wl, args.bg_bias)
+    args.warmup = max(args.warmup, 3)
+
+    env = Env(args)
+    cpu_budget = 0 if (args.no_cpu_baseline or env.world > 1) else 12.0
+    rec = measure(env, key, wl, args.steps, args.warmup, args.bg_bias, 3, True, cpu_budget)
+    subs = {}
+    if env.world == 1 and args.workload is None and not args.no_sub:
+        for sk in SUB_WORKLOADS:
+            sub_steps = max(args.steps, 20)
+            subs[sk] = measure(env, sk, WORKLOADS[sk], sub_steps, args.warmup, args.bg_bias, 3, True,
+                               0 if args.no_cpu_baseline else 6.0)
+    if env.rank == 0:
+        world = env.world
+        launches_per_step = 8 if world == 1 else 10      # ours; NCCL's kernels are not counted
+        line = dict(metric=METRIC, value=rec["value"], unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
+                    ms_per_step=rec["ms_per_step"], higher_is_better=True, scaling="strong", vs_baseline=None,
+                    dtype="bf16", data="synthetic",
+                    config=dict(workload=wl["name"], global_batch=wl["global_batch"], pixels_per_image=wl["h"] * wl["w"],
+                                proj_dim=wl["dim"], temperature=TEMPERATURE, bg_bias=args.bg_bias,
+                                parallelism="dp%d (batch-sharded, all-gather keys)" % world,
                                 l2="flushed (256 MiB write) before every timed step",
-                                accumulate="fp32 (TMEM); operands bf16"),
-                    e2e=dict(value=e2e_v, unit=UNIT, h2d_bytes_per_step=int(x_h.numel() * 4 + c_h.numel() * 8),
-                             d2h_bytes_per_step=4, ms_per_step=1e3 * t_e2e / args.steps,
-                             mode="pipelined: next step's pinned-host upload on a copy stream into one of two device buffers, loss read back "
-                                  "asynchronously; every step's H2D and D2H are inside the timed region",
-                             host_enqueue_ms_per_step=1e3 * e2e_host_s / args.steps,
-                             value_and_grad=fused_e2e,
-                             h2d_only_ms_per_step=1e3 * t_h2d / args.steps,
-                             h2d_gb_per_s=(x_h.numel() * 4 + c_h.numel() * 8) * args.steps / t_h2d / 1e9,
-                             runs_ms_per_step=[1e3 * r[0] / args.steps for r in e2e_runs],
-                             runs_note="three runs of `steps` steps each, the median is `value`",
-                             serial_value=pairs_per_step * args.steps / t_e2e_serial,
-                             serial_ms_per_step=1e3 * t_e2e_serial / args.steps,
-                             serial_note="upload -> step -> blocking .item() per step, nothing overlapped"),
-                    gpu_launches=int(args.steps * 8), clocks=clocks)
-        flops_step = 6.0 * dim * pairs_per_step
-        line["step_tensor"] = dict(algorithmic_tflops_per_gpu=flops_step * args.steps / t_dev / 1e12 / world,
-                                   frac_of_sustained=flops_step * args.steps / t_dev / 1e12 / world / pk["bf16_sustained"],
-                                   note="per GPU; 6*D flops per ordered pixel pair (S, dQ, dK) over ALL pairs, whole step "
-                                        "incl. HBM kernels and collectives; tile pairs whose pixels share one class are "
-                                        "fully masked and skipped, so this can exceed the executed tensor rate")
-        if kern:
-            # algorithmic flops of a launch = the LIVE 128 x 128 tile pairs only: pairs whose tiles hold one and
-            # the same class are masked by the loss and are never multiplied
-            allp = 4.0 * dim * float(n_local) * float(n_global) / kern["grad_s"] / 1e12
-            ach = allp * kern["live_frac"]
-            # DRAM bytes per launch of this kernel from the committed ncu --set full capture (same workload only)
-            traffic, traffic_src = None, None
-            tpath = os.path.join(ROOT, "profiles", "traffic.json")
-            if os.path.exists(tpath) and wl["name"].startswith("config2") and world == 1:
-                with open(tpath) as f:
-                    tj = json.load(f)
-                traffic = tj["bytes_per_launch"].get("pair_kernel<%d,MODE_GRAD>" % dim)
-                traffic_src = tj["source"]
-            line["roofline"] = dict(bound="tensor", kernel="pair_kernel<%d,MODE_GRAD>" % dim, achieved=ach,
-                                    peak=pk["bf16_burst"], unit="TFLOP/s", frac=ach / pk["bf16_burst"],
-                                    frac_of_sustained=ach / pk["bf16_sustained"], traffic=traffic,
-                                    traffic_source=traffic_src,
-                                    traffic_note="algorithmic DRAM bytes per launch = the bf16 operand once: "
-                                                 "%d bytes" % (rows_pad * dim * 2),
-                                    peak_source=pk["source"] + ", burst figure (kernel timed alone)",
-                                    algorithmic="4*D flops per ordered pixel pair of every live (row tile, column tile) "
-                                                "unit: S recomputed (2*D) + one T@E product (2*D) that serves dQ and dK "
-                                                "through the symmetric form",
-                                    us_per_launch=1e6 * kern["grad_s"], live_tile_fraction=kern["live_frac"],
-                                    all_pairs_tflops=allp,
-                                    all_pairs_note="the same launch counted over ALL pixel pairs, masked ones included "
-                                                   "(what a dense implementation would have to multiply)")
-            ach1 = 2.0 * dim * float(n_local) * float(n_global) / kern["rowsum_s"] / 1e12 * kern["live_frac"]
-            line["roofline_rowsum"] = dict(bound="tensor", kernel="pair_kernel<%d,MODE_ROWSUM>" % dim, achieved=ach1,
-                                           peak=pk["bf16_burst"], unit="TFLOP/s", frac=ach1 / pk["bf16_burst"],
-                                           us_per_launch=1e6 * kern["rowsum_s"])
-        if world == 1 and not args.no_cpu_baseline:
-            threads = os.cpu_count() or 1
-            q_rows = min(n_global, 4096)
-            cpu_reference_step(x_all, cls_all, q_rows, threads)
-            tt, pp, reps = 0.0, 0.0, 0
-            while tt < 10.0 and reps < 20:
-                dt, pairs = cpu_reference_step(x_all, cls_all, q_rows, threads)
-                tt += dt; pp += pairs; reps += 1
-            line["cpu_baseline"] = dict(value=pp / tt, unit=UNIT, cores=threads, kind="port",
-                                        sample="%d query pixels x all %d key pixels fwd+bwd, %d repeats, fp32 torch CPU "
-                                               "(oracle port of the reference info_nce composition)" % (q_rows, n_global, reps))
+                                accumulate="fp32 (TMEM); operands bf16",
+                                same_workload_at_every_n=args.workload is None),
+                    loss=rec["loss"], live_pair_fraction=rec["live_pair_fraction"],
+                    live_pairs_per_s=rec["live_pairs_per_s"], class_histogram=rec["class_histogram"],
+                    e2e=rec["e2e"], gpu_launches=int(args.steps * launches_per_step),
+                    gpu_launches_note="%d kernels of libmuscle_b200.so per step (hist, scan, prepare, class_sum, row-sum "
+                                      "pass, mid, gradient pass, final%s)" % (launches_per_step,
+                                                                                "" if world == 1 else ", plan, loss"),
+                    clocks=rec["clocks"], step_tensor=rec["step_tensor"], roofline=rec["roofline"],
+                    roofline_rowsum=rec["roofline_rowsum"])
+        if "cpu_baseline" in rec:
+            line["cpu_baseline"] = rec["cpu_baseline"]
+        if subs:
+            line["configs"] = {k: v for k, v in subs.items() if v is not None}
         print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    if env.world > 1:
+        env.dist.destroy_process_group()
 
 
 if __name__ == "__main__":

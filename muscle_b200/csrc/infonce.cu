@@ -164,15 +164,54 @@ int launch_pair_dim(int dim, bool poly, const void* ehat_rows, int64_t rows_pad,
 }
 
 // Row-sum pass over rows == columns (pair_sym_kernel.cuh): only the live units with c >= r.
-template <int D, int POLY>
-int launch_rowsum_sym(const void* ehat, int64_t rows_pad, PairParams prm, cudaStream_t stream) {
-  using C = SymCfg<D>;
+template <int D, int POLY, int NG>
+int launch_rowsum_sym_ng(const void* ehat, int64_t rows_pad, PairParams prm, cudaStream_t stream) {
+  using C = SymCfg<D, NG>;
   CUtensorMap tm;
   if (int rc = cached_panel_map(ehat, rows_pad, D, &tm)) return rc;
-  if (int rc = ensure_dynamic_smem<pair_sym_kernel<D, POLY>>(C::SMEM_BYTES)) return rc;
-  MB_CUDA(launch_pdl(pair_sym_kernel<D, POLY>, dim3(pair_grid()), dim3(C::THREADS), C::SMEM_BYTES, stream, tm, prm));
+  if (int rc = ensure_dynamic_smem<pair_sym_kernel<D, POLY, NG>>(C::SMEM_BYTES)) return rc;
+#if MB_PAIR_TIMING
+  static const bool timing = getenv("MUSCLE_PAIR_TIMING") != nullptr;
+  static unsigned long long* dbg = nullptr;
+  if (timing) {
+    if (!dbg) cudaMalloc(&dbg, pair_grid() * 16 * sizeof(unsigned long long));
+    cudaMemsetAsync(dbg, 0, pair_grid() * 16 * sizeof(unsigned long long), stream);
+    prm.dbg = dbg;
+  }
+#endif
+  MB_CUDA(launch_pdl(pair_sym_kernel<D, POLY, NG>, dim3(pair_grid()), dim3(C::THREADS), C::SMEM_BYTES, stream, tm, prm));
   MB_LAUNCH_CHECK();
+#if MB_PAIR_TIMING
+  if (timing) {
+    static int printed = 0;
+    cudaStreamSynchronize(stream);
+    const int grid = std::min(pair_grid(), 148);
+    unsigned long long h[148 * 16];
+    cudaMemcpy(h, dbg, grid * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    if (printed++ < 4) {
+      double s[16] = {0};
+      int n = 0;
+      for (int c = 0; c < grid; ++c)
+        if (h[c * 16 + 6]) { for (int k = 0; k < 16; ++k) s[k] += double(h[c * 16 + k]); ++n; }
+      if (n) {
+        const double own = s[6] / n;
+        fprintf(stderr, "[pair_sym D=%d NG=%d] active CTAs %d, own units/CTA (group 0) %.1f | per own unit: item %.0f "
+                        "ktile %.0f S %.0f drain %.0f ld %.0f math+store %.0f fence+publish %.0f cycles\n",
+                D, NG, n, own, s[0] / n / own, s[1] / n / own, s[2] / n / own, s[3] / n / own, s[4] / n / own, s[5] / n / own, s[15] / n / own);
+        fprintf(stderr, "    producer: wait k_empty %.0f of %.0f per unit (%.1f units/CTA) | S issuer: wait %.0f (column tile %.0f) of %.0f | column-sum issuer: wait %.0f of %.0f per unit\n",
+                s[8] / s[10], s[9] / s[10], s[10] / n, s[11] / s[10], s[7] / s[10], s[12] / s[10], s[13] / s[10], s[14] / s[10]);
+      }
+    }
+  }
+#endif
   return MUSCLE_OK;
+}
+template <int D, int POLY>
+int launch_rowsum_sym(const void* ehat, int64_t rows_pad, PairParams prm, cudaStream_t stream) {
+  // MUSCLE_SYM_NG=2: two epilogue groups and a three-stage column ring instead of three groups and two stages
+  static const int ng = getenv("MUSCLE_SYM_NG") ? atoi(getenv("MUSCLE_SYM_NG")) : 3;
+  if (ng == 2) return launch_rowsum_sym_ng<D, POLY, 2>(ehat, rows_pad, prm, stream);
+  return launch_rowsum_sym_ng<D, POLY, 3>(ehat, rows_pad, prm, stream);
 }
 
 // MUSCLE_ROWSUM_SYM=0 keeps the ordered row-sum pass in the single-GPU composite (A/B measurements)

@@ -15,27 +15,52 @@
 // Structure as pair_kernel (one persistent CTA per SM; NG epilogue groups of four warps, one TMA producer
 // warp, one MMA issuer warp), with these differences:
 //   * work list = live units with c >= r, numbered by pair_plan_sym_body; a CTA takes an even share;
-//   * the issuer runs two cursors, S products and column-sum products, and polls whichever can go
-//     (S(k) needs its column tile and a free S buffer; CS(k) needs the group's e tile);
+//   * two issuer threads (warps of their own), one for the S products and one for the column-sum products:
+//     the streams are independent (S(k) needs its column tile and a free S buffer; CS(k) the group's e tile);
 //   * a group drains the column sums of its unit k while it already works on unit k+NG (deferred, so
 //     the column-sum product's latency is never waited for);
-//   * the column-tile ring (2 stages at D = 128: the e tiles need the room) is shorter than the number of
-//     groups, so a group has not seen the previous phase of the stage it waits for (PairCfg's
-//     static_assert explains the hazard: a wait for phase n+1 is also satisfied while phase n-1 is the
-//     last complete one).  The producer therefore publishes the unit number a stage is being filled
-//     for (seq word, written before the barrier is armed) and a group first waits for ITS unit number.
-// TMEM: S buffer b at [128 b, 128 b + 128), b < NB = 3; column sums of group g at [384 + 16 g, +16).
+//   * the column-tile ring (2 stages at D = 128: the e tiles need the room) is private to the producer and
+//     the S issuer: a stage is free again as soon as its S product has completed, so the look-ahead lives
+//     in the NB TMEM buffers, not in shared memory.  What an epilogue group needs of a column tile -- its
+//     class bits (512 B) and the unit record (class union, tile index) -- travels through a separate ring
+//     of NBR = 16 slots with barriers of its own.  A slot is reused 16 units later: by then S(g+14) has
+//     completed, which needs the S buffer of unit g+11 back, so every group is past unit g (no "empty"
+//     barrier).  A group has not seen the previous phase of the slot it waits for (PairCfg's static_assert
+//     explains that hazard: a wait for phase n+1 is also satisfied while phase n-1 is the last complete
+//     one), so the producer publishes the unit number a slot is filled for before it arms the barrier,
+//     and a group first waits for ITS unit number.
+//   * S = R C^T takes R from TENSOR memory (tcgen05.mma with A in TMEM): group 0 copies the row tile from
+//     its staging buffer into TMEM once per work item, and the S products then read only the column tile
+//     from shared memory.  Shared-memory bandwidth is what bounds this pass (per unit: 32 KB TMA write,
+//     32 KB e-tile stores, 36 KB column-sum operands, and 64 KB of S operands in the SS form -- 32 KB now).
+// TMEM: S buffer b at [128 b, 128 b + 128), b < NB = 3; column sums of group g at [384 + 16 g, +16);
+// the row tile at [384 + 16 NG, + D/2).
 #pragma once
 #include "pair_kernel.cuh"
 
+// experiment switch (scripts/build_variants.sh -DMB_SYM_SPIN=n): bit 0 = producer / issuers poll with test_wait,
+// bit 1 = the epilogue groups do too
+#ifndef MB_SYM_SPIN
+#define MB_SYM_SPIN 1
+#endif
+
 namespace mb200 {
 
-template <int D>
+__device__ __forceinline__ void sym_wait_role(uint32_t bar, uint32_t parity) {
+  if (MB_SYM_SPIN & 1) mbar_wait_spin(bar, parity); else mbar_wait(bar, parity);
+}
+__device__ __forceinline__ void sym_wait_epi(uint32_t bar, uint32_t parity) {
+  if (MB_SYM_SPIN & 2) mbar_wait_spin(bar, parity); else mbar_wait(bar, parity);
+}
+
+template <int D, int NG_ = 3>
 struct SymCfg {
   static_assert(D == 64 || D == 128, "symmetric row-sum pass: projection dim 64 or 128");
-  static constexpr int NG = 3;
+  static_assert(NG_ == 2 || NG_ == 3, "two or three epilogue groups");
+  static constexpr int NG = NG_;
   static constexpr int NB = 3;
-  static constexpr int NST = (D == 128) ? 2 : 4;
+  // shared memory decides the ring depth at D = 128: row tile 32 KB + NST x 32 KB + NG e tiles of 32 KB
+  static constexpr int NST = (D == 128) ? (NG == 3 ? 2 : 3) : 4;
   static constexpr int TILE_BYTES = 128 * D * 2;
   static constexpr int PANEL_BYTES = 128 * 128;
   static constexpr int E_BYTES = 2 * PANEL_BYTES;          // bf16 [128 q][128 k] as two [128][64] panels
@@ -43,19 +68,24 @@ struct SymCfg {
   static constexpr int SMEM_K = SMEM_Q + TILE_BYTES;
   static constexpr int SMEM_E = SMEM_K + NST * TILE_BYTES;
   static constexpr int SMEM_ONES = SMEM_E + NG * E_BYTES;  // bf16 1.0 x 1024 (B operand of the column-sum product)
+  static constexpr int NBR = 16;                           // ring of class-bit vectors + unit records (see below)
   static constexpr int SMEM_BITS = SMEM_ONES + 2048;
-  static constexpr int SMEM_CB = SMEM_BITS + NST * 512;    // exponent-shift vectors [NG][2][BIAS_SLOTS][128]
+  static constexpr int SMEM_CB = SMEM_BITS + NBR * 512;    // exponent-shift vectors [NG][2][BIAS_SLOTS][128]
   static constexpr int SMEM_CBM = SMEM_CB + 2 * NG * BIAS_SLOTS * 512;   // one all-masked vector (rows outside the loss)
   static constexpr int SMEM_BAR = SMEM_CBM + 512;
-  static constexpr int NBAR = 2 * NST + 2 + 2 * NB + 2 * NG;
-  static constexpr int SMEM_INFO = SMEM_BAR + NBAR * 8;    // item headers [2][4], stage info [NST][4]
-  static constexpr int SMEM_TMEMPTR = SMEM_INFO + (8 + 4 * NST) * 4;
+  static constexpr int NBAR = 2 * NST + 2 + 2 * NB + 2 * NG + 1 + NBR;
+  static constexpr int SMEM_INFO = SMEM_BAR + NBAR * 8;    // item headers [2][4], unit records [NBR][4]
+  static constexpr int SMEM_TMEMPTR = SMEM_INFO + (8 + 4 * NBR) * 4;
   static constexpr int SMEM_BYTES = SMEM_TMEMPTR + 16 + 1024;
   static constexpr int CS_COL = NB * 128;
+  static constexpr int R_COL = CS_COL + 16 * NG;           // the row tile as the A operand: bf16 [128 lanes][D/2 columns]
   static constexpr int WARP_PRODUCER = 4 * NG;
-  static constexpr int WARP_ISSUER = 4 * NG + 1;
-  static constexpr int THREADS = (4 * NG + 2) * 32;
-  static_assert(CS_COL + 16 * NG <= 512, "TMEM budget");
+  static constexpr int WARP_ISSUER_S = 4 * NG + 1;
+  static constexpr int WARP_ISSUER_CS = 4 * NG + 2;
+  static constexpr int THREADS = (4 * NG + 4) * 32;
+  // (registers are allocated to warps in fours: 14 warps cost what 16 do, so 128 registers per thread is the
+  // limit with three groups -- a __maxnreg__(144) build does not launch -- and 168 with two)
+  static_assert(R_COL + D / 2 <= 512, "TMEM budget");
   static_assert(NG <= NB, "a group must have seen the previous phase of its S buffer");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
@@ -199,10 +229,10 @@ __device__ __forceinline__ void sym_half_math(uint32_t (&v)[2][32], uint32_t e_r
   }
 }
 
-template <int D, int POLY>
-__global__ void __launch_bounds__((SymCfg<D>::THREADS), 1)
+template <int D, int POLY, int NG_>
+__global__ void __launch_bounds__((SymCfg<D, NG_>::THREADS), 1)
 pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) {
-  using C = SymCfg<D>;
+  using C = SymCfg<D, NG_>;
   constexpr int NST = C::NST;
   constexpr int NB = C::NB;
   constexpr int NG = C::NG;
@@ -224,9 +254,12 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
   auto s_free = [&](int b) { return bar0 + 8u * (2 * NST + 2 + NB + b); };
   auto e_full = [&](int g) { return bar0 + 8u * (2 * NST + 2 + 2 * NB + g); };
   auto cs_full = [&](int g) { return bar0 + 8u * (2 * NST + 2 + 2 * NB + NG + g); };
+  const uint32_t r_full = bar0 + 8u * (2 * NST + 2 + 2 * NB + 2 * NG);   // row tile copied into TMEM
+  auto b_full = [&](int sl) { return bar0 + 8u * (2 * NST + 2 + 2 * NB + 2 * NG + 1 + sl); };   // class bits of slot sl landed
   volatile uint32_t* info = reinterpret_cast<volatile uint32_t*>(smem_gen + C::SMEM_INFO);
-  // info[4*(it&1) + {0,1}]: live units, row block of item `it`; info[8 + 4 st + {0,1,2}]: tor, index of the stage's column tile, number of the unit it is filled for
+  // info[4*(it&1) + {0,1,2}]: live units, row block of item `it`, first unit is the diagonal one; info[8 + 4 sl + {0,1,2}]: class union and index of the column tile of ring slot sl, number of the unit it is filled for
   volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + C::SMEM_TMEMPTR);
+  __shared__ uint2 ulist_sm[32];           // producer warp: (class union, index) of the next column tiles to load
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -234,10 +267,10 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NST; ++s) {
       mbar_init(k_full(s), 1);
-      mbar_init(k_empty(s), 1 + 4);      // S product done + the four warps of the group that owns the unit
+      mbar_init(k_empty(s), 1);          // S product done
     }
     mbar_init(q_full, 1);
-    mbar_init(q_empty, 1 + 4 * NG);
+    mbar_init(q_empty, 2 + 4 * NG);      // S issuer (last S of the item) + column-sum issuer + every epilogue warp
     for (int b = 0; b < NB; ++b) {
       mbar_init(s_full(b), 1);
       mbar_init(s_free(b), 4);
@@ -246,6 +279,8 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
       mbar_init(e_full(g), 4);
       mbar_init(cs_full(g), 1);
     }
+    mbar_init(r_full, 4);
+    for (int sl = 0; sl < C::NBR; ++sl) mbar_init(b_full(sl), 1);
     fence_barrier_init();
   }
   // constants in shared memory: the ones tile and the all-masked shift vector
@@ -253,9 +288,9 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
     reinterpret_cast<uint32_t*>(smem_gen + C::SMEM_ONES)[i] = 0x3f803f80u;
   for (int i = threadIdx.x; i < 128; i += blockDim.x)
     reinterpret_cast<float*>(smem_gen + C::SMEM_CBM)[i] = -p.scale_log2 - p.mask_shift;
-  if (threadIdx.x < NST) info[8 + 4 * threadIdx.x + 2] = 0xffffffffu;
+  if (threadIdx.x < C::NBR) info[8 + 4 * threadIdx.x + 2] = 0xffffffffu;
   fence_proxy_async_smem();
-  if (warp == C::WARP_ISSUER) {
+  if (warp == C::WARP_ISSUER_S) {
     tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_ptr_smem)), 512);
     tmem_relinquish();
   }
@@ -292,6 +327,7 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
       rb = lo;
     }
     uint32_t gcnt = 0, it = 0;
+    long long p_wait = 0, p_t0 = (kPairTiming && p.dbg) ? clock64() : 0;
     while (u < u1) {
       const uint32_t U0 = __ldg(p.unit_off + rb), U1 = __ldg(p.unit_off + rb + 1);
       if (U1 <= u) { ++rb; continue; }
@@ -302,6 +338,7 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
         mbar_wait(q_empty, (it & 1) ^ 1);
         info[4 * (it & 1) + 0] = e - a;
         info[4 * (it & 1) + 1] = static_cast<uint32_t>(rb);
+        info[4 * (it & 1) + 2] = (a == 0u && !tile_pair_dead(tor_r, tor_r)) ? 1u : 0u;   // first unit = (rb, rb)
         mbar_arrive_expect_tx(q_full, C::TILE_BYTES);
         tma_load_3d(q_smem, &tm_row, q_full, 0, rb * 128, 0);
       }
@@ -316,116 +353,121 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
         uint32_t live = __ballot_sync(0xffffffffu, jme >= rb && jme < p.n_col_tiles && !tile_pair_dead(tor_r, tc));
         const uint32_t cnt = __popc(live);
         if (li + cnt <= a) { li += cnt; continue; }
-        while (live != 0u && li < e) {
-          const int jj = __ffs(live) - 1;
-          live &= live - 1u;
-          const uint32_t tcj = __shfl_sync(0xffffffffu, tc, jj);
-          if (li++ < a) continue;
-          const int j = j0 + jj;
-          const int st = gcnt % NST;
-          if (lane == 0) {
-            mbar_wait(k_empty(st), ((gcnt / NST) & 1) ^ 1);
-            info[8 + 4 * st] = tcj;
-            info[8 + 4 * st + 1] = static_cast<uint32_t>(j);
-            info[8 + 4 * st + 2] = gcnt;
-            mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES + 512);
-            tma_load_3d(k_smem + st * C::TILE_BYTES, &tm_row, k_full(st), 0, j * 128, 0);
-            bulk_load_1d(bits_smem + st * 512, p.bits_col + static_cast<size_t>(j) * 128, 512, k_full(st));
+        // The lanes whose tile is one of the CTA's units write it into a 32-entry list (one step for up to 32
+        // units); lane 0 then only waits for a free stage and issues the copies.  (Walking the ballot word bit by
+        // bit on the issuing path cost ~900 cycles of this warp per unit -- it shares its scheduler with three busy
+        // epilogue warps -- and with a two-stage ring that latency was exposed on every unit.)
+        const uint32_t rank = __popc(live & ((1u << lane) - 1u));
+        const uint32_t idx = li + rank;                         // live index of this lane's tile in the row block
+        const uint32_t first = li > a ? li : a;
+        const uint32_t last = (li + cnt < e) ? li + cnt : e;    // units [first, last) of the row block come from this word
+        if (((live >> lane) & 1u) && idx >= first && idx < last)
+          ulist_sm[idx - first] = make_uint2(tc, static_cast<uint32_t>(jme));
+        __syncwarp();
+        if (lane == 0) {
+          for (uint32_t t = 0; t < last - first; ++t) {
+            const uint2 ent = ulist_sm[t];
+            const uint32_t g = gcnt + t;
+            const int st = static_cast<int>(g % NST);
+            { const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
+              sym_wait_role(k_empty(st), ((g / NST) & 1) ^ 1);
+              if (kPairTiming && p.dbg) p_wait += clock64() - w0; }
+            mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES);
+            tma_load_3d(k_smem + st * C::TILE_BYTES, &tm_row, k_full(st), 0, static_cast<int>(ent.y) * 128, 0);
+            const int sl = static_cast<int>(g % C::NBR);      // (after the stage wait: see the ring's reuse argument)
+            info[8 + 4 * sl] = ent.x;
+            info[8 + 4 * sl + 1] = ent.y;
+            info[8 + 4 * sl + 2] = g;
+            mbar_arrive_expect_tx(b_full(sl), 512);
+            bulk_load_1d(bits_smem + sl * 512, p.bits_col + static_cast<size_t>(ent.y) * 128, 512, b_full(sl));
           }
-          ++gcnt;
         }
+        gcnt += last - first;
+        li += cnt;
+        __syncwarp();
       }
       u = U0 + e;
       ++it;
     }
     if (lane == 0) {
+      if (kPairTiming && p.dbg) { p.dbg[blockIdx.x * 16 + 8] = p_wait; p.dbg[blockIdx.x * 16 + 9] = clock64() - p_t0; p.dbg[blockIdx.x * 16 + 10] = gcnt; }
       mbar_wait(q_empty, (it & 1) ^ 1);
       info[4 * (it & 1) + 0] = ITEM_END;
       mbar_arrive(q_full);
     }
-  } else if (warp == C::WARP_ISSUER) {
-    // ------------------------------------------------------------ MMA issuer: two cursors, polled
+  } else if (warp == C::WARP_ISSUER_S) {
+    // ------------------------------------------------------------ S = R C^T issuer
     if (elect_one()) {
       constexpr uint32_t IDESC_S = umma_idesc_bf16(128, 128, 0, 0);
+      uint32_t gS = 0;
+      long long i_t0 = (kPairTiming && p.dbg) ? clock64() : 0, i_wait = 0, i_wait_k = 0;
+      for (uint32_t it = 0;; ++it) {
+        mbar_wait(q_full, it & 1);
+        const uint32_t n_u = info[4 * (it & 1) + 0];
+        if (n_u == ITEM_END) break;
+        const int n = static_cast<int>(n_u);
+        mbar_wait(r_full, it & 1);       // group 0 has put the item's row tile into TMEM
+        tc_fence_after();
+        for (int k = 0; k < n; ++k, ++gS) {
+          const int st = static_cast<int>(gS % NST);
+          const int b = static_cast<int>(gS % NB);
+          { const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
+            sym_wait_role(k_full(st), (gS / NST) & 1);
+            const long long w1 = (kPairTiming && p.dbg) ? clock64() : 0;
+            sym_wait_role(s_free(b), ((gS / NB) & 1) ^ 1);
+            if (kPairTiming && p.dbg) { i_wait += clock64() - w0; i_wait_k += w1 - w0; } }
+          tc_fence_after();
+          const uint32_t b_base = k_smem + st * C::TILE_BYTES;
+#pragma unroll
+          for (int kk = 0; kk < D / 16; ++kk) {
+            const uint32_t off = (kk >> 2) * C::PANEL_BYTES + (kk & 3) * 32;
+            mma_ts(tmem + b * 128, tmem + C::R_COL + kk * 8, umma_desc_sw128(b_base + off, 16, 1024), IDESC_S, kk > 0);
+          }
+          tc_commit(s_full(b));
+          tc_commit(k_empty(st));
+          if (k == n - 1) tc_commit(q_empty);   // the item's last S is in flight: the TMEM row tile may be replaced after it
+        }
+      }
+      if (kPairTiming && p.dbg) { p.dbg[blockIdx.x * 16 + 11] = i_wait; p.dbg[blockIdx.x * 16 + 12] = clock64() - i_t0; p.dbg[blockIdx.x * 16 + 7] = i_wait_k; }
+    }
+  } else if (warp == C::WARP_ISSUER_CS) {
+    // ------------------------------------------------------------ column-sum issuer (its own thread: the two
+    // product streams are independent, and one thread polling for both spent more time on its own
+    // instructions -- it shares a scheduler with three busy epilogue warps -- than the tensor pipe on the products)
+    if (elect_one()) {
       constexpr uint32_t IDESC_CS = umma_idesc_bf16(128, 16, 1, 0);   // A = e tile MN-major, B = ones K-major
-      uint32_t gS = 0, gC = 0;          // units whose S / column-sum product has been issued (or skipped)
-      uint32_t diag_ring = 0;           // bit (g & 31): unit g is diagonal (no column sums)
+      uint32_t gC = 0;
       uint32_t ce[NG];                  // column-sum products issued per group
 #pragma unroll
       for (int g = 0; g < NG; ++g) ce[g] = 0;
-      uint32_t it = 0;
-      int n = 0, k = 0, rb = 0;
-      bool have_item = false, done = false;
-      uint32_t spins = 0;
-      while (true) {
-        bool progressed = false;
-        if (!have_item && !done && mbar_try_wait(q_full, it & 1)) {
-          const uint32_t n_u = info[4 * (it & 1) + 0];
-          if (n_u == ITEM_END) {
-            done = true;
-          } else {
-            n = static_cast<int>(n_u);
-            rb = static_cast<int>(info[4 * (it & 1) + 1]);
-            k = 0;
-            have_item = true;
-          }
-          progressed = true;
-        }
-        if (have_item && gS - gC < 24u) {
-          const int st = static_cast<int>(gS % NST);
-          const int b = static_cast<int>(gS % NB);
-          if (mbar_try_wait(k_full(st), (gS / NST) & 1) && mbar_try_wait(s_free(b), ((gS / NB) & 1) ^ 1)) {
-            tc_fence_after();
-            const bool diag = static_cast<int>(info[8 + 4 * st + 1]) == rb;
-            const uint32_t b_base = k_smem + st * C::TILE_BYTES;
+      long long c_t0 = (kPairTiming && p.dbg) ? clock64() : 0, c_wait = 0;
+      for (uint32_t it = 0;; ++it) {
+        mbar_wait(q_full, it & 1);
+        const uint32_t n_u = info[4 * (it & 1) + 0];
+        if (n_u == ITEM_END) break;
+        const int n = static_cast<int>(n_u);
+        const bool diag0 = info[4 * (it & 1) + 2] != 0u;      // the item's first unit is the diagonal one
+        mbar_arrive(q_empty);                                 // header read
+        for (int k = 0; k < n; ++k, ++gC) {
+          if (k == 0 && diag0) continue;
+          const int g = static_cast<int>(gC % NG);
+          { const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
+            sym_wait_role(e_full(g), ce[g] & 1);
+            if (kPairTiming && p.dbg) c_wait += clock64() - w0; }
+          tc_fence_after();
+          const uint32_t a_base = e_smem + g * C::E_BYTES;
 #pragma unroll
-            for (int kk = 0; kk < D / 16; ++kk) {
-              const uint32_t off = (kk >> 2) * C::PANEL_BYTES + (kk & 3) * 32;
-              mma_ss(tmem + b * 128, umma_desc_sw128(q_smem + off, 16, 1024),
-                     umma_desc_sw128(b_base + off, 16, 1024), IDESC_S, kk > 0);
-            }
-            tc_commit(s_full(b));
-            tc_commit(k_empty(st));
-            if (k == n - 1) {
-              tc_commit(q_empty);
-              have_item = false;
-              ++it;
-            }
-            diag_ring = (diag_ring & ~(1u << (gS & 31))) | (static_cast<uint32_t>(diag) << (gS & 31));
-            ++gS;
-            ++k;
-            progressed = true;
-          }
-        }
-        if (gC < gS) {
-          if ((diag_ring >> (gC & 31)) & 1u) {
-            ++gC;
-            progressed = true;
-          } else {
-            const int g = static_cast<int>(gC % NG);
-            if (mbar_try_wait(e_full(g), ce[g] & 1)) {
-              tc_fence_after();
-              const uint32_t a_base = e_smem + g * C::E_BYTES;
-#pragma unroll
-              for (int kk = 0; kk < 8; ++kk)
-                mma_ss(tmem + C::CS_COL + 16 * g, umma_desc_sw128(a_base + kk * 2048, C::PANEL_BYTES, 1024),
-                       umma_desc_sw128(ones_smem, 16, 1024), IDESC_CS, kk > 0);
-              tc_commit(cs_full(g));
-              ++ce[g];
-              ++gC;
-              progressed = true;
-            }
-          }
-        }
-        if (done && gC == gS) break;
-        if (progressed) {
-          spins = 0;
-        } else if (++spins > (1u << 26)) {
-          printf("pair_sym issuer timeout: block %d gS %u gC %u item %u\n", blockIdx.x, gS, gC, it);
-          __trap();
+          for (int kk = 0; kk < 8; ++kk)
+            mma_ss(tmem + C::CS_COL + 16 * g, umma_desc_sw128(a_base + kk * 2048, C::PANEL_BYTES, 1024),
+                   umma_desc_sw128(ones_smem, 16, 1024), IDESC_CS, kk > 0);
+          tc_commit(cs_full(g));
+          ++ce[g];
         }
       }
+      if (kPairTiming && p.dbg) { p.dbg[blockIdx.x * 16 + 13] = c_wait; p.dbg[blockIdx.x * 16 + 14] = clock64() - c_t0; }
     }
+  } else if (warp >= C::WARP_ISSUER_CS + 1) {
+    // (a fourth non-epilogue warp: registers are allocated to warps in fours, so it is free; it has nothing to do)
   } else {
     // ------------------------------------------------------------ epilogue groups
     const int g = warp >> 2;
@@ -437,24 +479,54 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
     const uint32_t swz = static_cast<uint32_t>(trow & 7);
     const uint8_t* cbm = smem_gen + C::SMEM_CBM;
     uint32_t gbase = 0, n_bias = 0, n_cs = 0;
-    bool pending = false;
+    bool pending = false, pend_valid = false;
     int pend_j = 0;
+    // cycle counters of one thread (timing builds, MUSCLE_PAIR_TIMING=1): [0] item wait, [1] column tile, [2] S,
+    // [3] column-sum drain, [4] tcgen05.ld, [5] math + e-tile stores, [6] own units, [7] off-diagonal own units
+    const bool timing = kPairTiming && (p.dbg != nullptr) && warp == 0 && lane == 0;
+    long long tacc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // [8] e-tile fence + publish
+    long long t_mark = timing ? clock64() : 0;
+    auto lap = [&](int i) { if (timing) { const long long t = clock64(); tacc[i] += t - t_mark; t_mark = t; } };
     auto drain = [&]() {   // column sums of this group's previous off-diagonal unit -> rowsum of its column pixels
-      mbar_wait(cs_full(g), n_cs & 1);
+      sym_wait_epi(cs_full(g), n_cs & 1);
       ++n_cs;
       tc_fence_after();
       const float cs = __uint_as_float(tmem_ld1(tmem + lane_addr + C::CS_COL + 16 * g));
       tmem_wait_ld();
       tc_fence_before();
-      if (cs != 0.f) atomicAdd(p.rowsum + static_cast<size_t>(pend_j) * 128 + trow, cs);
+      // (a masked column keeps 2^-shift of its terms: pixels outside the loss are skipped explicitly)
+      if (cs != 0.f && pend_valid) atomicAdd(p.rowsum + static_cast<size_t>(pend_j) * 128 + trow, cs);
       pending = false;
     };
     for (uint32_t it = 0;; ++it) {
       mbar_wait(q_full, it & 1);
+      lap(0);
       const uint32_t n_u = info[4 * (it & 1) + 0];
       if (n_u == ITEM_END) break;
       const int n = static_cast<int>(n_u);
       const int rb = static_cast<int>(info[4 * (it & 1) + 1]);
+      if (g == 0) {
+        // row tile: staging buffer (128-B-swizzled [128 rows][64] panels) -> TMEM, lane = row, column = k / 2
+        const uint32_t src = q_smem + trow * 128;
+#pragma unroll
+        for (int pnl = 0; pnl < D / 64; ++pnl) {
+          uint32_t rv[2][16];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t addr = src + pnl * C::PANEL_BYTES + ((static_cast<uint32_t>(j) ^ swz) << 4);
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(rv[j >> 2][(j & 3) * 4]), "=r"(rv[j >> 2][(j & 3) * 4 + 1]),
+                           "=r"(rv[j >> 2][(j & 3) * 4 + 2]), "=r"(rv[j >> 2][(j & 3) * 4 + 3])
+                         : "r"(addr));
+          }
+          tmem_st16(tmem + lane_addr + C::R_COL + pnl * 32, rv[0]);
+          tmem_st16(tmem + lane_addr + C::R_COL + pnl * 32 + 16, rv[1]);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(r_full);
+      }
       __syncwarp();
       if (lane == 0) mbar_arrive(q_empty);
       const int row = rb * 128 + trow;
@@ -466,9 +538,9 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
       uint64_t racc[4] = {0ull, 0ull, 0ull, 0ull};
       for (int k = 0; k < n; ++k) {
         const uint32_t gk = gbase + k;
-        const int st = static_cast<int>(gk % NST);
+        const int st = static_cast<int>(gk % C::NBR);        // slot of the bits / record ring
         if (gk % NG != static_cast<uint32_t>(g)) continue;
-        {   // the stage is being (or has been) filled for THIS unit: only then is the phase parity unambiguous
+        {   // the slot is being (or has been) filled for THIS unit: only then is the phase parity unambiguous
           uint32_t spins = 0;
           while (info[8 + 4 * st + 2] != gk) {
             if (++spins > (1u << 26)) {
@@ -477,11 +549,13 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
             }
           }
         }
-        mbar_wait(k_full(st), (gk / NST) & 1);
+        sym_wait_epi(b_full(st), (gk / C::NBR) & 1);
+        lap(1);
         const int b = static_cast<int>(gk % NB);
         const uint32_t tor_c = info[8 + 4 * st];
         const int j = static_cast<int>(info[8 + 4 * st + 1]);
         const bool diag = (j == rb);
+        const bool col_valid = reinterpret_cast<const uint32_t*>(smem_gen + C::SMEM_BITS + st * 512)[trow] != 0u;
         // no element masked, in either direction: disjoint class sets, every column and every row in the loss
         const bool full = (tor_r & tor_c & TOR_CLASSES) == 0u && ((tor_c | tor_r) & TOR_INVALID) == 0u;
         const int mask = full ? MASK_NONE : (bias_ok ? MASK_BIAS : MASK_SELECT);
@@ -495,13 +569,12 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
           ++n_bias;
           asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
         }
-        if (mask != MASK_SELECT) {   // no class bits left to read: the stage is only the tensor pipe's now
-          __syncwarp();
-          if (lane == 0) mbar_arrive(k_empty(st));
-        }
-        mbar_wait(s_full(b), (gk / NB) & 1);
+        sym_wait_epi(s_full(b), (gk / NB) & 1);
+        lap(2);
         tc_fence_after();
         if (!diag && pending) drain();    // the e tile is about to be overwritten: its product must be done
+        lap(3);
+        if (timing) { ++tacc[6]; tacc[7] += diag ? 0 : 1; }
         const uint8_t* my_cb = rbits ? cb + my_slot * 512 : cbm;
 #pragma unroll 1
         for (int h = 0; h < 2; ++h) {
@@ -512,6 +585,7 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
           tmem_ld32(s_addr, v[0]);
           tmem_ld32(s_addr + 32, v[1]);
           tmem_wait_ld();
+          lap(4);
           if (h == 1) {   // S is in registers: hand the buffer back before the math
             tc_fence_before();
             __syncwarp();
@@ -529,17 +603,16 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
           } else {
             sym_half_math<POLY, MASK_SELECT, true>(v, e_row, swz, bsm, cb, qmask, a, racc);
           }
+          lap(5);
         }
         if (!diag) {
           fence_proxy_async_smem();     // the e tile is read by the tensor pipe (async proxy)
           __syncwarp();
           if (lane == 0) mbar_arrive(e_full(g));
+          lap(8);
           pending = true;
           pend_j = j;
-        }
-        if (mask == MASK_SELECT) {
-          __syncwarp();
-          if (lane == 0) mbar_arrive(k_empty(st));
+          pend_valid = col_valid;
         }
       }
       {
@@ -552,11 +625,16 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
       gbase += n;
     }
     if (pending) drain();
+    if (timing) {
+      unsigned long long* d = p.dbg + blockIdx.x * 16;
+      for (int i = 0; i < 7; ++i) d[i] = static_cast<unsigned long long>(tacc[i]);
+      d[15] = static_cast<unsigned long long>(tacc[8]);
+    }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == C::WARP_ISSUER) tmem_dealloc(tmem, 512);
+  if (warp == C::WARP_ISSUER_S) tmem_dealloc(tmem, 512);
 }
 
 }  // namespace mb200

@@ -115,6 +115,30 @@ def dense_infonce(ehat_q, cls_q, ehat_k=None, cls_k=None, temperature=0.1,
     return total / n_valid
 
 
+def dense_infonce_per_class(ehat, cls, temperature=0.1, query_idx=None):
+    """The composition of SURVEY.md §8c written exactly the way the reference primitive would be
+    called: ONE ``info_nce(E[cls==c], E[cls==c], E[cls!=c], T, 'none')`` per class present
+    (src/loss_multilabel.py:9-21), i.e. only cross-class pairs are ever multiplied; the per-query
+    losses are concatenated and averaged over the valid queries.  ``query_idx`` restricts the
+    QUERIES to a sample (keys and prototypes stay the whole batch): the result is then the sum of the
+    sampled queries' losses / n_valid — the bounded-sample form bench.py's CPU arm times."""
+    valid = cls >= 0
+    n_valid = valid.sum()
+    in_sample = None
+    if query_idx is not None:
+        in_sample = torch.zeros_like(valid)
+        in_sample[query_idx] = True
+    total = ehat.new_zeros(())
+    for c in torch.unique(cls[valid]).tolist():
+        sel = cls == c
+        q_sel = sel if in_sample is None else (sel & in_sample)
+        if not bool(q_sel.any()):
+            continue
+        neg = valid & ~sel
+        total = total + info_nce(ehat[q_sel], ehat[sel], ehat[neg], temperature, reduction="none").sum()
+    return total / n_valid
+
+
 def dense_infonce_from_features(x, cls, temperature=0.1, num_classes=None):
     """Full op as the product exposes it: x [N,D] raw embeddings -> normalise -> dense_infonce."""
     return dense_infonce(l2_normalize_pixels(x), cls, temperature=temperature, num_classes=num_classes)

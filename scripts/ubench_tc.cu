@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(128, 1) mma_bench(int reps, long long* out) {
   __syncthreads();
   if (warp == 1) {
     if (elect_one()) {
-      const int N = (mode == 0 || mode >= 4) ? 64 : (mode == 3 ? 256 : 128);
+      const int N = (mode == 0 || (mode >= 4 && mode <= 6)) ? 64 : (mode == 3 ? 256 : 128);
       const uint32_t idesc_ts64 = umma_idesc_bf16(128, 64, 0, 0);
       const uint32_t idesc_ss = umma_idesc_bf16(128, N, 0, 0);
       const uint32_t idesc_ts = umma_idesc_bf16(128, 128, 0, 1);
@@ -40,6 +40,18 @@ __global__ void __launch_bounds__(128, 1) mma_bench(int reps, long long* out) {
           const uint32_t off = (kk >> 2) * 16384 + (kk & 3) * 32;
           if (mode == 2)
             mma_ts(tmem + 256, tmem + kk * 8, umma_desc_sw128(b_smem + kk * 2048, 16384, 1024), idesc_ts, 1);
+          else if (mode == 7)   // column sums: A = e tile MN-major (M contiguous) from smem, B = ones K-major, N = 16
+            mma_ss(tmem + 384, umma_desc_sw128(a_smem + kk * 2048, 16384, 1024), umma_desc_sw128(b_smem, 16, 1024), umma_idesc_bf16(128, 16, 1, 0), kk > 0);
+          else if (mode == 8)   // the same with N = 64
+            mma_ss(tmem + 384, umma_desc_sw128(a_smem + kk * 2048, 16384, 1024), umma_desc_sw128(b_smem, 16, 1024), umma_idesc_bf16(128, 64, 1, 0), kk > 0);
+          else if (mode == 9)   // column sums the other way round: A = ones K-major, B = e tile MN-major, N = 128
+            mma_ss(tmem + 384, umma_desc_sw128(b_smem, 16, 1024), umma_desc_sw128(a_smem + kk * 2048, 16384, 1024), umma_idesc_bf16(128, 128, 0, 1), kk > 0);
+          else if (mode == 10)  // A = ones K-major M = 64, B = e tile MN-major, N = 128
+            mma_ss(tmem + 384, umma_desc_sw128(b_smem, 16, 1024), umma_desc_sw128(a_smem + kk * 2048, 16384, 1024), umma_idesc_bf16(64, 128, 0, 1), kk > 0);
+          else if (mode == 11)  // K-major A, N = 16 (is a narrow N slow by itself?)
+            mma_ss(tmem + 384, umma_desc_sw128(a_smem + off, 16, 1024), umma_desc_sw128(b_smem, 16, 1024), umma_idesc_bf16(128, 16, 0, 0), kk > 0);
+          else if (mode == 12)  // A from TMEM (ones), B = e tile MN-major N = 128
+            mma_ts(tmem + 384, tmem + 8, umma_desc_sw128(a_smem + kk * 2048, 16384, 1024), umma_idesc_bf16(128, 128, 0, 1), kk > 0);
           else if (mode == 4)   // S from a TMEM-resident row tile: A in TMEM, B K-major N=64
             mma_ts(tmem + 256, tmem + kk * 8, umma_desc_sw128(b_smem + off, 16, 1024), idesc_ts64, kk > 0);
           else if (mode == 5)   // SS N=64, consecutive MMAs on alternating accumulators
@@ -123,9 +135,16 @@ int main() {
   cudaFuncSetAttribute(mma_bench<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
   cudaFuncSetAttribute(mma_bench<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
   cudaFuncSetAttribute(mma_bench<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-  const char* names[7] = {"SS M128 N64 K16", "SS M128 N128 K16", "TS M128 N128 K16", "SS M128 N256 K16",
-                          "TS M128 N64 Kmaj", "SS N64 alt-acc", "TS64x8+TS128x4 /8"};
-  for (int mode = 0; mode < 7; ++mode) {
+  cudaFuncSetAttribute(mma_bench<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  cudaFuncSetAttribute(mma_bench<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  cudaFuncSetAttribute(mma_bench<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  cudaFuncSetAttribute(mma_bench<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  cudaFuncSetAttribute(mma_bench<11>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  cudaFuncSetAttribute(mma_bench<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  const char* names[13] = {"SS M128 N64 K16", "SS M128 N128 K16", "TS M128 N128 K16", "SS M128 N256 K16",
+                          "TS M128 N64 Kmaj", "SS N64 alt-acc", "TS64x8+TS128x4 /8", "SS A-MNmaj N16", "SS A-MNmaj N64",
+                          "SS ones x B-MNmaj N128", "SS M64 ones x B-MN N128", "SS A-Kmaj N16", "TS ones x B-MNmaj N128"};
+  for (int mode = 0; mode < 13; ++mode) {
     for (int grid : {1, 148}) {
       const int reps = 512;
       switch (mode) {
@@ -135,7 +154,13 @@ int main() {
         case 3: mma_bench<3><<<grid, 128, 100 * 1024>>>(reps, out); break;
         case 4: mma_bench<4><<<grid, 128, 100 * 1024>>>(reps, out); break;
         case 5: mma_bench<5><<<grid, 128, 100 * 1024>>>(reps, out); break;
-        default: mma_bench<6><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        case 6: mma_bench<6><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        case 7: mma_bench<7><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        case 8: mma_bench<8><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        case 9: mma_bench<9><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        case 10: mma_bench<10><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        case 11: mma_bench<11><<<grid, 128, 100 * 1024>>>(reps, out); break;
+        default: mma_bench<12><<<grid, 128, 100 * 1024>>>(reps, out); break;
       }
       cudaError_t e = cudaDeviceSynchronize();
       if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }

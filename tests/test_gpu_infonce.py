@@ -116,7 +116,10 @@ def test_upstream_gradient_is_applied_in_backward(M):
         c = cls.reshape(-1).cuda() if xa.dim() == 2 else cls.cuda()
         M.dense_infonce(xa, c, 0.1, 21).backward()
         (2.5 * M.dense_infonce(xb, c, 0.1, 21)).backward()
-        assert torch.allclose(xb.grad, 2.5 * xa.grad, rtol=1e-5, atol=1e-9)
+        # two separate forward passes: the row sums are fp32 atomics (order varies from run to run), so the
+        # gradients agree to fp32 summation noise, not bit for bit
+        assert torch.allclose(xb.grad, 2.5 * xa.grad, rtol=1e-3, atol=1e-8)
+        assert _cos(xb.grad, 2.5 * xa.grad) >= 0.9999999
     # the fused C entry point and the fwd / bwd pair agree (row sums are float atomics: not bit for bit)
     import muscle_b200._lib as L
     lib = L.load()
