@@ -19,16 +19,16 @@
 //     the streams are independent (S(k) needs its column tile and a free S buffer; CS(k) the group's e tile);
 //   * a group drains the column sums of its unit k while it already works on unit k+NG (deferred, so
 //     the column-sum product's latency is never waited for);
-//   * the column-tile ring (2 stages at D = 128: the e tiles need the room) is private to the producer and
-//     the S issuer: a stage is free again as soon as its S product has completed, so the look-ahead lives
-//     in the NB TMEM buffers, not in shared memory.  What an epilogue group needs of a column tile -- its
-//     class bits (512 B) and the unit record (class union, tile index) -- travels through a separate ring
-//     of NBR = 16 slots with barriers of its own.  A slot is reused 16 units later: by then S(g+14) has
-//     completed, which needs the S buffer of unit g+11 back, so every group is past unit g (no "empty"
-//     barrier).  A group has not seen the previous phase of the slot it waits for (PairCfg's static_assert
-//     explains that hazard: a wait for phase n+1 is also satisfied while phase n-1 is the last complete
-//     one), so the producer publishes the unit number a slot is filled for before it arms the barrier,
-//     and a group first waits for ITS unit number.
+//   * the column-tile ring (2 stages at D = 128: the e tiles need the room) is shorter than the number of
+//     groups, so a group has not seen the previous phase of the stage it waits for (PairCfg's
+//     static_assert explains the hazard: a wait for phase n+1 is also satisfied while phase n-1 is the
+//     last complete one).  The producer therefore publishes the unit number a stage is being filled
+//     for (seq word, written before the barrier is armed) and a group first waits for ITS unit number.
+//     A stage is released by its S product AND by the owning group once it has taken what it needs of
+//     the class bits (measured on B200: making the stage private to producer and S issuer, with the bits
+//     in a deeper ring of their own, was 8-25 % slower -- the coupling keeps the groups in step);
+//   * the single-thread roles (producer, issuers) poll their barriers with test_wait instead of parking
+//     in try_wait (MB_SYM_SPIN): same mean time, but without the occasional 20 % slower launch;
 //   * S = R C^T takes R from TENSOR memory (tcgen05.mma with A in TMEM): group 0 copies the row tile from
 //     its staging buffer into TMEM once per work item, and the S products then read only the column tile
 //     from shared memory.  Shared-memory bandwidth is what bounds this pass (per unit: 32 KB TMA write,
@@ -68,12 +68,12 @@ struct SymCfg {
   static constexpr int SMEM_K = SMEM_Q + TILE_BYTES;
   static constexpr int SMEM_E = SMEM_K + NST * TILE_BYTES;
   static constexpr int SMEM_ONES = SMEM_E + NG * E_BYTES;  // bf16 1.0 x 1024 (B operand of the column-sum product)
-  static constexpr int NBR = 16;                           // ring of class-bit vectors + unit records (see below)
+  static constexpr int NBR = NST;                          // class bits and unit record travel with the column-tile stage
   static constexpr int SMEM_BITS = SMEM_ONES + 2048;
   static constexpr int SMEM_CB = SMEM_BITS + NBR * 512;    // exponent-shift vectors [NG][2][BIAS_SLOTS][128]
   static constexpr int SMEM_CBM = SMEM_CB + 2 * NG * BIAS_SLOTS * 512;   // one all-masked vector (rows outside the loss)
   static constexpr int SMEM_BAR = SMEM_CBM + 512;
-  static constexpr int NBAR = 2 * NST + 2 + 2 * NB + 2 * NG + 1 + NBR;
+  static constexpr int NBAR = 2 * NST + 2 + 2 * NB + 2 * NG + 1;
   static constexpr int SMEM_INFO = SMEM_BAR + NBAR * 8;    // item headers [2][4], unit records [NBR][4]
   static constexpr int SMEM_TMEMPTR = SMEM_INFO + (8 + 4 * NBR) * 4;
   static constexpr int SMEM_BYTES = SMEM_TMEMPTR + 16 + 1024;
@@ -255,9 +255,8 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
   auto e_full = [&](int g) { return bar0 + 8u * (2 * NST + 2 + 2 * NB + g); };
   auto cs_full = [&](int g) { return bar0 + 8u * (2 * NST + 2 + 2 * NB + NG + g); };
   const uint32_t r_full = bar0 + 8u * (2 * NST + 2 + 2 * NB + 2 * NG);   // row tile copied into TMEM
-  auto b_full = [&](int sl) { return bar0 + 8u * (2 * NST + 2 + 2 * NB + 2 * NG + 1 + sl); };   // class bits of slot sl landed
   volatile uint32_t* info = reinterpret_cast<volatile uint32_t*>(smem_gen + C::SMEM_INFO);
-  // info[4*(it&1) + {0,1,2}]: live units, row block of item `it`, first unit is the diagonal one; info[8 + 4 sl + {0,1,2}]: class union and index of the column tile of ring slot sl, number of the unit it is filled for
+  // info[4*(it&1) + {0,1,2}]: live units, row block of item `it`, first unit is the diagonal one; info[8 + 4 st + {0,1,2}]: class union and index of the stage's column tile, number of the unit it is filled for
   volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(smem_gen + C::SMEM_TMEMPTR);
   __shared__ uint2 ulist_sm[32];           // producer warp: (class union, index) of the next column tiles to load
 
@@ -267,7 +266,7 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NST; ++s) {
       mbar_init(k_full(s), 1);
-      mbar_init(k_empty(s), 1);          // S product done
+      mbar_init(k_empty(s), 1 + 4);      // S product done + the four warps of the group that owns the unit
     }
     mbar_init(q_full, 1);
     mbar_init(q_empty, 2 + 4 * NG);      // S issuer (last S of the item) + column-sum issuer + every epilogue warp
@@ -280,7 +279,6 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
       mbar_init(cs_full(g), 1);
     }
     mbar_init(r_full, 4);
-    for (int sl = 0; sl < C::NBR; ++sl) mbar_init(b_full(sl), 1);
     fence_barrier_init();
   }
   // constants in shared memory: the ones tile and the all-masked shift vector
@@ -372,14 +370,12 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
             { const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
               sym_wait_role(k_empty(st), ((g / NST) & 1) ^ 1);
               if (kPairTiming && p.dbg) p_wait += clock64() - w0; }
-            mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES);
+            info[8 + 4 * st] = ent.x;
+            info[8 + 4 * st + 1] = ent.y;
+            info[8 + 4 * st + 2] = g;
+            mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES + 512);
             tma_load_3d(k_smem + st * C::TILE_BYTES, &tm_row, k_full(st), 0, static_cast<int>(ent.y) * 128, 0);
-            const int sl = static_cast<int>(g % C::NBR);      // (after the stage wait: see the ring's reuse argument)
-            info[8 + 4 * sl] = ent.x;
-            info[8 + 4 * sl + 1] = ent.y;
-            info[8 + 4 * sl + 2] = g;
-            mbar_arrive_expect_tx(b_full(sl), 512);
-            bulk_load_1d(bits_smem + sl * 512, p.bits_col + static_cast<size_t>(ent.y) * 128, 512, b_full(sl));
+            bulk_load_1d(bits_smem + st * 512, p.bits_col + static_cast<size_t>(ent.y) * 128, 512, k_full(st));
           }
         }
         gcnt += last - first;
@@ -538,9 +534,9 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
       uint64_t racc[4] = {0ull, 0ull, 0ull, 0ull};
       for (int k = 0; k < n; ++k) {
         const uint32_t gk = gbase + k;
-        const int st = static_cast<int>(gk % C::NBR);        // slot of the bits / record ring
+        const int st = static_cast<int>(gk % NST);
         if (gk % NG != static_cast<uint32_t>(g)) continue;
-        {   // the slot is being (or has been) filled for THIS unit: only then is the phase parity unambiguous
+        {   // the stage is being (or has been) filled for THIS unit: only then is the phase parity unambiguous
           uint32_t spins = 0;
           while (info[8 + 4 * st + 2] != gk) {
             if (++spins > (1u << 26)) {
@@ -549,7 +545,7 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
             }
           }
         }
-        sym_wait_epi(b_full(st), (gk / C::NBR) & 1);
+        sym_wait_epi(k_full(st), (gk / NST) & 1);
         lap(1);
         const int b = static_cast<int>(gk % NB);
         const uint32_t tor_c = info[8 + 4 * st];
@@ -568,6 +564,10 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
             cbw[s * 128] = (kb & ~(rem & (0u - rem))) ? -a : -a - p.mask_shift;
           ++n_bias;
           asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+        }
+        if (mask != MASK_SELECT) {   // no class bits left to read: the stage is only the tensor pipe's now
+          __syncwarp();
+          if (lane == 0) mbar_arrive(k_empty(st));
         }
         sym_wait_epi(s_full(b), (gk / NB) & 1);
         lap(2);
@@ -613,6 +613,10 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
           pending = true;
           pend_j = j;
           pend_valid = col_valid;
+        }
+        if (mask == MASK_SELECT) {
+          __syncwarp();
+          if (lane == 0) mbar_arrive(k_empty(st));
         }
       }
       {
