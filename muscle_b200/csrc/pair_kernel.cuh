@@ -47,7 +47,16 @@
 #endif
 #include "ptx.cuh"
 
+// -DMB_PAIR_SPIN=0: the single-thread roles (producer, issuer) park in try_wait instead of polling with test_wait
+#ifndef MB_PAIR_SPIN
+#define MB_PAIR_SPIN 1
+#endif
+
 namespace mb200 {
+
+__device__ __forceinline__ void pair_wait_role(uint32_t bar, uint32_t parity) {
+  if (MB_PAIR_SPIN) mbar_wait_spin(bar, parity); else mbar_wait(bar, parity);
+}
 
 constexpr bool kPairTiming = MB_PAIR_TIMING != 0;
 
@@ -318,6 +327,7 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
   // info[4*(it&1) + {0,1,2}]: live tiles, row block, slot of item `it`; info[8+st]: tor of the stage's column tile
   volatile uint32_t* tmem_ptr_smem =
       reinterpret_cast<volatile uint32_t*>(smem_gen + C::SMEM_TMEMPTR);
+  __shared__ uint2 ulist_sm[32];           // producer warp: (class union, index) of the next column tiles to load
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -416,19 +426,28 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           // skip whole words that end before the share starts
           const uint32_t cnt = __popc(live);
           if (li + cnt <= a) { li += cnt; continue; }
-          while (live != 0u && li < e) {
-            const int jj = __ffs(live) - 1;
-            live &= live - 1u;
-            const uint32_t tcj = __shfl_sync(0xffffffffu, tc, jj);
-            if (li++ < a) continue;
-            const int j = j0 + jj;
-            const int st = gcnt % NST;
-            if (lane == 0) {
+          // The lanes whose tile is one of the CTA's units write it into a 32-entry list (one step for up to 32
+          // units); lane 0 then only waits for a free stage and issues the copies.  (Walking the ballot word bit
+          // by bit on the issuing path cost ~900 cycles of this warp per unit: it shares its scheduler with busy
+          // epilogue warps, and the issuer waited ~450 cycles per unit for column tiles.)
+          const uint32_t rank = __popc(live & ((1u << lane) - 1u));
+          const uint32_t idx = li + rank;                         // live index of this lane's tile in the row block
+          const uint32_t first = li > a ? li : a;
+          const uint32_t last = (li + cnt < e) ? li + cnt : e;    // units [first, last) of the row block come from this word
+          if (((live >> lane) & 1u) && idx >= first && idx < last)
+            ulist_sm[idx - first] = make_uint2(tc, static_cast<uint32_t>(j0 + lane));
+          __syncwarp();
+          if (lane == 0) {
+            for (uint32_t t = 0; t < last - first; ++t) {
+              const uint2 ent = ulist_sm[t];
+              const uint32_t g = gcnt + t;
+              const int st = static_cast<int>(g % NST);
+              const int j = static_cast<int>(ent.y);
               { const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
-                mbar_wait(k_empty(st), ((gcnt / NST) & 1) ^ 1);
+                pair_wait_role(k_empty(st), ((g / NST) & 1) ^ 1);
                 if (kPairTiming && p.dbg) p_wait += clock64() - w0; }
-              info[8 + st] = tcj;
-              if ((kPairTiming && (p.dbg_flags & 1)) && gcnt >= static_cast<uint32_t>(NST)) {
+              info[8 + st] = ent.x;
+              if ((kPairTiming && (p.dbg_flags & 1)) && g >= static_cast<uint32_t>(NST)) {
                 mbar_arrive(k_full(st));
               } else {
                 mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES + 512 + (MODE == MODE_GRAD ? 512 : 0));
@@ -440,8 +459,10 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
                                k_full(st));
               }
             }
-            ++gcnt;
           }
+          gcnt += last - first;
+          li += cnt;
+          __syncwarp();
         }
         u = U0 + e;
         ++it;
@@ -475,11 +496,11 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
           const int st = static_cast<int>(gk % NST);
           const int b = static_cast<int>(gk % NB);
           { const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
-            mbar_wait(k_full(st), (gk / NST) & 1);
+            pair_wait_role(k_full(st), (gk / NST) & 1);
             if (kPairTiming && p.dbg) i_kfull += clock64() - w0; }
           if (MODE == MODE_ROWSUM) {   // the buffer's previous unit has been read out
             const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
-            mbar_wait(t_full(b), ((gk / NB) & 1) ^ 1);
+            pair_wait_role(t_full(b), ((gk / NB) & 1) ^ 1);
             if (kPairTiming && p.dbg) i_tfull += clock64() - w0;
           }   // MODE_GRAD: the G MMA of that unit was issued earlier and the pipe runs in order
           tc_fence_after();
@@ -502,14 +523,14 @@ pair_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ 
         } else {
           const int pro = n < NB ? n : NB;
           for (int k = 0; k < pro; ++k) issue_S(k);
-          mbar_wait(acc_empty, (it & 1) ^ 1);   // the previous item's G has been read out
+          pair_wait_role(acc_empty, (it & 1) ^ 1);   // the previous item's G has been read out
           tc_fence_after();
           for (int k = 0; k < n; ++k) {
             const uint32_t gk = gbase + k;
             const int st = static_cast<int>(gk % NST);
             const int b = static_cast<int>(gk % NB);
             { const long long w0 = (kPairTiming && p.dbg) ? clock64() : 0;
-              mbar_wait(t_full(b), (gk / NB) & 1);
+              pair_wait_role(t_full(b), (gk / NB) & 1);
               if (kPairTiming && p.dbg) i_tfull += clock64() - w0; }
             tc_fence_after();
             const uint32_t b_base = k_smem + st * C::TILE_BYTES;
