@@ -61,6 +61,30 @@ def gen_dense_infonce(src):
         loss = torch.cat(per_query).mean()
         gx, = torch.autograd.grad(loss, x)
         out[tag] = dict(x=x.detach(), cls=cls, loss=loss.detach(), gx=gx)
+    # the same composition at the projection dims the tensor-pipe passes take (so that the CUDA path itself,
+    # not only the oracle, is checked against the reference primitive): x in fp32, reference run in fp32 and fp64
+    for d in (64, 128):
+        g = torch.Generator().manual_seed(23 + d)
+        b, h, w, c = 3, 14, 15, 6
+        cls = _blob_classes(b, h, w, c, g, smooth=5).reshape(-1)
+        cls[torch.rand(cls.shape, generator=g) < 0.04] = -1
+        x32 = torch.randn(b * h * w, d, generator=g)
+        x32 = x32 + 0.7 * torch.randn(c, d, generator=g)[cls.clamp_min(0)]
+        rec = dict(x=x32, cls=cls, num_classes=c)
+        for dt, tag in ((torch.float32, "f32"), (torch.float64, "f64")):
+            x = x32.to(dt).requires_grad_()
+            e = F.normalize(x, dim=1)
+            valid = cls >= 0
+            per_query = []
+            for ci in sorted(set(cls[valid].tolist())):
+                sel = cls == ci
+                per_query.append(src.loss_multilabel.info_nce(e[sel], e[sel], e[valid & ~sel], temperature=0.1,
+                                                              reduction="none"))
+            loss = torch.cat(per_query).mean()
+            gx, = torch.autograd.grad(loss, x)
+            rec["loss_" + tag] = loss.detach()
+            rec["gx_" + tag] = gx
+        out["d%d" % d] = rec
     return out
 
 
@@ -217,11 +241,167 @@ def gen_fieldloss(src):
                 pos=pos, out_idx_0_14=out_i, in_idx_0_14=in_i, gate_false=(loss0 is False), big_k_is_zero=(not torch.is_tensor(loss1) and loss1 == 0))
 
 
+def _reference_functions(rel_path, names):
+    """Compiles the named top-level functions of a reference SCRIPT (which cannot be imported: it pulls
+    in data / cv2 / tensorboardX at module level) from where it lies, and returns them."""
+    import ast
+    path = os.path.join(reference_loader.REFERENCE_ROOT, rel_path)
+    with open(path) as f:
+        text = f.read()
+    tree = ast.parse(text)
+    keep = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in names]
+    assert len(keep) == len(names), (rel_path, names)
+    mod = ast.Module(body=keep, type_ignores=[])
+    ns = {"torch": torch, "F": F, "np": np}
+    exec(compile(mod, path, "exec"), ns)
+    return [ns[n] for n in names]
+
+
+def _reference_lines(rel_path, first, last):
+    """Source lines [first, last] (1-based) of a reference file, dedented, for exec in a prepared namespace."""
+    import textwrap
+    path = os.path.join(reference_loader.REFERENCE_ROOT, rel_path)
+    with open(path) as f:
+        lines = f.readlines()
+    return compile(textwrap.dedent("".join(lines[first - 1:last])), path + ":%d-%d" % (first, last), "exec")
+
+
+def gen_cam_norms(src):
+    """train_mcl.py:21-36 (cam_maxnorm, cam_softmaxnorm) and the model's own variant src/MuSCLe.py:202-211."""
+    cam_maxnorm, cam_softmaxnorm = _reference_functions("train_mcl.py", ["cam_maxnorm", "cam_softmaxnorm"])
+    g = torch.Generator().manual_seed(31)
+    x = torch.randn(3, 21, 13, 11, generator=g)
+    x[0, 4] = 0.0                      # an all-zero plane: min == max
+    x[1, 7] = -x[1, 7].abs()           # an all-negative plane: relu -> all zero
+    out = {}
+    for name, fn in (("maxnorm", cam_maxnorm), ("softmaxnorm", cam_softmaxnorm)):
+        xi = x.clone().requires_grad_()
+        y = fn(xi)
+        go = torch.randn(y.shape, generator=g)
+        gx, = torch.autograd.grad((y * go).sum(), xi)
+        out[name] = dict(y=y.detach(), go=go, gx=gx)
+    out["x"] = x
+    return out
+
+
+def gen_er_loss(src):
+    """The ER loss of train_mcl.py:175-188 with the up-sampling of src/MuSCLe.py:256-257 in front of it: the
+    reference's own source lines are executed on seeded stand-ins for the model outputs."""
+    cam_softmaxnorm, = _reference_functions("train_mcl.py", ["cam_softmaxnorm"])
+    g = torch.Generator().manual_seed(37)
+    n, h, w, H, W = 3, 7, 9, 28, 36
+    cams_small = torch.relu(torch.randn(n, 21, h, w, generator=g))
+    SGC_small = torch.relu(torch.randn(n, 21, h, w, generator=g) + 0.3).requires_grad_()
+    label = torch.zeros(n, 20)
+    label[0, [1, 14]] = 1
+    label[1, [14]] = 1
+    label[2, [3, 7, 19]] = 1
+    ns = dict(torch=torch, F=F, cams=cams_small, SGC=SGC_small, H=H, W=W, label=label, cam_softmaxnorm=cam_softmaxnorm)
+    exec(_reference_lines("src/MuSCLe.py", 256, 257), ns)            # cams, SGC up-sampled (align_corners=True)
+    ns["raw_cams"], ns["raw_sgcs"] = ns["cams"], ns["SGC"]
+    up_cams, up_sgc = ns["cams"].detach().clone(), ns["SGC"].detach().clone()
+    exec(_reference_lines("train_mcl.py", 167, 170), ns)             # label_with_bg
+    exec(_reference_lines("train_mcl.py", 175, 178), ns)             # cams / sgcs normalised, valid_channel
+    exec(_reference_lines("train_mcl.py", 185, 188), ns)             # label mask, top-k mean
+    loss_er = ns["loss_er"]
+    g_small, = torch.autograd.grad(loss_er, SGC_small)
+    return dict(cams_small=cams_small, sgc_small=SGC_small.detach(), label=label, size=(H, W), up_cams=up_cams,
+                up_sgc=up_sgc, valid_channel=ns["valid_channel"], k=int(0.2 * ns["valid_channel"] * H * W),
+                loss_er=loss_er.detach(), g_sgc_small=g_small)
+
+
+def gen_cls_losses(src):
+    """FocalLoss, Log_Sum_Exp_Pairwise_Loss (src/loss_multilabel.py:24-33,68-91) and the soft-margin term, composed
+    as train_mcl.py:180-183 composes them."""
+    g = torch.Generator().manual_seed(41)
+    logits = (torch.randn(6, 21, generator=g) * 2).requires_grad_()
+    label = (torch.rand(6, 20, generator=g) < 0.15).float()
+    label[0] = 0
+    label[0, 14] = 1
+    import torch.nn as nn
+    ns = dict(torch=torch, logits=logits, label=label, criterion1=src.loss_multilabel.FocalLoss(),
+              criterion2=src.loss_multilabel.Log_Sum_Exp_Pairwise_Loss, criterion3=nn.MultiLabelSoftMarginLoss())
+    exec(_reference_lines("train_mcl.py", 180, 183), ns)
+    out = dict(logits=logits.detach(), label=label)
+    for name in ("loss_focal", "loss_softmargin", "loss_pair", "loss_cls"):
+        out[name] = ns[name].detach()
+    out["g_logits"], = torch.autograd.grad(ns["loss_cls"], logits)
+    out["pair_rows"] = src.loss_multilabel.Log_Sum_Exp_Pairwise_Loss(torch.sigmoid(logits[:, 1:]), label).detach()
+    return out
+
+
+def gen_decoder_tail(src):
+    """The decoder tail of src/MuSCLe.py:285-286 (8x bilinear up-sampling of p3_dec, align_corners=True, then the
+    1x1 fuse_dec) feeding FieldLoss the way train_muscle.py:196 does: loss and gradients w.r.t. p3_dec and
+    fuse_dec.  p3_dec is built so that the segmentation has blob structure (boundaries for the loss to sample)."""
+    import torch.nn as nn
+    g = torch.Generator().manual_seed(43)
+    n, ch, hs, ws, up, k, step = 2, 32, 11, 12, 4, 10, 3
+    H, W = hs * up, ws * up
+    torch.manual_seed(43)
+    fuse_dec = nn.Conv2d(ch, 21, 1)
+    label = torch.zeros(n, 20)
+    label[0, [2, 14]] = 1
+    label[1, [14]] = 1
+    label_bg = torch.cat([torch.ones(n, 1), label], 1)
+    noise = F.avg_pool2d(torch.randn(n, 21, hs, ws, generator=g), 5, 1, 2, count_include_pad=False)
+    noise = noise.masked_fill(~label_bg.bool()[:, :, None, None], -30.0) * 4
+    wmat = fuse_dec.weight.detach().reshape(21, ch)
+    target = noise - fuse_dec.bias.detach()[None, :, None, None]
+    p3 = torch.einsum("ck,nkhw->nchw", torch.linalg.pinv(wmat), target) + 0.2 * torch.randn(n, ch, hs, ws, generator=g)
+    p3_dec = p3.clone().requires_grad_()
+    mask = F.interpolate(noise, size=(H, W), mode="bilinear", align_corners=True) * 0.7 + 0.3 * torch.randn(n, 21, H, W, generator=g)
+
+    class _Self:            # the two source lines use self.fuse_dec only
+        pass
+    me = _Self()
+    me.fuse_dec = fuse_dec
+    ns = dict(F=F, self=me, p3_dec=p3_dec, H=H, W=W)
+    exec(_reference_lines("src/MuSCLe.py", 285, 286), ns)
+    seg_map, dense_ft = ns["seg_map"], ns["dense_ft"]
+    crit = src.edge.FieldLoss(sobel_size=5, beta=1e2, k=k)
+    random.seed(91)
+    loss, mag = crit(seg_map, dense_ft, mask, label_bg, step)
+    assert torch.is_tensor(loss), "fixture must exercise the bifilter"
+    gp, gw, gb = torch.autograd.grad(loss, (p3_dec, fuse_dec.weight, fuse_dec.bias), allow_unused=True)
+    return dict(p3_dec=p3_dec.detach(), fuse_w=fuse_dec.weight.detach().clone(), fuse_b=fuse_dec.bias.detach().clone(),
+                mask=mask, label_bg=label_bg, size=(H, W), k=k, step=step, beta=1e2, py_seed=91,
+                seg_map=seg_map.detach(), dense_ft=dense_ft.detach(), loss=loss.detach(), mag=mag,
+                g_p3=gp, g_w=None if gw is None else gw, g_b=None if gb is None else gb)
+
+
+def gen_irn(src):
+    """IRN random walk: src/indexing.py:116-150 (to_transition_matrix, propagate_to_edge; the latter hard-codes
+    .cuda(), made the identity for this CPU run)."""
+    import src.indexing as indexing
+    g = torch.Generator().manual_seed(47)
+    hw = 96
+    a = torch.rand(hw, hw, generator=g)
+    aff = 0.5 * (a + a.t())
+    aff.fill_diagonal_(1.0)
+    out = dict(aff=aff)
+    for times in (1, 4, 8):
+        out["trans_%d" % times] = indexing.to_transition_matrix(aff, beta=10, times=times)
+    out["trans_b2_3"] = indexing.to_transition_matrix(aff, beta=2, times=3)
+    h, w = 12, 14
+    x = torch.rand(3, h, w, generator=g)
+    edge = torch.sigmoid(4 * F.avg_pool2d(torch.randn(1, 1, h, w, generator=g), 3, 1, 1))[0, 0]
+    orig = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    try:
+        rw = indexing.propagate_to_edge(x.clone(), edge.clone(), radius=5, beta=10, exp_times=8)
+    finally:
+        torch.Tensor.cuda = orig
+    out.update(x=x, edge=edge, rw=rw)
+    return out
+
+
 def main():
     src = reference_loader.load()
     os.makedirs(OUT, exist_ok=True)
     jobs = dict(info_nce=gen_info_nce, dense_infonce=gen_dense_infonce, imc=gen_imc, pixpro=gen_pixpro,
-                emd=gen_emd, emd_static=gen_emd_static, heads=gen_heads, fieldloss=gen_fieldloss)
+                emd=gen_emd, emd_static=gen_emd_static, heads=gen_heads, fieldloss=gen_fieldloss, cam_norms=gen_cam_norms,
+                er_loss=gen_er_loss, cls_losses=gen_cls_losses, decoder_tail=gen_decoder_tail, irn=gen_irn)
     only = sys.argv[1:]
     for name, fn in jobs.items():
         if only and name not in only:

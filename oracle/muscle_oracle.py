@@ -594,6 +594,109 @@ def fieldloss_forward(seg_map, dense_ft, mask, label_with_bg, step=7, k=100, bet
 
 
 # --------------------------------------------------------------------------
+# f1  ER loss and the bilinear up-sampling in front of it
+# --------------------------------------------------------------------------
+
+
+def upsample_bilinear(x, size):
+    """src/MuSCLe.py:256-257: F.interpolate(x, size=(H,W), mode='bilinear', align_corners=True).
+    Source coordinate of output pixel o along an axis of n_in -> n_out samples: o*(n_in-1)/(n_out-1)
+    (0 when n_out == 1); linear weights between floor and floor+1 (clamped)."""
+    return F.interpolate(x, size=tuple(size), mode="bilinear", align_corners=True)
+
+
+def er_loss(raw_cams, raw_sgcs, label):
+    """train_mcl.py:175-188: cams = cam_softmaxnorm(raw_cams).detach(), sgcs = cam_softmaxnorm(raw_sgcs) (:175-176);
+    both masked by the image labels incl. background (:185-186); per image the k = int(0.2 * valid_channel * h * w)
+    largest |cams - sgcs| over (class, pixel) with valid_channel = int(label.sum()) over the WHOLE batch (:178),
+    and the mean of all n*k values (:188).  Gradient reaches raw_sgcs only."""
+    n, c, h, w = raw_cams.shape
+    label_with_bg = torch.cat([torch.ones(n, 1, dtype=label.dtype), label], dim=1)
+    cams = cam_softmaxnorm(raw_cams).detach() * label_with_bg[:, :, None, None]
+    sgcs = cam_softmaxnorm(raw_sgcs) * label_with_bg[:, :, None, None]
+    valid_channel = int(label.sum())
+    k = int(0.2 * valid_channel * h * w)
+    diff = torch.abs(cams - sgcs).flatten(1)
+    return torch.topk(diff, k=k, dim=-1)[0].mean()
+
+
+# --------------------------------------------------------------------------
+# f4  classification losses of the MCL stage
+# --------------------------------------------------------------------------
+
+
+def focal_loss(prob, target, gamma=2, alpha=0.5):
+    """src/loss_multilabel.py:68-91 (FocalLoss.forward): pt = p if y else 1-p; -alpha (1-pt)^gamma log(pt + 1e-9),
+    summed over classes, mean over images."""
+    pt = target * prob + (1 - target) * (1 - prob)
+    focal = -alpha * (1.0 - pt) ** gamma * torch.log(pt + 1e-9)
+    return focal.sum(1).mean()
+
+
+def lsep_loss(pred, labels):
+    """src/loss_multilabel.py:24-33 (Log_Sum_Exp_Pairwise_Loss): pos = pred where label == 1 else 0, neg = pred where
+    label == 0 else 0 (so the zeros take part in the pairs); log(1 + mean_{i,j} exp(neg_j - pos_i)) per image -> [N]."""
+    pos = torch.where(labels == 0, torch.zeros_like(pred), pred)
+    neg = torch.where(labels == 1, torch.zeros_like(pred), pred)
+    exp_sub = torch.exp(neg[:, None, :] - pos[:, :, None])
+    return torch.log(1 + exp_sub.sum(dim=(1, 2)) / (exp_sub.shape[1] * exp_sub.shape[2]))
+
+
+def soft_margin_loss(logits, target):
+    """nn.MultiLabelSoftMarginLoss (train_mcl.py:144,181): mean over images of the class-mean of
+    -(y log sigmoid(x) + (1-y) log sigmoid(-x))."""
+    per = -(target * F.logsigmoid(logits) + (1 - target) * F.logsigmoid(-logits))
+    return per.mean(1).mean()
+
+
+def mcl_cls_loss(logits, label):
+    """train_mcl.py:180-183: focal(sigmoid(l[:,1:])) + soft margin(l[:,1:]) + LSEP(sigmoid(l[:,1:])).mean().
+    -> (loss_cls, loss_focal, loss_softmargin, loss_pair)."""
+    fg = logits[:, 1:]
+    prob = torch.sigmoid(fg)
+    lf = focal_loss(prob, label)
+    ls = soft_margin_loss(fg, label)
+    lp = lsep_loss(prob, label).mean()
+    return lp + ls + lf, lf, ls, lp
+
+
+# --------------------------------------------------------------------------
+# f2  decoder tail feeding FieldLoss
+# --------------------------------------------------------------------------
+
+
+def decoder_tail(p3_dec, fuse_w, fuse_b, size):
+    """src/MuSCLe.py:285-286: dense_ft = bilinear up-sampling of p3_dec to (H, W) (align_corners=True);
+    seg_map = fuse_dec(dense_ft), a 1x1 convolution with bias.  -> (seg_map, dense_ft)."""
+    dense_ft = upsample_bilinear(p3_dec, size)
+    seg_map = torch.einsum("kc,nchw->nkhw", fuse_w.reshape(fuse_w.shape[0], -1), dense_ft) + fuse_b[None, :, None, None]
+    return seg_map, dense_ft
+
+
+# --------------------------------------------------------------------------
+# f3  IRN random walk
+# --------------------------------------------------------------------------
+
+
+def to_transition_matrix(affinity_dense, beta, times):
+    """src/indexing.py:116-123: element-wise power beta, columns normalised to sum 1, then squared `times` times
+    (T <- T @ T), i.e. the 2^times-step transition matrix."""
+    scaled = torch.pow(affinity_dense, beta)
+    trans = scaled / scaled.sum(dim=0, keepdim=True)
+    for _ in range(times):
+        trans = trans @ trans
+    return trans
+
+
+def random_walk(x, edge, trans_mat):
+    """src/indexing.py:144-148: rw = (x * (1 - edge)).view(-1, h*w) @ trans_mat -> [C, 1, h, w]."""
+    h, w = x.shape[-2:]
+    xx = x.reshape(-1, h, w) * (1 - edge)
+    rw = xx.reshape(-1, h * w) @ trans_mat
+    return rw.reshape(rw.shape[0], 1, h, w)
+
+
+# --------------------------------------------------------------------------
 # synthetic inputs of the tests: the generator lives beside bench.py (workloads.py); these keep the
 # tests' historical inputs (background channel biased by +0.15, i.e. ~75 % background pixels)
 # --------------------------------------------------------------------------

@@ -170,6 +170,81 @@ def test_fieldloss(golden):
     assert (not torch.is_tensor(loss1)) and loss1 == 0 and g["big_k_is_zero"]
 
 
+@pytest.mark.parametrize("d", [64, 128])
+def test_dense_infonce_composition_at_tensor_core_dims(golden, d):
+    """fixtures of the dims the CUDA passes take: reference info_nce per class, fp32 and fp64"""
+    g = golden("dense_infonce")["d%d" % d]
+    for dt, tag, tol in ((torch.float32, "f32", dict(rtol=3e-5, atol=1e-6)), (torch.float64, "f64", dict(rtol=1e-10, atol=1e-12))):
+        x = g["x"].to(dt).requires_grad_()
+        loss = O.dense_infonce_from_features(x, g["cls"], temperature=0.1, num_classes=g["num_classes"])
+        gx, = torch.autograd.grad(loss, x)
+        close(loss, g["loss_" + tag], **tol)
+        close(gx, g["gx_" + tag], **tol)
+        e = O.l2_normalize_pixels(x.detach())
+        close(O.dense_infonce_per_class(e, g["cls"], 0.1), g["loss_" + tag], **tol)
+
+
+def test_cam_normalisers_pinned_to_the_reference(golden):
+    """train_mcl.py:21-36 executed from the reference script (oracle/make_golden.py:gen_cam_norms)"""
+    g = golden("cam_norms")
+    for name, fn in (("maxnorm", O.cam_maxnorm), ("softmaxnorm", O.cam_softmaxnorm)):
+        x = g["x"].clone().requires_grad_()
+        y = fn(x)
+        close(y, g[name]["y"], rtol=1e-6, atol=1e-7)
+        gx, = torch.autograd.grad((y * g[name]["go"]).sum(), x)
+        close(gx, g[name]["gx"], rtol=1e-5, atol=1e-6)
+
+
+def test_er_loss_and_upsampling(golden):
+    g = golden("er_loss")
+    sg = g["sgc_small"].clone().requires_grad_()
+    up_c = O.upsample_bilinear(g["cams_small"], g["size"])
+    up_s = O.upsample_bilinear(sg, g["size"])
+    close(up_c, g["up_cams"], rtol=1e-6, atol=1e-7)
+    close(up_s, g["up_sgc"], rtol=1e-6, atol=1e-7)
+    loss = O.er_loss(up_c, up_s, g["label"])
+    close(loss, g["loss_er"], rtol=1e-6, atol=1e-8)
+    gs, = torch.autograd.grad(loss, sg)
+    close(gs, g["g_sgc_small"], rtol=1e-5, atol=1e-9)
+    assert g["k"] == int(0.2 * g["valid_channel"] * g["size"][0] * g["size"][1])
+
+
+def test_classification_losses(golden):
+    g = golden("cls_losses")
+    logits = g["logits"].clone().requires_grad_()
+    loss, lf, ls, lp = O.mcl_cls_loss(logits, g["label"])
+    close(lf, g["loss_focal"])
+    close(ls, g["loss_softmargin"])
+    close(lp, g["loss_pair"])
+    close(loss, g["loss_cls"])
+    close(torch.autograd.grad(loss, logits)[0], g["g_logits"], rtol=1e-5, atol=1e-7)
+    close(O.lsep_loss(torch.sigmoid(g["logits"][:, 1:]), g["label"]), g["pair_rows"])
+
+
+def test_decoder_tail_into_fieldloss(golden):
+    g = golden("decoder_tail")
+    p3 = g["p3_dec"].clone().requires_grad_()
+    fw = g["fuse_w"].clone().requires_grad_()
+    fb = g["fuse_b"].clone().requires_grad_()
+    seg, dense = O.decoder_tail(p3, fw, fb, g["size"])
+    close(seg, g["seg_map"], rtol=1e-4, atol=1e-4)      # |seg| reaches 120: fp32 summation order of the 1x1 conv
+    close(dense, g["dense_ft"], rtol=1e-5, atol=1e-6)
+    rng = random.Random(g["py_seed"])
+    loss, mag = O.fieldloss_forward(seg, dense, g["mask"], g["label_bg"], step=g["step"], k=g["k"], beta=g["beta"], rng=rng)
+    close(loss, g["loss"], rtol=1e-4, atol=1e-7)
+    close(mag, g["mag"], rtol=3e-3, atol=3e-3)     # softmax(seg * 100) amplifies the 1e-5 of seg a hundredfold
+    gp, = torch.autograd.grad(loss, p3, allow_unused=True)
+    close(gp, g["g_p3"], rtol=2e-3, atol=1e-9)
+    assert g["g_w"] is None and g["g_b"] is None      # seg_map enters FieldLoss under no_grad only (src/edge.py:366-374)
+
+
+def test_irn_transition_matrix_and_random_walk(golden):
+    g = golden("irn")
+    for times in (1, 4, 8):
+        close(O.to_transition_matrix(g["aff"], 10, times), g["trans_%d" % times], rtol=1e-4, atol=1e-9)
+    close(O.to_transition_matrix(g["aff"], 2, 3), g["trans_b2_3"], rtol=1e-4, atol=1e-9)
+
+
 def test_cam_normalisers():
     x = torch.randn(2, 21, 6, 7)
     sm = O.cam_softmaxnorm(x)
