@@ -71,17 +71,23 @@ __global__ void __launch_bounds__(256) field_prob_kernel(const float* seg, float
     if (k < C) dst[(k - 1) * HW] = v[k] / s;
 }
 
-// 8-bin quantisation of atan2 with the reference's constant 3.1416/8 (src/edge.py:63,72-88); bins 0..7
+// 8-bin quantisation of atan2 with the reference's constant 3.1416/8 (src/edge.py:63,72-88); bins 0..7.
+// The reference compares the fp32 angle with PYTHON floats k * (3.1416/8): the product is formed in double and
+// then takes the tensor's dtype, so the thresholds are fp32(k * 0.3927), not k * fp32(0.3927).
 __device__ __forceinline__ int orient_bin(float gy, float gx) {
   const float ang = atan2f(gy, gx);
-  const float d = 3.1416f / 8.f;
-  if (ang >= 1 * d && ang < 3 * d) return 0;
-  if (ang >= 3 * d && ang < 5 * d) return 1;
-  if (ang >= 5 * d && ang < 7 * d) return 2;
-  if (ang >= -7 * d && ang < -5 * d) return 4;
-  if (ang >= -5 * d && ang < -3 * d) return 5;
-  if (ang >= -3 * d && ang < -1 * d) return 6;
-  if (ang >= -1 * d && ang < 1 * d) return 7;
+  constexpr double d = 3.1416 / 8;
+  constexpr float t1 = static_cast<float>(1 * d), t3 = static_cast<float>(3 * d), t5 = static_cast<float>(5 * d),
+                  t7 = static_cast<float>(7 * d);
+  constexpr float m1 = static_cast<float>(-1 * d), m3 = static_cast<float>(-3 * d), m5 = static_cast<float>(-5 * d),
+                  m7 = static_cast<float>(-7 * d);
+  if (ang >= t1 && ang < t3) return 0;
+  if (ang >= t3 && ang < t5) return 1;
+  if (ang >= t5 && ang < t7) return 2;
+  if (ang >= m7 && ang < m5) return 4;
+  if (ang >= m5 && ang < m3) return 5;
+  if (ang >= m3 && ang < m1) return 6;
+  if (ang >= m1 && ang < t1) return 7;
   return 3;
 }
 

@@ -69,8 +69,9 @@ __global__ void __launch_bounds__(IMC_THREADS) imc_norm_kernel(const float* emb,
   if (threadIdx.x == 0) nrm[blockIdx.x] = n;
 }
 
-// pair type of images (i, j): 1 = positive (labels identical, :51), 2 = negative (labels
-// disjoint under `long & long`, :54), 0 = neither.  Warp-cooperative over the label width.
+// pair type of images (i, j) as a bit mask: bit 0 = positive (labels identical, :51), bit 1 = negative (labels
+// disjoint under `long & long`, :54).  The reference tests the two with independent `if`s, so a pair of
+// all-zero label rows is BOTH.  Warp-cooperative over the label width.
 __device__ __forceinline__ int imc_pair_type(const float* label, int n_labels, int i, int j, int lane) {
   bool same = true;
   long long inter = 0;
@@ -81,8 +82,7 @@ __device__ __forceinline__ int imc_pair_type(const float* label, int n_labels, i
   }
   same = __all_sync(0xffffffffu, same);
   const bool disjoint = __all_sync(0xffffffffu, inter == 0);
-  // the reference tests "identical" first and `elif` disjoint (:51,54)
-  return same ? 1 : (disjoint ? 2 : 0);
+  return (same ? 1 : 0) | (disjoint ? 2 : 0);
 }
 
 // stat[i] = {S_pos, S_neg, n_pos, n_neg} over partners j > i (:46), sums seeded with 1e-6 (:44-45)
@@ -102,7 +102,8 @@ __global__ void __launch_bounds__(IMC_THREADS) imc_rows_kernel(const float* ehat
     for (int d = lane; d < dim; d += 32) dot = fmaf(ei[d], ehat[static_cast<size_t>(j) * dim + d], dot);
     dot = warp_sum_f(dot);
     const float s = expf(dot * inv_tau);
-    if (type == 1) { sp += s; np += 1.f; } else { sn += s; nn += 1.f; }
+    if (type & 1) { sp += s; np += 1.f; }
+    if (type & 2) { sn += s; nn += 1.f; }
   }
   if (lane == 0) { red[0][warp] = sp; red[1][warp] = sn; red[2][warp] = np; red[3][warp] = nn; }
   __syncthreads();
@@ -144,7 +145,7 @@ __global__ void __launch_bounds__(IMC_THREADS) imc_grad_kernel(const float* ehat
       dot = warp_sum_f(dot);
       const float sim = expf(dot * inv_tau);
       // term = -log(S_pos) + log(S_pos + S_neg)
-      const float dterm = (type == 1) ? (1.f / (s.x + s.y) - 1.f / s.x) : (1.f / (s.x + s.y));
+      const float dterm = ((type & 1) ? (1.f / (s.x + s.y) - 1.f / s.x) : 0.f) + ((type & 2) ? (1.f / (s.x + s.y)) : 0.f);
       const float coef = inv_b * dterm * sim * inv_tau;
       for (int d = lane; d < dim; d += 32)
         acc[warp * dim + d] = fmaf(coef, ehat[static_cast<size_t>(j) * dim + d], acc[warp * dim + d]);

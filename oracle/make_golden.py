@@ -72,7 +72,7 @@ def gen_dense_infonce(src):
         x32 = x32 + 0.7 * torch.randn(c, d, generator=g)[cls.clamp_min(0)]
         rec = dict(x=x32, cls=cls, num_classes=c)
         for dt, tag in ((torch.float32, "f32"), (torch.float64, "f64")):
-            x = x32.to(dt).requires_grad_()
+            x = x32.to(dt).clone().requires_grad_()
             e = F.normalize(x, dim=1)
             valid = cls >= 0
             per_query = []

@@ -115,6 +115,27 @@ def dense_infonce(ehat_q, cls_q, ehat_k=None, cls_k=None, temperature=0.1,
     return total / n_valid
 
 
+def dense_infonce_value_and_grad_chunked(x, cls, temperature=0.1, num_classes=None, row_chunk=2048):
+    """(loss, d loss / d x) of ``dense_infonce_from_features`` at sizes whose [Q,K] logits do not fit: the loss is
+    a sum over query chunks, so each chunk's share is back-propagated on its own (through the normalisation and the
+    prototypes, like the whole) and the gradients are added — autograd exactly as the reference would obtain
+    them, only never holding more than one [row_chunk, K] block."""
+    x = x.detach().clone().requires_grad_()
+    n = x.shape[0]
+    n_valid = (cls >= 0).sum()
+    total = 0.0
+    for s0 in range(0, n, row_chunk):
+        e = l2_normalize_pixels(x)
+        if num_classes is None:
+            num_classes = int(cls.max()) + 1
+        proto, _ = class_prototypes(e, cls, num_classes)
+        part = dense_infonce(e[s0:s0 + row_chunk], cls[s0:s0 + row_chunk], e, cls, temperature, num_classes,
+                             proto=proto, n_valid=n_valid, row_chunk=row_chunk)
+        part.backward()
+        total += float(part.detach())
+    return total, x.grad.detach()
+
+
 def dense_infonce_per_class(ehat, cls, temperature=0.1, query_idx=None):
     """The composition of SURVEY.md §8c written exactly the way the reference primitive would be
     called: ONE ``info_nce(E[cls==c], E[cls==c], E[cls!=c], T, 'none')`` per class present

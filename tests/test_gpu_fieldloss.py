@@ -21,9 +21,20 @@ def test_fieldloss_stages_golden(golden):
     crit = FieldLoss(sobel_size=5, beta=g["beta"], k=g["k"])
     st = crit.edges(g["seg"].cuda(), g["label_bg"].cuda(), g["step"])
     torch.testing.assert_close(st["mag_sum"].cpu(), g["mag"], rtol=1e-4, atol=1e-4)
+    # Orientation bins (a14).  Where the class probability is saturated (flat regions) the Sobel sums are pure
+    # rounding residue of the reference's 1e-6 "zeros" (|g| ~ 1e-6): their ANGLE depends on the accumulation order
+    # of the convolution (mkl-dnn here, cuDNN on the reference's GPU) and no implementation can reproduce it.
+    # Such pixels have magnitude < 1e-3 and can never be boundary pixels (those need mag >= 0.8 max, max > 1).
+    # Everywhere else the bins are exact, and so is the boundary set.
     present = g["label_bg"][:, 1:].bool()[:, :, None, None].expand_as(g["orient"])
-    agree = (st["orient"].cpu().float() == g["orient"])[present].float().mean().item()
-    assert agree >= 0.999, agree
+    mag_ref = torch.sqrt((g["edges"] ** 2).sum(2) + 1e-8)
+    ours = st["orient"].cpu().float()
+    solid = present & (mag_ref >= 1e-3)
+    assert torch.equal(ours[solid], g["orient"][solid])
+    differ = present & (ours != g["orient"])
+    assert float(mag_ref[differ].max()) < 1e-3 if bool(differ.any()) else True
+    assert not bool((differ & g["pos"].bool()).any())
+    assert float(solid.float().mean()) > 0.05                             # the exact set is not empty
     assert torch.equal(st["pos"].cpu().bool(), g["pos"].bool())          # index work: exact
     # in/out lists of (image 0, class 14): run the full forward to materialise them
     random.seed(g["py_seed"])
@@ -93,3 +104,72 @@ def test_fieldloss_matches_oracle(n, h, w, ch, k, step):
         out.backward()
         assert abs(out.item() - ref.item()) <= 1e-3 * abs(ref.item()) + 1e-7, (out.item(), ref.item())
         assert _cos(dg.grad.cpu(), gref) >= 0.999
+
+
+def test_fieldloss_config3_size_every_plane(golden):
+    """BASELINE config 3's FieldLoss half at full size (train_muscle.py:196 with batch 16, 512x512, the 256-channel
+    dense_ft, k = 128, step = 7), image by image against the oracle:
+      * boundary sets: equal to the oracle's except pixels whose magnitude sits on the 0.8*max threshold to within
+        fp32 summation noise of the Sobel sums (the only way two correct implementations can differ);
+      * the in/out index lists of EVERY active (image, class) plane: exactly the oracle's index arithmetic applied
+        to the same orientation / boundary maps (integer work: bit-exact);
+      * loss (1e-3) over the whole batch and the dense_ft gradient (cosine >= 0.999) of three images, the oracle
+        consuming Python's random stream in the same order."""
+    from muscle_b200.edge import FieldLoss
+    n, h, w, ch, k, step, beta = 16, 512, 512, 256, 128, 7, 1e2
+    gen = torch.Generator().manual_seed(2024)
+    label = O.synth_labels(n, gen)
+    label_bg = torch.cat([torch.ones(n, 1), label], 1)
+    noise = F.avg_pool2d(torch.randn(n, 21, h // 4, w // 4, generator=gen), 9, 1, 4, count_include_pad=False)
+    noise = F.interpolate(noise, size=(h, w), mode="bilinear", align_corners=True)
+    noise = noise.masked_fill(~label_bg.bool()[:, :, None, None], -1e4)
+    seg = noise * 3 + 0.02 * torch.randn(n, 21, h, w, generator=gen)
+    mask = noise * 2 + 0.3 * torch.randn(n, 21, h, w, generator=gen)
+    cgen = torch.Generator(device="cuda").manual_seed(7)
+    dense = torch.randn(n, ch, h, w, device="cuda", generator=cgen)
+    crit = FieldLoss(sobel_size=5, beta=beta, k=k)
+    st = crit.edges(seg.cuda(), label_bg.cuda(), step)
+    orient_g, pos_g = st["orient"].cpu(), st["pos"].cpu().bool()
+    # boundary sets against the oracle's own edges
+    n_border = 0
+    for b in range(n):
+        edges = O.class_edges(seg[b:b + 1], label_bg[b:b + 1], beta=beta)
+        mag, _ = O.orient_quantize(edges)
+        pos_ref = O.boundary_positions(mag, label_bg[b:b + 1])[0]
+        differ = pos_ref != pos_g[b]
+        if bool(differ.any()):
+            mx = mag[0].reshape(20, -1).max(-1)[0][:, None, None].expand_as(mag[0])
+            assert float(((mag[0] - 0.8 * mx).abs() / mx)[differ].max()) < 1e-5
+            n_border += int(differ.sum())
+    assert n_border <= 16
+    dg = dense.clone().requires_grad_()
+    random.seed(99)
+    loss, mag_sum = crit(seg.cuda(), dg, mask.cuda(), label_bg.cuda(), step)
+    assert torch.is_tensor(loss)
+    loss.backward()
+    # every active plane's lists: exact
+    last = crit._last
+    lists = last["lists"].cpu().long()
+    assert len(last["planes"]) >= n          # the workload exercises many planes
+    for i, plane in enumerate(last["planes"]):
+        b, c = divmod(plane, 20)
+        out_i, in_i = O.in_out_indices(orient_g[b, c].float() + 1, pos_g[b, c], step)
+        o0, o1 = last["offsets"][2 * i], last["offsets"][2 * i + 1]
+        assert torch.equal(lists[o0:o1], out_i) and torch.equal(lists[o1:o1 + in_i.numel()], in_i), plane
+    # loss and gradient, image by image, same random stream
+    rng = random.Random(99)
+    total = 0.0
+    for b in range(n):
+        want_grad = b in (0, 7, 15)
+        d_b = dense[b:b + 1].cpu().requires_grad_(want_grad)
+        with torch.set_grad_enabled(want_grad):
+            l_b = O.fieldloss_bifilter(orient_g[b:b + 1].float(), d_b, mask[b:b + 1], pos_g[b:b + 1], label[b:b + 1], step, k, rng)
+        if torch.is_tensor(l_b):
+            total += float(l_b.detach())           # (bifilter divides by its own batch size, 1)
+            if want_grad:
+                g_b, = torch.autograd.grad(l_b, d_b)
+                assert _cos(dg.grad[b].cpu() * n, g_b[0]) >= 0.999, b
+    ref = total / n
+    # the loss is a signed sum of four means of similarities of magnitude 1/ch that nearly cancel on random
+    # features (|loss| ~ 1e-6 here): 1e-3 relative, with a floor of 2e-4 of one term's magnitude
+    assert abs(loss.item() - ref) <= 1e-3 * abs(ref) + 2e-4 / ch, (loss.item(), ref)

@@ -67,18 +67,44 @@ def test_dense_infonce_matches_oracle(M, batch, d, h, w, nchw):
     assert abs(g.norm().item() / gref.norm().item() - 1) < 2e-2
 
 
-def test_dense_infonce_golden_fixture(M, golden):
-    """The fixture was produced by calling the reference info_nce once per class (make_golden.py)."""
-    g = golden("dense_infonce")["f32"]
-    x = g["x"]
-    n, d = x.shape
-    if d not in (64, 128, 256):
-        pytest.skip("fixture dim %d not a tensor-core dim" % d)
-    xg = x.cuda().requires_grad_()
-    loss = M.dense_infonce(xg, g["cls"].cuda(), 0.1, 5)
+@pytest.mark.parametrize("d", [64, 128])
+def test_dense_infonce_golden_fixture(M, golden, d):
+    """The CUDA path against the REFERENCE itself: the fixture is the reference info_nce called once per class
+    (oracle/make_golden.py:gen_dense_infonce), run in fp32 ("the reference fp32 path") and in fp64."""
+    g = golden("dense_infonce")["d%d" % d]
+    xg = g["x"].detach().cuda().requires_grad_()
+    loss = M.dense_infonce(xg, g["cls"].cuda(), 0.1, g["num_classes"])
     loss.backward()
-    assert abs(loss.item() - g["loss"].item()) <= LOSS_RTOL * abs(g["loss"].item())
-    assert _cos(xg.grad.cpu(), g["gx"]) >= GRAD_COS
+    for tag in ("f32", "f64"):
+        ref = g["loss_" + tag].item()
+        assert abs(loss.item() - ref) <= LOSS_RTOL * abs(ref), (tag, loss.item(), ref)
+        assert _cos(xg.grad.cpu(), g["gx_" + tag]) >= GRAD_COS
+    assert abs(xg.grad.cpu().norm().item() / g["gx_f64"].norm().item() - 1) < 1e-2
+
+
+@pytest.mark.parametrize("temperature", [0.02, 0.05, 0.07, 0.5])
+def test_temperature_range(M, temperature):
+    """The label mask as an exponent shift must not leak at small temperatures (the shift follows the
+    temperature, csrc/pair_kernel.cuh:pair_mask_shift).  All embeddings share a common direction, so every
+    similarity is high (~0.75 across classes, ~0.9 within): masked columns are the largest terms there are, a
+    leak would dominate the row sums, and the loss stays O(1) at every temperature."""
+    gen = torch.Generator().manual_seed(5)
+    b, d, h, w = 2, 128, 24, 24
+    _, cls, _ = O.synth_embeddings(b, d, h, w, seed=41)
+    centers = torch.randn(21, d, generator=gen)
+    base = torch.randn(d, generator=gen)
+    x = (1.7 * base[None, :, None, None] + 0.7 * centers[cls].permute(0, 3, 1, 2)
+         + 0.45 * torch.randn(b, d, h, w, generator=gen))
+    loss, ref, g, gref = _run_both(M, x, cls, temperature=temperature)
+    assert ref > 1e-2, ref
+    assert abs(loss - ref) <= LOSS_RTOL * abs(ref), (loss, ref)
+    assert _cos(g, gref) >= GRAD_COS
+
+
+def test_temperature_below_the_fp32_range_is_refused(M):
+    x, cls, _ = O.synth_embeddings(1, 128, 8, 8, seed=3)
+    with pytest.raises(RuntimeError, match="temperature"):
+        M.dense_infonce(x.cuda(), cls.cuda(), 0.005, 21)
 
 
 def test_ignore_pixels_and_single_class(M):
@@ -175,10 +201,13 @@ def test_permutation_invariance_and_temperature(M):
     assert abs(l0 - ref) <= LOSS_RTOL * abs(ref)
 
 
-def test_config2_full_size_properties(M):
-    """BASELINE config 2 (B=8, 448 crop -> 56x56, D=128): value against the row-chunked oracle,
-    gradient orthogonal to x (normalisation), finite, and equal across layouts."""
-    x, cls, _ = O.synth_embeddings(8, 128, 56, 56, seed=1234)
+@pytest.mark.parametrize("bg_bias", [0.0, 0.15])
+def test_config2_full_size_value_and_gradient(M, bg_bias):
+    """BASELINE config 2 (B=8, 448 crop -> 56x56, D=128) as bench.py generates it (bg_bias 0) and as round 1
+    did (0.15, ~75 % background): value AND input gradient against the row-chunked oracle (north_star: 1e-3
+    relative, cosine >= 0.999), gradient orthogonal to x (normalisation), finite, and equal across layouts."""
+    import workloads
+    x, cls, _ = workloads.synth_embeddings(8, 128, 56, 56, seed=1234, bg_bias=bg_bias)
     xg = x.cuda().requires_grad_()
     loss = M.dense_infonce(xg, cls.cuda(), 0.1, 21)
     loss.backward()
@@ -187,8 +216,14 @@ def test_config2_full_size_properties(M):
     radial = (g * xg.detach()).sum(1).abs().max().item()
     assert radial <= 1e-3 * g.norm(dim=1).max().item() * xg.detach().norm(dim=1).max().item()
     flat = x.permute(0, 2, 3, 1).reshape(-1, 128)
-    ref = O.dense_infonce_from_features(flat, cls.reshape(-1), 0.1, 21).item()
+    ref, gref = O.dense_infonce_value_and_grad_chunked(flat, cls.reshape(-1), 0.1, 21)
     assert abs(loss.item() - ref) <= LOSS_RTOL * abs(ref)
+    g_flat = g.permute(0, 2, 3, 1).reshape(-1, 128).cpu()
+    assert _cos(g_flat, gref) >= GRAD_COS
+    assert abs(g_flat.norm().item() / gref.norm().item() - 1) < 1e-2
+    # per pixel, not only in aggregate: 99 % of the pixels' own gradient vectors point the reference's way
+    pix_cos = F.cosine_similarity(g_flat.double(), gref.double(), dim=1)
+    assert float((pix_cos >= 0.99).float().mean()) >= 0.99
     xp = flat.contiguous().cuda().requires_grad_()
     lp = M.dense_infonce(xp, cls.reshape(-1).cuda(), 0.1, 21)
     lp.backward()
@@ -197,9 +232,9 @@ def test_config2_full_size_properties(M):
     assert _cos(gp.cpu(), g.cpu()) >= 0.99999
 
 
-def test_config3_full_size_value_and_relabelling(M):
-    """BASELINE config 3 (B=16, 512 crop -> 64x64, D=128; 65 536 pixels, 4.3e9 pairs): value against
-    the row-chunked oracle forward; gradient finite and orthogonal to x; and a size-independent
+def test_config3_full_size_value_gradient_and_relabelling(M):
+    """BASELINE config 3 (B=16, 512 crop -> 64x64, D=128; 65 536 pixels, 4.3e9 pairs): value and input gradient
+    against the row-chunked oracle (forward and backward); gradient finite and orthogonal to x; and a size-independent
     property of the loss — renaming the classes (a permutation of the 21 labels, which reorders
     the class-sorted layout and every tile's mask) changes neither the value nor the gradient."""
     x, cls, _ = O.synth_embeddings(16, 128, 64, 64, seed=77)
@@ -210,9 +245,12 @@ def test_config3_full_size_value_and_relabelling(M):
     assert torch.isfinite(g).all()
     radial = (g * xg.detach()).sum(1).abs().max().item()
     assert radial <= 1e-3 * g.norm(dim=1).max().item() * xg.detach().norm(dim=1).max().item()
-    with torch.no_grad():
-        ref = O.dense_infonce_from_features(x.permute(0, 2, 3, 1).reshape(-1, 128), cls.reshape(-1), 0.1, 21).item()
+    ref, gref = O.dense_infonce_value_and_grad_chunked(x.permute(0, 2, 3, 1).reshape(-1, 128), cls.reshape(-1), 0.1, 21,
+                                                       row_chunk=4096)
     assert abs(loss.item() - ref) <= LOSS_RTOL * abs(ref), (loss.item(), ref)
+    g_flat = g.permute(0, 2, 3, 1).reshape(-1, 128).cpu()
+    assert _cos(g_flat, gref) >= GRAD_COS               # all 65 536 pixels against the chunked oracle backward
+    assert abs(g_flat.norm().item() / gref.norm().item() - 1) < 1e-2
     pi = torch.randperm(21, generator=torch.Generator().manual_seed(3))
     relabelled = torch.where(cls >= 0, pi[cls.clamp(min=0)], cls)
     xr = x.cuda().requires_grad_()

@@ -63,6 +63,27 @@ def test_imc_oracle_sizes(batch, dim):
         _close(eg.grad, 2 * gref, rtol=2e-3, atol=1e-6)
 
 
+def test_imc_pair_that_is_both_positive_and_negative():
+    """Two images with all-zero label rows are identical AND disjoint: the reference's two independent `if`s
+    (src/loss_multilabel.py:51,54) count the pair on both sides; the oracle does the same."""
+    from muscle_b200.loss_multilabel import image_level_contrast
+    gen = torch.Generator().manual_seed(77)
+    label = torch.zeros(6, 20)
+    label[2, 3] = 1
+    label[3, [3, 5]] = 1
+    label[4, 9] = 1               # rows 0, 1, 5 are all zero
+    emb = torch.randn(6, 64, generator=gen).abs()
+    er = emb.clone().requires_grad_()
+    ref = O.image_level_contrast(er, label)
+    assert torch.is_tensor(ref)
+    gref, = torch.autograd.grad(ref, er)
+    eg = emb.cuda().requires_grad_()
+    out = image_level_contrast(eg, label.cuda())
+    out.backward()
+    _close(out, ref, rtol=2e-4)
+    _close(eg.grad, gref, rtol=2e-3, atol=1e-6)
+
+
 # --------------------------------------------------------------------------------------- PixPro
 def test_pixpro_golden(golden):
     from muscle_b200.loss_multilabel import PixPro
@@ -138,6 +159,19 @@ def test_cam_head_and_embedding_grads(b, ch, h, w, k):
 
 
 # ---------------------------------------------------------------------------------- normalisers
+def test_cam_normalisers_golden(golden):
+    """train_mcl.py:21-36 as the reference script computes them (fixture minted from the script's own functions)"""
+    from muscle_b200 import heads
+    g = golden("cam_norms")
+    for name, fn in (("maxnorm", heads.cam_maxnorm), ("softmaxnorm", heads.cam_softmaxnorm)):
+        x = g["x"].cuda().requires_grad_()
+        y = fn(x)
+        (y * g[name]["go"].cuda()).sum().backward()
+        _close(y, g[name]["y"], rtol=1e-4, atol=1e-6)
+        assert _cos(x.grad.cpu(), g[name]["gx"]) >= 0.9999
+        _close(x.grad, g[name]["gx"], rtol=2e-3, atol=2e-4 * float(g[name]["gx"].abs().max()))
+
+
 @pytest.mark.parametrize("shape", [(2, 21, 28, 28), (3, 21, 17, 13), (2, 21, 224, 224)])
 def test_cam_normalisers(shape):
     from muscle_b200 import heads
