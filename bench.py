@@ -515,6 +515,52 @@ def measure(env, key, wl, steps, warmup, bg_bias, e2e_runs_n, with_fused, cpu_bu
     return rec
 
 
+def pool_record(env, n, dim, num_classes, steps):
+    """HBM roofline of the CAM-weighted prototype pooling kernels (csrc/pool.cu) at one workload's size: bf16
+    class-sorted embeddings [n, dim] + fp32 weights [n, C]; algorithmic bytes per SURVEY.md 8d."""
+    import muscle_b200 as M
+    from muscle_b200 import _lib
+    from muscle_b200._call import call
+    dev = env.dev
+    gen = torch.Generator(device=dev).manual_seed(SEED)
+    e = torch.nn.functional.normalize(torch.randn(n, dim, device=dev, generator=gen), dim=1).to(torch.bfloat16)
+    w = torch.relu(torch.randn(n, num_classes, device=dev, generator=gen))
+    sums = torch.empty(num_classes, dim, device=dev)
+    mass = torch.empty(num_classes, device=dev)
+    proto = torch.empty(num_classes, dim, device=dev)
+    dproto = torch.randn(num_classes, dim, device=dev, generator=gen)
+    de = torch.empty(n, dim, device=dev)
+    dw = torch.empty(n, num_classes, device=dev)
+    _lib.load()
+
+    def fwd():
+        call("muscle_pool_prototypes_fwd", dev, e.data_ptr(), 1, w.data_ptr(), n, dim, num_classes, 1e-30, sums.data_ptr(),
+             mass.data_ptr(), proto.data_ptr())
+
+    def bwd():
+        call("muscle_pool_prototypes_bwd", dev, e.data_ptr(), 1, w.data_ptr(), n, dim, num_classes, 1e-30, proto.data_ptr(),
+             mass.data_ptr(), dproto.data_ptr(), de.data_ptr(), dw.data_ptr())
+
+    for _ in range(3):
+        fwd()
+        bwd()
+    k = max(10, min(steps, 50))
+    t_f = env.timed(fwd, k) / k
+    t_b = env.timed(bwd, k) / k
+    pk = peaks()
+    b_f = n * dim * 2 + n * num_classes * 4 + num_classes * dim * 4
+    b_b = n * dim * (2 + 4) + n * num_classes * (4 + 4) + 2 * num_classes * dim * 4
+    rec = {}
+    for name, t, nbytes, note in (("fwd", t_f, b_f, "N*D*2 (bf16 rows) + N*C*4 (weights) + C*D*4 (SURVEY 8d)"),
+                                  ("bwd", t_b, b_b, "N*D*(2 read + 4 write) + N*C*(4 read + 4 write) + 2*C*D*4")):
+        ach = nbytes / t / 1e9
+        rec[name] = dict(bound="hbm", kernel="pool_%s_kernel" % name, achieved=ach, peak=pk["hbm"], unit="GB/s",
+                         frac=ach / pk["hbm"], us_per_launch=1e6 * t, algorithmic_bytes=nbytes, algorithmic=note,
+                         traffic=None, peak_source=pk["source"])
+    rec["shape"] = dict(pixels=n, dim=dim, num_classes=num_classes, e="bf16", w="f32")
+    return rec
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -543,6 +589,10 @@ def main():
             sub_steps = max(args.steps, 20)
             subs[sk] = measure(env, sk, WORKLOADS[sk], sub_steps, args.warmup, args.bg_bias, 3, True,
                                0 if args.no_cpu_baseline else 6.0)
+    pool = None
+    if env.world == 1 and args.workload is None and not args.no_sub:
+        c3 = WORKLOADS["config3"]       # the largest single-GPU configuration: 65 536 pixels, D = 128, 21 classes
+        pool = pool_record(env, c3["global_batch"] * c3["h"] * c3["w"], c3["dim"], NUM_CLASSES, args.steps)
     if env.rank == 0:
         world = env.world
         launches_per_step = 8 if world == 1 else 10      # ours; NCCL's kernels are not counted
@@ -567,6 +617,8 @@ def main():
             line["cpu_baseline"] = rec["cpu_baseline"]
         if subs:
             line["configs"] = {k: v for k, v in subs.items() if v is not None}
+        if pool is not None:
+            line["roofline_pool"] = pool
         print(json.dumps(line))
     if env.world > 1:
         env.dist.destroy_process_group()

@@ -68,6 +68,20 @@ int muscle_dense_infonce_bwd(int layout, int64_t batch, int64_t pixels_per_image
                              int num_classes, float temperature, const float* grad_scale,
                              float* dx_out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same pair with the class prototypes HANDED IN (proto_in device float [num_classes, dim], or NULL for the
+ * class means): CAM-weighted prototypes from muscle_pool_prototypes_fwd take the place of the hard class mean
+ * as every pixel's positive.  The backward then returns d loss / d prototype in dproto_out (times grad_scale)
+ * for the pooling op's backward; with proto_external != 0 no gradient flows to the pixels through the
+ * prototypes inside this op (the pooling op owns that path). */
+int muscle_dense_infonce_proto_fwd(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
+                                   int dim, const void* cls, int cls_is_int64, int num_classes,
+                                   float temperature, float eps, const float* proto_in, float* loss_out,
+                                   void* workspace, size_t workspace_bytes, void* stream);
+int muscle_dense_infonce_proto_bwd(int layout, int64_t batch, int64_t pixels_per_image, int dim,
+                                   int num_classes, float temperature, const float* grad_scale,
+                                   int proto_external, float* dx_out, float* dproto_out, void* workspace,
+                                   size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Staged form of the same op, for the batch-sharded multi-GPU path: the host
  * runs  prepare -> [all-gather ehat/bits/tor, all-reduce class_sum/class_mass] -> plan ->
@@ -165,6 +179,23 @@ int muscle_info_nce_fwd_bwd(const float* query, const float* positive_keys,
                             float* loss_out, float* row_loss_out, float* dquery_out,
                             float* dpositive_out, float* dnegative_out, void* workspace,
                             size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * CAM-weighted (soft) prototype pooling and its gradient scatter (north_star: "CAM-weighted pooling of
+ * backbone features into class and region prototypes ... and gradient-scatter kernels").  Instances in the
+ * reference: the positive-key mean of src/loss_multilabel.py:12 (0/1 weights), the region mean of
+ * src/loss_multilabel.py:255, the CAM aggregation `cam @ aff` of src/MuSCLe.py:222 (w = cam^T, `sum` output).
+ *   fwd: sum[c][:] = sum_p w[p][c] e[p][:];  mass[c] = sum_p w[p][c];  proto = sum / max(mass, eps) (proto may be NULL)
+ *   bwd: given dproto [C, dim]:  de[p][:] = sum_c w[p][c] dproto[c][:] / mass[c]
+ *                                dw[p][c] = (e[p] . dproto[c] - proto[c] . dproto[c]) / mass[c]     (either may be NULL)
+ * e [n, dim] pixel-major, bf16 (e_is_bf16 != 0: e.g. the class-sorted `ehat` of the InfoNCE path) or fp32;
+ * w [n, num_classes] pixel-major fp32; dim % 4 == 0, dim <= 256; num_classes <= 24.  de is fp32 [n, dim]. */
+int muscle_pool_prototypes_fwd(const void* e, int e_is_bf16, const float* w, int64_t n, int dim,
+                               int num_classes, float eps, float* sum, float* mass, float* proto,
+                               void* stream);
+int muscle_pool_prototypes_bwd(const void* e, int e_is_bf16, const float* w, int64_t n, int dim,
+                               int num_classes, float eps, const float* proto, const float* mass,
+                               const float* dproto, float* de, float* dw, void* stream);
 
 /* ==========================================================================================
  * The other members of the path.  Same conventions as above.

@@ -5,5 +5,6 @@ Everything computes in hand-written CUDA (libmuscle_b200.so, C ABI in include/mu
 there is no CPU or eager fallback.
 """
 from .ops import dense_infonce, dense_infonce_value_and_grad, debug_tile  # noqa: F401
+from .pool import pool_prototypes  # noqa: F401
 
-__all__ = ["dense_infonce", "dense_infonce_value_and_grad", "debug_tile"]
+__all__ = ["dense_infonce", "dense_infonce_value_and_grad", "debug_tile", "pool_prototypes"]

@@ -29,6 +29,10 @@ _SIGNATURES = {
                                          c_float, c_float, c_void_p, c_void_p, c_size_t, c_void_p]),
     "muscle_dense_infonce_bwd": (c_int, [c_int, c_int64, c_int64, c_int, c_int, c_float, c_void_p, c_void_p,
                                          c_void_p, c_size_t, c_void_p]),
+    "muscle_dense_infonce_proto_fwd": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int, c_void_p, c_int, c_int,
+                                               c_float, c_float, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "muscle_dense_infonce_proto_bwd": (c_int, [c_int, c_int64, c_int64, c_int, c_int, c_float, c_void_p, c_int, c_void_p,
+                                               c_void_p, c_void_p, c_size_t, c_void_p]),
     "muscle_infonce_prepare_scratch_bytes": (c_size_t, [c_int64]),
     "muscle_infonce_prepare": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int, c_void_p, c_int, c_int, c_float,
                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
@@ -47,6 +51,10 @@ _SIGNATURES = {
     "muscle_infonce_final": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64,
                                      c_int64, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                      c_void_p, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "muscle_pool_prototypes_fwd": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_int, c_float, c_void_p, c_void_p,
+                                           c_void_p, c_void_p]),
+    "muscle_pool_prototypes_bwd": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_int, c_float, c_void_p, c_void_p,
+                                           c_void_p, c_void_p, c_void_p, c_void_p]),
     "muscle_imc_workspace_bytes": (c_size_t, [c_int, c_int]),
     "muscle_imc_fwd_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_size_t, c_void_p]),

@@ -261,7 +261,8 @@ int prepare_impl(const float* x, int layout, int64_t batch, int64_t pixels_per_i
                  int dim, const void* cls, int cls_is_int64, int num_classes, float eps,
                  void* ehat, uint32_t* bits, float* inv_norm, int32_t* perm,
                  uint32_t* tor, uint32_t* seg, float* class_sum, float* class_mass,
-                 void* scratch, size_t scratch_bytes, uint32_t* unit_off, uint32_t* unit_off_sym, cudaStream_t stream) {
+                 void* scratch, size_t scratch_bytes, uint32_t* unit_off, uint32_t* unit_off_sym, const float* proto_in,
+                 cudaStream_t stream) {
   if (int rc = check_device()) return rc;
   if (!x || !cls || !ehat || !bits || !inv_norm || !perm || !tor || !seg || !class_sum ||
       !class_mass || !scratch)
@@ -295,19 +296,18 @@ int prepare_impl(const float* x, int layout, int64_t batch, int64_t pixels_per_i
 #define MB_PREP(DD)                                                                               \
   {                                                                                               \
     if (layout == MUSCLE_LAYOUT_NCHW) {                                                           \
-      static thread_local bool attr_set = false;   /* once per thread and instantiation: ~2 us per call */ \
-      if (!attr_set) {                                                                            \
-        MB_CUDA(cudaFuncSetAttribute(prepare_nchw_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                     static_cast<int>(SORT_CHUNK * (DD / 2 + 1) * sizeof(uint32_t)))); \
-        attr_set = true;                                                                          \
-      }                                                                                           \
+      if (int rca = ensure_dynamic_smem<prepare_nchw_kernel<DD>>(static_cast<int>(SORT_CHUNK * (DD / 2 + 1) * sizeof(uint32_t)))) return rca; \
       MB_CUDA(launch_pdl(prepare_nchw_kernel<DD>, dim3(n_blk), dim3(PREP_THREADS), smem, stream, p)); \
     } else {                                                                                      \
       MB_CUDA(launch_pdl(prepare_kernel<DD>, dim3(n_blk), dim3(SORT_CHUNK), 0, stream, p));       \
     }                                                                                             \
     MB_LAUNCH_CHECK();                                                                            \
-    MB_CUDA(launch_pdl(class_sum_kernel<DD>, dim3(n_tiles * (128 / SEG_ROWS)), dim3(SEG_THREADS), 0, stream, \
-                       static_cast<const __nv_bfloat16*>(p.ehat), static_cast<const uint32_t*>(seg), num_classes, class_sum)); \
+    if (proto_in != nullptr)                                                                      \
+      MB_CUDA(launch_pdl(proto_to_sum_kernel, dim3((num_classes * DD + 255) / 256), dim3(256), 0, stream, proto_in, \
+                         static_cast<const float*>(class_mass), num_classes, DD, class_sum));     \
+    else                                                                                          \
+      MB_CUDA(launch_pdl(class_sum_kernel<DD>, dim3(n_tiles * (128 / SEG_ROWS)), dim3(SEG_THREADS), 0, stream, \
+                         static_cast<const __nv_bfloat16*>(p.ehat), static_cast<const uint32_t*>(seg), num_classes, class_sum)); \
   }
   if (dim == 64) MB_PREP(64) else if (dim == 128) MB_PREP(128) else MB_PREP(256)
 #undef MB_PREP
@@ -324,7 +324,7 @@ int muscle_infonce_prepare(const float* x, int layout, int64_t batch, int64_t pi
                            uint32_t* tor, uint32_t* seg, float* class_sum, float* class_mass,
                            void* scratch, size_t scratch_bytes, void* stream_) {
   return prepare_impl(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes, eps, ehat,
-                      bits, inv_norm, perm, tor, seg, class_sum, class_mass, scratch, scratch_bytes, nullptr, nullptr,
+                      bits, inv_norm, perm, tor, seg, class_sum, class_mass, scratch, scratch_bytes, nullptr, nullptr, nullptr,
                       static_cast<cudaStream_t>(stream_));
 }
 
@@ -463,13 +463,16 @@ int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows,
                                     cols_pad, prm, stream);
 }
 
-int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* inv_norm,
-                         const int32_t* perm, const float* part, const uint32_t* unit_off,
-                         int64_t rows_pad, int64_t cols_pad, int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
-                         const float* class_sum, const float* class_mass, const float* gpos,
-                         const float* dproto, const double* loss_acc, float temperature,
-                         int layout, float* dx, float* loss_out, const float* grad_scale, void* stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+}  // extern "C"
+
+namespace {
+int final_impl(const void* ehat, const uint32_t* bits, const float* inv_norm,
+               const int32_t* perm, const float* part, const uint32_t* unit_off,
+               int64_t rows_pad, int64_t cols_pad, int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
+               const float* class_sum, const float* class_mass, const float* gpos,
+               const float* dproto, const double* loss_acc, float temperature,
+               int layout, float* dx, float* loss_out, const float* grad_scale, int proto_external,
+               float* dproto_out, cudaStream_t stream) {
   if (int rc = check_device()) return rc;
   if (!class_mass || !loss_acc) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (dx && (!ehat || !bits || !inv_norm || !perm || !part || !unit_off || !class_sum || !gpos || !dproto))
@@ -485,24 +488,33 @@ int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* in
   p.n = batch * pixels_per_image; p.ppi = pixels_per_image; p.C = num_classes;
   p.class_sum = class_sum; p.class_mass = class_mass; p.gpos = gpos; p.dproto = dproto;
   p.loss_acc = loss_acc; p.inv_tau = 1.f / temperature; p.layout = layout; p.dx = dx;
-  p.loss_out = loss_out; p.grad_scale = grad_scale;
+  p.loss_out = loss_out; p.grad_scale = grad_scale; p.proto_external = proto_external; p.dproto_out = dproto_out;
   const size_t smem = (dx && layout == MUSCLE_LAYOUT_NCHW)
                           ? static_cast<size_t>(SORT_CHUNK) * (dim + 1) * sizeof(float) : 0;
   const int grid = dx ? static_cast<int>((p.n + SORT_CHUNK - 1) / SORT_CHUNK) : 1;
 #define MB_FINAL(DD)                                                                            \
   {                                                                                             \
-    static thread_local bool attr_set = false;                                                  \
-    if (!attr_set) {                                                                            \
-      MB_CUDA(cudaFuncSetAttribute(final_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                   static_cast<int>(SORT_CHUNK * (DD + 1) * sizeof(float))));   \
-      attr_set = true;                                                                          \
-    }                                                                                           \
+    if (int rca = ensure_dynamic_smem<final_kernel<DD>>(static_cast<int>(SORT_CHUNK * (DD + 1) * sizeof(float)))) return rca; \
     MB_CUDA(launch_pdl(final_kernel<DD>, dim3(grid), dim3(FINAL_THREADS), smem, stream, p));     \
   }
   if (dim == 64) MB_FINAL(64) else if (dim == 128) MB_FINAL(128) else MB_FINAL(256)
 #undef MB_FINAL
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int muscle_infonce_final(const void* ehat, const uint32_t* bits, const float* inv_norm,
+                         const int32_t* perm, const float* part, const uint32_t* unit_off,
+                         int64_t rows_pad, int64_t cols_pad, int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
+                         const float* class_sum, const float* class_mass, const float* gpos,
+                         const float* dproto, const double* loss_acc, float temperature,
+                         int layout, float* dx, float* loss_out, const float* grad_scale, void* stream_) {
+  return final_impl(ehat, bits, inv_norm, perm, part, unit_off, rows_pad, cols_pad, batch, pixels_per_image, dim,
+                    num_classes, class_sum, class_mass, gpos, dproto, loss_acc, temperature, layout, dx, loss_out,
+                    grad_scale, 0, nullptr, static_cast<cudaStream_t>(stream_));
 }
 
 }  // extern "C"
@@ -647,7 +659,7 @@ struct StageTimer {
 int composite_forward(const float* x, int layout, int64_t batch, int64_t pixels_per_image, int dim,
                       const void* cls, int cls_is_int64, int num_classes, float temperature, float eps,
                       float* loss_out, void* workspace, const Workspace& ws, const Carved& c,
-                      cudaStream_t stream) {
+                      const float* proto_in, cudaStream_t stream) {
   const int64_t n = batch * pixels_per_image;
   StageTimer tm(stream);
   tm.mark("start");
@@ -658,7 +670,7 @@ int composite_forward(const float* x, int layout, int64_t batch, int64_t pixels_
   int rc = prepare_impl(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes, eps,
                         c.ehat, c.bits, c.inv_norm, c.perm, c.tor, c.seg, c.class_sum, c.class_mass,
                         c.scratch, muscle_infonce_prepare_scratch_bytes(n), c.unit_off,
-                        rowsum_sym_enabled(dim) ? c.unit_off_sym : nullptr, stream);
+                        rowsum_sym_enabled(dim) ? c.unit_off_sym : nullptr, proto_in, stream);
   if (rc) return rc;
   tm.mark("memset+hist+scan(+plan)+prepare+class_sum");
   if (!(temperature >= kMinTemperature))
@@ -680,7 +692,8 @@ int composite_forward(const float* x, int layout, int64_t batch, int64_t pixels_
 // gradient pass + final (dx may be null: loss only)
 int composite_backward(int layout, int64_t batch, int64_t pixels_per_image, int dim, int num_classes,
                        float temperature, const float* grad_scale, float* dx_out, float* loss_out,
-                       const Workspace& ws, const Carved& c, cudaStream_t stream) {
+                       const Workspace& ws, const Carved& c, int proto_external, float* dproto_out,
+                       cudaStream_t stream) {
   StageTimer tm(stream);
   tm.mark("start");
   if (dx_out) {
@@ -689,39 +702,20 @@ int composite_backward(int layout, int64_t batch, int64_t pixels_per_image, int 
     if (rc) return rc;
     tm.mark("grad");
   }
-  const int rcf = muscle_infonce_final(c.ehat, c.bits, c.inv_norm, c.perm, c.part, c.unit_off, ws.rows_pad,
-                              ws.rows_pad, batch, pixels_per_image, dim, num_classes, c.class_sum,
-                              c.class_mass, c.gpos, c.dproto, c.loss_acc, temperature, layout, dx_out,
-                              loss_out, grad_scale, stream);
+  const int rcf = final_impl(c.ehat, c.bits, c.inv_norm, c.perm, c.part, c.unit_off, ws.rows_pad,
+                             ws.rows_pad, batch, pixels_per_image, dim, num_classes, c.class_sum,
+                             c.class_mass, c.gpos, c.dproto, c.loss_acc, temperature, layout, dx_out,
+                             loss_out, grad_scale, proto_external, dproto_out, stream);
   tm.mark(dx_out ? "final" : "final (loss only)");
   tm.report(dx_out ? "backward" : "loss");
   return rcf;
 }
 }  // namespace
 
-int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
-                                 int64_t pixels_per_image, int dim, const void* cls,
-                                 int cls_is_int64, int num_classes, float temperature, float eps,
-                                 float* loss_out, float* dx_out, void* workspace,
-                                 size_t workspace_bytes, void* stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (!x || !cls || !loss_out) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
-  Workspace ws;
-  if (int rc = check_composite(dim, num_classes, temperature, batch, pixels_per_image, workspace, workspace_bytes, &ws))
-    return rc;
-  const Carved c = carve(workspace, ws);
-  if (int rc = composite_forward(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes,
-                                 temperature, eps, loss_out, workspace, ws, c, stream))
-    return rc;
-  if (!dx_out) return MUSCLE_OK;
-  return composite_backward(layout, batch, pixels_per_image, dim, num_classes, temperature, nullptr, dx_out,
-                            nullptr, ws, c, stream);
-}
-
-int muscle_dense_infonce_fwd(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
-                             int dim, const void* cls, int cls_is_int64, int num_classes,
-                             float temperature, float eps, float* loss_out, void* workspace,
-                             size_t workspace_bytes, void* stream_) {
+int muscle_dense_infonce_proto_fwd(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
+                                   int dim, const void* cls, int cls_is_int64, int num_classes,
+                                   float temperature, float eps, const float* proto_in, float* loss_out,
+                                   void* workspace, size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (!x || !cls || !loss_out) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   Workspace ws;
@@ -730,12 +724,13 @@ int muscle_dense_infonce_fwd(const float* x, int layout, int64_t batch, int64_t 
   const Carved c = carve(workspace, ws);
   // the loss is written by the last block of mid_kernel: no separate launch for it
   return composite_forward(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes,
-                           temperature, eps, loss_out, workspace, ws, c, stream);
+                           temperature, eps, loss_out, workspace, ws, c, proto_in, stream);
 }
 
-int muscle_dense_infonce_bwd(int layout, int64_t batch, int64_t pixels_per_image, int dim,
-                             int num_classes, float temperature, const float* grad_scale,
-                             float* dx_out, void* workspace, size_t workspace_bytes, void* stream_) {
+int muscle_dense_infonce_proto_bwd(int layout, int64_t batch, int64_t pixels_per_image, int dim,
+                                   int num_classes, float temperature, const float* grad_scale,
+                                   int proto_external, float* dx_out, float* dproto_out, void* workspace,
+                                   size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (!dx_out) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   Workspace ws;
@@ -743,7 +738,35 @@ int muscle_dense_infonce_bwd(int layout, int64_t batch, int64_t pixels_per_image
     return rc;
   const Carved c = carve(workspace, ws);
   return composite_backward(layout, batch, pixels_per_image, dim, num_classes, temperature, grad_scale, dx_out,
-                            nullptr, ws, c, stream);
+                            nullptr, ws, c, proto_external, dproto_out, stream);
+}
+
+int muscle_dense_infonce_fwd_bwd(const float* x, int layout, int64_t batch,
+                                 int64_t pixels_per_image, int dim, const void* cls,
+                                 int cls_is_int64, int num_classes, float temperature, float eps,
+                                 float* loss_out, float* dx_out, void* workspace,
+                                 size_t workspace_bytes, void* stream_) {
+  if (int rc = muscle_dense_infonce_proto_fwd(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes,
+                                              temperature, eps, nullptr, loss_out, workspace, workspace_bytes, stream_))
+    return rc;
+  if (!dx_out) return MUSCLE_OK;
+  return muscle_dense_infonce_proto_bwd(layout, batch, pixels_per_image, dim, num_classes, temperature, nullptr, 0,
+                                        dx_out, nullptr, workspace, workspace_bytes, stream_);
+}
+
+int muscle_dense_infonce_fwd(const float* x, int layout, int64_t batch, int64_t pixels_per_image,
+                             int dim, const void* cls, int cls_is_int64, int num_classes,
+                             float temperature, float eps, float* loss_out, void* workspace,
+                             size_t workspace_bytes, void* stream_) {
+  return muscle_dense_infonce_proto_fwd(x, layout, batch, pixels_per_image, dim, cls, cls_is_int64, num_classes,
+                                        temperature, eps, nullptr, loss_out, workspace, workspace_bytes, stream_);
+}
+
+int muscle_dense_infonce_bwd(int layout, int64_t batch, int64_t pixels_per_image, int dim,
+                             int num_classes, float temperature, const float* grad_scale,
+                             float* dx_out, void* workspace, size_t workspace_bytes, void* stream_) {
+  return muscle_dense_infonce_proto_bwd(layout, batch, pixels_per_image, dim, num_classes, temperature, grad_scale, 0,
+                                        dx_out, nullptr, workspace, workspace_bytes, stream_);
 }
 
 }  // extern "C"

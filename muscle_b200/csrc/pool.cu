@@ -1,0 +1,293 @@
+// CAM-weighted (soft) prototype pooling and its gradient scatter (include/muscle_b200.h,
+// muscle_pool_prototypes_*).  HBM-bound kernels: every embedding row and every weight row is read
+// once, nothing else of size N is written in the forward.
+//
+//   forward :  sum[c][:] = sum_p w[p][c] e[p][:],  mass[c] = sum_p w[p][c]      (prototype = sum / mass)
+//   backward:  de[p][:]  = sum_c w[p][c] ds[c][:],  dw[p][c] = e[p] . ds[c] + dm[c]
+//              with ds = dproto / mass and dm[c] = -(dproto[c] . proto[c]) / mass[c] formed on the fly
+//
+// References: the positive-key mean of src/loss_multilabel.py:12 (0/1 weights), the region mean of
+// src/loss_multilabel.py:255 and the CAM aggregation `cam @ aff` of src/MuSCLe.py:222 (w = cam^T, no
+// division) are all instances.  Layout: e [N, D] pixel-major (bf16 = the sorted `ehat` of the InfoNCE
+// path, or fp32), w [N, C] pixel-major fp32, C <= 32, D % 128 == 0 or D in {32, 64} handled by a
+// generic lane mapping (D % 4 == 0, D <= 512).
+//
+// Forward mapping: one warp = one pixel at a time, lane l owns the 4-channel groups l, l+32, ... of the
+// row (8-byte / 16-byte coalesced loads); the lane keeps C x (its channels) partial sums in registers
+// (C = 21, D = 128: 84 accumulators, updated with packed FFMA2), so a pixel costs one row load, C
+// broadcast weights from shared memory and 2 C packed FMAs per lane.  At 7.9 FMA per input byte plain
+// per-pixel FMAs could not keep up with HBM; with this register blocking they do.
+#include <cuda_bf16.h>
+
+#include "host_util.cuh"
+#include "ptx.cuh"
+
+using namespace mb200;
+
+namespace {
+
+constexpr int POOL_THREADS = 256;
+constexpr int POOL_WARPS = POOL_THREADS / 32;
+constexpr int POOL_CHUNK = 64;      // pixels whose weights are staged per step
+constexpr int POOL_MAXC = 24;
+
+__device__ __forceinline__ void load4(const float* row, int g, float (&v)[4]) {
+  const float4 t = __ldg(reinterpret_cast<const float4*>(row) + g);
+  v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+__device__ __forceinline__ void load4(const __nv_bfloat16* row, int g, float (&v)[4]) {
+  const uint2 t = __ldg(reinterpret_cast<const uint2*>(row) + g);
+  v[0] = __uint_as_float(t.x << 16); v[1] = __uint_as_float(t.x & 0xffff0000u);
+  v[2] = __uint_as_float(t.y << 16); v[3] = __uint_as_float(t.y & 0xffff0000u);
+}
+
+// NG = 4-channel groups per lane (D = 128 NG): D = 128 -> 1, 256 -> 2; smaller D: lanes >= D/4 idle.
+// CM = compile-time bound of the class count (register blocking), C <= CM the actual one.
+template <typename T, int CM, int NG>
+__global__ void __launch_bounds__(POOL_THREADS) pool_fwd_kernel(const T* __restrict__ e, const float* __restrict__ w,
+                                                                long long n, int dim, int C, float* __restrict__ sum,
+                                                                float* __restrict__ mass) {
+  __shared__ float2 w_sm[POOL_CHUNK][CM];         // weights duplicated into both halves (FFMA2 operand)
+  __shared__ float mass_sm[POOL_MAXC];
+  extern __shared__ float red_sm[];               // [C][dim] block reduction
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int groups = dim / 4;
+  if (threadIdx.x < POOL_MAXC) mass_sm[threadIdx.x] = 0.f;
+  for (int i = threadIdx.x; i < C * dim; i += POOL_THREADS) red_sm[i] = 0.f;
+  uint64_t acc[CM][NG][2];
+#pragma unroll
+  for (int c = 0; c < CM; ++c)
+#pragma unroll
+    for (int g = 0; g < NG; ++g) acc[c][g][0] = acc[c][g][1] = 0ull;
+  __syncthreads();
+  const long long n_chunks = (n + POOL_CHUNK - 1) / POOL_CHUNK;
+  for (long long ch = blockIdx.x; ch < n_chunks; ch += gridDim.x) {
+    const long long p0 = ch * POOL_CHUNK;
+    const int np = static_cast<int>(min(static_cast<long long>(POOL_CHUNK), n - p0));
+    // stage the chunk's weights (coalesced) and their per-class sums
+    for (int i = threadIdx.x; i < np * C; i += POOL_THREADS) {
+      const float v = __ldg(w + p0 * C + i);
+      w_sm[i / C][i % C] = make_float2(v, v);
+      if (v != 0.f) atomicAdd(&mass_sm[i % C], v);
+    }
+    __syncthreads();
+    for (int pp = warp; pp < np; pp += POOL_WARPS) {
+      const T* row = e + (p0 + pp) * dim;
+      float v[NG][4];
+#pragma unroll
+      for (int g = 0; g < NG; ++g)
+        if (lane + 32 * g < groups) load4(row, lane + 32 * g, v[g]);
+        else v[g][0] = v[g][1] = v[g][2] = v[g][3] = 0.f;
+#pragma unroll
+      for (int c = 0; c < CM; ++c) {
+        if (c < C) {
+          const uint64_t wc = *reinterpret_cast<const uint64_t*>(&w_sm[pp][c]);
+#pragma unroll
+          for (int g = 0; g < NG; ++g) {
+            acc[c][g][0] = fma2(pack2(v[g][0], v[g][1]), wc, acc[c][g][0]);
+            acc[c][g][1] = fma2(pack2(v[g][2], v[g][3]), wc, acc[c][g][1]);
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+  // block reduction through shared memory (one atomic per (class, channel) and warp), then one global atomic each
+#pragma unroll
+  for (int c = 0; c < CM; ++c)
+#pragma unroll
+    for (int g = 0; g < NG; ++g)
+      if (c < C && lane + 32 * g < groups) {
+        float a0, a1, a2, a3;
+        unpack2(acc[c][g][0], a0, a1);
+        unpack2(acc[c][g][1], a2, a3);
+        float* dst = red_sm + c * dim + 4 * (lane + 32 * g);
+        atomicAdd(dst, a0); atomicAdd(dst + 1, a1); atomicAdd(dst + 2, a2); atomicAdd(dst + 3, a3);
+      }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C * dim; i += POOL_THREADS)
+    if (red_sm[i] != 0.f) atomicAdd(sum + i, red_sm[i]);
+  if (threadIdx.x < C && mass_sm[threadIdx.x] != 0.f) atomicAdd(mass + threadIdx.x, mass_sm[threadIdx.x]);
+}
+
+// proto = sum / max(mass, eps)
+__global__ void pool_finish_kernel(const float* sum, const float* mass, int C, int dim, float eps, float* proto) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < C * dim) proto[i] = sum[i] / fmaxf(mass[i / dim], eps);
+}
+
+// Backward.  Block = POOL_CHUNK pixels.  Phase A (warp per pixel, as the forward): de = sum_c w_c ds_c.
+// Phase B (thread = (pixel, class group)): dw = e . ds_c + dm_c from the chunk's rows staged in shared memory
+// (row stride dim + 4 floats: conflict-free 16-byte reads down a column of pixels).
+template <typename T, int CM, int NG>
+__global__ void __launch_bounds__(POOL_THREADS) pool_bwd_kernel(const T* __restrict__ e, const float* __restrict__ w,
+                                                                long long n, int dim, int C, const float* __restrict__ proto,
+                                                                const float* __restrict__ mass,
+                                                                const float* __restrict__ dproto, float eps,
+                                                                float* __restrict__ de, float* __restrict__ dw) {
+  extern __shared__ float sm[];
+  float* ds = sm;                                  // [C][dim]   dproto / mass
+  float* e_sm = ds + C * dim;                      // [POOL_CHUNK][dim + 4]
+  __shared__ float w_sm[POOL_CHUNK][CM];
+  __shared__ float dm_sm[POOL_MAXC];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int groups = dim / 4;
+  const int estride = dim + 4;
+  for (int i = threadIdx.x; i < C * dim; i += POOL_THREADS) ds[i] = __ldg(dproto + i) / fmaxf(__ldg(mass + i / dim), eps);
+  __syncthreads();
+  for (int c = warp; c < C; c += POOL_WARPS) {     // dm[c] = -(ds[c] . proto[c])   (mass below eps: no dependence)
+    float s = 0.f;
+    for (int d = lane; d < dim; d += 32) s = fmaf(ds[c * dim + d], __ldg(proto + c * dim + d), s);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) dm_sm[c] = (__ldg(mass + c) >= eps) ? -s : 0.f;
+  }
+  const long long p0 = static_cast<long long>(blockIdx.x) * POOL_CHUNK;
+  const int np = static_cast<int>(min(static_cast<long long>(POOL_CHUNK), n - p0));
+  for (int i = threadIdx.x; i < np * C; i += POOL_THREADS) w_sm[i / C][i % C] = __ldg(w + p0 * C + i);
+  __syncthreads();
+  // phase A
+  for (int pp = warp; pp < np; pp += POOL_WARPS) {
+    const T* row = e + (p0 + pp) * dim;
+#pragma unroll
+    for (int g = 0; g < NG; ++g) {
+      const int gi = lane + 32 * g;
+      if (gi >= groups) continue;
+      float v[4];
+      load4(row, gi, v);
+      if (dw != nullptr) *reinterpret_cast<float4*>(e_sm + pp * estride + 4 * gi) = make_float4(v[0], v[1], v[2], v[3]);
+      if (de != nullptr) {
+        uint64_t a0 = 0ull, a1 = 0ull;
+#pragma unroll
+        for (int c = 0; c < CM; ++c) {
+          if (c < C) {
+            const float wc = w_sm[pp][c];
+            const float4 s4 = *reinterpret_cast<const float4*>(ds + c * dim + 4 * gi);
+            a0 = fma2(pack2(s4.x, s4.y), pack2(wc, wc), a0);
+            a1 = fma2(pack2(s4.z, s4.w), pack2(wc, wc), a1);
+          }
+        }
+        float r0, r1, r2, r3;
+        unpack2(a0, r0, r1);
+        unpack2(a1, r2, r3);
+        *reinterpret_cast<float4*>(de + (p0 + pp) * dim + 4 * gi) = make_float4(r0, r1, r2, r3);
+      }
+    }
+  }
+  if (dw == nullptr) return;
+  __syncthreads();
+  // phase B: thread -> pixel pp = tid % 64, classes c = cg, cg + 4, ... (cg = tid / 64)
+  const int pp = threadIdx.x & (POOL_CHUNK - 1), cg = threadIdx.x / POOL_CHUNK;
+  constexpr int CPT = (CM + 3) / 4;
+  if (pp < np) {
+    float acc[CPT];
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) acc[k] = 0.f;
+    const float* er = e_sm + pp * estride;
+    for (int d = 0; d < dim; d += 4) {
+      const float4 ev = *reinterpret_cast<const float4*>(er + d);
+#pragma unroll
+      for (int k = 0; k < CPT; ++k) {
+        const int c = cg + 4 * k;
+        if (c < C) {
+          const float4 s4 = *reinterpret_cast<const float4*>(ds + c * dim + d);
+          acc[k] = fmaf(ev.x, s4.x, fmaf(ev.y, s4.y, fmaf(ev.z, s4.z, fmaf(ev.w, s4.w, acc[k]))));
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+      const int c = cg + 4 * k;
+      if (c < C) dw[(p0 + pp) * C + c] = acc[k] + dm_sm[c];
+    }
+  }
+}
+
+int check_device_pool() {
+  const DeviceInfo& di = device_info();
+  if (!di.ok) return fail(MUSCLE_ERR_CUDA, "no CUDA device");
+  if (di.cc_major != 10) return fail(MUSCLE_ERR_UNSUPPORTED, "muscle_b200 needs an sm_100 GPU (found cc %d.x)", di.cc_major);
+  return MUSCLE_OK;
+}
+
+int check_pool_args(int64_t n, int dim, int C) {
+  if (n <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty input");
+  if (dim % 4 != 0 || dim < 4 || dim > 256) return fail(MUSCLE_ERR_BAD_ARG, "dim must be a multiple of 4 in [4,256] (got %d)", dim);
+  if (C < 1 || C > POOL_MAXC) return fail(MUSCLE_ERR_BAD_ARG, "num_classes must be in [1,%d]", POOL_MAXC);
+  return MUSCLE_OK;
+}
+
+template <typename T, int NG>
+int launch_fwd(const T* e, const float* w, int64_t n, int dim, int C, float* sum, float* mass, cudaStream_t stream) {
+  const long long n_chunks = (n + POOL_CHUNK - 1) / POOL_CHUNK;
+  const int grid = static_cast<int>(std::min<long long>(n_chunks, 2ll * device_info().sm_count));
+  const size_t smem = static_cast<size_t>(C) * dim * sizeof(float);
+  if (C <= 8) pool_fwd_kernel<T, 8, NG><<<grid, POOL_THREADS, smem, stream>>>(e, w, n, dim, C, sum, mass);
+  else if (C <= 16) pool_fwd_kernel<T, 16, NG><<<grid, POOL_THREADS, smem, stream>>>(e, w, n, dim, C, sum, mass);
+  else pool_fwd_kernel<T, 24, NG><<<grid, POOL_THREADS, smem, stream>>>(e, w, n, dim, C, sum, mass);
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
+}
+
+template <typename T, int CM, int NG>
+int launch_bwd_cm(const T* e, const float* w, int64_t n, int dim, int C, const float* proto, const float* mass,
+                  const float* dproto, float eps, float* de, float* dw, cudaStream_t stream) {
+  const int grid = static_cast<int>((n + POOL_CHUNK - 1) / POOL_CHUNK);
+  const size_t smem = (static_cast<size_t>(C) * dim + static_cast<size_t>(POOL_CHUNK) * (dim + 4)) * sizeof(float);
+  if (int rc = ensure_dynamic_smem<pool_bwd_kernel<T, CM, NG>>(static_cast<int>((24 * 256 + POOL_CHUNK * 260) * sizeof(float)))) return rc;
+  pool_bwd_kernel<T, CM, NG><<<grid, POOL_THREADS, smem, stream>>>(e, w, n, dim, C, proto, mass, dproto, eps, de, dw);
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
+}
+template <typename T, int NG>
+int launch_bwd(const T* e, const float* w, int64_t n, int dim, int C, const float* proto, const float* mass,
+               const float* dproto, float eps, float* de, float* dw, cudaStream_t stream) {
+  if (C <= 8) return launch_bwd_cm<T, 8, NG>(e, w, n, dim, C, proto, mass, dproto, eps, de, dw, stream);
+  if (C <= 16) return launch_bwd_cm<T, 16, NG>(e, w, n, dim, C, proto, mass, dproto, eps, de, dw, stream);
+  return launch_bwd_cm<T, 24, NG>(e, w, n, dim, C, proto, mass, dproto, eps, de, dw, stream);
+}
+
+}  // namespace
+
+extern "C" {
+
+int muscle_pool_prototypes_fwd(const void* e, int e_is_bf16, const float* w, int64_t n, int dim, int num_classes,
+                               float eps, float* sum, float* mass, float* proto, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = check_device_pool()) return rc;
+  if (!e || !w || !sum || !mass) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (int rc = check_pool_args(n, dim, num_classes)) return rc;
+  MB_CUDA(cudaMemsetAsync(sum, 0, static_cast<size_t>(num_classes) * dim * sizeof(float), stream));
+  MB_CUDA(cudaMemsetAsync(mass, 0, static_cast<size_t>(num_classes) * sizeof(float), stream));
+  int rc;
+  if (e_is_bf16)
+    rc = dim <= 128 ? launch_fwd<__nv_bfloat16, 1>(static_cast<const __nv_bfloat16*>(e), w, n, dim, num_classes, sum, mass, stream)
+                    : launch_fwd<__nv_bfloat16, 2>(static_cast<const __nv_bfloat16*>(e), w, n, dim, num_classes, sum, mass, stream);
+  else
+    rc = dim <= 128 ? launch_fwd<float, 1>(static_cast<const float*>(e), w, n, dim, num_classes, sum, mass, stream)
+                    : launch_fwd<float, 2>(static_cast<const float*>(e), w, n, dim, num_classes, sum, mass, stream);
+  if (rc) return rc;
+  if (proto) {
+    const int total = num_classes * dim;
+    pool_finish_kernel<<<(total + 255) / 256, 256, 0, stream>>>(sum, mass, num_classes, dim, eps, proto);
+    MB_LAUNCH_CHECK();
+  }
+  return MUSCLE_OK;
+}
+
+int muscle_pool_prototypes_bwd(const void* e, int e_is_bf16, const float* w, int64_t n, int dim, int num_classes,
+                               float eps, const float* proto, const float* mass, const float* dproto, float* de,
+                               float* dw, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = check_device_pool()) return rc;
+  if (!e || !w || !proto || !mass || !dproto) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (!de && !dw) return MUSCLE_OK;
+  if (int rc = check_pool_args(n, dim, num_classes)) return rc;
+  if (e_is_bf16)
+    return dim <= 128 ? launch_bwd<__nv_bfloat16, 1>(static_cast<const __nv_bfloat16*>(e), w, n, dim, num_classes, proto, mass, dproto, eps, de, dw, stream)
+                      : launch_bwd<__nv_bfloat16, 2>(static_cast<const __nv_bfloat16*>(e), w, n, dim, num_classes, proto, mass, dproto, eps, de, dw, stream);
+  return dim <= 128 ? launch_bwd<float, 1>(static_cast<const float*>(e), w, n, dim, num_classes, proto, mass, dproto, eps, de, dw, stream)
+                    : launch_bwd<float, 2>(static_cast<const float*>(e), w, n, dim, num_classes, proto, mass, dproto, eps, de, dw, stream);
+}
+
+}  // extern "C"

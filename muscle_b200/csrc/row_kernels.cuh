@@ -407,6 +407,15 @@ __global__ void __launch_bounds__(SEG_THREADS) class_sum_kernel(const __nv_bfloa
   }
 }
 
+// class_sum[c][:] = proto[c][:] * class_mass[c]: prototypes handed in by the caller (e.g. CAM-weighted ones from
+// muscle_pool_prototypes_fwd) take the place of the class means; everything downstream divides by the mass again.
+__global__ void proto_to_sum_kernel(const float* proto, const float* class_mass, int C, int dim, float* class_sum) {
+  pdl_trigger();
+  pdl_wait();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < C * dim) class_sum[i] = proto[i] * class_mass[i / dim];
+}
+
 struct MidParams {
   const __nv_bfloat16* ehat;   // sorted rows
   const uint32_t* seg;         // [C+2]
@@ -530,6 +539,8 @@ struct FinalParams {
   float* dx;                   // source order, `layout`
   float* loss_out;
   const float* grad_scale;     // upstream gradient of the loss (device scalar), or null = 1
+  int proto_external;          // the prototypes came from the caller: no gradient to the pixels through them here
+  float* dproto_out;           // optional [C][D]: d loss / d prototype (times grad_scale)
 };
 
 // One block = 128 consecutive source pixels, 16 warps of 8 pixels each (two pixels in flight per
@@ -560,6 +571,8 @@ __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams 
   __syncthreads();
   if (p.dx == nullptr) return;
   const float inv_n = (n_valid_sh > 0.f ? 1.f / n_valid_sh : 0.f) * (p.grad_scale ? __ldg(p.grad_scale) : 1.f);
+  if (p.dproto_out != nullptr && blockIdx.x == 0)
+    for (int i = threadIdx.x; i < p.C * D; i += FINAL_THREADS) p.dproto_out[i] = inv_n * __ldg(p.dproto + i);
   constexpr int RB = 128;  // rows per row block of the pair passes (PAIR_RB)
   const uint32_t per = pair_units_per_cta(__ldg(p.unit_off + p.n_row_blocks), p.n_ctas, p.n_col_tiles);
   const long long blk0 = static_cast<long long>(blockIdx.x) * SORT_CHUNK;
@@ -593,6 +606,7 @@ __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams 
     const float gq = __shfl_sync(0xffffffffu, gq_l, r);
     const float inv = __shfl_sync(0xffffffffu, inv_l, r);
     const float inv_mass = __shfl_sync(0xffffffffu, im_l, r);
+    const float key_mass = p.proto_external ? 0.f : inv_mass;   // pixel -> its class mean -> every query of the class
 #pragma unroll
     for (int k = 0; k < EPL; ++k) g[k] = 0.f;
     if (!bq) return;
@@ -608,7 +622,7 @@ __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams 
     for (int k = 0; k < EPL; ++k) {
       const int d = lane + 32 * k;
       e[k] = __bfloat162float(p.ehat[q * D + d]);
-      g[k] = inv_n * (p.inv_tau * g[k] + gq * __ldg(p.class_sum + c * D + d) + inv_mass * __ldg(p.dproto + c * D + d));
+      g[k] = inv_n * (p.inv_tau * g[k] + gq * __ldg(p.class_sum + c * D + d) + key_mass * __ldg(p.dproto + c * D + d));
       dot = fmaf(g[k], e[k], dot);
     }
     dot = warp_sum(dot);

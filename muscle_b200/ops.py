@@ -53,7 +53,7 @@ def _as_feature_operand(x: torch.Tensor):
 
 class _DenseInfoNCE(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, cls, temperature, num_classes, eps):
+    def forward(ctx, x, cls, temperature, num_classes, eps, proto=None):
         _require_cuda(x, "x")
         _require_cuda(cls, "cls")
         if x.dtype != torch.float32:
@@ -71,7 +71,13 @@ class _DenseInfoNCE(torch.autograd.Function):
         else:
             cls_c = cls_c.to(torch.int64)
             cls64 = 1
-        need_grad = x.requires_grad
+        need_grad = x.requires_grad or (proto is not None and proto.requires_grad)
+        proto_c = None
+        if proto is not None:
+            _require_cuda(proto, "proto")
+            if tuple(proto.shape) != (int(num_classes), dim):
+                raise ValueError("proto must be [num_classes, D] = [%d, %d]" % (num_classes, dim))
+            proto_c = proto.detach().contiguous().float()
         key = (n, dim, int(num_classes))
         ws_bytes = _WS_BYTES.get(key)
         if ws_bytes is None:
@@ -84,10 +90,12 @@ class _DenseInfoNCE(torch.autograd.Function):
         # forward: prepare -> plan -> row sums -> loss; the gradient pass runs in backward() from the
         # state kept in `ws`, with the upstream gradient multiplied in by the last kernel
         with _on_device(x.device):
-            rc = lib.muscle_dense_infonce_fwd(
+            rc = lib.muscle_dense_infonce_proto_fwd(
                 xc.data_ptr(), layout, batch, ppi, dim, cls_c.data_ptr(), cls64, num_classes,
-                float(temperature), float(eps), loss.data_ptr(), ws.data_ptr(), ws_bytes, _stream_ptr(x.device))
+                float(temperature), float(eps), None if proto_c is None else proto_c.data_ptr(), loss.data_ptr(),
+                ws.data_ptr(), ws_bytes, _stream_ptr(x.device))
         _lib.check(rc, "dense_infonce")
+        ctx.has_proto = proto_c is not None
         if need_grad:
             ctx.ws, ctx.ws_bytes = ws, ws_bytes
             ctx.args = (layout, batch, ppi, dim, int(num_classes), float(temperature))
@@ -98,22 +106,25 @@ class _DenseInfoNCE(torch.autograd.Function):
     def backward(ctx, grad_out):
         ws = getattr(ctx, "ws", None)
         if ws is None:
-            return None, None, None, None, None
+            return None, None, None, None, None, None
         lib = _lib.load()
         layout, batch, ppi, dim, num_classes, temperature = ctx.args
         g = grad_out.detach()
         if g.dtype != torch.float32 or g.device != ws.device or not g.is_contiguous():
             g = g.to(device=ws.device, dtype=torch.float32).contiguous()
         dx = torch.empty(ctx.xc_shape, dtype=torch.float32, device=ws.device)
+        dproto = torch.empty((num_classes, dim), dtype=torch.float32, device=ws.device) if ctx.has_proto else None
         with _on_device(ws.device):
-            rc = lib.muscle_dense_infonce_bwd(layout, batch, ppi, dim, num_classes, temperature, g.data_ptr(),
-                                              dx.data_ptr(), ws.data_ptr(), ctx.ws_bytes, _stream_ptr(ws.device))
+            rc = lib.muscle_dense_infonce_proto_bwd(layout, batch, ppi, dim, num_classes, temperature, g.data_ptr(),
+                                                    1 if ctx.has_proto else 0, dx.data_ptr(),
+                                                    None if dproto is None else dproto.data_ptr(), ws.data_ptr(),
+                                                    ctx.ws_bytes, _stream_ptr(ws.device))
         _lib.check(rc, "dense_infonce backward")
         ctx.ws = None   # the 8-slot partial buffer is the large part of the state: free it now
-        return dx.reshape(ctx.x_shape), None, None, None, None
+        return dx.reshape(ctx.x_shape), None, None, None, None, dproto
 
 
-def dense_infonce(x, cls, temperature=0.1, num_classes=21, eps=1e-12):
+def dense_infonce(x, cls, temperature=0.1, num_classes=21, eps=1e-12, proto=None):
     """Dense label-masked pixel InfoNCE over a batch (SURVEY.md §8c composition of the reference
     ``info_nce``, src/loss_multilabel.py:9-21): every valid pixel is a query, its positive is the
     prototype (mean normalised embedding) of its class, its negatives are all pixels of other
@@ -121,9 +132,13 @@ def dense_infonce(x, cls, temperature=0.1, num_classes=21, eps=1e-12):
 
     x   : float32 CUDA [B, D, h, w] (the model's layout), [B, D, P] or [N, D]; D in {64,128,256}
     cls : per-pixel class ids, same pixel order, int64/int32; < 0 = ignore
+    proto : optional [num_classes, D] prototypes that replace the hard class means as the positives — e.g.
+            CAM-weighted ones from :func:`muscle_b200.pool.pool_prototypes` (SURVEY.md §8c soft variant).  The
+            gradient then reaches ``proto`` (and, through the pooling op, the pixels and the weights); no
+            gradient flows to the pixels through the prototypes inside this op.
     Returns a 0-dim float32 tensor with grad to ``x`` (forward and input gradient are produced by
     one fused pass; backward only scales)."""
-    return _DenseInfoNCE.apply(x, cls, temperature, num_classes, eps)
+    return _DenseInfoNCE.apply(x, cls, temperature, num_classes, eps, proto)
 
 
 def dense_infonce_value_and_grad(x, cls, temperature=0.1, num_classes=21, eps=1e-12):
