@@ -231,6 +231,11 @@ class Env:
             raise SystemExit("launch with torch.distributed.run --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
         torch.cuda.set_device(self.local_rank)
         self.dev = torch.device("cuda", self.local_rank)
+        # stdout carries the ONE JSON line: everything else a library prints there (NCCL's version banner, say) is
+        # sent to stderr for the whole run, and the line is written to the saved descriptor at the end
+        sys.stdout.flush()
+        self.stdout_fd = os.dup(1)
+        os.dup2(2, 1)
         if self.world > 1:
             # NCCL prints its version banner on STDOUT at NCCL_DEBUG=VERSION; stdout carries the one JSON line
             if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
@@ -432,13 +437,15 @@ def measure(env, key, wl, steps, warmup, bg_bias, e2e_runs_n, with_fused, cpu_bu
                 state["tor_all"], w_cols, cols_pad, state["unit_off"], dim, TEMPERATURE, part)
 
     rs_tmp = st.zeros((rows_pad,), f32)
-    sym = world == 1 and dim <= 128 and os.environ.get("MUSCLE_ROWSUM_SYM", "1") != "0"
+    sym = dim <= 128 and os.environ.get("MUSCLE_ROWSUM_SYM", "1") != "0"
     if sym:
         uo_sym = st.empty((rows_pad // 128 + 1,), i32)
-        st.plan_sym(state["tor"], rows_pad, uo_sym)
+        rs_all = st.zeros((cols_pad,), f32)
+        st.plan_sym_ring(state["tor"], rows_pad, state["tor_all"], cols_pad, rank, world, uo_sym)
 
         def rowsum_fn():
-            st.rowsum_sym(state["ehat"], state["bits"], state["tor"], rows_pad, uo_sym, dim, TEMPERATURE, rs_tmp)
+            st.rowsum_sym_ring(state["ehat"], state["bits"], state["tor"], rows_pad, state["ehat_all"], state["bits_all"],
+                               state["tor_all"], cols_pad, uo_sym, rank, world, dim, TEMPERATURE, rs_all)
         rowsum_kernel = "pair_sym_kernel<%d>" % dim
     else:
         def rowsum_fn():
@@ -619,7 +626,7 @@ def main():
             line["configs"] = {k: v for k, v in subs.items() if v is not None}
         if pool is not None:
             line["roofline_pool"] = pool
-        print(json.dumps(line))
+        os.write(env.stdout_fd, (json.dumps(line) + "\n").encode())
     if env.world > 1:
         env.dist.destroy_process_group()
 

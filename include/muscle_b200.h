@@ -131,6 +131,22 @@ int muscle_infonce_plan_sym(const uint32_t* tor, int64_t rows_pad, uint32_t* uni
 int muscle_infonce_rowsum_sym(const void* ehat, const uint32_t* bits, const uint32_t* tor,
                               int64_t rows_pad, const uint32_t* unit_off_sym, int dim,
                               float temperature, float* rowsum, void* stream);
+/* The symmetric pass over `world` ranks: the global similarity matrix is symmetric too, so every
+ * unordered tile pair is computed by ONE rank.  The ranks' pixel blocks form a ring: a rank takes its own block's
+ * pairs with column tile >= row tile, all pairs with the next ceil((world-1)/2) blocks and (even world) half of
+ * the pairs with the opposite block.  rowsum_all [cols_pad] (zeroed by the caller) receives the rank's own row
+ * sums at rank * rows_pad AND its column-sum contributions to the other ranks' pixels: ONE all-reduce (sum) of
+ * rowsum_all over the ranks completes every pixel's row sum (cols_pad floats; 1 MiB at BASELINE config 4).
+ * cols_pad == world * rows_pad; scratch: muscle_infonce_plan_sym_ring_scratch_bytes. */
+size_t muscle_infonce_plan_sym_ring_scratch_bytes(int64_t rows_pad);
+int muscle_infonce_plan_sym_ring(const uint32_t* tor_rows, int64_t rows_pad, const uint32_t* tor_cols,
+                                 int64_t cols_pad, int rank, int world, void* scratch,
+                                 uint32_t* unit_off_sym, void* stream);
+int muscle_infonce_rowsum_sym_ring(const void* ehat_rows, const uint32_t* bits_rows,
+                                   const uint32_t* tor_rows, int64_t rows_pad, const void* ehat_cols,
+                                   const uint32_t* bits_cols, const uint32_t* tor_cols, int64_t cols_pad,
+                                   const uint32_t* unit_off_sym, int rank, int world, int dim,
+                                   float temperature, float* rowsum_all, void* stream);
 
 /* pos[q] = e_q . proto_{c_q} / T; rowsum[q] += exp(pos - 1/T); w[q] = 1/rowsum[q];
  * gpos[q] = (exp(pos - 1/T) w - 1)/T; loss_acc (double[1]) += sum_q (1/T + ln rowsum[q] - pos);

@@ -43,6 +43,10 @@ _SIGNATURES = {
     "muscle_infonce_plan_sym": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
     "muscle_infonce_rowsum_sym": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_float, c_void_p,
                                           c_void_p]),
+    "muscle_infonce_plan_sym_ring_scratch_bytes": (c_size_t, [c_int64]),
+    "muscle_infonce_plan_sym_ring": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "muscle_infonce_rowsum_sym_ring": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64,
+                                               c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p]),
     "muscle_infonce_mid": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                    c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "muscle_infonce_part_slots": (c_int, []),

@@ -165,10 +165,12 @@ int launch_pair_dim(int dim, bool poly, const void* ehat_rows, int64_t rows_pad,
 
 // Row-sum pass over rows == columns (pair_sym_kernel.cuh): only the live units with c >= r.
 template <int D, int POLY, int NG>
-int launch_rowsum_sym_ng(const void* ehat, int64_t rows_pad, PairParams prm, cudaStream_t stream) {
+int launch_rowsum_sym_ng(const void* ehat, int64_t rows_pad, const void* ehat_cols, int64_t cols_pad, PairParams prm,
+                         cudaStream_t stream) {
   using C = SymCfg<D, NG>;
-  CUtensorMap tm;
+  CUtensorMap tm, tm_col;
   if (int rc = cached_panel_map(ehat, rows_pad, D, &tm)) return rc;
+  if (int rc = cached_panel_map(ehat_cols, cols_pad, D, &tm_col)) return rc;
   if (int rc = ensure_dynamic_smem<pair_sym_kernel<D, POLY, NG>>(C::SMEM_BYTES)) return rc;
 #if MB_PAIR_TIMING
   static const bool timing = getenv("MUSCLE_PAIR_TIMING") != nullptr;
@@ -179,7 +181,7 @@ int launch_rowsum_sym_ng(const void* ehat, int64_t rows_pad, PairParams prm, cud
     prm.dbg = dbg;
   }
 #endif
-  MB_CUDA(launch_pdl(pair_sym_kernel<D, POLY, NG>, dim3(pair_grid()), dim3(C::THREADS), C::SMEM_BYTES, stream, tm, prm));
+  MB_CUDA(launch_pdl(pair_sym_kernel<D, POLY, NG>, dim3(pair_grid()), dim3(C::THREADS), C::SMEM_BYTES, stream, tm, tm_col, prm));
   MB_LAUNCH_CHECK();
 #if MB_PAIR_TIMING
   if (timing) {
@@ -207,11 +209,9 @@ int launch_rowsum_sym_ng(const void* ehat, int64_t rows_pad, PairParams prm, cud
   return MUSCLE_OK;
 }
 template <int D, int POLY>
-int launch_rowsum_sym(const void* ehat, int64_t rows_pad, PairParams prm, cudaStream_t stream) {
-  // MUSCLE_SYM_NG=2: two epilogue groups and a three-stage column ring instead of three groups and two stages
-  static const int ng = getenv("MUSCLE_SYM_NG") ? atoi(getenv("MUSCLE_SYM_NG")) : 3;
-  if (ng == 2) return launch_rowsum_sym_ng<D, POLY, 2>(ehat, rows_pad, prm, stream);
-  return launch_rowsum_sym_ng<D, POLY, 3>(ehat, rows_pad, prm, stream);
+int launch_rowsum_sym(const void* ehat, int64_t rows_pad, const void* ehat_cols, int64_t cols_pad, PairParams prm,
+                      cudaStream_t stream) {
+  return launch_rowsum_sym_ng<D, POLY, 3>(ehat, rows_pad, ehat_cols, cols_pad, prm, stream);
 }
 
 // MUSCLE_ROWSUM_SYM=0 keeps the ordered row-sum pass in the single-GPU composite (A/B measurements)
@@ -220,20 +220,27 @@ bool rowsum_sym_enabled(int dim) {
   return !off && (dim == 64 || dim == 128);
 }
 
-int rowsum_sym(const void* ehat, const uint32_t* bits, const uint32_t* tor, int64_t rows_pad,
-               const uint32_t* unit_off_sym, int dim, float temperature, float* rowsum, cudaStream_t stream) {
+// rows = this rank's pixels, cols = all ranks' pixels (one GPU: the same arrays, rank 0 of 1); rowsum_all [cols_pad]
+// receives the row sums of the rank's own rows (at rank * rows_pad) AND its column-sum contributions to the other ranks'
+int rowsum_sym(const void* ehat, const uint32_t* bits, const uint32_t* tor, int64_t rows_pad, const void* ehat_cols,
+               const uint32_t* bits_cols, const uint32_t* tor_cols, int64_t cols_pad, const uint32_t* unit_off_sym,
+               int rank, int world, int dim, float temperature, float* rowsum_all, cudaStream_t stream) {
   PairParams prm{};
-  prm.bits_row = bits; prm.bits_col = bits; prm.tor_row = tor; prm.tor_col = tor;
-  prm.rowsum = rowsum; prm.unit_off = unit_off_sym;
+  prm.bits_row = bits; prm.bits_col = bits_cols; prm.tor_row = tor; prm.tor_col = tor_cols;
+  prm.rowsum = rowsum_all + static_cast<size_t>(rank) * rows_pad; prm.rowsum_cols = rowsum_all;
+  prm.unit_off = unit_off_sym;
   prm.scale_log2 = kLog2e / temperature;
   const bool poly = poly_ok(temperature);
   prm.mask_shift = pair_mask_shift(prm.scale_log2, poly);
   prm.n_row_blocks = static_cast<int>(rows_pad / 128);
-  prm.n_col_tiles = prm.n_row_blocks;
+  prm.n_col_tiles = static_cast<int>(cols_pad / 128);
   prm.rows_pad = static_cast<int>(rows_pad);
+  prm.rb_off = rank * prm.n_row_blocks; prm.own_g = rank; prm.own_G = world;
   if (dim == 64)
-    return poly ? launch_rowsum_sym<64, kPoly>(ehat, rows_pad, prm, stream) : launch_rowsum_sym<64, 0>(ehat, rows_pad, prm, stream);
-  return poly ? launch_rowsum_sym<128, kPoly>(ehat, rows_pad, prm, stream) : launch_rowsum_sym<128, 0>(ehat, rows_pad, prm, stream);
+    return poly ? launch_rowsum_sym<64, kPoly>(ehat, rows_pad, ehat_cols, cols_pad, prm, stream)
+                : launch_rowsum_sym<64, 0>(ehat, rows_pad, ehat_cols, cols_pad, prm, stream);
+  return poly ? launch_rowsum_sym<128, kPoly>(ehat, rows_pad, ehat_cols, cols_pad, prm, stream)
+              : launch_rowsum_sym<128, 0>(ehat, rows_pad, ehat_cols, cols_pad, prm, stream);
 }
 
 int rows_per_block(int) { return PAIR_RB; }
@@ -432,7 +439,43 @@ int muscle_infonce_rowsum_sym(const void* ehat, const uint32_t* bits, const uint
   if (!(temperature >= kMinTemperature))
     return fail(MUSCLE_ERR_BAD_ARG, "temperature must be >= %g (exp((s-1)/T) underflows fp32 below it)", kMinTemperature);
   if (rows_pad % 256 || rows_pad <= 0) return fail(MUSCLE_ERR_BAD_ARG, "padded size must be a positive multiple of 256");
-  return rowsum_sym(ehat, bits, tor, rows_pad, unit_off_sym, dim, temperature, rowsum, static_cast<cudaStream_t>(stream_));
+  return rowsum_sym(ehat, bits, tor, rows_pad, ehat, bits, tor, rows_pad, unit_off_sym, 0, 1, dim, temperature, rowsum,
+                    static_cast<cudaStream_t>(stream_));
+}
+
+size_t muscle_infonce_plan_sym_ring_scratch_bytes(int64_t rows_pad) { return static_cast<size_t>(rows_pad / 128 + 1) * 4; }
+
+int muscle_infonce_plan_sym_ring(const uint32_t* tor_rows, int64_t rows_pad, const uint32_t* tor_cols, int64_t cols_pad,
+                                 int rank, int world, void* scratch, uint32_t* unit_off_sym, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = check_device()) return rc;
+  if (!tor_rows || !tor_cols || !scratch || !unit_off_sym) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (rows_pad % 256 || rows_pad <= 0 || world < 1 || rank < 0 || rank >= world || cols_pad != rows_pad * world)
+    return fail(MUSCLE_ERR_BAD_ARG, "every rank holds rows_pad rows (a multiple of 256) and cols_pad = world * rows_pad");
+  const int n_rb = static_cast<int>(rows_pad / 128), n_ct = static_cast<int>(cols_pad / 128);
+  uint32_t* cnt = static_cast<uint32_t*>(scratch);
+  MB_CUDA(launch_pdl(pair_plan_sym_count_kernel, dim3((n_rb + 7) / 8), dim3(256), 0, stream, tor_rows, n_rb, tor_cols, n_ct,
+                     rank, world, cnt));
+  MB_LAUNCH_CHECK();
+  MB_CUDA(launch_pdl(pair_plan_scan_kernel, dim3(1), dim3(1024), 0, stream, static_cast<const uint32_t*>(cnt), n_rb, unit_off_sym));
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
+}
+
+int muscle_infonce_rowsum_sym_ring(const void* ehat_rows, const uint32_t* bits_rows, const uint32_t* tor_rows,
+                                   int64_t rows_pad, const void* ehat_cols, const uint32_t* bits_cols,
+                                   const uint32_t* tor_cols, int64_t cols_pad, const uint32_t* unit_off_sym, int rank,
+                                   int world, int dim, float temperature, float* rowsum_all, void* stream_) {
+  if (int rc = check_device()) return rc;
+  if (!ehat_rows || !bits_rows || !tor_rows || !ehat_cols || !bits_cols || !tor_cols || !unit_off_sym || !rowsum_all)
+    return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (dim != 64 && dim != 128) return fail(MUSCLE_ERR_BAD_ARG, "symmetric row-sum pass: dim must be 64 or 128 (got %d)", dim);
+  if (!(temperature >= kMinTemperature))
+    return fail(MUSCLE_ERR_BAD_ARG, "temperature must be >= %g (exp((s-1)/T) underflows fp32 below it)", kMinTemperature);
+  if (rows_pad % 256 || rows_pad <= 0 || world < 1 || rank < 0 || rank >= world || cols_pad != rows_pad * world)
+    return fail(MUSCLE_ERR_BAD_ARG, "every rank holds rows_pad rows (a multiple of 256) and cols_pad = world * rows_pad");
+  return rowsum_sym(ehat_rows, bits_rows, tor_rows, rows_pad, ehat_cols, bits_cols, tor_cols, cols_pad, unit_off_sym, rank,
+                    world, dim, temperature, rowsum_all, static_cast<cudaStream_t>(stream_));
 }
 
 int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows,
@@ -676,7 +719,8 @@ int composite_forward(const float* x, int layout, int64_t batch, int64_t pixels_
   if (!(temperature >= kMinTemperature))
     return fail(MUSCLE_ERR_BAD_ARG, "temperature must be >= %g (exp((s-1)/T) underflows fp32 below it)", kMinTemperature);
   if (rowsum_sym_enabled(dim))   // rows == columns: the symmetric pass (half the products and exponentials)
-    rc = rowsum_sym(c.ehat, c.bits, c.tor, ws.rows_pad, c.unit_off_sym, dim, temperature, c.rowsum, stream);
+    rc = rowsum_sym(c.ehat, c.bits, c.tor, ws.rows_pad, c.ehat, c.bits, c.tor, ws.rows_pad, c.unit_off_sym, 0, 1, dim,
+                    temperature, c.rowsum, stream);
   else
     rc = muscle_infonce_rowsum(c.ehat, c.bits, c.tor, ws.rows_pad, c.ehat, c.bits, c.tor, ws.rows_pad,
                                c.unit_off, dim, temperature, c.rowsum, stream);

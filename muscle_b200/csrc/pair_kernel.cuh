@@ -74,6 +74,9 @@ struct PairParams {
   const float* w_row;        // [rows_pad]  MODE_GRAD: 1/rowsum of the row pixel (0 = no query role)
   const float* w_col;        // [cols_pad]  MODE_GRAD: 1/rowsum of the column pixel
   float* rowsum;             // [rows_pad]  MODE_ROWSUM: += sum_k mask * exp((s - 1)/tau)
+  float* rowsum_cols;        // symmetric pass: [cols_pad] row sums of ALL column pixels (== rowsum on one GPU)
+  int rb_off;                // symmetric pass: global tile index of this rank's row tile 0
+  int own_g, own_G;          // symmetric pass: this rank and the number of ranks (unit ownership, sym_owned)
   float* part;               // [PAIR_SLOTS][rows_pad][D]  MODE_GRAD: partial sum_k T_qk c_k
   float scale_log2;          // log2(e) / tau
   float mask_shift;          // extra exponent shift of a masked column in the MASK_BIAS form (see pair_mask_shift)

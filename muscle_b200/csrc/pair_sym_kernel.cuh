@@ -147,6 +147,70 @@ __device__ __forceinline__ void pair_plan_sym_body(const uint32_t* tor, int n_ti
   if (threadIdx.x == 0) unit_off[n_tiles] = carry_s;
 }
 
+// Which rank computes the unordered tile pair {row tile r of rank g, column tile j}?  Over G ranks the pixel
+// blocks form a ring: a rank takes its own block's pairs with column >= row, every pair with the next
+// ceil((G-1)/2) blocks -- and, for even G, one half of the pairs with the block opposite (by the parity of the
+// two local tile indices; the opposite rank takes the other half).  Every unordered pair has exactly one owner,
+// and every rank owns the same number of (row tile, column tile) slots.  T = tiles per rank.
+__host__ __device__ inline bool sym_owned(int r_loc, int j, int T, int g, int G) {
+  const int bj = j / T, jl = j - bj * T;
+  int o = bj - g;
+  if (o < 0) o += G;
+  if (o == 0) return jl >= r_loc;
+  if (2 * o < G) return true;
+  if (2 * o == G) return ((r_loc + jl) & 1) == (g < bj ? 0 : 1);
+  return false;
+}
+
+// Multi-rank plan, step 1: cnt[rb] = live units the rank owns in row block rb (one warp per row block; the column
+// tiles are visited from the diagonal tile on, wrapping around -- the order the producer uses).  Step 2
+// (pair_plan_scan_kernel): exclusive scan -> unit_off.
+__global__ void __launch_bounds__(256) pair_plan_sym_count_kernel(const uint32_t* tor_row, int n_row_blocks,
+                                                                  const uint32_t* tor_col, int n_col_tiles, int g, int G,
+                                                                  uint32_t* cnt) {
+  pdl_trigger();
+  pdl_wait();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rb = blockIdx.x * 8 + warp;
+  if (rb >= n_row_blocks) return;
+  const uint32_t tor_r = tor_row[rb];
+  uint32_t c = 0;
+  for (int j = lane; j < n_col_tiles; j += 32)
+    c += (sym_owned(rb, j, n_row_blocks, g, G) && !tile_pair_dead(tor_r, tor_col[j])) ? 1u : 0u;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if (lane == 0) cnt[rb] = c;
+}
+__global__ void __launch_bounds__(1024) pair_plan_scan_kernel(const uint32_t* cnt, int n, uint32_t* unit_off) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ uint32_t warp_tot[32];
+  __shared__ uint32_t carry;
+  if (threadIdx.x == 0) carry = 0u;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int base = 0; base < n; base += 1024) {
+    const int i = base + threadIdx.x;
+    const uint32_t v = i < n ? cnt[i] : 0u;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += u;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    uint32_t woff = 0;
+    for (int w = 0; w < warp; ++w) woff += warp_tot[w];
+    const uint32_t before = carry + woff + inc - v;
+    if (i < n) unit_off[i] = before;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = before + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) unit_off[n] = carry;
+}
+
 // One block of 1024 threads (the single-GPU composite runs the same body at the end of class_scan_kernel).
 __global__ void __launch_bounds__(1024) pair_plan_sym_kernel(const uint32_t* tor, int n_tiles, uint32_t* unit_off) {
   pdl_trigger();
@@ -231,7 +295,8 @@ __device__ __forceinline__ void sym_half_math(uint32_t (&v)[2][32], uint32_t e_r
 
 template <int D, int POLY, int NG_>
 __global__ void __launch_bounds__((SymCfg<D, NG_>::THREADS), 1)
-pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) {
+pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ CUtensorMap tm_col,
+                const PairParams p) {
   using C = SymCfg<D, NG_>;
   constexpr int NST = C::NST;
   constexpr int NB = C::NB;
@@ -292,7 +357,10 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
     tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_ptr_smem)), 512);
     tmem_relinquish();
   }
-  if (warp == C::WARP_PRODUCER && lane == 0) tma_prefetch_desc(&tm_row);
+  if (warp == C::WARP_PRODUCER && lane == 0) {
+    tma_prefetch_desc(&tm_row);
+    tma_prefetch_desc(&tm_col);
+  }
   pdl_trigger();
   tc_fence_before();
   __syncthreads();
@@ -336,19 +404,24 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
         mbar_wait(q_empty, (it & 1) ^ 1);
         info[4 * (it & 1) + 0] = e - a;
         info[4 * (it & 1) + 1] = static_cast<uint32_t>(rb);
-        info[4 * (it & 1) + 2] = (a == 0u && !tile_pair_dead(tor_r, tor_r)) ? 1u : 0u;   // first unit = (rb, rb)
+        info[4 * (it & 1) + 2] = (a == 0u && !tile_pair_dead(tor_r, tor_r)) ? 1u : 0u;   // first unit = the diagonal one
         mbar_arrive_expect_tx(q_full, C::TILE_BYTES);
         tma_load_3d(q_smem, &tm_row, q_full, 0, rb * 128, 0);
       }
       uint32_t li = 0;
-      const int jbase = rb & ~31;
-      uint32_t tc_next = (jbase + lane < p.n_col_tiles) ? __ldg(p.tor_col + jbase + lane) : 0u;
-      for (int j0 = jbase; j0 < p.n_col_tiles && li < e; j0 += 32) {
+      // column tiles from the diagonal tile on, wrapping around (so the diagonal unit, if live, is the item's first)
+      const int jstart = rb + p.rb_off;
+      auto col_of = [&](int t) { const int j = jstart + t; return j >= p.n_col_tiles ? j - p.n_col_tiles : j; };
+      uint32_t tc_next = (lane < p.n_col_tiles) ? __ldg(p.tor_col + col_of(lane)) : 0u;
+      for (int t0 = 0; t0 < p.n_col_tiles && li < e; t0 += 32) {
         const uint32_t tc = tc_next;
-        const int jn = j0 + 32 + lane;
-        tc_next = (jn < p.n_col_tiles) ? __ldg(p.tor_col + jn) : 0u;
-        const int jme = j0 + lane;
-        uint32_t live = __ballot_sync(0xffffffffu, jme >= rb && jme < p.n_col_tiles && !tile_pair_dead(tor_r, tc));
+        const int tn = t0 + 32 + lane;
+        tc_next = (tn < p.n_col_tiles) ? __ldg(p.tor_col + col_of(tn)) : 0u;
+        const int tme = t0 + lane;
+        const int jme = tme < p.n_col_tiles ? col_of(tme) : 0;
+        uint32_t live = __ballot_sync(0xffffffffu, tme < p.n_col_tiles &&
+                                                       sym_owned(rb, jme, p.n_row_blocks, p.own_g, p.own_G) &&
+                                                       !tile_pair_dead(tor_r, tc));
         const uint32_t cnt = __popc(live);
         if (li + cnt <= a) { li += cnt; continue; }
         // The lanes whose tile is one of the CTA's units write it into a 32-entry list (one step for up to 32
@@ -374,7 +447,7 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
             info[8 + 4 * st + 1] = ent.y;
             info[8 + 4 * st + 2] = g;
             mbar_arrive_expect_tx(k_full(st), C::TILE_BYTES + 512);
-            tma_load_3d(k_smem + st * C::TILE_BYTES, &tm_row, k_full(st), 0, static_cast<int>(ent.y) * 128, 0);
+            tma_load_3d(k_smem + st * C::TILE_BYTES, &tm_col, k_full(st), 0, static_cast<int>(ent.y) * 128, 0);
             bulk_load_1d(bits_smem + st * 512, p.bits_col + static_cast<size_t>(ent.y) * 128, 512, k_full(st));
           }
         }
@@ -491,7 +564,7 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
       tmem_wait_ld();
       tc_fence_before();
       // (a masked column keeps 2^-shift of its terms: pixels outside the loss are skipped explicitly)
-      if (cs != 0.f && pend_valid) atomicAdd(p.rowsum + static_cast<size_t>(pend_j) * 128 + trow, cs);
+      if (cs != 0.f && pend_valid) atomicAdd(p.rowsum_cols + static_cast<size_t>(pend_j) * 128 + trow, cs);
       pending = false;
     };
     for (uint32_t it = 0;; ++it) {
@@ -550,7 +623,7 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const PairParams p) 
         const int b = static_cast<int>(gk % NB);
         const uint32_t tor_c = info[8 + 4 * st];
         const int j = static_cast<int>(info[8 + 4 * st + 1]);
-        const bool diag = (j == rb);
+        const bool diag = (j == rb + p.rb_off);
         const bool col_valid = reinterpret_cast<const uint32_t*>(smem_gen + C::SMEM_BITS + st * 512)[trow] != 0u;
         // no element masked, in either direction: disjoint class sets, every column and every row in the loss
         const bool full = (tor_r & tor_c & TOR_CLASSES) == 0u && ((tor_c | tor_r) & TOR_INVALID) == 0u;

@@ -52,6 +52,13 @@ def _all_gather_many(pairs, group):
         _all_gather_into(out, inp, group)
 
 
+def _use_sym_ring(stages, dim):
+    import os
+    if os.environ.get("MUSCLE_ROWSUM_SYM", "1") == "0":
+        return False
+    return hasattr(stages, "rowsum_sym_ring") and dim in stages.sym_dims()
+
+
 def sharded_fwd(stages, x, cls, temperature, num_classes, eps, need_grad, group=None):
     """Runs the forward stages on this rank.  -> (loss 0-dim tensor, state for `sharded_bwd` or None).  `stages` is a
     CudaStages (or the CPU stand-in the gloo tests use)."""
@@ -103,8 +110,21 @@ def sharded_fwd(stages, x, cls, temperature, num_classes, eps, need_grad, group=
         _all_gather_many([(ehat_all, ehat), (bits_all, bits), (tor_all, tor)], group)
     unit_off = stages.empty((rows_pad // stages.unit_rows(dim) + 1,), i32)
     stages.plan(tor, rows_pad, tor_all, cols_pad, dim, unit_off)
-    stages.rowsum(ehat, bits, tor, rows_pad, ehat_all, bits_all, tor_all, cols_pad, unit_off, dim, temperature,
-                  rowsum)
+    if G > 1 and _use_sym_ring(stages, dim):
+        # The global similarity matrix is symmetric: every unordered tile pair is computed ONCE, by the rank that owns
+        # it in the ring (stages.rowsum_sym_ring); a rank's pass leaves row sums for its own pixels and column-sum
+        # contributions for the others' in rowsum_all, and one all-reduce of N_g floats completes them.  Half the
+        # products and exponentials of the ordered pass for 4 bytes per global pixel of extra traffic.
+        rowsum_all = stages.zeros((cols_pad,), f32)
+        unit_off_sym = stages.empty((rows_pad // 128 + 1,), i32)
+        stages.plan_sym_ring(tor, rows_pad, tor_all, cols_pad, rank, G, unit_off_sym)
+        stages.rowsum_sym_ring(ehat, bits, tor, rows_pad, ehat_all, bits_all, tor_all, cols_pad, unit_off_sym, rank, G,
+                               dim, temperature, rowsum_all)
+        dist.all_reduce(rowsum_all, group=group)
+        rowsum = rowsum_all[sl]
+    else:
+        stages.rowsum(ehat, bits, tor, rows_pad, ehat_all, bits_all, tor_all, cols_pad, unit_off, dim, temperature,
+                      rowsum)
     stages.mid(ehat, seg, rows_pad, dim, C, class_sum, class_mass, rowsum, temperature, w, gpos, loss_acc, dproto)
     if G > 1:
         dist.all_reduce(loss_acc, group=group)

@@ -80,6 +80,28 @@ class CudaStages:
                                                     rowsum.data_ptr(), _sp(self.device))
         _lib.check(rc, "infonce_rowsum_sym")
 
+    def plan_sym_ring(self, tor_rows, rows_pad, tor_cols, cols_pad, rank, world, unit_off_sym):
+        sb = int(self.lib.muscle_infonce_plan_sym_ring_scratch_bytes(rows_pad))
+        scratch = torch.empty(sb, dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            rc = self.lib.muscle_infonce_plan_sym_ring(tor_rows.data_ptr(), rows_pad, tor_cols.data_ptr(), cols_pad, rank,
+                                                       world, scratch.data_ptr(), unit_off_sym.data_ptr(), _sp(self.device))
+        _lib.check(rc, "infonce_plan_sym_ring")
+
+    def rowsum_sym_ring(self, ehat_rows, bits_rows, tor_rows, rows_pad, ehat_cols, bits_cols, tor_cols, cols_pad,
+                        unit_off_sym, rank, world, dim, temperature, rowsum_all):
+        """symmetric row-sum pass over `world` ranks: every unordered tile pair once, on the rank that owns it;
+        rowsum_all [cols_pad] must be all-reduced (sum) afterwards"""
+        with torch.cuda.device(self.device):
+            rc = self.lib.muscle_infonce_rowsum_sym_ring(
+                ehat_rows.data_ptr(), bits_rows.data_ptr(), tor_rows.data_ptr(), rows_pad, ehat_cols.data_ptr(),
+                bits_cols.data_ptr(), tor_cols.data_ptr(), cols_pad, unit_off_sym.data_ptr(), rank, world, dim,
+                float(temperature), rowsum_all.data_ptr(), _sp(self.device))
+        _lib.check(rc, "infonce_rowsum_sym_ring")
+
+    def sym_dims(self):
+        return (64, 128)
+
     def mid(self, ehat, seg, rows_pad, dim, num_classes, class_sum, class_mass, rowsum, temperature, w, gpos,
             loss_acc, dproto):
         with torch.cuda.device(self.device):

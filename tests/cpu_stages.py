@@ -91,6 +91,40 @@ class CpuStages:
                dim, temperature, rowsum):
         rowsum += self._pair_weights(ehat_rows, bits_rows, ehat_cols, bits_cols, temperature).sum(1)
 
+    # -- ring-symmetric row sums (include/muscle_b200.h: muscle_infonce_rowsum_sym_ring) --------------
+    def sym_dims(self):
+        return (64, 128)
+
+    @staticmethod
+    def sym_owned(r_loc, j, tiles, g, G):
+        bj, jl = divmod(j, tiles)
+        o = (bj - g) % G
+        if o == 0:
+            return jl >= r_loc
+        if 2 * o < G:
+            return True
+        if 2 * o == G:
+            return ((r_loc + jl) & 1) == (0 if g < bj else 1)
+        return False
+
+    def plan_sym_ring(self, tor_rows, rows_pad, tor_cols, cols_pad, rank, world, unit_off_sym):
+        unit_off_sym.zero_()
+
+    def rowsum_sym_ring(self, ehat_rows, bits_rows, tor_rows, rows_pad, ehat_cols, bits_cols, tor_cols, cols_pad,
+                        unit_off_sym, rank, world, dim, temperature, rowsum_all):
+        """every unordered tile pair on the rank that owns it: row sums into this rank's slice of rowsum_all, column
+        sums into the column pixels' entries (off-diagonal tiles only)"""
+        p = self._pair_weights(ehat_rows, bits_rows, ehat_cols, bits_cols, temperature)
+        tiles = rows_pad // 128
+        for r in range(tiles):
+            for j in range(cols_pad // 128):
+                if not self.sym_owned(r, j, tiles, rank, world):
+                    continue
+                blk = p[r * 128:(r + 1) * 128, j * 128:(j + 1) * 128]
+                rowsum_all[rank * rows_pad + r * 128:rank * rows_pad + (r + 1) * 128] += blk.sum(1)
+                if j != rank * tiles + r:
+                    rowsum_all[j * 128:(j + 1) * 128] += blk.sum(0)
+
     def mid(self, ehat, seg, rows_pad, dim, num_classes, class_sum, class_mass, rowsum, temperature, w, gpos,
             loss_acc, dproto):
         w.zero_()

@@ -71,3 +71,43 @@ def test_rowsum_sym_matches_ordered_pass_and_oracle(batch, d, h, w, temperature,
     rel = ((got[ok] - ref[ok]).abs() / ref[ok].clamp_min(1e-300))
     assert float(rel.max()) < 2e-2, float(rel.max())          # bf16 operands: per-row sums of e^{s/T}
     assert float(rel.mean()) < 3e-3, float(rel.mean())
+
+
+@pytest.mark.parametrize("world,batch,d,h,w", [(2, 4, 128, 24, 24), (3, 3, 64, 20, 20), (4, 8, 128, 16, 16), (8, 8, 128, 16, 16)])
+def test_ring_symmetric_pass_over_emulated_ranks(world, batch, d, h, w):
+    """The multi-rank form on ONE device: every rank's shard is prepared on its own (class-sorted per rank, like
+    dist.sharded_fwd), the shards are concatenated the way the all-gather lays them out, and each rank's pass is run
+    in turn into one rowsum_all buffer (which is what the all-reduce of the real thing sums up).  Every unordered tile
+    pair must then have been counted exactly once: equal to the ordered pass of every rank over all columns."""
+    from muscle_b200.stages import CudaStages
+    st = CudaStages(torch.device("cuda", 0))
+    x, cls, _ = O.synth_embeddings(batch, d, h, w, seed=500 + world)
+    cls = cls.clone()
+    cls[0, :2] = -1
+    lb = batch // world
+    shards = [_prepare(st, x[r * lb:(r + 1) * lb], cls[r * lb:(r + 1) * lb]) for r in range(world)]
+    rp = shards[0][0]
+    assert all(s[0] == rp for s in shards)
+    ehat_all = torch.cat([s[1] for s in shards]).contiguous()
+    bits_all = torch.cat([s[2] for s in shards]).contiguous()
+    tor_all = torch.cat([s[3] for s in shards]).contiguous()
+    cp = rp * world
+    rs_all = st.zeros((cp,), torch.float32)
+    ref_all = st.zeros((cp,), torch.float32)
+    total_units = 0
+    for r in range(world):
+        _, ehat, bits, tor, _ = shards[r]
+        uo = st.empty((rp // 128 + 1,), torch.int32)
+        st.plan_sym_ring(tor, rp, tor_all, cp, r, world, uo)
+        st.rowsum_sym_ring(ehat, bits, tor, rp, ehat_all, bits_all, tor_all, cp, uo, r, world, d, 0.1, rs_all)
+        total_units += int(uo[-1])
+        uo2 = st.empty((rp // 128 + 1,), torch.int32)
+        st.plan(tor, rp, tor_all, cp, d, uo2)
+        st.rowsum(ehat, bits, tor, rp, ehat_all, bits_all, tor_all, cp, uo2, d, 0.1, ref_all[r * rp:(r + 1) * rp])
+    torch.cuda.synchronize()
+    # live unordered pairs (diagonal included) over the concatenated tiles
+    tc = tor_all.cpu().numpy().astype("int64") & 0x7fffffff
+    live = sum(1 for a in range(len(tc)) for b_ in range(a, len(tc))
+               if not (tc[a] == 0 or tc[b_] == 0 or (tc[a] == tc[b_] and (tc[a] & (tc[a] - 1)) == 0)))
+    assert total_units == live
+    torch.testing.assert_close(rs_all.cpu(), ref_all.cpu(), rtol=2e-3, atol=0)
