@@ -39,6 +39,17 @@ def _all_gather_into(out, inp, group):
         dist.all_gather(list(out.chunk(g, dim=0)), inp, group=group)
 
 
+def _all_reduce_many(tensors, group):
+    """Sum all-reduces of several tensors (different dtypes) as ONE NCCL group call."""
+    if dist.get_backend(group) == "nccl":
+        with dist._coalescing_manager(group=group, device=tensors[0].device):
+            for t in tensors:
+                dist.all_reduce(t, group=group)
+        return
+    for t in tensors:
+        dist.all_reduce(t, group=group)
+
+
 def _all_gather_many(pairs, group):
     """All-gathers of several (out, inp) pairs of different dtypes.  On NCCL they are issued as ONE
     group call (ncclGroupStart/End through torch's coalescing manager), so the class bits and tile
@@ -95,39 +106,55 @@ def sharded_fwd(stages, x, cls, temperature, num_classes, eps, need_grad, group=
     inv_norm = stages.empty((rows_pad,), f32)
     perm = stages.empty((max(n, 1),), i32)
     seg = stages.empty((C + 2,), i32)
-    rowsum = stages.zeros((rows_pad,), f32)
     gpos = stages.empty((rows_pad,), f32)
-    stats = stages.zeros((C * dim + C,), f32)           # class_sum | class_mass
+    sym = G > 1 and _use_sym_ring(stages, dim)
+    # everything that starts at zero, in ONE buffer and one fill: [row sums | class_sum | class_mass | dproto | loss_acc].
+    # The first three are also what the ranks sum up after the row-sum pass, as ONE all-reduce (the class sums are
+    # not needed before `mid`, so they ride with the row sums instead of paying a collective of their own).
+    n_rs = cols_pad if sym else rows_pad
+    n_red = n_rs + C * dim + C
+    off_loss = (n_red + C * dim + 1) // 2 * 2           # the double sits on an 8-byte boundary
+    zbuf = stages.zeros((off_loss + 2,), f32)
+    red = zbuf[:n_red]
+    stats = zbuf[n_rs:n_red]                            # class_sum | class_mass
     class_sum, class_mass = stats[:C * dim], stats[C * dim:]
-    dproto = stages.zeros((C * dim,), f32)
-    loss_acc = stages.zeros((1,), torch.float64)
+    dproto = zbuf[n_red:n_red + C * dim]
+    loss_acc = zbuf[off_loss:off_loss + 2].view(torch.float64)
     loss = stages.empty((), f32)
 
     stages.prepare(xc, layout, batch, ppi, dim, cls_c, C, eps, ehat, bits, inv_norm, perm, tor, seg, class_sum,
                    class_mass)
     if G > 1:
-        dist.all_reduce(stats, group=group)
         _all_gather_many([(ehat_all, ehat), (bits_all, bits), (tor_all, tor)], group)
     unit_off = stages.empty((rows_pad // stages.unit_rows(dim) + 1,), i32)
     stages.plan(tor, rows_pad, tor_all, cols_pad, dim, unit_off)
-    if G > 1 and _use_sym_ring(stages, dim):
+    if sym:
         # The global similarity matrix is symmetric: every unordered tile pair is computed ONCE, by the rank that owns
         # it in the ring (stages.rowsum_sym_ring); a rank's pass leaves row sums for its own pixels and column-sum
         # contributions for the others' in rowsum_all, and one all-reduce of N_g floats completes them.  Half the
         # products and exponentials of the ordered pass for 4 bytes per global pixel of extra traffic.
-        rowsum_all = stages.zeros((cols_pad,), f32)
+        rowsum_all = zbuf[:cols_pad]
         unit_off_sym = stages.empty((rows_pad // 128 + 1,), i32)
         stages.plan_sym_ring(tor, rows_pad, tor_all, cols_pad, rank, G, unit_off_sym)
         stages.rowsum_sym_ring(ehat, bits, tor, rows_pad, ehat_all, bits_all, tor_all, cols_pad, unit_off_sym, rank, G,
                                dim, temperature, rowsum_all)
-        dist.all_reduce(rowsum_all, group=group)
+        dist.all_reduce(red, group=group)
         rowsum = rowsum_all[sl]
     else:
+        rowsum = zbuf[:rows_pad]
         stages.rowsum(ehat, bits, tor, rows_pad, ehat_all, bits_all, tor_all, cols_pad, unit_off, dim, temperature,
                       rowsum)
+        if G > 1:
+            dist.all_reduce(stats, group=group)
     stages.mid(ehat, seg, rows_pad, dim, C, class_sum, class_mass, rowsum, temperature, w, gpos, loss_acc, dproto)
     if G > 1:
-        dist.all_reduce(loss_acc, group=group)
+        # everything the gradient half needs from the other ranks is exchanged here, in two launches: the loss
+        # and prototype-gradient sums and every pixel's 1/rowsum (N_g floats) — the backward then runs without a
+        # collective, and no rank waits for another between the two pair passes' halves
+        dist.all_reduce(loss_acc, group=group)            # (float64: cannot share a coalesced call with the fp32 sums)
+        if need_grad:
+            dist.all_reduce(dproto, group=group)
+            _all_gather_into(w_all, w, group)
     part0 = stages.empty((1,), f32)
     stages.final(ehat, bits, inv_norm, perm, part0, unit_off, rows_pad, cols_pad, batch, ppi, dim, C, class_sum,
                  class_mass, gpos, dproto, loss_acc, temperature, layout, None, loss)
@@ -142,13 +169,10 @@ def sharded_fwd(stages, x, cls, temperature, num_classes, eps, need_grad, group=
 
 
 def sharded_bwd(stages, st, grad_scale=None):
-    """The gradient half: all-gather of `w` (N_g floats) and all-reduce of the prototype gradient, the
-    gradient pass, and the final kernel with the upstream gradient `grad_scale` (0-dim tensor or None)
-    multiplied in.  -> dx in the layout of the forward input."""
+    """The gradient half: the gradient pass and the final kernel with the upstream gradient `grad_scale` (0-dim
+    tensor or None) multiplied in (the exchange of `w` and of the prototype gradient happened at the end of the
+    forward half).  -> dx in the layout of the forward input."""
     f32 = torch.float32
-    if st["G"] > 1:
-        dist.all_reduce(st["dproto"], group=st["group"])
-        _all_gather_into(st["w_all"], st["w"], st["group"])
     dim, rows_pad, cols_pad = st["dim"], st["rows_pad"], st["cols_pad"]
     part = stages.empty((stages.part_slots(), rows_pad, dim), f32)
     stages.grad(st["ehat"], st["bits"], st["tor"], st["w"], rows_pad, st["ehat_all"], st["bits_all"], st["tor_all"],

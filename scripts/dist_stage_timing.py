@@ -33,9 +33,10 @@ def main():
     import muscle_b200.dist as MD
     from muscle_b200.stages import CudaStages
 
-    wl = bench.workload(max(world, 2))
+    import workloads
+    wl = bench.WORKLOADS[bench.DEFAULT_WORKLOAD]
     per = wl["global_batch"] // world
-    x, cls = bench.synth(wl["global_batch"], wl["dim"], wl["h"], wl["w"], 1234)
+    x, cls, _ = workloads.synth_embeddings(wl["global_batch"], wl["dim"], wl["h"], wl["w"], bench.SEED, bg_bias=0.0)
     xd = x[rank * per:(rank + 1) * per].to(dev)
     cg = cls[rank * per:(rank + 1) * per].to(dev)
 
@@ -53,11 +54,12 @@ def main():
             return out
         setattr(owner, name, timed)
 
-    for m in ("prepare", "plan", "rowsum", "mid", "grad", "final"):
+    for m in ("prepare", "plan", "plan_sym_ring", "rowsum", "rowsum_sym_ring", "mid", "grad", "final"):
         wrap(CudaStages, m, m)
     wrap(MD.dist, "all_reduce", "nccl all_reduce")
     wrap(MD, "_all_gather_into", "nccl all_gather")
     wrap(MD, "_all_gather_many", "nccl all_gather")
+    wrap(CudaStages, "zeros", "torch.zeros")
 
     totals, step_ms = {}, []
     for it in range(args.warmup + args.steps):
@@ -74,11 +76,19 @@ def main():
         torch.cuda.synchronize()
         if it < args.warmup:
             continue
+        # gaps between consecutive recorded calls (allocations, torch glue, waiting for the host)
+        gap = 0.0
+        prev_end = s0
+        for label, e0, e1 in records:
+            gap += max(0.0, prev_end.elapsed_time(e0))
+            prev_end = e1
+        gap += max(0.0, prev_end.elapsed_time(s1))
+        totals.setdefault("gaps between calls", []).append(gap)
         seen = {}
         for label, e0, e1 in records:
             k = seen.get(label, 0)
             seen[label] = k + 1
-            key = "%s #%d" % (label, k) if label.startswith("nccl") or label == "final" else label
+            key = "%s #%d" % (label, k) if label.startswith("nccl") or label in ("final", "torch.zeros") else label
             totals.setdefault(key, []).append(e0.elapsed_time(e1))
         step_ms.append(s0.elapsed_time(s1))
     keys = list(totals)
