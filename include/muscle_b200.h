@@ -228,6 +228,23 @@ int muscle_imc_fwd_bwd(const float* emb, const float* label, int batch, int dim,
                        void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Classification losses of the MCL stage — replace FocalLoss (src/loss_multilabel.py:68-91),
+ * Log_Sum_Exp_Pairwise_Loss (:24-33) and nn.MultiLabelSoftMarginLoss as composed at train_mcl.py:180-183:
+ *   loss_cls = focal(sigmoid(l)) + softmargin(l) + mean_b LSEP(sigmoid(l)),  l = logits[:, offset : offset+num_fg]
+ * in ONE launch.  losses_out float[4] = {loss_cls, focal, soft margin, pair}; dlogits_out [batch, logit_stride] =
+ * grad_scale[0] * d loss_cls / d logits (columns outside the class range zeroed), or NULL.  label [batch, num_fg].
+ * muscle_focal_loss_fwd_bwd / muscle_lsep_fwd_bwd are the two reference callables on their own inputs
+ * (probabilities): loss_out4[1] = focal; rows_out [batch] = the LSEP values, dpred = sum_b row_grad[b] d row_b. */
+int muscle_cls_losses_fwd_bwd(const float* logits, const float* label, int batch, int num_fg,
+                              int logit_stride, int logit_offset, float gamma, float alpha,
+                              const float* grad_scale, float* losses_out, float* dlogits_out, void* stream);
+int muscle_focal_loss_fwd_bwd(const float* prob, const float* target, int batch, int num_classes,
+                              float gamma, float alpha, const float* grad_scale, float* loss_out4,
+                              float* dprob_out, void* stream);
+int muscle_lsep_fwd_bwd(const float* pred, const float* labels, int batch, int num_classes,
+                        const float* row_grad, float* rows_out, float* dpred_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * PixPro — replaces src/loss_multilabel.py:93-105 (train_mcl.py:209).  fm1, fm2 [batch, 21,
  * height, width] NCHW; box1, box2 device int32 [batch,4] = (top, left, h, w), equal h,w per image,
  * inside the map; max_box_pixels = max_b h*w (grid sizing).  loss_out float[1]; dfm1_out (same

@@ -62,6 +62,11 @@ _SIGNATURES = {
     "muscle_imc_workspace_bytes": (c_size_t, [c_int, c_int]),
     "muscle_imc_fwd_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_size_t, c_void_p]),
+    "muscle_cls_losses_fwd_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_float, c_void_p,
+                                          c_void_p, c_void_p, c_void_p]),
+    "muscle_focal_loss_fwd_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_void_p, c_void_p,
+                                          c_void_p, c_void_p]),
+    "muscle_lsep_fwd_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "muscle_pixpro_fwd_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                       c_void_p, c_void_p, c_void_p, c_void_p]),
     "muscle_cam_head_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),

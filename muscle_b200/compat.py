@@ -7,7 +7,7 @@ import importlib
 
 def install(src_package: str = "src"):
     """Rebinds, inside the already importable reference package `src_package`:
-    loss_multilabel.{info_nce,image_level_contrast,PixPro,EMD}, torchutils.{get_dynamic_crops,get_static_crops},
+    loss_multilabel.{info_nce,image_level_contrast,PixPro,EMD,FocalLoss,Log_Sum_Exp_Pairwise_Loss}, torchutils.{get_dynamic_crops,get_static_crops},
     edge.FieldLoss, and MuSCLe.PCM.  Returns the list of rebound names."""
     from . import edge, heads, loss_multilabel, torchutils
 
@@ -22,12 +22,15 @@ def install(src_package: str = "src"):
     rebind("loss_multilabel", "image_level_contrast", loss_multilabel.image_level_contrast)
     rebind("loss_multilabel", "PixPro", loss_multilabel.PixPro)
     rebind("loss_multilabel", "EMD", loss_multilabel.EMD)
+    rebind("loss_multilabel", "FocalLoss", loss_multilabel.FocalLoss)
+    rebind("loss_multilabel", "Log_Sum_Exp_Pairwise_Loss", loss_multilabel.Log_Sum_Exp_Pairwise_Loss)
     rebind("torchutils", "get_dynamic_crops", torchutils.get_dynamic_crops)
     rebind("torchutils", "get_static_crops", torchutils.get_static_crops)
     rebind("edge", "FieldLoss", edge.FieldLoss)
     top = importlib.import_module(src_package)
     for name, value in (("image_level_contrast", loss_multilabel.image_level_contrast), ("PixPro", loss_multilabel.PixPro),
-                        ("EMD", loss_multilabel.EMD), ("FieldLoss", edge.FieldLoss)):
+                        ("EMD", loss_multilabel.EMD), ("FieldLoss", edge.FieldLoss), ("FocalLoss", loss_multilabel.FocalLoss),
+                        ("Log_Sum_Exp_Pairwise_Loss", loss_multilabel.Log_Sum_Exp_Pairwise_Loss)):
         if hasattr(top, name):           # `from src import *` re-exports (src/__init__.py:1-6)
             setattr(top, name, value)
     muscle_mod = importlib.import_module(src_package + ".MuSCLe")

@@ -296,3 +296,107 @@ def info_nce(query, positive_keys, negative_keys, temperature=0.1, reduction="me
         raise ValueError("info_nce expects unit-norm rows (max norm %.4f): normalise the embeddings first" % worst)
     dim_pad = 64 if d <= 64 else (128 if d <= 128 else 256)
     return _InfoNce.apply(query, positive_keys, negative_keys, temperature, reduction, dim_pad)
+
+
+# --------------------------------------------------------------------------------------------------
+# f4: the classification losses of the MCL stage
+# --------------------------------------------------------------------------------------------------
+
+class _ClsLosses(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, label, offset, gamma, alpha):
+        lg = logits.contiguous()
+        lb = label.contiguous().float()
+        b, stride = lg.shape
+        c = lb.shape[1]
+        out = torch.empty(4, dtype=torch.float32, device=lg.device)
+        ctx.save_for_backward(lg, lb)
+        ctx.args = (b, c, stride, int(offset), float(gamma), float(alpha))
+        call("muscle_cls_losses_fwd_bwd", lg.device, lg.data_ptr(), lb.data_ptr(), b, c, stride, int(offset), float(gamma),
+             float(alpha), None, out.data_ptr(), None)
+        return out
+
+    @staticmethod
+    def backward(ctx, gout):
+        lg, lb = ctx.saved_tensors
+        b, c, stride, offset, gamma, alpha = ctx.args
+        # the four outputs are {total, focal, soft margin, pair}: the usual upstream is on the total alone
+        g = gout.detach().float()
+        if bool((g[1:] != 0).any()):
+            raise NotImplementedError("differentiate loss_cls (output 0); the three parts are reported for logging")
+        scale = g[0:1].contiguous()
+        out = torch.empty(4, dtype=torch.float32, device=lg.device)
+        dlg = torch.empty_like(lg)
+        call("muscle_cls_losses_fwd_bwd", lg.device, lg.data_ptr(), lb.data_ptr(), b, c, stride, offset, gamma, alpha,
+             scale.data_ptr(), out.data_ptr(), dlg.data_ptr())
+        return dlg, None, None, None, None
+
+
+def mcl_cls_loss(logits, label, gamma=2.0, alpha=0.5):
+    """train_mcl.py:180-183 in one launch: ``FocalLoss()(sigmoid(l), y) + MultiLabelSoftMarginLoss()(l, y) +
+    Log_Sum_Exp_Pairwise_Loss(sigmoid(l), y).mean()`` with l = logits[:, 1:] ([B, 21] logits incl. the background
+    column) or logits itself ([B, 20]).  -> (loss_cls, loss_focal, loss_softmargin, loss_pair); differentiate loss_cls."""
+    require_cuda_f32(logits, "logits")
+    if logits.dim() != 2 or label.dim() != 2 or logits.shape[0] != label.shape[0]:
+        raise ValueError("expected logits [B, C(+1)] and label [B, C]")
+    offset = logits.shape[1] - label.shape[1]
+    if offset not in (0, 1):
+        raise ValueError("logits must have as many columns as the labels, or one more (background first)")
+    out = _ClsLosses.apply(logits, label.to(logits.device), offset, gamma, alpha)
+    return out[0], out[1], out[2], out[3]
+
+
+class _Focal(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, prob, target, gamma, alpha):
+        p, t = prob.contiguous(), target.contiguous().float()
+        b, c = p.shape
+        out = torch.empty(4, dtype=torch.float32, device=p.device)
+        dp = torch.empty_like(p) if prob.requires_grad else None
+        call("muscle_focal_loss_fwd_bwd", p.device, p.data_ptr(), t.data_ptr(), b, c, float(gamma), float(alpha), None,
+             out.data_ptr(), ptr(dp))
+        ctx.save_for_backward(dp)
+        return out[1]
+
+    @staticmethod
+    def backward(ctx, g):
+        dp, = ctx.saved_tensors
+        return (None if dp is None else dp * g), None, None, None
+
+
+class FocalLoss(torch.nn.Module):
+    """src/loss_multilabel.py:68-91: input = probabilities [n, c], target [n, c]; sum over classes, mean over images."""
+
+    def __init__(self, gamma=2, alpha=0.5, size_average=True, weight=None):
+        super().__init__()
+        self.gamma, self.alpha, self.size_average, self.weight = gamma, alpha, size_average, weight
+
+    def forward(self, input, target):
+        require_cuda_f32(input, "input")
+        return _Focal.apply(input, target.to(input.device), self.gamma, self.alpha)
+
+
+class _Lsep(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, labels):
+        p, l = pred.contiguous(), labels.contiguous().float()
+        b, c = p.shape
+        rows = torch.empty(b, dtype=torch.float32, device=p.device)
+        call("muscle_lsep_fwd_bwd", p.device, p.data_ptr(), l.data_ptr(), b, c, None, rows.data_ptr(), None)
+        ctx.save_for_backward(p, l)
+        return rows
+
+    @staticmethod
+    def backward(ctx, grows):
+        p, l = ctx.saved_tensors
+        b, c = p.shape
+        g = grows.detach().contiguous().float()
+        dp = torch.empty_like(p)
+        call("muscle_lsep_fwd_bwd", p.device, p.data_ptr(), l.data_ptr(), b, c, g.data_ptr(), None, dp.data_ptr())
+        return dp, None
+
+
+def Log_Sum_Exp_Pairwise_Loss(pred, labels):
+    """src/loss_multilabel.py:24-33: pred, labels [N, C] -> [N] (the caller takes the mean, train_mcl.py:182)."""
+    require_cuda_f32(pred, "pred")
+    return _Lsep.apply(pred, labels.to(pred.device))

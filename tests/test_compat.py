@@ -17,7 +17,7 @@ def _stand_in_package(name):
     pkg.__path__ = []
     sys.modules[name] = pkg
     mods = {}
-    for sub, attrs in (("loss_multilabel", ["info_nce", "image_level_contrast", "PixPro", "EMD"]),
+    for sub, attrs in (("loss_multilabel", ["info_nce", "image_level_contrast", "PixPro", "EMD", "FocalLoss", "Log_Sum_Exp_Pairwise_Loss"]),
                        ("torchutils", ["get_dynamic_crops", "get_static_crops"]), ("edge", ["FieldLoss"]), ("MuSCLe", [])):
         m = types.ModuleType(name + "." + sub)
         for a in attrs:
@@ -51,7 +51,8 @@ def test_install_rebinds_every_name_on_the_path():
     try:
         done = compat.install("fake_src_cpu")
         assert set(done) == {"loss_multilabel.info_nce", "loss_multilabel.image_level_contrast", "loss_multilabel.PixPro",
-                             "loss_multilabel.EMD", "torchutils.get_dynamic_crops", "torchutils.get_static_crops",
+                             "loss_multilabel.EMD", "loss_multilabel.FocalLoss", "loss_multilabel.Log_Sum_Exp_Pairwise_Loss",
+                             "torchutils.get_dynamic_crops", "torchutils.get_static_crops",
                              "edge.FieldLoss", "MuSCLe.MuSCLe.PCM"}
         assert mods["loss_multilabel"].info_nce is loss_multilabel.info_nce
         assert mods["loss_multilabel"].image_level_contrast is loss_multilabel.image_level_contrast
