@@ -309,6 +309,30 @@ int muscle_cam_maxnorm_bwd(const float* cam, const float* dout, const float* loh
                            void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * SURVEY.md 8f rank 1 — bilinear re-sampling with align_corners=True (F.interpolate as called at
+ * src/MuSCLe.py:256-257 and :285) and the ER loss of train_mcl.py:175-188.
+ * x [planes, height, width] -> y [planes, out_height, out_width]; the backward is the exact adjoint (separable, two
+ * launches; scratch: muscle_upsample_bilinear_bwd_scratch_bytes).
+ * ER loss: raw_cams, raw_sgcs [batch, 21, height, width] (the model's outputs at full resolution), label [batch, 20]:
+ *   cams = cam_softmaxnorm(raw_cams) (no gradient), sgcs = cam_softmaxnorm(raw_sgcs), both times the label mask
+ *   (background on); per image the k = int(0.2 * int(label.sum()) * H * W) largest |cams - sgcs|; loss = their mean over
+ *   all batch * k values.  Forward: six launches, no host synchronisation (the reference reads valid_channel back and
+ *   sorts 21 H W values per image); `state` (muscle_er_loss_state_bytes) carries the per-image thresholds to the
+ *   backward, which writes dsgcs_out [batch, 21, H, W] = grad_scale[0] * d loss / d raw_sgcs. */
+int muscle_upsample_bilinear_fwd(const float* x, int64_t planes, int height, int width, int out_height,
+                                 int out_width, float* y, void* stream);
+size_t muscle_upsample_bilinear_bwd_scratch_bytes(int64_t planes, int out_height, int width);
+int muscle_upsample_bilinear_bwd(const float* dy, int64_t planes, int height, int width, int out_height,
+                                 int out_width, float* dx, void* scratch, size_t scratch_bytes, void* stream);
+size_t muscle_er_loss_state_bytes(int batch);
+int muscle_er_loss_fwd(const float* raw_cams, const float* raw_sgcs, const float* label, int batch,
+                       int num_classes, int height, int width, float* loss_out, void* state,
+                       size_t state_bytes, void* stream);
+int muscle_er_loss_bwd(const float* raw_cams, const float* raw_sgcs, const float* label, int batch,
+                       int num_classes, int height, int width, const void* state, size_t state_bytes,
+                       const float* grad_scale, float* dsgcs_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * FieldLoss — replaces src/edge.py:175-384 (constructed train_muscle.py:163, called :196).
  * Stage 1 (muscle_field_edges; replaces Mix_fg.forward :423-440, OrientQuantize :65-89 and the
  * selection of FieldLoss.forward :370-374): seg_map [batch, C, H, W], label_with_bg [batch, C]

@@ -67,6 +67,15 @@ _SIGNATURES = {
     "muscle_focal_loss_fwd_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_void_p, c_void_p,
                                           c_void_p, c_void_p]),
     "muscle_lsep_fwd_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "muscle_upsample_bilinear_fwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "muscle_upsample_bilinear_bwd_scratch_bytes": (c_size_t, [c_int64, c_int, c_int]),
+    "muscle_upsample_bilinear_bwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t,
+                                             c_void_p]),
+    "muscle_er_loss_state_bytes": (c_size_t, [c_int]),
+    "muscle_er_loss_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t,
+                                   c_void_p]),
+    "muscle_er_loss_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p,
+                                   c_void_p, c_void_p]),
     "muscle_pixpro_fwd_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                       c_void_p, c_void_p, c_void_p, c_void_p]),
     "muscle_cam_head_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
