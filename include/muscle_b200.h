@@ -416,6 +416,20 @@ int muscle_emd_static_fwd_bwd(const float* flat1, const float* flat2, const int6
 int muscle_debug_tile(const void* a_bf16, const void* b_bf16, int dim, float* s_out,
                       float* g_out, void* stream);
 
+/* SURVEY.md 8f rank 2 — the decoder tail (src/MuSCLe.py:285-286: dense_ft = bilinear up-sampling of p3_dec, seg_map =
+ * fuse_dec(dense_ft)) feeding FieldLoss without ever materialising dense_ft: the 1x1 fuse_dec commutes with the
+ * up-sampling, so seg_map = upsample(muscle_conv1x1_fwd(p3_dec)) (21 channels instead of 256 at full resolution), and
+ * stage 3 interpolates only the <= 2 k sampled columns per plane from p3_dec [batch, channels, small_height, small_width]
+ * (align_corners=True); dp3_out has p3_dec's shape.  Everything else as muscle_field_loss. */
+int muscle_field_loss_decoder(const float* p3_dec, int small_height, int small_width, const float* mask,
+                              int batch, int channels, int num_classes, int height, int width,
+                              const int32_t* planes, const int64_t* offsets, const int32_t* sel,
+                              const int32_t* lists, int n_active, int k, float* loss_out, float* dp3_out,
+                              void* scratch, size_t scratch_bytes, void* stream);
+/* y[b][k][p] = bias[k] + sum_c weight[k][c] x[b][c][p]  (NCHW, out_channels <= 32; bias may be NULL) */
+int muscle_conv1x1_fwd(const float* x, const float* weight, const float* bias, int batch, int channels,
+                       int out_channels, int64_t pixels, float* y, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -101,6 +101,10 @@ _SIGNATURES = {
     "muscle_field_loss_scratch_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "muscle_field_loss": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "muscle_field_loss_decoder": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p,
+                                          c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t,
+                                          c_void_p]),
+    "muscle_conv1x1_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_void_p]),
     "muscle_crops_fwd": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int64, c_void_p,
                                  c_void_p]),
     "muscle_crops_bwd": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int64, c_void_p,

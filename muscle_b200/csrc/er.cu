@@ -16,6 +16,7 @@
 // Ties at the k-th value share the remaining weight equally (torch.topk picks arbitrary ones: equal in value).
 #include <cfloat>
 
+#include "bilinear.cuh"
 #include "host_util.cuh"
 
 using namespace mb200;
@@ -247,16 +248,6 @@ __global__ void __launch_bounds__(ER_THREADS) er_bwd_kernel(const float* __restr
 
 // ---------------------------------------------------------------------------------------------------------------
 // bilinear up/down-sampling, align_corners=True (F.interpolate as called at src/MuSCLe.py:256-257, :285)
-struct Tap { int i0, i1; float w0, w1; };
-__device__ __forceinline__ Tap tap_of(int o, float scale, int n_in) {   // ATen's area_pixel_compute_source_index
-  const float src = scale * static_cast<float>(o);
-  int i0 = static_cast<int>(src);
-  if (i0 > n_in - 1) i0 = n_in - 1;
-  const int i1 = i0 + (i0 < n_in - 1 ? 1 : 0);
-  const float l1 = src - static_cast<float>(i0);
-  return Tap{i0, i1, 1.f - l1, l1};
-}
-
 __global__ void __launch_bounds__(256) upsample_fwd_kernel(const float* __restrict__ x, long long planes, int h, int w, int H,
                                                            int W, float sy, float sx, float* __restrict__ y) {
   const long long total = planes * H * W;
@@ -334,7 +325,7 @@ int need_sm100_er() {
   if (di.cc_major != 10) return fail(MUSCLE_ERR_UNSUPPORTED, "muscle_b200 needs an sm_100 GPU (found cc %d.x)", di.cc_major);
   return MUSCLE_OK;
 }
-float scale_of(int n_in, int n_out) { return n_out > 1 ? static_cast<float>(n_in - 1) / static_cast<float>(n_out - 1) : 0.f; }
+float scale_of(int n_in, int n_out) { return bilinear_scale(n_in, n_out); }
 int grid_for(long long total) {
   const long long blocks = (total + 255) / 256;
   const long long cap = 32ll * device_info().sm_count;

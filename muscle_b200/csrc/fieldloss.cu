@@ -18,6 +18,7 @@
 #include <algorithm>
 #include <cfloat>
 
+#include "bilinear.cuh"
 #include "host_util.cuh"
 
 using namespace mb200;
@@ -263,13 +264,86 @@ __global__ void __launch_bounds__(256) field_gather_softmax_kernel(const float* 
   }
 }
 
+// The same when dense_ft is never materialised (src/MuSCLe.py:285): the sampled pixel's
+// dense_ft column is the bilinear interpolation (align_corners=True) of four columns of the low-resolution decoder
+// output p3_dec [batch, ch, hs, ws] — 4 * ch reads per sample instead of a [batch, ch, H, W] tensor.
+struct UpGeom { int hs, ws, W; float sy, sx; };
+__global__ void __launch_bounds__(256) field_gather_up_softmax_kernel(const float* p3, const float* mask, int ch, int C,
+                                                                      long long HW, UpGeom g, const int* planes,
+                                                                      const long long* offsets, const int* sel,
+                                                                      const int* lists, int k, int n_samples,
+                                                                      float* probs_d, float* probs_m, int* pix) {
+  const int s = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (s >= n_samples) return;
+  const int lane = threadIdx.x & 31;
+  const int pi = s / (2 * k), side = (s / k) & 1;
+  const int plane = planes[pi];
+  const int b = plane / (C - 1);
+  const int px = lists[offsets[pi * 2 + side] + sel[s]];
+  if (lane == 0) pix[s] = px;
+  {
+    const Tap ty = tap_of(px / g.W, g.sy, g.hs), tx = tap_of(px % g.W, g.sx, g.ws);
+    const long long hw_s = static_cast<long long>(g.hs) * g.ws;
+    const float* src = p3 + static_cast<long long>(b) * ch * hw_s;
+    const int o00 = ty.i0 * g.ws + tx.i0, o01 = ty.i0 * g.ws + tx.i1, o10 = ty.i1 * g.ws + tx.i0, o11 = ty.i1 * g.ws + tx.i1;
+    float* dst = probs_d + static_cast<long long>(s) * ch;
+    float mx = -FLT_MAX;
+    for (int c = lane; c < ch; c += 32) {
+      const float* pc = src + c * hw_s;
+      const float v = ty.w0 * (tx.w0 * pc[o00] + tx.w1 * pc[o01]) + ty.w1 * (tx.w0 * pc[o10] + tx.w1 * pc[o11]);
+      dst[c] = v;
+      mx = fmaxf(mx, v);
+    }
+    mx = warp_max_f(mx);
+    float sum = 0.f;
+    for (int c = lane; c < ch; c += 32) { const float e = expf(dst[c] - mx); dst[c] = e; sum += e; }
+    sum = warp_sum_f(sum);
+    for (int c = lane; c < ch; c += 32) dst[c] = dst[c] / sum;
+  }
+  {
+    const float* src = mask + static_cast<long long>(b) * C * HW + px;
+    float* dst = probs_m + static_cast<long long>(s) * C;
+    const float v = (lane < C) ? src[lane * HW] : -FLT_MAX;
+    const float mx = warp_max_f(v);
+    const float e = (lane < C) ? expf(v - mx) : 0.f;
+    const float sum = warp_sum_f(e);
+    if (lane < C) dst[lane] = e / sum;
+  }
+}
+
+// seg_small[b][k][p] = bias[k] + sum_c W[k][c] x[b][c][p]: the 1x1 `fuse_dec` at the decoder's own resolution
+// (it commutes with the bilinear up-sampling that follows, src/MuSCLe.py:285-286).  Thread = pixel, K <= 32 outputs.
+__global__ void __launch_bounds__(128) conv1x1_kernel(const float* __restrict__ x, const float* __restrict__ wgt,
+                                                      const float* __restrict__ bias, int ch, int K, long long hw,
+                                                      float* __restrict__ y) {
+  extern __shared__ float w_sm[];   // [K][ch]
+  for (int i = threadIdx.x; i < K * ch; i += blockDim.x) w_sm[i] = wgt[i];
+  __syncthreads();
+  const long long p = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (p >= hw) return;
+  float acc[32];
+#pragma unroll
+  for (int k = 0; k < 32; ++k) acc[k] = (k < K && bias) ? bias[k] : 0.f;
+  const float* src = x + static_cast<long long>(b) * ch * hw + p;
+  for (int c = 0; c < ch; ++c) {
+    const float v = __ldg(src + c * hw);
+#pragma unroll
+    for (int k = 0; k < 32; ++k)
+      if (k < K) acc[k] = fmaf(w_sm[k * ch + c], v, acc[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < 32; ++k)
+    if (k < K) y[(static_cast<long long>(b) * K + k) * hw + p] = acc[k];
+}
+
 // One block per active plane: means, sign tests, BEACON terms, gradient scatter.
 // smem (floats): sumO[ch] sumI[ch] wI[ch] | msumO[32] msumI[32] | m1[k] m0[k] mm1[k] mm0[k] coefA[k] coefB[k]
 constexpr int FP_THREADS = 256;
 __global__ void __launch_bounds__(FP_THREADS) field_plane_kernel(const float* probs_d, const float* probs_m,
                                                                  const int* pix, const int* planes, int ch, int C,
                                                                  long long HW, int k, float grad_scale, double* acc,
-                                                                 float* ddense) {
+                                                                 float* ddense, UpGeom up) {
   extern __shared__ float sm[];
   float* sumO = sm;
   float* sumI = sumO + ch;
@@ -379,6 +453,23 @@ __global__ void __launch_bounds__(FP_THREADS) field_plane_kernel(const float* pr
       dot = fmaf(outs[static_cast<long long>(j) * ch + c], dy, dot);
     }
     dot = warp_sum_f(dot);
+    if (up.hs > 0) {   // dense_ft was interpolated from p3_dec: the gradient goes to the four source columns
+      const int px = pix_out[j];
+      const Tap ty = tap_of(px / up.W, up.sy, up.hs), tx = tap_of(px % up.W, up.sx, up.ws);
+      const long long hw_s = static_cast<long long>(up.hs) * up.ws;
+      float* dst = ddense + static_cast<long long>(b) * ch * hw_s;
+      for (int c = lane; c < ch; c += 32) {
+        const float dy = (ca * sumI[c] + wI[c]) * inv_k;
+        const float yv = outs[static_cast<long long>(j) * ch + c];
+        const float gv = grad_scale * yv * (dy - dot);
+        float* dc = dst + c * hw_s;
+        atomicAdd(dc + ty.i0 * up.ws + tx.i0, gv * ty.w0 * tx.w0);
+        atomicAdd(dc + ty.i0 * up.ws + tx.i1, gv * ty.w0 * tx.w1);
+        atomicAdd(dc + ty.i1 * up.ws + tx.i0, gv * ty.w1 * tx.w0);
+        atomicAdd(dc + ty.i1 * up.ws + tx.i1, gv * ty.w1 * tx.w1);
+      }
+      continue;
+    }
     float* dst = ddense + static_cast<long long>(b) * ch * HW + pix_out[j];
     for (int c = lane; c < ch; c += 32) {
       const float dy = (ca * sumI[c] + wI[c]) * inv_k;
@@ -443,11 +534,14 @@ size_t muscle_field_loss_scratch_bytes(int n_active, int k, int channels, int nu
   return (ns * channels * 4 + 255) / 256 * 256 + (ns * num_classes * 4 + 255) / 256 * 256 + (ns * 4 + 255) / 256 * 256 + 256;
 }
 
-int muscle_field_loss(const float* dense_ft, const float* mask, int batch, int channels, int num_classes,
-                      int height, int width, const int32_t* planes, const int64_t* offsets, const int32_t* sel,
-                      const int32_t* lists, int n_active, int k, float* loss_out, float* ddense_out, void* scratch,
-                      size_t scratch_bytes, void* stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+}  // extern "C"
+
+namespace {
+// dense_ft [batch, channels, height, width] (small_h == 0) or p3_dec [batch, channels, small_h, small_w] interpolated on the fly
+int field_loss_impl(const float* dense_ft, int small_h, int small_w, const float* mask, int batch, int channels,
+                    int num_classes, int height, int width, const int32_t* planes, const int64_t* offsets,
+                    const int32_t* sel, const int32_t* lists, int n_active, int k, float* loss_out, float* ddense_out,
+                    void* scratch, size_t scratch_bytes, cudaStream_t stream) {
   if (int rc = need_sm100()) return rc;
   if (!dense_ft || !mask || !planes || !offsets || !sel || !lists || !loss_out || !scratch)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
@@ -465,20 +559,64 @@ int muscle_field_loss(const float* dense_ft, const float* mask, int batch, int c
   int* pix = reinterpret_cast<int*>(base + off);
   off += (ns * 4 + 255) / 256 * 256;
   double* acc = reinterpret_cast<double*>(base + off);
+  UpGeom up{small_h, small_w, width, small_h > 0 ? bilinear_scale(small_h, height) : 0.f,
+            small_h > 0 ? bilinear_scale(small_w, width) : 0.f};
+  const size_t grad_elems = static_cast<size_t>(batch) * channels * (small_h > 0 ? static_cast<size_t>(small_h) * small_w : static_cast<size_t>(HW));
   MB_CUDA(cudaMemsetAsync(acc, 0, sizeof(double), stream));
-  if (ddense_out) MB_CUDA(cudaMemsetAsync(ddense_out, 0, static_cast<size_t>(batch) * channels * HW * sizeof(float), stream));
-  field_gather_softmax_kernel<<<static_cast<unsigned>((ns + 7) / 8), 256, 0, stream>>>(
-      dense_ft, mask, channels, num_classes, HW, planes, reinterpret_cast<const long long*>(offsets), sel, lists, k,
-      static_cast<int>(ns), probs_d, probs_m, pix);
+  if (ddense_out) MB_CUDA(cudaMemsetAsync(ddense_out, 0, grad_elems * sizeof(float), stream));
+  if (small_h > 0)
+    field_gather_up_softmax_kernel<<<static_cast<unsigned>((ns + 7) / 8), 256, 0, stream>>>(
+        dense_ft, mask, channels, num_classes, HW, up, planes, reinterpret_cast<const long long*>(offsets), sel, lists, k,
+        static_cast<int>(ns), probs_d, probs_m, pix);
+  else
+    field_gather_softmax_kernel<<<static_cast<unsigned>((ns + 7) / 8), 256, 0, stream>>>(
+        dense_ft, mask, channels, num_classes, HW, planes, reinterpret_cast<const long long*>(offsets), sel, lists, k,
+        static_cast<int>(ns), probs_d, probs_m, pix);
   MB_LAUNCH_CHECK();
   const size_t smem = (static_cast<size_t>(3) * channels + 64 + static_cast<size_t>(6) * k) * sizeof(float);
   if (smem > 200 * 1024) return fail(MUSCLE_ERR_BAD_ARG, "k or channel count too large for one block");
-  MB_CUDA(cudaFuncSetAttribute(field_plane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  if (int rc = ensure_dynamic_smem<field_plane_kernel>(200 * 1024)) return rc;
   const float inv_n = 1.f / static_cast<float>(batch);   // loss / n  (src/edge.py:359-360)
   field_plane_kernel<<<n_active, FP_THREADS, smem, stream>>>(probs_d, probs_m, pix, planes, channels, num_classes, HW, k,
-                                                             inv_n, acc, ddense_out);
+                                                             inv_n, acc, ddense_out, up);
   MB_LAUNCH_CHECK();
   field_final_kernel<<<1, 1, 0, stream>>>(acc, inv_n, loss_out);
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int muscle_field_loss(const float* dense_ft, const float* mask, int batch, int channels, int num_classes,
+                      int height, int width, const int32_t* planes, const int64_t* offsets, const int32_t* sel,
+                      const int32_t* lists, int n_active, int k, float* loss_out, float* ddense_out, void* scratch,
+                      size_t scratch_bytes, void* stream_) {
+  return field_loss_impl(dense_ft, 0, 0, mask, batch, channels, num_classes, height, width, planes, offsets, sel, lists,
+                         n_active, k, loss_out, ddense_out, scratch, scratch_bytes, static_cast<cudaStream_t>(stream_));
+}
+
+int muscle_field_loss_decoder(const float* p3_dec, int small_height, int small_width, const float* mask, int batch,
+                              int channels, int num_classes, int height, int width, const int32_t* planes,
+                              const int64_t* offsets, const int32_t* sel, const int32_t* lists, int n_active, int k,
+                              float* loss_out, float* dp3_out, void* scratch, size_t scratch_bytes, void* stream_) {
+  if (small_height <= 0 || small_width <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty decoder map");
+  return field_loss_impl(p3_dec, small_height, small_width, mask, batch, channels, num_classes, height, width, planes,
+                         offsets, sel, lists, n_active, k, loss_out, dp3_out, scratch, scratch_bytes,
+                         static_cast<cudaStream_t>(stream_));
+}
+
+int muscle_conv1x1_fwd(const float* x, const float* weight, const float* bias, int batch, int channels, int out_channels,
+                       int64_t pixels, float* y, void* stream_) {
+  if (int rc = need_sm100()) return rc;
+  if (!x || !weight || !y) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (batch <= 0 || channels <= 0 || pixels <= 0 || out_channels < 1 || out_channels > 32)
+    return fail(MUSCLE_ERR_BAD_ARG, "1 <= out_channels <= 32 and a non-empty input");
+  const size_t smem = static_cast<size_t>(out_channels) * channels * sizeof(float);
+  if (smem > 160 * 1024) return fail(MUSCLE_ERR_BAD_ARG, "weight matrix too large for shared memory");
+  if (int rc = ensure_dynamic_smem<conv1x1_kernel>(160 * 1024)) return rc;
+  conv1x1_kernel<<<dim3(static_cast<unsigned>((pixels + 127) / 128), batch), 128, smem, static_cast<cudaStream_t>(stream_)>>>(
+      x, weight, bias, channels, out_channels, pixels, y);
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
 }

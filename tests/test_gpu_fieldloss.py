@@ -173,3 +173,51 @@ def test_fieldloss_config3_size_every_plane(golden):
     # the loss is a signed sum of four means of similarities of magnitude 1/ch that nearly cancel on random
     # features (|loss| ~ 1e-6 here): 1e-3 relative, with a floor of 2e-4 of one term's magnitude
     assert abs(loss.item() - ref) <= 1e-3 * abs(ref) + 2e-4 / ch, (loss.item(), ref)
+
+
+def test_decoder_tail_into_fieldloss_golden(golden):
+    """model(img, cam='seg') tail (src/MuSCLe.py:285-286) + FieldLoss (train_muscle.py:196) from the
+    decoder output, dense_ft never formed, against the fixture minted by executing the reference's own lines."""
+    from muscle_b200.edge import FieldLoss
+    g = golden("decoder_tail")
+    crit = FieldLoss(sobel_size=5, beta=g["beta"], k=g["k"])
+    p3 = g["p3_dec"].cuda().requires_grad_()
+    random.seed(g["py_seed"])
+    loss, mag, seg = crit.forward_from_decoder(p3, g["fuse_w"].cuda(), g["fuse_b"].cuda(), g["mask"].cuda(),
+                                               g["label_bg"].cuda(), g["step"], g["size"])
+    torch.testing.assert_close(seg.cpu(), g["seg_map"], rtol=1e-4, atol=2e-4)     # |seg| reaches 120
+    assert torch.is_tensor(loss)
+    loss.backward()
+    assert abs(loss.item() - g["loss"].item()) <= 1e-3 * abs(g["loss"].item()) + 1e-7, (loss.item(), g["loss"].item())
+    assert _cos(p3.grad.cpu(), g["g_p3"]) >= 0.999
+    torch.testing.assert_close(mag.cpu(), g["mag"], rtol=5e-3, atol=5e-3)        # softmax(seg * 100): see the oracle test
+
+
+@pytest.mark.parametrize("n,hs,ws,up,ch,k,step", [(2, 16, 16, 8, 256, 16, 3), (3, 20, 14, 4, 64, 12, 5)])
+def test_decoder_tail_matches_materialised_path(n, hs, ws, up, ch, k, step):
+    """the fused tail == up-sampling + 1x1 conv in torch followed by the ordinary FieldLoss (same random stream)"""
+    from muscle_b200.edge import FieldLoss
+    gen = torch.Generator().manual_seed(hs * ch)
+    h, w = hs * up, ws * up
+    label = O.synth_labels(n, gen)
+    label_bg = torch.cat([torch.ones(n, 1), label], 1)
+    noise = F.avg_pool2d(torch.randn(n, 21, hs, ws, generator=gen), 5, 1, 2, count_include_pad=False)
+    noise = noise.masked_fill(~label_bg.bool()[:, :, None, None], -30.0) * 4
+    wmat = torch.randn(21, ch, generator=gen) / ch ** 0.5
+    bias = 0.1 * torch.randn(21, generator=gen)
+    p3 = (torch.einsum("ck,nkhw->nchw", torch.linalg.pinv(wmat), noise - bias[None, :, None, None])
+          + 0.2 * torch.randn(n, ch, hs, ws, generator=gen))
+    mask = F.interpolate(noise, size=(h, w), mode="bilinear", align_corners=True) * 0.7 + 0.3 * torch.randn(n, 21, h, w, generator=gen)
+    crit = FieldLoss(sobel_size=5, beta=1e2, k=k)
+    pa = p3.cuda().requires_grad_()
+    random.seed(3)
+    la, mag_a, seg_a = crit.forward_from_decoder(pa, wmat.cuda(), bias.cuda(), mask.cuda(), label_bg.cuda(), step, (h, w))
+    pb = p3.cuda().requires_grad_()
+    dense = F.interpolate(pb, size=(h, w), mode="bilinear", align_corners=True)
+    random.seed(3)
+    lb, mag_b = crit(seg_a, dense, mask.cuda(), label_bg.cuda(), step)       # same seg_map: the comparison is about dense_ft
+    assert torch.is_tensor(la) and torch.is_tensor(lb)
+    la.backward()
+    lb.backward()
+    assert abs(la.item() - lb.item()) <= 1e-4 * abs(lb.item()) + 1e-8
+    assert _cos(pa.grad, pb.grad) >= 0.9999
