@@ -621,6 +621,12 @@ def main():
     if env.world == 1 and args.workload is None and not args.no_sub:
         c3 = WORKLOADS["config3"]       # the largest single-GPU configuration: 65 536 pixels, D = 128, 21 classes
         pool = pool_record(env, c3["global_batch"] * c3["h"] * c3["w"], c3["dim"], NUM_CLASSES, args.steps)
+    ops = None
+    if env.world == 1 and args.workload is None and not args.no_sub:
+        # the other members of the path (PCM, CAM head, IMC, PixPro, EMD, FieldLoss, ER loss, ...): device time fwd+bwd
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import bench_ops
+        ops = bench_ops.collect(iters=10, with_cpu=False, big=True)
     if env.rank == 0:
         world = env.world
         launches_per_step = 8 if world == 1 else 10      # ours; NCCL's kernels are not counted
@@ -647,6 +653,8 @@ def main():
             line["configs"] = {k: v for k, v in subs.items() if v is not None}
         if pool is not None:
             line["roofline_pool"] = pool
+        if ops is not None:
+            line["ops"] = ops
         os.write(env.stdout_fd, (json.dumps(line) + "\n").encode())
     if env.world > 1:
         env.dist.destroy_process_group()

@@ -9,8 +9,7 @@
 // References: the positive-key mean of src/loss_multilabel.py:12 (0/1 weights), the region mean of
 // src/loss_multilabel.py:255 and the CAM aggregation `cam @ aff` of src/MuSCLe.py:222 (w = cam^T, no
 // division) are all instances.  Layout: e [N, D] pixel-major (bf16 = the sorted `ehat` of the InfoNCE
-// path, or fp32), w [N, C] pixel-major fp32, C <= 32, D % 128 == 0 or D in {32, 64} handled by a
-// generic lane mapping (D % 4 == 0, D <= 512).
+// path, or fp32), w [N, C] pixel-major fp32, C <= 24, D % 4 == 0, D <= 256 (generic lane mapping).
 //
 // Forward mapping: one warp = one pixel at a time, lane l owns the 4-channel groups l, l+32, ... of the
 // row (8-byte / 16-byte coalesced loads); the lane keeps C x (its channels) partial sums in registers
@@ -28,7 +27,9 @@ namespace {
 
 constexpr int POOL_THREADS = 256;
 constexpr int POOL_WARPS = POOL_THREADS / 32;
-constexpr int POOL_CHUNK = 64;      // pixels whose weights are staged per step
+constexpr int POOL_CHUNK = 64;      // backward: pixels per block
+constexpr int POOL_FCHUNK = 128;    // forward: pixels whose weights are staged per step
+constexpr int POOL_UNROLL = 4;      // rows in flight per warp (one row per warp left the kernels latency bound: 5 % of HBM)
 constexpr int POOL_MAXC = 24;
 
 __device__ __forceinline__ void load4(const float* row, int g, float (&v)[4]) {
@@ -41,73 +42,106 @@ __device__ __forceinline__ void load4(const __nv_bfloat16* row, int g, float (&v
   v[2] = __uint_as_float(t.y << 16); v[3] = __uint_as_float(t.y & 0xffff0000u);
 }
 
-// NG = 4-channel groups per lane (D = 128 NG): D = 128 -> 1, 256 -> 2; smaller D: lanes >= D/4 idle.
-// CM = compile-time bound of the class count (register blocking), C <= CM the actual one.
+// Forward.  One accumulator set [C x D] per BLOCK (an earlier version kept one per warp: its end-of-kernel
+// reduction moved as many values as the kernel read and ran at shared-memory-atomic speed, 65 us for 22 MB):
+// warp w owns the classes w, w + 8, w + 16 (CM = 24: three per warp), lane l the 4-channel groups l, l + 32, ...;
+// the chunk's rows are staged in shared memory once (coalesced 16-byte loads, the next chunk's in flight in
+// registers while this one is consumed) and every warp reads all of them: per pixel and warp one 8/16-byte
+// shared load, CPW broadcast weights and 2 CPW packed FMAs.  NG = 4-channel groups per lane (D <= 128: 1, else 2).
 template <typename T, int CM, int NG>
 __global__ void __launch_bounds__(POOL_THREADS) pool_fwd_kernel(const T* __restrict__ e, const float* __restrict__ w,
                                                                 long long n, int dim, int C, float* __restrict__ sum,
                                                                 float* __restrict__ mass) {
-  __shared__ float2 w_sm[POOL_CHUNK][CM];         // weights duplicated into both halves (FFMA2 operand)
-  __shared__ float mass_sm[POOL_MAXC];
-  extern __shared__ float red_sm[];               // [C][dim] block reduction
+  constexpr int CPW = (CM + POOL_WARPS - 1) / POOL_WARPS;      // classes per warp
+  constexpr int ROW16 = 128 * NG * static_cast<int>(sizeof(T)) / 16;   // 16-byte pieces per staged row (row padded to 128 NG)
+  constexpr int PIECES = POOL_FCHUNK * ROW16 / POOL_THREADS;   // per thread and chunk
+  __shared__ float2 w_sm[POOL_FCHUNK][CM];                     // weights duplicated into both halves (FFMA2 operand)
+  extern __shared__ uint4 rows_sm[];                           // [POOL_FCHUNK][ROW16]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int groups = dim / 4;
-  if (threadIdx.x < POOL_MAXC) mass_sm[threadIdx.x] = 0.f;
-  for (int i = threadIdx.x; i < C * dim; i += POOL_THREADS) red_sm[i] = 0.f;
-  uint64_t acc[CM][NG][2];
+  const int row16 = dim * static_cast<int>(sizeof(T)) / 16;    // valid 16-byte pieces per row
+  uint64_t acc[CPW][NG][2];
 #pragma unroll
-  for (int c = 0; c < CM; ++c)
+  for (int k = 0; k < CPW; ++k)
 #pragma unroll
-    for (int g = 0; g < NG; ++g) acc[c][g][0] = acc[c][g][1] = 0ull;
-  __syncthreads();
-  const long long n_chunks = (n + POOL_CHUNK - 1) / POOL_CHUNK;
-  for (long long ch = blockIdx.x; ch < n_chunks; ch += gridDim.x) {
-    const long long p0 = ch * POOL_CHUNK;
-    const int np = static_cast<int>(min(static_cast<long long>(POOL_CHUNK), n - p0));
-    // stage the chunk's weights (coalesced) and their per-class sums
+    for (int g = 0; g < NG; ++g) acc[k][g][0] = acc[k][g][1] = 0ull;
+  float macc[CPW];
+#pragma unroll
+  for (int k = 0; k < CPW; ++k) macc[k] = 0.f;
+  const long long n_chunks = (n + POOL_FCHUNK - 1) / POOL_FCHUNK;
+  uint4 pre[PIECES];
+  auto fetch = [&](long long ch) {                             // the chunk's rows -> registers (coalesced)
+    const long long p0 = ch * POOL_FCHUNK;
+#pragma unroll
+    for (int i = 0; i < PIECES; ++i) {
+      const int idx = threadIdx.x + i * POOL_THREADS;
+      const int pp = idx / ROW16, q = idx - pp * ROW16;
+      pre[i] = (p0 + pp < n && q < row16) ? __ldg(reinterpret_cast<const uint4*>(e + (p0 + pp) * dim) + q) : make_uint4(0u, 0u, 0u, 0u);
+    }
+  };
+  long long ch = blockIdx.x;
+  if (ch < n_chunks) fetch(ch);
+  for (; ch < n_chunks; ch += gridDim.x) {
+    const long long p0 = ch * POOL_FCHUNK;
+    const int np = static_cast<int>(min(static_cast<long long>(POOL_FCHUNK), n - p0));
+    __syncthreads();                                           // the previous chunk has been consumed
+#pragma unroll
+    for (int i = 0; i < PIECES; ++i) rows_sm[threadIdx.x + i * POOL_THREADS] = pre[i];
     for (int i = threadIdx.x; i < np * C; i += POOL_THREADS) {
       const float v = __ldg(w + p0 * C + i);
       w_sm[i / C][i % C] = make_float2(v, v);
-      if (v != 0.f) atomicAdd(&mass_sm[i % C], v);
     }
     __syncthreads();
-    for (int pp = warp; pp < np; pp += POOL_WARPS) {
-      const T* row = e + (p0 + pp) * dim;
+    if (ch + gridDim.x < n_chunks) fetch(ch + gridDim.x);      // next chunk in flight under this one's arithmetic
+    for (int pp = 0; pp < np; ++pp) {
       float v[NG][4];
 #pragma unroll
-      for (int g = 0; g < NG; ++g)
-        if (lane + 32 * g < groups) load4(row, lane + 32 * g, v[g]);
-        else v[g][0] = v[g][1] = v[g][2] = v[g][3] = 0.f;
+      for (int g = 0; g < NG; ++g) {
+        if (sizeof(T) == 2) {
+          const uint2 t = reinterpret_cast<const uint2*>(rows_sm + pp * ROW16)[lane + 32 * g];
+          v[g][0] = __uint_as_float(t.x << 16); v[g][1] = __uint_as_float(t.x & 0xffff0000u);
+          v[g][2] = __uint_as_float(t.y << 16); v[g][3] = __uint_as_float(t.y & 0xffff0000u);
+        } else {
+          const uint4 t = rows_sm[pp * ROW16 + lane + 32 * g];
+          v[g][0] = __uint_as_float(t.x); v[g][1] = __uint_as_float(t.y);
+          v[g][2] = __uint_as_float(t.z); v[g][3] = __uint_as_float(t.w);
+        }
+      }
 #pragma unroll
-      for (int c = 0; c < CM; ++c) {
+      for (int k = 0; k < CPW; ++k) {
+        const int c = warp + POOL_WARPS * k;
         if (c < C) {
-          const uint64_t wc = *reinterpret_cast<const uint64_t*>(&w_sm[pp][c]);
+          const float2 wv = w_sm[pp][c];
+          const uint64_t wc = pack2(wv.x, wv.y);
+          macc[k] += wv.x;
 #pragma unroll
           for (int g = 0; g < NG; ++g) {
-            acc[c][g][0] = fma2(pack2(v[g][0], v[g][1]), wc, acc[c][g][0]);
-            acc[c][g][1] = fma2(pack2(v[g][2], v[g][3]), wc, acc[c][g][1]);
+            acc[k][g][0] = fma2(pack2(v[g][0], v[g][1]), wc, acc[k][g][0]);
+            acc[k][g][1] = fma2(pack2(v[g][2], v[g][3]), wc, acc[k][g][1]);
           }
         }
       }
     }
-    __syncthreads();
   }
-  // block reduction through shared memory (one atomic per (class, channel) and warp), then one global atomic each
+  // one global atomic per (class, channel) and block
 #pragma unroll
-  for (int c = 0; c < CM; ++c)
+  for (int k = 0; k < CPW; ++k) {
+    const int c = warp + POOL_WARPS * k;
+    if (c >= C) continue;
 #pragma unroll
     for (int g = 0; g < NG; ++g)
-      if (c < C && lane + 32 * g < groups) {
+      if (lane + 32 * g < groups) {
         float a0, a1, a2, a3;
-        unpack2(acc[c][g][0], a0, a1);
-        unpack2(acc[c][g][1], a2, a3);
-        float* dst = red_sm + c * dim + 4 * (lane + 32 * g);
-        atomicAdd(dst, a0); atomicAdd(dst + 1, a1); atomicAdd(dst + 2, a2); atomicAdd(dst + 3, a3);
+        unpack2(acc[k][g][0], a0, a1);
+        unpack2(acc[k][g][1], a2, a3);
+        float* dst = sum + c * dim + 4 * (lane + 32 * g);
+        if (a0 != 0.f) atomicAdd(dst, a0);
+        if (a1 != 0.f) atomicAdd(dst + 1, a1);
+        if (a2 != 0.f) atomicAdd(dst + 2, a2);
+        if (a3 != 0.f) atomicAdd(dst + 3, a3);
       }
-  __syncthreads();
-  for (int i = threadIdx.x; i < C * dim; i += POOL_THREADS)
-    if (red_sm[i] != 0.f) atomicAdd(sum + i, red_sm[i]);
-  if (threadIdx.x < C && mass_sm[threadIdx.x] != 0.f) atomicAdd(mass + threadIdx.x, mass_sm[threadIdx.x]);
+    if (lane == 0 && macc[k] != 0.f) atomicAdd(mass + c, macc[k]);
+  }
 }
 
 // proto = sum / max(mass, eps)
@@ -146,31 +180,44 @@ __global__ void __launch_bounds__(POOL_THREADS) pool_bwd_kernel(const T* __restr
   const int np = static_cast<int>(min(static_cast<long long>(POOL_CHUNK), n - p0));
   for (int i = threadIdx.x; i < np * C; i += POOL_THREADS) w_sm[i / C][i % C] = __ldg(w + p0 * C + i);
   __syncthreads();
-  // phase A
-  for (int pp = warp; pp < np; pp += POOL_WARPS) {
-    const T* row = e + (p0 + pp) * dim;
+  // phase A  (ds read from shared memory per class: keeping the lane's slice of ds in registers instead -- 84 of
+  // them -- drops the occupancy to one block per SM and measured 111 us against 70 us at 65 536 pixels)
+  for (int pp0 = warp; pp0 < np; pp0 += POOL_WARPS * POOL_UNROLL) {
+    float v[POOL_UNROLL][NG][4];
 #pragma unroll
-    for (int g = 0; g < NG; ++g) {
-      const int gi = lane + 32 * g;
-      if (gi >= groups) continue;
-      float v[4];
-      load4(row, gi, v);
-      if (dw != nullptr) *reinterpret_cast<float4*>(e_sm + pp * estride + 4 * gi) = make_float4(v[0], v[1], v[2], v[3]);
-      if (de != nullptr) {
-        uint64_t a0 = 0ull, a1 = 0ull;
+    for (int u = 0; u < POOL_UNROLL; ++u) {                      // row loads first: POOL_UNROLL lines in flight per warp
+      const int pp = pp0 + u * POOL_WARPS;
 #pragma unroll
-        for (int c = 0; c < CM; ++c) {
-          if (c < C) {
-            const float wc = w_sm[pp][c];
-            const float4 s4 = *reinterpret_cast<const float4*>(ds + c * dim + 4 * gi);
-            a0 = fma2(pack2(s4.x, s4.y), pack2(wc, wc), a0);
-            a1 = fma2(pack2(s4.z, s4.w), pack2(wc, wc), a1);
+      for (int g = 0; g < NG; ++g)
+        if (pp < np && lane + 32 * g < groups) load4(e + (p0 + pp) * dim, lane + 32 * g, v[u][g]);
+    }
+#pragma unroll
+    for (int u = 0; u < POOL_UNROLL; ++u) {
+      const int pp = pp0 + u * POOL_WARPS;
+      if (pp >= np) break;
+#pragma unroll
+      for (int g = 0; g < NG; ++g) {
+        const int gi = lane + 32 * g;
+        if (gi >= groups) continue;
+        if (dw != nullptr)
+          *reinterpret_cast<float4*>(e_sm + pp * estride + 4 * gi) = make_float4(v[u][g][0], v[u][g][1], v[u][g][2], v[u][g][3]);
+        if (de != nullptr) {
+          uint64_t a0 = 0ull, a1 = 0ull;
+#pragma unroll
+          for (int c = 0; c < CM; ++c) {
+            if (c < C) {
+              const float wc = w_sm[pp][c];
+              const uint64_t wc2 = pack2(wc, wc);
+              const float4 s4 = *reinterpret_cast<const float4*>(ds + c * dim + 4 * gi);
+              a0 = fma2(pack2(s4.x, s4.y), wc2, a0);
+              a1 = fma2(pack2(s4.z, s4.w), wc2, a1);
+            }
           }
+          float r0, r1, r2, r3;
+          unpack2(a0, r0, r1);
+          unpack2(a1, r2, r3);
+          *reinterpret_cast<float4*>(de + (p0 + pp) * dim + 4 * gi) = make_float4(r0, r1, r2, r3);
         }
-        float r0, r1, r2, r3;
-        unpack2(a0, r0, r1);
-        unpack2(a1, r2, r3);
-        *reinterpret_cast<float4*>(de + (p0 + pp) * dim + 4 * gi) = make_float4(r0, r1, r2, r3);
       }
     }
   }
@@ -217,16 +264,21 @@ int check_pool_args(int64_t n, int dim, int C) {
   return MUSCLE_OK;
 }
 
-template <typename T, int NG>
-int launch_fwd(const T* e, const float* w, int64_t n, int dim, int C, float* sum, float* mass, cudaStream_t stream) {
-  const long long n_chunks = (n + POOL_CHUNK - 1) / POOL_CHUNK;
+template <typename T, int CM, int NG>
+int launch_fwd_cm(const T* e, const float* w, int64_t n, int dim, int C, float* sum, float* mass, cudaStream_t stream) {
+  const long long n_chunks = (n + POOL_FCHUNK - 1) / POOL_FCHUNK;
   const int grid = static_cast<int>(std::min<long long>(n_chunks, 2ll * device_info().sm_count));
-  const size_t smem = static_cast<size_t>(C) * dim * sizeof(float);
-  if (C <= 8) pool_fwd_kernel<T, 8, NG><<<grid, POOL_THREADS, smem, stream>>>(e, w, n, dim, C, sum, mass);
-  else if (C <= 16) pool_fwd_kernel<T, 16, NG><<<grid, POOL_THREADS, smem, stream>>>(e, w, n, dim, C, sum, mass);
-  else pool_fwd_kernel<T, 24, NG><<<grid, POOL_THREADS, smem, stream>>>(e, w, n, dim, C, sum, mass);
+  const size_t smem = static_cast<size_t>(POOL_FCHUNK) * 128 * NG * sizeof(T);
+  if (int rc = ensure_dynamic_smem<pool_fwd_kernel<T, CM, NG>>(static_cast<int>(smem))) return rc;
+  pool_fwd_kernel<T, CM, NG><<<grid, POOL_THREADS, smem, stream>>>(e, w, n, dim, C, sum, mass);
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
+}
+template <typename T, int NG>
+int launch_fwd(const T* e, const float* w, int64_t n, int dim, int C, float* sum, float* mass, cudaStream_t stream) {
+  if (C <= 8) return launch_fwd_cm<T, 8, NG>(e, w, n, dim, C, sum, mass, stream);
+  if (C <= 16) return launch_fwd_cm<T, 16, NG>(e, w, n, dim, C, sum, mass, stream);
+  return launch_fwd_cm<T, 24, NG>(e, w, n, dim, C, sum, mass, stream);
 }
 
 template <typename T, int CM, int NG>

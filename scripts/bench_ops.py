@@ -21,10 +21,13 @@ import torch
 import torch.nn.functional as F
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--iters", type=int, default=20)
-    args = ap.parse_args()
+def collect(iters=20, with_cpu=True, big=True):
+    """-> dict of op records (device ms fwd+bwd, roofline-style figures; the oracle's CPU time beside each when
+    `with_cpu`).  `big`: include the config-3-size FieldLoss entries (8.6 GB of device memory)."""
+    class _A:
+        pass
+    args = _A()
+    args.iters = iters
     from muscle_b200 import heads
     from muscle_b200.edge import FieldLoss
     from muscle_b200.loss_multilabel import EMD, PixPro, image_level_contrast
@@ -48,7 +51,10 @@ def main():
         return sum(x.elapsed_time(y) for x, y in evs) / len(evs)
 
     import time
-    from oracle import muscle_oracle as O   # CPU baseline legs + synthetic label generator
+    import workloads
+    O = None
+    if with_cpu:
+        from oracle import muscle_oracle as O   # CPU baseline legs only (the checker is never on the product arm's path)
 
     def cpu_timed(fn, budget_s=6.0, max_reps=5):
         fn()
@@ -57,7 +63,10 @@ def main():
             t0 = time.perf_counter(); fn(); t += time.perf_counter() - t0; reps += 1
         return 1e3 * t / reps
 
-    def beside(entry, cpu_ms):
+    def beside(entry, cpu_fn, **kw):
+        if not with_cpu:
+            return entry
+        cpu_ms = cpu_timed(cpu_fn, **kw)
         entry["cpu_ms"] = cpu_ms
         entry["cpu_cores"] = torch.get_num_threads()
         entry["cpu_kind"] = "port (oracle, fp32 torch CPU, same inputs)"
@@ -90,7 +99,7 @@ def main():
         cam_c.grad = wt_c.grad = b_c.grad = None
     out["pcm_fwd_bwd_config2_stride8"] = beside(dict(ms=ms, pixel_pairs_per_s=pairs / ms * 1e3, executed_tflops=flops / ms / 1e9,
                                                      frac_of_bf16_burst=flops / ms / 1e9 / peaks["bf16_tflops"], bound="tensor"),
-                                                cpu_timed(pcm_cpu))
+                                                pcm_cpu)
     p7 = torch.relu(torch.randn(B, 640, P_h, P_h, generator=gen)).to(dev).requires_grad_()
     fw = (torch.randn(21, 640, generator=gen) * 0.05).to(dev).requires_grad_()
     gcam = torch.randn(B, 21, P_h, P_h, generator=gen).to(dev)
@@ -111,10 +120,10 @@ def main():
         p7_c.grad = fw_c.grad = None
     out["cam_head_gap_logits_fwd_bwd"] = beside(dict(ms=ms, algorithmic_gb_s=byt / ms / 1e6,
                                                      frac_of_hbm=byt / ms / 1e6 / peaks["hbm_gbs"], bound="hbm"),
-                                                cpu_timed(cam_cpu))
+                                                cam_cpu)
     # ---- IMC, B=64 images, ch=640
     emb = torch.randn(64, 640, generator=gen).abs().to(dev).requires_grad_()
-    lab = O.synth_labels(64, gen).to(dev)
+    lab = workloads.synth_labels(64, gen).to(dev)
 
     def imc_step():
         l = image_level_contrast(emb, lab)
@@ -128,7 +137,7 @@ def main():
         if torch.is_tensor(l):
             l.backward()
         emb_c.grad = None
-    out["imc_fwd_bwd_B64"] = beside(dict(ms=timed(imc_step), bound="latency"), cpu_timed(imc_cpu))
+    out["imc_fwd_bwd_B64"] = beside(dict(ms=timed(imc_step), bound="latency"), imc_cpu)
     # ---- PixPro, B=8, 21x224x224
     fm1 = torch.rand(8, 21, 224, 224, generator=gen).to(dev).requires_grad_()
     fm2 = torch.rand(8, 21, 224, 224, generator=gen).to(dev)
@@ -146,7 +155,7 @@ def main():
     def pix_cpu():
         O.pixpro(fm1_c, fm2_c, c1, c2).backward()
         fm1_c.grad = None
-    out["pixpro_fwd_bwd_B8"] = beside(dict(ms=ms, algorithmic_gb_s=byt / ms / 1e6, bound="hbm/latency"), cpu_timed(pix_cpu))
+    out["pixpro_fwd_bwd_B8"] = beside(dict(ms=ms, algorithmic_gb_s=byt / ms / 1e6, bound="hbm/latency"), pix_cpu)
     # ---- crops + EMD dynamic, B=8
     raw1 = F.avg_pool2d(torch.randn(8, 21, 224, 224, generator=gen), 9, 1, 4).to(dev).requires_grad_()
     raw2 = F.avg_pool2d(torch.randn(8, 21, 224, 224, generator=gen), 9, 1, 4).to(dev)
@@ -166,7 +175,7 @@ def main():
         a, b, _ = O.get_dynamic_crops(v1, c1, v2.detach(), c2, rng=np.random.RandomState(3))
         O.emd_dynamic(a, b).backward()
         raw1_c.grad = None
-    out["crops_emd_dynamic_fwd_bwd_B8"] = beside(dict(ms=timed(emd_step), bound="latency"), cpu_timed(emd_cpu))
+    out["crops_emd_dynamic_fwd_bwd_B8"] = beside(dict(ms=timed(emd_step), bound="latency"), emd_cpu)
     # ---- static crops + EMD static (the class's default mode), same CAM maps
     from muscle_b200.torchutils import get_static_crops
 
@@ -185,10 +194,10 @@ def main():
         raw1_c.grad = None
     out["crops_emd_static_fwd_bwd_B8"] = beside(dict(ms=timed(emd_static_step), bound="latency",
                                                      note="72 window pairs; windows gathered by one launch per view (muscle_crops_fwd), 3 launches for the matching"),
-                                                cpu_timed(emd_static_cpu))
+                                                emd_static_cpu)
     # ---- FieldLoss, config 3 scale reduced to B=4 (512x512, 256 ch) to bound memory in this table
     n, h, w, ch = 4, 512, 512, 256
-    label = O.synth_labels(n, gen)
+    label = workloads.synth_labels(n, gen)
     label_bg = torch.cat([torch.ones(n, 1), label], 1)
     noise = F.avg_pool2d(torch.randn(n, 21, h, w, generator=gen), 31, 1, 15, count_include_pad=False)
     noise = noise.masked_fill(~label_bg.bool()[:, :, None, None], -1e4)
@@ -215,8 +224,92 @@ def main():
         dense_c.grad = None
     out["fieldloss_fwd_bwd_B4_512"] = beside(dict(ms=ms, note="includes the one device->host read of the counts and the "
                                                   "memset of the dense gradient (%.0f MB)" % (dense.numel() * 4 / 1e6),
-                                                  bound="hbm/latency"), cpu_timed(field_cpu, budget_s=10.0, max_reps=2))
-    print(json.dumps(out))
+                                                  bound="hbm/latency"), field_cpu, budget_s=10.0, max_reps=2)
+    # ---- ER loss at config 2's full resolution: B=8, 21 x 448 x 448, from stride-8 maps
+    from muscle_b200.er import er_loss, upsample_bilinear
+    cams_s = torch.relu(torch.randn(8, 21, 56, 56, generator=gen)).to(dev)
+    sgcs_s = torch.relu(torch.randn(8, 21, 56, 56, generator=gen) + 0.3).to(dev).requires_grad_()
+    lab8 = workloads.synth_labels(8, gen).to(dev)
+
+    def er_step():
+        l = er_loss(upsample_bilinear(cams_s, (448, 448)), upsample_bilinear(sgcs_s, (448, 448)), lab8)
+        l.backward()
+        sgcs_s.grad = None
+    ms = timed(er_step)
+    full = 8 * 21 * 448 * 448 * 4
+    byt = 2 * full + 3 * 2 * full + (2 * full + full) + 2 * full      # 2 up-samplings written, 3 select passes, bwd, adjoint
+    cams_c, sgcs_c, lab8_c = cams_s.cpu(), cpu_leaf(sgcs_s), lab8.cpu()
+
+    def er_cpu():
+        O.er_loss(O.upsample_bilinear(cams_c, (448, 448)), O.upsample_bilinear(sgcs_c, (448, 448)), lab8_c).backward()
+        sgcs_c.grad = None
+    out["er_loss_upsample_fwd_bwd_B8_448"] = beside(dict(ms=ms, algorithmic_gb_s=byt / ms / 1e6,
+                                                         frac_of_hbm=byt / ms / 1e6 / peaks["hbm_gbs"], bound="hbm",
+                                                         note="two 8x bilinear up-samplings + three radix-select passes "
+                                                              "+ backward + adjoint; no host sync"), er_cpu, max_reps=2)
+    # ---- classification losses (8f rank 4), B=16
+    from muscle_b200.loss_multilabel import mcl_cls_loss
+    lg = (torch.randn(16, 21, generator=gen) * 2).to(dev).requires_grad_()
+    lab16 = workloads.synth_labels(16, gen).to(dev)
+
+    def cls_step():
+        mcl_cls_loss(lg, lab16)[0].backward()
+        lg.grad = None
+    lg_c, lab16_c = cpu_leaf(lg), lab16.cpu()
+
+    def cls_cpu():
+        O.mcl_cls_loss(lg_c, lab16_c)[0].backward()
+        lg_c.grad = None
+    out["cls_losses_fwd_bwd_B16"] = beside(dict(ms=timed(cls_step), bound="latency"), cls_cpu)
+    if big:
+        # ---- FieldLoss at BASELINE config 3's size: B=16, 512x512, 256 channels, k=128, step=7 — the materialised
+        # path (the trainer's: dense_ft [16,256,512,512] exists) and the decoder-tail path (8f rank 2: from p3_dec)
+        n, hs, ws, ch, h, w = 16, 64, 64, 256, 512, 512
+        label = workloads.synth_labels(n, gen)
+        label_bg = torch.cat([torch.ones(n, 1), label], 1)
+        noise = F.avg_pool2d(torch.randn(n, 21, hs, ws, generator=gen), 5, 1, 2, count_include_pad=False)
+        noise = noise.masked_fill(~label_bg.bool()[:, :, None, None], -3.0)
+        wmat = (torch.randn(21, ch, generator=gen) / ch ** 0.5)
+        bias2 = 0.1 * torch.randn(21, generator=gen)
+        p3 = (torch.einsum("ck,nkhw->nchw", torch.linalg.pinv(wmat), noise - bias2[None, :, None, None])
+              + 0.2 * torch.randn(n, ch, hs, ws, generator=gen)).to(dev).requires_grad_()
+        mask16 = (F.interpolate(noise, size=(h, w), mode="bilinear", align_corners=True) * 0.7).to(dev)
+        wd, bd, lbg16 = wmat.to(dev), bias2.to(dev), label_bg.to(dev)
+        crit16 = FieldLoss(sobel_size=5, beta=1e2, k=128)
+
+        def tail_step():
+            random.seed(1)
+            l, _, _ = crit16.forward_from_decoder(p3, wd, bd, mask16, lbg16, 7, (h, w))
+            if torch.is_tensor(l):
+                l.backward()
+            p3.grad = None
+        ms_tail = timed(tail_step)
+
+        def mat_step():     # what the reference's data flow costs on this path: dense_ft and seg_map at full resolution
+            random.seed(1)
+            dense16 = upsample_bilinear(p3, (h, w))
+            seg16 = torch.nn.functional.conv2d(dense16.detach(), wd[:, :, None, None], bd)
+            l, _ = crit16(seg16, dense16, mask16, lbg16, 7)
+            if torch.is_tensor(l):
+                l.backward()
+            p3.grad = None
+        ms_mat = timed(mat_step)
+        out["fieldloss_decoder_tail_fwd_bwd_B16_512"] = dict(
+            ms=ms_tail, bound="hbm/latency",
+            note="config 3: p3_dec [16,256,64,64] -> loss + d p3_dec; dense_ft [16,256,512,512] (4.3 GB) never formed")
+        out["fieldloss_materialised_fwd_bwd_B16_512"] = dict(
+            ms=ms_mat, bound="hbm",
+            note="same inputs with dense_ft up-sampled to full resolution first (the reference's data flow; fuse_dec by "
+                 "torch conv2d), then the ordinary FieldLoss and the adjoint of the up-sampling")
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    print(json.dumps(collect(args.iters, not args.no_cpu)))
 
 
 if __name__ == "__main__":
