@@ -430,6 +430,16 @@ int muscle_field_loss_decoder(const float* p3_dec, int small_height, int small_w
 int muscle_conv1x1_fwd(const float* x, const float* weight, const float* bias, int batch, int channels,
                        int out_channels, int64_t pixels, float* y, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * SURVEY.md 8f rank 3 — IRN random walk (src/indexing.py:116-150; inference-time refinement, no gradient).
+ * muscle_irn_transition_init: trans_out[i][j] = affinity[i][j]^beta / sum_i affinity[i][j]^beta  ([n, n] row-major;
+ * colsum_scratch float[n]) — the element-wise half of to_transition_matrix (:117-119) in two passes.  The `times`
+ * squarings (:120-121) and the final product (:147) are plain dense fp32 GEMMs and are left to the GEMM library by
+ * the Python mirror (muscle_b200.indexing).  muscle_irn_mask_edge: y = x * (1 - edge) (:145), x [planes, hw], edge [hw]. */
+int muscle_irn_transition_init(const float* affinity, int n, float beta, float* colsum_scratch,
+                               float* trans_out, void* stream);
+int muscle_irn_mask_edge(const float* x, const float* edge, int planes, int hw, float* y, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

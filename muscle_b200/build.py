@@ -18,7 +18,7 @@ LIBDIR = os.path.join(HERE, "lib")
 OBJDIR = os.path.join(LIBDIR, "obj")
 LIB = os.path.join(LIBDIR, "libmuscle_b200.so")
 
-SOURCES = ["infonce.cu", "debug_tile.cu", "small_losses.cu", "pcm.cu", "fieldloss.cu", "emd.cu", "infonce_qk.cu", "pool.cu", "cls_losses.cu", "er.cu"]
+SOURCES = ["infonce.cu", "debug_tile.cu", "small_losses.cu", "pcm.cu", "fieldloss.cu", "emd.cu", "infonce_qk.cu", "pool.cu", "cls_losses.cu", "er.cu", "irn.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
