@@ -70,8 +70,11 @@ def peaks():
 class ClockSampler:
     """Samples SM clock and throttle reasons of one GPU while the timed region runs."""
 
-    def __init__(self, index):
+    def __init__(self, index, period_s=0.02):
+        # NVML clock / event-reason queries take ~2 ms each and serialise in the driver across processes: polled
+        # flat out from every rank they showed up in the 8-rank step time, so ONE rank samples, every 20 ms
         self.index = index
+        self.period_s = period_s
         self.samples, self.reasons = [], set()
         self.max_mhz = None
         self._stop = threading.Event()
@@ -99,7 +102,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            time.sleep(0.002)
+            self._stop.wait(self.period_s)
 
     def start(self):
         if self.nv is not None:
@@ -345,11 +348,17 @@ def measure(env, key, wl, steps, warmup, bg_bias, e2e_runs_n, with_fused, cpu_bu
     for _ in range(warm_run):
         step_device()
     env.barrier()
-    sampler = ClockSampler(env.local_rank)
-    sampler.start()
+    # rank 0's GPU speaks for the box
+    sampler = ClockSampler(env.local_rank, 0.02 if world > 1 else 0.004) if rank == 0 else None
+    if sampler is not None:
+        sampler.start()
+    gc_was = gc.isenabled()
+    gc.disable()                      # (as in the end-to-end loop below: a collection costs several short steps)
     t_dev = env.timed_block(step_device, steps) if big else env.timed(step_device, steps)
+    if gc_was:
+        gc.enable()
     env.barrier()
-    clocks = sampler.stop()
+    clocks = sampler.stop() if sampler is not None else None
     loss_value = float(last["loss"].item())
     for _ in range(3):
         step_e2e()
@@ -457,13 +466,22 @@ def measure(env, key, wl, steps, warmup, bg_bias, e2e_runs_n, with_fused, cpu_bu
     rs_tmp = st.zeros((rows_pad,), f32)
     sym = dim <= 128 and os.environ.get("MUSCLE_ROWSUM_SYM", "1") != "0"
     if sym:
-        uo_sym = st.empty((rows_pad // 128 + 1,), i32)
         rs_all = st.zeros((cols_pad,), f32)
-        st.plan_sym_ring(state["tor"], rows_pad, state["tor_all"], cols_pad, rank, world, uo_sym)
+        if world > 1 and os.environ.get("MUSCLE_ROWSUM_RING", "0") != "1":    # as muscle_b200.dist does it: split by count
+            uo_sym = st.empty((cols_pad // 128 + 1,), i32)
+            st.plan_sym_ring(state["tor_all"], cols_pad, state["tor_all"], cols_pad, 0, 1, uo_sym)
 
-        def rowsum_fn():
-            st.rowsum_sym_ring(state["ehat"], state["bits"], state["tor"], rows_pad, state["ehat_all"], state["bits_all"],
-                               state["tor_all"], cols_pad, uo_sym, rank, world, dim, TEMPERATURE, rs_all)
+            def rowsum_fn():
+                st.rowsum_sym_share(state["ehat_all"], state["bits_all"], state["tor_all"], cols_pad, uo_sym, rank, world,
+                                    dim, TEMPERATURE, rs_all)
+        else:
+            uo_sym = st.empty((rows_pad // 128 + 1,), i32)
+            st.plan_sym_ring(state["tor"], rows_pad, state["tor_all"], cols_pad, rank, world, uo_sym)
+
+            def rowsum_fn():
+                st.rowsum_sym_ring(state["ehat"], state["bits"], state["tor"], rows_pad, state["ehat_all"],
+                                   state["bits_all"], state["tor_all"], cols_pad, uo_sym, rank, world, dim, TEMPERATURE,
+                                   rs_all)
         rowsum_kernel = "pair_sym_kernel<%d>" % dim
     else:
         def rowsum_fn():

@@ -224,8 +224,10 @@ bool rowsum_sym_enabled(int dim) {
 // receives the row sums of the rank's own rows (at rank * rows_pad) AND its column-sum contributions to the other ranks'
 int rowsum_sym(const void* ehat, const uint32_t* bits, const uint32_t* tor, int64_t rows_pad, const void* ehat_cols,
                const uint32_t* bits_cols, const uint32_t* tor_cols, int64_t cols_pad, const uint32_t* unit_off_sym,
-               int rank, int world, int dim, float temperature, float* rowsum_all, cudaStream_t stream) {
+               int rank, int world, int dim, float temperature, float* rowsum_all, cudaStream_t stream,
+               int share = 0, int n_shares = 1) {
   PairParams prm{};
+  prm.share_g = share; prm.share_G = n_shares;
   prm.bits_row = bits; prm.bits_col = bits_cols; prm.tor_row = tor; prm.tor_col = tor_cols;
   prm.rowsum = rowsum_all + static_cast<size_t>(rank) * rows_pad; prm.rowsum_cols = rowsum_all;
   prm.unit_off = unit_off_sym;
@@ -476,6 +478,20 @@ int muscle_infonce_rowsum_sym_ring(const void* ehat_rows, const uint32_t* bits_r
     return fail(MUSCLE_ERR_BAD_ARG, "every rank holds rows_pad rows (a multiple of 256) and cols_pad = world * rows_pad");
   return rowsum_sym(ehat_rows, bits_rows, tor_rows, rows_pad, ehat_cols, bits_cols, tor_cols, cols_pad, unit_off_sym, rank,
                     world, dim, temperature, rowsum_all, static_cast<cudaStream_t>(stream_));
+}
+
+int muscle_infonce_rowsum_sym_share(const void* ehat_all, const uint32_t* bits_all, const uint32_t* tor_all,
+                                    int64_t cols_pad, const uint32_t* unit_off_sym, int share, int n_shares, int dim,
+                                    float temperature, float* rowsum_all, void* stream_) {
+  if (int rc = check_device()) return rc;
+  if (!ehat_all || !bits_all || !tor_all || !unit_off_sym || !rowsum_all) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (dim != 64 && dim != 128) return fail(MUSCLE_ERR_BAD_ARG, "symmetric row-sum pass: dim must be 64 or 128 (got %d)", dim);
+  if (!(temperature >= kMinTemperature))
+    return fail(MUSCLE_ERR_BAD_ARG, "temperature must be >= %g (exp((s-1)/T) underflows fp32 below it)", kMinTemperature);
+  if (cols_pad % 256 || cols_pad <= 0 || n_shares < 1 || share < 0 || share >= n_shares)
+    return fail(MUSCLE_ERR_BAD_ARG, "cols_pad must be a positive multiple of 256 and 0 <= share < n_shares");
+  return rowsum_sym(ehat_all, bits_all, tor_all, cols_pad, ehat_all, bits_all, tor_all, cols_pad, unit_off_sym, 0, 1, dim,
+                    temperature, rowsum_all, static_cast<cudaStream_t>(stream_), share, n_shares);
 }
 
 int muscle_infonce_grad(const void* ehat_rows, const uint32_t* bits_rows,

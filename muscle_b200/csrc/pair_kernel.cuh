@@ -77,6 +77,7 @@ struct PairParams {
   float* rowsum_cols;        // symmetric pass: [cols_pad] row sums of ALL column pixels (== rowsum on one GPU)
   int rb_off;                // symmetric pass: global tile index of this rank's row tile 0
   int own_g, own_G;          // symmetric pass: this rank and the number of ranks (unit ownership, sym_owned)
+  int share_g, share_G;      // symmetric pass: the launch covers share share_g of share_G equal parts of the unit list (0 = 1)
   float* part;               // [PAIR_SLOTS][rows_pad][D]  MODE_GRAD: partial sum_k T_qk c_k
   float scale_log2;          // log2(e) / tau
   float mask_shift;          // extra exponent shift of a masked column in the MASK_BIAS form (see pair_mask_shift)

@@ -370,9 +370,15 @@ pair_sym_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constan
 
   if (warp == C::WARP_PRODUCER) {
     // ------------------------------------------------------------ TMA producer + work partition
-    const uint32_t total = __ldg(p.unit_off + p.n_row_blocks);
-    const uint32_t per = (total + gridDim.x - 1) / gridDim.x;
-    const uint64_t lo64 = static_cast<uint64_t>(per) * blockIdx.x;
+    // this launch's part of the unit list (all of it, or one of share_G equal parts: ranks that split ONE global
+    // list evenly finish together whatever their own images' class mix), then this CTA's even share of that
+    const uint32_t all_units = __ldg(p.unit_off + p.n_row_blocks);
+    const uint32_t sG = p.share_G > 1 ? static_cast<uint32_t>(p.share_G) : 1u;
+    const uint32_t sg = p.share_G > 1 ? static_cast<uint32_t>(p.share_g) : 0u;
+    const uint32_t base = static_cast<uint32_t>(static_cast<uint64_t>(all_units) * sg / sG);
+    const uint32_t total = static_cast<uint32_t>(static_cast<uint64_t>(all_units) * (sg + 1) / sG);
+    const uint32_t per = (total - base + gridDim.x - 1) / gridDim.x;
+    const uint64_t lo64 = base + static_cast<uint64_t>(per) * blockIdx.x;
     uint32_t u = lo64 < total ? static_cast<uint32_t>(lo64) : total;
     const uint32_t u1 = (lo64 + per < total) ? static_cast<uint32_t>(lo64 + per) : total;
     int rb = 0;

@@ -14,6 +14,8 @@ average the returned gradient across ranks again.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -64,7 +66,6 @@ def _all_gather_many(pairs, group):
 
 
 def _use_sym_ring(stages, dim):
-    import os
     if os.environ.get("MUSCLE_ROWSUM_SYM", "1") == "0":
         return False
     return hasattr(stages, "rowsum_sym_ring") and dim in stages.sym_dims()
@@ -129,15 +130,21 @@ def sharded_fwd(stages, x, cls, temperature, num_classes, eps, need_grad, group=
     unit_off = stages.empty((rows_pad // stages.unit_rows(dim) + 1,), i32)
     stages.plan(tor, rows_pad, tor_all, cols_pad, dim, unit_off)
     if sym:
-        # The global similarity matrix is symmetric: every unordered tile pair is computed ONCE, by the rank that owns
-        # it in the ring (stages.rowsum_sym_ring); a rank's pass leaves row sums for its own pixels and column-sum
-        # contributions for the others' in rowsum_all, and one all-reduce of N_g floats completes them.  Half the
-        # products and exponentials of the ordered pass for 4 bytes per global pixel of extra traffic.
+        # The global similarity matrix is symmetric: every unordered tile pair is computed ONCE.  Every rank numbers the
+        # live pairs of the gathered array identically and computes an equal contiguous share of that list (split by
+        # count, not by pixel block: the ranks finish together whatever their own images' class mix); a rank's pass
+        # leaves row- and column-sum contributions for ANY pixel in rowsum_all, and one all-reduce of N_g floats
+        # completes them.  Half the products and exponentials of the ordered pass for 4 bytes per global pixel.
         rowsum_all = zbuf[:cols_pad]
-        unit_off_sym = stages.empty((rows_pad // 128 + 1,), i32)
-        stages.plan_sym_ring(tor, rows_pad, tor_all, cols_pad, rank, G, unit_off_sym)
-        stages.rowsum_sym_ring(ehat, bits, tor, rows_pad, ehat_all, bits_all, tor_all, cols_pad, unit_off_sym, rank, G,
-                               dim, temperature, rowsum_all)
+        unit_off_sym = stages.empty((cols_pad // 128 + 1,), i32)
+        if hasattr(stages, "rowsum_sym_share") and os.environ.get("MUSCLE_ROWSUM_RING", "0") != "1":
+            stages.plan_sym_ring(tor_all, cols_pad, tor_all, cols_pad, 0, 1, unit_off_sym)
+            stages.rowsum_sym_share(ehat_all, bits_all, tor_all, cols_pad, unit_off_sym, rank, G, dim, temperature,
+                                    rowsum_all)
+        else:       # the split by pixel block (ring ownership; kept for A/B measurements: MUSCLE_ROWSUM_RING=1)
+            stages.plan_sym_ring(tor, rows_pad, tor_all, cols_pad, rank, G, unit_off_sym)
+            stages.rowsum_sym_ring(ehat, bits, tor, rows_pad, ehat_all, bits_all, tor_all, cols_pad, unit_off_sym, rank,
+                                   G, dim, temperature, rowsum_all)
         dist.all_reduce(red, group=group)
         rowsum = rowsum_all[sl]
     else:

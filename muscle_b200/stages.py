@@ -99,6 +99,17 @@ class CudaStages:
                 float(temperature), rowsum_all.data_ptr(), _sp(self.device))
         _lib.check(rc, "infonce_rowsum_sym_ring")
 
+    def rowsum_sym_share(self, ehat_all, bits_all, tor_all, cols_pad, unit_off_sym, share, n_shares, dim, temperature,
+                         rowsum_all):
+        """symmetric row-sum pass over the whole gathered array, split by COUNT: share `share` of `n_shares` equal
+        parts of the live unordered tile pairs (plan: plan_sym_ring over the gathered arrays, rank 0 of world 1);
+        rowsum_all [cols_pad] must be all-reduced (sum) afterwards"""
+        with torch.cuda.device(self.device):
+            rc = self.lib.muscle_infonce_rowsum_sym_share(
+                ehat_all.data_ptr(), bits_all.data_ptr(), tor_all.data_ptr(), cols_pad, unit_off_sym.data_ptr(), share,
+                n_shares, dim, float(temperature), rowsum_all.data_ptr(), _sp(self.device))
+        _lib.check(rc, "infonce_rowsum_sym_share")
+
     def sym_dims(self):
         return (64, 128)
 

@@ -54,7 +54,7 @@ def main():
             return out
         setattr(owner, name, timed)
 
-    for m in ("prepare", "plan", "plan_sym_ring", "rowsum", "rowsum_sym_ring", "mid", "grad", "final"):
+    for m in ("prepare", "plan", "plan_sym_ring", "rowsum", "rowsum_sym_ring", "rowsum_sym_share", "mid", "grad", "final"):
         wrap(CudaStages, m, m)
     wrap(MD.dist, "all_reduce", "nccl all_reduce")
     wrap(MD, "_all_gather_into", "nccl all_gather")

@@ -125,6 +125,26 @@ class CpuStages:
                 if j != rank * tiles + r:
                     rowsum_all[j * 128:(j + 1) * 128] += blk.sum(0)
 
+    def rowsum_sym_share(self, ehat_all, bits_all, tor_all, cols_pad, unit_off_sym, share, n_shares, dim, temperature,
+                         rowsum_all):
+        """the live unordered tile pairs of the whole gathered array, numbered row-major from the diagonal on
+        (include/muscle_b200.h: muscle_infonce_rowsum_sym_share); this rank computes one contiguous share"""
+        tiles = cols_pad // 128
+        t = _u32(tor_all).astype(np.int64) & 0x7fffffff
+        units = []
+        for r in range(tiles):
+            for j in range(r, tiles):
+                dead = t[r] == 0 or t[j] == 0 or (t[r] == t[j] and (t[r] & (t[r] - 1)) == 0)
+                if not dead:
+                    units.append((r, j))
+        lo, hi = len(units) * share // n_shares, len(units) * (share + 1) // n_shares
+        for r, j in units[lo:hi]:
+            blk = self._pair_weights(ehat_all[r * 128:(r + 1) * 128], bits_all[r * 128:(r + 1) * 128],
+                                     ehat_all[j * 128:(j + 1) * 128], bits_all[j * 128:(j + 1) * 128], temperature)
+            rowsum_all[r * 128:(r + 1) * 128] += blk.sum(1)
+            if j != r:
+                rowsum_all[j * 128:(j + 1) * 128] += blk.sum(0)
+
     def mid(self, ehat, seg, rows_pad, dim, num_classes, class_sum, class_mass, rowsum, temperature, w, gpos,
             loss_acc, dproto):
         w.zero_()

@@ -111,3 +111,39 @@ def test_ring_symmetric_pass_over_emulated_ranks(world, batch, d, h, w):
                if not (tc[a] == 0 or tc[b_] == 0 or (tc[a] == tc[b_] and (tc[a] & (tc[a] - 1)) == 0)))
     assert total_units == live
     torch.testing.assert_close(rs_all.cpu(), ref_all.cpu(), rtol=2e-3, atol=0)
+
+
+@pytest.mark.parametrize("world,batch,d,h,w", [(2, 4, 128, 24, 24), (3, 3, 64, 20, 20), (8, 8, 128, 16, 16), (5, 8, 128, 40, 40)])
+def test_share_split_symmetric_pass_over_emulated_ranks(world, batch, d, h, w):
+    """The split by COUNT (muscle_infonce_rowsum_sym_share): one plan over the gathered array (class-sorted per rank
+    block only), every emulated rank computes its contiguous share of the live unordered tile pairs into one
+    rowsum_all buffer; the total must equal the ordered pass over all rows x all columns.  (`world` shares need not
+    divide the batch: the shards here only fix how the gathered array is laid out.)"""
+    from muscle_b200.stages import CudaStages
+    st = CudaStages(torch.device("cuda", 0))
+    x, cls, _ = O.synth_embeddings(batch, d, h, w, seed=700 + world)
+    cls = cls.clone()
+    cls[0, :2] = -1
+    blocks = 2 if batch % 2 == 0 else batch
+    lb = batch // blocks
+    shards = [_prepare(st, x[r * lb:(r + 1) * lb], cls[r * lb:(r + 1) * lb]) for r in range(blocks)]
+    rp = shards[0][0]
+    ehat_all = torch.cat([s[1] for s in shards]).contiguous()
+    bits_all = torch.cat([s[2] for s in shards]).contiguous()
+    tor_all = torch.cat([s[3] for s in shards]).contiguous()
+    cp = rp * blocks
+    rs_all = st.zeros((cp,), torch.float32)
+    ref_all = st.zeros((cp,), torch.float32)
+    uo = st.empty((cp // 128 + 1,), torch.int32)
+    st.plan_sym_ring(tor_all, cp, tor_all, cp, 0, 1, uo)
+    for share in range(world):
+        st.rowsum_sym_share(ehat_all, bits_all, tor_all, cp, uo, share, world, d, 0.1, rs_all)
+    uo2 = st.empty((cp // 128 + 1,), torch.int32)
+    st.plan(tor_all, cp, tor_all, cp, d, uo2)
+    st.rowsum(ehat_all, bits_all, tor_all, cp, ehat_all, bits_all, tor_all, cp, uo2, d, 0.1, ref_all)
+    torch.cuda.synchronize()
+    tc = tor_all.cpu().numpy().astype("int64") & 0x7fffffff
+    live = sum(1 for a in range(len(tc)) for b_ in range(a, len(tc))
+               if not (tc[a] == 0 or tc[b_] == 0 or (tc[a] == tc[b_] and (tc[a] & (tc[a] - 1)) == 0)))
+    assert int(uo[-1]) == live
+    torch.testing.assert_close(rs_all.cpu(), ref_all.cpu(), rtol=2e-3, atol=0)
