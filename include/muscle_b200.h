@@ -142,6 +142,20 @@ size_t muscle_infonce_plan_sym_ring_scratch_bytes(int64_t rows_pad);
 int muscle_infonce_plan_sym_ring(const uint32_t* tor_rows, int64_t rows_pad, const uint32_t* tor_cols,
                                  int64_t cols_pad, int rank, int world, void* scratch,
                                  uint32_t* unit_off_sym, void* stream);
+/* muscle_infonce_plan_sym_ring without caller scratch and WITHOUT ANY ALLOCATION.  No counterpart in the reference:
+ * added for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  The per-row-tile counts live in a file-scope
+ * `static __device__` array of the library (64 KB, held by every GPU that loads the library until exit), so
+ * rows_pad is limited to muscle_infonce_plan_sym_ring_static_max_rows() = 2 097 152 rows; larger sizes are refused
+ * with MUSCLE_ERR_BAD_ARG (use the variant above).  Same inputs, same unit_off_sym (bit-identical).  The entry
+ * point calls no cudaMalloc / cudaFree / allocating library routine.  ALL calls on one GPU share the one array: it
+ * keeps the last call's contents (every entry a call reads is overwritten by that call first, nothing needs
+ * clearing), and two calls that overlap on the GPU (different streams, no ordering between them) RACE on it --
+ * order them, or give one of them caller-owned scratch through muscle_infonce_plan_sym_ring. */
+int muscle_infonce_plan_sym_ring_static_max_rows(void);
+int muscle_infonce_plan_sym_ring_static(const uint32_t* tor_rows, int64_t rows_pad, const uint32_t* tor_cols,
+                                        int64_t cols_pad, int rank, int world, uint32_t* unit_off_sym,
+                                        void* stream);
 int muscle_infonce_rowsum_sym_ring(const void* ehat_rows, const uint32_t* bits_rows,
                                    const uint32_t* tor_rows, int64_t rows_pad, const void* ehat_cols,
                                    const uint32_t* bits_cols, const uint32_t* tor_cols, int64_t cols_pad,

@@ -47,6 +47,8 @@ _SIGNATURES = {
     "muscle_infonce_plan_sym_ring": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "muscle_infonce_rowsum_sym_ring": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64,
                                                c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p]),
+    "muscle_infonce_plan_sym_ring_static_max_rows": (c_int, []),
+    "muscle_infonce_plan_sym_ring_static": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p]),
     "muscle_infonce_rowsum_sym_share": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_float,
                                                 c_void_p, c_void_p]),
     "muscle_infonce_mid": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p,

@@ -1,5 +1,6 @@
 // C-ABI of the dense label-masked pixel InfoNCE (include/muscle_b200.h) and its launch logic.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdlib>
 
@@ -9,6 +10,12 @@
 #include "row_kernels.cuh"
 
 using namespace mb200;
+
+// Scratch of muscle_infonce_plan_sym_ring_static (the allocation-free variant of muscle_infonce_plan_sym_ring): the
+// per-row-tile live-unit counts.  Lives in the module image: every GPU that loads the library holds these 64 KB until
+// exit.  In HOST code this name is a stand-in, not a device address -- static_plan_scratch() asks the runtime for it.
+constexpr int kStaticPlanMaxTiles = 16384;       // row tiles of 128 pixels: rows_pad <= 2 097 152
+static __device__ __align__(256) uint32_t g_static_plan_cnt[kStaticPlanMaxTiles + 1];
 
 namespace {
 
@@ -456,6 +463,46 @@ int muscle_infonce_plan_sym_ring(const uint32_t* tor_rows, int64_t rows_pad, con
     return fail(MUSCLE_ERR_BAD_ARG, "every rank holds rows_pad rows (a multiple of 256) and cols_pad = world * rows_pad");
   const int n_rb = static_cast<int>(rows_pad / 128), n_ct = static_cast<int>(cols_pad / 128);
   uint32_t* cnt = static_cast<uint32_t*>(scratch);
+  MB_CUDA(launch_pdl(pair_plan_sym_count_kernel, dim3((n_rb + 7) / 8), dim3(256), 0, stream, tor_rows, n_rb, tor_cols, n_ct,
+                     rank, world, cnt));
+  MB_LAUNCH_CHECK();
+  MB_CUDA(launch_pdl(pair_plan_scan_kernel, dim3(1), dim3(1024), 0, stream, static_cast<const uint32_t*>(cnt), n_rb, unit_off_sym));
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
+}
+
+int muscle_infonce_plan_sym_ring_static_max_rows(void) { return kStaticPlanMaxTiles * 128; }
+
+int muscle_infonce_plan_sym_ring_static(const uint32_t* tor_rows, int64_t rows_pad, const uint32_t* tor_cols,
+                                        int64_t cols_pad, int rank, int world, uint32_t* unit_off_sym, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = check_device()) return rc;
+  if (!tor_rows || !tor_cols || !unit_off_sym) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (rows_pad % 256 || rows_pad <= 0 || world < 1 || rank < 0 || rank >= world || cols_pad != rows_pad * world)
+    return fail(MUSCLE_ERR_BAD_ARG, "every rank holds rows_pad rows (a multiple of 256) and cols_pad = world * rows_pad");
+  if (rows_pad > static_cast<int64_t>(kStaticPlanMaxTiles) * 128)
+    return fail(MUSCLE_ERR_BAD_ARG,
+                "muscle_infonce_plan_sym_ring_static: rows_pad %lld exceeds the built-in scratch (at most %d rows); use "
+                "muscle_infonce_plan_sym_ring with caller-owned scratch",
+                static_cast<long long>(rows_pad), kStaticPlanMaxTiles * 128);
+  // device address of the scratch array, looked up once per device with that device current
+  constexpr int kMaxDevices = 64;
+  static std::atomic<uint32_t*> addr[kMaxDevices] = {};
+  int dev = -1;
+  MB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(MUSCLE_ERR_UNSUPPORTED, "device ordinal %d out of range", dev);
+  uint32_t* cnt = addr[dev].load(std::memory_order_acquire);
+  if (cnt == nullptr) {
+    void* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_plan_cnt);
+    if (e != cudaSuccess || ptr == nullptr)
+      return fail(MUSCLE_ERR_CUDA, "cudaGetSymbolAddress(g_static_plan_cnt) failed on device %d: %s", dev, cudaGetErrorString(e));
+    cnt = static_cast<uint32_t*>(ptr);
+    addr[dev].store(cnt, std::memory_order_release);
+  }
+  // cnt[0, n_rb) is written in full by the count kernel before the scan reads it: nothing has to start at zero, and what
+  // the previous call left behind is never read
+  const int n_rb = static_cast<int>(rows_pad / 128), n_ct = static_cast<int>(cols_pad / 128);
   MB_CUDA(launch_pdl(pair_plan_sym_count_kernel, dim3((n_rb + 7) / 8), dim3(256), 0, stream, tor_rows, n_rb, tor_cols, n_ct,
                      rank, world, cnt));
   MB_LAUNCH_CHECK();
