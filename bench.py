@@ -588,9 +588,12 @@ def pool_record(env, n, dim, num_classes, steps):
     dw = torch.empty(n, num_classes, device=dev)
     _lib.load()
 
+    sb = int(_lib.load().muscle_pool_prototypes_fwd_scratch_bytes(dim, num_classes))
+    scratch = torch.empty(sb, dtype=torch.uint8, device=dev)
+
     def fwd():
-        call("muscle_pool_prototypes_fwd", dev, e.data_ptr(), 1, w.data_ptr(), n, dim, num_classes, 1e-30, sums.data_ptr(),
-             mass.data_ptr(), proto.data_ptr())
+        call("muscle_pool_prototypes_fwd_ws", dev, e.data_ptr(), 1, w.data_ptr(), n, dim, num_classes, 1e-30,
+             sums.data_ptr(), mass.data_ptr(), proto.data_ptr(), scratch.data_ptr(), sb)
 
     def bwd():
         call("muscle_pool_prototypes_bwd", dev, e.data_ptr(), 1, w.data_ptr(), n, dim, num_classes, 1e-30, proto.data_ptr(),

@@ -232,6 +232,15 @@ int muscle_info_nce_fwd_bwd(const float* query, const float* positive_keys,
 int muscle_pool_prototypes_fwd(const void* e, int e_is_bf16, const float* w, int64_t n, int dim,
                                int num_classes, float eps, float* sum, float* mass, float* proto,
                                void* stream);
+/* The forward with caller scratch (muscle_pool_prototypes_fwd_scratch_bytes(dim, num_classes) bytes, 16-byte aligned):
+ * for bf16 e with dim in {64,128,256} (128-byte aligned) the product runs on the tensor pipe (csrc/pool_tc.cuh: weights
+ * split into bf16 hi + lo parts, fp32 accumulation in TMEM), every CTA stores its part into the scratch and a second
+ * kernel adds the parts in a fixed order: no atomics, bit-reproducible, two launches.  Other inputs (fp32 e, other
+ * dims) and scratch == NULL take muscle_pool_prototypes_fwd's path; results agree to fp32 rounding. */
+size_t muscle_pool_prototypes_fwd_scratch_bytes(int dim, int num_classes);
+int muscle_pool_prototypes_fwd_ws(const void* e, int e_is_bf16, const float* w, int64_t n, int dim,
+                                  int num_classes, float eps, float* sum, float* mass, float* proto,
+                                  void* scratch, size_t scratch_bytes, void* stream);
 int muscle_pool_prototypes_bwd(const void* e, int e_is_bf16, const float* w, int64_t n, int dim,
                                int num_classes, float eps, const float* proto, const float* mass,
                                const float* dproto, float* de, float* dw, void* stream);

@@ -61,6 +61,9 @@ _SIGNATURES = {
                                      c_void_p, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "muscle_pool_prototypes_fwd": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_int, c_float, c_void_p, c_void_p,
                                            c_void_p, c_void_p]),
+    "muscle_pool_prototypes_fwd_scratch_bytes": (c_size_t, [c_int, c_int]),
+    "muscle_pool_prototypes_fwd_ws": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_int, c_float, c_void_p, c_void_p,
+                                              c_void_p, c_void_p, c_size_t, c_void_p]),
     "muscle_pool_prototypes_bwd": (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_int, c_float, c_void_p, c_void_p,
                                            c_void_p, c_void_p, c_void_p, c_void_p]),
     "muscle_imc_workspace_bytes": (c_size_t, [c_int, c_int]),

@@ -114,7 +114,7 @@ inline int make_bf16_tile_map(CUtensorMap* map, const void* base, int64_t rows, 
 
 // bf16 [rows, dim] row-major seen as [dim/64 panels][rows][64]: ONE copy brings a whole 128-row tile as
 // dim/64 consecutive [128 x 64] 128-B-swizzled panels (coordinates: 0, row, 0).
-inline int make_bf16_panel_map(CUtensorMap* map, const void* base, int64_t rows, int dim) {
+inline int make_bf16_panel_map(CUtensorMap* map, const void* base, int64_t rows, int dim, int box_rows = 128) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return fail(MUSCLE_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   if ((reinterpret_cast<uintptr_t>(base) & 127) != 0)
@@ -122,7 +122,7 @@ inline int make_bf16_panel_map(CUtensorMap* map, const void* base, int64_t rows,
   if (dim % 64 != 0) return fail(MUSCLE_ERR_BAD_ARG, "bf16 operand rows must be multiples of 64 elements");
   cuuint64_t gdim[3] = {64, static_cast<cuuint64_t>(rows), static_cast<cuuint64_t>(dim / 64)};
   cuuint64_t gstride[2] = {static_cast<cuuint64_t>(dim) * 2, 128};
-  cuuint32_t box[3] = {64, 128, static_cast<cuuint32_t>(dim / 64)};
+  cuuint32_t box[3] = {64, static_cast<cuuint32_t>(box_rows), static_cast<cuuint32_t>(dim / 64)};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim, gstride,
                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,

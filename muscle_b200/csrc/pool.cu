@@ -17,9 +17,12 @@
 // broadcast weights from shared memory and 2 C packed FMAs per lane.  At 7.9 FMA per input byte plain
 // per-pixel FMAs could not keep up with HBM; with this register blocking they do.
 #include <cuda_bf16.h>
+#include <algorithm>
+#include <cstdlib>
 
 #include "host_util.cuh"
 #include "ptx.cuh"
+#include "pool_tc.cuh"
 
 using namespace mb200;
 
@@ -146,6 +149,8 @@ __global__ void __launch_bounds__(POOL_THREADS) pool_fwd_kernel(const T* __restr
 
 // proto = sum / max(mass, eps)
 __global__ void pool_finish_kernel(const float* sum, const float* mass, int C, int dim, float eps, float* proto) {
+  pdl_trigger();
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < C * dim) proto[i] = sum[i] / fmaxf(mass[i / dim], eps);
 }
@@ -250,6 +255,58 @@ __global__ void __launch_bounds__(POOL_THREADS) pool_bwd_kernel(const T* __restr
   }
 }
 
+// sum[] and mass[] start at zero (one launch instead of two memset nodes: it takes part in the programmatic launch chain)
+__global__ void pool_zero_kernel(float* sum, int n_sum, float* mass, int n_mass) {
+  pdl_trigger();
+  pdl_wait();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_sum) sum[i] = 0.f;
+  if (i < n_mass) mass[i] = 0.f;
+}
+
+// MUSCLE_POOL_TC=0 keeps the CUDA-core kernels for bf16 inputs too (A/B measurements, tests of both paths); read per call
+bool pool_tc_enabled() {
+  const char* v = getenv("MUSCLE_POOL_TC");
+  return v == nullptr || atoi(v) != 0;
+}
+bool pool_tc_fwd_ok(const void* e, int e_is_bf16, int dim, const float* sum) {
+  return e_is_bf16 && (dim == 64 || dim == 128 || dim == 256) && (reinterpret_cast<uintptr_t>(e) & 127) == 0 &&
+         (reinterpret_cast<uintptr_t>(sum) & 15) == 0 && pool_tc_enabled();
+}
+
+constexpr int PTC_MAX_PARTS = 192;     // CTAs of the tensor-pipe forward (<= SMs): bounds the caller's scratch
+
+template <int D>
+int launch_fwd_tc(const void* e, const float* w, int64_t n, int C, float* sum, float* mass, float* partial, int* parts,
+                  cudaStream_t stream) {
+  using Cfg = PoolTcCfg<D>;
+  CUtensorMap tm;
+  if (int rc = make_bf16_panel_map(&tm, e, n, D, PTC_K)) return rc;
+  if (int rc = ensure_dynamic_smem<pool_tc_fwd_kernel<D>>(Cfg::SMEM_BYTES)) return rc;
+  const long long n_chunks = (n + PTC_K - 1) / PTC_K;
+  const int grid = static_cast<int>(std::min<long long>(n_chunks, std::min(device_info().sm_count, PTC_MAX_PARTS)));
+  MB_CUDA(launch_pdl(pool_tc_fwd_kernel<D>, dim3(grid), dim3(PTC_THREADS), Cfg::SMEM_BYTES, stream, tm, w,
+                     static_cast<long long>(n), C, sum, mass, partial));
+  MB_LAUNCH_CHECK();
+  *parts = grid;
+  return MUSCLE_OK;
+}
+
+template <int D>
+int launch_bwd_tc(const void* e, const float* w, int64_t n, int C, const float* proto, const float* mass, const float* dproto,
+                  float eps, float* de, float* dw, cudaStream_t stream) {
+  using Cfg = PoolTcBwdCfg<D>;
+  CUtensorMap tm;
+  if (int rc = make_bf16_panel_map(&tm, e, n, D, PTB_M)) return rc;
+  if (int rc = ensure_dynamic_smem<pool_tc_bwd_kernel<D>>(Cfg::SMEM_BYTES)) return rc;
+  const long long n_chunks = (n + PTB_M - 1) / PTB_M;
+  const int grid = static_cast<int>(std::min<long long>(n_chunks, device_info().sm_count));
+  MB_CUDA(launch_pdl(pool_tc_bwd_kernel<D>, dim3(grid), dim3(PTB_THREADS), Cfg::SMEM_BYTES, stream, tm, w,
+                     static_cast<long long>(n), C, proto, mass, dproto, eps, de, dw));
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
+}
+
 int check_device_pool() {
   const DeviceInfo& di = device_info();
   if (!di.ok) return fail(MUSCLE_ERR_CUDA, "no CUDA device");
@@ -303,12 +360,61 @@ int launch_bwd(const T* e, const float* w, int64_t n, int dim, int C, const floa
 
 extern "C" {
 
+size_t muscle_pool_prototypes_fwd_scratch_bytes(int dim, int num_classes) {
+  if (dim <= 0 || num_classes <= 0) return 0;
+  return static_cast<size_t>(PTC_MAX_PARTS) * (static_cast<size_t>(num_classes) * dim + 32) * sizeof(float);
+}
+
+int muscle_pool_prototypes_fwd_ws(const void* e, int e_is_bf16, const float* w, int64_t n, int dim, int num_classes,
+                                  float eps, float* sum, float* mass, float* proto, void* scratch, size_t scratch_bytes,
+                                  void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = check_device_pool()) return rc;
+  if (!e || !w || !sum || !mass) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
+  if (int rc = check_pool_args(n, dim, num_classes)) return rc;
+  const bool ws_ok = scratch != nullptr && (reinterpret_cast<uintptr_t>(scratch) & 15) == 0 &&
+                     scratch_bytes >= muscle_pool_prototypes_fwd_scratch_bytes(dim, num_classes);
+  if (scratch != nullptr && !ws_ok)
+    return fail(MUSCLE_ERR_BAD_ARG, "scratch must be 16-byte aligned and hold muscle_pool_prototypes_fwd_scratch_bytes() bytes");
+  if (!ws_ok || !pool_tc_fwd_ok(e, e_is_bf16, dim, sum))
+    return muscle_pool_prototypes_fwd(e, e_is_bf16, w, n, dim, num_classes, eps, sum, mass, proto, stream_);
+  // tensor-pipe kernel with per-CTA parts in the scratch, then one kernel that adds them in a fixed order: two launches,
+  // no atomics, bit-reproducible
+  float* partial = static_cast<float*>(scratch);
+  int parts = 0;
+  int rc = dim == 64    ? launch_fwd_tc<64>(e, w, n, num_classes, sum, mass, partial, &parts, stream)
+           : dim == 128 ? launch_fwd_tc<128>(e, w, n, num_classes, sum, mass, partial, &parts, stream)
+                        : launch_fwd_tc<256>(e, w, n, num_classes, sum, mass, partial, &parts, stream);
+  if (rc) return rc;
+  const int total = num_classes * dim;
+  MB_CUDA(launch_pdl(pool_tc_finish_kernel, dim3(total / 32), dim3(256), 0, stream, static_cast<const float*>(partial), parts,
+                     num_classes, dim, eps, sum, mass, proto));
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
+}
+
 int muscle_pool_prototypes_fwd(const void* e, int e_is_bf16, const float* w, int64_t n, int dim, int num_classes,
                                float eps, float* sum, float* mass, float* proto, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = check_device_pool()) return rc;
   if (!e || !w || !sum || !mass) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (int rc = check_pool_args(n, dim, num_classes)) return rc;
+  if (pool_tc_fwd_ok(e, e_is_bf16, dim, sum)) {      // the tensor-pipe kernel (pool_tc.cuh): zero -> pool -> finish, one chain
+    const int total = num_classes * dim;
+    MB_CUDA(launch_pdl(pool_zero_kernel, dim3((total + 255) / 256), dim3(256), 0, stream, sum, total, mass, num_classes));
+    MB_LAUNCH_CHECK();
+    int parts = 0;
+    int rc = dim == 64    ? launch_fwd_tc<64>(e, w, n, num_classes, sum, mass, nullptr, &parts, stream)
+             : dim == 128 ? launch_fwd_tc<128>(e, w, n, num_classes, sum, mass, nullptr, &parts, stream)
+                          : launch_fwd_tc<256>(e, w, n, num_classes, sum, mass, nullptr, &parts, stream);
+    if (rc) return rc;
+    if (proto) {
+      MB_CUDA(launch_pdl(pool_finish_kernel, dim3((total + 255) / 256), dim3(256), 0, stream, static_cast<const float*>(sum),
+                         static_cast<const float*>(mass), num_classes, dim, eps, proto));
+      MB_LAUNCH_CHECK();
+    }
+    return MUSCLE_OK;
+  }
   MB_CUDA(cudaMemsetAsync(sum, 0, static_cast<size_t>(num_classes) * dim * sizeof(float), stream));
   MB_CUDA(cudaMemsetAsync(mass, 0, static_cast<size_t>(num_classes) * sizeof(float), stream));
   int rc;
@@ -335,6 +441,10 @@ int muscle_pool_prototypes_bwd(const void* e, int e_is_bf16, const float* w, int
   if (!e || !w || !proto || !mass || !dproto) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (!de && !dw) return MUSCLE_OK;
   if (int rc = check_pool_args(n, dim, num_classes)) return rc;
+  if (e_is_bf16 && (dim == 64 || dim == 128) && (reinterpret_cast<uintptr_t>(e) & 127) == 0 &&
+      (reinterpret_cast<uintptr_t>(de) & 15) == 0 && pool_tc_enabled())      // the tensor-pipe kernel (pool_tc.cuh)
+    return dim == 64 ? launch_bwd_tc<64>(e, w, n, num_classes, proto, mass, dproto, eps, de, dw, stream)
+                     : launch_bwd_tc<128>(e, w, n, num_classes, proto, mass, dproto, eps, de, dw, stream);
   if (e_is_bf16)
     return dim <= 128 ? launch_bwd<__nv_bfloat16, 1>(static_cast<const __nv_bfloat16*>(e), w, n, dim, num_classes, proto, mass, dproto, eps, de, dw, stream)
                       : launch_bwd<__nv_bfloat16, 2>(static_cast<const __nv_bfloat16*>(e), w, n, dim, num_classes, proto, mass, dproto, eps, de, dw, stream);

@@ -20,8 +20,10 @@ class _PoolPrototypes(torch.autograd.Function):
         sums = torch.empty((c, d), dtype=torch.float32, device=dev)
         mass = torch.empty((c,), dtype=torch.float32, device=dev)
         proto = torch.empty((c, d), dtype=torch.float32, device=dev)
-        call("muscle_pool_prototypes_fwd", dev, e.data_ptr(), 1 if e.dtype == torch.bfloat16 else 0, w.data_ptr(), n, d, c,
-             float(eps), sums.data_ptr(), mass.data_ptr(), proto.data_ptr())
+        sb = int(_lib.load().muscle_pool_prototypes_fwd_scratch_bytes(d, c))
+        scratch = torch.empty(sb, dtype=torch.uint8, device=dev)
+        call("muscle_pool_prototypes_fwd_ws", dev, e.data_ptr(), 1 if e.dtype == torch.bfloat16 else 0, w.data_ptr(), n, d,
+             c, float(eps), sums.data_ptr(), mass.data_ptr(), proto.data_ptr(), scratch.data_ptr(), sb)
         ctx.save_for_backward(e, w, proto, mass)
         ctx.eps = float(eps)
         ctx.mark_non_differentiable(mass)

@@ -2,6 +2,8 @@
 variant) against the oracle, against the reference's own instances of it (the positive-key mean of info_nce,
 src/loss_multilabel.py:12, and `cam @ aff` of src/MuSCLe.py:222 via the reference-minted PCM fixture), and inside the
 dense InfoNCE as soft positives."""
+import os
+
 import pytest
 import torch
 import torch.nn.functional as F
@@ -54,7 +56,8 @@ def test_cam_at_aff_is_an_instance(golden):
 
 
 @pytest.mark.parametrize("n,d,c,dtype", [(3000, 128, 21, torch.float32), (2048, 128, 21, torch.bfloat16), (1000, 64, 7, torch.float32),
-                                         (65536, 128, 21, torch.bfloat16)])
+                                         (65536, 128, 21, torch.bfloat16), (5000, 64, 7, torch.bfloat16),
+                                         (300, 128, 24, torch.bfloat16), (33000, 256, 21, torch.bfloat16)])
 def test_soft_weights_forward_and_scatter(n, d, c, dtype):
     from muscle_b200 import pool_prototypes
     gen = torch.Generator().manual_seed(n + c)
@@ -115,3 +118,53 @@ def test_dense_infonce_with_cam_weighted_positives():
     lb.backward()
     assert abs(la.item() - lb.item()) <= 1e-3 * abs(la.item())     # (the built-in means are taken over the bf16 rows)
     assert _cos(xa.grad, xb.grad) >= 0.9999
+
+
+@pytest.mark.parametrize("n,d,c", [(65536, 128, 21), (4999, 64, 24), (131, 128, 3), (9000, 256, 21)])
+def test_tensor_pipe_paths_through_the_c_abi(n, d, c):
+    """bf16 rows take the tensor-pipe kernels (csrc/pool_tc.cuh).  Through the C ABI: the scratch variant of the forward
+    (per-CTA parts, fixed-order sum) is bit-reproducible and agrees with the reduction variant and with fp64; the
+    backward's fp32 de / dw (both, de only, dw only) agree with fp64 to the hi/lo split's accuracy."""
+    from muscle_b200 import _lib
+    from muscle_b200._call import call
+    lib = _lib.load()
+    dev = torch.device("cuda", 0)
+    gen = torch.Generator().manual_seed(n + d + c)
+    e = F.normalize(torch.randn(n, d, generator=gen), dim=1).to(torch.bfloat16)
+    w = torch.relu(torch.randn(n, c, generator=gen)) * torch.rand(n, c, generator=gen)
+    dproto = torch.randn(c, d, generator=gen)
+    eg, wg, dpg = e.to(dev), w.to(dev), dproto.to(dev)
+    f32 = dict(dtype=torch.float32, device=dev)
+    sb = int(lib.muscle_pool_prototypes_fwd_scratch_bytes(d, c))
+    scratch = torch.empty(sb, dtype=torch.uint8, device=dev)
+    outs = []
+    for _ in range(2):
+        sums, mass, proto = torch.empty(c, d, **f32), torch.empty(c, **f32), torch.empty(c, d, **f32)
+        scratch.fill_(0xff)
+        call("muscle_pool_prototypes_fwd_ws", dev, eg.data_ptr(), 1, wg.data_ptr(), n, d, c, 1e-30, sums.data_ptr(),
+             mass.data_ptr(), proto.data_ptr(), scratch.data_ptr(), sb)
+        outs.append((sums.cpu(), mass.cpu(), proto.cpu()))
+    if os.environ.get("MUSCLE_POOL_TC", "1") != "0":
+        assert all(torch.equal(a, b) for a, b in zip(outs[0], outs[1]))       # fixed summation order
+    sums2, mass2, proto2 = torch.empty(c, d, **f32), torch.empty(c, **f32), torch.empty(c, d, **f32)
+    call("muscle_pool_prototypes_fwd", dev, eg.data_ptr(), 1, wg.data_ptr(), n, d, c, 1e-30, sums2.data_ptr(), mass2.data_ptr(),
+         proto2.data_ptr())
+    ed, wd = e.double(), w.double()
+    ref_sum, ref_mass = wd.t() @ ed, wd.sum(0)
+    scale = float(ref_sum.abs().max())
+    for got_s, got_m in ((outs[0][0], outs[0][1]), (sums2.cpu(), mass2.cpu())):
+        torch.testing.assert_close(got_s.double(), ref_sum, rtol=1e-4, atol=2e-5 * scale)
+        torch.testing.assert_close(got_m.double(), ref_mass, rtol=1e-5, atol=0)
+    proto, mass = outs[0][2].to(dev), outs[0][1].to(dev)
+    g = dproto.double() / ref_mass[:, None]
+    ref_de = wd @ g
+    ref_dw = ed @ g.t() - (g * (ref_sum / ref_mass[:, None])).sum(1)[None, :]
+    for want_de, want_dw in ((True, True), (True, False), (False, True)):
+        de = torch.full((n, d), float("nan"), **f32) if want_de else None
+        dw = torch.full((n, c), float("nan"), **f32) if want_dw else None
+        call("muscle_pool_prototypes_bwd", dev, eg.data_ptr(), 1, wg.data_ptr(), n, d, c, 1e-30, proto.data_ptr(),
+             mass.data_ptr(), dpg.data_ptr(), None if de is None else de.data_ptr(), None if dw is None else dw.data_ptr())
+        if want_de:
+            torch.testing.assert_close(de.cpu().double(), ref_de, rtol=1e-3, atol=1e-5 * float(ref_de.abs().max()))
+        if want_dw:
+            torch.testing.assert_close(dw.cpu().double(), ref_dw, rtol=1e-3, atol=2e-5 * float(ref_dw.abs().max()))
