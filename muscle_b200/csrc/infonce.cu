@@ -596,11 +596,11 @@ int final_impl(const void* ehat, const uint32_t* bits, const float* inv_norm,
   p.loss_acc = loss_acc; p.inv_tau = 1.f / temperature; p.layout = layout; p.dx = dx;
   p.loss_out = loss_out; p.grad_scale = grad_scale; p.proto_external = proto_external; p.dproto_out = dproto_out;
   const size_t smem = (dx && layout == MUSCLE_LAYOUT_NCHW)
-                          ? static_cast<size_t>(SORT_CHUNK) * (dim + 1) * sizeof(float) : 0;
-  const int grid = dx ? static_cast<int>((p.n + SORT_CHUNK - 1) / SORT_CHUNK) : 1;
+                          ? static_cast<size_t>(FINAL_CHUNK) * (dim + 1) * sizeof(float) : 0;
+  const int grid = dx ? static_cast<int>((p.n + FINAL_CHUNK - 1) / FINAL_CHUNK) : 1;
 #define MB_FINAL(DD)                                                                            \
   {                                                                                             \
-    if (int rca = ensure_dynamic_smem<final_kernel<DD>>(static_cast<int>(SORT_CHUNK * (DD + 1) * sizeof(float)))) return rca; \
+    if (int rca = ensure_dynamic_smem<final_kernel<DD>>(static_cast<int>(FINAL_CHUNK * (DD + 1) * sizeof(float)))) return rca; \
     MB_CUDA(launch_pdl(final_kernel<DD>, dim3(grid), dim3(FINAL_THREADS), smem, stream, p));     \
   }
   if (dim == 64) MB_FINAL(64) else if (dim == 128) MB_FINAL(128) else MB_FINAL(256)

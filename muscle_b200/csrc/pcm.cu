@@ -19,6 +19,7 @@
 //   dg from dghat through the normalisation (kernel epilogue), stored d-major bf16
 //   dW = dg f^T, db = dg 1                          pcm_dw_kernel (f carries a row of ones)
 #include <algorithm>
+#include <cstdlib>
 #include <cuda_bf16.h>
 
 #include "host_util.cuh"
@@ -85,23 +86,34 @@ PcmScratch plan_scratch(int batch, int cin, int64_t P) {
 
 // ------------------------------------------------------------------------------------------
 // element-wise preparation (HBM bound)
-// fb[b][c][p] = bf16(f[b][c][p]) for c < cin, 1 for c == cin (p < P), 0 elsewhere
+// fb[b][c][p] = bf16(f[b][c][p]) for c < cin, 1 for c == cin (p < P), 0 elsewhere.  Eight pixels per thread (two
+// 16-byte loads, one 16-byte store) when the rows of f are 16-byte aligned (P % 4 == 0).
 __global__ void __launch_bounds__(256) pcm_cast_f_kernel(const float* f, int cin, int cp, int64_t P, int64_t pp,
                                                          __nv_bfloat16* fb) {
   const int64_t row = blockIdx.x;  // b * cp + c
   const int b = static_cast<int>(row / cp), c = static_cast<int>(row - static_cast<int64_t>(b) * cp);
-  const int64_t p = (static_cast<int64_t>(blockIdx.y) * blockDim.x + threadIdx.x) * 2;
+  const int64_t p = (static_cast<int64_t>(blockIdx.y) * blockDim.x + threadIdx.x) * 8;
   if (p >= pp) return;
-  float v0 = 0.f, v1 = 0.f;
+  float v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = 0.f;
   if (c < cin) {
     const float* src = f + (static_cast<int64_t>(b) * cin + c) * P;
-    if (p < P) v0 = src[p];
-    if (p + 1 < P) v1 = src[p + 1];
+    if ((P & 3) == 0 && p + 8 <= P) {
+      const float4 lo = __ldg(reinterpret_cast<const float4*>(src + p));
+      const float4 hi = __ldg(reinterpret_cast<const float4*>(src + p) + 1);
+      v[0] = lo.x; v[1] = lo.y; v[2] = lo.z; v[3] = lo.w; v[4] = hi.x; v[5] = hi.y; v[6] = hi.z; v[7] = hi.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (p + j < P) v[j] = __ldg(src + p + j);
+    }
   } else if (c == cin) {
-    v0 = (p < P) ? 1.f : 0.f;
-    v1 = (p + 1 < P) ? 1.f : 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = (p + j < P) ? 1.f : 0.f;
   }
-  *reinterpret_cast<uint32_t*>(fb + row * pp + p) = pack_bf16x2(v0, v1);
+  *reinterpret_cast<uint4*>(fb + row * pp + p) =
+      make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
 }
 __global__ void __launch_bounds__(256) pcm_cast_w_kernel(const float* w, int cin, int cp, __nv_bfloat16* wb) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -109,60 +121,84 @@ __global__ void __launch_bounds__(256) pcm_cast_w_kernel(const float* w, int cin
   const int d = i / cp, c = i - d * cp;
   wb[i] = __float2bfloat16(c < cin ? w[d * cin + c] : 0.f);
 }
-// vb[b][k][p] = bf16(src[b][k][p] * (inv_den ? 1/den[b][p] : 1)) for k < K; row 31 = ones ? 1 : 0; pad = 0
+// vb[b][k][p] = bf16(src[b][k][p] * (inv_den ? 1/den[b][p] : 1)) for k < K; row 31 = ones ? 1 : 0; pad = 0.
+// grid (pixels / 256, VROWS, batch): one element per thread (the per-pixel loop over the 32 rows this replaced ran 104
+// blocks and took 14 us for 3.7 MB).
 __global__ void __launch_bounds__(256) pcm_cast_v_kernel(const float* src, const float* den, int K, int64_t P,
                                                          int64_t pp, int ones, __nv_bfloat16* vb) {
-  const int b = blockIdx.y;
+  const int b = blockIdx.z, k = blockIdx.y;
   const int64_t p = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (p >= pp) return;
   const bool in = p < P;
-  const float s = (in && den) ? 1.f / den[static_cast<int64_t>(b) * pp + p] : 1.f;
-  for (int k = 0; k < VROWS; ++k) {
-    float v = 0.f;
-    if (in && k < K) v = src[(static_cast<int64_t>(b) * K + k) * P + p] * s;
-    if (in && ones && k == VROWS - 1) v = 1.f;
-    vb[(static_cast<int64_t>(b) * VROWS + k) * pp + p] = __float2bfloat16(v);
+  float v = 0.f;
+  if (in && k < K) {
+    v = __ldg(src + (static_cast<int64_t>(b) * K + k) * P + p);
+    if (den) v *= 1.f / __ldg(den + static_cast<int64_t>(b) * pp + p);
   }
+  if (in && ones && k == VROWS - 1) v = 1.f;
+  vb[(static_cast<int64_t>(b) * VROWS + k) * pp + p] = __float2bfloat16(v);
 }
 // Per pixel: A = dOut/den, r = sum_c out A; A rows -> ab (V operand of the dcam pass);
 // X = [ch ch cl | ah al ah], Y = [ah al ah | ch ch cl] in segments of 21 (128 bf16 each), with
 // cam = ch + cl and A = ah + al split into bf16 hi + lo parts; rr = r (fp32).
-__global__ void __launch_bounds__(128) pcm_bwd_prep_kernel(const float* dout, const float* out, const float* cam,
+// Block = 32 pixels x 8 warps: warp w takes the classes w, w + 8, w + 16, w + 24 (lane = pixel: every global read and
+// the ab store are coalesced), the X / Y rows are assembled in shared memory and leave as whole 256-byte rows.  (One
+// thread per pixel -- 25 600 threads in all at config 2, 63 loads and 32 scattered 16-byte stores each -- took 20 us.)
+constexpr int PREP_PX = 32;
+constexpr int PREP_ROW_W = XK / 2 + 1;      // shared row stride in 32-bit words (odd: conflict-free)
+__global__ void __launch_bounds__(256) pcm_bwd_prep_kernel(const float* dout, const float* out, const float* cam,
                                                            const float* den, int K, int64_t P, int64_t pp,
                                                            __nv_bfloat16* ab, __nv_bfloat16* xp, __nv_bfloat16* yp,
                                                            float* rr) {
-  const int b = blockIdx.y;
-  const int64_t p = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (p >= pp) return;
+  __shared__ uint32_t xs_w[PREP_PX * PREP_ROW_W], ys_w[PREP_PX * PREP_ROW_W];
+  __shared__ float rs[8][PREP_PX];
+  const int b = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t p0 = static_cast<int64_t>(blockIdx.x) * PREP_PX, p = p0 + lane;     // pp % 128 == 0: p < pp
   const bool in = p < P;
-  __align__(16) __nv_bfloat16 x[XK], y[XK];
-#pragma unroll
-  for (int i = 0; i < XK; ++i) { x[i] = __float2bfloat16(0.f); y[i] = __float2bfloat16(0.f); }
+  __nv_bfloat16* xs = reinterpret_cast<__nv_bfloat16*>(xs_w) + lane * (2 * PREP_ROW_W);
+  __nv_bfloat16* ys = reinterpret_cast<__nv_bfloat16*>(ys_w) + lane * (2 * PREP_ROW_W);
+  if (warp == 0) {                                     // the two columns past the six segments
+    xs[6 * XSEG] = xs[6 * XSEG + 1] = __float2bfloat16(0.f);
+    ys[6 * XSEG] = ys[6 * XSEG + 1] = __float2bfloat16(0.f);
+  }
+  const float inv = in ? 1.f / __ldg(den + static_cast<int64_t>(b) * pp + p) : 0.f;
   float r = 0.f;
-  const float inv = in ? 1.f / den[static_cast<int64_t>(b) * pp + p] : 0.f;
 #pragma unroll
-  for (int k = 0; k < VROWS; ++k) {
+  for (int k = warp; k < VROWS; k += 8) {
     float a = 0.f, c = 0.f;
     if (in && k < K) {
       const int64_t idx = (static_cast<int64_t>(b) * K + k) * P + p;
-      a = dout[idx] * inv;
-      c = cam[idx];
-      r = fmaf(out[idx], a, r);
+      a = __ldg(dout + idx) * inv;
+      c = __ldg(cam + idx);
+      r = fmaf(__ldg(out + idx), a, r);
     }
     const __nv_bfloat16 ah = __float2bfloat16(a), ch = __float2bfloat16(c);
     ab[(static_cast<int64_t>(b) * VROWS + k) * pp + p] = ah;
     if (k < XSEG) {
       const __nv_bfloat16 al = __float2bfloat16(a - __bfloat162float(ah));
       const __nv_bfloat16 cl = __float2bfloat16(c - __bfloat162float(ch));
-      x[k] = ch; x[XSEG + k] = ch; x[2 * XSEG + k] = cl; x[3 * XSEG + k] = ah; x[4 * XSEG + k] = al; x[5 * XSEG + k] = ah;
-      y[k] = ah; y[XSEG + k] = al; y[2 * XSEG + k] = ah; y[3 * XSEG + k] = ch; y[4 * XSEG + k] = ch; y[5 * XSEG + k] = cl;
+      xs[k] = ch; xs[XSEG + k] = ch; xs[2 * XSEG + k] = cl; xs[3 * XSEG + k] = ah; xs[4 * XSEG + k] = al; xs[5 * XSEG + k] = ah;
+      ys[k] = ah; ys[XSEG + k] = al; ys[2 * XSEG + k] = ah; ys[3 * XSEG + k] = ch; ys[4 * XSEG + k] = ch; ys[5 * XSEG + k] = cl;
     }
   }
-  rr[static_cast<int64_t>(b) * pp + p] = r;
-  uint4* xd = reinterpret_cast<uint4*>(xp + (static_cast<int64_t>(b) * pp + p) * XK);
-  uint4* yd = reinterpret_cast<uint4*>(yp + (static_cast<int64_t>(b) * pp + p) * XK);
+  rs[warp][lane] = r;
+  __syncthreads();
+  if (warp == 0) {
+    float t = 0.f;
 #pragma unroll
-  for (int i = 0; i < XK / 8; ++i) { xd[i] = reinterpret_cast<uint4*>(x)[i]; yd[i] = reinterpret_cast<uint4*>(y)[i]; }
+    for (int w = 0; w < 8; ++w) t += rs[w][lane];
+    rr[static_cast<int64_t>(b) * pp + p] = t;
+  }
+  // rows out: warp w writes rows w, w + 8, ...; a row is 64 words = two coalesced 128-byte stores
+  for (int row = warp; row < PREP_PX; row += 8) {
+    uint32_t* xd = reinterpret_cast<uint32_t*>(xp + (static_cast<int64_t>(b) * pp + p0 + row) * XK);
+    uint32_t* yd = reinterpret_cast<uint32_t*>(yp + (static_cast<int64_t>(b) * pp + p0 + row) * XK);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      xd[lane + 32 * h] = xs_w[row * PREP_ROW_W + lane + 32 * h];
+      yd[lane + 32 * h] = ys_w[row * PREP_ROW_W + lane + 32 * h];
+    }
+  }
 }
 // dw[d][c] = dwp[d][c] (c < cin), db[d] = dwp[d][cin]
 __global__ void __launch_bounds__(256) pcm_unpad_dw_kernel(const float* dwp, int cin, int cp, float* dw, float* db) {
@@ -241,7 +277,7 @@ pcm_project_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
         const int b = tile / tiles_per_image, p0 = (tile - b * tiles_per_image) * 128;
         for (int k = 0; k < kc; ++k, ++cnt) {
           const int st = cnt % PJ_NST;
-          mbar_wait(f_empty(st), ((cnt / PJ_NST) & 1) ^ 1);
+          mbar_wait_spin(f_empty(st), ((cnt / PJ_NST) & 1) ^ 1);
           mbar_arrive_expect_tx(f_full(st), PJ_STAGE);
           for (int h = 0; h < 2; ++h)
             tma_load_2d(f_smem + st * PJ_STAGE + h * 8192, &tm_f, f_full(st), p0 + h * 64, b * cp + k * 64);
@@ -251,16 +287,16 @@ pcm_project_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
   } else if (warp == 4) {
     if (elect_one()) {
       constexpr uint32_t IDESC = umma_idesc_bf16(128, 128, 0, 1);  // A = W K-major, B = f MN-major
-      mbar_wait(w_full, 0);
+      mbar_wait_spin(w_full, 0);
       tc_fence_after();
       uint32_t cnt = 0, it = 0;
       for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
         const int acc = it & 1;
-        mbar_wait(d_empty(acc), ((it >> 1) & 1) ^ 1);
+        mbar_wait_spin(d_empty(acc), ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         for (int k = 0; k < kc; ++k, ++cnt) {
           const int st = cnt % PJ_NST;
-          mbar_wait(f_full(st), (cnt / PJ_NST) & 1);
+          mbar_wait_spin(f_full(st), (cnt / PJ_NST) & 1);
           tc_fence_after();
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)
@@ -281,7 +317,7 @@ pcm_project_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const int acc = it & 1;
       const int b = tile / tiles_per_image, p0 = (tile - b * tiles_per_image) * 128;
-      mbar_wait(d_full(acc), (it >> 1) & 1);
+      mbar_wait_warp(d_full(acc), (it >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1
       for (int c4 = 0; c4 < 4; ++c4) {
@@ -322,13 +358,32 @@ pcm_project_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
 
 // ==========================================================================================
 // pair passes over one image: work item = (image, 128-pixel row tile); loops over all column tiles
+//
+// Every column tile is two HALF units of 64 columns.  A half unit u runs through
+//   S(u) [+ W(u)]  (SS products into TMEM buffer u % HB)  ->  epilogue group u % NG: relu / mask, bf16, tcgen05.st over the
+//   first half of the same buffer's columns  ->  O += T(u) V(u)  (TS product)  ->  the buffer takes S(u + HB).
+// A unit is a whole column tile forward and a 64-column half backward (PpCfg::UC).  The issuer keeps HB products in
+// flight and NG epilogue groups of four warps alternate units.  ncu (profiles/r2z_*): the issuer never waits for an
+// epilogue (its t_full polls succeed at once) and the tcgen05.mma queue is full (stall_mio) at 32 % pipe activity: the
+// passes are bound by the NUMBER of tcgen05.mma per tile (~100 cycles each here, whatever N), which is why whole-tile
+// S products (8 instead of 16 per tile) gave 58 -> 44 us forward while deeper buffering alone gave nothing.  MMAs
+// complete in issue order, which is what makes the parity waits safe with NG <= HB: when a group has seen S(u) it has
+// seen every earlier phase of every buffer.
 // ==========================================================================================
 enum PcmMode { PCM_FWD = 0, PCM_BWD = 1 };
-constexpr int PP_THREADS = 192;
+constexpr int PP_THREADS = 320;   // warps 0-3, 4-7: epilogue groups; 8: MMA issuer + TMEM allocator; 9: TMA producer
 
-template <int MODE>
+template <int MODE, int HB_ = 3, int NG_ = 2>
 struct PpCfg {
-  static constexpr int NST = (MODE == PCM_BWD) ? 2 : 3;
+  // A unit = UC columns of a column tile: the whole tile forward (one N = 128 product for S: a tcgen05.mma costs about
+  // the same pipe time at N = 64 as at N = 128 here, so half as many is nearly twice as fast), a 64-column half backward
+  // (S and W buffers + the 128-column accumulator leave no room for whole tiles).
+  static constexpr int UC = (MODE == PCM_BWD) ? 64 : 128;
+  static constexpr int UPT = 128 / UC;                      // units per column tile
+  static constexpr int HB = HB_;                            // UC-column S (and W) buffers in TMEM
+  static constexpr int NG = NG_;                            // epilogue groups of four warps (warps 4 NG .. 7 idle)
+  static_assert(NG <= HB, "a group must have seen the previous phase of every buffer it waits on");
+  static constexpr int NST = (MODE == PCM_BWD) ? 2 : 4;     // column-tile ring
   static constexpr int Q_BYTES = 2 * PANEL + (MODE == PCM_BWD ? 2 * PANEL : 0);      // ghat row tile (+ X tile)
   static constexpr int AUX_BYTES = (MODE == PCM_BWD) ? 2 * PANEL : 2 * VROWS * 128;  // Y tile | two V halves
   static constexpr int TX_BYTES = 2 * PANEL + AUX_BYTES + (MODE == PCM_BWD ? 512 : 0);  // + r of the column pixels
@@ -336,8 +391,13 @@ struct PpCfg {
   static constexpr int SMEM_K = Q_BYTES;
   static constexpr int SMEM_BAR = SMEM_K + NST * STAGE;
   static constexpr int SMEM_BYTES = SMEM_BAR + 256 + 1024;
-  static constexpr int ACC_COL = (MODE == PCM_BWD) ? 256 : 128;
+  static constexpr int NBAR = 2 + 2 * NST + 2 * HB;
+  static constexpr int W_COL = HB * UC;                                         // BWD: W buffers
+  static constexpr int ACC_COL = (MODE == PCM_BWD) ? 2 * HB * UC : HB * UC;     // 384 | 384
   static constexpr int ACC_N = (MODE == PCM_BWD) ? PD : VROWS;
+  static_assert(ACC_COL + ACC_N <= 512, "TMEM budget");
+  static_assert(NBAR * 8 + 8 <= 256, "barrier block");
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
 
 struct PpParams {
@@ -353,12 +413,13 @@ struct PpParams {
   __nv_bfloat16* dgt;         // BWD: [B][128][pp]
 };
 
-template <int MODE>
+template <int MODE, int HB_, int NG_>
 __global__ void __launch_bounds__(PP_THREADS, 1)
 pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant__ CUtensorMap tm_aux_row,
                 const __grid_constant__ CUtensorMap tm_aux_col, const PpParams p) {
-  using C = PpCfg<MODE>;
-  constexpr int PP_NST = C::NST;
+  using C = PpCfg<MODE, HB_, NG_>;
+  constexpr int NG = NG_;
+  constexpr int PP_NST = C::NST, HB = C::HB, UC = C::UC, UPT = C::UPT;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
@@ -367,29 +428,30 @@ pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant_
   const uint32_t q_full = bar0;
   auto k_full = [&](int s) { return bar0 + 8u * (1 + s); };
   auto k_empty = [&](int s) { return bar0 + 8u * (1 + PP_NST + s); };
-  auto s_full = [&](int h) { return bar0 + 8u * (1 + 2 * PP_NST + h); };
-  auto t_full = [&](int h) { return bar0 + 8u * (3 + 2 * PP_NST + h); };
-  const uint32_t o_full = bar0 + 8u * (5 + 2 * PP_NST);
-  volatile uint32_t* tptr = reinterpret_cast<volatile uint32_t*>(gen + C::SMEM_BAR + 8 * (6 + 2 * PP_NST));
+  auto s_full = [&](int b) { return bar0 + 8u * (1 + 2 * PP_NST + b); };
+  auto t_full = [&](int b) { return bar0 + 8u * (1 + 2 * PP_NST + HB + b); };
+  const uint32_t o_full = bar0 + 8u * (1 + 2 * PP_NST + 2 * HB);
+  volatile uint32_t* tptr = reinterpret_cast<volatile uint32_t*>(gen + C::SMEM_BAR + 8 * C::NBAR);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int T = p.tiles_per_image;
+  const int U = UPT * T;                                     // units of this item
   const int b = blockIdx.x / T, rt = blockIdx.x - b * T;
   const int row0 = static_cast<int>(b * p.pp) + rt * 128;   // row of the [B*pp, *] pixel-major operands
 
   if (threadIdx.x == 0) {
     mbar_init(q_full, 1);
     for (int s = 0; s < PP_NST; ++s) { mbar_init(k_full(s), 1); mbar_init(k_empty(s), 1); }
-    for (int h = 0; h < 2; ++h) { mbar_init(s_full(h), 1); mbar_init(t_full(h), 4); }
+    for (int h = 0; h < HB; ++h) { mbar_init(s_full(h), 1); mbar_init(t_full(h), 4); }
     mbar_init(o_full, 1);
     fence_barrier_init();
   }
-  if (warp == 4) { tmem_alloc(smem_u32(const_cast<uint32_t*>(tptr)), 512); tmem_relinquish(); }
+  if (warp == 8) { tmem_alloc(smem_u32(const_cast<uint32_t*>(tptr)), 512); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tptr;
 
-  if (warp == 5) {
+  if (warp == 9) {
     if (lane == 0) {
       tma_prefetch_desc(&tm_g);
       tma_prefetch_desc(&tm_aux_col);
@@ -402,7 +464,7 @@ pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant_
       }
       for (int t = 0; t < T; ++t) {
         const int st = t % PP_NST;
-        mbar_wait(k_empty(st), ((t / PP_NST) & 1) ^ 1);
+        mbar_wait_spin(k_empty(st), ((t / PP_NST) & 1) ^ 1);
         mbar_arrive_expect_tx(k_full(st), C::TX_BYTES);
         const uint32_t ks = k_smem + st * C::STAGE;
         const int col_row = static_cast<int>(b * p.pp) + t * 128;
@@ -418,72 +480,70 @@ pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant_
         }
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == 8) {
     if (elect_one()) {
-      constexpr uint32_t IDESC_S = umma_idesc_bf16(128, 64, 0, 0);
+      constexpr uint32_t IDESC_S = umma_idesc_bf16(128, UC, 0, 0);
       constexpr uint32_t IDESC_O = (MODE == PCM_BWD) ? umma_idesc_bf16(128, PD, 0, 1) : umma_idesc_bf16(128, VROWS, 0, 0);
-      mbar_wait(q_full, 0);
+      mbar_wait_spin(q_full, 0);
       tc_fence_after();
-      const int U = 2 * T;
       auto issue_S = [&](int u) {
-        const int t = u >> 1, h = u & 1, st = t % PP_NST;
-        mbar_wait(k_full(st), (t / PP_NST) & 1);
+        const int t = u / UPT, h = u % UPT, st = t % PP_NST, hb = u % HB;
+        mbar_wait_spin(k_full(st), (t / PP_NST) & 1);
         tc_fence_after();
         const uint32_t ks = k_smem + st * C::STAGE;
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint32_t off = (kk >> 2) * PANEL + (kk & 3) * 32;
-          mma_ss(tmem + h * 64, umma_desc_sw128(q_smem + off, 16, 1024),
+          mma_ss(tmem + hb * UC, umma_desc_sw128(q_smem + off, 16, 1024),
                  umma_desc_sw128(ks + h * 8192 + off, 16, 1024), IDESC_S, kk > 0);
         }
         if (MODE == PCM_BWD) {
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk) {
             const uint32_t off = (kk >> 2) * PANEL + (kk & 3) * 32;
-            mma_ss(tmem + 128 + h * 64, umma_desc_sw128(x_smem + off, 16, 1024),
+            mma_ss(tmem + C::W_COL + hb * UC, umma_desc_sw128(x_smem + off, 16, 1024),
                    umma_desc_sw128(ks + 2 * PANEL + h * 8192 + off, 16, 1024), IDESC_S, kk > 0);
           }
         }
-        tc_commit(s_full(h));
+        tc_commit(s_full(hb));
       };
-      issue_S(0);
-      issue_S(1);
+      for (int u = 0; u < HB && u < U; ++u) issue_S(u);
       for (int u = 0; u < U; ++u) {
-        const int t = u >> 1, h = u & 1, st = t % PP_NST;
-        mbar_wait(t_full(h), (u >> 1) & 1);
+        const int t = u / UPT, h = u % UPT, st = t % PP_NST, hb = u % HB;
+        mbar_wait_spin(t_full(hb), (u / HB) & 1);
         tc_fence_after();
         const uint32_t ks = k_smem + st * C::STAGE;
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
+        for (int kk = 0; kk < UC / 16; ++kk) {     // K = the unit's column pixels, 16 per product
           const uint64_t bdesc = (MODE == PCM_BWD)
                                      ? umma_desc_sw128(ks + (h * 4 + kk) * 2048, PANEL, 1024)
-                                     : umma_desc_sw128(ks + 2 * PANEL + h * VROWS * 128 + kk * 32, 16, 1024);
-          mma_ts(tmem + C::ACC_COL, tmem + h * 64 + kk * 8, bdesc, IDESC_O, (u | kk) != 0);
+                                     : umma_desc_sw128(ks + 2 * PANEL + (kk >> 2) * VROWS * 128 + (kk & 3) * 32, 16, 1024);
+          mma_ts(tmem + C::ACC_COL, tmem + hb * UC + kk * 8, bdesc, IDESC_O, (u | kk) != 0);
         }
-        if (h == 1) tc_commit(k_empty(st));
-        if (u + 2 < U) issue_S(u + 2);
+        if (h == UPT - 1) tc_commit(k_empty(st));
+        if (u + HB < U) issue_S(u + HB);     // after O(u) in the pipe: it overwrites the buffer O(u) reads T from
       }
       tc_commit(o_full);
     }
-  } else {
-    const uint32_t lane_addr = static_cast<uint32_t>(warp * 32) << 16;
-    const int U = 2 * T;
+  } else if (warp < 4 * NG) {
+    const int grp = warp >> 2, wq = warp & 3;                // wq = this warp's TMEM lane quarter
+    const uint32_t lane_addr = static_cast<uint32_t>(wq * 32) << 16;
     float r_row = 0.f;
-    if (MODE == PCM_BWD) r_row = p.rr[row0 + warp * 32 + lane];
-    for (int u = 0; u < U; ++u) {
-      const int h = u & 1;
-      const int st = (u >> 1) % PP_NST;
-      if (MODE == PCM_BWD && h == 0) mbar_wait(k_full(st), ((u >> 1) / PP_NST) & 1);   // r of the column pixels landed
-      mbar_wait(s_full(h), (u >> 1) & 1);
+    if (MODE == PCM_BWD) r_row = p.rr[row0 + wq * 32 + lane];
+    for (int u = grp; u < U; u += NG) {
+      const int h = u % UPT, hb = u % HB;
+      const int t = u / UPT, st = t % PP_NST;
+      if (MODE == PCM_BWD) mbar_wait_warp(k_full(st), (t / PP_NST) & 1);   // r of the column pixels landed (bulk copy)
+      mbar_wait_warp(s_full(hb), (u / HB) & 1);   // one polling lane per warp (32 lanes on one mbarrier word serialise)
       tc_fence_after();
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      for (int c = 0; c < UC / 32; ++c) {
         uint32_t z[32];
-        tmem_ld32(tmem + lane_addr + h * 64 + c * 32, z);
+        tmem_ld32(tmem + lane_addr + hb * UC + c * 32, z);
         uint32_t packed[16];
         if (MODE == PCM_BWD) {
           uint32_t w[32];
-          tmem_ld32(tmem + lane_addr + 128 + h * 64 + c * 32, w);
+          tmem_ld32(tmem + lane_addr + C::W_COL + hb * UC + c * 32, w);
           tmem_wait_ld();
           const float* rc = reinterpret_cast<const float*>(gen + C::SMEM_K + st * C::STAGE + 4 * PANEL) + h * 64 + c * 32;
 #pragma unroll
@@ -500,34 +560,37 @@ pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant_
             packed[k] = pack_bf16x2(fmaxf(__uint_as_float(z[2 * k]), 0.f), fmaxf(__uint_as_float(z[2 * k + 1]), 0.f));
         }
         // chunk c reads columns 32c..32c+31 and writes 16c..16c+15: never a column still to be read
-        tmem_st16(tmem + lane_addr + h * 64 + c * 16, packed);
+        tmem_st16(tmem + lane_addr + hb * UC + c * 16, packed);
       }
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(t_full(h));
+      if (lane == 0) mbar_arrive(t_full(hb));
     }
     // ---- item epilogue
-    mbar_wait(o_full, 0);
+    mbar_wait_warp(o_full, 0);
     tc_fence_after();
-    const int64_t px = static_cast<int64_t>(rt) * 128 + warp * 32 + lane;  // pixel within the image
+    const int64_t px = static_cast<int64_t>(rt) * 128 + wq * 32 + lane;  // pixel within the image
     if (MODE == PCM_FWD) {
-      uint32_t o[32];
-      tmem_ld32(tmem + lane_addr + C::ACC_COL, o);
-      tmem_wait_ld();
-      if (px < p.P) {
-        float scale = 1.f;
-        if (p.normalise) {
-          const float dn = __uint_as_float(o[VROWS - 1]) + PCM_EPS;
-          p.den[static_cast<int64_t>(b) * p.pp + px] = dn;
-          scale = 1.f / dn;
-        }
+      if (grp == 0) {
+        uint32_t o[32];
+        tmem_ld32(tmem + lane_addr + C::ACC_COL, o);
+        tmem_wait_ld();
+        if (px < p.P) {
+          float scale = 1.f;
+          if (p.normalise) {
+            const float dn = __uint_as_float(o[VROWS - 1]) + PCM_EPS;
+            p.den[static_cast<int64_t>(b) * p.pp + px] = dn;
+            scale = 1.f / dn;
+          }
 #pragma unroll
-        for (int k = 0; k < VROWS; ++k)
-          if (k < p.K) p.out[(static_cast<int64_t>(b) * p.K + k) * p.P + px] = __uint_as_float(o[k]) * scale;
+          for (int k = 0; k < VROWS; ++k)
+            if (k < p.K) p.out[(static_cast<int64_t>(b) * p.K + k) * p.P + px] = __uint_as_float(o[k]) * scale;
+        }
       }
     } else {
-      // dghat row in TMEM -> dg through ghat = g / (n + eps) -> bf16, d-major
+      // dghat row in TMEM -> dg through ghat = g / (n + eps) -> bf16, d-major.  Both groups form the row's radial
+      // component; group g stores columns 64g .. 64g+63.
       const int64_t row = static_cast<int64_t>(b) * p.pp + px;
       const bool in = px < p.P;
       const float n = in ? p.gnorm[row] : 0.f;
@@ -554,7 +617,7 @@ pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant_
       const float radial = (n > 0.f) ? dot * (n + PCM_EPS) / n : 0.f;
       __nv_bfloat16* dst = p.dgt + static_cast<int64_t>(b) * PD * p.pp + px;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int c = (4 / NG) * grp; c < (4 / NG) * (grp + 1); ++c) {
         uint32_t v[32];
         tmem_ld32(tmem + lane_addr + C::ACC_COL + c * 32, v);
         tmem_wait_ld();
@@ -575,7 +638,7 @@ pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) tmem_dealloc(tmem, 512);
+  if (warp == 8) tmem_dealloc(tmem, 512);
 }
 
 // ==========================================================================================
@@ -583,7 +646,7 @@ pcm_pair_kernel(const __grid_constant__ CUtensorMap tm_g, const __grid_constant_
 // work item = (image, chunk of DW_CHUNK pixels)
 // ==========================================================================================
 constexpr int DW_NST = 3;
-constexpr int DW_CHUNK = 1024;
+constexpr int DW_CHUNK = 512;     // (1024 gave 32 CTAs at config 2 and 37.6 us; the epilogue's reductions are 16-byte vectors now)
 constexpr int DW_THREADS = 192;
 
 __host__ __device__ inline int dw_stage_bytes(int cp) { return PANEL + cp * 128; }
@@ -626,7 +689,7 @@ pcm_dw_kernel(const __grid_constant__ CUtensorMap tm_dg, const __grid_constant__
       tma_prefetch_desc(&tm_f);
       for (int s = 0; s < steps; ++s) {
         const int st = s % DW_NST;
-        mbar_wait(empty(st), ((s / DW_NST) & 1) ^ 1);
+        mbar_wait_spin(empty(st), ((s / DW_NST) & 1) ^ 1);
         mbar_arrive_expect_tx(full(st), stage);
         const uint32_t a = base + st * stage;
         const int col = static_cast<int>(px0) + s * 64;
@@ -639,7 +702,7 @@ pcm_dw_kernel(const __grid_constant__ CUtensorMap tm_dg, const __grid_constant__
       const uint32_t idesc = umma_idesc_bf16(128, NH, 0, 0);
       for (int s = 0; s < steps; ++s) {
         const int st = s % DW_NST;
-        mbar_wait(full(st), (s / DW_NST) & 1);
+        mbar_wait_spin(full(st), (s / DW_NST) & 1);
         tc_fence_after();
         const uint32_t a = base + st * stage;
         for (int n = 0; n < nh; ++n)
@@ -652,7 +715,7 @@ pcm_dw_kernel(const __grid_constant__ CUtensorMap tm_dg, const __grid_constant__
       tc_commit(d_full);
     }
   } else {
-    mbar_wait(d_full, 0);
+    mbar_wait_warp(d_full, 0);
     tc_fence_after();
     const uint32_t lane_addr = static_cast<uint32_t>(warp * 32) << 16;
     const int d = threadIdx.x;
@@ -661,11 +724,11 @@ pcm_dw_kernel(const __grid_constant__ CUtensorMap tm_dg, const __grid_constant__
         uint32_t v[32];
         tmem_ld32(tmem + lane_addr + c * 32, v);
         tmem_wait_ld();
+        float* dst = dwp + static_cast<size_t>(d) * cp + c * 32;     // 16-byte aligned: cp % 64 == 0
 #pragma unroll
-        for (int k = 0; k < 32; ++k) {
-          const float x = __uint_as_float(v[k]);
-          if (x != 0.f) atomicAdd(dwp + static_cast<size_t>(d) * cp + c * 32 + k, x);
-        }
+        for (int k = 0; k < 32; k += 4)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + k), "r"(v[k]), "r"(v[k + 1]), "r"(v[k + 2]),
+                       "r"(v[k + 3]) : "memory");
       }
     }
   }
@@ -682,14 +745,24 @@ int check_shapes(int batch, int num_classes, int cin, int64_t pixels) {
   return MUSCLE_OK;
 }
 
+template <int MODE, int HB_, int NG_>
+int launch_pair_v(const CUtensorMap& tm_g, const CUtensorMap& tm_row, const CUtensorMap& tm_col, const PpParams& prm,
+                  int items, cudaStream_t stream) {
+  using C = PpCfg<MODE, HB_, NG_>;
+  MB_CUDA(cudaFuncSetAttribute(pcm_pair_kernel<MODE, HB_, NG_>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+  pcm_pair_kernel<MODE, HB_, NG_><<<items, PP_THREADS, C::SMEM_BYTES, stream>>>(tm_g, tm_row, tm_col, prm);
+  MB_LAUNCH_CHECK();
+  return MUSCLE_OK;
+}
+// Buffers and epilogue groups per mode, from the A/B runs on B200 (profiles/r2aa_pcm_variants.txt): forward 3 whole-tile
+// buffers (2 or 3 buffers, 1 or 2 groups: the same 44 us -- the pass is bound by the number of tcgen05.mma per tile, 16
+// after the switch from 64- to 128-column S products, 58 us before); backward 2 half-tile buffers, 2 groups (three
+// buffers were SLOWER: 137 vs 107 us).
 template <int MODE>
 int launch_pair(const CUtensorMap& tm_g, const CUtensorMap& tm_row, const CUtensorMap& tm_col, const PpParams& prm,
                 int items, cudaStream_t stream) {
-  using C = PpCfg<MODE>;
-  MB_CUDA(cudaFuncSetAttribute(pcm_pair_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-  pcm_pair_kernel<MODE><<<items, PP_THREADS, C::SMEM_BYTES, stream>>>(tm_g, tm_row, tm_col, prm);
-  MB_LAUNCH_CHECK();
-  return MUSCLE_OK;
+  if (MODE == PCM_BWD) return launch_pair_v<MODE, 2, 2>(tm_g, tm_row, tm_col, prm, items, stream);
+  return launch_pair_v<MODE, 3, 2>(tm_g, tm_row, tm_col, prm, items, stream);
 }
 
 }  // namespace
@@ -725,11 +798,11 @@ int muscle_pcm_fwd(const float* cam, const float* f, const float* fuse_w, const 
   auto* camb = reinterpret_cast<__nv_bfloat16*>(base + S.camb);
   float* den = reinterpret_cast<float*>(base + S.den);
 
-  pcm_cast_f_kernel<<<dim3(batch * cp, static_cast<unsigned>((pp / 2 + 255) / 256)), 256, 0, stream>>>(f, cin, cp, pixels, pp, fb);
+  pcm_cast_f_kernel<<<dim3(batch * cp, static_cast<unsigned>((pp / 8 + 255) / 256)), 256, 0, stream>>>(f, cin, cp, pixels, pp, fb);
   MB_LAUNCH_CHECK();
   pcm_cast_w_kernel<<<(PD * cp + 255) / 256, 256, 0, stream>>>(fuse_w, cin, cp, wb);
   MB_LAUNCH_CHECK();
-  pcm_cast_v_kernel<<<dim3(static_cast<unsigned>((pp + 255) / 256), batch), 256, 0, stream>>>(cam, nullptr, num_classes, pixels, pp, 1, camb);
+  pcm_cast_v_kernel<<<dim3(static_cast<unsigned>((pp + 255) / 256), VROWS, batch), 256, 0, stream>>>(cam, nullptr, num_classes, pixels, pp, 1, camb);
   MB_LAUNCH_CHECK();
 
   CUtensorMap tm_w, tm_f, tm_g, tm_v;
@@ -780,7 +853,7 @@ int muscle_pcm_bwd(const float* dout, const float* cam, const float* out, int ba
   auto* dgt = reinterpret_cast<__nv_bfloat16*>(wb + W.dgt);
   float* dwp = reinterpret_cast<float*>(wb + W.dwp);
 
-  pcm_bwd_prep_kernel<<<dim3(static_cast<unsigned>((pp + 127) / 128), batch), 128, 0, stream>>>(dout, out, cam, den, num_classes, pixels, pp, ab, xp, yp, rr);
+  pcm_bwd_prep_kernel<<<dim3(static_cast<unsigned>(pp / PREP_PX), batch), 256, 0, stream>>>(dout, out, cam, den, num_classes, pixels, pp, ab, xp, yp, rr);
   MB_LAUNCH_CHECK();
   CUtensorMap tm_g, tm_a, tm_x, tm_y;
   if (int rc = make_bf16_box_map(&tm_g, ghat, static_cast<int64_t>(batch) * pp, PD, 128)) return rc;

@@ -275,6 +275,7 @@ bool pool_tc_fwd_ok(const void* e, int e_is_bf16, int dim, const float* sum) {
 }
 
 constexpr int PTC_MAX_PARTS = 192;     // CTAs of the tensor-pipe forward (<= SMs): bounds the caller's scratch
+static_assert(PTC_MAX_PARTS <= 32 * PTC_FIN_LOADS, "pool_tc_finish_kernel reads at most 32 x PTC_FIN_LOADS parts");
 
 template <int D>
 int launch_fwd_tc(const void* e, const float* w, int64_t n, int C, float* sum, float* mass, float* partial, int* parts,
@@ -285,8 +286,9 @@ int launch_fwd_tc(const void* e, const float* w, int64_t n, int C, float* sum, f
   if (int rc = ensure_dynamic_smem<pool_tc_fwd_kernel<D>>(Cfg::SMEM_BYTES)) return rc;
   const long long n_chunks = (n + PTC_K - 1) / PTC_K;
   const int grid = static_cast<int>(std::min<long long>(n_chunks, std::min(device_info().sm_count, PTC_MAX_PARTS)));
+  const int w_bulk = (reinterpret_cast<uintptr_t>(w) & 15) == 0 ? 1 : 0;     // bulk copies want 16-byte aligned sources
   MB_CUDA(launch_pdl(pool_tc_fwd_kernel<D>, dim3(grid), dim3(PTC_THREADS), Cfg::SMEM_BYTES, stream, tm, w,
-                     static_cast<long long>(n), C, sum, mass, partial));
+                     static_cast<long long>(n), C, w_bulk, sum, mass, partial));
   MB_LAUNCH_CHECK();
   *parts = grid;
   return MUSCLE_OK;
@@ -387,7 +389,7 @@ int muscle_pool_prototypes_fwd_ws(const void* e, int e_is_bf16, const float* w, 
                         : launch_fwd_tc<256>(e, w, n, num_classes, sum, mass, partial, &parts, stream);
   if (rc) return rc;
   const int total = num_classes * dim;
-  MB_CUDA(launch_pdl(pool_tc_finish_kernel, dim3(total / 32), dim3(256), 0, stream, static_cast<const float*>(partial), parts,
+  MB_CUDA(launch_pdl(pool_tc_finish_kernel, dim3(total / 32), dim3(PTC_FIN_THREADS), 0, stream, static_cast<const float*>(partial), parts,
                      num_classes, dim, eps, sum, mass, proto));
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;

@@ -37,14 +37,17 @@ struct PoolTcCfg {
   static constexpr int E_PANEL = PTC_K * 128;              // [64 pixels][64 columns] bf16
   static constexpr int E_STAGE = E_PANEL * (D / 64);
   static constexpr int A_STAGE = PTC_K * 128;              // [64 pixels][32 hi | 32 lo] bf16
+  static constexpr int W_STAGE = PTC_K * PTC_MAXC * 4;      // the chunk's fp32 weights as they lie in HBM (one bulk copy)
   static constexpr int OFF_A = NST * E_STAGE;
   static constexpr int OFF_ZERO = OFF_A + NST * A_STAGE;   // panel of zeros: rows 64..127 of M
-  static constexpr int OFF_BAR = OFF_ZERO + A_STAGE;
+  static constexpr int OFF_W32 = OFF_ZERO + A_STAGE;
+  static constexpr int OFF_BAR = OFF_W32 + NST * W_STAGE;
   static constexpr int OFF_MASS = OFF_BAR + 256;           // [4 warps][32] partial masses
   static constexpr int SMEM_BYTES = OFF_MASS + 512 + 1024; // + alignment slack
   static constexpr int X_STRIDE = D + 4;                   // floats per row of the hi/lo exchange (reuses stage 0)
   static_assert(32 * X_STRIDE * 4 <= NST * E_STAGE, "exchange buffer fits the embedding ring");
   static constexpr int TMEM_COLS = D < 32 ? 32 : D;
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -69,8 +72,13 @@ __device__ __forceinline__ void ptc_split8(const float (&w)[32], int c0, uint4& 
 
 template <int D>
 __global__ void __launch_bounds__(PTC_THREADS, 1)
-pool_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_e, const float* __restrict__ w, long long n, int C,
+pool_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_e, const float* __restrict__ w, long long n, int C, int w_bulk,
                    float* __restrict__ sum, float* __restrict__ mass, float* __restrict__ partial) {
+  // w_bulk != 0 (w is 16-byte aligned): the producer brings every full chunk's fp32 weights -- 64 * C * 4 contiguous
+  //   bytes of w -- into a shared-memory ring with one bulk copy on the embedding tile's barrier, NST chunks ahead;
+  //   the converting threads read their pixel's row from there.  Loading them with ld.global one chunk ahead left the
+  //   kernel waiting on HBM latency (1 800 cycles per chunk against ~950 at the HBM rate, profiles/r2v_*).  The last,
+  //   partial chunk and unaligned w are loaded directly.
   // partial == nullptr: this CTA's sums are ADDED to sum[] / mass[] (zeroed by the caller) with reductions.
   // partial != nullptr: they are STORED to partial[blockIdx.x][C*D] and partial[gridDim.x*C*D + blockIdx.x*32 + c]
   //   (no atomics, no zeroing; pool_tc_finish_kernel adds the CTAs' parts in a fixed order: deterministic, and it does
@@ -124,8 +132,11 @@ pool_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_e, const float* __rest
       for (long long k = 0; k < mine; ++k) {
         const int st = static_cast<int>(k % NST);
         mbar_wait(empty(st), static_cast<uint32_t>(((k / NST) & 1) ^ 1));
-        mbar_arrive_expect_tx(e_full(st), Cfg::E_STAGE);
-        tma_load_3d(e_smem + st * Cfg::E_STAGE, &tm_e, e_full(st), 0, static_cast<int>((first + k * stride) * PTC_K), 0);
+        const long long p0 = (first + k * stride) * PTC_K;
+        const uint32_t wbytes = (w_bulk && p0 + PTC_K <= n) ? static_cast<uint32_t>(PTC_K * C * 4) : 0u;
+        mbar_arrive_expect_tx(e_full(st), Cfg::E_STAGE + wbytes);
+        tma_load_3d(e_smem + st * Cfg::E_STAGE, &tm_e, e_full(st), 0, static_cast<int>(p0), 0);
+        if (wbytes) bulk_load_1d(base + Cfg::OFF_W32 + st * Cfg::W_STAGE, w + p0 * C, wbytes, e_full(st));
       }
     }
   } else if (warp == 5) {
@@ -155,21 +166,24 @@ pool_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_e, const float* __rest
     float macc[PTC_MAXC];
 #pragma unroll
     for (int c = 0; c < PTC_MAXC; ++c) macc[c] = 0.f;
-    float wn[PTC_MAXC];
-    auto load_w = [&](long long k) {
-      const long long p = (first + k * stride) * PTC_K + t;
-#pragma unroll
-      for (int c = 0; c < PTC_MAXC; ++c) wn[c] = (p < n && c < C) ? __ldg(w + p * C + c) : 0.f;
-    };
-    if (grp < mine) load_w(grp);
     for (long long k = grp; k < mine; k += 2) {
+      const int st = static_cast<int>(k % NST);
+      const long long p0 = (first + k * stride) * PTC_K;
       float wc[32];
+      if (w_bulk && p0 + PTC_K <= n) {
+        mbar_wait_warp(e_full(st), static_cast<uint32_t>((k / NST) & 1));
+        const float* ws = reinterpret_cast<const float*>(gen + Cfg::OFF_W32 + st * Cfg::W_STAGE) + t * C;
 #pragma unroll
-      for (int c = 0; c < 32; ++c) wc[c] = c < PTC_MAXC ? wn[c < PTC_MAXC ? c : 0] : 0.f;
-      if (k + 2 < mine) load_w(k + 2);
+        for (int c = 0; c < PTC_MAXC; ++c) wc[c] = c < C ? ws[c] : 0.f;
+      } else {
+        const long long p = p0 + t;
+#pragma unroll
+        for (int c = 0; c < PTC_MAXC; ++c) wc[c] = (p < n && c < C) ? __ldg(w + p * C + c) : 0.f;
+      }
+#pragma unroll
+      for (int c = PTC_MAXC; c < 32; ++c) wc[c] = 0.f;
 #pragma unroll
       for (int c = 0; c < PTC_MAXC; ++c) macc[c] += wc[c];
-      const int st = static_cast<int>(k % NST);
       mbar_wait_warp(empty(st), static_cast<uint32_t>(((k / NST) & 1) ^ 1));
       const uint32_t row = a_smem + st * Cfg::A_STAGE + t * 128;
       const uint32_t swz = static_cast<uint32_t>(t & 7);
@@ -261,26 +275,35 @@ pool_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_e, const float* __rest
   if (warp == 5) tmem_dealloc(tmem, Cfg::TMEM_COLS);
 }
 
-// sum[i] = sum over the CTAs' parts (fixed order), mass likewise, proto = sum / max(mass, eps).  Block = 32 elements x 8
-// slices of the CTA list (a warp reads 128 contiguous bytes of one part).
-__global__ void __launch_bounds__(256) pool_tc_finish_kernel(const float* __restrict__ partial, int parts, int C, int dim,
-                                                             float eps, float* __restrict__ sum, float* __restrict__ mass,
-                                                             float* __restrict__ proto) {
+// sum[i] = sum over the CTAs' parts (fixed order), mass likewise, proto = sum / max(mass, eps).  Block = 32 elements x 32
+// slices of the CTA list: a warp reads 128 contiguous bytes of one part, a thread at most PTC_FIN_LOADS parts, all loads
+// issued before the first add (the first version's 8 slices walked 19 dependent-latency loads each: 9 us for 1.6 MB).
+constexpr int PTC_FIN_THREADS = 1024;
+constexpr int PTC_FIN_LOADS = 6;           // 32 slices x 6 = 192 parts (PTC_MAX_PARTS in pool.cu)
+__global__ void __launch_bounds__(PTC_FIN_THREADS) pool_tc_finish_kernel(const float* __restrict__ partial, int parts, int C,
+                                                                         int dim, float eps, float* __restrict__ sum,
+                                                                         float* __restrict__ mass, float* __restrict__ proto) {
   pdl_trigger();
   pdl_wait();
-  __shared__ float red[8][33];
-  __shared__ float mred[8];
+  __shared__ float red[32][33];
+  __shared__ float mred[32];
   const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
   const int total = C * dim;
   const int i = blockIdx.x * 32 + lane;
   const int c = (blockIdx.x * 32) / dim;              // dim % 32 == 0: one class per block
+  float v[PTC_FIN_LOADS];
+#pragma unroll
+  for (int j = 0; j < PTC_FIN_LOADS; ++j) {
+    const int p = slice + 32 * j;
+    v[j] = (i < total && p < parts) ? __ldg(partial + static_cast<size_t>(p) * total + i) : 0.f;
+  }
+  // the class's mass: thread t < parts holds part t's mass (parts <= 192 < 1024)
+  const int t = threadIdx.x;
+  float m = (t < parts) ? __ldg(partial + static_cast<size_t>(parts) * total + t * 32 + c) : 0.f;
   float acc = 0.f;
-  if (i < total)
-    for (int p = slice; p < parts; p += 8) acc += __ldg(partial + static_cast<size_t>(p) * total + i);
+#pragma unroll
+  for (int j = 0; j < PTC_FIN_LOADS; ++j) acc += v[j];
   red[slice][lane] = acc;
-  // the class's mass: slice s adds parts s, s + 8, ...; lanes stride the parts of the slice
-  float m = 0.f;
-  for (int p = slice + 8 * lane; p < parts; p += 256) m += __ldg(partial + static_cast<size_t>(parts) * total + p * 32 + c);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) m += __shfl_xor_sync(0xffffffffu, m, o);
   if (lane == 0) mred[slice] = m;
@@ -288,7 +311,9 @@ __global__ void __launch_bounds__(256) pool_tc_finish_kernel(const float* __rest
   if (slice == 0 && i < total) {
     float s = 0.f, mm = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) { s += red[k][lane]; mm += mred[k]; }
+    for (int k = 0; k < 32; ++k) s += red[k][lane];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) mm += mred[k];          // warps 0..5 hold parts; the rest added zeros
     sum[i] = s;
     if (i % dim == 0) mass[c] = mm;
     if (proto != nullptr) proto[i] = s / fmaxf(mm, eps);
@@ -381,32 +406,72 @@ pool_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_e, const float* __rest
   }
   if (warp == 8 && lane == 0) tma_prefetch_desc(&tm_e);
   pdl_trigger();
+  __syncthreads();                       // barriers initialised
   pdl_wait();
+  const long long n_chunks = (n + PTB_M - 1) / PTB_M;
+  const long long first = blockIdx.x, stride = gridDim.x;
+  const long long mine = first < n_chunks ? (n_chunks - first + stride - 1) / stride : 0;
+  // the first two embedding tiles are on their way while the operands below are built
+  if (warp == 8 && lane == 0 && need_dw)
+    for (long long k = 0; k < mine && k < NST; ++k) {
+      mbar_arrive_expect_tx(e_full(static_cast<int>(k)), Cfg::E_STAGE);
+      tma_load_3d(e_smem + static_cast<int>(k) * Cfg::E_STAGE, &tm_e, e_full(static_cast<int>(k)), 0,
+                  static_cast<int>((first + k * stride) * PTB_M), 0);
+    }
   // ---- the two B operands (constant for the launch) and dm[c] = -(g[c] . proto[c])
   for (int i = threadIdx.x; i < (Cfg::G1_BYTES + Cfg::G2_BYTES) / 16; i += PTB_THREADS)
     reinterpret_cast<uint4*>(gen + Cfg::OFF_G1)[i] = make_uint4(0u, 0u, 0u, 0u);
   __syncthreads();
-  for (int i = threadIdx.x; i < C * D; i += PTB_THREADS) {
-    const int c = i / D, d = i - c * D;
-    const float g = __ldg(dproto + i) / fmaxf(__ldg(mass + c), eps);
-    const __nv_bfloat16 gh = __float2bfloat16_rn(g);
-    const __nv_bfloat16 gl = __float2bfloat16_rn(g - __bfloat162float(gh));
-    const int panel = d >> 6, dd = d & 63;
-    auto at1 = [&](int r) { return Cfg::OFF_G1 + panel * Cfg::G1_PANEL + r * 128 + ((((dd >> 3) ^ (r & 7))) << 4) + (dd & 7) * 2; };
-    auto at2 = [&](int r) { return Cfg::OFF_G2 + panel * Cfg::G2_PANEL + r * 128 + ((((dd >> 3) ^ (r & 7))) << 4) + (dd & 7) * 2; };
-    *reinterpret_cast<__nv_bfloat16*>(gen + at1(c)) = gh;
-    *reinterpret_cast<__nv_bfloat16*>(gen + at1(32 + c)) = gh;
-    *reinterpret_cast<__nv_bfloat16*>(gen + at1(64 + c)) = gl;
-    *reinterpret_cast<__nv_bfloat16*>(gen + at2(c)) = gh;
-    *reinterpret_cast<__nv_bfloat16*>(gen + at2(32 + c)) = gl;
-  }
-  for (int c = warp; c < C; c += PTB_THREADS / 32) {
-    const float im = 1.f / fmaxf(__ldg(mass + c), eps);
-    float s = 0.f;
-    for (int d = lane; d < D; d += 32) s = fmaf(__ldg(dproto + c * D + d) * im, __ldg(proto + c * D + d), s);
+  // (every load of a round is issued before the first use: a thread walks up to PTB_G_ROUND elements per round, and the
+  //  one-element-per-iteration form of this loop cost ~7 us of dependent HBM latency per launch, profiles/r2v_*)
+  constexpr int PTB_G_ROUND = 9;
+  for (int i0 = 0; i0 < C * D; i0 += PTB_G_ROUND * PTB_THREADS) {
+    float gv[PTB_G_ROUND], mv[PTB_G_ROUND];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == 0) dm_sm[c] = (__ldg(mass + c) >= eps) ? -s : 0.f;
+    for (int j = 0; j < PTB_G_ROUND; ++j) {
+      const int i = i0 + j * PTB_THREADS + threadIdx.x;
+      const bool in = i < C * D;
+      gv[j] = in ? __ldg(dproto + i) : 0.f;
+      mv[j] = in ? __ldg(mass + i / D) : 1.f;
+    }
+#pragma unroll
+    for (int j = 0; j < PTB_G_ROUND; ++j) {
+      const int i = i0 + j * PTB_THREADS + threadIdx.x;
+      if (i < C * D) {
+        const int c = i / D, d = i - c * D;
+        const float g = gv[j] / fmaxf(mv[j], eps);
+        const __nv_bfloat16 gh = __float2bfloat16_rn(g);
+        const __nv_bfloat16 gl = __float2bfloat16_rn(g - __bfloat162float(gh));
+        const int panel = d >> 6, dd = d & 63;
+        auto at1 = [&](int r) { return Cfg::OFF_G1 + panel * Cfg::G1_PANEL + r * 128 + ((((dd >> 3) ^ (r & 7))) << 4) + (dd & 7) * 2; };
+        auto at2 = [&](int r) { return Cfg::OFF_G2 + panel * Cfg::G2_PANEL + r * 128 + ((((dd >> 3) ^ (r & 7))) << 4) + (dd & 7) * 2; };
+        *reinterpret_cast<__nv_bfloat16*>(gen + at1(c)) = gh;
+        *reinterpret_cast<__nv_bfloat16*>(gen + at1(32 + c)) = gh;
+        *reinterpret_cast<__nv_bfloat16*>(gen + at1(64 + c)) = gl;
+        *reinterpret_cast<__nv_bfloat16*>(gen + at2(c)) = gh;
+        *reinterpret_cast<__nv_bfloat16*>(gen + at2(32 + c)) = gl;
+      }
+    }
+  }
+  static_assert(D % 32 == 0 && D / 32 <= 4, "dm loop below");
+  for (int c0 = 0; c0 < C; c0 += PTB_THREADS / 32) {      // warp = class (C <= 24: at most three rounds, usually three)
+    const int c = c0 + warp;
+    float dp[D / 32], pr[D / 32], ms = 1.f;
+    if (c < C) {
+      ms = __ldg(mass + c);
+#pragma unroll
+      for (int j = 0; j < D / 32; ++j) {
+        dp[j] = __ldg(dproto + c * D + lane + 32 * j);
+        pr[j] = __ldg(proto + c * D + lane + 32 * j);
+      }
+      const float im = 1.f / fmaxf(ms, eps);
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < D / 32; ++j) s = fmaf(dp[j] * im, pr[j], s);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (lane == 0) dm_sm[c] = (ms >= eps) ? -s : 0.f;
+    }
   }
   fence_proxy_async_smem();
   tc_fence_before();
@@ -414,14 +479,10 @@ pool_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_e, const float* __rest
   tc_fence_after();
   const uint32_t tmem = *tmem_ptr_smem;
 
-  const long long n_chunks = (n + PTB_M - 1) / PTB_M;
-  const long long first = blockIdx.x, stride = gridDim.x;
-  const long long mine = first < n_chunks ? (n_chunks - first + stride - 1) / stride : 0;
-
   if (warp == 8) {
     // ------------------------------------------------------------ TMA producer (embedding tiles: product 2 only)
     if (lane == 0 && need_dw) {
-      for (long long k = 0; k < mine; ++k) {
+      for (long long k = NST; k < mine; ++k) {
         const int st = static_cast<int>(k & 1);
         mbar_wait(in_empty(st), static_cast<uint32_t>(((k >> 1) & 1) ^ 1));
         mbar_arrive_expect_tx(e_full(st), Cfg::E_STAGE);

@@ -543,22 +543,28 @@ struct FinalParams {
   float* dproto_out;           // optional [C][D]: d loss / d prototype (times grad_scale)
 };
 
-// One block = 128 consecutive source pixels, 16 warps of 8 pixels each (two pixels in flight per
+// One block = FINAL_CHUNK consecutive source pixels, one warp per 8 pixels (two pixels in flight per
 // warp, so the dependent gather -> reduce -> store chains of different pixels overlap).  Per pixel
 // the warp gathers its sorted row (lane holds channels lane, lane+32, ...), forms
 //   g = 1/n_valid (1/tau sum_slots part + gpos/mass class_sum_c + dproto_c/mass),
 //   dx = inv_norm (g - e (g.e))
 // and writes it back in the caller's layout (NCHW through a shared-memory transpose, so the global
-// stores are coalesced along the pixel index).
-constexpr int FINAL_THREADS = 512;
-constexpr int FINAL_ROWS_PER_WARP = SORT_CHUNK / (FINAL_THREADS / 32);
+// stores are coalesced along the pixel index).  64-pixel blocks (round 1: 128): 392 blocks instead of 196 at
+// config 2 fill 148 SMs more evenly, and six of them fit an SM's shared memory instead of three.
+#ifndef MB_FINAL_CHUNK
+#define MB_FINAL_CHUNK 64
+#endif
+constexpr int FINAL_CHUNK = MB_FINAL_CHUNK;
+constexpr int FINAL_ROWS_PER_WARP = 8;
+constexpr int FINAL_THREADS = FINAL_CHUNK / FINAL_ROWS_PER_WARP * 32;
+static_assert(FINAL_CHUNK == 64 || FINAL_CHUNK == 128, "final_kernel: 64 or 128 pixels per block");
 
 template <int D>
 __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams p) {
   pdl_trigger();
   pdl_wait();
   constexpr int EPL = D / 32;
-  extern __shared__ float smem_f[];  // NCHW only: [SORT_CHUNK][D+1]
+  extern __shared__ float smem_f[];  // NCHW only: [FINAL_CHUNK][D+1]
   __shared__ float n_valid_sh;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -575,7 +581,7 @@ __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams 
     for (int i = threadIdx.x; i < p.C * D; i += FINAL_THREADS) p.dproto_out[i] = inv_n * __ldg(p.dproto + i);
   constexpr int RB = 128;  // rows per row block of the pair passes (PAIR_RB)
   const uint32_t per = pair_units_per_cta(__ldg(p.unit_off + p.n_row_blocks), p.n_ctas, p.n_col_tiles);
-  const long long blk0 = static_cast<long long>(blockIdx.x) * SORT_CHUNK;
+  const long long blk0 = static_cast<long long>(blockIdx.x) * FINAL_CHUNK;
 
   // Per-row scalars of this warp's rows, fetched up front by lane (r mod 8 = row): the dependent
   // chain perm -> bits / unit_off / gpos / inv_norm is paid once per warp instead of once per row.
@@ -653,13 +659,13 @@ __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams 
   }
   if (p.layout == MUSCLE_LAYOUT_NCHW) {
     __syncthreads();
-    // thread -> (pixel = tid % 128, channel group = tid / 128): consecutive threads write consecutive pixels
-    const int px = threadIdx.x & (SORT_CHUNK - 1);
+    // thread -> (pixel = tid % FINAL_CHUNK, channel group = tid / FINAL_CHUNK): consecutive threads write consecutive pixels
+    const int px = threadIdx.x & (FINAL_CHUNK - 1);
     const long long i = blk0 + px;
     if (i < p.n) {
       const long long b = i / p.ppi;
       float* dst = p.dx + (b * D) * p.ppi + (i - b * p.ppi);
-      for (int d = threadIdx.x / SORT_CHUNK; d < D; d += FINAL_THREADS / SORT_CHUNK)
+      for (int d = threadIdx.x / FINAL_CHUNK; d < D; d += FINAL_THREADS / FINAL_CHUNK)
         dst[static_cast<long long>(d) * p.ppi] = smem_f[px * (D + 1) + d];
     }
   }

@@ -1,0 +1,9 @@
+#!/bin/bash
+# round-2 check y: PCM kernels with single-lane / spinning mbarrier waits
+mkdir -p gpurun_out
+tag=${1:-r2y}
+timeout 200 python -m pytest tests/test_gpu_pcm.py -m gpu -q --timeout 60 -x 2>&1 | tail -5 | tee gpurun_out/${tag}_pytest_pcm.log
+timeout 120 python scripts/pcm_bench.py 2> gpurun_out/${tag}_pcm_bench.txt; cat gpurun_out/${tag}_pcm_bench.txt
+timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/${tag}_pcm_launches.csv \
+  python scripts/pcm_bench.py --once > /dev/null 2>&1
+python scripts/launch_summary.py gpurun_out/${tag}_pcm_launches.csv 2>/dev/null | head -12

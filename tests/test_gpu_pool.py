@@ -168,3 +168,30 @@ def test_tensor_pipe_paths_through_the_c_abi(n, d, c):
             torch.testing.assert_close(de.cpu().double(), ref_de, rtol=1e-3, atol=1e-5 * float(ref_de.abs().max()))
         if want_dw:
             torch.testing.assert_close(dw.cpu().double(), ref_dw, rtol=1e-3, atol=2e-5 * float(ref_dw.abs().max()))
+
+
+def test_tensor_pipe_forward_with_unaligned_weights():
+    """The tensor-pipe forward stages a chunk's weights with one bulk copy when `w` is 16-byte aligned; a `w` that is not
+    (here: a row-offset view, 84 bytes in) is loaded directly.  Both give the same sums."""
+    from muscle_b200 import _lib
+    from muscle_b200._call import call
+    _lib.load()
+    dev = torch.device("cuda", 0)
+    n, d, c = 7001, 128, 21
+    gen = torch.Generator().manual_seed(5)
+    e = F.normalize(torch.randn(n, d, generator=gen), dim=1).to(torch.bfloat16).to(dev)
+    w_big = torch.rand(n + 1, c, generator=gen).to(dev)
+    w_off = w_big[1:]                                   # data_ptr 84 bytes past an aligned address
+    w_al = w_off.clone()
+    assert w_off.data_ptr() % 16 != 0 and w_al.data_ptr() % 16 == 0 and w_off.is_contiguous()
+    f32 = dict(dtype=torch.float32, device=dev)
+    res = []
+    for w in (w_off, w_al):
+        sums, mass, proto = torch.empty(c, d, **f32), torch.empty(c, **f32), torch.empty(c, d, **f32)
+        call("muscle_pool_prototypes_fwd", dev, e.data_ptr(), 1, w.data_ptr(), n, d, c, 1e-30, sums.data_ptr(), mass.data_ptr(),
+             proto.data_ptr())
+        res.append((sums.cpu(), mass.cpu()))
+    ref = w_al.double().t().cpu() @ e.double().cpu()
+    for s_, m_ in res:
+        torch.testing.assert_close(s_.double(), ref, rtol=1e-4, atol=2e-5 * float(ref.abs().max()))
+        torch.testing.assert_close(m_.double(), w_al.double().sum(0).cpu(), rtol=1e-5, atol=0)
