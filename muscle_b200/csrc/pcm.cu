@@ -757,7 +757,9 @@ int launch_pair_v(const CUtensorMap& tm_g, const CUtensorMap& tm_row, const CUte
 // Buffers and epilogue groups per mode, from the A/B runs on B200 (profiles/r2aa_pcm_variants.txt): forward 3 whole-tile
 // buffers (2 or 3 buffers, 1 or 2 groups: the same 44 us -- the pass is bound by the number of tcgen05.mma per tile, 16
 // after the switch from 64- to 128-column S products, 58 us before); backward 2 half-tile buffers, 2 groups (three
-// buffers were SLOWER: 137 vs 107 us).
+// buffers were SLOWER: 137 vs 107 us).  A forward variant with ONE buffer, 256 TMEM columns and 113 KB of shared memory, so
+// that two CTAs share an SM and all 200 items of config 2 are resident at once, ran at the same 42-44 us
+// (profiles/r2ac_*): per SM the passes sustain one tcgen05.mma per ~100 cycles however the work is interleaved.
 template <int MODE>
 int launch_pair(const CUtensorMap& tm_g, const CUtensorMap& tm_row, const CUtensorMap& tm_col, const PpParams& prm,
                 int items, cudaStream_t stream) {
