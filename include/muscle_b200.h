@@ -385,6 +385,14 @@ int muscle_field_edges(const float* seg_map, const float* label_with_bg, int bat
                        float* mag_scratch, uint8_t* orient_out, uint8_t* pos_out,
                        float* mag_sum_out, uint32_t* plane_max_out, int32_t* counts_out,
                        void* stream);
+/* The same with the Sobel pair chosen like the reference class's constructor argument (src/edge.py:29-43:
+ * kernel_size 3 or 5, each with its 1e-6 stand-ins for zero); muscle_field_edges is sobel_size = 5, the value
+ * train_muscle.py:163 passes. */
+int muscle_field_edges_sobel(const float* seg_map, const float* label_with_bg, int batch, int num_classes,
+                             int height, int width, float beta, int step, int sobel_size, float* prob_scratch,
+                             float* mag_scratch, uint8_t* orient_out, uint8_t* pos_out,
+                             float* mag_sum_out, uint32_t* plane_max_out, int32_t* counts_out,
+                             void* stream);
 int muscle_field_compact(const uint8_t* orient, const uint8_t* pos, int height, int width, int step,
                          const int32_t* planes, const int64_t* offsets, int n_active,
                          int32_t* lists, void* stream);

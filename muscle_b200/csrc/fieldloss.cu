@@ -51,6 +51,10 @@ __constant__ float c_kx[25] = {2.f, 1.f, 1e-6f, -1.f, -2.f, 3.f, 2.f, 1e-6f, -2.
 __constant__ float c_ky[25] = {2.f, 3.f, 4.f, 3.f, 2.f, 1.f, 2.f, 3.f, 2.f, 1.f, 1e-6f, 1e-6f, 1e-6f, 1e-6f, 1e-6f,
                                -1.f, -2.f, -3.f, -2.f, -1.f, -2.f, -3.f, -4.f, -3.f, -2.f};
 
+// ... and the 3x3 pair (src/edge.py:33-35)
+__constant__ float c_kx3[9] = {1.f, 1e-6f, -1.f, 2.f, 1e-6f, -2.f, 1.f, 1e-6f, -1.f};
+__constant__ float c_ky3[9] = {1.f, 2.f, 1.f, 1e-6f, 1e-6f, 1e-6f, -1.f, -2.f, -1.f};
+
 // prob[b][c][p] = softmax_k(seg[b][k][p] * beta)[1 + c]
 __global__ void __launch_bounds__(256) field_prob_kernel(const float* seg, float beta, int C, long long HW, float* prob) {
   const long long p = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -92,7 +96,8 @@ __device__ __forceinline__ int orient_bin(float gy, float gx) {
   return 3;
 }
 
-// Thread = pixel, loops over the fg classes present in the image.
+// Thread = pixel, loops over the fg classes present in the image.  KS = 5 (the trainer's choice) or 3.
+template <int KS>
 __global__ void __launch_bounds__(256) field_sobel_kernel(const float* prob, const float* label, int C, int H, int W,
                                                           float* mag, uint8_t* orient, float* mag_sum,
                                                           unsigned int* plane_max) {
@@ -108,16 +113,16 @@ __global__ void __launch_bounds__(256) field_sobel_kernel(const float* prob, con
     if (lab != 0.f) {
       const float* pl = prob + (static_cast<long long>(b) * (C - 1) + c) * HW;
 #pragma unroll
-      for (int r = 0; r < 5; ++r) {
-        const int yy = y + r - 2;
+      for (int r = 0; r < KS; ++r) {
+        const int yy = y + r - KS / 2;
         if (yy < 0 || yy >= H) continue;
 #pragma unroll
-        for (int s = 0; s < 5; ++s) {
-          const int xx = x + s - 2;
+        for (int s = 0; s < KS; ++s) {
+          const int xx = x + s - KS / 2;
           if (xx < 0 || xx >= W) continue;
           const float v = pl[static_cast<long long>(yy) * W + xx];
-          gx = fmaf(c_kx[r * 5 + s], v, gx);
-          gy = fmaf(c_ky[r * 5 + s], v, gy);
+          gx = fmaf(KS == 5 ? c_kx[r * 5 + s] : c_kx3[r * 3 + s], v, gx);
+          gy = fmaf(KS == 5 ? c_ky[r * 5 + s] : c_ky3[r * 3 + s], v, gy);
         }
       }
       gx *= lab;
@@ -489,8 +494,18 @@ int muscle_field_edges(const float* seg_map, const float* label_with_bg, int bat
                        int width, float beta, int step, float* prob_scratch, float* mag_scratch,
                        uint8_t* orient_out, uint8_t* pos_out, float* mag_sum_out, uint32_t* plane_max_out,
                        int32_t* counts_out, void* stream_) {
+  return muscle_field_edges_sobel(seg_map, label_with_bg, batch, num_classes, height, width, beta, step, 5, prob_scratch,
+                                  mag_scratch, orient_out, pos_out, mag_sum_out, plane_max_out, counts_out, stream_);
+}
+
+int muscle_field_edges_sobel(const float* seg_map, const float* label_with_bg, int batch, int num_classes, int height,
+                             int width, float beta, int step, int sobel_size, float* prob_scratch, float* mag_scratch,
+                             uint8_t* orient_out, uint8_t* pos_out, float* mag_sum_out, uint32_t* plane_max_out,
+                             int32_t* counts_out, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (int rc = need_sm100()) return rc;
+  if (sobel_size != 3 && sobel_size != 5)
+    return fail(MUSCLE_ERR_BAD_ARG, "sobel_size must be 3 or 5 like src/edge.py:33-43 (got %d)", sobel_size);
   if (!seg_map || !label_with_bg || !prob_scratch || !mag_scratch || !orient_out || !pos_out || !mag_sum_out ||
       !plane_max_out || !counts_out)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
@@ -504,8 +519,12 @@ int muscle_field_edges(const float* seg_map, const float* label_with_bg, int bat
   const dim3 gpx(static_cast<unsigned>((HW + 255) / 256), batch);
   field_prob_kernel<<<gpx, 256, 0, stream>>>(seg_map, beta, num_classes, HW, prob_scratch);
   MB_LAUNCH_CHECK();
-  field_sobel_kernel<<<gpx, 256, 0, stream>>>(prob_scratch, label_with_bg, num_classes, height, width, mag_scratch,
-                                              orient_out, mag_sum_out, plane_max_out);
+  if (sobel_size == 5)
+    field_sobel_kernel<5><<<gpx, 256, 0, stream>>>(prob_scratch, label_with_bg, num_classes, height, width, mag_scratch,
+                                                   orient_out, mag_sum_out, plane_max_out);
+  else
+    field_sobel_kernel<3><<<gpx, 256, 0, stream>>>(prob_scratch, label_with_bg, num_classes, height, width, mag_scratch,
+                                                   orient_out, mag_sum_out, plane_max_out);
   MB_LAUNCH_CHECK();
   const unsigned gx = static_cast<unsigned>(std::min<long long>((HW + 255) / 256, 64));
   field_pos_kernel<<<dim3(gx, planes), 256, 0, stream>>>(mag_scratch, orient_out, label_with_bg, plane_max_out,

@@ -5,8 +5,13 @@
 // columns, so every (query, key) pair is live; the gradient pass runs twice, once per role
 //   dQ = 1/T sum_k p_qk k + gpos_q proto        (rows = queries, w_row = 1/rowsum, w_col = 0)
 //   dK = 1/T sum_q p_qk q                        (rows = keys,    w_row = 0, w_col = 1/rowsum)
-// Like the reference, nothing is normalised here: the caller passes unit-norm rows (the exponent
-// shift of the pair passes assumes |q.k| <= 1).
+// Like the reference, nothing is normalised here.  The pair passes assume |q.k| <= 1 (their exponent shift), so rows
+// of any norm are handled by a uniform scale: with Rq >= max |q| and Rk >= max(|k|, |mean P|) (given by the caller),
+//   q.k / T = (q/Rq).(k/Rk) / T'   with T' = T / (Rq Rk),
+// the staged passes run on q/Rq and k/Rk at temperature T', and the gradients are scaled back by 1/Rq resp. 1/Rk.
+// (muscle_infonce_prepare divides a row by max(|row|, eps): eps = the bound makes that division the uniform scale.)
+// row_weight (optional, [Q]): the gradients become those of sum_q row_weight[q] loss_q -- the backward of
+// reduction = 'none' with an upstream gradient per row.
 #include <algorithm>
 
 #include "host_util.cuh"
@@ -56,15 +61,40 @@ __global__ void fill_int_kernel(int* p, int v, long long n) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
 }
-// class_sum[0][d] = sum_p pos[p][d]; class_mass[0] = P
-__global__ void __launch_bounds__(256) pos_sum_kernel(const float* pos, long long P, int dim, float* cs, float* cm) {
+// class_sum[0][d] = scale * sum_p pos[p][d]; class_mass[0] = P
+__global__ void __launch_bounds__(256) pos_sum_kernel(const float* pos, long long P, int dim, float scale, float* cs, float* cm) {
   const int d = blockIdx.x * blockDim.x + threadIdx.x;
   if (d < dim) {
     float s = 0.f;
     for (long long p = 0; p < P; ++p) s += pos[p * dim + d];
-    cs[d] = s;
+    cs[d] = s * scale;
   }
   if (d == 0) cm[0] = static_cast<float>(P);
+}
+// Per-row upstream gradient: w[q] *= g[q], gpos[q] *= g[q] (queries are all "class 0", so the class-sorted order of the
+// staged passes is the caller's order), and dproto[0][:] = sum_q gpos[q] ehat[q][:] formed again with the weighted gpos.
+__global__ void __launch_bounds__(128) qk_row_weight_kernel(const float* row_weight, long long Q, int dim,
+                                                            const __nv_bfloat16* ehat, float* w, float* gpos, float* dproto) {
+  const long long r0 = static_cast<long long>(blockIdx.x) * 64;
+  const long long r1 = r0 + 64 < Q ? r0 + 64 : Q;
+  __shared__ float gs[64];
+  if (threadIdx.x < 64) {
+    const long long r = r0 + threadIdx.x;
+    float gv = 0.f;
+    if (r < Q) {
+      const float wt = row_weight[r];
+      w[r] *= wt;
+      gv = gpos[r] * wt;
+      gpos[r] = gv;
+    }
+    gs[threadIdx.x] = gv;
+  }
+  __syncthreads();
+  for (int d = threadIdx.x; d < dim; d += 128) {
+    float acc = 0.f;
+    for (long long r = r0; r < r1; ++r) acc = fmaf(gs[r - r0], __bfloat162float(ehat[r * dim + d]), acc);
+    atomicAdd(dproto + d, acc);
+  }
 }
 
 struct QkFinal {
@@ -99,11 +129,11 @@ __global__ void __launch_bounds__(256) qk_final_kernel(const QkFinal p) {
   }
   if (p.row_loss && lane == 0) p.row_loss[r] = -logf(fmaxf(1.f + p.gpos[r] / p.inv_tau, 1e-30f));
 }
-// dpos[p][d] = scale * dproto[0][d] / P ;  loss = loss_acc * scale
+// dpos[p][d] = scale * key_scale * dproto[0][d] / P ;  loss = loss_acc * scale
 __global__ void __launch_bounds__(256) qk_pos_final_kernel(const float* dproto, const double* lacc, long long P, int dim,
-                                                           float scale, float* dpos, float* loss) {
+                                                           float scale, float key_scale, float* dpos, float* loss) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (dpos && i < P * dim) dpos[i] = scale * dproto[i % dim] / static_cast<float>(P);
+  if (dpos && i < P * dim) dpos[i] = scale * key_scale * dproto[i % dim] / static_cast<float>(P);
   if (i == 0 && loss) *loss = static_cast<float>(*lacc * static_cast<double>(scale));
 }
 
@@ -121,7 +151,26 @@ int muscle_info_nce_fwd_bwd(const float* query, const float* positive_keys, cons
                             int reduction_mean, float* loss_out, float* row_loss_out, float* dquery_out,
                             float* dpositive_out, float* dnegative_out, void* workspace, size_t workspace_bytes,
                             void* stream_) {
+  return muscle_info_nce_fwd_bwd_ex(query, positive_keys, negative_keys, n_query, n_positive, n_negative, dim, temperature,
+                                    reduction_mean, 1.f, 1.f, nullptr, loss_out, row_loss_out, dquery_out, dpositive_out,
+                                    dnegative_out, workspace, workspace_bytes, stream_);
+}
+
+int muscle_info_nce_fwd_bwd_ex(const float* query, const float* positive_keys, const float* negative_keys,
+                               int64_t n_query, int64_t n_positive, int64_t n_negative, int dim, float temperature,
+                               int reduction_mean, float query_norm_bound, float key_norm_bound, const float* row_weight,
+                               float* loss_out, float* row_loss_out, float* dquery_out, float* dpositive_out,
+                               float* dnegative_out, void* workspace, size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!(query_norm_bound > 0.f) || !(key_norm_bound > 0.f) || !isfinite(query_norm_bound) || !isfinite(key_norm_bound))
+    return fail(MUSCLE_ERR_BAD_ARG, "norm bounds must be positive and finite");
+  if (row_weight && row_loss_out) return fail(MUSCLE_ERR_BAD_ARG, "row_loss_out is not available together with row_weight");
+  const float Rq = query_norm_bound, Rk = key_norm_bound;
+  const float user_temperature = temperature;
+  temperature = temperature / (Rq * Rk);      // the staged passes see q/Rq, k/Rk (|q.k| <= 1) at this temperature
+  if (!(temperature >= muscle_infonce_min_temperature()))
+    return fail(MUSCLE_ERR_BAD_ARG, "temperature %g over norm bounds %g x %g is below the supported minimum %g", user_temperature,
+                Rq, Rk, muscle_infonce_min_temperature());
   if (!query || !positive_keys || !negative_keys || !loss_out || !workspace)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (n_query <= 0 || n_positive <= 0 || n_negative <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty input");
@@ -139,18 +188,18 @@ int muscle_info_nce_fwd_bwd(const float* query, const float* positive_keys, cons
   MB_CUDA(cudaMemsetAsync(b + W.zero_lo, 0, W.zero_hi - W.zero_lo, stream));
   // queries: class 0
   MB_CUDA(cudaMemsetAsync(cls, 0, Q * 4, stream));
-  int rc = muscle_infonce_prepare(query, MUSCLE_LAYOUT_PIXEL_MAJOR, 1, Q, dim, cls, 0, 2, 1e-12f, b + W.eq, U(W.bq),
+  int rc = muscle_infonce_prepare(query, MUSCLE_LAYOUT_PIXEL_MAJOR, 1, Q, dim, cls, 0, 2, Rq, b + W.eq, U(W.bq),
                                   F(W.inq), reinterpret_cast<int32_t*>(b + W.pq), U(W.tq), U(W.segq), F(W.stats_tmp),
                                   F(W.stats_tmp) + 2 * dim, b + W.scratch, muscle_infonce_prepare_scratch_bytes(Q), stream_);
   if (rc) return rc;
   // negative keys: class 1
   fill_int_kernel<<<static_cast<unsigned>((K + 255) / 256), 256, 0, stream>>>(cls, 1, K);
   MB_LAUNCH_CHECK();
-  rc = muscle_infonce_prepare(negative_keys, MUSCLE_LAYOUT_PIXEL_MAJOR, 1, K, dim, cls, 0, 2, 1e-12f, b + W.ek, U(W.bk),
+  rc = muscle_infonce_prepare(negative_keys, MUSCLE_LAYOUT_PIXEL_MAJOR, 1, K, dim, cls, 0, 2, Rk, b + W.ek, U(W.bk),
                               F(W.ink), reinterpret_cast<int32_t*>(b + W.pk), U(W.tk), U(W.segk), F(W.stats_tmp),
                               F(W.stats_tmp) + 2 * dim, b + W.scratch, muscle_infonce_prepare_scratch_bytes(K), stream_);
   if (rc) return rc;
-  pos_sum_kernel<<<(dim + 255) / 256, 256, 0, stream>>>(positive_keys, n_positive, dim, F(W.cs), F(W.cm));
+  pos_sum_kernel<<<(dim + 255) / 256, 256, 0, stream>>>(positive_keys, n_positive, dim, 1.f / Rk, F(W.cs), F(W.cm));
   MB_LAUNCH_CHECK();
   if ((rc = muscle_infonce_plan(U(W.tq), W.qp, U(W.tk), W.kp, dim, U(W.uo_qk), stream_))) return rc;
   if ((rc = muscle_infonce_rowsum(b + W.eq, U(W.bq), U(W.tq), W.qp, b + W.ek, U(W.bk), U(W.tk), W.kp, U(W.uo_qk), dim,
@@ -159,6 +208,12 @@ int muscle_info_nce_fwd_bwd(const float* query, const float* positive_keys, cons
   if ((rc = muscle_infonce_mid(b + W.eq, U(W.segq), W.qp, dim, 2, F(W.cs), F(W.cm), F(W.rowsum), temperature, F(W.w),
                                F(W.gpos), reinterpret_cast<double*>(b + W.lacc), F(W.dproto), stream_)))
     return rc;
+  if (row_weight) {
+    MB_CUDA(cudaMemsetAsync(b + W.dproto, 0, static_cast<size_t>(dim) * 4, stream));
+    qk_row_weight_kernel<<<static_cast<unsigned>((Q + 63) / 64), 128, 0, stream>>>(
+        row_weight, Q, dim, reinterpret_cast<const __nv_bfloat16*>(b + W.eq), F(W.w), F(W.gpos), F(W.dproto));
+    MB_LAUNCH_CHECK();
+  }
   const float scale = reduction_mean ? 1.f / static_cast<float>(Q) : 1.f;
   const int rb = PAIR_RB;
   const int n_ctas = device_info().sm_count;
@@ -171,7 +226,7 @@ int muscle_info_nce_fwd_bwd(const float* query, const float* positive_keys, cons
     f.part = F(W.part_q); f.unit_off = U(W.uo_qk); f.n_row_blocks = static_cast<int>(W.qp / rb);
     f.n_col_tiles = static_cast<int>(W.kp / 128); f.n_ctas = n_ctas; f.rb = rb; f.rows_pad = W.qp; f.n = Q; f.dim = dim;
     f.gpos = F(W.gpos); f.proto_sum = F(W.cs); f.inv_mass = 1.f / static_cast<float>(n_positive);
-    f.inv_tau = 1.f / temperature; f.scale = scale; f.dst = dquery_out; f.w = F(W.w); f.row_loss = row_loss_out;
+    f.inv_tau = 1.f / temperature; f.scale = scale / Rq; f.dst = dquery_out; f.w = F(W.w); f.row_loss = row_loss_out;
     if (!dquery_out) { f.dim = 0; }
     qk_final_kernel<<<static_cast<unsigned>((Q + 7) / 8), 256, 0, stream>>>(f);
     MB_LAUNCH_CHECK();
@@ -184,14 +239,14 @@ int muscle_info_nce_fwd_bwd(const float* query, const float* positive_keys, cons
     QkFinal f{};
     f.part = F(W.part_k); f.unit_off = U(W.uo_kq); f.n_row_blocks = static_cast<int>(W.kp / rb);
     f.n_col_tiles = static_cast<int>(W.qp / 128); f.n_ctas = n_ctas; f.rb = rb; f.rows_pad = W.kp; f.n = K; f.dim = dim;
-    f.gpos = nullptr; f.inv_tau = 1.f / temperature; f.scale = scale; f.dst = dnegative_out;
+    f.gpos = nullptr; f.inv_tau = 1.f / temperature; f.scale = scale / Rk; f.dst = dnegative_out;
     qk_final_kernel<<<static_cast<unsigned>((K + 7) / 8), 256, 0, stream>>>(f);
     MB_LAUNCH_CHECK();
   }
   (void)need_grad;
   const long long np = dpositive_out ? n_positive * dim : 1;
   qk_pos_final_kernel<<<static_cast<unsigned>((np + 255) / 256), 256, 0, stream>>>(
-      F(W.dproto), reinterpret_cast<const double*>(b + W.lacc), n_positive, dim, scale, dpositive_out, loss_out);
+      F(W.dproto), reinterpret_cast<const double*>(b + W.lacc), n_positive, dim, scale, 1.f / Rk, dpositive_out, loss_out);
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
 }

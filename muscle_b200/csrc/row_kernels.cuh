@@ -455,30 +455,47 @@ __global__ void __launch_bounds__(SEG_THREADS) mid_kernel(const MidParams p) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) proto[i] = __ldg(p.class_sum + c * D + l * 8 + i) * inv_mass;
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (long long rr = lo; rr < hi; rr += RPP) {   // uniform trip count: shuffles stay converged
-      const long long r = rr + sub;
-      const bool on = r < hi;
-      float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (on) load_row8<D>(p.ehat + r * D, l, v);
-      const float rs_in = on ? p.rowsum[r] : 0.f;   // issued with the row: off the shuffle chain
-      float dot = 0.f;
+    // MID_BATCH passes of RPP rows at a time: all their rows and row sums are requested before the first dot product
+    // (one pass per iteration left four dependent load -> shuffle -> exp chains in a row per 64-row block)
+    constexpr int MID_BATCH = 4;
+    for (long long rr = lo; rr < hi; rr += MID_BATCH * RPP) {   // uniform trip count: shuffles stay converged
+      float v[MID_BATCH][8];
+      float rs_in[MID_BATCH];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) dot = fmaf(v[i], proto[i], dot);
+      for (int j = 0; j < MID_BATCH; ++j) {
+        const long long r = rr + j * RPP + sub;
 #pragma unroll
-      for (int o = TPR / 2; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
-      if (on) {
-        const float pos = dot * p.inv_tau;
-        const float ep = __expf(pos - bt);
-        const float rs = rs_in + ep;
-        const float w = 1.f / rs;
-        const float g = (ep * w - 1.f) * p.inv_tau;
+        for (int i = 0; i < 8; ++i) v[j][i] = 0.f;
+        rs_in[j] = 0.f;
+        if (r < hi) {
+          load_row8<D>(p.ehat + r * D, l, v[j]);
+          rs_in[j] = p.rowsum[r];
+        }
+      }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) acc[i] = fmaf(g, v[i], acc[i]);
-        if (l == 0) {
-          p.rowsum[r] = rs;
-          p.w[r] = w;
-          p.gpos[r] = g;
-          loss += static_cast<double>(bt + logf(rs) - pos);
+      for (int j = 0; j < MID_BATCH; ++j) {
+        if (rr + j * RPP >= hi) break;              // block-uniform
+        const long long r = rr + j * RPP + sub;
+        const bool on = r < hi;
+        float dot = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dot = fmaf(v[j][i], proto[i], dot);
+#pragma unroll
+        for (int o = TPR / 2; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+        if (on) {
+          const float pos = dot * p.inv_tau;
+          const float ep = __expf(pos - bt);
+          const float rs = rs_in[j] + ep;
+          const float w = 1.f / rs;
+          const float g = (ep * w - 1.f) * p.inv_tau;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[i] = fmaf(g, v[j][i], acc[i]);
+          if (l == 0) {
+            p.rowsum[r] = rs;
+            p.w[r] = w;
+            p.gpos[r] = g;
+            loss += static_cast<double>(bt + logf(rs) - pos);
+          }
         }
       }
     }
@@ -605,55 +622,75 @@ __global__ void __launch_bounds__(FINAL_THREADS) final_kernel(const FinalParams 
     }
   }
 
-  auto row_grad = [&](int r, float (&g)[EPL]) {   // r = row of the warp (its pixel is < p.n)
-    const long long q = __shfl_sync(0xffffffffu, q_l, r);
-    const uint32_t bq = __shfl_sync(0xffffffffu, bq_l, r);
-    const int n_slots = __shfl_sync(0xffffffffu, ns_l, r);
-    const float gq = __shfl_sync(0xffffffffu, gq_l, r);
-    const float inv = __shfl_sync(0xffffffffu, inv_l, r);
-    const float inv_mass = __shfl_sync(0xffffffffu, im_l, r);
-    const float key_mass = p.proto_external ? 0.f : inv_mass;   // pixel -> its class mean -> every query of the class
-#pragma unroll
-    for (int k = 0; k < EPL; ++k) g[k] = 0.f;
-    if (!bq) return;
-    const int c = class_of_bits(bq);
-    for (int s = 0; s < n_slots; ++s) {
-      const float* src = p.part + (static_cast<long long>(s) * p.rows_pad + q) * D + lane;
-#pragma unroll
-      for (int k = 0; k < EPL; ++k) g[k] += __ldg(src + 32 * k);
-    }
-    float e[EPL];
-    float dot = 0.f;
-#pragma unroll
-    for (int k = 0; k < EPL; ++k) {
-      const int d = lane + 32 * k;
-      e[k] = __bfloat162float(p.ehat[q * D + d]);
-      g[k] = inv_n * (p.inv_tau * g[k] + gq * __ldg(p.class_sum + c * D + d) + key_mass * __ldg(p.dproto + c * D + d));
-      dot = fmaf(g[k], e[k], dot);
-    }
-    dot = warp_sum(dot);
-#pragma unroll
-    for (int k = 0; k < EPL; ++k) g[k] = inv * (g[k] - e[k] * dot);
-  };
-
+  // Two phases per batch of FINAL_INFLIGHT rows, written out so that the loads of ALL rows of the batch are issued
+  // before the first use: (1) the first two partial-sum slots (predicated; 1.75 slots per row on average at config 2)
+  // and the bf16 row itself, (2) further slots (rare), prototype terms, the normalisation's backward.  With one lambda
+  // per row (an early return for rows outside the loss, a slot loop of variable length) the compiler kept the rows of a
+  // warp strictly one after the other, and neither smaller blocks nor more rows "in flight" changed the 23 us.
+  // A row outside the loss (bq == 0: ignored pixel, or a pixel past n) has n_slots = 0 and inv = 0: it comes out as zeros.
+#ifndef MB_FINAL_INFLIGHT
+#define MB_FINAL_INFLIGHT 4
+#endif
+  constexpr int NF = MB_FINAL_INFLIGHT;
+  static_assert(FINAL_ROWS_PER_WARP % NF == 0, "rows in flight divide the warp's rows");
 #pragma unroll 1
-  for (int r = 0; r < FINAL_ROWS_PER_WARP; r += 2) {
-    const int l0 = warp * FINAL_ROWS_PER_WARP + r, l1 = l0 + 1;   // local pixel index within the block
-    const long long i0 = blk0 + l0, i1 = blk0 + l1;
-    float g0[EPL], g1[EPL];
-    if (i0 < p.n) row_grad(r, g0);       // warp-uniform conditions: the shuffles stay converged
-    if (i1 < p.n) row_grad(r + 1, g1);
-    if (p.layout == MUSCLE_LAYOUT_NCHW) {
+  for (int r = 0; r < FINAL_ROWS_PER_WARP; r += NF) {
+    float g[NF][EPL], e[NF][EPL];
+    long long q[NF];
+    int ns[NF];
+    // ---- phase 1
+#pragma unroll
+    for (int j = 0; j < NF; ++j) {
+      q[j] = __shfl_sync(0xffffffffu, q_l, r + j);
+      ns[j] = __shfl_sync(0xffffffffu, ns_l, r + j);
+      const float* s0 = p.part + q[j] * D + lane;
+      const float* s1 = s0 + p.rows_pad * D;
 #pragma unroll
       for (int k = 0; k < EPL; ++k) {
-        if (i0 < p.n) smem_f[l0 * (D + 1) + lane + 32 * k] = g0[k];
-        if (i1 < p.n) smem_f[l1 * (D + 1) + lane + 32 * k] = g1[k];
+        const float a0 = ns[j] > 0 ? __ldg(s0 + 32 * k) : 0.f;
+        const float a1 = ns[j] > 1 ? __ldg(s1 + 32 * k) : 0.f;
+        g[j][k] = a0 + a1;
+        e[j][k] = __bfloat162float(p.ehat[q[j] * D + lane + 32 * k]);
       }
-    } else {
+    }
+    // ---- phase 2
+#pragma unroll
+    for (int j = 0; j < NF; ++j) {
+      const uint32_t bq = __shfl_sync(0xffffffffu, bq_l, r + j);
+      const float gq = __shfl_sync(0xffffffffu, gq_l, r + j);
+      const float inv = __shfl_sync(0xffffffffu, inv_l, r + j);
+      const float inv_mass = __shfl_sync(0xffffffffu, im_l, r + j);
+      const float key_mass = p.proto_external ? 0.f : inv_mass;   // pixel -> its class mean -> every query of the class
+      const int c = bq ? class_of_bits(bq) : 0;
+      for (int s = 2; s < ns[j]; ++s) {                            // warp-uniform trip count
+        const float* src = p.part + (static_cast<long long>(s) * p.rows_pad + q[j]) * D + lane;
+#pragma unroll
+        for (int k = 0; k < EPL; ++k) g[j][k] += __ldg(src + 32 * k);
+      }
+      float dot = 0.f;
 #pragma unroll
       for (int k = 0; k < EPL; ++k) {
-        if (i0 < p.n) p.dx[i0 * D + lane + 32 * k] = g0[k];
-        if (i1 < p.n) p.dx[i1 * D + lane + 32 * k] = g1[k];
+        const int d = lane + 32 * k;
+        g[j][k] = inv_n * (p.inv_tau * g[j][k] + gq * __ldg(p.class_sum + c * D + d) + key_mass * __ldg(p.dproto + c * D + d));
+        dot = fmaf(g[j][k], e[j][k], dot);
+      }
+      dot = warp_sum(dot);
+#pragma unroll
+      for (int k = 0; k < EPL; ++k) g[j][k] = inv * (g[j][k] - e[j][k] * dot);
+    }
+    // ---- out
+#pragma unroll
+    for (int j = 0; j < NF; ++j) {
+      const int l = warp * FINAL_ROWS_PER_WARP + r + j;      // local pixel index within the block
+      const long long i = blk0 + l;
+      if (i < p.n) {
+        if (p.layout == MUSCLE_LAYOUT_NCHW) {
+#pragma unroll
+          for (int k = 0; k < EPL; ++k) smem_f[l * (D + 1) + lane + 32 * k] = g[j][k];
+        } else {
+#pragma unroll
+          for (int k = 0; k < EPL; ++k) p.dx[i * D + lane + 32 * k] = g[j][k];
+        }
       }
     }
   }

@@ -65,12 +65,13 @@ class _FieldPairLossDecoder(torch.autograd.Function):
 
 
 class FieldLoss(nn.Module):
-    """src/edge.py:175-193.  Only the 5x5 Sobel pair the trainer uses (train_muscle.py:163) is built."""
+    """src/edge.py:175-193.  sobel_size 3 or 5 (src/edge.py:33-43; train_muscle.py:163 passes 5)."""
 
     def __init__(self, num_classes=21, gaussian_size=7, k=100, guassian_sigma=None, sobel_size=5, beta=1e3):
         super().__init__()
-        if sobel_size != 5:
-            raise NotImplementedError("muscle_b200.edge.FieldLoss implements the 5x5 Sobel pair of train_muscle.py:163")
+        if sobel_size not in (3, 5):
+            raise ValueError("sobel_size must be 3 or 5 (src/edge.py:33-43 defines no other filter)")
+        self.sobel_size = int(sobel_size)
         self.num_classes = num_classes
         self.num_fg_cls = num_classes - 1
         self.k = k
@@ -90,8 +91,8 @@ class FieldLoss(nn.Module):
         mag_sum = torch.empty((n, h, w), dtype=torch.float32, device=dev)
         plane_max = torch.empty((n, c - 1), dtype=torch.int32, device=dev)
         counts = torch.empty((n, c - 1, 3), dtype=torch.int32, device=dev)
-        call("muscle_field_edges", dev, seg_map.detach().contiguous().data_ptr(), lab.data_ptr(), n, c, h, w,
-             self.beta, int(step), prob.data_ptr(), mag.data_ptr(), orient.data_ptr(), pos.data_ptr(),
+        call("muscle_field_edges_sobel", dev, seg_map.detach().contiguous().data_ptr(), lab.data_ptr(), n, c, h, w,
+             self.beta, int(step), self.sobel_size, prob.data_ptr(), mag.data_ptr(), orient.data_ptr(), pos.data_ptr(),
              mag_sum.data_ptr(), plane_max.data_ptr(), counts.data_ptr())
         return dict(mag_sum=mag_sum, orient=orient, pos=pos, counts=counts, label=lab, mag=mag)
 

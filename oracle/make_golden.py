@@ -241,6 +241,31 @@ def gen_fieldloss(src):
                 pos=pos, out_idx_0_14=out_i, in_idx_0_14=in_i, gate_false=(loss0 is False), big_k_is_zero=(not torch.is_tensor(loss1) and loss1 == 0))
 
 
+def gen_fieldloss_sobel3(src):
+    """FieldLoss built with sobel_size=3 (src/edge.py:33-35; the trainer passes 5, the constructor accepts both)."""
+    g = torch.Generator().manual_seed(31)
+    n, c, h, w, ch, k, step = 2, 21, 40, 48, 16, 10, 2
+    label = torch.zeros(n, 20)
+    label[0, [0, 7]] = 1
+    label[1, [7, 11]] = 1
+    label_bg = torch.cat([torch.ones(n, 1), label], 1)
+    noise = F.avg_pool2d(torch.randn(n, c, h, w, generator=g), 9, 1, 4, count_include_pad=False)
+    noise = noise.masked_fill(~label_bg.bool()[:, :, None, None], -1e4)
+    seg = noise * 3 + 0.05 * torch.randn(n, c, h, w, generator=g)
+    mask = noise * 2 + 0.3 * torch.randn(n, c, h, w, generator=g)
+    dense = torch.randn(n, ch, h, w, generator=g).requires_grad_()
+    crit = src.edge.FieldLoss(sobel_size=3, beta=1e2, k=k)
+    random.seed(91)
+    loss, mag = crit(seg, dense, mask, label_bg, step)
+    assert torch.is_tensor(loss), "fixture must exercise the bifilter"
+    gd, = torch.autograd.grad(loss, dense)
+    with torch.no_grad():
+        edges = crit.fg_edge(seg, label_bg, reduction=False)
+        _, orient = crit.quantize(edges.clone())
+    return dict(seg=seg, dense=dense.detach(), mask=mask, label_bg=label_bg, k=k, step=step, beta=1e2, py_seed=91,
+                loss=loss.detach(), mag=mag, gd=gd, orient=orient.to(torch.uint8))
+
+
 def _reference_functions(rel_path, names):
     """Compiles the named top-level functions of a reference SCRIPT (which cannot be imported: it pulls
     in data / cv2 / tensorboardX at module level) from where it lies, and returns them."""
@@ -400,7 +425,8 @@ def main():
     src = reference_loader.load()
     os.makedirs(OUT, exist_ok=True)
     jobs = dict(info_nce=gen_info_nce, dense_infonce=gen_dense_infonce, imc=gen_imc, pixpro=gen_pixpro,
-                emd=gen_emd, emd_static=gen_emd_static, heads=gen_heads, fieldloss=gen_fieldloss, cam_norms=gen_cam_norms,
+                emd=gen_emd, emd_static=gen_emd_static, heads=gen_heads, fieldloss=gen_fieldloss,
+                fieldloss_sobel3=gen_fieldloss_sobel3, cam_norms=gen_cam_norms,
                 er_loss=gen_er_loss, cls_losses=gen_cls_losses, decoder_tail=gen_decoder_tail, irn=gen_irn)
     only = sys.argv[1:]
     for name, fn in jobs.items():

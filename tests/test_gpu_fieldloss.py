@@ -80,6 +80,24 @@ def test_fieldloss_gates(golden):
         crit(g["seg"], g["dense"], g["mask"], g["label_bg"], g["step"])      # CPU tensors: no fallback
 
 
+def test_fieldloss_sobel3_golden(golden):
+    """FieldLoss(sobel_size=3): the reference class's other filter pair (src/edge.py:33-35) against a fixture minted from
+    the reference built that way."""
+    from muscle_b200.edge import FieldLoss
+    g = golden("fieldloss_sobel3")
+    crit = FieldLoss(sobel_size=3, beta=g["beta"], k=g["k"])
+    dg = g["dense"].cuda().requires_grad_()
+    random.seed(g["py_seed"])
+    out, mag = crit(g["seg"].cuda(), dg, g["mask"].cuda(), g["label_bg"].cuda(), g["step"])
+    torch.testing.assert_close(mag.cpu(), g["mag"], rtol=1e-4, atol=1e-4)
+    assert torch.is_tensor(out)
+    out.backward()
+    assert abs(out.item() - g["loss"].item()) <= 1e-3 * abs(g["loss"].item()) + 1e-7, (out.item(), g["loss"].item())
+    assert _cos(dg.grad.cpu(), g["gd"]) >= 0.999
+    with pytest.raises(ValueError):
+        FieldLoss(sobel_size=7)
+
+
 @pytest.mark.parametrize("n,h,w,ch,k,step", [(2, 64, 64, 256, 16, 3), (3, 96, 80, 64, 24, 5)])
 def test_fieldloss_matches_oracle(n, h, w, ch, k, step):
     from muscle_b200.edge import FieldLoss

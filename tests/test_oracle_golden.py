@@ -144,6 +144,21 @@ def test_pcm_gradients(golden):
     close(b.grad, g["pcm_gb"], rtol=2e-3, atol=2e-5)
 
 
+def test_fieldloss_sobel3(golden):
+    """the constructor's other filter size (src/edge.py:33-35)"""
+    g = golden("fieldloss_sobel3")
+    edges = O.class_edges(g["seg"], g["label_bg"], beta=g["beta"], sobel_size=3)
+    _, orient = O.orient_quantize(edges)
+    assert (orient.to(torch.uint8) == g["orient"]).float().mean() > 0.9999      # (atan2 of two conv2d results: same ops)
+    dense = g["dense"].clone().requires_grad_()
+    rng = random.Random(g["py_seed"])
+    loss, mag_sum = O.fieldloss_forward(g["seg"], dense, g["mask"], g["label_bg"], step=g["step"], k=g["k"],
+                                        beta=g["beta"], sobel_size=3, rng=rng)
+    close(mag_sum, g["mag"], rtol=1e-4, atol=1e-4)
+    close(loss, g["loss"], rtol=1e-4, atol=1e-7)
+    close(torch.autograd.grad(loss, dense)[0], g["gd"], rtol=1e-3, atol=1e-9)
+
+
 def test_fieldloss(golden):
     g = golden("fieldloss")
     edges = O.class_edges(g["seg"], g["label_bg"], beta=g["beta"], sobel_size=5)
