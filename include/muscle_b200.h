@@ -218,6 +218,21 @@ int muscle_info_nce_fwd_bwd(const float* query, const float* positive_keys,
                             float* loss_out, float* row_loss_out, float* dquery_out,
                             float* dpositive_out, float* dnegative_out, void* workspace,
                             size_t workspace_bytes, void* stream);
+/* The same for rows of ANY norm (the reference, src/loss_multilabel.py:9-21, never normalises) and with an upstream
+ * gradient per row (the backward of reduction='none').  query_norm_bound >= max_q |q|, key_norm_bound >= max(max_k |k|,
+ * |mean_p positive_keys[p]|): the passes then run on q / query_norm_bound and k / key_norm_bound at temperature / (the
+ * product of the bounds), which must stay >= MUSCLE_MIN_TEMPERATURE; results are those of the unscaled problem.
+ * muscle_info_nce_fwd_bwd is the case of both bounds = 1 (rows shorter than 1 keep their length).
+ * row_weight [Q] or NULL: the three gradients become those of sum_q row_weight[q] * loss_q (times 1/Q when
+ * reduction_mean); loss_out stays the unweighted value and row_loss_out must be NULL. */
+#define MUSCLE_MIN_TEMPERATURE 0.0125f
+int muscle_info_nce_fwd_bwd_ex(const float* query, const float* positive_keys,
+                               const float* negative_keys, int64_t n_query, int64_t n_positive,
+                               int64_t n_negative, int dim, float temperature, int reduction_mean,
+                               float query_norm_bound, float key_norm_bound, const float* row_weight,
+                               float* loss_out, float* row_loss_out, float* dquery_out,
+                               float* dpositive_out, float* dnegative_out, void* workspace,
+                               size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * CAM-weighted (soft) prototype pooling and its gradient scatter (north_star: "CAM-weighted pooling of

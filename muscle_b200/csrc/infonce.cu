@@ -141,7 +141,7 @@ constexpr int kPoly = 1;
 bool poly_ok(float temperature) { return pair_poly_ok(kLog2e / temperature); }
 // exp((s - 1)/T) leaves the fp32 range for every s < 0 once log2(e)/T > 126: refuse instead of returning
 // a silently wrong loss (the reference works in log space and has no such limit)
-constexpr float kMinTemperature = 0.0125f;
+constexpr float kMinTemperature = MUSCLE_MIN_TEMPERATURE;
 
 template <int MODE>
 int launch_pair_dim(int dim, bool poly, const void* ehat_rows, int64_t rows_pad,

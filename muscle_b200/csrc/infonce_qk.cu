@@ -13,6 +13,8 @@
 // row_weight (optional, [Q]): the gradients become those of sum_q row_weight[q] loss_q -- the backward of
 // reduction = 'none' with an upstream gradient per row.
 #include <algorithm>
+#include <cmath>
+#include <cuda_bf16.h>
 
 #include "host_util.cuh"
 #include "pair_kernel.cuh"
@@ -168,9 +170,9 @@ int muscle_info_nce_fwd_bwd_ex(const float* query, const float* positive_keys, c
   const float Rq = query_norm_bound, Rk = key_norm_bound;
   const float user_temperature = temperature;
   temperature = temperature / (Rq * Rk);      // the staged passes see q/Rq, k/Rk (|q.k| <= 1) at this temperature
-  if (!(temperature >= muscle_infonce_min_temperature()))
-    return fail(MUSCLE_ERR_BAD_ARG, "temperature %g over norm bounds %g x %g is below the supported minimum %g", user_temperature,
-                Rq, Rk, muscle_infonce_min_temperature());
+  if (!(temperature >= MUSCLE_MIN_TEMPERATURE))
+    return fail(MUSCLE_ERR_BAD_ARG, "temperature %g over norm bounds %g x %g is below the supported minimum %g",
+                static_cast<double>(user_temperature), static_cast<double>(Rq), static_cast<double>(Rk), static_cast<double>(MUSCLE_MIN_TEMPERATURE));
   if (!query || !positive_keys || !negative_keys || !loss_out || !workspace)
     return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (n_query <= 0 || n_positive <= 0 || n_negative <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty input");

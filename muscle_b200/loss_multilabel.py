@@ -46,6 +46,16 @@ def image_level_contrast(emb, label):
     return loss
 
 
+def image_level_contrast_nosync(emb, label):
+    """The same loss without the device->host read: -> (loss, n_used), both 0-dim CUDA tensors.  `loss` is 0 (with a
+    zero gradient) when `n_used` == 0, i.e. where the reference returns python ``0``; a training loop can add it
+    unconditionally and never stalls the stream (SURVEY.md 7.3 asks for this form beside the reference's convention)."""
+    require_cuda_f32(emb, "emb")
+    if not label.is_cuda:
+        raise RuntimeError("muscle_b200: `label` must be a CUDA tensor (there is no CPU path)")
+    return _ImageLevelContrast.apply(emb, label)
+
+
 class _PixPro(torch.autograd.Function):
     @staticmethod
     def forward(ctx, fm1s, fm2s, box1, box2, max_px):
@@ -241,47 +251,66 @@ class EMD:
 
 
 class _InfoNce(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, query, positive_keys, negative_keys, temperature, mode, dim_pad):
-        lib = _lib.load()
-        dev = query.device
+    """mean / sum: value and the three gradients in ONE C call at forward time (backward multiplies by the upstream
+    scalar).  none: forward = the [Q] row losses; backward calls the C path again with the upstream gradient as per-row
+    weights (muscle_info_nce_fwd_bwd_ex)."""
 
+    @staticmethod
+    def _run(q, p, k, temperature, mode_mean, rq, rk, row_weight, want_rows, need):
+        lib = _lib.load()
+        dev = q.device
+        nq, npos, nk, dim_pad = q.shape[0], p.shape[0], k.shape[0], q.shape[1]
+        wsb = lib.muscle_info_nce_workspace_bytes(nq, nk, dim_pad)
+        ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+        loss = torch.empty((), dtype=torch.float32, device=dev)
+        rows = torch.empty(nq, dtype=torch.float32, device=dev) if want_rows else None
+        dq = torch.empty_like(q) if need[0] else None
+        dp = torch.empty_like(p) if need[1] else None
+        dk = torch.empty_like(k) if need[2] else None
+        call("muscle_info_nce_fwd_bwd_ex", dev, q.data_ptr(), p.data_ptr(), k.data_ptr(), nq, npos, nk, dim_pad,
+             float(temperature), 1 if mode_mean else 0, float(rq), float(rk), ptr(row_weight), loss.data_ptr(), ptr(rows),
+             ptr(dq), ptr(dp), ptr(dk), ws.data_ptr(), wsb)
+        return loss, rows, dq, dp, dk
+
+    @staticmethod
+    def forward(ctx, query, positive_keys, negative_keys, temperature, mode, dim_pad, rq, rk):
         def padded(t):      # zero columns change no dot product; the tensor-pipe passes need dim in {64,128,256}
             t = t.contiguous()
             return t if t.shape[1] == dim_pad else torch.nn.functional.pad(t, (0, dim_pad - t.shape[1]))
 
         q, p, k = padded(query), padded(positive_keys), padded(negative_keys)
-        nq, npos, nk = q.shape[0], p.shape[0], k.shape[0]
-        wsb = lib.muscle_info_nce_workspace_bytes(nq, nk, dim_pad)
-        ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
-        loss = torch.empty((), dtype=torch.float32, device=dev)
-        rows = torch.empty(nq, dtype=torch.float32, device=dev) if mode == "none" else None
-        need = ctx.needs_input_grad
-        dq = torch.empty_like(q) if need[0] else None
-        dp = torch.empty_like(p) if need[1] else None
-        dk = torch.empty_like(k) if need[2] else None
-        call("muscle_info_nce_fwd_bwd", dev, q.data_ptr(), p.data_ptr(), k.data_ptr(), nq, npos, nk, dim_pad,
-             float(temperature), 1 if mode == "mean" else 0, loss.data_ptr(), ptr(rows), ptr(dq), ptr(dp), ptr(dk),
-             ws.data_ptr(), wsb)
-        d = query.shape[1]
+        need = ctx.needs_input_grad[:3]
+        ctx.mode, ctx.d = mode, query.shape[1]
+        if mode == "none":
+            _, rows, _, _, _ = _InfoNce._run(q, p, k, temperature, False, rq, rk, None, True, (False, False, False))
+            ctx.save_for_backward(q, p, k)
+            ctx.args = (float(temperature), float(rq), float(rk), tuple(need))
+            return rows
+        loss, _, dq, dp, dk = _InfoNce._run(q, p, k, temperature, mode == "mean", rq, rk, None, False, need)
+        d = ctx.d
         ctx.save_for_backward(*(None if t is None else t[:, :d] for t in (dq, dp, dk)))
-        ctx.mode = mode
-        return rows if mode == "none" else loss
+        return loss
 
     @staticmethod
     def backward(ctx, g):
-        dq, dp, dk = ctx.saved_tensors
+        d = ctx.d
         if ctx.mode == "none":
-            raise NotImplementedError("info_nce(reduction='none') is forward-only here; reduce before backward")
+            q, p, k = ctx.saved_tensors
+            temperature, rq, rk, need = ctx.args
+            gw = g.detach().to(torch.float32).contiguous()
+            _, _, dq, dp, dk = _InfoNce._run(q, p, k, temperature, False, rq, rk, gw, False, need)
+            return (None if dq is None else dq[:, :d], None if dp is None else dp[:, :d], None if dk is None else dk[:, :d],
+                    None, None, None, None, None)
+        dq, dp, dk = ctx.saved_tensors
         return (None if dq is None else dq * g, None if dp is None else dp * g, None if dk is None else dk * g,
-                None, None, None)
+                None, None, None, None, None)
 
 
 def info_nce(query, positive_keys, negative_keys, temperature=0.1, reduction="mean"):
-    """src/loss_multilabel.py:9-21.  query [Q,D], positive_keys [P,D], negative_keys [K,D], fp32 CUDA,
-    rows unit-norm (the reference does not normalise either; it is the caller's job — here it is also
-    a precondition of the tensor-pipe passes and is checked).  reduction in {'mean','sum','none'};
-    'none' returns the [Q] losses without a backward."""
+    """src/loss_multilabel.py:9-21.  query [Q,D], positive_keys [P,D], negative_keys [K,D], fp32 CUDA, rows of any norm
+    (the reference does not normalise and neither does this: the largest row norms are read once -- one device->host
+    copy of two floats -- and handed to the C path as uniform scales, see muscle_info_nce_fwd_bwd_ex).
+    reduction in {'mean','sum','none'}, all three differentiable."""
     for name, t in (("query", query), ("positive_keys", positive_keys), ("negative_keys", negative_keys)):
         require_cuda_f32(t, name)
         if t.dim() != 2 or t.shape[1] != query.shape[1]:
@@ -291,11 +320,14 @@ def info_nce(query, positive_keys, negative_keys, temperature=0.1, reduction="me
     d = query.shape[1]
     if d > 256:
         raise ValueError("info_nce supports D <= 256 (got %d)" % d)
-    worst = max(float(query.detach().norm(dim=1).max()), float(negative_keys.detach().norm(dim=1).max()))
-    if worst > 1.0 + 1e-3:
-        raise ValueError("info_nce expects unit-norm rows (max norm %.4f): normalise the embeddings first" % worst)
+    with torch.no_grad():
+        rq = query.norm(dim=1).max()
+        rk = torch.maximum(negative_keys.norm(dim=1).max(), positive_keys.mean(0).norm())
+        rq, rk = (float(v) for v in torch.stack([rq, rk]).cpu())
+    if not (rq > 0.0 and rk > 0.0 and rq < float("inf") and rk < float("inf")):
+        raise ValueError("info_nce needs finite, non-zero queries and keys (max norms %g, %g)" % (rq, rk))
     dim_pad = 64 if d <= 64 else (128 if d <= 128 else 256)
-    return _InfoNce.apply(query, positive_keys, negative_keys, temperature, reduction, dim_pad)
+    return _InfoNce.apply(query, positive_keys, negative_keys, temperature, reduction, dim_pad, rq, rk)
 
 
 # --------------------------------------------------------------------------------------------------

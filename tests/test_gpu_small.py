@@ -44,6 +44,25 @@ def test_imc_golden(golden):
         _close(emb2.grad, g["ge2"], rtol=1e-3, atol=1e-6)
 
 
+def test_imc_nosync_variant(golden):
+    """(loss, n_used) on the device, no host read: the same value and gradient; 0 with a zero gradient where the
+    reference returns python 0"""
+    from muscle_b200.loss_multilabel import image_level_contrast_nosync
+    g = golden("imc")
+    emb = g["emb"].cuda().requires_grad_()
+    loss, n_used = image_level_contrast_nosync(emb, g["label"].cuda())
+    assert loss.is_cuda and n_used.is_cuda and int(n_used) > 0
+    loss.backward()
+    _close(loss, g["loss"], rtol=1e-4)
+    _close(emb.grad, g["ge"], rtol=1e-3, atol=1e-6)
+    label0 = torch.zeros(3, 20)
+    label0[:, 1] = 1
+    e0 = torch.randn(3, 48).cuda().requires_grad_()
+    z, n0 = image_level_contrast_nosync(e0, label0.cuda())
+    z.backward()
+    assert int(n0) == 0 and float(z.detach()) == 0.0 and float(e0.grad.abs().max()) == 0.0
+
+
 @pytest.mark.parametrize("batch,dim", [(16, 640), (64, 384), (256, 640), (5, 33)])
 def test_imc_oracle_sizes(batch, dim):
     from muscle_b200.loss_multilabel import image_level_contrast
