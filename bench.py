@@ -609,12 +609,14 @@ def pool_record(env, n, dim, num_classes, steps):
     b_f = n * dim * 2 + n * num_classes * 4 + num_classes * dim * 4
     b_b = n * dim * (2 + 4) + n * num_classes * (4 + 4) + 2 * num_classes * dim * 4
     rec = {}
+    tkey = "pool_%dx%dx%d" % (n, dim, num_classes)
     for name, t, nbytes, note in (("fwd", t_f, b_f, "N*D*2 (bf16 rows) + N*C*4 (weights) + C*D*4 (SURVEY 8d)"),
                                   ("bwd", t_b, b_b, "N*D*(2 read + 4 write) + N*C*(4 read + 4 write) + 2*C*D*4")):
         ach = nbytes / t / 1e9
-        rec[name] = dict(bound="hbm", kernel="pool_%s_kernel" % name, achieved=ach, peak=pk["hbm"], unit="GB/s",
+        kern = ("pool_tc_fwd_kernel<%d> + pool_tc_finish_kernel" % dim) if name == "fwd" else ("pool_tc_bwd_kernel<%d>" % dim)
+        rec[name] = dict(bound="hbm", kernel=kern, achieved=ach, peak=pk["hbm"], unit="GB/s",
                          frac=ach / pk["hbm"], us_per_launch=1e6 * t, algorithmic_bytes=nbytes, algorithmic=note,
-                         traffic=None, peak_source=pk["source"])
+                         traffic=traffic_for(tkey, "pool_" + name)[0], peak_source=pk["source"])
     rec["shape"] = dict(pixels=n, dim=dim, num_classes=num_classes, e="bf16", w="f32")
     return rec
 
@@ -651,6 +653,9 @@ def main():
     if env.world == 1 and args.workload is None and not args.no_sub:
         c3 = WORKLOADS["config3"]       # the largest single-GPU configuration: 65 536 pixels, D = 128, 21 classes
         pool = pool_record(env, c3["global_batch"] * c3["h"] * c3["w"], c3["dim"], NUM_CLASSES, args.steps)
+        # ... and at the headline workload's size (config 4: 262 144 pixels): at 65 536 pixels the whole input is 22 MB, a
+        # few microseconds of HBM time, and launch + pipeline fill dominate the launch
+        pool["at_config4_size"] = pool_record(env, wl["global_batch"] * wl["h"] * wl["w"], wl["dim"], NUM_CLASSES, args.steps)
     ops = None
     if env.world == 1 and args.workload is None and not args.no_sub:
         # the other members of the path (PCM, CAM head, IMC, PixPro, EMD, FieldLoss, ER loss, ...): device time fwd+bwd

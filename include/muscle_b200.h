@@ -465,12 +465,6 @@ int muscle_emd_static_fwd_bwd(const float* flat1, const float* flat2, const int6
                               float* dflat1_out, int64_t total1, void* scratch,
                               size_t scratch_bytes, void* stream);
 
-/* ------------------------------------------------------------------------------------------
- * Debug / unit-test entry points for the tcgen05 building blocks (used by tests/ only).
- * sim: S[128,128] = A[128,dim] B[128,dim]^T ;  tsg: G[128,dim] = bf16(S) B  (A from TMEM). */
-int muscle_debug_tile(const void* a_bf16, const void* b_bf16, int dim, float* s_out,
-                      float* g_out, void* stream);
-
 /* SURVEY.md 8f rank 2 — the decoder tail (src/MuSCLe.py:285-286: dense_ft = bilinear up-sampling of p3_dec, seg_map =
  * fuse_dec(dense_ft)) feeding FieldLoss without ever materialising dense_ft: the 1x1 fuse_dec commutes with the
  * up-sampling, so seg_map = upsample(muscle_conv1x1_fwd(p3_dec)) (21 channels instead of 256 at full resolution), and

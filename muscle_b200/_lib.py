@@ -134,7 +134,6 @@ _SIGNATURES = {
     "muscle_info_nce_fwd_bwd_ex": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_float, c_int,
                                            c_float, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                            c_void_p, c_size_t, c_void_p]),
-    "muscle_debug_tile": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
 }
 
 _lib = None
@@ -160,6 +159,23 @@ def load():
         fn.argtypes = args
     _lib = lib
     return lib
+
+
+DIAG_LIB_PATH = os.path.join(_HERE, "lib", "libmuscle_b200_diag.so")
+_diag = None
+
+
+def load_diag():
+    """The test fixture library (include/muscle_b200_diag.h): one-tile checks of the tcgen05 building blocks."""
+    global _diag
+    if _diag is None:
+        if not os.path.exists(DIAG_LIB_PATH):
+            raise RuntimeError("muscle_b200: %s not found. Build it with `python -m muscle_b200.build`." % DIAG_LIB_PATH)
+        lib = ctypes.CDLL(DIAG_LIB_PATH)
+        lib.muscle_debug_tile.restype = c_int
+        lib.muscle_debug_tile.argtypes = [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]
+        _diag = lib
+    return _diag
 
 
 def check(rc: int, what: str):

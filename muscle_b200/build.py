@@ -18,7 +18,9 @@ LIBDIR = os.path.join(HERE, "lib")
 OBJDIR = os.path.join(LIBDIR, "obj")
 LIB = os.path.join(LIBDIR, "libmuscle_b200.so")
 
-SOURCES = ["infonce.cu", "debug_tile.cu", "small_losses.cu", "pcm.cu", "fieldloss.cu", "emd.cu", "infonce_qk.cu", "pool.cu", "cls_losses.cu", "er.cu", "irn.cu"]
+DIAG_LIB = os.path.join(LIBDIR, "libmuscle_b200_diag.so")    # test fixture (include/muscle_b200_diag.h), not the product
+
+SOURCES = ["infonce.cu", "small_losses.cu", "pcm.cu", "fieldloss.cu", "emd.cu", "infonce_qk.cu", "pool.cu", "cls_losses.cu", "er.cu", "irn.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -44,7 +46,7 @@ def _newest_dep():
 
 def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJDIR, exist_ok=True)
-    if not force and os.path.exists(LIB) and os.path.getmtime(LIB) >= _newest_dep():
+    if not force and os.path.exists(LIB) and os.path.exists(DIAG_LIB) and min(os.path.getmtime(LIB), os.path.getmtime(DIAG_LIB)) >= _newest_dep():
         return LIB
     nvcc = _nvcc()
 
@@ -62,11 +64,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
         return obj
 
     with ThreadPoolExecutor(max_workers=4) as ex:
-        objs = list(ex.map(compile_one, SOURCES))
-    cmd = [nvcc, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
-    r = subprocess.run(cmd, capture_output=True, text=True)
-    if r.returncode != 0:
-        raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
+        objs = list(ex.map(compile_one, SOURCES + ["debug_tile.cu"]))
+    for lib, members in ((LIB, objs[:-1]), (DIAG_LIB, objs[-1:])):
+        cmd = [nvcc, "-shared", "-o", lib, *members, "-gencode", "arch=compute_100a,code=sm_100a"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
     return LIB
 
 

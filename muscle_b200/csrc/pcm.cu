@@ -763,8 +763,8 @@ int launch_pair_v(const CUtensorMap& tm_g, const CUtensorMap& tm_row, const CUte
 template <int MODE>
 int launch_pair(const CUtensorMap& tm_g, const CUtensorMap& tm_row, const CUtensorMap& tm_col, const PpParams& prm,
                 int items, cudaStream_t stream) {
-  if (MODE == PCM_BWD) return launch_pair_v<MODE, 2, 2>(tm_g, tm_row, tm_col, prm, items, stream);
-  return launch_pair_v<MODE, 3, 2>(tm_g, tm_row, tm_col, prm, items, stream);
+  if constexpr (MODE == PCM_BWD) return launch_pair_v<MODE, 2, 2>(tm_g, tm_row, tm_col, prm, items, stream);
+  else return launch_pair_v<MODE, 3, 2>(tm_g, tm_row, tm_col, prm, items, stream);
 }
 
 }  // namespace

@@ -180,8 +180,9 @@ def dense_infonce_value_and_grad(x, cls, temperature=0.1, num_classes=21, eps=1e
 
 
 def debug_tile(a_bf16: torch.Tensor, b_bf16: torch.Tensor):
-    """S = A B^T [128,128] and G = bf16(S) B [128,D] through the tcgen05 building blocks (tests)."""
-    lib = _lib.load()
+    """S = A B^T [128,128] and G = bf16(S) B [128,D] through the tcgen05 building blocks: a test fixture, served by
+    libmuscle_b200_diag.so (include/muscle_b200_diag.h), not by the product library."""
+    lib = _lib.load_diag()
     assert a_bf16.dtype == torch.bfloat16 and b_bf16.dtype == torch.bfloat16
     assert a_bf16.shape == b_bf16.shape and a_bf16.shape[0] == 128
     a = a_bf16.contiguous()
@@ -191,5 +192,6 @@ def debug_tile(a_bf16: torch.Tensor, b_bf16: torch.Tensor):
     g = torch.empty(128, d, dtype=torch.float32, device=a.device)
     with torch.cuda.device(a.device):
         rc = lib.muscle_debug_tile(a.data_ptr(), b.data_ptr(), d, s.data_ptr(), g.data_ptr(), _stream_ptr(a.device))
-    _lib.check(rc, "debug_tile")
+    if rc != 0:
+        raise RuntimeError("muscle_debug_tile failed (code %d)" % rc)
     return s, g

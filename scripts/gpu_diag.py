@@ -13,7 +13,7 @@ print(torch.cuda.get_device_name(0))
 def tile_check(d):
     a = (torch.randn(128, d) / d ** 0.5).to(torch.bfloat16)
     b = (torch.randn(128, d) / d ** 0.5).to(torch.bfloat16)
-    s, g = M.debug_tile(a.to(dev), b.to(dev))
+    s, g = M.ops.debug_tile(a.to(dev), b.to(dev))
     torch.cuda.synchronize()
     s_ref = a.float() @ b.float().t()
     g_ref = s_ref.to(torch.bfloat16).float() @ b.float()

@@ -49,6 +49,15 @@ def test_library_exports_are_plain_c(lib):
     assert "torch" not in ldd and "c10" not in ldd
 
 
+def test_diag_fixture_is_a_library_of_its_own(lib):
+    """muscle_debug_tile (include/muscle_b200_diag.h) is a test fixture: built, but not inside the product library"""
+    from muscle_b200 import _lib
+    diag = _lib.load_diag()
+    assert diag.muscle_debug_tile is not None
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "muscle_debug_tile" not in out and "debug_tile_kernel" not in out
+
+
 def test_size_helpers_without_gpu(lib):
     assert lib.muscle_version() >= 200
     assert lib.muscle_pad_rows(1) == 256 and lib.muscle_pad_rows(256) == 256 and lib.muscle_pad_rows(257) == 512

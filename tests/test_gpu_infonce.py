@@ -28,7 +28,8 @@ def test_tcgen05_tile_blocks(M, d):
     torch.manual_seed(d)
     a = (torch.randn(128, d) / d ** 0.5).to(torch.bfloat16)
     b = (torch.randn(128, d) / d ** 0.5).to(torch.bfloat16)
-    s, g = M.debug_tile(a.cuda(), b.cuda())
+    from muscle_b200.ops import debug_tile       # libmuscle_b200_diag.so: a test fixture, not in the product library
+    s, g = debug_tile(a.cuda(), b.cuda())
     s_ref = a.float() @ b.float().t()
     g_ref = s_ref.to(torch.bfloat16).float() @ b.float()
     torch.testing.assert_close(s.cpu(), s_ref, rtol=1e-3, atol=1e-3)
