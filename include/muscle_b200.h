@@ -488,6 +488,18 @@ int muscle_conv1x1_fwd(const float* x, const float* weight, const float* bias, i
 int muscle_irn_transition_init(const float* affinity, int n, float beta, float* colsum_scratch,
                                float* trans_out, void* stream);
 int muscle_irn_mask_edge(const float* x, const float* edge, int planes, int hw, float* y, void* stream);
+/* The squarings T <- T T (src/indexing.py:120-121) and the final product (x * (1 - edge)) T (:147) as fp32-ACCURATE products
+ * on the tensor pipe: every fp32 value is split into three bf16 parts (x = h + m + l, 24 mantissa bits) and
+ * A B ~= Ah Bh + Ah Bm + Am Bh + Ah Bl + Al Bh + Am Bm is accumulated in fp32 (TMEM); a transition matrix has no
+ * negative entries, so an output entry is as accurate as its terms (~2^-23 relative).
+ *   muscle_irn_split3: parts [3][rows_pad][cols_pad] bf16 (hi, mid, lo), zero outside rows x cols; pads multiples of 128.
+ *   muscle_irn_matmul_split3: C = A B from the parts of A [m_pad, k_pad] and B [k_pad, n_pad]; c_out fp32 [m, n] (row-major,
+ *   unpadded) and / or c_parts_out [3][m_pad][n_pad] (the next squaring's operand: no separate split pass); either may be
+ *   NULL, not both; the output must not alias an input. */
+size_t muscle_irn_split3_bytes(int rows_pad, int cols_pad);
+int muscle_irn_split3(const float* x, int rows, int cols, int rows_pad, int cols_pad, void* parts, void* stream);
+int muscle_irn_matmul_split3(const void* a_parts, const void* b_parts, int m_pad, int k_pad, int n_pad, int m, int n,
+                             float* c_out, void* c_parts_out, void* stream);
 
 #ifdef __cplusplus
 }

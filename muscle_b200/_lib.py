@@ -116,6 +116,9 @@ _SIGNATURES = {
     "muscle_conv1x1_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_void_p]),
     "muscle_irn_transition_init": (c_int, [c_void_p, c_int, c_float, c_void_p, c_void_p, c_void_p]),
     "muscle_irn_mask_edge": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "muscle_irn_split3_bytes": (c_size_t, [c_int, c_int]),
+    "muscle_irn_split3": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "muscle_irn_matmul_split3": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "muscle_crops_fwd": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int64, c_void_p,
                                  c_void_p]),
     "muscle_crops_bwd": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int64, c_void_p,
