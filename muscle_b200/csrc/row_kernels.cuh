@@ -86,10 +86,24 @@ __global__ void __launch_bounds__(1024) class_scan_kernel(uint32_t* hist, int n_
   // per 32 chunks.
   const int per = (n_blk + 31) / 32;
   const int b0 = lane * per;
+  // (the run's counts stay in registers for the rewrite below when they fit: the second pass over hist[] was `per`
+  //  dependent L2 round trips, the loads not being movable across the stores to the same array)
+  constexpr int SCAN_KEEP = 16;
+  uint32_t kept[SCAN_KEEP];
+  const bool keep = per <= SCAN_KEEP;
   uint32_t mine = 0;
-  if (warp <= C)
-    for (int i = 0; i < per; ++i)
-      if (b0 + i < n_blk) mine += hist[static_cast<size_t>(b0 + i) * MAX_BINS + warp];
+  if (warp <= C) {
+    if (keep) {
+#pragma unroll
+      for (int i = 0; i < SCAN_KEEP; ++i) {
+        kept[i] = (i < per && b0 + i < n_blk) ? hist[static_cast<size_t>(b0 + i) * MAX_BINS + warp] : 0u;
+        mine += kept[i];
+      }
+    } else {
+      for (int i = 0; i < per; ++i)
+        if (b0 + i < n_blk) mine += hist[static_cast<size_t>(b0 + i) * MAX_BINS + warp];
+    }
+  }
   uint32_t inc = mine;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -115,16 +129,29 @@ __global__ void __launch_bounds__(1024) class_scan_kernel(uint32_t* hist, int n_
   // in place: hist[blk][c] -> sorted position of the first pixel of class c in chunk blk
   if (warp <= C) {
     uint32_t run = start[warp] + inc - mine;
-    for (int i = 0; i < per; ++i)
-      if (b0 + i < n_blk) {
-        const size_t idx = static_cast<size_t>(b0 + i) * MAX_BINS + warp;
-        const uint32_t v = hist[idx];
-        hist[idx] = run;
-        run += v;
-      }
+    if (keep) {
+#pragma unroll
+      for (int i = 0; i < SCAN_KEEP; ++i)
+        if (i < per && b0 + i < n_blk) {
+          hist[static_cast<size_t>(b0 + i) * MAX_BINS + warp] = run;
+          run += kept[i];
+        }
+    } else {
+      for (int i = 0; i < per; ++i)
+        if (b0 + i < n_blk) {
+          const size_t idx = static_cast<size_t>(b0 + i) * MAX_BINS + warp;
+          const uint32_t v = hist[idx];
+          hist[idx] = run;
+          run += v;
+        }
+    }
   }
-  // tile class unions
+  // tile class unions (also kept in shared memory for the numbering below when they fit: the plan bodies read every
+  // tile's set twice)
+  constexpr int SCAN_TOR_SM = 4096;
+  __shared__ uint32_t tor_sm[SCAN_TOR_SM];
   const long long n_tiles = rows_pad / 128;
+  const bool tor_in_sm = n_tiles <= SCAN_TOR_SM;
   for (long long tile = threadIdx.x; tile < n_tiles; tile += blockDim.x) {
     const long long r0 = tile * 128, r1 = r0 + 128;
     uint32_t u = 0;
@@ -132,16 +159,18 @@ __global__ void __launch_bounds__(1024) class_scan_kernel(uint32_t* hist, int n_
       if (static_cast<long long>(start[c]) < r1 && static_cast<long long>(start[c + 1]) > r0) u |= 1u << c;
     if (r1 > static_cast<long long>(start[C])) u |= 0x80000000u;
     tor[tile] = u;
+    if (tor_in_sm) tor_sm[tile] = u;
   }
+  const uint32_t* tor_rd = tor_in_sm ? tor_sm : tor;
   // rows and columns are the same pixels (single GPU): number the live (row tile, column tile)
   // units here instead of in a launch of their own
   if (unit_off != nullptr) {
     __syncthreads();
-    pair_plan_body<1>(tor, static_cast<int>(n_tiles), tor, static_cast<int>(n_tiles), unit_off);
+    pair_plan_body<1>(tor_rd, static_cast<int>(n_tiles), tor_rd, static_cast<int>(n_tiles), unit_off);
   }
   if (unit_off_sym != nullptr) {   // and the units with column tile >= row tile for the symmetric row-sum pass
     __syncthreads();
-    pair_plan_sym_body(tor, static_cast<int>(n_tiles), unit_off_sym);
+    pair_plan_sym_body(tor_rd, static_cast<int>(n_tiles), unit_off_sym);
   }
 }
 
