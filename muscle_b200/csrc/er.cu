@@ -101,8 +101,13 @@ __global__ void __launch_bounds__(ER_THREADS) er_hist_kernel(const float* __rest
     }
 #pragma unroll
     for (int c = 0; c < ER_C; ++c) {
+      // a channel whose label is off is exactly 0 on both sides (softmaxnorm_masked multiplies by the label): nothing to
+      // count, and skipping it -- a block-uniform branch, one image per blockIdx.y -- skips its match.any / redux, which
+      // is what this kernel spends its time on (typically 2-4 of the 21 channels are on)
+      if (c > 0 && lab_sm[c - 1] == 0.f) continue;
       const unsigned int u = in ? fixed_of(fabsf(a[c] - q[c])) : 0u;
       const bool take = u != 0u && prefix_ok(u, prefix, level);
+      if (!__any_sync(0xffffffffu, take)) continue;      // levels 1 and 2: almost no warp holds a value with the chosen prefix
       const unsigned int dg = take ? digit_of(u, level) : 0xffffffffu;
       const unsigned int peers = __match_any_sync(0xffffffffu, dg);
       if (take) {
@@ -142,24 +147,66 @@ __global__ void __launch_bounds__(256) er_pick_kernel(const float* __restrict__ 
     k_sh = sel[b].k;
   }
   __syncthreads();
-  if (threadIdx.x == 0 && !sel[b].done) {
-    ErSel s = sel[b];
+  // Walk from the top bin down until `need` values are covered -- as a block-wide scan: thread t owns the eight bins
+  // r = 8t .. 8t+7 counted from the top (r = nb - 1 - i), an exclusive scan over the threads gives the count and the
+  // fixed-point sum above its run, and the one thread whose run crosses `need` finishes the walk inside its eight bins.
+  // (One thread walking up to 2 048 bins of global memory took 212 us per level: a third of the whole ER loss.)
+  __shared__ unsigned int cnt_w[8];
+  __shared__ unsigned long long sum_w[8];
+  __shared__ int found_sh;
+  if (threadIdx.x == 0) found_sh = 0;
+  const bool active = !sel[b].done;            // uniform: every thread reads the same word
+  if (active) {
     const unsigned int* h = hist + static_cast<size_t>(b) * ER_BINS;
     const unsigned long long* hs = hsum + static_cast<size_t>(b) * ER_BINS;
-    unsigned long long need = (level == 0) ? s.k : s.need;
     const int nb = (level == 2) ? 1024 : ER_BINS;
-    int chosen = -1;
-    for (int i = nb - 1; i >= 0; --i) {
-      const unsigned int c = h[i];
-      if (c == 0u) continue;
-      if (c >= need) { chosen = i; break; }
-      need -= c;
-      s.cnt_above += c;
-      s.sum_above += hs[i];
+    const int per = nb / 256;                  // 8 or 4 bins per thread
+    unsigned int c_loc[8];
+    unsigned long long s_loc[8];
+    unsigned int c_tot = 0u;
+    unsigned long long s_tot = 0ull;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int i = nb - 1 - (static_cast<int>(threadIdx.x) * per + q);
+      const bool in = q < per;
+      c_loc[q] = in ? h[i] : 0u;
+      s_loc[q] = in ? hs[i] : 0ull;
+      c_tot += c_loc[q];
+      s_tot += s_loc[q];
     }
-    if (chosen < 0) {                          // fewer non-zero values than k: every one of them is taken, the rest are zeros
-      s.done = 1u; s.tie_weight = 0.f;
-    } else {
+    // exclusive scan over the 256 threads (top run first)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned int c_inc = c_tot;
+    unsigned long long s_inc = s_tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned int cu = __shfl_up_sync(0xffffffffu, c_inc, o);
+      const unsigned long long su = __shfl_up_sync(0xffffffffu, s_inc, o);
+      if (lane >= o) { c_inc += cu; s_inc += su; }
+    }
+    if (lane == 31) { cnt_w[warp] = c_inc; sum_w[warp] = s_inc; }
+    __syncthreads();
+    unsigned long long c_before = 0ull, s_before = 0ull;     // (counts of a whole image can exceed 32 bits only in theory: 64-bit anyway)
+    for (int w = 0; w < warp; ++w) { c_before += cnt_w[w]; s_before += sum_w[w]; }
+    c_before += c_inc - c_tot;
+    s_before += s_inc - s_tot;
+    ErSel s = sel[b];
+    const unsigned long long need0 = (level == 0) ? s.k : s.need;
+    if (c_before < need0 && c_before + c_tot >= need0) {     // this thread's run holds the bin that completes `need`
+      unsigned long long need = need0 - c_before;
+      s.cnt_above += c_before;
+      s.sum_above += s_before;
+      int chosen = -1;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        if (chosen >= 0 || q >= per) continue;
+        const unsigned int c = c_loc[q];
+        if (c == 0u) continue;
+        if (c >= need) { chosen = nb - 1 - (static_cast<int>(threadIdx.x) * per + q); continue; }
+        need -= c;
+        s.cnt_above += c;
+        s.sum_above += s_loc[q];
+      }
       s.prefix |= (level == 0) ? (static_cast<unsigned int>(chosen) << 21)
                                : (level == 1 ? (static_cast<unsigned int>(chosen) << 10) : static_cast<unsigned int>(chosen));
       s.need = static_cast<unsigned int>(need);
@@ -168,8 +215,19 @@ __global__ void __launch_bounds__(256) er_pick_kernel(const float* __restrict__ 
         s.tie_weight = static_cast<float>(static_cast<double>(need) / static_cast<double>(ties));
         s.sum_above += need * static_cast<unsigned long long>(s.prefix);
       }
+      sel[b] = s;
+      found_sh = 1;
     }
-    sel[b] = s;
+    __syncthreads();
+    if (threadIdx.x == 0 && !found_sh) {       // fewer non-zero values than k: every one of them is taken, the rest are zeros
+      unsigned long long c_all = 0ull, s_all = 0ull;
+      for (int w = 0; w < 8; ++w) { c_all += cnt_w[w]; s_all += sum_w[w]; }
+      s.cnt_above += c_all;
+      s.sum_above += s_all;
+      s.done = 1u;
+      s.tie_weight = 0.f;
+      sel[b] = s;
+    }
   }
   // clear the image's histogram for the next level
   __syncthreads();
@@ -248,20 +306,37 @@ __global__ void __launch_bounds__(ER_THREADS) er_bwd_kernel(const float* __restr
 
 // ---------------------------------------------------------------------------------------------------------------
 // bilinear up/down-sampling, align_corners=True (F.interpolate as called at src/MuSCLe.py:256-257, :285)
-__global__ void __launch_bounds__(256) upsample_fwd_kernel(const float* __restrict__ x, long long planes, int h, int w, int H,
-                                                           int W, float sy, float sx, float* __restrict__ y) {
-  const long long total = planes * H * W;
-  for (long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * 256) {
-    const int ox = static_cast<int>(i % W);
-    const long long r = i / W;
-    const int oy = static_cast<int>(r % H);
-    const long long pl = r / H;
-    const Tap ty = tap_of(oy, sy, h), tx = tap_of(ox, sx, w);
-    const float* src = x + pl * h * w;
-    const float v00 = __ldg(src + ty.i0 * w + tx.i0), v01 = __ldg(src + ty.i0 * w + tx.i1);
-    const float v10 = __ldg(src + ty.i1 * w + tx.i0), v11 = __ldg(src + ty.i1 * w + tx.i1);
-    y[i] = ty.w0 * (tx.w0 * v00 + tx.w1 * v01) + ty.w1 * (tx.w0 * v10 + tx.w1 * v11);
+// Block = one output row (blockIdx.x = plane * H + oy) x a 512-pixel stretch of it, four consecutive outputs per thread:
+// the row's two source rows and y taps are fixed per block, and the stores are 16-byte vectors.  (One output per thread
+// on a flat index spent its time on three 64-bit divisions per element: 148 us for a 135 MB map.)
+constexpr int UP_THREADS = 128;
+__global__ void __launch_bounds__(UP_THREADS) upsample_fwd_kernel(const float* __restrict__ x, long long planes, int h, int w, int H,
+                                                                  int W, float sy, float sx, float* __restrict__ y) {
+  const long long row = blockIdx.x;
+  const long long pl = row / H;
+  const int oy = static_cast<int>(row - pl * H);
+  const Tap ty = tap_of(oy, sy, h);
+  const float* r0 = x + pl * h * w + static_cast<long long>(ty.i0) * w;
+  const float* r1 = x + pl * h * w + static_cast<long long>(ty.i1) * w;
+  float* dst = y + row * W;
+  const bool vec = (W & 3) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0;
+  for (int ox0 = (blockIdx.y * UP_THREADS + threadIdx.x) * 4; ox0 < W; ox0 += gridDim.y * UP_THREADS * 4) {
+    float o[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int ox = ox0 + q < W ? ox0 + q : W - 1;
+      const Tap tx = tap_of(ox, sx, w);
+      const float v00 = __ldg(r0 + tx.i0), v01 = __ldg(r0 + tx.i1);
+      const float v10 = __ldg(r1 + tx.i0), v11 = __ldg(r1 + tx.i1);
+      o[q] = ty.w0 * (tx.w0 * v00 + tx.w1 * v01) + ty.w1 * (tx.w0 * v10 + tx.w1 * v11);
+    }
+    if (vec) {
+      *reinterpret_cast<float4*>(dst + ox0) = make_float4(o[0], o[1], o[2], o[3]);
+    } else {
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (ox0 + q < W) dst[ox0 + q] = o[q];
+    }
   }
 }
 
@@ -342,7 +417,10 @@ int muscle_upsample_bilinear_fwd(const float* x, int64_t planes, int height, int
   if (!x || !y) return fail(MUSCLE_ERR_BAD_ARG, "null pointer argument");
   if (planes <= 0 || height <= 0 || width <= 0 || out_height <= 0 || out_width <= 0) return fail(MUSCLE_ERR_BAD_ARG, "empty input");
   const long long total = planes * out_height * out_width;
-  upsample_fwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+  const long long rows = planes * out_height;
+  if (rows >= (1ll << 31)) return fail(MUSCLE_ERR_BAD_ARG, "too many output rows");
+  const unsigned gy = static_cast<unsigned>((out_width + UP_THREADS * 4 - 1) / (UP_THREADS * 4));
+  upsample_fwd_kernel<<<dim3(static_cast<unsigned>(rows), gy), UP_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
       x, planes, height, width, out_height, out_width, scale_of(height, out_height), scale_of(width, out_width), y);
   MB_LAUNCH_CHECK();
   return MUSCLE_OK;
