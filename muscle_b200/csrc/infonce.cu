@@ -306,6 +306,9 @@ int prepare_impl(const float* x, int layout, int64_t batch, int64_t pixels_per_i
   p.x = x; p.cls = cls; p.cls64 = cls_is_int64; p.layout = layout; p.n = n;
   p.ppi = pixels_per_image; p.C = num_classes; p.eps = eps; p.chunk_off = hist;
   p.ehat = static_cast<__nv_bfloat16*>(ehat); p.bits = bits; p.inv_norm = inv_norm; p.perm = perm;
+  // NCHW input: the class sums come out of prepare_nchw_kernel itself (one launch and one pass over ehat less)
+  const bool fold_class_sum = layout == MUSCLE_LAYOUT_NCHW && proto_in == nullptr;
+  p.class_sum = fold_class_sum ? class_sum : nullptr;
   const size_t smem = (layout == MUSCLE_LAYOUT_NCHW)
                           ? static_cast<size_t>(SORT_CHUNK) * (dim / 2 + 1) * sizeof(uint32_t) : 0;
   const int n_tiles = static_cast<int>(rows_pad / 128);
@@ -321,7 +324,7 @@ int prepare_impl(const float* x, int layout, int64_t batch, int64_t pixels_per_i
     if (proto_in != nullptr)                                                                      \
       MB_CUDA(launch_pdl(proto_to_sum_kernel, dim3((num_classes * DD + 255) / 256), dim3(256), 0, stream, proto_in, \
                          static_cast<const float*>(class_mass), num_classes, DD, class_sum));     \
-    else                                                                                          \
+    else if (!fold_class_sum)                                                                     \
       MB_CUDA(launch_pdl(class_sum_kernel<DD>, dim3(n_tiles * (128 / SEG_ROWS)), dim3(SEG_THREADS), 0, stream, \
                          static_cast<const __nv_bfloat16*>(p.ehat), static_cast<const uint32_t*>(seg), num_classes, class_sum)); \
   }

@@ -189,6 +189,8 @@ struct PrepareParams {
   uint32_t* bits;             // [rows_pad]     sorted
   float* inv_norm;            // [rows_pad]     sorted
   int* perm;                  // [n]            source pixel -> sorted row
+  float* class_sum;           // [C][D] zeroed, or null: prepare_nchw_kernel adds its block's per-class sums of the
+                              // bf16-rounded rows (the job of class_sum_kernel, without the extra launch and pass over ehat)
 };
 
 // One block = 128 consecutive source pixels, one warp = 32 of them.  The sorted position of a
@@ -293,6 +295,7 @@ __global__ void __launch_bounds__(PREP_THREADS) prepare_nchw_kernel(const Prepar
   __shared__ uint32_t warp_hist[SORT_WARPS][MAX_BINS];
   __shared__ float ss_sm[4][SORT_CHUNK];
   __shared__ int dest_sm[SORT_CHUNK];
+  __shared__ int cls_sm[SORT_CHUNK];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int pg = warp & 3, cq = warp >> 2;
   for (int i = threadIdx.x; i < SORT_WARPS * MAX_BINS; i += PREP_THREADS) (&warp_hist[0][0])[i] = 0u;
@@ -344,6 +347,37 @@ __global__ void __launch_bounds__(PREP_THREADS) prepare_nchw_kernel(const Prepar
     uint32_t* out = reinterpret_cast<uint32_t*>(p.ehat + static_cast<size_t>(dest_sm[r]) * D);
 #pragma unroll
     for (int k = 0; k < WPR; ++k) out[lane + 32 * k] = trow[lane + 32 * k];
+  }
+  // per-class column sums of this block's (bf16-rounded) rows: thread = (bf16-pair column, slice of the 128 rows); a
+  // chunk of 128 consecutive pixels holds two or three classes on blob-like maps, so this is a few dozen shared loads
+  if (p.class_sum != nullptr) {
+    constexpr int NCOL = D / 2, NSL = PREP_THREADS / NCOL, RPS = SORT_CHUNK / NSL;
+    __shared__ float2 csum_sm[PREP_THREADS];
+    if (cq == 0) cls_sm[px] = live ? c : MAX_BINS;
+    __syncthreads();
+    const int col = threadIdx.x % NCOL, sl = threadIdx.x / NCOL;
+    for (int cc = 0; cc < p.C; ++cc) {
+      if (warp_hist[0][cc] + warp_hist[1][cc] + warp_hist[2][cc] + warp_hist[3][cc] == 0u) continue;   // block-uniform
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll 4
+      for (int r = sl * RPS; r < (sl + 1) * RPS; ++r)
+        if (cls_sm[r] == cc) {
+          const uint32_t wv = smem_u[r * ROW_W + col];
+          a0 += __uint_as_float(wv << 16);
+          a1 += __uint_as_float(wv & 0xffff0000u);
+        }
+      csum_sm[threadIdx.x] = make_float2(a0, a1);
+      __syncthreads();
+      if (threadIdx.x < NCOL) {
+        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+        for (int k = 0; k < NSL; ++k) { const float2 t = csum_sm[k * NCOL + threadIdx.x]; s0 += t.x; s1 += t.y; }
+        float* dst = p.class_sum + static_cast<size_t>(cc) * D + 2 * threadIdx.x;
+        if (s0 != 0.f) atomicAdd(dst, s0);
+        if (s1 != 0.f) atomicAdd(dst + 1, s1);
+      }
+      __syncthreads();
+    }
   }
 }
 
