@@ -40,6 +40,26 @@ def gen_info_nce(src):
     return out
 
 
+def gen_info_nce_anynorm(src):
+    """The reference primitive on rows that are NOT unit-norm (it never normalises, src/loss_multilabel.py:9-21), with
+    reduction='none' and an upstream gradient per row."""
+    out = {}
+    for dt, tag in ((torch.float32, "f32"), (torch.float64, "f64")):
+        g = torch.Generator().manual_seed(29)
+        d = 48
+        q = (torch.randn(200, d, generator=g, dtype=dt) * (0.3 + torch.rand(200, 1, generator=g, dtype=dt)) / d ** 0.5).requires_grad_()
+        p = ((q[:1].detach() + 0.4 * torch.randn(9, d, generator=g, dtype=dt) / d ** 0.5) * 0.8).requires_grad_()
+        k = (torch.randn(333, d, generator=g, dtype=dt) * (0.2 + 1.1 * torch.rand(333, 1, generator=g, dtype=dt)) / d ** 0.5).requires_grad_()
+        up = torch.randn(200, generator=g, dtype=dt)
+        loss = src.loss_multilabel.info_nce(q, p, k, temperature=0.3)
+        gq, gp, gk = torch.autograd.grad(loss, (q, p, k))
+        rows = src.loss_multilabel.info_nce(q, p, k, temperature=0.3, reduction="none")
+        nq, np_, nk = torch.autograd.grad((rows * up).sum(), (q, p, k))
+        out[tag] = dict(q=q.detach(), p=p.detach(), k=k.detach(), up=up, loss=loss.detach(), gq=gq, gp=gp, gk=gk,
+                        rows=rows.detach(), nq=nq, np=np_, nk=nk)
+    return out
+
+
 def gen_dense_infonce(src):
     """The composition of SURVEY §8c evaluated with the reference primitive only."""
     out = {}
@@ -424,7 +444,7 @@ def gen_irn(src):
 def main():
     src = reference_loader.load()
     os.makedirs(OUT, exist_ok=True)
-    jobs = dict(info_nce=gen_info_nce, dense_infonce=gen_dense_infonce, imc=gen_imc, pixpro=gen_pixpro,
+    jobs = dict(info_nce=gen_info_nce, info_nce_anynorm=gen_info_nce_anynorm, dense_infonce=gen_dense_infonce, imc=gen_imc, pixpro=gen_pixpro,
                 emd=gen_emd, emd_static=gen_emd_static, heads=gen_heads, fieldloss=gen_fieldloss,
                 fieldloss_sobel3=gen_fieldloss_sobel3, cam_norms=gen_cam_norms,
                 er_loss=gen_er_loss, cls_losses=gen_cls_losses, decoder_tail=gen_decoder_tail, irn=gen_irn)

@@ -92,3 +92,24 @@ def test_info_nce_reduction_none_backward(unit):
     for a, b in ((qg, qr), (pg, pr), (kg, kr)):
         assert _cos(a.grad.cpu(), b.grad) >= 0.999
         assert abs(a.grad.norm().item() / b.grad.norm().item() - 1) < 2e-2
+
+
+def test_info_nce_any_norm_reference_fixture(golden):
+    """rows of any norm and the backward of reduction='none' against outputs of the reference itself
+    (tests/golden/info_nce_anynorm.pt, minted by oracle/make_golden.py from src/loss_multilabel.py:9-21)"""
+    from muscle_b200.loss_multilabel import info_nce
+    g = golden("info_nce_anynorm")["f32"]
+    q, p, k = (g[n].cuda().requires_grad_() for n in "qpk")
+    loss = info_nce(q, p, k, temperature=0.3)
+    loss.backward()
+    assert abs(loss.item() - g["loss"].item()) <= 1e-3 * abs(g["loss"].item())
+    for name, t in (("gq", q), ("gp", p), ("gk", k)):
+        assert _cos(t.grad.cpu(), g[name]) >= 0.999, name
+        assert abs(t.grad.norm().item() / g[name].norm().item() - 1) < 2e-2, name
+    q2, p2, k2 = (g[n].cuda().requires_grad_() for n in "qpk")
+    rows = info_nce(q2, p2, k2, temperature=0.3, reduction="none")
+    torch.testing.assert_close(rows.cpu(), g["rows"], rtol=5e-3, atol=5e-3)
+    (rows * g["up"].cuda()).sum().backward()
+    for name, t in (("nq", q2), ("np", p2), ("nk", k2)):
+        assert _cos(t.grad.cpu(), g[name]) >= 0.999, name
+        assert abs(t.grad.norm().item() / g[name].norm().item() - 1) < 2e-2, name

@@ -29,6 +29,22 @@ def test_info_nce(golden, tag):
 
 
 @pytest.mark.parametrize("tag", ["f32", "f64"])
+def test_info_nce_rows_of_any_norm(golden, tag):
+    """the primitive never normalises: rows of any length, reduction='none' with an upstream gradient per row"""
+    g = golden("info_nce_anynorm")[tag]
+    q, p, k = (g[n].clone().requires_grad_() for n in "qpk")
+    tol = dict(rtol=2e-5, atol=1e-6) if tag == "f32" else dict(rtol=1e-11, atol=1e-12)
+    loss = O.info_nce(q, p, k, temperature=0.3)
+    for got, want in zip(torch.autograd.grad(loss, (q, p, k)), (g["gq"], g["gp"], g["gk"])):
+        close(got, want, **tol)
+    close(loss, g["loss"], **tol)
+    rows = O.info_nce(q, p, k, temperature=0.3, reduction="none")
+    close(rows, g["rows"], **tol)
+    for got, want in zip(torch.autograd.grad((rows * g["up"]).sum(), (q, p, k)), (g["nq"], g["np"], g["nk"])):
+        close(got, want, **tol)
+
+
+@pytest.mark.parametrize("tag", ["f32", "f64"])
 def test_dense_infonce_composition(golden, tag):
     g = golden("dense_infonce")[tag]
     x = g["x"].clone().requires_grad_()
